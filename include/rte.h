@@ -1,0 +1,263 @@
+/*
+ * rte.h — C ABI of the B200-native render path (librte_b200.so).
+ *
+ * The reference (Sorax5/RaytracingEngine, "RE/" = RaytracingEngine/) has no FFI: its de-facto
+ * boundary is the public C++ API of `Scene` plus the free functions of RaytracingEngine.cpp and
+ * Image.cpp.  Each entry point below names the reference interface it replaces (file:line).
+ * The C++20 host mirror (include/rte/engine.hpp) and the Python binding
+ * (raytracingengine_b200/binding.py) are thin layers over exactly these symbols.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++/torch types cross this boundary;
+ *   - every function returns 0 on success, a negative rte_status otherwise; the message is
+ *     available from rte_last_error() (the C++ wrapper rethrows it as std::runtime_error, which
+ *     is the reference's error convention, RE/RaytracingEngine.cpp:38, RE/Image.cpp:15,27);
+ *   - one rte_ctx per GPU, externally synchronised; all work is enqueued on the ctx stream;
+ *   - image layout: row-major, idx = y*W + x, row 0 = top (RE/Scene.h:214-216,321-324);
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef RTE_H_
+#define RTE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTE_VERSION 1
+
+typedef enum rte_status {
+    RTE_OK = 0,
+    RTE_ERR_INVALID = -1,   /* bad argument / inconsistent description */
+    RTE_ERR_CUDA = -2,      /* CUDA runtime error (sticky for the ctx) */
+    RTE_ERR_NO_DEVICE = -3, /* no usable CUDA device: there is no CPU path */
+    RTE_ERR_IO = -4,        /* file open / write failure (RE/Image.cpp:14-16,26-28) */
+    RTE_ERR_LIMIT = -5      /* scene exceeds a documented capacity */
+} rte_status;
+
+/* HitType, RE/Shape.h:21-26 */
+enum { RTE_HIT_NONE = 0, RTE_HIT_SPHERE = 1, RTE_HIT_PLANE = 2, RTE_HIT_TRIANGLE = 3 };
+
+/* Tonemap operators in tonemapAll order, RE/RaytracingEngine.cpp:205-211,303-311 */
+enum {
+    RTE_TM_SIMPLE = 0,
+    RTE_TM_REINHARD_SIMPLE = 1,
+    RTE_TM_REINHARD_EXTENDED = 2,
+    RTE_TM_REINHARD_EXTENDED_LUMINANCE = 3,
+    RTE_TM_REINHARD_JODIE = 4,
+    RTE_TM_UNCHARTED2 = 5,
+    RTE_TM_ACES = 6,
+    RTE_TM_COUNT = 7,
+    RTE_TM_NONE = -1
+};
+
+/* ------------------------------------------------------------------------------------------
+ * Scene description (host side, FP64 exactly like the reference's structs).
+ * ---------------------------------------------------------------------------------------- */
+
+/* Material, RE/Shape.h:13-19 (same field order, 56 bytes) */
+typedef struct rte_material {
+    double color[3];
+    double shininess;        /* default 128 */
+    double specular;         /* default 0 */
+    double transparency;     /* default 0 */
+    double refractive_index; /* default 1 */
+} rte_material;
+
+/* Sphere(r, pos, mat), RE/Shape.h:59-70 */
+typedef struct rte_sphere {
+    double center[3];
+    double radius;
+    int32_t material; /* index into rte_scene_desc.materials */
+    int32_t reserved;
+} rte_sphere;
+
+/* Plane(pos, norm, mat), RE/Shape.h:135-147 — `normal` is given un-normalised, the library
+ * normalises it in FP64 exactly like the constructor does (RE/Shape.h:142). */
+typedef struct rte_plane {
+    double point[3];
+    double normal[3];
+    int32_t material;
+    int32_t reserved;
+} rte_plane;
+
+/* Triangle(v0,v1,v2,mat,transform), RE/Shape.h:188-200 — only transform.position is ever
+ * applied by the reference (tv0..tv2); rotation/scale are ignored there and absent here. */
+typedef struct rte_triangle {
+    double v0[3], v1[3], v2[3];
+    double translate[3];
+    int32_t material;
+    int32_t reserved;
+} rte_triangle;
+
+/* Model(indices, transform, material, vertexPositions), RE/Shape.h:248-256.
+ * Vertex positions and indices of all models live in two shared arrays of the scene. */
+typedef struct rte_model {
+    int64_t first_vertex; /* offset (in vertices) into model_vertices */
+    int64_t vertex_count;
+    int64_t first_index;  /* offset into model_indices; indices are relative to first_vertex */
+    int64_t index_count;  /* multiple of 3 */
+    double translate[3];
+    int32_t material;
+    int32_t reserved;
+} rte_model;
+
+/* Light{position,color,intensity}, RE/Light.h:6-12 */
+typedef struct rte_light {
+    double position[3];
+    double color[3];
+    double intensity;
+} rte_light;
+
+/* Camera(position, focal, width, height, near, far), RE/Math.h:85-97 */
+typedef struct rte_camera {
+    double position[3];
+    double focal;
+    uint64_t width, height;
+    double near_plane, far_plane;
+    int32_t anti_aliasing; /* RE/Math.h:94; only 1 is deterministic */
+    int32_t reserved;
+} rte_camera;
+
+/* The vectors a reference `Scene` owns (RE/Scene.h:17-23), flattened. */
+typedef struct rte_scene_desc {
+    const rte_material* materials; int64_t n_materials;
+    const rte_sphere* spheres;     int64_t n_spheres;
+    const rte_plane* planes;       int64_t n_planes;
+    const rte_triangle* triangles; int64_t n_triangles;
+    const rte_model* models;       int64_t n_models;
+    const double* model_vertices;  int64_t n_model_vertices; /* xyz triples */
+    const int32_t* model_indices;  int64_t n_model_indices;
+    const rte_light* lights;       int64_t n_lights;
+} rte_scene_desc;
+
+/* ------------------------------------------------------------------------------------------
+ * Render options / outputs
+ * ---------------------------------------------------------------------------------------- */
+
+typedef struct rte_render_opts {
+    int32_t row0, row1;     /* render rows [row0,row1) of the camera image (row band of one GPU);
+                               row1 <= 0 means camera.height */
+    int32_t max_depth;      /* Scene::maxRecursion, RE/Scene.h:24; <= 0 means 10 */
+    int32_t tonemap_op;     /* RTE_TM_* fused into the render pass (RGB8 output), or RTE_TM_NONE */
+    double bias;            /* RE/Scene.h:291; <= 0 means 1e-3 */
+    double max_white;       /* reinhardExtended*(…, max_white); <= 0 means 5.0 (RE/RaytracingEngine.cpp:193,195) */
+    double jodie_a;         /* reinhardJodie(…, a); <= 0 means 0.18 (RE/RaytracingEngine.cpp:150) */
+    int32_t spp_seed;       /* counter-based jitter seed when camera.anti_aliasing > 1 */
+    int32_t reserved;
+} rte_render_opts;
+
+/* Output buffers of one render call.  Every pointer is optional (NULL = not wanted) and is a
+ * DEVICE pointer for rte_render() and a HOST pointer for rte_render_host().  Each buffer holds
+ * (row1-row0)*W elements in band-local row-major order. */
+typedef struct rte_frame {
+    float* hdr;          /* float4 per pixel: linear RGB, w = 0 (RenderImage() result, RE/Scene.h:311) */
+    double* hdr64;       /* 3 doubles per pixel, the same values before rounding to FP32 */
+    uint8_t* rgb8;       /* 3 bytes per pixel, opts.tonemap_op applied + toColor (RE/RaytracingEngine.cpp:113-121) */
+    /* AOVs of the primary hit (the remnants of the reference's depth/normal/colour maps,
+     * RE/Scene.h:278-281, RE/Shape.h:40-42; miss values documented in DESIGN.md) */
+    uint32_t* prim_id;   /* (type << 30) | index, 0xFFFFFFFF on miss (HitInfo.type/.index, RE/Shape.h:29-31) */
+    float* depth;        /* HitInfo.distance, +inf on miss */
+    double* depth64;     /* the same in FP64 */
+    float* normal;       /* float4: HitInfo.normal (geometric, un-flipped), 0 on miss */
+    float* albedo;       /* float4: HitInfo.material.color, sky colour on miss */
+    uint32_t* light_mask;/* bit j: light j contributes at the primary hit (transmittance > bias);
+                            bit 16+j: a shadow ray was cast to light j (guards RE/Scene.h:89-101) */
+} rte_frame;
+
+/* Counters accumulated by the render kernels of the last rte_render*() call. */
+typedef struct rte_stats {
+    uint64_t primary_rays;
+    uint64_t shadow_rays;      /* pixel-light pairs passing the guards at RE/Scene.h:89-101 */
+    uint64_t secondary_rays;   /* reflection rays that were intersected (depth >= 1) */
+    uint64_t sphere_tests;     /* algorithmic test counts: closest-hit rays test */
+    uint64_t plane_tests;      /*   every primitive, shadow rays count canonical-order tests up  */
+    uint64_t triangle_tests;   /*   to and including the first occluder                           */
+    uint64_t exact_marches;    /* shadow rays resolved by the exact RE/Scene.h:35-77 march */
+    uint64_t fp64_confirms;    /* FP64 re-evaluations triggered by the FP32 filter */
+    double kernel_ms;          /* device time of the render kernel (CUDA events on the ctx stream) */
+    double tonemap_ms;         /* device time of the last tonemap kernel */
+} rte_stats;
+
+typedef struct rte_ctx rte_ctx;
+
+/* Hit record of one ray query: HitInfo, RE/Shape.h:28-34 (material by index). */
+typedef struct rte_hit {
+    double distance;
+    double normal[3];
+    double point[3];
+    uint32_t prim_id; /* as rte_frame.prim_id */
+    int32_t material;
+} rte_hit;
+
+/* ------------------------------------------------------------------------------------------
+ * Entry points
+ * ---------------------------------------------------------------------------------------- */
+
+/* Library/ABI version and availability (no device needed). */
+int rte_version(void);
+int rte_device_count(void);
+/* Message of the last failure on this ctx (or, with ctx == NULL, of the calling thread). */
+const char* rte_last_error(const rte_ctx* ctx);
+
+/* One context per GPU.  Fails with RTE_ERR_NO_DEVICE when no sm_100 device is visible. */
+int rte_create(int device, rte_ctx** out);
+void rte_destroy(rte_ctx* ctx);
+/* Use an externally owned cudaStream_t (e.g. torch's current stream); NULL = ctx-private stream. */
+int rte_set_stream(rte_ctx* ctx, void* cuda_stream);
+int rte_synchronize(rte_ctx* ctx);
+
+/* Replaces Scene::Add{Sphere,Plane,Light,Triangle,Model} (RE/Scene.h:208-212) + the implicit
+ * "scene is ready" of RenderImage: validates, flattens models into triangles in canonical
+ * order, packs FP32 SoA filter arrays + FP64 exact arrays and copies them to the device.
+ * The description is copied; the caller keeps ownership of its arrays. */
+int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* scene);
+/* explicit Scene(const Camera&), RE/Scene.h:200 */
+int rte_set_camera(rte_ctx* ctx, const rte_camera* camera);
+
+/* Scene::RenderImage(), RE/Scene.h:311-328 (+ fused tonemap()/toColor, RE/RaytracingEngine.cpp:165-174).
+ * `frame` holds device pointers. Asynchronous on the ctx stream. */
+int rte_render(rte_ctx* ctx, const rte_render_opts* opts, const rte_frame* frame);
+/* Same with host buffers: device staging + D2H copies inside the call, synchronous.  This is the
+ * call the end-to-end number is measured through. */
+int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const rte_frame* host_frame);
+int rte_get_stats(rte_ctx* ctx, rte_stats* out);
+
+/* tonemap() / tonemapAll(), RE/RaytracingEngine.cpp:165-214: `hdr` = float4 per pixel (device),
+ * rgb8[op] = 3 bytes per pixel (device) for every op whose bit is set in op_mask. */
+int rte_tonemap(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t op_mask,
+                double max_white, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]);
+int rte_tonemap_host(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t op_mask,
+                     double max_white, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]);
+/* Max of luminance() (RE/RaytracingEngine.cpp:100-104) over a device HDR buffer; the per-rank
+ * value that an auto-max-white run all-reduces (MAX) across GPUs. Result on the host. */
+int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max);
+
+/* Scene::IntersectClosest(ray), RE/Scene.h:218-257, for a batch of rays (host arrays:
+ * origins/directions = xyz triples).  hits[i].prim_id == 0xFFFFFFFF means std::nullopt. */
+int rte_intersect_closest(rte_ctx* ctx, int64_t n_rays, const double* origins,
+                          const double* directions, rte_hit* hits);
+/* Scene::IntersectAnyBefore(ray, maxDist), RE/Scene.h:259-276: out[i] = 1 if any primitive
+ * reports 0 < t < max_dist[i]. */
+int rte_intersect_any_before(rte_ctx* ctx, int64_t n_rays, const double* origins,
+                             const double* directions, const double* max_dist, uint8_t* out);
+
+/* Device memory helpers for callers without their own allocator. */
+int rte_malloc(rte_ctx* ctx, size_t bytes, void** out_dev);
+int rte_free(rte_ctx* ctx, void* dev);
+int rte_memcpy_d2h(rte_ctx* ctx, void* host, const void* dev, size_t bytes);
+int rte_memcpy_h2d(rte_ctx* ctx, void* dev, const void* host, size_t bytes);
+/* Pinned host memory (used for the RGB8 staging buffer of writePPM). */
+int rte_malloc_host(size_t bytes, void** out_host);
+int rte_free_host(void* host);
+
+/* writePPM(filename, pixels, width, height), RE/Image.cpp:11-31: "P6\n<W> <H>\n255\n" + RGB
+ * bytes, one fwrite from the (pinned) host buffer. Needs no device. */
+int rte_write_ppm(const char* filename, const uint8_t* rgb8, uint64_t width, uint64_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTE_H_ */
