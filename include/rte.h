@@ -146,8 +146,13 @@ typedef struct rte_render_opts {
     double max_white;       /* reinhardExtended*(…, max_white); <= 0 means 5.0 (RE/RaytracingEngine.cpp:193,195) */
     double jodie_a;         /* reinhardJodie(…, a); <= 0 means 0.18 (RE/RaytracingEngine.cpp:150) */
     int32_t spp_seed;       /* counter-based jitter seed when camera.anti_aliasing > 1 */
-    int32_t reserved;
+    int32_t flags;          /* RTE_FLAG_* (validation switches; 0 = production path) */
 } rte_render_opts;
+
+/* Validation switches for rte_render_opts.flags.  Both must leave every output bit-identical:
+ *   EXACT_SHADOWS  every shadow ray takes the literal RE/Scene.h:35-77 march instead of the any-hit query;
+ *   NO_FILTER      the FP32 filters accept everything, i.e. every primitive is tested in FP64. */
+enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2 };
 
 /* Output buffers of one render call.  Every pointer is optional (NULL = not wanted) and is a
  * DEVICE pointer for rte_render() and a HOST pointer for rte_render_host().  Each buffer holds

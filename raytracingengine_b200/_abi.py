@@ -35,6 +35,7 @@ TM_NAMES = (
 TM_COUNT = 7
 TM_NONE = -1
 TM_ACES = 6
+FLAG_EXACT_SHADOWS, FLAG_NO_FILTER = 1, 2
 
 # --- numpy dtypes (C layout) -------------------------------------------------------------------
 material_dt = np.dtype(  # Material, RE/Shape.h:13-19
@@ -82,7 +83,7 @@ class SceneDesc(C.Structure):  # the vectors of Scene, RE/Scene.h:17-23
 class RenderOpts(C.Structure):
     _fields_ = [("row0", C.c_int32), ("row1", C.c_int32), ("max_depth", C.c_int32),
                 ("tonemap_op", C.c_int32), ("bias", C.c_double), ("max_white", C.c_double),
-                ("jodie_a", C.c_double), ("spp_seed", C.c_int32), ("reserved", C.c_int32)]
+                ("jodie_a", C.c_double), ("spp_seed", C.c_int32), ("flags", C.c_int32)]
 
 
 class Frame(C.Structure):

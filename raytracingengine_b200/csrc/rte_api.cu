@@ -1,0 +1,656 @@
+// rte_api.cu — the extern "C" boundary of librte_b200.so (include/rte.h): context, scene packing,
+// launches, host-buffer variants, PPM output.  No torch types, no CPU compute path: every compute entry
+// point needs a CUDA device and fails with RTE_ERR_NO_DEVICE / RTE_ERR_CUDA otherwise.
+//
+// Scene packing replaces what the reference does implicitly in Scene::Add* / the shape constructors
+// ("RE/" = /root/reference/RaytracingEngine/): Plane ctor normalisation (RE/Shape.h:141-147), Triangle
+// tv0..tv2 / edges / flat normal (RE/Shape.h:198-227), Model -> triangles in index order reporting the
+// MODEL index (RE/Shape.h:258-283), Light E = color * intensity (RE/Scene.h:110).  All of that is FP64
+// host arithmetic done once per upload, in the reference's operation order.
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "rte_kernels.h"
+
+using namespace rte;
+
+namespace {
+
+thread_local std::string tl_error;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+}  // namespace
+
+struct rte_ctx {
+    int device = 0;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    std::string err;
+    bool sticky = false;
+
+    // scene
+    bool has_scene = false, has_camera = false;
+    DevScene sc{};
+    DevCamera cam{};
+    rte_camera cam_host{};
+    DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights;
+
+    // launch scratch
+    unsigned int* d_tile_counter = nullptr;
+    unsigned long long* d_stats = nullptr;
+    unsigned int* d_maxlum = nullptr;
+    unsigned long long* h_stats = nullptr;  // pinned
+    cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
+    bool render_timed = false, tonemap_timed = false;
+    rte_stats stats{};
+
+    // staging for the *_host variants (grow-only)
+    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask;
+    DevBuf s_tm_in, s_tm_out[RTE_TM_COUNT], s_q_o, s_q_d, s_q_m, s_q_out;
+};
+
+namespace {
+
+int fail(rte_ctx* ctx, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    tl_error = buf;
+    if (ctx) ctx->err = buf;
+    return code;
+}
+
+int cuda_fail(rte_ctx* ctx, cudaError_t e, const char* what) {
+    if (ctx) ctx->sticky = true;
+    return fail(ctx, RTE_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+}
+
+#define RTE_CUDA(ctx, call)                                       \
+    do {                                                          \
+        cudaError_t e__ = (call);                                 \
+        if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
+    } while (0)
+
+#define RTE_ENTER(ctx)                                                                        \
+    do {                                                                                      \
+        if (!(ctx)) return fail(nullptr, RTE_ERR_INVALID, "%s: ctx is NULL", __func__);        \
+        if ((ctx)->sticky) return fail(nullptr, RTE_ERR_CUDA, "ctx is in a failed CUDA state: %s", (ctx)->err.c_str()); \
+        cudaError_t e__ = cudaSetDevice((ctx)->device);                                       \
+        if (e__ != cudaSuccess) return cuda_fail(ctx, e__, "cudaSetDevice");                  \
+    } while (0)
+
+int reserve(rte_ctx* ctx, DevBuf& b, size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    if (b.cap >= bytes) return RTE_OK;
+    if (b.p) {
+        RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        RTE_CUDA(ctx, cudaFree(b.p));
+        b.p = nullptr; b.cap = 0;
+    }
+    RTE_CUDA(ctx, cudaMalloc(&b.p, bytes));
+    b.cap = bytes;
+    return RTE_OK;
+}
+
+template <class T>
+int upload(rte_ctx* ctx, DevBuf& b, const std::vector<T>& v) {
+    int rc = reserve(ctx, b, v.size() * sizeof(T));
+    if (rc) return rc;
+    if (!v.empty()) RTE_CUDA(ctx, cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    return RTE_OK;
+}
+
+// ---- FP64 host Vec3 in the reference's operation order (RE/Math.h:14-37), compiled without contraction
+struct H3 { double x, y, z; };
+inline H3 h3(const double* p) { return H3{p[0], p[1], p[2]}; }
+inline H3 hadd(H3 a, H3 b) { return H3{a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline H3 hsub(H3 a, H3 b) { return H3{a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline H3 hmul(H3 a, double s) { return H3{a.x * s, a.y * s, a.z * s}; }
+inline double hdot(H3 a, H3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline H3 hcross(H3 a, H3 b) { return H3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline double hlen(H3 a) { return std::sqrt(hdot(a, a)); }
+inline H3 hnorm(H3 a) {
+    const double l = hlen(a);
+    if (l <= 1e-12) return H3{0, 0, 0};
+    return H3{a.x / l, a.y / l, a.z / l};
+}
+inline void put3(double* d, H3 v) { d[0] = v.x; d[1] = v.y; d[2] = v.z; }
+inline float up(float v) { return std::nextafter(v, INFINITY); }
+inline bool finite3(const double* p) { return std::isfinite(p[0]) && std::isfinite(p[1]) && std::isfinite(p[2]); }
+
+struct Defaults {
+    int max_depth; int tonemap_op; double bias, max_white, jodie_a; int row0, row1; uint32_t flags;
+};
+
+int resolve_opts(rte_ctx* ctx, const rte_render_opts* o, Defaults& d) {
+    const int H = (int)ctx->cam_host.height;
+    d.row0 = o ? o->row0 : 0;
+    d.row1 = (o && o->row1 > 0) ? o->row1 : H;
+    d.max_depth = (o && o->max_depth > 0) ? o->max_depth : 10;
+    d.tonemap_op = o ? o->tonemap_op : RTE_TM_NONE;
+    d.bias = (o && o->bias > 0) ? o->bias : 1e-3;
+    d.max_white = (o && o->max_white > 0) ? o->max_white : 5.0;
+    d.jodie_a = (o && o->jodie_a > 0) ? o->jodie_a : 0.18;
+    d.flags = o ? (uint32_t)o->flags : 0u;
+    if (d.row0 < 0 || d.row1 > H || d.row0 > d.row1)
+        return fail(ctx, RTE_ERR_INVALID, "row band [%d,%d) outside the camera image (height %d)", d.row0, d.row1, H);
+    if (d.tonemap_op < RTE_TM_NONE || d.tonemap_op >= RTE_TM_COUNT)
+        return fail(ctx, RTE_ERR_INVALID, "tonemap_op %d is not an RTE_TM_* value", d.tonemap_op);
+    return RTE_OK;
+}
+
+}  // namespace
+
+// ====================================================================================== basics
+extern "C" int rte_version(void) { return RTE_VERSION; }
+
+extern "C" int rte_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" const char* rte_last_error(const rte_ctx* ctx) { return ctx ? ctx->err.c_str() : tl_error.c_str(); }
+
+extern "C" int rte_create(int device, rte_ctx** out) {
+    if (!out) return fail(nullptr, RTE_ERR_INVALID, "rte_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        cudaGetLastError();
+        return fail(nullptr, RTE_ERR_NO_DEVICE, "no CUDA device visible (%s): librte_b200 has no CPU path",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    }
+    if (device < 0 || device >= n) return fail(nullptr, RTE_ERR_INVALID, "device %d out of range [0,%d)", device, n);
+    cudaDeviceProp prop;
+    if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return cuda_fail(nullptr, e, "cudaGetDeviceProperties");
+    if (prop.major != 10)
+        return fail(nullptr, RTE_ERR_NO_DEVICE, "device %d is sm_%d%d; this library carries sm_100a code only", device, prop.major, prop.minor);
+    rte_ctx* ctx = new (std::nothrow) rte_ctx();
+    if (!ctx) return fail(nullptr, RTE_ERR_INVALID, "out of host memory");
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+#define CK(call) do { cudaError_t e2 = (call); if (e2 != cudaSuccess) { int rc = cuda_fail(nullptr, e2, #call); rte_destroy(ctx); return rc; } } while (0)
+    CK(cudaSetDevice(device));
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CK(cudaMalloc(&ctx->d_tile_counter, sizeof(unsigned int)));
+    CK(cudaMalloc(&ctx->d_stats, sizeof(unsigned long long) * kStatCount));
+    CK(cudaMalloc(&ctx->d_maxlum, sizeof(unsigned int)));
+    CK(cudaMallocHost(&ctx->h_stats, sizeof(unsigned long long) * (kStatCount + 1)));
+    CK(cudaEventCreate(&ctx->ev_r0)); CK(cudaEventCreate(&ctx->ev_r1));
+    CK(cudaEventCreate(&ctx->ev_t0)); CK(cudaEventCreate(&ctx->ev_t1));
+#undef CK
+    *out = ctx;
+    return RTE_OK;
+}
+
+extern "C" void rte_destroy(rte_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
+                      &ctx->s_q_m, &ctx->s_q_out};
+    for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
+    for (DevBuf& b : ctx->s_tm_out) if (b.p) cudaFree(b.p);
+    if (ctx->d_tile_counter) cudaFree(ctx->d_tile_counter);
+    if (ctx->d_stats) cudaFree(ctx->d_stats);
+    if (ctx->d_maxlum) cudaFree(ctx->d_maxlum);
+    if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
+    cudaEvent_t evs[] = {ctx->ev_r0, ctx->ev_r1, ctx->ev_t0, ctx->ev_t1};
+    for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    cudaGetLastError();
+    delete ctx;
+}
+
+extern "C" int rte_set_stream(rte_ctx* ctx, void* cuda_stream) {
+    RTE_ENTER(ctx);
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (cuda_stream) {
+        if (ctx->own_stream) RTE_CUDA(ctx, cudaStreamDestroy(ctx->stream));
+        ctx->stream = (cudaStream_t)cuda_stream;
+        ctx->own_stream = false;
+    } else if (!ctx->own_stream) {
+        RTE_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        ctx->own_stream = true;
+    }
+    return RTE_OK;
+}
+
+extern "C" int rte_synchronize(rte_ctx* ctx) {
+    RTE_ENTER(ctx);
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+
+// ====================================================================================== scene
+extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
+    RTE_ENTER(ctx);
+    if (!d) return fail(ctx, RTE_ERR_INVALID, "rte_upload_scene: scene is NULL");
+    const int64_t counts[] = {d->n_materials, d->n_spheres, d->n_planes, d->n_triangles, d->n_models, d->n_model_vertices, d->n_model_indices, d->n_lights};
+    const void* ptrs[] = {d->materials, d->spheres, d->planes, d->triangles, d->models, d->model_vertices, d->model_indices, d->lights};
+    static const char* names[] = {"materials", "spheres", "planes", "triangles", "models", "model_vertices", "model_indices", "lights"};
+    for (int i = 0; i < 8; ++i) {
+        if (counts[i] < 0) return fail(ctx, RTE_ERR_INVALID, "n_%s is negative", names[i]);
+        if (counts[i] > 0 && !ptrs[i]) return fail(ctx, RTE_ERR_INVALID, "%s is NULL with n_%s = %lld", names[i], names[i], (long long)counts[i]);
+    }
+    if (d->n_lights > 16) return fail(ctx, RTE_ERR_LIMIT, "at most 16 lights (light_mask AOV is 16+16 bits), got %lld", (long long)d->n_lights);
+    if (d->n_spheres >= (1ll << 30) || d->n_planes >= (1ll << 30)) return fail(ctx, RTE_ERR_LIMIT, "primitive index does not fit 30 bits");
+
+    // materials (+ the default Material at index nm, RE/Shape.h:13-19)
+    std::vector<rte_material> mats(d->materials, d->materials + d->n_materials);
+    for (int64_t i = 0; i < d->n_materials; ++i) {
+        if (mats[i].transparency > 0.0)
+            return fail(ctx, RTE_ERR_LIMIT, "material %lld has transparency > 0: refraction (RE/Scene.h:175-187) is not built yet", (long long)i);
+    }
+    rte_material def{};
+    def.shininess = 128.0; def.refractive_index = 1.0;
+    mats.push_back(def);
+
+    // spheres
+    const int ns = (int)d->n_spheres, ns_pad = (ns + 7) & ~7;  // kSphUnroll
+    std::vector<float4> sph32((size_t)ns_pad);
+    std::vector<double4> sph64((size_t)ns_pad);
+    std::vector<int32_t> sphmat((size_t)ns_pad, -1);
+    double s_ext = 0.0;
+    for (int i = 0; i < ns; ++i) {
+        const rte_sphere& s = d->spheres[i];
+        if (!finite3(s.center) || !std::isfinite(s.radius)) return fail(ctx, RTE_ERR_INVALID, "sphere %d is not finite", i);
+        sph64[i] = make_double4(s.center[0], s.center[1], s.center[2], s.radius);
+        const float r = up((float)std::fabs(s.radius));
+        sph32[i] = make_float4((float)s.center[0], (float)s.center[1], (float)s.center[2], up(r * r));
+        sphmat[i] = s.material;
+        s_ext = std::fmax(s_ext, hlen(h3(s.center)) + std::fabs(s.radius));
+    }
+    for (int i = ns; i < ns_pad; ++i) {  // never-hit padding: q = +inf
+        sph32[i] = make_float4(0.f, 0.f, 0.f, -INFINITY);
+        sph64[i] = make_double4(0, 0, 0, 0);
+    }
+
+    // planes — Plane ctor normalises the normal (RE/Shape.h:142)
+    const int np = (int)d->n_planes;
+    std::vector<DevPlane> planes((size_t)np);
+    for (int i = 0; i < np; ++i) {
+        const rte_plane& p = d->planes[i];
+        if (!finite3(p.point) || !finite3(p.normal)) return fail(ctx, RTE_ERR_INVALID, "plane %d is not finite", i);
+        put3(planes[i].n, hnorm(h3(p.normal)));
+        put3(planes[i].p0, h3(p.point));
+        planes[i].mat = p.material; planes[i].pad = 0;
+    }
+
+    // triangles: standalone ones, then every model's triples in order (canonical order of RE/Scene.h:218-257)
+    int64_t nt64 = d->n_triangles;
+    for (int64_t m = 0; m < d->n_models; ++m) {
+        const rte_model& mo = d->models[m];
+        if (mo.index_count < 0 || mo.index_count % 3) return fail(ctx, RTE_ERR_INVALID, "model %lld: index_count must be a non-negative multiple of 3", (long long)m);
+        if (mo.first_vertex < 0 || mo.vertex_count < 0 || mo.first_vertex + mo.vertex_count > d->n_model_vertices ||
+            mo.first_index < 0 || mo.first_index + mo.index_count > d->n_model_indices)
+            return fail(ctx, RTE_ERR_INVALID, "model %lld: vertex/index range outside the shared arrays", (long long)m);
+        nt64 += mo.index_count / 3;
+    }
+    if (nt64 >= (1ll << 30)) return fail(ctx, RTE_ERR_LIMIT, "too many triangles");
+    const int nt = (int)nt64, nt_pad = (nt + 1) & ~1;
+    std::vector<float4> tri32((size_t)nt_pad * 3);
+    std::vector<DevTri64> tri64((size_t)nt_pad);
+    std::vector<int2> triinfo((size_t)nt_pad, make_int2(-1, 0));
+    double t_ext = 0.0, t_edge = 0.0;
+    int k = 0;
+    auto add_tri = [&](H3 v0, H3 v1, H3 v2, H3 T, int mat, int report) {
+        const H3 a0 = hadd(v0, T);                 // tv0, RE/Shape.h:198
+        const H3 e1 = hsub(hadd(v1, T), a0);       // edge1 = tv1 - tv0, :204-205
+        const H3 e2 = hsub(hadd(v2, T), a0);       // edge2 = tv2 - tv0, :206
+        const H3 n = hnorm(hcross(hsub(v1, v0), hsub(v2, v0)));  // GetNormalAt, :222-227 (untranslated vertices)
+        put3(tri64[k].a0, a0); put3(tri64[k].e1, e1); put3(tri64[k].e2, e2); put3(tri64[k].n, n);
+        tri32[3 * (size_t)k + 0] = make_float4((float)a0.x, (float)a0.y, (float)a0.z, 0.f);
+        tri32[3 * (size_t)k + 1] = make_float4((float)e1.x, (float)e1.y, (float)e1.z, 0.f);
+        tri32[3 * (size_t)k + 2] = make_float4((float)e2.x, (float)e2.y, (float)e2.z, 0.f);
+        triinfo[k] = make_int2(mat, report);
+        t_ext = std::fmax(t_ext, std::fmax(hlen(a0), std::fmax(hlen(hadd(v1, T)), hlen(hadd(v2, T)))));
+        t_edge = std::fmax(t_edge, std::fmax(hlen(e1), hlen(e2)));
+        ++k;
+    };
+    for (int64_t i = 0; i < d->n_triangles; ++i) {
+        const rte_triangle& t = d->triangles[i];
+        if (!finite3(t.v0) || !finite3(t.v1) || !finite3(t.v2) || !finite3(t.translate)) return fail(ctx, RTE_ERR_INVALID, "triangle %lld is not finite", (long long)i);
+        add_tri(h3(t.v0), h3(t.v1), h3(t.v2), h3(t.translate), t.material, (int)i);
+    }
+    for (int64_t m = 0; m < d->n_models; ++m) {
+        const rte_model& mo = d->models[m];
+        const double* vb = d->model_vertices + 3 * mo.first_vertex;
+        const int32_t* ib = d->model_indices + mo.first_index;
+        if (!finite3(mo.translate)) return fail(ctx, RTE_ERR_INVALID, "model %lld translate is not finite", (long long)m);
+        for (int64_t i = 0; i + 2 < mo.index_count; i += 3) {
+            for (int c = 0; c < 3; ++c) {
+                if (ib[i + c] < 0 || ib[i + c] >= mo.vertex_count)
+                    return fail(ctx, RTE_ERR_INVALID, "model %lld: index %d out of range [0,%lld)", (long long)m, ib[i + c], (long long)mo.vertex_count);
+                if (!finite3(vb + 3 * ib[i + c])) return fail(ctx, RTE_ERR_INVALID, "model %lld has a non-finite vertex", (long long)m);
+            }
+            add_tri(h3(vb + 3 * ib[i]), h3(vb + 3 * ib[i + 1]), h3(vb + 3 * ib[i + 2]), h3(mo.translate), mo.material, (int)m);
+        }
+    }
+    const float qnan = std::nanf("");
+    for (int i = nt; i < nt_pad; ++i) {  // never-candidate padding: every filter comparison is false on NaN
+        for (int c = 0; c < 3; ++c) tri32[3 * (size_t)i + c] = make_float4(qnan, qnan, qnan, 0.f);
+        std::memset(&tri64[i], 0, sizeof(DevTri64));
+    }
+
+    // lights — E = color * intensity (RE/Scene.h:110)
+    const int nl = (int)d->n_lights;
+    std::vector<DevLight> lights((size_t)nl);
+    for (int i = 0; i < nl; ++i) {
+        put3(lights[i].pos, h3(d->lights[i].position));
+        put3(lights[i].E, hmul(h3(d->lights[i].color), d->lights[i].intensity));
+    }
+
+    const size_t smem = (size_t)ns_pad * 16 + (size_t)nt_pad * 48;
+    const size_t smem_budget = ctx->smem_optin > 4096 ? ctx->smem_optin - 4096 : 0;  // static smem + headroom
+    if (smem > smem_budget)
+        return fail(ctx, RTE_ERR_LIMIT, "scene filter arrays need %zu B of shared memory (%d spheres, %d triangles); the per-CTA limit is %zu B",
+                    smem, ns, nt, smem_budget);
+
+    int rc;
+    if ((rc = upload(ctx, ctx->b_sph32, sph32)) || (rc = upload(ctx, ctx->b_sph64, sph64)) || (rc = upload(ctx, ctx->b_sphmat, sphmat)) ||
+        (rc = upload(ctx, ctx->b_planes, planes)) || (rc = upload(ctx, ctx->b_tri32, tri32)) || (rc = upload(ctx, ctx->b_tri64, tri64)) ||
+        (rc = upload(ctx, ctx->b_triinfo, triinfo)) || (rc = upload(ctx, ctx->b_mats, mats)) || (rc = upload(ctx, ctx->b_lights, lights)))
+        return rc;
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the host vectors go out of scope
+
+    DevScene& sc = ctx->sc;
+    sc.sph32 = (const float4*)ctx->b_sph32.p; sc.tri32 = (const float4*)ctx->b_tri32.p;
+    sc.ns = ns; sc.ns_pad = ns_pad; sc.nt = nt; sc.nt_pad = nt_pad;
+    sc.sph64 = (const double4*)ctx->b_sph64.p; sc.sph_mat = (const int32_t*)ctx->b_sphmat.p;
+    sc.planes = (const DevPlane*)ctx->b_planes.p; sc.tri64 = (const DevTri64*)ctx->b_tri64.p;
+    sc.tri_info = (const int2*)ctx->b_triinfo.p; sc.materials = (const rte_material*)ctx->b_mats.p;
+    sc.lights = (const DevLight*)ctx->b_lights.p;
+    sc.np = np; sc.nm = (int)d->n_materials; sc.nl = nl; sc.pad0 = 0;
+    sc.sph_extent = up((float)s_ext) * 1.000001f;
+    sc.tri_extent = up((float)t_ext) * 1.000001f;
+    sc.tri_edge = up((float)t_edge) * 1.000001f;
+    sc.pad1 = 0.f;
+    ctx->has_scene = true;
+    return RTE_OK;
+}
+
+extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
+    RTE_ENTER(ctx);
+    if (!c) return fail(ctx, RTE_ERR_INVALID, "rte_set_camera: camera is NULL");
+    if (c->width == 0 || c->height == 0 || c->width > (1u << 20) || c->height > (1u << 20))
+        return fail(ctx, RTE_ERR_INVALID, "camera size %llux%llu not supported", (unsigned long long)c->width, (unsigned long long)c->height);
+    if (!finite3(c->position) || !std::isfinite(c->focal)) return fail(ctx, RTE_ERR_INVALID, "camera is not finite");
+    if (c->anti_aliasing != 1)
+        return fail(ctx, RTE_ERR_LIMIT, "anti_aliasing = %d: only 1 sample per pixel is built (the reference's jitter is non-reproducible, RE/Math.h:103-116)", c->anti_aliasing);
+    ctx->cam_host = *c;
+    DevCamera& dc = ctx->cam;
+    dc.pos[0] = c->position[0]; dc.pos[1] = c->position[1]; dc.pos[2] = c->position[2];
+    dc.focal = c->focal;
+    dc.half_w = (double)c->width / 2.0;   // RE/Math.h:100
+    dc.half_h = (double)c->height / 2.0;  // RE/Math.h:101
+    dc.width = (int)c->width; dc.height = (int)c->height;
+    ctx->has_camera = true;
+    return RTE_OK;
+}
+
+// ====================================================================================== render
+static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
+    RenderParams p{};
+    p.sc = ctx->sc; p.cam = ctx->cam;
+    p.row0 = o.row0; p.row1 = o.row1; p.max_depth = o.max_depth; p.tonemap_op = o.tonemap_op;
+    p.exact_shadows = (o.flags & RTE_FLAG_EXACT_SHADOWS) ? 1 : 0;
+    p.no_filter = (o.flags & RTE_FLAG_NO_FILTER) ? 1 : 0;
+    p.bias = o.bias; p.max_white = o.max_white; p.jodie_a = o.jodie_a;
+    p.out = *frame;
+    p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
+    if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
+    RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));
+    RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * kStatCount, ctx->stream));
+    RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
+    if (o.row1 > o.row0) RTE_CUDA(ctx, launch_render(p, ctx->sm_count, ctx->stream));
+    RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->render_timed = true;
+    return RTE_OK;
+}
+
+extern "C" int rte_render(rte_ctx* ctx, const rte_render_opts* opts, const rte_frame* frame) {
+    RTE_ENTER(ctx);
+    if (!ctx->has_scene || !ctx->has_camera) return fail(ctx, RTE_ERR_INVALID, "rte_render: upload a scene and set a camera first");
+    if (!frame) return fail(ctx, RTE_ERR_INVALID, "rte_render: frame is NULL");
+    Defaults o;
+    int rc = resolve_opts(ctx, opts, o);
+    if (rc) return rc;
+    return do_render(ctx, o, frame);
+}
+
+extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const rte_frame* hf) {
+    RTE_ENTER(ctx);
+    if (!ctx->has_scene || !ctx->has_camera) return fail(ctx, RTE_ERR_INVALID, "rte_render_host: upload a scene and set a camera first");
+    if (!hf) return fail(ctx, RTE_ERR_INVALID, "rte_render_host: frame is NULL");
+    Defaults o;
+    int rc = resolve_opts(ctx, opts, o);
+    if (rc) return rc;
+    const size_t n = (size_t)(o.row1 - o.row0) * (size_t)ctx->cam.width;
+    rte_frame df{};
+    struct Item { void* host; DevBuf* buf; size_t bytes; void** dev; };
+    Item items[] = {
+        {hf->hdr, &ctx->s_hdr, n * 16, (void**)&df.hdr},          {hf->hdr64, &ctx->s_hdr64, n * 24, (void**)&df.hdr64},
+        {hf->rgb8, &ctx->s_rgb8, n * 3, (void**)&df.rgb8},         {hf->prim_id, &ctx->s_prim, n * 4, (void**)&df.prim_id},
+        {hf->depth, &ctx->s_depth, n * 4, (void**)&df.depth},      {hf->depth64, &ctx->s_depth64, n * 8, (void**)&df.depth64},
+        {hf->normal, &ctx->s_normal, n * 16, (void**)&df.normal},  {hf->albedo, &ctx->s_albedo, n * 16, (void**)&df.albedo},
+        {hf->light_mask, &ctx->s_lmask, n * 4, (void**)&df.light_mask}};
+    for (Item& it : items) {
+        if (!it.host) continue;
+        if ((rc = reserve(ctx, *it.buf, it.bytes))) return rc;
+        *it.dev = it.buf->p;
+    }
+    if ((rc = do_render(ctx, o, &df))) return rc;
+    for (Item& it : items)
+        if (it.host && it.bytes) RTE_CUDA(ctx, cudaMemcpyAsync(it.host, it.buf->p, it.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+
+extern "C" int rte_get_stats(rte_ctx* ctx, rte_stats* out) {
+    RTE_ENTER(ctx);
+    if (!out) return fail(ctx, RTE_ERR_INVALID, "rte_get_stats: out is NULL");
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    rte_stats& s = ctx->stats;
+    if (ctx->render_timed) {
+        const unsigned long long* h = ctx->h_stats;
+        s.primary_rays = h[kStatPrimary]; s.shadow_rays = h[kStatShadow]; s.secondary_rays = h[kStatSecondary];
+        s.sphere_tests = h[kStatSphTests]; s.plane_tests = h[kStatPlTests]; s.triangle_tests = h[kStatTriTests];
+        s.exact_marches = h[kStatMarches]; s.fp64_confirms = h[kStatConfirms];
+        float ms = 0.f;
+        RTE_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_r0, ctx->ev_r1));
+        s.kernel_ms = ms;
+    }
+    if (ctx->tonemap_timed) {
+        float ms = 0.f;
+        RTE_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_t0, ctx->ev_t1));
+        s.tonemap_ms = ms;
+    }
+    *out = s;
+    return RTE_OK;
+}
+
+// ====================================================================================== tonemap
+static int check_tonemap_args(rte_ctx* ctx, const float* hdr, int64_t n, uint32_t mask, uint8_t* const rgb8[RTE_TM_COUNT]) {
+    if (n < 0) return fail(ctx, RTE_ERR_INVALID, "n_pixels is negative");
+    if (mask == 0 || mask >= (1u << RTE_TM_COUNT)) return fail(ctx, RTE_ERR_INVALID, "op_mask 0x%x selects no / unknown operators", mask);
+    if (n > 0 && !hdr) return fail(ctx, RTE_ERR_INVALID, "hdr is NULL");
+    if (!rgb8) return fail(ctx, RTE_ERR_INVALID, "rgb8 is NULL");
+    for (int op = 0; op < RTE_TM_COUNT; ++op)
+        if ((mask & (1u << op)) && n > 0 && !rgb8[op]) return fail(ctx, RTE_ERR_INVALID, "rgb8[%d] is NULL but its bit is set in op_mask", op);
+    return RTE_OK;
+}
+
+static int do_tonemap(rte_ctx* ctx, const float* hdr, int64_t n, uint32_t mask, double max_white, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]) {
+    TonemapParams p{};
+    p.hdr = (const float4*)hdr; p.n_pixels = n; p.op_mask = mask;
+    p.max_white = (float)(max_white > 0 ? max_white : 5.0);
+    p.jodie_a = (float)(jodie_a > 0 ? jodie_a : 0.18);
+    if (((uintptr_t)hdr & 15u) != 0) return fail(ctx, RTE_ERR_INVALID, "hdr must be 16-byte aligned");
+    for (int op = 0; op < RTE_TM_COUNT; ++op) {
+        p.rgb8[op] = (mask & (1u << op)) ? rgb8[op] : nullptr;
+        if (p.rgb8[op] && ((uintptr_t)p.rgb8[op] & 3u) != 0) return fail(ctx, RTE_ERR_INVALID, "rgb8[%d] must be 4-byte aligned", op);
+    }
+    RTE_CUDA(ctx, cudaEventRecord(ctx->ev_t0, ctx->stream));
+    RTE_CUDA(ctx, launch_tonemap(p, ctx->sm_count, ctx->stream));
+    RTE_CUDA(ctx, cudaEventRecord(ctx->ev_t1, ctx->stream));
+    ctx->tonemap_timed = true;
+    return RTE_OK;
+}
+
+extern "C" int rte_tonemap(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t op_mask, double max_white, double jodie_a,
+                           uint8_t* const rgb8[RTE_TM_COUNT]) {
+    RTE_ENTER(ctx);
+    int rc = check_tonemap_args(ctx, hdr, n_pixels, op_mask, rgb8);
+    if (rc) return rc;
+    return do_tonemap(ctx, hdr, n_pixels, op_mask, max_white, jodie_a, rgb8);
+}
+
+extern "C" int rte_tonemap_host(rte_ctx* ctx, const float* hdr, int64_t n, uint32_t mask, double max_white, double jodie_a,
+                                uint8_t* const rgb8[RTE_TM_COUNT]) {
+    RTE_ENTER(ctx);
+    int rc = check_tonemap_args(ctx, hdr, n, mask, rgb8);
+    if (rc) return rc;
+    if (n == 0) return RTE_OK;
+    if ((rc = reserve(ctx, ctx->s_tm_in, (size_t)n * 16))) return rc;
+    uint8_t* dev[RTE_TM_COUNT] = {};
+    for (int op = 0; op < RTE_TM_COUNT; ++op) {
+        if (!(mask & (1u << op))) continue;
+        if ((rc = reserve(ctx, ctx->s_tm_out[op], (size_t)n * 3 + 16))) return rc;
+        dev[op] = (uint8_t*)ctx->s_tm_out[op].p;
+    }
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->s_tm_in.p, hdr, (size_t)n * 16, cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = do_tonemap(ctx, (const float*)ctx->s_tm_in.p, n, mask, max_white, jodie_a, dev))) return rc;
+    for (int op = 0; op < RTE_TM_COUNT; ++op)
+        if (dev[op]) RTE_CUDA(ctx, cudaMemcpyAsync(rgb8[op], dev[op], (size_t)n * 3, cudaMemcpyDeviceToHost, ctx->stream));
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+
+extern "C" int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max) {
+    RTE_ENTER(ctx);
+    if (!out_max || (n_pixels > 0 && !hdr) || n_pixels < 0) return fail(ctx, RTE_ERR_INVALID, "rte_max_luminance: bad arguments");
+    RTE_CUDA(ctx, launch_max_luminance((const float4*)hdr, n_pixels, ctx->d_maxlum, ctx->sm_count, ctx->stream));
+    unsigned int* h = (unsigned int*)&ctx->h_stats[kStatCount];
+    RTE_CUDA(ctx, cudaMemcpyAsync(h, ctx->d_maxlum, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    std::memcpy(out_max, h, sizeof(float));
+    return RTE_OK;
+}
+
+// ====================================================================================== ray queries
+extern "C" int rte_intersect_closest(rte_ctx* ctx, int64_t n, const double* origins, const double* directions, rte_hit* hits) {
+    RTE_ENTER(ctx);
+    if (!ctx->has_scene) return fail(ctx, RTE_ERR_INVALID, "rte_intersect_closest: upload a scene first");
+    if (n < 0 || (n > 0 && (!origins || !directions || !hits))) return fail(ctx, RTE_ERR_INVALID, "rte_intersect_closest: bad arguments");
+    if (n == 0) return RTE_OK;
+    int rc;
+    if ((rc = reserve(ctx, ctx->s_q_o, (size_t)n * 24)) || (rc = reserve(ctx, ctx->s_q_d, (size_t)n * 24)) ||
+        (rc = reserve(ctx, ctx->s_q_out, (size_t)n * sizeof(rte_hit))))
+        return rc;
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->s_q_o.p, origins, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->s_q_d.p, directions, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+    RTE_CUDA(ctx, launch_intersect_closest(ctx->sc, n, (const double*)ctx->s_q_o.p, (const double*)ctx->s_q_d.p, (rte_hit*)ctx->s_q_out.p,
+                                           ctx->sm_count, ctx->stream));
+    RTE_CUDA(ctx, cudaMemcpyAsync(hits, ctx->s_q_out.p, (size_t)n * sizeof(rte_hit), cudaMemcpyDeviceToHost, ctx->stream));
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+
+extern "C" int rte_intersect_any_before(rte_ctx* ctx, int64_t n, const double* origins, const double* directions, const double* max_dist,
+                                        uint8_t* out) {
+    RTE_ENTER(ctx);
+    if (!ctx->has_scene) return fail(ctx, RTE_ERR_INVALID, "rte_intersect_any_before: upload a scene first");
+    if (n < 0 || (n > 0 && (!origins || !directions || !max_dist || !out))) return fail(ctx, RTE_ERR_INVALID, "rte_intersect_any_before: bad arguments");
+    if (n == 0) return RTE_OK;
+    int rc;
+    if ((rc = reserve(ctx, ctx->s_q_o, (size_t)n * 24)) || (rc = reserve(ctx, ctx->s_q_d, (size_t)n * 24)) ||
+        (rc = reserve(ctx, ctx->s_q_m, (size_t)n * 8)) || (rc = reserve(ctx, ctx->s_q_out, (size_t)n)))
+        return rc;
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->s_q_o.p, origins, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->s_q_d.p, directions, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->s_q_m.p, max_dist, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    RTE_CUDA(ctx, launch_intersect_any_before(ctx->sc, n, (const double*)ctx->s_q_o.p, (const double*)ctx->s_q_d.p, (const double*)ctx->s_q_m.p,
+                                              (uint8_t*)ctx->s_q_out.p, ctx->sm_count, ctx->stream));
+    RTE_CUDA(ctx, cudaMemcpyAsync(out, ctx->s_q_out.p, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+
+// ====================================================================================== memory helpers
+extern "C" int rte_malloc(rte_ctx* ctx, size_t bytes, void** out_dev) {
+    RTE_ENTER(ctx);
+    if (!out_dev) return fail(ctx, RTE_ERR_INVALID, "rte_malloc: out is NULL");
+    *out_dev = nullptr;
+    cudaError_t e = cudaMalloc(out_dev, bytes ? bytes : 16);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, RTE_ERR_CUDA, "cudaMalloc(%zu): %s", bytes, cudaGetErrorString(e)); }
+    return RTE_OK;
+}
+extern "C" int rte_free(rte_ctx* ctx, void* dev) {
+    RTE_ENTER(ctx);
+    if (dev) RTE_CUDA(ctx, cudaFree(dev));
+    return RTE_OK;
+}
+extern "C" int rte_memcpy_d2h(rte_ctx* ctx, void* host, const void* dev, size_t bytes) {
+    RTE_ENTER(ctx);
+    if (bytes && (!host || !dev)) return fail(ctx, RTE_ERR_INVALID, "rte_memcpy_d2h: NULL pointer");
+    if (bytes) RTE_CUDA(ctx, cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+extern "C" int rte_memcpy_h2d(rte_ctx* ctx, void* dev, const void* host, size_t bytes) {
+    RTE_ENTER(ctx);
+    if (bytes && (!host || !dev)) return fail(ctx, RTE_ERR_INVALID, "rte_memcpy_h2d: NULL pointer");
+    if (bytes) RTE_CUDA(ctx, cudaMemcpyAsync(dev, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+extern "C" int rte_malloc_host(size_t bytes, void** out_host) {
+    if (!out_host) return fail(nullptr, RTE_ERR_INVALID, "rte_malloc_host: out is NULL");
+    *out_host = nullptr;
+    cudaError_t e = cudaMallocHost(out_host, bytes ? bytes : 16);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(nullptr, e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? RTE_ERR_NO_DEVICE : RTE_ERR_CUDA,
+                    "cudaMallocHost(%zu): %s", bytes, cudaGetErrorString(e));
+    }
+    return RTE_OK;
+}
+extern "C" int rte_free_host(void* host) {
+    if (host && cudaFreeHost(host) != cudaSuccess) { cudaGetLastError(); return fail(nullptr, RTE_ERR_CUDA, "cudaFreeHost failed"); }
+    return RTE_OK;
+}
+
+// ====================================================================================== PPM
+// writePPM, RE/Image.cpp:11-31: "P6\n<W> <H>\n255\n" + W*H RGB triplets; the reference streams one char at
+// a time, this is one fwrite from the caller's (pinned) buffer.  Error texts are the reference's.
+extern "C" int rte_write_ppm(const char* filename, const uint8_t* rgb8, uint64_t width, uint64_t height) {
+    if (!filename || (!rgb8 && width * height)) return fail(nullptr, RTE_ERR_INVALID, "rte_write_ppm: NULL argument");
+    FILE* f = std::fopen(filename, "wb");
+    if (!f) return fail(nullptr, RTE_ERR_IO, "Could not open file for writing");
+    const size_t n = (size_t)width * (size_t)height * 3;
+    bool ok = std::fprintf(f, "P6\n%llu %llu\n255\n", (unsigned long long)width, (unsigned long long)height) > 0;
+    ok = ok && (n == 0 || std::fwrite(rgb8, 1, n, f) == n);
+    ok = (std::fclose(f) == 0) && ok;
+    if (!ok) return fail(nullptr, RTE_ERR_IO, "Error occurred while writing to file");
+    return RTE_OK;
+}

@@ -1,0 +1,152 @@
+// rte_device.cuh — device-side scene layout and exact (FP64) primitive arithmetic.
+//
+// Design: the brute-force loops over primitives run in FP32 FMA as *conservative
+// filters* over SoA arrays staged in shared memory; every candidate that passes a filter is
+// re-evaluated here in FP64 with exactly the reference's operation order, so nearest-hit index,
+// shadow visibility, depth and normals are the reference's own FP64 values.  This translation unit
+// is compiled with -fmad=false: FP64 expressions below are never contracted (the x86 oracle is built
+// with -ffp-contract=off), FP32 filter code asks for FMAs explicitly with __fmaf_rn.
+//
+// "RE/" = /root/reference/RaytracingEngine/.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/rte.h"
+
+namespace rte {
+
+// ------------------------------------------------------------------------------ device scene
+struct DevPlane {   // Plane, RE/Shape.h:135-147: normal already normalised in FP64 (ctor :142)
+    double n[3];
+    double p0[3];
+    int32_t mat;
+    int32_t pad;
+};
+struct DevLight {   // Light, RE/Light.h:6-12; E = color * intensity (RE/Scene.h:110)
+    double pos[3];
+    double E[3];
+};
+struct DevTri64 {   // Triangle, RE/Shape.h:198-227, evaluated once on the host in FP64:
+    double a0[3];   //   a0 = v0 + T
+    double e1[3];   //   e1 = (v1 + T) - a0
+    double e2[3];   //   e2 = (v2 + T) - a0
+    double n[3];    //   normalize((v1 - v0) x (v2 - v0))  — from the untranslated vertices
+};
+
+struct DevScene {
+    // FP32 filter arrays (sources of the TMA bulk copies into shared memory)
+    const float4* sph32;  // {cx, cy, cz, r*r}; padded to a multiple of 4 with never-hit entries
+    const float4* tri32;  // 3 x float4 per triangle: {a0,_}, {e1,_}, {e2,_}; padded to a multiple of 2
+    int32_t ns, ns_pad, nt, nt_pad;
+    // FP64 exact arrays
+    const double4* sph64; // {cx, cy, cz, r}
+    const int32_t* sph_mat;
+    const DevPlane* planes;
+    const DevTri64* tri64;
+    const int2* tri_info; // {material, reported index (triangle index or MODEL index, RE/Shape.h:276)}
+    const rte_material* materials;  // nm entries + one default Material at index nm
+    const DevLight* lights;
+    int32_t np, nm, nl, pad0;
+    // bounds used by the filter margins
+    float sph_extent;  // max_i(|C_i| + r_i)
+    float tri_extent;  // max |vertex|
+    float tri_edge;    // max edge length
+    float pad1;
+};
+
+struct DevCamera {  // Camera, RE/Math.h:85-97
+    double pos[3];
+    double focal;
+    double half_w, half_h;  // double(width)/2.0, double(height)/2.0 (RE/Math.h:100-101)
+    int32_t width, height;
+};
+
+// ------------------------------------------------------------------------------ Vec3 (FP64)
+struct d3 { double x, y, z; };
+
+__device__ __forceinline__ d3 mk(double x, double y, double z) { d3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ d3 ld3(const double* p) { return mk(p[0], p[1], p[2]); }
+__device__ __forceinline__ d3 operator+(d3 a, d3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }   // RE/Math.h:14
+__device__ __forceinline__ d3 operator-(d3 a, d3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }   // :16
+__device__ __forceinline__ d3 operator*(d3 a, double s) { return mk(a.x * s, a.y * s, a.z * s); }      // :18
+__device__ __forceinline__ d3 operator*(d3 a, d3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }   // :19
+__device__ __forceinline__ d3 operator/(d3 a, double s) { return mk(a.x / s, a.y / s, a.z / s); }      // :21
+__device__ __forceinline__ d3 operator/(d3 a, d3 b) { return mk(a.x / b.x, a.y / b.y, a.z / b.z); }   // :20
+__device__ __forceinline__ d3 operator-(d3 a) { return mk(-a.x, -a.y, -a.z); }                         // :23
+__device__ __forceinline__ d3 adds(d3 a, double s) { return mk(a.x + s, a.y + s, a.z + s); }           // :15
+__device__ __forceinline__ d3 subs(d3 a, double s) { return mk(a.x - s, a.y - s, a.z - s); }           // :17
+__device__ __forceinline__ double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }        // :27
+__device__ __forceinline__ d3 cross(d3 a, d3 b) {                                                       // :28
+    return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__device__ __forceinline__ double length(d3 a) { return sqrt(dot(a, a)); }                             // :30
+__device__ __forceinline__ d3 normalize(d3 a) {                                                         // :31-37
+    const double len = length(a);
+    if (len <= 1e-12) return mk(0.0, 0.0, 0.0);
+    return a / len;
+}
+__device__ __forceinline__ d3 reflect(d3 i, d3 n) { return i - (n * 2.0) * dot(i, n); }                // :39-41
+__device__ __forceinline__ double std_max(double a, double b) { return (a < b) ? b : a; }              // std::max
+__device__ __forceinline__ double std_min(double a, double b) { return (b < a) ? b : a; }              // std::min
+__device__ __forceinline__ double std_clamp(double v, double lo, double hi) { return (v < lo) ? lo : (hi < v) ? hi : v; }
+
+// Camera::getRay(px, py, false), RE/Math.h:99-121
+__device__ __forceinline__ d3 camera_dir(const DevCamera& c, int px, int py) {
+    double sx = (double)px - c.half_w;
+    double sy = c.half_h - (double)py;
+    const d3 screen = mk(sx, sy, c.pos[2] + c.focal);
+    return normalize(screen - ld3(c.pos));
+}
+
+// ------------------------------------------------------------------------------ exact primitive tests
+// Sphere::Intersect, RE/Shape.h:72-98
+__device__ __forceinline__ bool sphere_exact(const double4 s, d3 o, d3 d, double& t_out) {
+    const d3 oc = o - mk(s.x, s.y, s.z);
+    const double a = dot(d, d);
+    const double b = 2.0 * dot(oc, d);
+    const double c = dot(oc, oc) - s.w * s.w;
+    const double disc = b * b - 4.0 * a * c;
+    if (disc < 0.0) return false;
+    const double sq = sqrt(disc);
+    double t0 = (-b - sq) / (2.0 * a);
+    double t1 = (-b + sq) / (2.0 * a);
+    if (t0 > t1) { const double tmp = t0; t0 = t1; t1 = tmp; }
+    double t = t0;
+    if (t < 1e-6) { t = t1; if (t < 1e-6) return false; }
+    t_out = t;
+    return true;
+}
+// Plane::Intersect, RE/Shape.h:149-159
+__device__ __forceinline__ bool plane_exact(const DevPlane& p, d3 o, d3 d, double& t_out) {
+    const d3 n = ld3(p.n);
+    const double denom = dot(n, d);
+    if (fabs(denom) > 1e-6) {
+        const d3 p0l0 = ld3(p.p0) - o;
+        const double t = dot(p0l0, n) / denom;
+        if (t >= 0.0) { t_out = t; return true; }
+    }
+    return false;
+}
+// Triangle::Intersect, RE/Shape.h:202-220 (a0/e1/e2 are the host-evaluated :204-206)
+__device__ __forceinline__ bool tri_exact(const DevTri64& tr, d3 o, d3 d, double& t_out) {
+    const d3 e1 = ld3(tr.e1), e2 = ld3(tr.e2);
+    const d3 h = cross(d, e2);
+    const double a = dot(e1, h);
+    if (a > -1e-6 && a < 1e-6) return false;
+    const double f = 1.0 / a;
+    const d3 s = o - ld3(tr.a0);
+    const double u = f * dot(s, h);
+    if (u < 0.0 || u > 1.0) return false;
+    const d3 q = cross(s, e1);
+    const double v = f * dot(d, q);
+    if (v < 0.0 || u + v > 1.0) return false;
+    const double t = f * dot(e2, q);
+    if (t > 1e-6) { t_out = t; return true; }
+    return false;
+}
+
+constexpr uint32_t kMiss = 0xFFFFFFFFu;
+constexpr float kEps32 = 5.9604645e-8f;  // 2^-24
+
+}  // namespace rte

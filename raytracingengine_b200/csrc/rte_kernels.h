@@ -1,0 +1,52 @@
+// rte_kernels.h — host-visible launch interface of the CUDA kernels (internal to librte_b200.so).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "rte_device.cuh"
+
+namespace rte {
+
+enum StatSlot {
+    kStatPrimary = 0, kStatShadow, kStatSecondary, kStatSphTests, kStatPlTests, kStatTriTests,
+    kStatMarches, kStatConfirms, kStatCount
+};
+
+struct RenderParams {
+    DevScene sc;
+    DevCamera cam;
+    int32_t row0, row1;      // band [row0,row1)
+    int32_t max_depth;       // Scene::maxRecursion, RE/Scene.h:24
+    int32_t tonemap_op;      // RTE_TM_* or RTE_TM_NONE
+    int32_t exact_shadows;   // RTE_FLAG_EXACT_SHADOWS: every shadow ray takes the literal march
+    int32_t no_filter;       // RTE_FLAG_NO_FILTER: FP32 filters accept everything
+    double bias, max_white, jodie_a;
+    rte_frame out;           // device pointers, any may be NULL
+    unsigned int* tile_counter;        // zeroed before launch
+    unsigned long long* stats;         // kStatCount counters, zeroed before launch
+};
+
+// dynamic shared memory the render / query kernels need for this scene (FP32 filter arrays)
+size_t scene_smem_bytes(const DevScene& sc);
+// largest dynamic shared memory size the device allows per block (opt-in)
+cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream);
+
+// Scene::IntersectClosest / IntersectAnyBefore for a batch of rays (device arrays)
+cudaError_t launch_intersect_closest(const DevScene& sc, int64_t n, const double* origins, const double* dirs,
+                                     rte_hit* hits, int sm_count, cudaStream_t stream);
+cudaError_t launch_intersect_any_before(const DevScene& sc, int64_t n, const double* origins, const double* dirs,
+                                        const double* max_dist, uint8_t* out, int sm_count, cudaStream_t stream);
+
+// tonemapAll / tonemap over a float4 HDR buffer (stand-alone HBM-bound pass)
+struct TonemapParams {
+    const float4* hdr;
+    int64_t n_pixels;
+    uint32_t op_mask;
+    float max_white, jodie_a;
+    uint8_t* rgb8[RTE_TM_COUNT];
+};
+cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t stream);
+// max luminance (RE/RaytracingEngine.cpp:100-104) into *out (device float, bit pattern max as uint)
+cudaError_t launch_max_luminance(const float4* hdr, int64_t n_pixels, unsigned int* out_bits, int sm_count,
+                                 cudaStream_t stream);
+
+}  // namespace rte

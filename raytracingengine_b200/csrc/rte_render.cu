@@ -1,0 +1,382 @@
+// rte_render.cu — the per-pixel render kernel (sm_100a).
+//
+// Replaces Scene::RenderImage / GeneratePixelAt / TraceRay / directLightning
+// (RE/Scene.h:311-328, 283-304, 131-198, 79-129; "RE/" = /root/reference/RaytracingEngine/).
+//
+//  * persistent grid (a multiple of the SM count), every warp owns one 8x4 pixel tile at a time and
+//    pulls the next one from a global atomic counter (sky rows are cheap, sphere-dense rows are not);
+//  * the FP32 filter arrays of the scene are staged once per CTA into shared memory with 1-D TMA
+//    bulk copies (cp.async.bulk + mbarrier complete_tx);
+//  * per pixel the ray state is FP64 (bit-identical to the reference's doubles), the O(primitives)
+//    loops are FP32 FMA filters (rte_trace.cuh);
+//  * reflection (material.specular) is an iterative loop; refraction is rejected at upload time.
+#include "rte_kernels.h"
+#include "rte_tonemap.cuh"
+#include "rte_trace.cuh"
+
+namespace rte {
+
+// ------------------------------------------------------------------------------ TMA / mbarrier
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(phase)
+            : "memory");
+    }
+}
+
+constexpr uint32_t kTmaChunk = 32768;
+
+size_t scene_smem_bytes(const DevScene& sc) { return (size_t)sc.ns_pad * 16 + (size_t)sc.nt_pad * 48; }
+
+// Stage {sph32, tri32} into dynamic shared memory.  Called by every thread of the CTA.
+__device__ __forceinline__ void stage_scene(const DevScene& sc, unsigned char* dyn, uint64_t* bar,
+                                            const float4*& s_sph, const float4*& s_tri) {
+    const uint32_t sph_bytes = (uint32_t)sc.ns_pad * 16u, tri_bytes = (uint32_t)sc.nt_pad * 48u;
+    s_sph = reinterpret_cast<const float4*>(dyn);
+    s_tri = reinterpret_cast<const float4*>(dyn + sph_bytes);
+    if (threadIdx.x == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(bar, sph_bytes + tri_bytes);
+        for (uint32_t off = 0; off < sph_bytes; off += kTmaChunk)
+            tma_bulk_g2s(dyn + off, reinterpret_cast<const unsigned char*>(sc.sph32) + off, min(kTmaChunk, sph_bytes - off), bar);
+        for (uint32_t off = 0; off < tri_bytes; off += kTmaChunk)
+            tma_bulk_g2s(dyn + sph_bytes + off, reinterpret_cast<const unsigned char*>(sc.tri32) + off, min(kTmaChunk, tri_bytes - off), bar);
+    }
+    mbar_wait(bar, 0);
+}
+
+// Scene::backgroundColor, RE/Scene.h:30-33
+__device__ __forceinline__ d3 background(d3 dir) {
+    const double t = 0.5 * (normalize(dir).y + 1.0);
+    return mk(1.0, 1.0, 1.0) * (1.0 - t) + mk(0.5, 0.7, 1.0) * t;
+}
+
+struct PixelCounters {
+    uint32_t shadow, secondary, sph, pl, tri, marches, confirms;
+};
+
+// TraceRay for one pixel, all 32 lanes of the warp in lock step (lanes outside the image: alive=false).
+__device__ __forceinline__ d3 trace_pixel(const RenderParams& P, const DevScene& sc, const float4* s_sph,
+                                          const float4* s_tri, int px, int py, bool inb, int64_t out_idx,
+                                          PixelCounters& cnt) {
+    d3 o = ld3(P.cam.pos);
+    d3 d = camera_dir(P.cam, px, py);
+    d3 acc = mk(0.0, 0.0, 0.0);
+    double w = 1.0;
+    bool alive = inb;
+    const double bias = P.bias;
+    const int max_depth = P.max_depth, nl = sc.nl;
+    const bool nf = P.no_filter != 0;
+#pragma unroll 1
+    for (int depth = 0; depth < max_depth; ++depth) {
+        if (!__any_sync(kFullMask, alive)) break;
+        Hit h;
+        closest_hit_body(sc, s_sph, s_tri, o, d, alive, nf, h, cnt.confirms);
+        if (alive) {
+            cnt.sph += (uint32_t)sc.ns; cnt.pl += (uint32_t)sc.np; cnt.tri += (uint32_t)sc.nt;
+            if (depth > 0) cnt.secondary += 1;
+        }
+        const bool hitv = alive && h.kind != RTE_HIT_NONE;
+        if (alive && !hitv) {
+            acc = acc + background(d) * w;
+            alive = false;
+        }
+        // hit record (GetHitInfoAt, RE/Shape.h:104-121,165-180,229-243)
+        d3 Pn = mk(0, 0, 0), ng = mk(0, 0, 0);
+        int mat = sc.nm;
+        uint32_t report = 0;
+        if (hitv) {
+            Pn = o + d * h.t;
+            mat = material_of(sc, h);
+            if (h.kind == RTE_HIT_SPHERE) {
+                const double4 s = sc.sph64[h.idx];
+                ng = normalize(Pn - mk(s.x, s.y, s.z));
+                report = h.idx;
+            } else if (h.kind == RTE_HIT_PLANE) {
+                ng = ld3(sc.planes[h.idx].n);
+                report = h.idx;
+            } else {
+                ng = ld3(sc.tri64[h.idx].n);
+                report = (uint32_t)sc.tri_info[h.idx].y;
+            }
+        }
+        const rte_material& M = sc.materials[mat];
+        // TraceRay, RE/Scene.h:144-148
+        const d3 incoming = normalize(d);
+        const bool frontFace = dot(ng, incoming) < 0.0;
+        const d3 N = frontFace ? ng : -ng;
+        const d3 viewDir = -incoming;
+        // directLightning, RE/Scene.h:79-129
+        const d3 normal = normalize(N);
+        d3 diffuseAcc = mk(0, 0, 0), specAcc = mk(0, 0, 0);
+        uint32_t lmask = 0;
+        const bool want_spec = hitv && M.transparency <= 0.0 && M.specular > 0.0;
+#pragma unroll 1
+        for (int j = 0; j < nl; ++j) {
+            const d3 Lp = ld3(sc.lights[j].pos);
+            const d3 vecToLight = Lp - Pn;
+            const double dist = length(vecToLight);
+            bool cast = hitv && dist > 0.0;
+            d3 L = mk(0, 0, 1);
+            double ndl = 0.0;
+            if (cast) {
+                L = vecToLight / dist;
+                ndl = std_max(0.0, dot(normal, L));
+                cast = ndl > 0.0 && dist > bias;
+            }
+            if (!__any_sync(kFullMask, cast)) continue;
+            const d3 so = Pn + normal * bias;
+            const double maxDist = dist - bias;
+            double T = 1.0;
+            if (P.exact_shadows) {
+                if (cast) { T = march_exact(sc, s_sph, s_tri, so, L, maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
+            } else {
+                const OccResult r = occluded(sc, s_sph, s_tri, so, L, maxDist, bias, cast, nf, cnt.confirms);
+                cnt.sph += r.sph_tests; cnt.pl += r.pl_tests; cnt.tri += r.tri_tests;
+                if (cast) {
+                    if (r.near) { T = march_exact(sc, s_sph, s_tri, so, L, maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
+                    else T = r.occluded ? 0.0 : 1.0;
+                }
+            }
+            if (cast) {
+                cnt.shadow += 1;
+                if (j < 16) lmask |= 1u << (16 + j);
+                if (T > bias) {
+                    if (j < 16) lmask |= 1u << j;
+                    const d3 emitted = ld3(sc.lights[j].E);
+                    const d3 contribution = (emitted * (1.0 / (dist * dist))) * ndl;
+                    diffuseAcc = diffuseAcc + contribution * T;
+                    if (want_spec) {
+                        const d3 H = normalize(L + viewDir);
+                        const double ndh = std_max(0.0, dot(normal, H));
+                        if (ndh > 0.0) {
+                            const double specFactor = pow(ndh, M.shininess);
+                            specAcc = specAcc + ((emitted * (1.0 / (dist * dist))) * specFactor) * T;
+                        }
+                    }
+                }
+            }
+        }
+        if (hitv) {
+            const d3 local = ld3(M.color) * diffuseAcc + specAcc * M.specular;
+            // finalLight += localLight * (1.0 - transparency), transparency == 0 (RE/Scene.h:171-173)
+            acc = acc + (local * (1.0 - 0.0)) * w;
+        }
+        if (depth == 0 && inb) {  // AOVs of the primary hit
+            if (P.out.prim_id) P.out.prim_id[out_idx] = hitv ? ((h.kind << 30) | report) : kMiss;
+            if (P.out.depth) P.out.depth[out_idx] = hitv ? (float)h.t : INFINITY;
+            if (P.out.depth64) P.out.depth64[out_idx] = hitv ? h.t : (double)INFINITY;
+            if (P.out.normal) reinterpret_cast<float4*>(P.out.normal)[out_idx] = make_float4((float)ng.x, (float)ng.y, (float)ng.z, 0.f);
+            if (P.out.albedo) {
+                const d3 a = hitv ? ld3(M.color) : background(d);
+                reinterpret_cast<float4*>(P.out.albedo)[out_idx] = make_float4((float)a.x, (float)a.y, (float)a.z, 0.f);
+            }
+            if (P.out.light_mask) P.out.light_mask[out_idx] = lmask;
+        }
+        // reflection, RE/Scene.h:189-195 (transparency == 0: reflectiveness = material.specular)
+        if (hitv && M.specular > bias) {
+            const d3 R = normalize(reflect(incoming, N));
+            w = w * M.specular;
+            o = Pn + R * bias;
+            d = R;
+        } else {
+            alive = false;
+        }
+    }
+    if (alive) acc = acc + background(d) * w;  // TraceRay(depth >= maxRecursion), RE/Scene.h:132-134
+    return acc;
+}
+
+// ------------------------------------------------------------------------------ the kernel
+constexpr int kRenderThreads = 256;
+constexpr int kTileW = 8, kTileH = 4;  // one warp = 8x4 pixels (coherent primary and shadow rays)
+
+__global__ void __launch_bounds__(kRenderThreads, 2) render_kernel(const __grid_constant__ RenderParams P) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ DevScene s_sc;
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ unsigned long long s_stats[kRenderThreads / 32][kStatCount];
+
+    if (threadIdx.x == 0) s_sc = P.sc;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane < kStatCount) s_stats[warp][lane] = 0ull;
+    const float4 *s_sph, *s_tri;
+    stage_scene(P.sc, dyn_smem, &s_bar, s_sph, s_tri);  // contains __syncthreads: s_sc visible after it
+    const DevScene& sc = s_sc;
+
+    const int W = P.cam.width, rows = P.row1 - P.row0;
+    const int tiles_x = (W + kTileW - 1) / kTileW, tiles_y = (rows + kTileH - 1) / kTileH;
+    const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
+    const int lx = lane & (kTileW - 1), ly = lane >> 3;
+
+    unsigned int tile = 0;
+    if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
+    tile = __shfl_sync(kFullMask, tile, 0);
+    while (tile < n_tiles) {
+        unsigned int next = 0;
+        if (lane == 0) next = atomicAdd(P.tile_counter, 1u);  // prefetch the next tile id behind the work
+        const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
+        const int px = tx * kTileW + lx, band_y = ty * kTileH + ly, py = P.row0 + band_y;
+        const bool inb = px < W && band_y < rows;
+        const int64_t out_idx = (int64_t)band_y * W + px;
+        PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0};
+        const d3 c = trace_pixel(P, sc, s_sph, s_tri, px, py, inb, out_idx, cnt);
+        if (inb) {
+            if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[out_idx] = make_float4((float)c.x, (float)c.y, (float)c.z, 0.f);
+            if (P.out.hdr64) { P.out.hdr64[3 * out_idx] = c.x; P.out.hdr64[3 * out_idx + 1] = c.y; P.out.hdr64[3 * out_idx + 2] = c.z; }
+            if (P.out.rgb8 && P.tonemap_op >= 0) {
+                const uchar3 q = tm64::to_color(tm64::apply(P.tonemap_op, c, P.max_white, P.jodie_a));
+                P.out.rgb8[3 * out_idx] = q.x; P.out.rgb8[3 * out_idx + 1] = q.y; P.out.rgb8[3 * out_idx + 2] = q.z;
+            }
+        }
+        // per-warp statistics: one REDUX per counter, lane 0 accumulates in shared memory
+        const uint32_t v[kStatCount] = {inb ? 1u : 0u, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms};
+#pragma unroll
+        for (int k = 0; k < kStatCount; ++k) {
+            const uint32_t s = __reduce_add_sync(kFullMask, v[k]);
+            if (lane == 0) s_stats[warp][k] += s;
+        }
+        tile = __shfl_sync(kFullMask, next, 0);
+    }
+    __syncwarp();
+    if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
+}
+
+static cudaError_t ensure_smem(const void* fn, size_t bytes) {
+    return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
+cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream) {
+    const size_t smem = scene_smem_bytes(p.sc);
+    cudaError_t e = ensure_smem((const void*)render_kernel, smem);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel, kRenderThreads, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorInvalidConfiguration;
+    const int W = p.cam.width, rows = p.row1 - p.row0;
+    const long long n_tiles = (long long)((W + kTileW - 1) / kTileW) * ((rows + kTileH - 1) / kTileH);
+    long long blocks = (long long)sm_count * per_sm;  // persistent: a multiple of the SM count
+    const long long needed = (n_tiles + kRenderThreads / 32 - 1) / (kRenderThreads / 32);
+    if (blocks > needed) blocks = needed > 0 ? needed : 1;
+    render_kernel<<<(unsigned)blocks, kRenderThreads, smem, stream>>>(p);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------ ray queries
+struct QueryParams {
+    DevScene sc;
+    int64_t n;
+    const double* origins;
+    const double* dirs;
+    const double* max_dist;
+    rte_hit* hits;
+    uint8_t* any_out;
+};
+
+// Scene::IntersectClosest, RE/Scene.h:218-257, one ray per thread
+__global__ void __launch_bounds__(kRenderThreads, 2) closest_kernel(const __grid_constant__ QueryParams Q) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ DevScene s_sc;
+    __shared__ __align__(8) uint64_t s_bar;
+    if (threadIdx.x == 0) s_sc = Q.sc;
+    const float4 *s_sph, *s_tri;
+    stage_scene(Q.sc, dyn_smem, &s_bar, s_sph, s_tri);
+    const DevScene& sc = s_sc;
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < Q.n; base += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = base + threadIdx.x;
+        const bool alive = i < Q.n;
+        const d3 o = alive ? ld3(Q.origins + 3 * i) : mk(0, 0, 0);
+        const d3 d = alive ? ld3(Q.dirs + 3 * i) : mk(0, 0, 1);
+        Hit h;
+        uint32_t confirms = 0;
+        closest_hit_body(sc, s_sph, s_tri, o, d, alive, false, h, confirms);
+        if (!alive) continue;
+        rte_hit out;
+        out.distance = INFINITY; out.prim_id = kMiss; out.material = -1;
+        out.normal[0] = out.normal[1] = out.normal[2] = 0.0;
+        out.point[0] = out.point[1] = out.point[2] = 0.0;
+        if (h.kind != RTE_HIT_NONE) {
+            const d3 Pn = o + d * h.t;
+            d3 ng;
+            uint32_t report = h.idx;
+            if (h.kind == RTE_HIT_SPHERE) { const double4 s = sc.sph64[h.idx]; ng = normalize(Pn - mk(s.x, s.y, s.z)); }
+            else if (h.kind == RTE_HIT_PLANE) ng = ld3(sc.planes[h.idx].n);
+            else { ng = ld3(sc.tri64[h.idx].n); report = (uint32_t)sc.tri_info[h.idx].y; }
+            out.distance = h.t;
+            out.normal[0] = ng.x; out.normal[1] = ng.y; out.normal[2] = ng.z;
+            out.point[0] = Pn.x; out.point[1] = Pn.y; out.point[2] = Pn.z;
+            out.prim_id = (h.kind << 30) | report;
+            const int m = material_of(sc, h);
+            out.material = m < sc.nm ? m : -1;
+        }
+        Q.hits[i] = out;
+    }
+}
+
+// Scene::IntersectAnyBefore, RE/Scene.h:259-276: any primitive reporting 0 < t < maxDist
+__global__ void __launch_bounds__(kRenderThreads, 2) any_before_kernel(const __grid_constant__ QueryParams Q) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ DevScene s_sc;
+    __shared__ __align__(8) uint64_t s_bar;
+    if (threadIdx.x == 0) s_sc = Q.sc;
+    const float4 *s_sph, *s_tri;
+    stage_scene(Q.sc, dyn_smem, &s_bar, s_sph, s_tri);
+    const DevScene& sc = s_sc;
+    for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < Q.n; base += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = base + threadIdx.x;
+        const bool alive = i < Q.n;
+        const d3 o = alive ? ld3(Q.origins + 3 * i) : mk(0, 0, 0);
+        const d3 d = alive ? ld3(Q.dirs + 3 * i) : mk(0, 0, 1);
+        const double md = alive ? Q.max_dist[i] : 0.0;
+        uint32_t confirms = 0;
+        // bias = 0: "t <= bias" can only be a plane at t == 0, which within() rejects as well
+        const OccResult r = occluded(sc, s_sph, s_tri, o, d, md, 0.0, alive, false, confirms);
+        if (alive) Q.any_out[i] = r.occluded ? 1 : 0;
+    }
+}
+
+static cudaError_t launch_query(const void* fn, const QueryParams& q, int sm_count, cudaStream_t stream) {
+    const size_t smem = scene_smem_bytes(q.sc);
+    cudaError_t e = ensure_smem(fn, smem);
+    if (e != cudaSuccess) return e;
+    long long blocks = (q.n + kRenderThreads - 1) / kRenderThreads;
+    if (blocks > 2ll * sm_count) blocks = 2ll * sm_count;
+    if (blocks < 1) blocks = 1;
+    void* args[] = {(void*)&q};
+    return cudaLaunchKernel(fn, dim3((unsigned)blocks), dim3(kRenderThreads), args, smem, stream);
+}
+
+cudaError_t launch_intersect_closest(const DevScene& sc, int64_t n, const double* origins, const double* dirs,
+                                     rte_hit* hits, int sm_count, cudaStream_t stream) {
+    QueryParams q{sc, n, origins, dirs, nullptr, hits, nullptr};
+    return launch_query((const void*)closest_kernel, q, sm_count, stream);
+}
+cudaError_t launch_intersect_any_before(const DevScene& sc, int64_t n, const double* origins, const double* dirs,
+                                        const double* max_dist, uint8_t* out, int sm_count, cudaStream_t stream) {
+    QueryParams q{sc, n, origins, dirs, max_dist, nullptr, out};
+    return launch_query((const void*)any_before_kernel, q, sm_count, stream);
+}
+
+}  // namespace rte

@@ -1,0 +1,111 @@
+// rte_tonemap.cu — stand-alone tonemap / quantise pass over a float4 HDR buffer (sm_100a), HBM-bound.
+//
+// Replaces tonemap() / tonemapAll() + toColor (RE/RaytracingEngine.cpp:113-121,165-214; "RE/" =
+// /root/reference/RaytracingEngine/).  Algorithmic traffic: 12 B read + 3 B written per
+// pixel and operator; all seven operators in one pass = 33 B/px.  The implementation reads the float4
+// (16 B/px) once and writes every selected operator from registers:
+//   * one thread = 4 consecutive pixels: 4 x LDG.128 in, 3 x STG.32 per operator out (12 B, aligned);
+//   * grid = a multiple of the SM count, grid-stride loop, streaming loads (ld.global.cs) because
+//     nothing is re-read.
+#include "rte_kernels.h"
+#include "rte_tonemap.cuh"
+
+namespace rte {
+
+constexpr int kTmThreads = 256;
+
+__device__ __forceinline__ float4 ldg_stream(const float4* p) { return __ldcs(p); }
+
+template <uint32_t kMask>
+__global__ void __launch_bounds__(kTmThreads) tonemap_kernel(const __grid_constant__ TonemapParams P, const tm32::Consts K) {
+    const int64_t n_quads = P.n_pixels >> 2;
+    const uint32_t mask = kMask ? kMask : P.op_mask;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_quads; q += (int64_t)gridDim.x * blockDim.x) {
+        const float4* src = P.hdr + 4 * q;
+        float4 px[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) px[j] = ldg_stream(src + j);
+        uint32_t c[4][RTE_TM_COUNT];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tm32::apply_all<kMask>(tm32::mk3(px[j].x, px[j].y, px[j].z), K, mask, c[j]);
+#pragma unroll
+        for (int op = 0; op < RTE_TM_COUNT; ++op) {
+            if (!(mask & (1u << op))) continue;
+            // 4 pixels x RGB = 12 bytes = 3 aligned words
+            uint32_t* dst = reinterpret_cast<uint32_t*>(P.rgb8[op] + 12 * q);
+            __stcs(dst + 0, c[0][op] | (c[1][op] << 24));
+            __stcs(dst + 1, (c[1][op] >> 8) | (c[2][op] << 16));
+            __stcs(dst + 2, (c[2][op] >> 16) | (c[3][op] << 8));
+        }
+    }
+    // tail (n_pixels % 4) — bytes
+    const int64_t tail0 = n_quads << 2;
+    const int64_t i = tail0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P.n_pixels) {
+        const float4 v = P.hdr[i];
+        uint32_t c[RTE_TM_COUNT];
+        tm32::apply_all<kMask>(tm32::mk3(v.x, v.y, v.z), K, mask, c);
+#pragma unroll
+        for (int op = 0; op < RTE_TM_COUNT; ++op) {
+            if (!(mask & (1u << op))) continue;
+            uint8_t* d = P.rgb8[op] + 3 * i;
+            d[0] = (uint8_t)(c[op] & 255u); d[1] = (uint8_t)((c[op] >> 8) & 255u); d[2] = (uint8_t)((c[op] >> 16) & 255u);
+        }
+    }
+}
+
+static float u2p_host(float x) {
+    const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+    return ((x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F)) - E / F;
+}
+
+cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t stream) {
+    if (p.n_pixels <= 0) return cudaSuccess;
+    tm32::Consts k;
+    k.inv_wsq = 1.0f / (p.max_white * p.max_white);
+    k.jodie_a = p.jodie_a;
+    k.white_scale = 1.0f / u2p_host(11.2f);
+    const int64_t n_quads = (p.n_pixels + 3) / 4;
+    int64_t blocks = (n_quads + kTmThreads - 1) / kTmThreads;
+    const int64_t cap = (int64_t)sm_count * 8;  // 8 resident CTAs of 256 threads per SM
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    constexpr uint32_t kAll = (1u << RTE_TM_COUNT) - 1u;
+    if (p.op_mask == kAll) tonemap_kernel<kAll><<<(unsigned)blocks, kTmThreads, 0, stream>>>(p, k);
+    else if (p.op_mask == (1u << RTE_TM_ACES)) tonemap_kernel<(1u << RTE_TM_ACES)><<<(unsigned)blocks, kTmThreads, 0, stream>>>(p, k);
+    else tonemap_kernel<0u><<<(unsigned)blocks, kTmThreads, 0, stream>>>(p, k);
+    return cudaGetLastError();
+}
+
+// max over pixels of luminance() (RE/RaytracingEngine.cpp:100-104); non-negative floats order like their bits
+__global__ void __launch_bounds__(kTmThreads) max_luminance_kernel(const float4* __restrict__ hdr, int64_t n, unsigned int* out_bits) {
+    float m = 0.0f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldcs(hdr + i);
+        m = fmaxf(m, tm32::luminance(tm32::mk3(v.x, v.y, v.z)));  // fmaxf drops NaN
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+    __shared__ float s_m[kTmThreads / 32];
+    if ((threadIdx.x & 31) == 0) s_m[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = threadIdx.x < kTmThreads / 32 ? s_m[threadIdx.x] : 0.0f;
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+        if (threadIdx.x == 0) atomicMax(out_bits, __float_as_uint(fmaxf(m, 0.0f)));
+    }
+}
+
+cudaError_t launch_max_luminance(const float4* hdr, int64_t n_pixels, unsigned int* out_bits, int sm_count, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(out_bits, 0, sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return e;
+    if (n_pixels <= 0) return cudaSuccess;
+    int64_t blocks = (n_pixels + kTmThreads - 1) / kTmThreads;
+    const int64_t cap = (int64_t)sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    max_luminance_kernel<<<(unsigned)blocks, kTmThreads, 0, stream>>>(hdr, n_pixels, out_bits);
+    return cudaGetLastError();
+}
+
+}  // namespace rte

@@ -237,5 +237,4 @@ class Scene:
 
     def RenderImage(self) -> np.ndarray:
         """Scene::RenderImage(), RE/Scene.h:311 — (H*W, 3) float64 linear HDR, rendered on the GPU."""
-        out = self.engine().render_host(hdr64=True)
-        return out["hdr64"].reshape(-1, 3)
+        return self.engine().render_host(outputs=("hdr64",))["hdr64"].reshape(-1, 3)
