@@ -147,6 +147,11 @@ typedef struct rte_render_opts {
     double jodie_a;         /* reinhardJodie(…, a); <= 0 means 0.18 (RE/RaytracingEngine.cpp:150) */
     int32_t spp_seed;       /* counter-based jitter seed when camera.anti_aliasing > 1 */
     int32_t flags;          /* RTE_FLAG_* (validation switches; 0 = production path) */
+    /* Interleaved row stripes (multi-GPU load balance): with stripe_rows > 0 the call
+     * renders rows row0 + k*stripe_period + [0, stripe_rows) for k = 0,1,... that lie below row1, packed
+     * densely in that order into the output buffers.  stripe_rows must be a multiple of 4 and
+     * <= stripe_period.  0 = the contiguous band [row0,row1). */
+    int32_t stripe_rows, stripe_period;
 } rte_render_opts;
 
 /* Validation switches for rte_render_opts.flags.  Both must leave every output bit-identical:
@@ -239,6 +244,11 @@ int rte_tonemap_host(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t 
 /* Max of luminance() (RE/RaytracingEngine.cpp:100-104) over a device HDR buffer; the per-rank
  * value that an auto-max-white run all-reduces (MAX) across GPUs. Result on the host. */
 int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max);
+
+/* Measurement aid (no reference counterpart): runs a register-resident FFMA kernel on every SM of the
+ * ctx device for about `target_ms` and reports the achieved FP32 rate — the measured FP32-FMA roofline
+ * denominator bench.py quotes the render kernel against (MEASURED_PEAKS.json has none). */
+int rte_measure_fp32_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms);
 
 /* Scene::IntersectClosest(ray), RE/Scene.h:218-257, for a batch of rays (host arrays:
  * origins/directions = xyz triples).  hits[i].prim_id == 0xFFFFFFFF means std::nullopt. */

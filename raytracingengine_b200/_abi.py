@@ -83,7 +83,8 @@ class SceneDesc(C.Structure):  # the vectors of Scene, RE/Scene.h:17-23
 class RenderOpts(C.Structure):
     _fields_ = [("row0", C.c_int32), ("row1", C.c_int32), ("max_depth", C.c_int32),
                 ("tonemap_op", C.c_int32), ("bias", C.c_double), ("max_white", C.c_double),
-                ("jodie_a", C.c_double), ("spp_seed", C.c_int32), ("flags", C.c_int32)]
+                ("jodie_a", C.c_double), ("spp_seed", C.c_int32), ("flags", C.c_int32),
+                ("stripe_rows", C.c_int32), ("stripe_period", C.c_int32)]
 
 
 class Frame(C.Structure):
@@ -104,7 +105,7 @@ class Stats(C.Structure):
 
 
 assert C.sizeof(Camera) == 72 and C.sizeof(SceneDesc) == 128
-assert C.sizeof(RenderOpts) == 48 and C.sizeof(Frame) == 72 and C.sizeof(Stats) == 80
+assert C.sizeof(RenderOpts) == 56 and C.sizeof(Frame) == 72 and C.sizeof(Stats) == 80
 
 # algorithmic flops per ray-primitive test
 FLOP_SPHERE, FLOP_PLANE, FLOP_TRIANGLE = 20, 14, 46

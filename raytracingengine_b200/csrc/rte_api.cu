@@ -133,6 +133,7 @@ inline bool finite3(const double* p) { return std::isfinite(p[0]) && std::isfini
 
 struct Defaults {
     int max_depth; int tonemap_op; double bias, max_white, jodie_a; int row0, row1; uint32_t flags;
+    int stripe_rows, stripe_period, n_rows;
 };
 
 int resolve_opts(rte_ctx* ctx, const rte_render_opts* o, Defaults& d) {
@@ -147,6 +148,15 @@ int resolve_opts(rte_ctx* ctx, const rte_render_opts* o, Defaults& d) {
     d.flags = o ? (uint32_t)o->flags : 0u;
     if (d.row0 < 0 || d.row1 > H || d.row0 > d.row1)
         return fail(ctx, RTE_ERR_INVALID, "row band [%d,%d) outside the camera image (height %d)", d.row0, d.row1, H);
+    d.stripe_rows = o ? o->stripe_rows : 0;
+    d.stripe_period = o ? o->stripe_period : 0;
+    d.n_rows = d.row1 - d.row0;
+    if (d.stripe_rows != 0) {
+        if (d.stripe_rows < 0 || d.stripe_rows % 4 || d.stripe_period < d.stripe_rows)
+            return fail(ctx, RTE_ERR_INVALID, "stripe_rows %d must be a positive multiple of 4 and <= stripe_period %d", d.stripe_rows, d.stripe_period);
+        const int span = d.row1 - d.row0, full = span / d.stripe_period, rem = span % d.stripe_period;
+        d.n_rows = full * d.stripe_rows + (rem < d.stripe_rows ? rem : d.stripe_rows);
+    }
     if (d.tonemap_op < RTE_TM_NONE || d.tonemap_op >= RTE_TM_COUNT)
         return fail(ctx, RTE_ERR_INVALID, "tonemap_op %d is not an RTE_TM_* value", d.tonemap_op);
     return RTE_OK;
@@ -411,7 +421,7 @@ extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
 static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
     RenderParams p{};
     p.sc = ctx->sc; p.cam = ctx->cam;
-    p.row0 = o.row0; p.row1 = o.row1; p.max_depth = o.max_depth; p.tonemap_op = o.tonemap_op;
+    p.row0 = o.row0; p.row1 = o.row1; p.n_rows = o.n_rows; p.stripe_rows = o.stripe_rows; p.stripe_period = o.stripe_period; p.max_depth = o.max_depth; p.tonemap_op = o.tonemap_op;
     p.exact_shadows = (o.flags & RTE_FLAG_EXACT_SHADOWS) ? 1 : 0;
     p.no_filter = (o.flags & RTE_FLAG_NO_FILTER) ? 1 : 0;
     p.bias = o.bias; p.max_white = o.max_white; p.jodie_a = o.jodie_a;
@@ -421,7 +431,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
     RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));
     RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * kStatCount, ctx->stream));
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
-    if (o.row1 > o.row0) RTE_CUDA(ctx, launch_render(p, ctx->sm_count, ctx->stream));
+    if (o.n_rows > 0) RTE_CUDA(ctx, launch_render(p, ctx->sm_count, ctx->stream));
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
     RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));
     ctx->render_timed = true;
@@ -445,7 +455,7 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
     Defaults o;
     int rc = resolve_opts(ctx, opts, o);
     if (rc) return rc;
-    const size_t n = (size_t)(o.row1 - o.row0) * (size_t)ctx->cam.width;
+    const size_t n = (size_t)o.n_rows * (size_t)ctx->cam.width;
     rte_frame df{};
     struct Item { void* host; DevBuf* buf; size_t bytes; void** dev; };
     Item items[] = {
@@ -557,6 +567,36 @@ extern "C" int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixel
     return RTE_OK;
 }
 
+// ====================================================================================== FP32 peak
+extern "C" int rte_measure_fp32_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms) {
+    RTE_ENTER(ctx);
+    if (!out_tflops) return fail(ctx, RTE_ERR_INVALID, "rte_measure_fp32_peak: out_tflops is NULL");
+    if (!(target_ms > 0)) target_ms = 20.0;
+    int rc = reserve(ctx, ctx->s_q_out, (size_t)ctx->sm_count * 8 * 256 * sizeof(float));
+    if (rc) return rc;
+    double flop = 0.0, best_tf = 0.0, best_ms = 0.0;
+    int outer = 256;
+    for (int pass = 0; pass < 4; ++pass) {  // pass 0 calibrates `outer`, the best of the other three is reported
+        RTE_CUDA(ctx, cudaEventRecord(ctx->ev_t0, ctx->stream));
+        RTE_CUDA(ctx, launch_ffma_peak((float*)ctx->s_q_out.p, outer, ctx->sm_count, ctx->stream, &flop));
+        RTE_CUDA(ctx, cudaEventRecord(ctx->ev_t1, ctx->stream));
+        RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        float ms = 0.f;
+        RTE_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_t0, ctx->ev_t1));
+        if (pass == 0) {
+            const double scale = target_ms / (ms > 1e-3f ? ms : 1e-3f);
+            outer = (int)std::fmin(1.0e6, std::fmax(64.0, outer * scale));
+            continue;
+        }
+        const double tf = flop / (ms * 1e-3) / 1e12;
+        if (tf > best_tf) { best_tf = tf; best_ms = ms; }
+    }
+    ctx->tonemap_timed = false;  // ev_t0/ev_t1 no longer bracket a tonemap launch
+    *out_tflops = best_tf;
+    if (out_ms) *out_ms = best_ms;
+    return RTE_OK;
+}
+
 // ====================================================================================== ray queries
 extern "C" int rte_intersect_closest(rte_ctx* ctx, int64_t n, const double* origins, const double* directions, rte_hit* hits) {
     RTE_ENTER(ctx);
@@ -644,7 +684,7 @@ extern "C" int rte_free_host(void* host) {
 // writePPM, RE/Image.cpp:11-31: "P6\n<W> <H>\n255\n" + W*H RGB triplets; the reference streams one char at
 // a time, this is one fwrite from the caller's (pinned) buffer.  Error texts are the reference's.
 extern "C" int rte_write_ppm(const char* filename, const uint8_t* rgb8, uint64_t width, uint64_t height) {
-    if (!filename || (!rgb8 && width * height)) return fail(nullptr, RTE_ERR_INVALID, "rte_write_ppm: NULL argument");
+    if (!filename || (!rgb8 && width != 0 && height != 0)) return fail(nullptr, RTE_ERR_INVALID, "rte_write_ppm: NULL argument");
     FILE* f = std::fopen(filename, "wb");
     if (!f) return fail(nullptr, RTE_ERR_IO, "Could not open file for writing");
     const size_t n = (size_t)width * (size_t)height * 3;

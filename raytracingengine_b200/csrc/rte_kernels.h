@@ -15,6 +15,8 @@ struct RenderParams {
     DevScene sc;
     DevCamera cam;
     int32_t row0, row1;      // band [row0,row1)
+    int32_t n_rows;          // rows this launch renders (== row1-row0 unless striped)
+    int32_t stripe_rows, stripe_period;  // interleaved stripes (0 = contiguous), see rte_render_opts
     int32_t max_depth;       // Scene::maxRecursion, RE/Scene.h:24
     int32_t tonemap_op;      // RTE_TM_* or RTE_TM_NONE
     int32_t exact_shadows;   // RTE_FLAG_EXACT_SHADOWS: every shadow ray takes the literal march
@@ -48,5 +50,8 @@ cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t st
 // max luminance (RE/RaytracingEngine.cpp:100-104) into *out (device float, bit pattern max as uint)
 cudaError_t launch_max_luminance(const float4* hdr, int64_t n_pixels, unsigned int* out_bits, int sm_count,
                                  cudaStream_t stream);
+
+// register-resident FFMA chains on every SM (rte_peak.cu): *flop_out = FP32 flop the launch executes
+cudaError_t launch_ffma_peak(float* scratch, int outer, int sm_count, cudaStream_t stream, double* flop_out);
 
 }  // namespace rte

@@ -225,7 +225,8 @@ __global__ void __launch_bounds__(kRenderThreads, 2) render_kernel(const __grid_
     stage_scene(P.sc, dyn_smem, &s_bar, s_sph, s_tri);  // contains __syncthreads: s_sc visible after it
     const DevScene& sc = s_sc;
 
-    const int W = P.cam.width, rows = P.row1 - P.row0;
+    const int W = P.cam.width, rows = P.n_rows;
+    const int sr = P.stripe_rows, sp = P.stripe_period;
     const int tiles_x = (W + kTileW - 1) / kTileW, tiles_y = (rows + kTileH - 1) / kTileH;
     const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
     const int lx = lane & (kTileW - 1), ly = lane >> 3;
@@ -237,7 +238,8 @@ __global__ void __launch_bounds__(kRenderThreads, 2) render_kernel(const __grid_
         unsigned int next = 0;
         if (lane == 0) next = atomicAdd(P.tile_counter, 1u);  // prefetch the next tile id behind the work
         const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
-        const int px = tx * kTileW + lx, band_y = ty * kTileH + ly, py = P.row0 + band_y;
+        const int px = tx * kTileW + lx, band_y = ty * kTileH + ly;
+        const int py = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
         const bool inb = px < W && band_y < rows;
         const int64_t out_idx = (int64_t)band_y * W + px;
         PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0};
@@ -275,7 +277,7 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel, kRenderThreads, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
-    const int W = p.cam.width, rows = p.row1 - p.row0;
+    const int W = p.cam.width, rows = p.n_rows;
     const long long n_tiles = (long long)((W + kTileW - 1) / kTileW) * ((rows + kTileH - 1) / kTileH);
     long long blocks = (long long)sm_count * per_sm;  // persistent: a multiple of the SM count
     const long long needed = (n_tiles + kRenderThreads / 32 - 1) / (kRenderThreads / 32);

@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "librte_b200
 SYMBOLS = (
     "rte_version", "rte_device_count", "rte_last_error", "rte_create", "rte_destroy", "rte_set_stream",
     "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats",
-    "rte_tonemap", "rte_tonemap_host", "rte_max_luminance", "rte_intersect_closest", "rte_intersect_any_before",
+    "rte_tonemap", "rte_tonemap_host", "rte_max_luminance", "rte_measure_fp32_peak", "rte_intersect_closest", "rte_intersect_any_before",
     "rte_malloc", "rte_free", "rte_memcpy_d2h", "rte_memcpy_h2d", "rte_malloc_host", "rte_free_host",
     "rte_write_ppm",
 )
@@ -62,6 +62,7 @@ def load_library() -> C.CDLL:
     lib.rte_tonemap.argtypes = tm_args
     lib.rte_tonemap_host.argtypes = tm_args
     lib.rte_max_luminance.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_float)]
+    lib.rte_measure_fp32_peak.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.rte_intersect_closest.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rte_intersect_any_before.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rte_malloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
@@ -194,12 +195,25 @@ class Engine:
 
     # ---- render
     @staticmethod
-    def _opts(row0=0, row1=0, max_depth=0, tonemap_op=_abi.TM_NONE, bias=0.0, max_white=0.0, jodie_a=0.0, flags=0):
-        return _abi.RenderOpts(row0, row1, max_depth, tonemap_op, bias, max_white, jodie_a, 0, flags)
+    def _opts(row0=0, row1=0, max_depth=0, tonemap_op=_abi.TM_NONE, bias=0.0, max_white=0.0, jodie_a=0.0, flags=0,
+              stripe_rows=0, stripe_period=0):
+        return _abi.RenderOpts(row0, row1, max_depth, tonemap_op, bias, max_white, jodie_a, 0, flags, stripe_rows, stripe_period)
 
-    def band_pixels(self, row0=0, row1=0) -> int:
+    @staticmethod
+    def supports_stripes() -> bool:
+        return True
+
+    @staticmethod
+    def striped_rows(row0: int, row1: int, stripe_rows: int, stripe_period: int) -> int:
+        """Rows a striped call renders (mirrors resolve_opts in rte_api.cu)."""
+        if stripe_rows <= 0:
+            return row1 - row0
+        span = row1 - row0
+        return (span // stripe_period) * stripe_rows + min(span % stripe_period, stripe_rows)
+
+    def band_pixels(self, row0=0, row1=0, stripe_rows=0, stripe_period=0) -> int:
         H, W = self.camera.height, self.camera.width
-        return ((row1 if row1 > 0 else H) - row0) * W
+        return self.striped_rows(row0, row1 if row1 > 0 else H, stripe_rows, stripe_period) * W
 
     def render_device(self, frame_ptrs: Dict[str, int], **opts) -> None:
         """rte_render: asynchronous, `frame_ptrs` maps rte_frame member names to device pointers."""
@@ -211,7 +225,7 @@ class Engine:
 
     def render_host(self, outputs: Iterable[str] = ("hdr",), into: Optional[Dict[str, np.ndarray]] = None, **opts) -> Dict[str, np.ndarray]:
         """rte_render_host: renders and copies the requested rte_frame members to host arrays."""
-        n = self.band_pixels(opts.get("row0", 0), opts.get("row1", 0))
+        n = self.band_pixels(opts.get("row0", 0), opts.get("row1", 0), opts.get("stripe_rows", 0), opts.get("stripe_period", 0))
         o = self._opts(**opts)
         f = _abi.Frame()
         res = {}
@@ -257,6 +271,12 @@ class Engine:
         v = C.c_float()
         self._ck(self.lib.rte_max_luminance(self.ctx, C.c_void_p(hdr_dev), n_pixels, C.byref(v)))
         return float(v.value)
+
+    def measure_fp32_peak(self, target_ms: float = 20.0):
+        """(TFLOP/s, ms) of a register-resident FFMA kernel on this GPU: the FP32 roofline denominator."""
+        tf, ms = C.c_double(), C.c_double()
+        self._ck(self.lib.rte_measure_fp32_peak(self.ctx, target_ms, C.byref(tf), C.byref(ms)))
+        return float(tf.value), float(ms.value)
 
     # ---- ray queries
     def intersect_closest(self, origins, directions) -> np.ndarray:
