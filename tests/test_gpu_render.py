@@ -101,11 +101,16 @@ def test_config4_specular(engine, oracle):
     assert_parity(g, o, exact_hdr=False, hdr_rtol=1e-9)
 
 
-def test_max_depth_and_bias_options(engine, oracle):
+def test_max_depth_and_bias_options(engine, port_oracle):
+    """max_depth / bias are constants in the reference (RE/Scene.h:24,291): only the port checker takes them."""
     arrays, cam = scenes.config1(96, 96)
     engine.upload(arrays, cam)
     g = engine.render_host(outputs=("hdr64",), max_depth=3)
-    o = oracle.render(arrays, cam, max_depth=3)
+    o = port_oracle.render(arrays, cam, max_depth=3)
+    np.testing.assert_allclose(g["hdr64"], o["hdr"], rtol=1e-9, atol=1e-14)
+    g = engine.render_host(outputs=("hdr64", "light_mask"), bias=5e-3)
+    o = port_oracle.render(arrays, cam, bias=5e-3, want_aovs=True)
+    assert np.array_equal(g["light_mask"], o["light_mask"])
     np.testing.assert_allclose(g["hdr64"], o["hdr"], rtol=1e-9, atol=1e-14)
 
 
