@@ -250,6 +250,7 @@ def run_gpu(args) -> None:
             torch.cuda.synchronize()
 
     fp32_peak_tf, _ = eng.measure_fp32_peak(15.0)
+    fp32x2_peak_tf, _ = eng.measure_fp32_peak(15.0, packed=True)
 
     for _ in range(max(args.warmup, 3)):
         flush.zero_()
@@ -351,7 +352,7 @@ def run_gpu(args) -> None:
         "roofline": {"bound": "fp32", "kernel": "rte::render_kernel", "achieved": round(achieved_tf, 3), "peak": round(fp32_peak_tf, 3),
                      "unit": "TFLOP/s", "frac": round(achieved_tf / fp32_peak_tf, 4), "traffic": None,
                      "peak_source": "FFMA micro-benchmark in this process (rte_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
-                     "nominal_peak_at_sampled_clock": round(nominal_tf, 2),
+                     "nominal_peak_at_sampled_clock": round(nominal_tf, 2), "ffma2_peak": round(fp32x2_peak_tf, 3),
                      "algorithmic_flop_per_launch": flops / world, "kernel_ms": round(kern_ms, 4),
                      "tests": {"sphere": sph_t, "plane": pl_t, "triangle": tri_t}, "fp64_confirms": confirms, "exact_marches": marches},
         "roofline_tonemap": {"bound": "hbm", "kernel": "rte::tonemap_kernel<all 7 operators>", "achieved": round(n_px * 33 / (tm_med * 1e-3) / 1e9, 1),

@@ -249,6 +249,8 @@ int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* o
  * ctx device for about `target_ms` and reports the achieved FP32 rate — the measured FP32-FMA roofline
  * denominator bench.py quotes the render kernel against (MEASURED_PEAKS.json has none). */
 int rte_measure_fp32_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms);
+/* The same with packed fma.rn.f32x2 instructions (two FMAs per lane and instruction, sm_100+). */
+int rte_measure_fp32x2_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms);
 
 /* Scene::IntersectClosest(ray), RE/Scene.h:218-257, for a batch of rays (host arrays:
  * origins/directions = xyz triples).  hits[i].prim_id == 0xFFFFFFFF means std::nullopt. */

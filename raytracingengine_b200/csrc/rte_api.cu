@@ -44,7 +44,9 @@ struct rte_ctx {
     DevScene sc{};
     DevCamera cam{};
     rte_camera cam_host{};
-    DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights;
+    DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views;
+    bool views_dirty = true;
+    double views_bias = -1.0;
 
     // launch scratch
     unsigned int* d_tile_counter = nullptr;
@@ -214,7 +216,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
-                      &ctx->b_mats, &ctx->b_lights, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -275,7 +277,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     mats.push_back(def);
 
     // spheres
-    const int ns = (int)d->n_spheres, ns_pad = (ns + 7) & ~7;  // kSphUnroll
+    const int ns = (int)d->n_spheres, ns_pad = (ns + 31) & ~31;  // kViewBlock (a multiple of kSphUnroll)
     std::vector<float4> sph32((size_t)ns_pad);
     std::vector<double4> sph64((size_t)ns_pad);
     std::vector<int32_t> sphmat((size_t)ns_pad, -1);
@@ -376,6 +378,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
                     smem, ns, nt, smem_budget);
 
     int rc;
+    if ((rc = reserve(ctx, ctx->b_views, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
     if ((rc = upload(ctx, ctx->b_sph32, sph32)) || (rc = upload(ctx, ctx->b_sph64, sph64)) || (rc = upload(ctx, ctx->b_sphmat, sphmat)) ||
         (rc = upload(ctx, ctx->b_planes, planes)) || (rc = upload(ctx, ctx->b_tri32, tri32)) || (rc = upload(ctx, ctx->b_tri64, tri64)) ||
         (rc = upload(ctx, ctx->b_triinfo, triinfo)) || (rc = upload(ctx, ctx->b_mats, mats)) || (rc = upload(ctx, ctx->b_lights, lights)))
@@ -384,6 +387,10 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
 
     DevScene& sc = ctx->sc;
     sc.sph32 = (const float4*)ctx->b_sph32.p; sc.tri32 = (const float4*)ctx->b_tri32.p;
+    sc.views = ns > 0 ? (const float*)ctx->b_views.p : nullptr;
+    sc.reflective = 0; sc.pad2 = 0;
+    for (const rte_material& m : mats) if (m.specular > 0.0) sc.reflective = 1;
+    ctx->views_dirty = true;
     sc.ns = ns; sc.ns_pad = ns_pad; sc.nt = nt; sc.nt_pad = nt_pad;
     sc.sph64 = (const double4*)ctx->b_sph64.p; sc.sph_mat = (const int32_t*)ctx->b_sphmat.p;
     sc.planes = (const DevPlane*)ctx->b_planes.p; sc.tri64 = (const DevTri64*)ctx->b_tri64.p;
@@ -414,6 +421,7 @@ extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
     dc.half_h = (double)c->height / 2.0;  // RE/Math.h:101
     dc.width = (int)c->width; dc.height = (int)c->height;
     ctx->has_camera = true;
+    ctx->views_dirty = true;
     return RTE_OK;
 }
 
@@ -421,6 +429,13 @@ extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
 static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
     RenderParams p{};
     p.sc = ctx->sc; p.cam = ctx->cam;
+    const size_t smem_budget = ctx->smem_optin > 4096 ? ctx->smem_optin - 4096 : 0;  // static smem + headroom
+    p.plan = plan_smem(ctx->sc, smem_budget);
+    if (p.plan.use_views && (ctx->views_dirty || ctx->views_bias != o.bias)) {
+        RTE_CUDA(ctx, launch_build_views(ctx->sc, ctx->cam, o.bias, ctx->stream));
+        ctx->views_dirty = false;
+        ctx->views_bias = o.bias;
+    }
     p.row0 = o.row0; p.row1 = o.row1; p.n_rows = o.n_rows; p.stripe_rows = o.stripe_rows; p.stripe_period = o.stripe_period; p.max_depth = o.max_depth; p.tonemap_op = o.tonemap_op;
     p.exact_shadows = (o.flags & RTE_FLAG_EXACT_SHADOWS) ? 1 : 0;
     p.no_filter = (o.flags & RTE_FLAG_NO_FILTER) ? 1 : 0;
@@ -568,7 +583,14 @@ extern "C" int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixel
 }
 
 // ====================================================================================== FP32 peak
+static int measure_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms, int packed);
 extern "C" int rte_measure_fp32_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms) {
+    return measure_peak(ctx, target_ms, out_tflops, out_ms, 0);
+}
+extern "C" int rte_measure_fp32x2_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms) {
+    return measure_peak(ctx, target_ms, out_tflops, out_ms, 1);
+}
+static int measure_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms, int packed) {
     RTE_ENTER(ctx);
     if (!out_tflops) return fail(ctx, RTE_ERR_INVALID, "rte_measure_fp32_peak: out_tflops is NULL");
     if (!(target_ms > 0)) target_ms = 20.0;
@@ -578,7 +600,7 @@ extern "C" int rte_measure_fp32_peak(rte_ctx* ctx, double target_ms, double* out
     int outer = 256;
     for (int pass = 0; pass < 4; ++pass) {  // pass 0 calibrates `outer`, the best of the other three is reported
         RTE_CUDA(ctx, cudaEventRecord(ctx->ev_t0, ctx->stream));
-        RTE_CUDA(ctx, launch_ffma_peak((float*)ctx->s_q_out.p, outer, ctx->sm_count, ctx->stream, &flop));
+        RTE_CUDA(ctx, launch_ffma_peak((float*)ctx->s_q_out.p, outer, ctx->sm_count, ctx->stream, &flop, packed));
         RTE_CUDA(ctx, cudaEventRecord(ctx->ev_t1, ctx->stream));
         RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         float ms = 0.f;

@@ -36,7 +36,10 @@ struct DevTri64 {   // Triangle, RE/Shape.h:198-227, evaluated once on the host 
 
 struct DevScene {
     // FP32 filter arrays (sources of the TMA bulk copies into shared memory)
-    const float4* sph32;  // {cx, cy, cz, r*r}; padded to a multiple of 4 with never-hit entries
+    const float4* sph32;  // {cx, cy, cz, r*r}; padded to a multiple of 32 with never-hit entries
+    const float* views;   // (1+nl) per-origin views of the spheres (rte_views.cuh), rebuilt per camera / bias; may be NULL
+    int32_t reflective;   // some material has specular > 0: reflection rays (generic closest-hit) will be traced
+    int32_t pad2;
     const float4* tri32;  // 3 x float4 per triangle: {a0,_}, {e1,_}, {e2,_}; padded to a multiple of 2
     int32_t ns, ns_pad, nt, nt_pad;
     // FP64 exact arrays

@@ -11,8 +11,18 @@ enum StatSlot {
     kStatMarches, kStatConfirms, kStatCount
 };
 
+// what the render kernel stages into dynamic shared memory (rte_render.cu: plan_smem)
+struct SmemPlan {
+    uint32_t view_bytes, sph_bytes, tri_bytes;
+    int32_t use_views;   // sphere phases of primary / shadow rays go through the per-origin views (rte_views.cuh)
+    int32_t stage_sph;   // generic sph32 array is in shared memory (else read from global by the rare generic queries)
+    size_t total;
+};
+SmemPlan plan_smem(const DevScene& sc, size_t budget);
+
 struct RenderParams {
     DevScene sc;
+    SmemPlan plan;
     DevCamera cam;
     int32_t row0, row1;      // band [row0,row1)
     int32_t n_rows;          // rows this launch renders (== row1-row0 unless striped)
@@ -31,6 +41,8 @@ struct RenderParams {
 size_t scene_smem_bytes(const DevScene& sc);
 // largest dynamic shared memory size the device allows per block (opt-in)
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream);
+// (re)builds sc.views for this camera / bias (rte_views.cuh); a no-op for scenes without spheres
+cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double bias, cudaStream_t stream);
 
 // Scene::IntersectClosest / IntersectAnyBefore for a batch of rays (device arrays)
 cudaError_t launch_intersect_closest(const DevScene& sc, int64_t n, const double* origins, const double* dirs,
@@ -52,6 +64,6 @@ cudaError_t launch_max_luminance(const float4* hdr, int64_t n_pixels, unsigned i
                                  cudaStream_t stream);
 
 // register-resident FFMA chains on every SM (rte_peak.cu): *flop_out = FP32 flop the launch executes
-cudaError_t launch_ffma_peak(float* scratch, int outer, int sm_count, cudaStream_t stream, double* flop_out);
+cudaError_t launch_ffma_peak(float* scratch, int outer, int sm_count, cudaStream_t stream, double* flop_out, int packed);
 
 }  // namespace rte

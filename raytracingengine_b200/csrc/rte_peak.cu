@@ -30,9 +30,38 @@ __global__ void __launch_bounds__(kPeakThreads) ffma_peak_kernel(float* out, int
     if (s == 12345.678f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;  // keeps the chains alive
 }
 
-cudaError_t launch_ffma_peak(float* scratch, int outer, int sm_count, cudaStream_t stream, double* flop_out) {
+// The same with the packed fma.rn.f32x2 (SASS FFMA2, sm_100+): 2 FMAs per lane per instruction.
+__global__ void __launch_bounds__(kPeakThreads) ffma2_peak_kernel(float* out, int outer, float a, float b) {
+    unsigned long long acc[kPeakChains], a2, b2;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(a2) : "f"(a));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(b2) : "f"(b));
+#pragma unroll
+    for (int k = 0; k < kPeakChains; ++k) {
+        const float v = (float)(threadIdx.x + k) * 1e-3f;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(acc[k]) : "f"(v), "f"(-v));
+    }
+#pragma unroll 1
+    for (int it = 0; it < outer; ++it) {
+#pragma unroll
+        for (int j = 0; j < kPeakInner / 2; ++j) {
+#pragma unroll
+            for (int k = 0; k < kPeakChains; ++k) asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(acc[k]) : "l"(a2), "l"(b2));
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < kPeakChains; ++k) {
+        float lo, hi;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(acc[k]));
+        s += lo + hi;
+    }
+    if (s == 12345.678f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+cudaError_t launch_ffma_peak(float* scratch, int outer, int sm_count, cudaStream_t stream, double* flop_out, int packed) {
     const int blocks = sm_count * 8;
-    ffma_peak_kernel<<<blocks, kPeakThreads, 0, stream>>>(scratch, outer, 0.999f, 1e-3f);
+    if (packed) ffma2_peak_kernel<<<blocks, kPeakThreads, 0, stream>>>(scratch, outer, 0.999f, 1e-3f);
+    else ffma_peak_kernel<<<blocks, kPeakThreads, 0, stream>>>(scratch, outer, 0.999f, 1e-3f);
     *flop_out = 2.0 * (double)blocks * kPeakThreads * (double)outer * kPeakInner * kPeakChains;
     return cudaGetLastError();
 }

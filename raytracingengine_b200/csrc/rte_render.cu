@@ -13,6 +13,7 @@
 #include "rte_kernels.h"
 #include "rte_tonemap.cuh"
 #include "rte_trace.cuh"
+#include "rte_views.cuh"
 
 namespace rte {
 
@@ -46,22 +47,46 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
 
 constexpr uint32_t kTmaChunk = 32768;
 
+// Dynamic shared memory layout of the render kernel: [views (1+nl) x ns_pad x 16 B][generic sph32][tri32].
+// The generic sphere array is only staged when something can use it often (reflection rays, or no views);
+// otherwise the rare generic queries (exact shadow marches) read it from global memory.
+SmemPlan plan_smem(const DevScene& sc, size_t budget) {
+    SmemPlan pl{};
+    const size_t tri = (size_t)sc.nt_pad * 48, sph = (size_t)sc.ns_pad * 16;
+    const size_t views = sc.ns > 0 ? (size_t)(1 + sc.nl) * view_bytes(sc.ns_pad) : 0;
+    pl.tri_bytes = (uint32_t)tri;
+    if (sc.views && tri + views <= budget) {
+        pl.use_views = 1;
+        pl.view_bytes = (uint32_t)views;
+        pl.stage_sph = (sc.reflective && tri + views + sph <= budget) ? 1 : 0;
+    } else {
+        pl.stage_sph = 1;
+    }
+    pl.sph_bytes = pl.stage_sph ? (uint32_t)sph : 0u;
+    pl.total = (size_t)pl.view_bytes + pl.sph_bytes + pl.tri_bytes;
+    return pl;
+}
+
 size_t scene_smem_bytes(const DevScene& sc) { return (size_t)sc.ns_pad * 16 + (size_t)sc.nt_pad * 48; }
 
-// Stage {sph32, tri32} into dynamic shared memory.  Called by every thread of the CTA.
-__device__ __forceinline__ void stage_scene(const DevScene& sc, unsigned char* dyn, uint64_t* bar,
-                                            const float4*& s_sph, const float4*& s_tri) {
-    const uint32_t sph_bytes = (uint32_t)sc.ns_pad * 16u, tri_bytes = (uint32_t)sc.nt_pad * 48u;
-    s_sph = reinterpret_cast<const float4*>(dyn);
-    s_tri = reinterpret_cast<const float4*>(dyn + sph_bytes);
+__device__ __forceinline__ void tma_chunks(unsigned char* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    for (uint32_t off = 0; off < bytes; off += kTmaChunk)
+        tma_bulk_g2s(dst + off, reinterpret_cast<const unsigned char*>(src) + off, min(kTmaChunk, bytes - off), bar);
+}
+
+// Stage the filter arrays into dynamic shared memory with TMA bulk copies.  Called by every thread of the CTA.
+__device__ __forceinline__ void stage_scene(const DevScene& sc, const SmemPlan& pl, unsigned char* dyn, uint64_t* bar,
+                                            const ulonglong2*& s_views, const float4*& s_sph, const float4*& s_tri) {
+    s_views = reinterpret_cast<const ulonglong2*>(dyn);
+    s_sph = pl.stage_sph ? reinterpret_cast<const float4*>(dyn + pl.view_bytes) : sc.sph32;
+    s_tri = reinterpret_cast<const float4*>(dyn + pl.view_bytes + pl.sph_bytes);
     if (threadIdx.x == 0) mbar_init(bar, 1);
     __syncthreads();
     if (threadIdx.x == 0) {
-        mbar_expect_tx(bar, sph_bytes + tri_bytes);
-        for (uint32_t off = 0; off < sph_bytes; off += kTmaChunk)
-            tma_bulk_g2s(dyn + off, reinterpret_cast<const unsigned char*>(sc.sph32) + off, min(kTmaChunk, sph_bytes - off), bar);
-        for (uint32_t off = 0; off < tri_bytes; off += kTmaChunk)
-            tma_bulk_g2s(dyn + sph_bytes + off, reinterpret_cast<const unsigned char*>(sc.tri32) + off, min(kTmaChunk, tri_bytes - off), bar);
+        mbar_expect_tx(bar, pl.view_bytes + pl.sph_bytes + pl.tri_bytes);
+        tma_chunks(dyn, sc.views, pl.view_bytes, bar);
+        tma_chunks(dyn + pl.view_bytes, sc.sph32, pl.sph_bytes, bar);
+        tma_chunks(dyn + pl.view_bytes + pl.sph_bytes, sc.tri32, pl.tri_bytes, bar);
     }
     mbar_wait(bar, 0);
 }
@@ -77,7 +102,7 @@ struct PixelCounters {
 };
 
 // TraceRay for one pixel, all 32 lanes of the warp in lock step (lanes outside the image: alive=false).
-__device__ __forceinline__ d3 trace_pixel(const RenderParams& P, const DevScene& sc, const float4* s_sph,
+__device__ __forceinline__ d3 trace_pixel(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const float4* s_sph,
                                           const float4* s_tri, int px, int py, bool inb, int64_t out_idx,
                                           PixelCounters& cnt) {
     d3 o = ld3(P.cam.pos);
@@ -88,11 +113,14 @@ __device__ __forceinline__ d3 trace_pixel(const RenderParams& P, const DevScene&
     const double bias = P.bias;
     const int max_depth = P.max_depth, nl = sc.nl;
     const bool nf = P.no_filter != 0;
+    const bool uv = P.plan.use_views != 0;
+    const int view_stride = sc.ns_pad;  // ulonglong2 elements per view
 #pragma unroll 1
     for (int depth = 0; depth < max_depth; ++depth) {
         if (!__any_sync(kFullMask, alive)) break;
         Hit h;
-        closest_hit_body(sc, s_sph, s_tri, o, d, alive, nf, h, cnt.confirms);
+        if (uv && depth == 0) closest_hit_view(sc, s_views, s_tri, o, d, alive, nf, h, cnt.confirms);
+        else closest_hit_body(sc, s_sph, s_tri, o, d, alive, nf, h, cnt.confirms);
         if (alive) {
             cnt.sph += (uint32_t)sc.ns; cnt.pl += (uint32_t)sc.np; cnt.tri += (uint32_t)sc.nt;
             if (depth > 0) cnt.secondary += 1;
@@ -152,7 +180,8 @@ __device__ __forceinline__ d3 trace_pixel(const RenderParams& P, const DevScene&
             if (P.exact_shadows) {
                 if (cast) { T = march_exact(sc, s_sph, s_tri, so, L, maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
             } else {
-                const OccResult r = occluded(sc, s_sph, s_tri, so, L, maxDist, bias, cast, nf, cnt.confirms);
+                const OccResult r = uv ? occluded_view(sc, s_views + (size_t)(1 + j) * view_stride, s_tri, so, L, dist, Lp, maxDist, bias, cast, nf, cnt.confirms)
+                                       : occluded(sc, s_sph, s_tri, so, L, maxDist, bias, cast, nf, cnt.confirms);
                 cnt.sph += r.sph_tests; cnt.pl += r.pl_tests; cnt.tri += r.tri_tests;
                 if (cast) {
                     if (r.near) { T = march_exact(sc, s_sph, s_tri, so, L, maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
@@ -209,20 +238,22 @@ __device__ __forceinline__ d3 trace_pixel(const RenderParams& P, const DevScene&
 }
 
 // ------------------------------------------------------------------------------ the kernel
-constexpr int kRenderThreads = 256;
+constexpr int kRenderThreads = 256;     // block size of the query kernels and of the render kernel at 2 CTAs/SM
+constexpr int kRenderMaxThreads = 512;  // render kernel at 1 CTA/SM (large scenes: more shared memory per CTA)
 constexpr int kTileW = 8, kTileH = 4;  // one warp = 8x4 pixels (coherent primary and shadow rays)
 
-__global__ void __launch_bounds__(kRenderThreads, 2) render_kernel(const __grid_constant__ RenderParams P) {
+__global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ DevScene s_sc;
     __shared__ __align__(8) uint64_t s_bar;
-    __shared__ unsigned long long s_stats[kRenderThreads / 32][kStatCount];
+    __shared__ unsigned long long s_stats[kRenderMaxThreads / 32][kStatCount];
 
     if (threadIdx.x == 0) s_sc = P.sc;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
     const float4 *s_sph, *s_tri;
-    stage_scene(P.sc, dyn_smem, &s_bar, s_sph, s_tri);  // contains __syncthreads: s_sc visible after it
+    const ulonglong2* s_views;
+    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);  // contains __syncthreads: s_sc visible after it
     const DevScene& sc = s_sc;
 
     const int W = P.cam.width, rows = P.n_rows;
@@ -243,7 +274,7 @@ __global__ void __launch_bounds__(kRenderThreads, 2) render_kernel(const __grid_
         const bool inb = px < W && band_y < rows;
         const int64_t out_idx = (int64_t)band_y * W + px;
         PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0};
-        const d3 c = trace_pixel(P, sc, s_sph, s_tri, px, py, inb, out_idx, cnt);
+        const d3 c = trace_pixel(P, sc, s_views, s_sph, s_tri, px, py, inb, out_idx, cnt);
         if (inb) {
             if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[out_idx] = make_float4((float)c.x, (float)c.y, (float)c.z, 0.f);
             if (P.out.hdr64) { P.out.hdr64[3 * out_idx] = c.x; P.out.hdr64[3 * out_idx + 1] = c.y; P.out.hdr64[3 * out_idx + 2] = c.z; }
@@ -269,26 +300,40 @@ static cudaError_t ensure_smem(const void* fn, size_t bytes) {
     return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
 
+cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double bias, cudaStream_t stream) {
+    if (!sc.views || sc.ns == 0) return cudaSuccess;
+    const int total = (1 + sc.nl) * sc.ns_pad;
+    build_views_kernel<<<(total + 255) / 256, 256, 0, stream>>>(sc, cam, bias, const_cast<float*>(sc.views));
+    return cudaGetLastError();
+}
+
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream) {
-    const size_t smem = scene_smem_bytes(p.sc);
+    const size_t smem = p.plan.total;
     cudaError_t e = ensure_smem((const void*)render_kernel, smem);
     if (e != cudaSuccess) return e;
-    int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel, kRenderThreads, smem);
+    // 2 CTAs of 256 threads per SM when the arrays fit twice, else 1 CTA of 512 threads
+    int threads = kRenderThreads, per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel, threads, smem);
     if (e != cudaSuccess) return e;
+    if (per_sm < 2) {
+        threads = kRenderMaxThreads;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel, threads, smem);
+        if (e != cudaSuccess) return e;
+    }
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
     const int W = p.cam.width, rows = p.n_rows;
     const long long n_tiles = (long long)((W + kTileW - 1) / kTileW) * ((rows + kTileH - 1) / kTileH);
     long long blocks = (long long)sm_count * per_sm;  // persistent: a multiple of the SM count
-    const long long needed = (n_tiles + kRenderThreads / 32 - 1) / (kRenderThreads / 32);
+    const long long needed = (n_tiles + threads / 32 - 1) / (threads / 32);
     if (blocks > needed) blocks = needed > 0 ? needed : 1;
-    render_kernel<<<(unsigned)blocks, kRenderThreads, smem, stream>>>(p);
+    render_kernel<<<(unsigned)blocks, threads, smem, stream>>>(p);
     return cudaGetLastError();
 }
 
 // ------------------------------------------------------------------------------ ray queries
 struct QueryParams {
     DevScene sc;
+    SmemPlan plan;  // generic arrays only (no views: query rays have arbitrary origins)
     int64_t n;
     const double* origins;
     const double* dirs;
@@ -304,7 +349,8 @@ __global__ void __launch_bounds__(kRenderThreads, 2) closest_kernel(const __grid
     __shared__ __align__(8) uint64_t s_bar;
     if (threadIdx.x == 0) s_sc = Q.sc;
     const float4 *s_sph, *s_tri;
-    stage_scene(Q.sc, dyn_smem, &s_bar, s_sph, s_tri);
+    const ulonglong2* s_views;
+    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);
     const DevScene& sc = s_sc;
     for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < Q.n; base += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = base + threadIdx.x;
@@ -344,7 +390,8 @@ __global__ void __launch_bounds__(kRenderThreads, 2) any_before_kernel(const __g
     __shared__ __align__(8) uint64_t s_bar;
     if (threadIdx.x == 0) s_sc = Q.sc;
     const float4 *s_sph, *s_tri;
-    stage_scene(Q.sc, dyn_smem, &s_bar, s_sph, s_tri);
+    const ulonglong2* s_views;
+    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);
     const DevScene& sc = s_sc;
     for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < Q.n; base += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = base + threadIdx.x;
@@ -359,8 +406,17 @@ __global__ void __launch_bounds__(kRenderThreads, 2) any_before_kernel(const __g
     }
 }
 
+static SmemPlan generic_plan(const DevScene& sc) {
+    SmemPlan pl{};
+    pl.stage_sph = 1;
+    pl.sph_bytes = (uint32_t)((size_t)sc.ns_pad * 16);
+    pl.tri_bytes = (uint32_t)((size_t)sc.nt_pad * 48);
+    pl.total = (size_t)pl.sph_bytes + pl.tri_bytes;
+    return pl;
+}
+
 static cudaError_t launch_query(const void* fn, const QueryParams& q, int sm_count, cudaStream_t stream) {
-    const size_t smem = scene_smem_bytes(q.sc);
+    const size_t smem = q.plan.total;
     cudaError_t e = ensure_smem(fn, smem);
     if (e != cudaSuccess) return e;
     long long blocks = (q.n + kRenderThreads - 1) / kRenderThreads;
@@ -372,12 +428,12 @@ static cudaError_t launch_query(const void* fn, const QueryParams& q, int sm_cou
 
 cudaError_t launch_intersect_closest(const DevScene& sc, int64_t n, const double* origins, const double* dirs,
                                      rte_hit* hits, int sm_count, cudaStream_t stream) {
-    QueryParams q{sc, n, origins, dirs, nullptr, hits, nullptr};
+    QueryParams q{sc, generic_plan(sc), n, origins, dirs, nullptr, hits, nullptr};
     return launch_query((const void*)closest_kernel, q, sm_count, stream);
 }
 cudaError_t launch_intersect_any_before(const DevScene& sc, int64_t n, const double* origins, const double* dirs,
                                         const double* max_dist, uint8_t* out, int sm_count, cudaStream_t stream) {
-    QueryParams q{sc, n, origins, dirs, max_dist, nullptr, out};
+    QueryParams q{sc, generic_plan(sc), n, origins, dirs, max_dist, nullptr, out};
     return launch_query((const void*)any_before_kernel, q, sm_count, stream);
 }
 

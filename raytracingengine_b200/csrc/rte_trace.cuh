@@ -152,6 +152,38 @@ __device__ __forceinline__ void scan_triangles(const float4* __restrict__ s_tri,
     }
 }
 
+// Planes (exact) then triangles (FP32 filter + FP64 confirm) of a closest-hit query, after the spheres.
+__device__ __forceinline__ void closest_planes_triangles(const DevScene& sc, const float4* __restrict__ s_tri, const Ray32& r, d3 o, d3 d,
+                                                         bool alive, Hit& best, bool& found, uint32_t& confirms) {
+    if (alive) {
+        const int np = sc.np;
+#pragma unroll 1
+        for (int i = 0; i < np; ++i) {
+            double t;
+            if (plane_exact(sc.planes[i], o, d, t) && (!found || t < best.t)) {
+                found = true; best.t = t; best.kind = RTE_HIT_PLANE; best.idx = (uint32_t)i;
+            }
+        }
+    }
+    if (sc.nt == 0) return;
+    CandList L;
+    L.n = 0;
+    auto flush = [&]() {
+#pragma unroll 1
+        for (int j = 0; j < L.n; ++j) {
+            const int k = L.idx[j];
+            double t;
+            ++confirms;
+            if (tri_exact(sc.tri64[k], o, d, t) && (!found || t < best.t)) {
+                found = true; best.t = t; best.kind = RTE_HIT_TRIANGLE; best.idx = (uint32_t)k;
+            }
+        }
+        L.n = 0;
+    };
+    scan_triangles(s_tri, 0, sc.nt_pad, r, alive, L, flush);
+    flush();
+}
+
 // Scene::IntersectClosest.  No warp-synchronous operation inside: callable from divergent code.
 __device__ __forceinline__ void closest_hit_body(const DevScene& sc, const float4* __restrict__ s_sph,
                                                  const float4* __restrict__ s_tri, d3 o, d3 d, bool alive, bool no_filter,
@@ -159,9 +191,9 @@ __device__ __forceinline__ void closest_hit_body(const DevScene& sc, const float
     const Ray32 r = make_ray32(sc, o, d, no_filter);
     best.t = 0.0; best.kind = RTE_HIT_NONE; best.idx = 0;
     bool found = false;
-    CandList L;
-    L.n = 0;
-    {
+    if (sc.ns > 0) {
+        CandList L;
+        L.n = 0;
         auto flush = [&]() {
 #pragma unroll 1
             for (int j = 0; j < L.n; ++j) {
@@ -177,32 +209,7 @@ __device__ __forceinline__ void closest_hit_body(const DevScene& sc, const float
         scan_spheres(s_sph, 0, sc.ns_pad, r, alive ? r.m_sph : -INFINITY, INFINITY, L, flush);
         flush();
     }
-    if (alive) {
-        const int np = sc.np;
-#pragma unroll 1
-        for (int i = 0; i < np; ++i) {
-            double t;
-            if (plane_exact(sc.planes[i], o, d, t) && (!found || t < best.t)) {
-                found = true; best.t = t; best.kind = RTE_HIT_PLANE; best.idx = (uint32_t)i;
-            }
-        }
-    }
-    {
-        auto flush = [&]() {
-#pragma unroll 1
-            for (int j = 0; j < L.n; ++j) {
-                const int k = L.idx[j];
-                double t;
-                ++confirms;
-                if (tri_exact(sc.tri64[k], o, d, t) && (!found || t < best.t)) {
-                    found = true; best.t = t; best.kind = RTE_HIT_TRIANGLE; best.idx = (uint32_t)k;
-                }
-            }
-            L.n = 0;
-        };
-        scan_triangles(s_tri, 0, sc.nt_pad, r, alive, L, flush);
-        flush();
-    }
+    closest_planes_triangles(sc, s_tri, r, o, d, alive, best, found, confirms);
 }
 
 __device__ __noinline__ void closest_hit_cold(const DevScene& sc, const float4* s_sph, const float4* s_tri, d3 o,
@@ -245,6 +252,72 @@ struct OccResult {
     uint32_t sph_tests, pl_tests, tri_tests;  // canonical-order tests up to and incl. the first occluder
 };
 
+// State of one any-hit shadow query while it walks the primitive classes in canonical order.
+struct OccState {
+    OccResult res;
+    bool done;       // decided (occluded) or inactive lane
+    double bias, maxDist, t_safe;
+    __device__ __forceinline__ void on_t(double t, uint32_t& firstv, uint32_t k) {
+        if (t <= bias) res.near = true;
+        else if (t < maxDist) {
+            res.occluded = true; done = true; firstv = k + 1u;
+            if (t <= t_safe) res.near = true;
+        }
+    }
+};
+
+__device__ __forceinline__ OccState occ_begin(double maxDist, double bias, bool active) {
+    OccState st;
+    st.res.occluded = false; st.res.near = false;
+    st.res.sph_tests = st.res.pl_tests = st.res.tri_tests = 0;
+    st.done = !active;
+    st.bias = bias; st.maxDist = maxDist; st.t_safe = 130.0 * bias;
+    return st;
+}
+
+// Planes (exact) and triangles (FP32 filter + FP64 confirm) of an any-hit query; all 32 lanes call it.
+__device__ __forceinline__ void occ_planes_triangles(const DevScene& sc, const float4* __restrict__ s_tri, const Ray32& r, d3 o, d3 d,
+                                                     OccState& st, uint32_t& confirms) {
+    if (__all_sync(kFullMask, st.done)) return;
+    const int np = sc.np;
+    if (!st.done) {
+        uint32_t firstp = (uint32_t)np;
+#pragma unroll 1
+        for (int i = 0; i < np; ++i) {
+            double t;
+            if (plane_exact(sc.planes[i], o, d, t)) {
+                st.on_t(t, firstp, (uint32_t)i);
+                if (st.done) break;
+            }
+        }
+        st.res.pl_tests = firstp;
+    }
+    const int nt_pad = sc.nt_pad, nt = sc.nt;
+    if (nt == 0) return;
+    const bool scan_tris = !st.done;
+    uint32_t firstt = (uint32_t)nt;
+    CandList L;
+    L.n = 0;
+    auto flush = [&]() {
+#pragma unroll 1
+        for (int j = 0; j < L.n; ++j) {
+            const int k = L.idx[j];
+            double t;
+            if (st.done) break;
+            ++confirms;
+            if (tri_exact(sc.tri64[k], o, d, t)) st.on_t(t, firstt, (uint32_t)k);
+        }
+        L.n = 0;
+    };
+#pragma unroll 1
+    for (int base = 0; base < nt_pad; base += kTriChunk) {
+        scan_triangles(s_tri, base, min(base + kTriChunk, nt_pad), r, !st.done, L, flush);
+        flush();
+        if (__all_sync(kFullMask, st.done)) break;
+    }
+    if (scan_tris) st.res.tri_tests = firstt;
+}
+
 // Any-hit shadow query for opaque scenes.  Must be called by all 32 lanes of the warp (votes inside).
 //
 // Equivalence with the reference march (RE/Scene.h:35-77) for opaque scenes: if no primitive reports
@@ -258,81 +331,35 @@ __device__ __forceinline__ OccResult occluded(const DevScene& sc, const float4* 
                                               const float4* __restrict__ s_tri, d3 o, d3 d, double maxDist,
                                               double bias, bool active, bool no_filter, uint32_t& confirms) {
     const Ray32 r = make_ray32(sc, o, d, no_filter);
-    OccResult res;
-    res.occluded = false; res.near = false;
-    res.sph_tests = res.pl_tests = res.tri_tests = 0;
-    bool done = !active;
-    const double t_safe = 130.0 * bias;
+    OccState st = occ_begin(maxDist, bias, active);
     // unit-direction distance bound for pruning (|d| may differ from 1 for user queries)
     const float tmax32 = (float)(maxDist * sqrt(dot(d, d))) * 1.00001f + r.m_b;
     const int ns_pad = sc.ns_pad, ns = sc.ns;
     uint32_t first = (uint32_t)ns;
     CandList L;
     L.n = 0;
-    auto on_t = [&](double t, uint32_t& firstv, uint32_t k) {
-        if (t <= bias) res.near = true;
-        else if (t < maxDist) {
-            res.occluded = true; done = true; firstv = k + 1u;
-            if (t <= t_safe) res.near = true;
-        }
-    };
     {
         auto flush = [&]() {
 #pragma unroll 1
             for (int j = 0; j < L.n; ++j) {
                 const int k = L.idx[j];
                 double t;
-                if (done) break;
+                if (st.done) break;
                 ++confirms;
-                if (sphere_exact(sc.sph64[k], o, d, t)) on_t(t, first, (uint32_t)k);
+                if (sphere_exact(sc.sph64[k], o, d, t)) st.on_t(t, first, (uint32_t)k);
             }
             L.n = 0;
         };
 #pragma unroll 1
         for (int base = 0; base < ns_pad; base += kSphChunk) {
-            scan_spheres(s_sph, base, min(base + kSphChunk, ns_pad), r, done ? -INFINITY : r.m_sph, tmax32, L, flush);
+            scan_spheres(s_sph, base, min(base + kSphChunk, ns_pad), r, st.done ? -INFINITY : r.m_sph, tmax32, L, flush);
             flush();
-            if (__all_sync(kFullMask, done)) break;
+            if (__all_sync(kFullMask, st.done)) break;
         }
     }
-    if (active) res.sph_tests = first;
-    if (!__all_sync(kFullMask, done)) {
-        const int np = sc.np;
-        if (!done) {
-            uint32_t firstp = (uint32_t)np;
-#pragma unroll 1
-            for (int i = 0; i < np; ++i) {
-                double t;
-                if (plane_exact(sc.planes[i], o, d, t)) {
-                    on_t(t, firstp, (uint32_t)i);
-                    if (done) break;
-                }
-            }
-            res.pl_tests = firstp;
-        }
-        const int nt_pad = sc.nt_pad, nt = sc.nt;
-        const bool scan_tris = !done;
-        uint32_t firstt = (uint32_t)nt;
-        auto flush = [&]() {
-#pragma unroll 1
-            for (int j = 0; j < L.n; ++j) {
-                const int k = L.idx[j];
-                double t;
-                if (done) break;
-                ++confirms;
-                if (tri_exact(sc.tri64[k], o, d, t)) on_t(t, firstt, (uint32_t)k);
-            }
-            L.n = 0;
-        };
-#pragma unroll 1
-        for (int base = 0; base < nt_pad; base += kTriChunk) {
-            scan_triangles(s_tri, base, min(base + kTriChunk, nt_pad), r, !done, L, flush);
-            flush();
-            if (__all_sync(kFullMask, done)) break;
-        }
-        if (scan_tris) res.tri_tests = firstt;
-    }
-    return res;
+    if (active) st.res.sph_tests = first;
+    occ_planes_triangles(sc, s_tri, r, o, d, st, confirms);
+    return st.res;
 }
 
 }  // namespace rte

@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "librte_b200
 SYMBOLS = (
     "rte_version", "rte_device_count", "rte_last_error", "rte_create", "rte_destroy", "rte_set_stream",
     "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats",
-    "rte_tonemap", "rte_tonemap_host", "rte_max_luminance", "rte_measure_fp32_peak", "rte_intersect_closest", "rte_intersect_any_before",
+    "rte_tonemap", "rte_tonemap_host", "rte_max_luminance", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
     "rte_malloc", "rte_free", "rte_memcpy_d2h", "rte_memcpy_h2d", "rte_malloc_host", "rte_free_host",
     "rte_write_ppm",
 )
@@ -63,6 +63,7 @@ def load_library() -> C.CDLL:
     lib.rte_tonemap_host.argtypes = tm_args
     lib.rte_max_luminance.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_float)]
     lib.rte_measure_fp32_peak.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    lib.rte_measure_fp32x2_peak.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.rte_intersect_closest.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rte_intersect_any_before.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rte_malloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
@@ -272,10 +273,11 @@ class Engine:
         self._ck(self.lib.rte_max_luminance(self.ctx, C.c_void_p(hdr_dev), n_pixels, C.byref(v)))
         return float(v.value)
 
-    def measure_fp32_peak(self, target_ms: float = 20.0):
-        """(TFLOP/s, ms) of a register-resident FFMA kernel on this GPU: the FP32 roofline denominator."""
+    def measure_fp32_peak(self, target_ms: float = 20.0, packed: bool = False):
+        """(TFLOP/s, ms) of a register-resident FFMA (or packed FFMA2) kernel on this GPU: the FP32 roofline denominator."""
         tf, ms = C.c_double(), C.c_double()
-        self._ck(self.lib.rte_measure_fp32_peak(self.ctx, target_ms, C.byref(tf), C.byref(ms)))
+        fn = self.lib.rte_measure_fp32x2_peak if packed else self.lib.rte_measure_fp32_peak
+        self._ck(fn(self.ctx, target_ms, C.byref(tf), C.byref(ms)))
         return float(tf.value), float(ms.value)
 
     # ---- ray queries
