@@ -156,8 +156,9 @@ typedef struct rte_render_opts {
 
 /* Validation switches for rte_render_opts.flags.  Both must leave every output bit-identical:
  *   EXACT_SHADOWS  every shadow ray takes the literal RE/Scene.h:35-77 march instead of the any-hit query;
- *   NO_FILTER      the FP32 filters accept everything, i.e. every primitive is tested in FP64. */
-enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2 };
+ *   NO_FILTER      the FP32 filters accept everything, i.e. every primitive is tested in FP64;
+ *   GENERAL_KERNEL never take the lean kernel specialised for diffuse sphere/plane scenes without AOVs. */
+enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4 };
 
 /* Output buffers of one render call.  Every pointer is optional (NULL = not wanted) and is a
  * DEVICE pointer for rte_render() and a HOST pointer for rte_render_host().  Each buffer holds
@@ -189,6 +190,8 @@ typedef struct rte_stats {
     uint64_t fp64_confirms;    /* FP64 re-evaluations triggered by the FP32 filter */
     double kernel_ms;          /* device time of the render kernel (CUDA events on the ctx stream) */
     double tonemap_ms;         /* device time of the last tonemap kernel */
+    uint64_t sphere_tests_executed; /* ray-sphere filter evaluations the kernel really ran (any-hit rays stop
+                                       when their whole warp is decided; padding entries included) */
 } rte_stats;
 
 typedef struct rte_ctx rte_ctx;

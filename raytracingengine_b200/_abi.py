@@ -35,7 +35,7 @@ TM_NAMES = (
 TM_COUNT = 7
 TM_NONE = -1
 TM_ACES = 6
-FLAG_EXACT_SHADOWS, FLAG_NO_FILTER = 1, 2
+FLAG_EXACT_SHADOWS, FLAG_NO_FILTER, FLAG_GENERAL_KERNEL = 1, 2, 4
 
 # --- numpy dtypes (C layout) -------------------------------------------------------------------
 material_dt = np.dtype(  # Material, RE/Shape.h:13-19
@@ -98,14 +98,14 @@ class Stats(C.Structure):
                 ("secondary_rays", C.c_uint64), ("sphere_tests", C.c_uint64),
                 ("plane_tests", C.c_uint64), ("triangle_tests", C.c_uint64),
                 ("exact_marches", C.c_uint64), ("fp64_confirms", C.c_uint64),
-                ("kernel_ms", C.c_double), ("tonemap_ms", C.c_double)]
+                ("kernel_ms", C.c_double), ("tonemap_ms", C.c_double), ("sphere_tests_executed", C.c_uint64)]
 
     def as_dict(self) -> dict:
         return {name: getattr(self, name) for name, _ in self._fields_}
 
 
 assert C.sizeof(Camera) == 72 and C.sizeof(SceneDesc) == 128
-assert C.sizeof(RenderOpts) == 56 and C.sizeof(Frame) == 72 and C.sizeof(Stats) == 80
+assert C.sizeof(RenderOpts) == 56 and C.sizeof(Frame) == 72 and C.sizeof(Stats) == 88
 
 # algorithmic flops per ray-primitive test
 FLOP_SPHERE, FLOP_PLANE, FLOP_TRIANGLE = 20, 14, 46

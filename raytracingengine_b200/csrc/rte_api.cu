@@ -439,6 +439,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
     p.row0 = o.row0; p.row1 = o.row1; p.n_rows = o.n_rows; p.stripe_rows = o.stripe_rows; p.stripe_period = o.stripe_period; p.max_depth = o.max_depth; p.tonemap_op = o.tonemap_op;
     p.exact_shadows = (o.flags & RTE_FLAG_EXACT_SHADOWS) ? 1 : 0;
     p.no_filter = (o.flags & RTE_FLAG_NO_FILTER) ? 1 : 0;
+    p.force_general = (o.flags & RTE_FLAG_GENERAL_KERNEL) ? 1 : 0;
     p.bias = o.bias; p.max_white = o.max_white; p.jodie_a = o.jodie_a;
     p.out = *frame;
     p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
@@ -501,6 +502,7 @@ extern "C" int rte_get_stats(rte_ctx* ctx, rte_stats* out) {
         s.primary_rays = h[kStatPrimary]; s.shadow_rays = h[kStatShadow]; s.secondary_rays = h[kStatSecondary];
         s.sphere_tests = h[kStatSphTests]; s.plane_tests = h[kStatPlTests]; s.triangle_tests = h[kStatTriTests];
         s.exact_marches = h[kStatMarches]; s.fp64_confirms = h[kStatConfirms];
+        s.sphere_tests_executed = h[kStatSphExec];
         float ms = 0.f;
         RTE_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_r0, ctx->ev_r1));
         s.kernel_ms = ms;

@@ -8,7 +8,7 @@ namespace rte {
 
 enum StatSlot {
     kStatPrimary = 0, kStatShadow, kStatSecondary, kStatSphTests, kStatPlTests, kStatTriTests,
-    kStatMarches, kStatConfirms, kStatCount
+    kStatMarches, kStatConfirms, kStatSphExec, kStatCount
 };
 
 // what the render kernel stages into dynamic shared memory (rte_render.cu: plan_smem)
@@ -31,6 +31,7 @@ struct RenderParams {
     int32_t tonemap_op;      // RTE_TM_* or RTE_TM_NONE
     int32_t exact_shadows;   // RTE_FLAG_EXACT_SHADOWS: every shadow ray takes the literal march
     int32_t no_filter;       // RTE_FLAG_NO_FILTER: FP32 filters accept everything
+    int32_t force_general;   // RTE_FLAG_GENERAL_KERNEL: never take the lean fast kernel (validation)
     double bias, max_white, jodie_a;
     rte_frame out;           // device pointers, any may be NULL
     unsigned int* tile_counter;        // zeroed before launch

@@ -46,6 +46,10 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
 }
 
 constexpr uint32_t kTmaChunk = 32768;
+#ifndef RTE_VIEW_PIXELS
+#define RTE_VIEW_PIXELS 2
+#endif
+constexpr int kViewPixels = RTE_VIEW_PIXELS;  // pixels per thread of the view-mode render kernel
 
 // Dynamic shared memory layout of the render kernel: [views (1+nl) x ns_pad x 16 B][generic sph32][tri32].
 // The generic sphere array is only staged when something can use it often (reflection rays, or no views);
@@ -98,150 +102,213 @@ __device__ __forceinline__ d3 background(d3 dir) {
 }
 
 struct PixelCounters {
-    uint32_t shadow, secondary, sph, pl, tri, marches, confirms;
+    uint32_t shadow, secondary, sph, pl, tri, marches, confirms, sph_exec;
 };
 
-// TraceRay for one pixel, all 32 lanes of the warp in lock step (lanes outside the image: alive=false).
-__device__ __forceinline__ d3 trace_pixel(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const float4* s_sph,
-                                          const float4* s_tri, int px, int py, bool inb, int64_t out_idx,
-                                          PixelCounters& cnt) {
-    d3 o = ld3(P.cam.pos);
-    d3 d = camera_dir(P.cam, px, py);
-    d3 acc = mk(0.0, 0.0, 0.0);
-    double w = 1.0;
-    bool alive = inb;
+// TraceRay for the K pixels of one thread, all 32 lanes of the warp in lock step (pixels outside the image:
+// alive = false).  kReflect = false compiles the diffuse-only path (no material has specular > 0): the depth loop,
+// Blinn-Phong and the reflection state disappear.  Per pixel the ray state is FP64, bit-identical to the reference.
+template <int K, bool kReflect>
+__device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const float4* s_sph,
+                                             const float4* s_tri, const int (&px)[K], const int (&py)[K], const bool (&inb)[K],
+                                             const int64_t (&out_idx)[K], PixelCounters& cnt, d3 (&result)[K]) {
+    const d3 cam_o = ld3(P.cam.pos);
+    d3 o[K], d[K], acc[K];
+    double w[K];
+    bool alive[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        o[k] = cam_o;
+        d[k] = camera_dir(P.cam, px[k], py[k]);
+        acc[k] = mk(0.0, 0.0, 0.0);
+        w[k] = 1.0;
+        alive[k] = inb[k];
+    }
     const double bias = P.bias;
-    const int max_depth = P.max_depth, nl = sc.nl;
+    const int max_depth = kReflect ? P.max_depth : 1, nl = sc.nl;
     const bool nf = P.no_filter != 0;
     const bool uv = P.plan.use_views != 0;
     const int view_stride = sc.ns_pad;  // ulonglong2 elements per view
 #pragma unroll 1
     for (int depth = 0; depth < max_depth; ++depth) {
-        if (!__any_sync(kFullMask, alive)) break;
-        Hit h;
-        if (uv && depth == 0) closest_hit_view(sc, s_views, s_tri, o, d, alive, nf, h, cnt.confirms);
-        else closest_hit_body(sc, s_sph, s_tri, o, d, alive, nf, h, cnt.confirms);
-        if (alive) {
-            cnt.sph += (uint32_t)sc.ns; cnt.pl += (uint32_t)sc.np; cnt.tri += (uint32_t)sc.nt;
-            if (depth > 0) cnt.secondary += 1;
-        }
-        const bool hitv = alive && h.kind != RTE_HIT_NONE;
-        if (alive && !hitv) {
-            acc = acc + background(d) * w;
-            alive = false;
-        }
-        // hit record (GetHitInfoAt, RE/Shape.h:104-121,165-180,229-243)
-        d3 Pn = mk(0, 0, 0), ng = mk(0, 0, 0);
-        int mat = sc.nm;
-        uint32_t report = 0;
-        if (hitv) {
-            Pn = o + d * h.t;
-            mat = material_of(sc, h);
-            if (h.kind == RTE_HIT_SPHERE) {
-                const double4 s = sc.sph64[h.idx];
-                ng = normalize(Pn - mk(s.x, s.y, s.z));
-                report = h.idx;
-            } else if (h.kind == RTE_HIT_PLANE) {
-                ng = ld3(sc.planes[h.idx].n);
-                report = h.idx;
-            } else {
-                ng = ld3(sc.tri64[h.idx].n);
-                report = (uint32_t)sc.tri_info[h.idx].y;
+        bool any_alive = false;
+#pragma unroll
+        for (int k = 0; k < K; ++k) any_alive = any_alive || alive[k];
+        if (!__any_sync(kFullMask, any_alive)) break;
+        Hit h[K];
+        if (uv && depth == 0) {
+            closest_hit_view<K>(sc, s_views, s_tri, cam_o, d, alive, nf, h, cnt.confirms);
+#pragma unroll
+            for (int k = 0; k < K; ++k) if (alive[k]) cnt.sph_exec += (uint32_t)sc.ns_pad;
+        } else {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                closest_hit_body(sc, s_sph, s_tri, o[k], d[k], alive[k], nf, h[k], cnt.confirms);
+                if (alive[k]) cnt.sph_exec += (uint32_t)sc.ns_pad;
             }
         }
-        const rte_material& M = sc.materials[mat];
-        // TraceRay, RE/Scene.h:144-148
-        const d3 incoming = normalize(d);
-        const bool frontFace = dot(ng, incoming) < 0.0;
-        const d3 N = frontFace ? ng : -ng;
-        const d3 viewDir = -incoming;
+        // hit records (GetHitInfoAt, RE/Shape.h:104-121,165-180,229-243) and TraceRay's frame, RE/Scene.h:144-148
+        bool hitv[K];
+        d3 Pn[K], normal[K], ngeo[K], viewDir[K], incoming[K];
+        int mat[K], self[K];
+        uint32_t report[K], lmask[K];
+        d3 diffuseAcc[K], specAcc[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (alive[k]) {
+                cnt.sph += (uint32_t)sc.ns; cnt.pl += (uint32_t)sc.np; cnt.tri += (uint32_t)sc.nt;
+                if (depth > 0) cnt.secondary += 1;
+            }
+            hitv[k] = alive[k] && h[k].kind != RTE_HIT_NONE;
+            if (alive[k] && !hitv[k]) {
+                acc[k] = acc[k] + background(d[k]) * w[k];
+                alive[k] = false;
+            }
+            Pn[k] = mk(0, 0, 0); ngeo[k] = mk(0, 0, 0);
+            mat[k] = sc.nm; report[k] = 0; self[k] = -1; lmask[k] = 0;
+            if (hitv[k]) {
+                Pn[k] = o[k] + d[k] * h[k].t;
+                mat[k] = material_of(sc, h[k]);
+                if (h[k].kind == RTE_HIT_SPHERE) {
+                    const double4 s = sc.sph64[h[k].idx];
+                    ngeo[k] = normalize(Pn[k] - mk(s.x, s.y, s.z));
+                    report[k] = h[k].idx;
+                } else if (h[k].kind == RTE_HIT_PLANE) {
+                    ngeo[k] = ld3(sc.planes[h[k].idx].n);
+                    report[k] = h[k].idx;
+                } else {
+                    ngeo[k] = ld3(sc.tri64[h[k].idx].n);
+                    report[k] = (uint32_t)sc.tri_info[h[k].idx].y;
+                }
+            }
+            incoming[k] = normalize(d[k]);
+            const bool frontFace = dot(ngeo[k], incoming[k]) < 0.0;
+            const d3 N = frontFace ? ngeo[k] : -ngeo[k];
+            if (hitv[k] && h[k].kind == RTE_HIT_SPHERE && frontFace) self[k] = (int)h[k].idx;
+            viewDir[k] = -incoming[k];
+            normal[k] = normalize(N);  // directLightning re-normalises, RE/Scene.h:81
+            diffuseAcc[k] = mk(0, 0, 0); specAcc[k] = mk(0, 0, 0);
+        }
         // directLightning, RE/Scene.h:79-129
-        const d3 normal = normalize(N);
-        d3 diffuseAcc = mk(0, 0, 0), specAcc = mk(0, 0, 0);
-        uint32_t lmask = 0;
-        const bool want_spec = hitv && M.transparency <= 0.0 && M.specular > 0.0;
 #pragma unroll 1
         for (int j = 0; j < nl; ++j) {
             const d3 Lp = ld3(sc.lights[j].pos);
-            const d3 vecToLight = Lp - Pn;
-            const double dist = length(vecToLight);
-            bool cast = hitv && dist > 0.0;
-            d3 L = mk(0, 0, 1);
-            double ndl = 0.0;
-            if (cast) {
-                L = vecToLight / dist;
-                ndl = std_max(0.0, dot(normal, L));
-                cast = ndl > 0.0 && dist > bias;
-            }
-            if (!__any_sync(kFullMask, cast)) continue;
-            const d3 so = Pn + normal * bias;
-            const double maxDist = dist - bias;
-            double T = 1.0;
-            if (P.exact_shadows) {
-                if (cast) { T = march_exact(sc, s_sph, s_tri, so, L, maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
-            } else {
-                const OccResult r = uv ? occluded_view(sc, s_views + (size_t)(1 + j) * view_stride, s_tri, so, L, dist, Lp, maxDist, bias, cast, nf, cnt.confirms)
-                                       : occluded(sc, s_sph, s_tri, so, L, maxDist, bias, cast, nf, cnt.confirms);
-                cnt.sph += r.sph_tests; cnt.pl += r.pl_tests; cnt.tri += r.tri_tests;
+            ShadowRay sr[K];
+            bool any_cast = false;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const d3 vecToLight = Lp - Pn[k];
+                const double dist = length(vecToLight);
+                bool cast = hitv[k] && dist > 0.0;
+                d3 L = mk(0, 0, 1);
+                double ndl = 0.0;
                 if (cast) {
-                    if (r.near) { T = march_exact(sc, s_sph, s_tri, so, L, maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
-                    else T = r.occluded ? 0.0 : 1.0;
+                    L = vecToLight / dist;
+                    ndl = std_max(0.0, dot(normal[k], L));
+                    cast = ndl > 0.0 && dist > bias;
+                }
+                sr[k].o = Pn[k] + normal[k] * bias;
+                sr[k].d = L; sr[k].dist = dist; sr[k].maxDist = dist - bias; sr[k].ndl = ndl;
+                sr[k].self = self[k]; sr[k].cast = cast;
+                any_cast = any_cast || cast;
+            }
+            if (!__any_sync(kFullMask, any_cast)) continue;
+            double T[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) T[k] = 1.0;
+            if (P.exact_shadows) {
+#pragma unroll
+                for (int k = 0; k < K; ++k)
+                    if (sr[k].cast) { T[k] = march_exact(sc, s_sph, s_tri, sr[k].o, sr[k].d, sr[k].maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
+            } else {
+                OccResult r[K];
+                if (uv) {
+                    occluded_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, s_tri, Lp, sr, bias, nf, r, cnt.confirms, cnt.sph_exec);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < K; ++k)
+                        r[k] = occluded(sc, s_sph, s_tri, sr[k].o, sr[k].d, sr[k].maxDist, bias, sr[k].cast, nf, cnt.confirms);
+                }
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    cnt.sph += r[k].sph_tests; cnt.pl += r[k].pl_tests; cnt.tri += r[k].tri_tests;
+                    if (sr[k].cast) {
+                        if (r[k].near) { T[k] = march_exact(sc, s_sph, s_tri, sr[k].o, sr[k].d, sr[k].maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
+                        else T[k] = r[k].occluded ? 0.0 : 1.0;
+                    }
                 }
             }
-            if (cast) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                if (!sr[k].cast) continue;
                 cnt.shadow += 1;
-                if (j < 16) lmask |= 1u << (16 + j);
-                if (T > bias) {
-                    if (j < 16) lmask |= 1u << j;
+                if (j < 16) lmask[k] |= 1u << (16 + j);
+                if (T[k] > bias) {
+                    if (j < 16) lmask[k] |= 1u << j;
                     const d3 emitted = ld3(sc.lights[j].E);
-                    const d3 contribution = (emitted * (1.0 / (dist * dist))) * ndl;
-                    diffuseAcc = diffuseAcc + contribution * T;
-                    if (want_spec) {
-                        const d3 H = normalize(L + viewDir);
-                        const double ndh = std_max(0.0, dot(normal, H));
-                        if (ndh > 0.0) {
-                            const double specFactor = pow(ndh, M.shininess);
-                            specAcc = specAcc + ((emitted * (1.0 / (dist * dist))) * specFactor) * T;
+                    const double dist = sr[k].dist;
+                    const d3 contribution = (emitted * (1.0 / (dist * dist))) * sr[k].ndl;
+                    diffuseAcc[k] = diffuseAcc[k] + contribution * T[k];
+                    if (kReflect) {
+                        const rte_material& M = sc.materials[mat[k]];
+                        if (M.transparency <= 0.0 && M.specular > 0.0) {
+                            const d3 H = normalize(sr[k].d + viewDir[k]);
+                            const double ndh = std_max(0.0, dot(normal[k], H));
+                            if (ndh > 0.0) {
+                                const double specFactor = pow(ndh, M.shininess);
+                                specAcc[k] = specAcc[k] + ((emitted * (1.0 / (dist * dist))) * specFactor) * T[k];
+                            }
                         }
                     }
                 }
             }
         }
-        if (hitv) {
-            const d3 local = ld3(M.color) * diffuseAcc + specAcc * M.specular;
-            // finalLight += localLight * (1.0 - transparency), transparency == 0 (RE/Scene.h:171-173)
-            acc = acc + (local * (1.0 - 0.0)) * w;
-        }
-        if (depth == 0 && inb) {  // AOVs of the primary hit
-            if (P.out.prim_id) P.out.prim_id[out_idx] = hitv ? ((h.kind << 30) | report) : kMiss;
-            if (P.out.depth) P.out.depth[out_idx] = hitv ? (float)h.t : INFINITY;
-            if (P.out.depth64) P.out.depth64[out_idx] = hitv ? h.t : (double)INFINITY;
-            if (P.out.normal) reinterpret_cast<float4*>(P.out.normal)[out_idx] = make_float4((float)ng.x, (float)ng.y, (float)ng.z, 0.f);
-            if (P.out.albedo) {
-                const d3 a = hitv ? ld3(M.color) : background(d);
-                reinterpret_cast<float4*>(P.out.albedo)[out_idx] = make_float4((float)a.x, (float)a.y, (float)a.z, 0.f);
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const rte_material& M = sc.materials[mat[k]];
+            if (hitv[k]) {
+                const d3 local = ld3(M.color) * diffuseAcc[k] + specAcc[k] * M.specular;
+                // finalLight += localLight * (1.0 - transparency), transparency == 0 (RE/Scene.h:171-173)
+                acc[k] = acc[k] + (local * (1.0 - 0.0)) * w[k];
             }
-            if (P.out.light_mask) P.out.light_mask[out_idx] = lmask;
-        }
-        // reflection, RE/Scene.h:189-195 (transparency == 0: reflectiveness = material.specular)
-        if (hitv && M.specular > bias) {
-            const d3 R = normalize(reflect(incoming, N));
-            w = w * M.specular;
-            o = Pn + R * bias;
-            d = R;
-        } else {
-            alive = false;
+            if (depth == 0 && inb[k]) {  // AOVs of the primary hit
+                const int64_t oi = out_idx[k];
+                if (P.out.prim_id) P.out.prim_id[oi] = hitv[k] ? ((h[k].kind << 30) | report[k]) : kMiss;
+                if (P.out.depth) P.out.depth[oi] = hitv[k] ? (float)h[k].t : INFINITY;
+                if (P.out.depth64) P.out.depth64[oi] = hitv[k] ? h[k].t : (double)INFINITY;
+                if (P.out.normal) reinterpret_cast<float4*>(P.out.normal)[oi] = make_float4((float)ngeo[k].x, (float)ngeo[k].y, (float)ngeo[k].z, 0.f);
+                if (P.out.albedo) {
+                    const d3 a = hitv[k] ? ld3(M.color) : background(d[k]);
+                    reinterpret_cast<float4*>(P.out.albedo)[oi] = make_float4((float)a.x, (float)a.y, (float)a.z, 0.f);
+                }
+                if (P.out.light_mask) P.out.light_mask[oi] = lmask[k];
+            }
+            // reflection, RE/Scene.h:189-195 (transparency == 0: reflectiveness = material.specular)
+            if (kReflect && hitv[k] && M.specular > bias) {
+                const d3 N = dot(ngeo[k], incoming[k]) < 0.0 ? ngeo[k] : -ngeo[k];
+                const d3 R = normalize(reflect(incoming[k], N));
+                w[k] = w[k] * M.specular;
+                o[k] = Pn[k] + R * bias;
+                d[k] = R;
+            } else {
+                alive[k] = false;
+            }
         }
     }
-    if (alive) acc = acc + background(d) * w;  // TraceRay(depth >= maxRecursion), RE/Scene.h:132-134
-    return acc;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (alive[k]) acc[k] = acc[k] + background(d[k]) * w[k];  // TraceRay(depth >= maxRecursion), RE/Scene.h:132-134
+        result[k] = acc[k];
+    }
 }
 
 // ------------------------------------------------------------------------------ the kernel
 constexpr int kRenderThreads = 256;     // block size of the query kernels and of the render kernel at 2 CTAs/SM
 constexpr int kRenderMaxThreads = 512;  // render kernel at 1 CTA/SM (large scenes: more shared memory per CTA)
-constexpr int kTileW = 8, kTileH = 4;  // one warp = 8x4 pixels (coherent primary and shadow rays)
+constexpr int kTileW = 8, kTileH = 4;   // one warp = K stacked 8x4 pixel groups (coherent primary and shadow rays)
 
+// K = pixels per thread: lane (lx, ly) owns pixels (x0 + lx, y0 + ly + 4k), k < K, of its warp's 8 x 4K tile.
+template <int K, bool kReflect>
 __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ DevScene s_sc;
@@ -258,7 +325,8 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
 
     const int W = P.cam.width, rows = P.n_rows;
     const int sr = P.stripe_rows, sp = P.stripe_period;
-    const int tiles_x = (W + kTileW - 1) / kTileW, tiles_y = (rows + kTileH - 1) / kTileH;
+    constexpr int TH = kTileH * K;
+    const int tiles_x = (W + kTileW - 1) / kTileW, tiles_y = (rows + TH - 1) / TH;
     const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
     const int lx = lane & (kTileW - 1), ly = lane >> 3;
 
@@ -269,22 +337,240 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
         unsigned int next = 0;
         if (lane == 0) next = atomicAdd(P.tile_counter, 1u);  // prefetch the next tile id behind the work
         const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
-        const int px = tx * kTileW + lx, band_y = ty * kTileH + ly;
-        const int py = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
-        const bool inb = px < W && band_y < rows;
-        const int64_t out_idx = (int64_t)band_y * W + px;
-        PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0};
-        const d3 c = trace_pixel(P, sc, s_views, s_sph, s_tri, px, py, inb, out_idx, cnt);
-        if (inb) {
-            if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[out_idx] = make_float4((float)c.x, (float)c.y, (float)c.z, 0.f);
-            if (P.out.hdr64) { P.out.hdr64[3 * out_idx] = c.x; P.out.hdr64[3 * out_idx + 1] = c.y; P.out.hdr64[3 * out_idx + 2] = c.z; }
+        int px[K], py[K];
+        bool inb[K];
+        int64_t out_idx[K];
+        uint32_t n_in = 0;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int band_y = ty * TH + k * kTileH + ly;
+            px[k] = tx * kTileW + lx;
+            py[k] = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
+            inb[k] = px[k] < W && band_y < rows;
+            out_idx[k] = (int64_t)band_y * W + px[k];
+            n_in += inb[k] ? 1u : 0u;
+        }
+        PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
+        d3 c[K];
+        trace_pixels<K, kReflect>(P, sc, s_views, s_sph, s_tri, px, py, inb, out_idx, cnt, c);
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            if (!inb[k]) continue;
+            const int64_t oi = out_idx[k];
+            if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[oi] = make_float4((float)c[k].x, (float)c[k].y, (float)c[k].z, 0.f);
+            if (P.out.hdr64) { P.out.hdr64[3 * oi] = c[k].x; P.out.hdr64[3 * oi + 1] = c[k].y; P.out.hdr64[3 * oi + 2] = c[k].z; }
             if (P.out.rgb8 && P.tonemap_op >= 0) {
-                const uchar3 q = tm64::to_color(tm64::apply(P.tonemap_op, c, P.max_white, P.jodie_a));
-                P.out.rgb8[3 * out_idx] = q.x; P.out.rgb8[3 * out_idx + 1] = q.y; P.out.rgb8[3 * out_idx + 2] = q.z;
+                const uchar3 q = tm64::to_color(tm64::apply(P.tonemap_op, c[k], P.max_white, P.jodie_a));
+                P.out.rgb8[3 * oi] = q.x; P.out.rgb8[3 * oi + 1] = q.y; P.out.rgb8[3 * oi + 2] = q.z;
             }
         }
         // per-warp statistics: one REDUX per counter, lane 0 accumulates in shared memory
-        const uint32_t v[kStatCount] = {inb ? 1u : 0u, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms};
+        const uint32_t v[kStatCount] = {n_in, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms, cnt.sph_exec};
+#pragma unroll
+        for (int k = 0; k < kStatCount; ++k) {
+            const uint32_t s = __reduce_add_sync(kFullMask, v[k]);
+            if (lane == 0) s_stats[warp][k] += s;
+        }
+        tile = __shfl_sync(kFullMask, next, 0);
+    }
+    __syncwarp();
+    if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
+}
+
+// ------------------------------------------------------------------------------ the fast kernel
+// Production path of diffuse sphere/plane scenes (C2/C3/C5 families): views resident in shared memory, no
+// material with specular > 0, no triangles, no validation switch, no AOV output.  Same arithmetic as
+// trace_pixels (bit-identical results, tests/test_gpu_render.py::test_fast_kernel_*), but laid out for the
+// instruction caches: everything that runs once per pixel sits in `#pragma unroll 1` loops over the K pixels of
+// the thread (one copy of the FP64 code, per-pixel state in local memory), only the two sphere scans are
+// unrolled over K.  The general kernel's per-pixel code is ~4x larger and stalls on instruction fetch.
+template <int K>
+__device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const float4* s_sph,
+                                                const float4* s_tri, const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K],
+                                                PixelCounters& cnt, d3 (&result)[K]) {
+    const d3 cam_o = ld3(P.cam.pos);
+    const double bias = P.bias;
+    const int nl = sc.nl, np = sc.np, ns = sc.ns;
+    const int view_stride = sc.ns_pad;
+    d3 dir[K];
+    bool alive[K], found[K];
+    Hit h[K];
+#pragma unroll 1
+    for (int k = 0; k < K; ++k) {
+        dir[k] = camera_dir(P.cam, pxs[k], pys[k]);
+        alive[k] = inb[k];
+        found[k] = false;
+        h[k].t = 0.0; h[k].kind = RTE_HIT_NONE; h[k].idx = 0;
+    }
+    if (ns > 0) closest_spheres_view<K>(sc, s_views, cam_o, dir, alive, false, h, found, cnt.confirms);
+
+    d3 Pn[K], normal[K], diffuse[K];
+    int mat[K], self[K];
+    bool hitv[K];
+#pragma unroll 1
+    for (int k = 0; k < K; ++k) {
+        const d3 d = dir[k];
+        Hit hk = h[k];
+        bool fk = found[k];
+        if (alive[k]) {
+            cnt.sph += (uint32_t)ns; cnt.pl += (uint32_t)np; cnt.sph_exec += (uint32_t)sc.ns_pad;
+#pragma unroll 1
+            for (int i = 0; i < np; ++i) {  // planes after the spheres, strict '<' (RE/Scene.h:218-257)
+                double t;
+                if (plane_exact(sc.planes[i], cam_o, d, t) && (!fk || t < hk.t)) {
+                    fk = true; hk.t = t; hk.kind = RTE_HIT_PLANE; hk.idx = (uint32_t)i;
+                }
+            }
+        }
+        const bool hv = alive[k] && fk;
+        hitv[k] = hv;
+        result[k] = mk(0.0, 0.0, 0.0);
+        if (alive[k] && !hv) result[k] = result[k] + background(d) * 1.0;  // miss: sky (RE/Scene.h:137-141)
+        d3 P_ = mk(0, 0, 0), ng = mk(0, 0, 0);
+        int m = sc.nm, sf = -1;
+        if (hv) {
+            P_ = cam_o + d * hk.t;
+            m = material_of(sc, hk);
+            if (hk.kind == RTE_HIT_SPHERE) {
+                const double4 s = sc.sph64[hk.idx];
+                ng = normalize(P_ - mk(s.x, s.y, s.z));
+            } else {
+                ng = ld3(sc.planes[hk.idx].n);
+            }
+        }
+        const d3 incoming = normalize(d);
+        const bool frontFace = dot(ng, incoming) < 0.0;
+        const d3 N = frontFace ? ng : -ng;
+        if (hv && hk.kind == RTE_HIT_SPHERE && frontFace) sf = (int)hk.idx;
+        Pn[k] = P_; normal[k] = normalize(N); mat[k] = m; self[k] = sf;
+        diffuse[k] = mk(0.0, 0.0, 0.0);
+    }
+    // directLightning, RE/Scene.h:79-129 (diffuse term; specAcc stays 0 without specular materials)
+#pragma unroll 1
+    for (int j = 0; j < nl; ++j) {
+        const d3 Lp = ld3(sc.lights[j].pos);
+        ShadowRay sr[K];
+        bool any_cast = false;
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            const d3 vecToLight = Lp - Pn[k];
+            const double dist = length(vecToLight);
+            bool cast = hitv[k] && dist > 0.0;
+            d3 L = mk(0, 0, 1);
+            double ndl = 0.0;
+            if (cast) {
+                L = vecToLight / dist;
+                ndl = std_max(0.0, dot(normal[k], L));
+                cast = ndl > 0.0 && dist > bias;
+            }
+            ShadowRay s;
+            s.o = Pn[k] + normal[k] * bias;
+            s.d = L; s.dist = dist; s.maxDist = dist - bias; s.ndl = ndl; s.self = self[k]; s.cast = cast;
+            sr[k] = s;
+            any_cast = any_cast || cast;
+        }
+        if (!__any_sync(kFullMask, any_cast)) continue;
+        OccState st[K];
+        occluded_spheres_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, Lp, sr, bias, false, st, cnt.confirms, cnt.sph_exec);
+        bool all_done = true;
+#pragma unroll
+        for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;
+        const bool skip_planes = __all_sync(kFullMask, all_done);
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            OccState s = st[k];
+            const ShadowRay r = sr[k];
+            if (!skip_planes && !s.done) {  // planes, any-hit in canonical order
+                uint32_t firstp = (uint32_t)np;
+#pragma unroll 1
+                for (int i = 0; i < np; ++i) {
+                    double t;
+                    if (plane_exact(sc.planes[i], r.o, r.d, t)) {
+                        s.on_t(t, firstp, (uint32_t)i);
+                        if (s.done) break;
+                    }
+                }
+                s.res.pl_tests = firstp;
+            }
+            cnt.sph += s.res.sph_tests; cnt.pl += s.res.pl_tests;
+            if (!r.cast) continue;
+            double T;
+            if (s.res.near) { T = march_exact(sc, s_sph, s_tri, r.o, r.d, r.maxDist, bias, false, cnt.confirms); cnt.marches += 1; }
+            else T = s.res.occluded ? 0.0 : 1.0;
+            cnt.shadow += 1;
+            if (T > bias) {
+                const d3 emitted = ld3(sc.lights[j].E);
+                const d3 contribution = (emitted * (1.0 / (r.dist * r.dist))) * r.ndl;
+                diffuse[k] = diffuse[k] + contribution * T;
+            }
+        }
+    }
+#pragma unroll 1
+    for (int k = 0; k < K; ++k) {
+        if (!hitv[k]) continue;
+        const rte_material& M = sc.materials[mat[k]];
+        const d3 local = ld3(M.color) * diffuse[k] + mk(0.0, 0.0, 0.0) * M.specular;
+        result[k] = result[k] + (local * (1.0 - 0.0)) * 1.0;  // finalLight += localLight * (1 - transparency), w = 1
+    }
+}
+
+template <int K>
+__global__ void __launch_bounds__(kRenderMaxThreads, 1) render_fast_kernel(const __grid_constant__ RenderParams P) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ DevScene s_sc;
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ unsigned long long s_stats[kRenderMaxThreads / 32][kStatCount];
+
+    if (threadIdx.x == 0) s_sc = P.sc;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane < kStatCount) s_stats[warp][lane] = 0ull;
+    const float4 *s_sph, *s_tri;
+    const ulonglong2* s_views;
+    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);
+    const DevScene& sc = s_sc;
+
+    const int W = P.cam.width, rows = P.n_rows;
+    const int sr = P.stripe_rows, sp = P.stripe_period;
+    constexpr int TH = kTileH * K;
+    const int tiles_x = (W + kTileW - 1) / kTileW, tiles_y = (rows + TH - 1) / TH;
+    const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
+    const int lx = lane & (kTileW - 1), ly = lane >> 3;
+
+    unsigned int tile = 0;
+    if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
+    tile = __shfl_sync(kFullMask, tile, 0);
+    while (tile < n_tiles) {
+        unsigned int next = 0;
+        if (lane == 0) next = atomicAdd(P.tile_counter, 1u);
+        const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
+        int px[K], py[K];
+        bool inb[K];
+        uint32_t n_in = 0;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const int band_y = ty * TH + k * kTileH + ly;
+            px[k] = tx * kTileW + lx;
+            py[k] = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
+            inb[k] = px[k] < W && band_y < rows;
+            n_in += inb[k] ? 1u : 0u;
+        }
+        PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
+        d3 c[K];
+        trace_tile_fast<K>(P, sc, s_views, s_sph, s_tri, px, py, inb, cnt, c);
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            if (!inb[k]) continue;
+            const int band_y = ty * TH + k * kTileH + ly;
+            const int64_t oi = (int64_t)band_y * W + px[k];
+            const d3 v = c[k];
+            if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[oi] = make_float4((float)v.x, (float)v.y, (float)v.z, 0.f);
+            if (P.out.hdr64) { P.out.hdr64[3 * oi] = v.x; P.out.hdr64[3 * oi + 1] = v.y; P.out.hdr64[3 * oi + 2] = v.z; }
+            if (P.out.rgb8 && P.tonemap_op >= 0) {
+                const uchar3 q = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));
+                P.out.rgb8[3 * oi] = q.x; P.out.rgb8[3 * oi + 1] = q.y; P.out.rgb8[3 * oi + 2] = q.z;
+            }
+        }
+        const uint32_t v[kStatCount] = {n_in, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms, cnt.sph_exec};
 #pragma unroll
         for (int k = 0; k < kStatCount; ++k) {
             const uint32_t s = __reduce_add_sync(kFullMask, v[k]);
@@ -307,27 +593,40 @@ cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double 
     return cudaGetLastError();
 }
 
-cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream) {
+static cudaError_t launch_render_fn(const void* fn, int K, const RenderParams& p, int sm_count, cudaStream_t stream) {
     const size_t smem = p.plan.total;
-    cudaError_t e = ensure_smem((const void*)render_kernel, smem);
+    cudaError_t e = ensure_smem(fn, smem);
     if (e != cudaSuccess) return e;
     // 2 CTAs of 256 threads per SM when the arrays fit twice, else 1 CTA of 512 threads
     int threads = kRenderThreads, per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel, threads, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem);
     if (e != cudaSuccess) return e;
     if (per_sm < 2) {
         threads = kRenderMaxThreads;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, render_kernel, threads, smem);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem);
         if (e != cudaSuccess) return e;
     }
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
     const int W = p.cam.width, rows = p.n_rows;
-    const long long n_tiles = (long long)((W + kTileW - 1) / kTileW) * ((rows + kTileH - 1) / kTileH);
+    const long long n_tiles = (long long)((W + kTileW - 1) / kTileW) * ((rows + kTileH * K - 1) / (kTileH * K));
     long long blocks = (long long)sm_count * per_sm;  // persistent: a multiple of the SM count
     const long long needed = (n_tiles + threads / 32 - 1) / (threads / 32);
     if (blocks > needed) blocks = needed > 0 ? needed : 1;
-    render_kernel<<<(unsigned)blocks, threads, smem, stream>>>(p);
-    return cudaGetLastError();
+    void* args[] = {(void*)&p};
+    return cudaLaunchKernel(fn, dim3((unsigned)blocks), dim3((unsigned)threads), args, smem, stream);
+}
+
+bool fast_path_eligible(const RenderParams& p) {
+    const rte_frame& f = p.out;
+    return p.plan.use_views && !p.sc.reflective && p.sc.nt == 0 && !p.exact_shadows && !p.no_filter && !f.prim_id && !f.depth &&
+           !f.depth64 && !f.normal && !f.albedo && !f.light_mask;
+}
+
+cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream) {
+    if (fast_path_eligible(p) && !p.force_general)
+        return launch_render_fn((const void*)render_fast_kernel<kViewPixels>, kViewPixels, p, sm_count, stream);
+    if (!p.sc.reflective) return launch_render_fn((const void*)render_kernel<1, false>, 1, p, sm_count, stream);
+    return launch_render_fn((const void*)render_kernel<1, true>, 1, p, sm_count, stream);
 }
 
 // ------------------------------------------------------------------------------ ray queries

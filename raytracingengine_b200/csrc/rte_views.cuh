@@ -85,143 +85,313 @@ __global__ void __launch_bounds__(256) build_views_kernel(const DevScene sc, con
 }
 
 // ------------------------------------------------------------------------------ the scan
-// Filters spheres [base, base+32) of one view against the unit direction (ux,uy,uz) given as duplicated
-// pairs; returns the candidate bits, bit (31-k) <-> sphere base+k.
-__device__ __forceinline__ uint32_t view_block_mask(const ulonglong2* __restrict__ v, f32x2 ux2, f32x2 uy2, f32x2 uz2) {
-    uint32_t m = 0;
-#pragma unroll
-    for (int p = 0; p < kViewBlock / 2; ++p) {
-        const ulonglong2 A = v[2 * p], B = v[2 * p + 1];
-        f32x2 b = mul2(A.x, ux2);
-        b = fma2(A.y, uy2, b);
-        b = fma2(B.x, uz2, b);
-        const f32x2 h = fma2(b, b, B.y);
-        uint32_t h0, h1;
-        unpack2_bits(h, h0, h1);
-        m = __funnelshift_l(h0, m, 1);  // m = (m << 1) | sign(h0)
-        m = __funnelshift_l(h1, m, 1);
-    }
-    return ~m;  // sign clear (h >= 0, or NaN with the sign clear) -> candidate
-}
-
+// K rays per thread share every LDS.128 of sphere data (a broadcast LDS.128 costs two shared-memory
+// wavefronts: with one ray per thread the loop is shared-memory bound, not FMA bound).
 struct ViewRay {
-    f32x2 ux2, uy2, uz2;  // fl32 of the unit direction the view is scanned with, duplicated
-    float ux, uy, uz;
-    float slack;          // absolute slack on distances along the ray
+    float ux, uy, uz;  // fl32 of the unit direction the view is scanned with
 };
 
-__device__ __forceinline__ ViewRay make_view_ray(d3 u, float S) {
+__device__ __forceinline__ ViewRay make_view_ray(d3 u) {
     ViewRay r;
     r.ux = (float)u.x; r.uy = (float)u.y; r.uz = (float)u.z;
-    r.ux2 = pack2(r.ux, r.ux); r.uy2 = pack2(r.uy, r.uy); r.uz2 = pack2(r.uz, r.uz);
-    r.slack = 16.0f * kEps32 * S + 1e-6f;
     return r;
 }
 
-// [s_lo, s_hi] (conservatively widened) where the scan line is inside sphere `idx`
-__device__ __forceinline__ void view_interval(const float* __restrict__ view, int idx, const ViewRay& r, float& s_lo, float& s_hi) {
+// Filters spheres [base, base+32) of one view against K directions; cand[k] bit (31-i) <-> sphere base+i.
+// The 16 sphere pairs are walked in chunks of kPairs unrolled pairs: the loop body (kPairs * (2 LDS + 6K) SASS
+// instructions) has to stay well inside the ~6 KB L0 instruction cache, or the warps of an SMSP starve on fetch.
+template <int K>
+__device__ __forceinline__ void view_block_masks(const ulonglong2* __restrict__ v, const ViewRay (&r)[K], uint32_t (&cand)[K]) {
+    constexpr int kPairs = K == 1 ? 16 : (K == 2 ? 8 : 4);
+    uint32_t m[K];
+    f32x2 ux2[K], uy2[K], uz2[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        m[k] = 0;
+        ux2[k] = pack2(r[k].ux, r[k].ux); uy2[k] = pack2(r[k].uy, r[k].uy); uz2[k] = pack2(r[k].uz, r[k].uz);  // SASS: scalar-broadcast operand
+    }
+#pragma unroll 1
+    for (int c = 0; c < kViewBlock / 2; c += kPairs) {
+#pragma unroll
+        for (int p = 0; p < kPairs; ++p) {
+            const ulonglong2 A = v[2 * (c + p)], B = v[2 * (c + p) + 1];
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                f32x2 b = mul2(A.x, ux2[k]);
+                b = fma2(A.y, uy2[k], b);
+                b = fma2(B.x, uz2[k], b);
+                const f32x2 h = fma2(b, b, B.y);
+                uint32_t h0, h1;
+                unpack2_bits(h, h0, h1);
+                m[k] = __funnelshift_l(h0, m[k], 1);  // m = (m << 1) | sign(h0)
+                m[k] = __funnelshift_l(h1, m[k], 1);
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) cand[k] = ~m[k];  // sign clear (h >= 0) -> candidate
+}
+
+// The FP64 confirmation as ONE out-of-line copy: it is the rare path of every scan site, and inlining it K times
+// per site bloats the kernel far beyond the instruction caches.
+__device__ __noinline__ bool confirm_sphere(const double4* __restrict__ sph64, int idx, d3 o, d3 d, double& t) {
+    return sphere_exact(sph64[idx], o, d, t);
+}
+
+// Per-view constants of the FP32 interval arithmetic on candidates.
+struct ViewBounds {
+    float slack;   // absolute error bound on distances along the ray
+    float m2;      // 2 * (upper bound of every M_ij of the view): h~ - m2 <= true half-chord^2 <= h~
+};
+__device__ __forceinline__ ViewBounds view_bounds(const DevScene& sc, d3 origin, double bias, bool light_view) {
+    const float S = sqrtf((float)dot(origin, origin)) * 1.0000002f + sc.sph_extent;
+    ViewBounds vb;
+    vb.slack = 24.0f * kEps32 * S + 1e-6f;
+    float m = 24.0f * kEps32 * S * S + 1e-30f;
+    if (light_view) m += (float)(2.0 * bias) * sc.sph_extent + (float)(bias * bias);
+    vb.m2 = 2.0f * m * 1.0001f;
+    return vb;
+}
+
+// Centre parameter and half-chord bounds of candidate `idx` along the scan line.
+struct ViewChord { float sc, hc_lo, hc_hi; };
+__device__ __forceinline__ ViewChord view_chord(const float* __restrict__ view, int idx, const ViewRay& r, const ViewBounds& vb) {
     const ViewEntry e = view_entry(view, idx);
     const float b = __fmaf_rn(e.fz, r.uz, __fmaf_rn(e.fy, r.uy, e.fx * r.ux));
     const float h = __fmaf_rn(b, b, e.ng);
-    const float sq = sqrtf(fmaxf(h, 0.0f)) * 1.000001f;
-    s_lo = b - sq - r.slack;
-    s_hi = b + sq + r.slack;
+    ViewChord c;
+    c.sc = b;
+    c.hc_hi = sqrtf(fmaxf(h, 0.0f)) * 1.000001f;
+    c.hc_lo = sqrtf(fmaxf(h - vb.m2, 0.0f)) * 0.999999f;
+    return c;
 }
 
-// Scene::IntersectClosest over the spheres for a PRIMARY ray (view 0).  `best`/`found` carry on.
-__device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, d3 o, d3 d, bool alive,
-                                                     bool no_filter, Hit& best, bool& found, uint32_t& confirms) {
-    const float S = sqrtf((float)dot(o, o)) * 1.0000002f + sc.sph_extent;
-    const ViewRay r = make_view_ray(d, S);
+// ------------------------------------------------------------------------------ candidate queue
+// With ~2 line candidates per ray and 32 lanes, almost every 32-sphere block has a candidate in SOME lane:
+// resolving candidates where they are found runs the divergent path ~30 times per scan with 1-2 lanes active.
+// Instead every lane appends its candidates, (ray k << 28) | sphere index, to a small private queue during
+// the scan, and the warp resolves the queues lane-parallel in one compact loop per window: trip count =
+// the longest queue in the warp, one copy of the resolution code for all K rays.
+template <int K>
+struct CandQueue {
+    static constexpr int kCap = 64 * K;
+    uint32_t q[kCap];
+    int n;
+    __device__ __forceinline__ void push_block(uint32_t c, int base, int k, int ns) {
+        while (c) {  // short, divergent
+            const int i = __clz(c);
+            c &= ~(0x80000000u >> i);
+            if (base + i < ns) q[n++] = ((uint32_t)k << 28) | (uint32_t)(base + i);
+        }
+    }
+    __device__ __forceinline__ bool room() const { return n <= kCap - kViewBlock * K; }
+};
+
+template <int K, class T>
+__device__ __forceinline__ T pick(const T (&a)[K], int k) {
+    T v = a[0];
+#pragma unroll
+    for (int i = 1; i < K; ++i) if (k == i) v = a[i];
+    return v;
+}
+
+// Scene::IntersectClosest over the spheres for K PRIMARY rays of one thread (view 0, common origin o).
+template <int K>
+__device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, d3 o, const d3 (&d)[K],
+                                                     const bool (&alive)[K], bool no_filter, Hit (&best)[K], bool (&found)[K],
+                                                     uint32_t& confirms) {
+    const ViewBounds vb = view_bounds(sc, o, 0.0, false);
+    ViewRay r[K];
+    float best_f[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) { r[k] = make_view_ray(d[k]); best_f[k] = INFINITY; }
     const float* vf = reinterpret_cast<const float*>(view);
     const int ns = sc.ns, ns_pad = sc.ns_pad;
-    float best_f = INFINITY;
+    CandQueue<K> Q;
+    Q.n = 0;
+    int base = 0;
 #pragma unroll 1
-    for (int base = 0; base < ns_pad; base += kViewBlock) {
-        uint32_t cand = view_block_mask(view + base, r.ux2, r.uy2, r.uz2);
-        if (no_filter) cand = 0xFFFFFFFFu;
-        if (!alive) cand = 0u;
-        while (cand) {  // rare, divergent
-            const int k = __clz(cand);
-            cand &= ~(0x80000000u >> k);
-            const int idx = base + k;
-            if (idx >= ns) break;
+    while (base < ns_pad) {
+#pragma unroll 1
+        do {  // scan until the view ends or some lane's queue could overflow
+            uint32_t cand[K];
+            view_block_masks<K>(view + base, r, cand);
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                uint32_t c = no_filter ? 0xFFFFFFFFu : cand[k];
+                if (!alive[k]) c = 0u;
+                Q.push_block(c, base, k, ns);
+            }
+            base += kViewBlock;
+        } while (base < ns_pad && __all_sync(kFullMask, Q.room()));
+        const int nmax = __reduce_max_sync(kFullMask, Q.n);
+#pragma unroll 1
+        for (int e = 0; e < nmax; ++e) {  // lane-parallel resolution, ascending index per ray
+            if (e >= Q.n) continue;
+            const uint32_t ent = Q.q[e];
+            const int k = (int)(ent >> 28), idx = (int)(ent & 0x0FFFFFFFu);
+            const d3 dk = d[k];  // FP64 ray data is indexed dynamically: it lives in local memory, not in K selects
             if (!no_filter) {
-                float s_lo, s_hi;
-                view_interval(vf, idx, r, s_lo, s_hi);
-                if (s_hi < 0.0f || s_lo > best_f) continue;  // behind the camera / cannot beat the best so far
+                const ViewChord ch = view_chord(vf, idx, pick<K>(r, k), vb);
+                // behind the camera, or its near root cannot beat the best so far
+                if (ch.sc + ch.hc_hi + vb.slack < 0.0f || ch.sc - ch.hc_hi - vb.slack > pick<K>(best_f, k)) continue;
             }
             double t;
             ++confirms;
-            if (sphere_exact(sc.sph64[idx], o, d, t) && (!found || t < best.t)) {  // strict '<', RE/Scene.h:223
-                found = true; best.t = t; best.kind = RTE_HIT_SPHERE; best.idx = (uint32_t)idx;
-                best_f = __double2float_ru(t);
+            if (!confirm_sphere(sc.sph64, idx, o, dk, t)) continue;
+#pragma unroll
+            for (int i = 0; i < K; ++i) {
+                if (i == k && (!found[i] || t < best[i].t)) {  // strict '<', RE/Scene.h:223
+                    found[i] = true; best[i].t = t; best[i].kind = RTE_HIT_SPHERE; best[i].idx = (uint32_t)idx;
+                    best_f[i] = __double2float_ru(t);
+                }
             }
         }
+        Q.n = 0;
     }
 }
 
-// Scene::IntersectClosest for a primary ray: spheres through view 0, then planes and triangles.
+// Scene::IntersectClosest for K primary rays: spheres through view 0, then planes and triangles.
+template <int K>
 __device__ __forceinline__ void closest_hit_view(const DevScene& sc, const ulonglong2* __restrict__ view0, const float4* __restrict__ s_tri,
-                                                 d3 o, d3 d, bool alive, bool no_filter, Hit& best, uint32_t& confirms) {
-    best.t = 0.0; best.kind = RTE_HIT_NONE; best.idx = 0;
-    bool found = false;
-    if (sc.ns > 0) closest_spheres_view(sc, view0, o, d, alive, no_filter, best, found, confirms);
+                                                 d3 o, const d3 (&d)[K], const bool (&alive)[K], bool no_filter, Hit (&best)[K],
+                                                 uint32_t& confirms) {
+    bool found[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) { best[k].t = 0.0; best[k].kind = RTE_HIT_NONE; best[k].idx = 0; found[k] = false; }
+    if (sc.ns > 0) closest_spheres_view<K>(sc, view0, o, d, alive, no_filter, best, found, confirms);
     if (sc.np > 0 || sc.nt > 0) {
-        const Ray32 r = make_ray32(sc, o, d, no_filter);
-        closest_planes_triangles(sc, s_tri, r, o, d, alive, best, found, confirms);
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            const Ray32 r = make_ray32(sc, o, d[k], no_filter);
+            closest_planes_triangles(sc, s_tri, r, o, d[k], alive[k], best[k], found[k], confirms);
+        }
     }
 }
 
-// Any-hit shadow query (see occluded() in rte_trace.cuh for the equivalence argument) with the sphere phase
-// scanned through the view of light `Lp`: the line is walked from the light, direction -L, parameter s;
-// forward distance t from the shadow origin so = P + N*bias is  t = (dist - bias*ndl) - s.
-// (o, d, maxDist) are the reference's forward shadow ray; every confirmation uses them untouched.
-__device__ __forceinline__ OccResult occluded_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float4* __restrict__ s_tri,
-                                                   d3 o, d3 d, double dist, d3 Lp, double maxDist, double bias, bool active,
-                                                   bool no_filter, uint32_t& confirms) {
-    OccState st = occ_begin(maxDist, bias, active);
+// One forward shadow ray of the reference (RE/Scene.h:86-104) plus what the reversed scan needs.
+struct ShadowRay {
+    d3 o, d;          // shadow origin so = P + N*bias and unit direction L: every FP64 confirmation uses them untouched
+    double dist;      // |Lp - P|
+    double maxDist;   // dist - bias
+    double ndl;       // N.L (> 0 when cast)
+    int self;         // sphere the shading point lies on, hit from outside (-1: none): its exact test cannot succeed
+    bool cast;
+};
+
+// Any-hit shadow query (see occluded() in rte_trace.cuh for the equivalence argument) for K rays of one thread
+// towards the light `Lp`, sphere phase scanned through that light's view: the line is walked from the light,
+// direction -L, parameter s; the forward distance from the shadow origin is  t = (dist - bias*ndl) - s.
+//
+// Candidates are resolved in canonical order, each one either
+//   * skipped: it is the front-face sphere the shading point lies on (both roots <= -bias: the exact test misses),
+//   * decided in FP32 when the interval arithmetic is conclusive: a certain occluder with t in (t_safe, maxDist),
+//     or certainly outside (behind the light / beyond the shaded point),
+//   * or confirmed in FP64 with the reference's own operation order.
+template <int K>
+__device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, d3 Lp,
+                                                      const ShadowRay (&ray)[K], double bias, bool no_filter, OccState (&st)[K],
+                                                      uint32_t& confirms, uint32_t& executed) {
+    uint32_t first[K];
     const int ns = sc.ns, ns_pad = sc.ns_pad;
-    uint32_t first = (uint32_t)ns;
+#pragma unroll
+    for (int k = 0; k < K; ++k) { st[k] = occ_begin(ray[k].maxDist, bias, ray[k].cast); first[k] = (uint32_t)ns; }
     if (ns > 0) {
-        const float S = sqrtf((float)dot(Lp, Lp)) * 1.0000002f + sc.sph_extent;
-        const ViewRay r = make_view_ray(-d, S);
+        const ViewBounds vb = view_bounds(sc, Lp, bias, true);
         const float* vf = reinterpret_cast<const float*>(view);
-        // occluders (and the `t <= bias` near cases) have s in (-bias, dist + bias): widen by 2*bias
-        const float s_max = __double2float_ru(dist + 2.0 * bias), s_min = -__double2float_ru(2.0 * bias);
+        const bool skip_self = bias >= 1e-5;
+        ViewRay r[K];
+        float tref[K], tmax_lo[K], tmax_hi[K];
+        const float tsafe_hi = __double2float_ru(130.0 * bias) + vb.slack;
+        const float bias_hi = __double2float_ru(bias) + vb.slack;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+            r[k] = make_view_ray(-ray[k].d);
+            tref[k] = (float)(ray[k].dist - bias * ray[k].ndl);
+            tmax_lo[k] = __double2float_rd(ray[k].maxDist) - vb.slack;
+            tmax_hi[k] = fmaxf(__double2float_ru(ray[k].maxDist) + vb.slack, bias_hi);  // also keeps every t <= bias (`near`)
+        }
+        constexpr int kWindow = 256;  // spheres between two resolutions + warp votes (any-hit early exit)
+        CandQueue<K> Q;
+        Q.n = 0;
+        int base = 0;
 #pragma unroll 1
-        for (int base = 0; base < ns_pad; base += kViewBlock) {
-            uint32_t cand = view_block_mask(view + base, r.ux2, r.uy2, r.uz2);
-            if (no_filter) cand = 0xFFFFFFFFu;
-            if (st.done) cand = 0u;
-            while (cand) {  // rare, divergent
-                const int k = __clz(cand);
-                cand &= ~(0x80000000u >> k);
-                const int idx = base + k;
-                if (idx >= ns) break;
-                if (!no_filter) {
-                    float s_lo, s_hi;
-                    view_interval(vf, idx, r, s_lo, s_hi);
-                    if (s_hi < s_min || s_lo > s_max) continue;  // behind the light / beyond the shaded point
+        while (base < ns_pad) {
+            const int stop = min(base + kWindow, ns_pad);
+#pragma unroll 1
+            do {
+                uint32_t cand[K];
+                view_block_masks<K>(view + base, r, cand);
+                executed += kViewBlock;
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    uint32_t c = no_filter ? 0xFFFFFFFFu : cand[k];
+                    if (st[k].done) c = 0u;
+                    Q.push_block(c, base, k, ns);
                 }
-                double t;
-                ++confirms;
-                if (sphere_exact(sc.sph64[idx], o, d, t)) {
-                    st.on_t(t, first, (uint32_t)idx);
-                    if (st.done) break;
+                base += kViewBlock;
+            } while (base < stop && __all_sync(kFullMask, Q.room()));
+            const int nmax = __reduce_max_sync(kFullMask, Q.n);
+#pragma unroll 1
+            for (int e = 0; e < nmax; ++e) {  // lane-parallel resolution, canonical order per ray
+                if (e >= Q.n) continue;
+                const uint32_t ent = Q.q[e];
+                const int k = (int)(ent >> 28), idx = (int)(ent & 0x0FFFFFFFu);
+                bool dn = false;
+#pragma unroll
+                for (int i = 0; i < K; ++i) if (i == k) dn = st[i].done;
+                if (dn) continue;  // decided by an earlier entry of this window
+                bool certain = false;
+                if (!no_filter) {
+                    if (skip_self && idx == ray[k].self) continue;
+                    const ViewChord ch = view_chord(vf, idx, pick<K>(r, k), vb);
+                    const float tc = tref[k] - ch.sc;  // forward distance of the chord centre
+                    const float t0_lo = tc - ch.hc_hi - vb.slack, t0_hi = tc - ch.hc_lo + vb.slack, t1_hi = tc + ch.hc_hi + vb.slack;
+                    if (t1_hi < 0.0f || t0_lo > tmax_hi[k]) continue;  // certainly no hit in (1e-6, maxDist), none <= bias
+                    certain = ch.hc_lo > 0.0f && t0_lo > tsafe_hi && t0_hi < tmax_lo[k];  // certainly t in (t_safe, maxDist)
+                }
+                double t = 0.0;
+                bool hit = false;
+                if (!certain) {
+                    ++confirms;
+                    hit = confirm_sphere(sc.sph64, idx, ray[k].o, ray[k].d, t);
+                }
+#pragma unroll
+                for (int i = 0; i < K; ++i) {
+                    if (i != k) continue;
+                    if (certain) { st[i].res.occluded = true; st[i].done = true; first[i] = (uint32_t)idx + 1u; }
+                    else if (hit) st[i].on_t(t, first[i], (uint32_t)idx);
                 }
             }
-            if ((base & 63) == 32 && __all_sync(kFullMask, st.done)) break;
+            Q.n = 0;
+            bool all_done = true;
+#pragma unroll
+            for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;
+            if (__all_sync(kFullMask, all_done)) break;
         }
     }
-    if (active) st.res.sph_tests = first;
-    if (sc.np > 0 || sc.nt > 0) {
-        if (!__all_sync(kFullMask, st.done)) {
-            const Ray32 r32 = make_ray32(sc, o, d, no_filter);
-            occ_planes_triangles(sc, s_tri, r32, o, d, st, confirms);
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+        if (ray[k].cast) st[k].res.sph_tests = first[k];
+}
+
+// Spheres through the light's view, then planes and triangles (general kernel).
+template <int K>
+__device__ __forceinline__ void occluded_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float4* __restrict__ s_tri,
+                                              d3 Lp, const ShadowRay (&ray)[K], double bias, bool no_filter, OccResult (&out)[K],
+                                              uint32_t& confirms, uint32_t& executed) {
+    OccState st[K];
+    occluded_spheres_view<K>(sc, view, Lp, ray, bias, no_filter, st, confirms, executed);
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (sc.np > 0 || sc.nt > 0) {
+            if (!__all_sync(kFullMask, st[k].done)) {
+                const Ray32 r32 = make_ray32(sc, ray[k].o, ray[k].d, no_filter);
+                occ_planes_triangles(sc, s_tri, r32, ray[k].o, ray[k].d, st[k], confirms);
+            }
         }
+        out[k] = st[k].res;
     }
-    return st.res;
 }
 
 }  // namespace rte

@@ -174,3 +174,46 @@ def test_errors(engine):
         engine.upload(bad, cam)
     engine.upload(arrays, cam)  # the ctx stays usable after argument errors
     assert engine.render_host(outputs=("prim_id",))["prim_id"].size == cam.width * cam.height
+
+
+@pytest.mark.parametrize("cfg", ["c2", "c3", "c2_band", "c2_odd"])
+def test_fast_kernel_is_bit_identical(engine, oracle, cfg):
+    """Without AOV outputs diffuse sphere/plane scenes take the lean multi-pixel kernel (render_fast_kernel):
+    same HDR bits, same fused RGB8, same algorithmic counters as the oracle and as the general kernel."""
+    opts = {}
+    if cfg == "c2":
+        arrays, cam = scenes.config2(scale=0.125)
+    elif cfg == "c3":
+        arrays, cam = scenes.config3(scale=0.125)
+    elif cfg == "c2_band":
+        arrays, cam = scenes.config2(scale=0.1)
+        opts = dict(row0=37, row1=150)
+    else:  # width / height not multiples of the 8 x 8 warp tile
+        arrays, cam = scenes.synthetic_room(203, 117, 100.0, 300, 3, 77)
+    engine.upload(arrays, cam)
+    fast = engine.render_host(outputs=("hdr64", "hdr", "rgb8"), tonemap_op=_abi.TM_ACES, **opts)
+    sf = engine.stats()
+    gen = engine.render_host(outputs=("hdr64", "hdr", "rgb8"), tonemap_op=_abi.TM_ACES, flags=_abi.FLAG_GENERAL_KERNEL, **opts)
+    sg = engine.stats()
+    o = oracle.render(arrays, cam, want_aovs=True, **opts)
+    assert np.array_equal(fast["hdr64"], o["hdr"]), f"max |dHDR| = {np.abs(fast['hdr64'] - o['hdr']).max()}"
+    for k in ("hdr64", "hdr", "rgb8"):
+        assert np.array_equal(fast[k], gen[k]), k
+    assert np.array_equal(fast["rgb8"], oracle.tonemap_all(o["hdr"])[_abi.TM_ACES])
+    for k in COUNTERS:
+        assert sf[k] == o[k] == sg[k], f"counter {k}: fast {sf[k]}, general {sg[k]}, oracle {o[k]}"
+    assert sf["sphere_tests_executed"] > 0
+
+
+def test_fast_kernel_stripes(engine):
+    """Interleaved stripes through the fast kernel == the same rows of the full frame."""
+    from raytracingengine_b200 import sharding
+    arrays, cam = scenes.config2(scale=0.1)
+    engine.upload(arrays, cam)
+    full = engine.render_host(outputs=("hdr64",))["hdr64"].reshape(cam.height, cam.width, 3)
+    world, S = 3, 8
+    for r in range(world):
+        o = sharding.stripe_opts(r, world, cam.height, S)
+        part = engine.render_host(outputs=("hdr64",), **o)["hdr64"]
+        rows = sharding.stripe_row_list(r, world, cam.height, S)
+        assert np.array_equal(part.reshape(len(rows), cam.width, 3), full[rows])

@@ -25,7 +25,7 @@ def main():
             t = e.stats()["tonemap_ms"]
         print(json.dumps({"cfg": name, "W": cam.width, "H": cam.height, "kernel_ms": round(s["kernel_ms"], 3),
                           "Mrays/s": round(rays / s["kernel_ms"] / 1e3, 1), "alg_TFLOPs": round(flops / s["kernel_ms"] / 1e9, 2),
-                          "confirms_per_ray": round(s["fp64_confirms"] / rays, 2), "marches": s["exact_marches"],
+                          "confirms_per_ray": round(s["fp64_confirms"] / rays, 2), "exec_frac": round(s["sphere_tests_executed"] / max(1, s["sphere_tests"]), 3), "marches": s["exact_marches"],
                           "tonemap7_ms": round(t, 4), "tonemap_GBs": round(n * 33 / t / 1e6, 1)}), flush=True)
 
 main()
