@@ -514,8 +514,19 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
     }
 }
 
-template <int K>
-__global__ void __launch_bounds__(kRenderMaxThreads, 1) render_fast_kernel(const __grid_constant__ RenderParams P) {
+#ifndef RTE_FAST_THREADS
+#define RTE_FAST_THREADS 320
+#endif
+#ifndef RTE_FAST_MINB
+#define RTE_FAST_MINB 2
+#endif
+constexpr int kFastThreads = RTE_FAST_THREADS;  // block size of the fast kernel when kFastMinBlocks CTAs fit one SM
+constexpr int kFastMinBlocks = RTE_FAST_MINB;
+
+// kBig = false: kFastThreads x kFastMinBlocks CTAs per SM; kBig = true: one 512-thread CTA per SM (views of large scenes)
+template <int K, bool kBig>
+__global__ void __launch_bounds__(kBig ? kRenderMaxThreads : kFastThreads, kBig ? 1 : kFastMinBlocks)
+render_fast_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ DevScene s_sc;
     __shared__ __align__(8) uint64_t s_bar;
@@ -593,16 +604,19 @@ cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double 
     return cudaGetLastError();
 }
 
-static cudaError_t launch_render_fn(const void* fn, int K, const RenderParams& p, int sm_count, cudaStream_t stream) {
+static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int small_threads, int small_min_blocks, int K,
+                                    const RenderParams& p, int sm_count, cudaStream_t stream) {
     const size_t smem = p.plan.total;
     cudaError_t e = ensure_smem(fn, smem);
     if (e != cudaSuccess) return e;
-    // 2 CTAs of 256 threads per SM when the arrays fit twice, else 1 CTA of 512 threads
-    int threads = kRenderThreads, per_sm = 0;
+    // several CTAs per SM when the staged arrays fit that often, else one CTA of 512 threads
+    int threads = small_threads, per_sm = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem);
     if (e != cudaSuccess) return e;
-    if (per_sm < 2) {
+    if (per_sm < small_min_blocks) {
+        fn = fn_big;
         threads = kRenderMaxThreads;
+        if ((e = ensure_smem(fn, smem)) != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem);
         if (e != cudaSuccess) return e;
     }
@@ -624,9 +638,10 @@ bool fast_path_eligible(const RenderParams& p) {
 
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream) {
     if (fast_path_eligible(p) && !p.force_general)
-        return launch_render_fn((const void*)render_fast_kernel<kViewPixels>, kViewPixels, p, sm_count, stream);
-    if (!p.sc.reflective) return launch_render_fn((const void*)render_kernel<1, false>, 1, p, sm_count, stream);
-    return launch_render_fn((const void*)render_kernel<1, true>, 1, p, sm_count, stream);
+        return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false>, (const void*)render_fast_kernel<kViewPixels, true>,
+                                kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream);
+    const void* fn = p.sc.reflective ? (const void*)render_kernel<1, true> : (const void*)render_kernel<1, false>;
+    return launch_render_fn(fn, fn, kRenderThreads, 2, 1, p, sm_count, stream);
 }
 
 // ------------------------------------------------------------------------------ ray queries

@@ -172,19 +172,19 @@ __device__ __forceinline__ ViewChord view_chord(const float* __restrict__ view, 
 // Instead every lane appends its candidates, (ray k << 28) | sphere index, to a small private queue during
 // the scan, and the warp resolves the queues lane-parallel in one compact loop per window: trip count =
 // the longest queue in the warp, one copy of the resolution code for all K rays.
+constexpr int kWindow = 256;  // spheres between two resolutions (+ warp vote for any-hit rays): bounds the queue
 template <int K>
 struct CandQueue {
-    static constexpr int kCap = 64 * K;
-    uint32_t q[kCap];
-    int n;
-    __device__ __forceinline__ void push_block(uint32_t c, int base, int k, int ns) {
+    uint16_t q[kWindow * K];  // (ray k << 8) | (sphere index - window start); local memory, only written entries are touched
+    // `n` is passed in and out so that it stays in a register (the dynamically indexed array lives in local memory)
+    __device__ __forceinline__ int push_block(uint32_t c, int rel, int k, int left, int n) {  // rel = base - window start, left = ns - base
         while (c) {  // short, divergent
             const int i = __clz(c);
             c &= ~(0x80000000u >> i);
-            if (base + i < ns) q[n++] = ((uint32_t)k << 28) | (uint32_t)(base + i);
+            if (i < left) q[n++] = (uint16_t)((k << 8) | (rel + i));
         }
+        return n;
     }
-    __device__ __forceinline__ bool room() const { return n <= kCap - kViewBlock * K; }
 };
 
 template <int K, class T>
@@ -208,28 +208,34 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
     const float* vf = reinterpret_cast<const float*>(view);
     const int ns = sc.ns, ns_pad = sc.ns_pad;
     CandQueue<K> Q;
-    Q.n = 0;
+    int qn = 0;
     int base = 0;
 #pragma unroll 1
     while (base < ns_pad) {
+        const int wbase = base, stop = min(base + kWindow, ns_pad);
 #pragma unroll 1
-        do {  // scan until the view ends or some lane's queue could overflow
+        do {
             uint32_t cand[K];
             view_block_masks<K>(view + base, r, cand);
+            uint32_t any = 0;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                uint32_t c = no_filter ? 0xFFFFFFFFu : cand[k];
-                if (!alive[k]) c = 0u;
-                Q.push_block(c, base, k, ns);
+                cand[k] = no_filter ? 0xFFFFFFFFu : cand[k];
+                if (!alive[k]) cand[k] = 0u;
+                any |= cand[k];
+            }
+            if (any) {  // ~5 % of the blocks
+#pragma unroll
+                for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn);
             }
             base += kViewBlock;
-        } while (base < ns_pad && __all_sync(kFullMask, Q.room()));
-        const int nmax = __reduce_max_sync(kFullMask, Q.n);
+        } while (base < stop);
+        const int nmax = __reduce_max_sync(kFullMask, qn);
 #pragma unroll 1
         for (int e = 0; e < nmax; ++e) {  // lane-parallel resolution, ascending index per ray
-            if (e >= Q.n) continue;
+            if (e >= qn) continue;
             const uint32_t ent = Q.q[e];
-            const int k = (int)(ent >> 28), idx = (int)(ent & 0x0FFFFFFFu);
+            const int k = (int)(ent >> 8), idx = wbase + (int)(ent & 0xFFu);
             const d3 dk = d[k];  // FP64 ray data is indexed dynamically: it lives in local memory, not in K selects
             if (!no_filter) {
                 const ViewChord ch = view_chord(vf, idx, pick<K>(r, k), vb);
@@ -247,7 +253,7 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
                 }
             }
         }
-        Q.n = 0;
+        qn = 0;
     }
 }
 
@@ -311,32 +317,36 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
             tmax_lo[k] = __double2float_rd(ray[k].maxDist) - vb.slack;
             tmax_hi[k] = fmaxf(__double2float_ru(ray[k].maxDist) + vb.slack, bias_hi);  // also keeps every t <= bias (`near`)
         }
-        constexpr int kWindow = 256;  // spheres between two resolutions + warp votes (any-hit early exit)
         CandQueue<K> Q;
-        Q.n = 0;
+        int qn = 0;
         int base = 0;
 #pragma unroll 1
         while (base < ns_pad) {
-            const int stop = min(base + kWindow, ns_pad);
+            const int wbase = base, stop = min(base + kWindow, ns_pad);
 #pragma unroll 1
             do {
                 uint32_t cand[K];
                 view_block_masks<K>(view + base, r, cand);
                 executed += kViewBlock;
+                uint32_t any = 0;
 #pragma unroll
                 for (int k = 0; k < K; ++k) {
-                    uint32_t c = no_filter ? 0xFFFFFFFFu : cand[k];
-                    if (st[k].done) c = 0u;
-                    Q.push_block(c, base, k, ns);
+                    cand[k] = no_filter ? 0xFFFFFFFFu : cand[k];
+                    if (st[k].done) cand[k] = 0u;
+                    any |= cand[k];
+                }
+                if (any) {  // ~5 % of the blocks
+#pragma unroll
+                    for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn);
                 }
                 base += kViewBlock;
-            } while (base < stop && __all_sync(kFullMask, Q.room()));
-            const int nmax = __reduce_max_sync(kFullMask, Q.n);
+            } while (base < stop);
+            const int nmax = __reduce_max_sync(kFullMask, qn);
 #pragma unroll 1
             for (int e = 0; e < nmax; ++e) {  // lane-parallel resolution, canonical order per ray
-                if (e >= Q.n) continue;
+                if (e >= qn) continue;
                 const uint32_t ent = Q.q[e];
-                const int k = (int)(ent >> 28), idx = (int)(ent & 0x0FFFFFFFu);
+                const int k = (int)(ent >> 8), idx = wbase + (int)(ent & 0xFFu);
                 bool dn = false;
 #pragma unroll
                 for (int i = 0; i < K; ++i) if (i == k) dn = st[i].done;
@@ -363,7 +373,7 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
                     else if (hit) st[i].on_t(t, first[i], (uint32_t)idx);
                 }
             }
-            Q.n = 0;
+            qn = 0;
             bool all_done = true;
 #pragma unroll
             for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;

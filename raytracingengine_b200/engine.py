@@ -15,7 +15,7 @@ import numpy as np
 from . import _abi
 from .scene import Camera, SceneArrays
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "librte_b200.so")
+LIB_PATH = os.environ.get("RTE_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "librte_b200.so")  # env: developer A/B builds
 
 # every symbol include/rte.h declares (tests/test_abi.py checks the header against this list)
 SYMBOLS = (
