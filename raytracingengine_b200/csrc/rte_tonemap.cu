@@ -25,17 +25,17 @@ __global__ void __launch_bounds__(kTmThreads) tonemap_kernel(const __grid_consta
         float4 px[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) px[j] = ldg_stream(src + j);
-        uint32_t c[4][RTE_TM_COUNT];
+        tm32::Q3 c[4][RTE_TM_COUNT];
 #pragma unroll
         for (int j = 0; j < 4; ++j) tm32::apply_all<kMask>(tm32::mk3(px[j].x, px[j].y, px[j].z), K, mask, c[j]);
 #pragma unroll
         for (int op = 0; op < RTE_TM_COUNT; ++op) {
             if (!(mask & (1u << op))) continue;
-            // 4 pixels x RGB = 12 bytes = 3 aligned words
+            // 4 pixels x RGB = 12 bytes = 3 aligned words: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
             uint32_t* dst = reinterpret_cast<uint32_t*>(P.rgb8[op] + 12 * q);
-            __stcs(dst + 0, c[0][op] | (c[1][op] << 24));
-            __stcs(dst + 1, (c[1][op] >> 8) | (c[2][op] << 16));
-            __stcs(dst + 2, (c[2][op] >> 16) | (c[3][op] << 8));
+            __stcs(dst + 0, tm32::pack4(c[0][op].r, c[0][op].g, c[0][op].b, c[1][op].r));
+            __stcs(dst + 1, tm32::pack4(c[1][op].g, c[1][op].b, c[2][op].r, c[2][op].g));
+            __stcs(dst + 2, tm32::pack4(c[2][op].b, c[3][op].r, c[3][op].g, c[3][op].b));
         }
     }
     // tail (n_pixels % 4) — bytes
@@ -43,13 +43,13 @@ __global__ void __launch_bounds__(kTmThreads) tonemap_kernel(const __grid_consta
     const int64_t i = tail0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < P.n_pixels) {
         const float4 v = P.hdr[i];
-        uint32_t c[RTE_TM_COUNT];
+        tm32::Q3 c[RTE_TM_COUNT];
         tm32::apply_all<kMask>(tm32::mk3(v.x, v.y, v.z), K, mask, c);
 #pragma unroll
         for (int op = 0; op < RTE_TM_COUNT; ++op) {
             if (!(mask & (1u << op))) continue;
             uint8_t* d = P.rgb8[op] + 3 * i;
-            d[0] = (uint8_t)(c[op] & 255u); d[1] = (uint8_t)((c[op] >> 8) & 255u); d[2] = (uint8_t)((c[op] >> 16) & 255u);
+            d[0] = (uint8_t)(c[op].r & 255u); d[1] = (uint8_t)(c[op].g & 255u); d[2] = (uint8_t)(c[op].b & 255u);
         }
     }
 }

@@ -82,27 +82,26 @@ __device__ __forceinline__ uchar3 to_color(d3 p) {
 
 }  // namespace tm64
 
-// FP32 flavour for the stand-alone HBM-bound pass (tonemapAll over a float4 HDR buffer).  Results may
-// differ from the FP64 reference by one quantisation step when c*255 lands within ~1e-4 of an integer
-// (tolerance of the pass: +-1 LSB, tests/test_gpu_tonemap.py); divisions are rcp.approx based and
-// log/pow are lg2/ex2.approx based, i.e. 2 instructions each instead of the ~10/~50 of the IEEE forms.
+// FP32 flavour for the stand-alone HBM-bound pass (tonemapAll over a float4 HDR buffer).  Results may differ
+// from the FP64 reference by one quantisation step when c*255 lands within ~1e-4 of an integer (tolerance of
+// the pass: +-1 LSB, tests/test_gpu_tonemap.py).  Built to stay off the XU pipe (16 lanes/clk/SM), which bounded
+// the first version (ncu r01a: XU 77 %, DRAM 32 %):
+//   * divisions are one MUFU.RCP (rcp.approx.ftz) + one FMUL; log/pow are MUFU.LG2 / MUFU.EX2;
+//   * clamp to [0,1] is the .SAT modifier of the producing FMUL/FFMA (NaN -> 0 exactly like ClampVec3's
+//     std::max(0, NaN), +inf -> 1);
+//   * float -> byte is NOT an F2I (XU pipe): fma.rz(y, 255, 2^23) leaves floor(y*255) in the low mantissa byte,
+//     and four such bytes are merged with PRMT (ALU pipe).
 namespace tm32 {
 
 struct f3 { float x, y, z; };
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
-__device__ __forceinline__ float sat(float v) { return fminf(1.0f, fmaxf(0.0f, v)); }  // NaN -> 0 like ClampVec3
-__device__ __forceinline__ float qdiv(float a, float b) { return __fdividef(a, b); }
+__device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float mul_sat(float a, float b) { float r; asm("mul.rn.sat.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
 __device__ __forceinline__ float luminance(f3 c) { return fmaf(c.z, 0.0722f, fmaf(c.y, 0.7152f, c.x * 0.2126f)); }
-
-__device__ __forceinline__ float u2p(float x) {  // uncharted2_tonemap_partial, RE/RaytracingEngine.cpp:78-87
-    const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
-    const float num = fmaf(x, fmaf(x, A, C * B), D * E), den = fmaf(x, fmaf(x, A, B), D * F);
-    return qdiv(num, den) - E / F;
-}
-__device__ __forceinline__ float aces1(float x) {  // aces_approx, :89-98
-    const float v = x * 0.6f;
-    return sat(qdiv(v * fmaf(v, 2.51f, 0.03f), fmaf(v, fmaf(v, 2.43f, 0.59f), 0.14f)));
-}
+// toColor's (uint8)(c * 255.0) for c already in [0,1]: the byte sits in bits 0..7 of the result
+__device__ __forceinline__ uint32_t qbyte(float y01) { return __float_as_uint(__fmaf_rz(y01, 255.0f, 8388608.0f)); }
 
 struct Consts {
     float inv_wsq;      // 1 / max_white^2
@@ -110,35 +109,62 @@ struct Consts {
     float white_scale;  // 1 / uncharted2_partial(11.2)
 };
 
-// all operators of `mask` for one pixel; out[op] = quantised RGB packed as r | g<<8 | b<<16
+// One pixel, all operators of `mask`: out[op] = three quantised channels with the byte in bits 0..7 each.
+struct Q3 { uint32_t r, g, b; };
 template <uint32_t kMask>
-__device__ __forceinline__ void apply_all(f3 c, const Consts& k, uint32_t mask, uint32_t out[RTE_TM_COUNT]) {
-    auto pack = [](float r, float g, float b) -> uint32_t {
-        return __float2uint_rz(sat(r) * 255.0f) | (__float2uint_rz(sat(g) * 255.0f) << 8) | (__float2uint_rz(sat(b) * 255.0f) << 16);
-    };
+__device__ __forceinline__ void apply_all(f3 c, const Consts& k, uint32_t mask, Q3 (&out)[RTE_TM_COUNT]) {
     const uint32_t m = kMask ? kMask : mask;
-    const f3 r1 = mk3(__frcp_rn(c.x + 1.0f), __frcp_rn(c.y + 1.0f), __frcp_rn(c.z + 1.0f));  // shared by ops 1 and 2
-    if (m & (1u << RTE_TM_SIMPLE)) out[RTE_TM_SIMPLE] = pack(c.x, c.y, c.z);
-    if (m & (1u << RTE_TM_REINHARD_SIMPLE)) out[RTE_TM_REINHARD_SIMPLE] = pack(c.x * r1.x, c.y * r1.y, c.z * r1.z);
-    if (m & (1u << RTE_TM_REINHARD_EXTENDED))
-        out[RTE_TM_REINHARD_EXTENDED] = pack(c.x * fmaf(c.x, k.inv_wsq, 1.0f) * r1.x, c.y * fmaf(c.y, k.inv_wsq, 1.0f) * r1.y,
-                                             c.z * fmaf(c.z, k.inv_wsq, 1.0f) * r1.z);
+    auto put = [&](int op, float r, float g, float b) { out[op].r = qbyte(r); out[op].g = qbyte(g); out[op].b = qbyte(b); };
+    if (m & (1u << RTE_TM_SIMPLE)) put(RTE_TM_SIMPLE, __saturatef(c.x), __saturatef(c.y), __saturatef(c.z));  // :123-131
+    if (m & ((1u << RTE_TM_REINHARD_SIMPLE) | (1u << RTE_TM_REINHARD_EXTENDED))) {
+        const f3 r1 = mk3(rcp(c.x + 1.0f), rcp(c.y + 1.0f), rcp(c.z + 1.0f));  // shared by both operators
+        if (m & (1u << RTE_TM_REINHARD_SIMPLE))  // x / (1 + x), :133-135
+            put(RTE_TM_REINHARD_SIMPLE, mul_sat(c.x, r1.x), mul_sat(c.y, r1.y), mul_sat(c.z, r1.z));
+        if (m & (1u << RTE_TM_REINHARD_EXTENDED))  // x (1 + x / w^2) / (1 + x), :137-141
+            put(RTE_TM_REINHARD_EXTENDED, mul_sat(c.x * fmaf(c.x, k.inv_wsq, 1.0f), r1.x), mul_sat(c.y * fmaf(c.y, k.inv_wsq, 1.0f), r1.y),
+                mul_sat(c.z * fmaf(c.z, k.inv_wsq, 1.0f), r1.z));
+    }
     if (m & ((1u << RTE_TM_REINHARD_EXTENDED_LUMINANCE) | (1u << RTE_TM_REINHARD_JODIE))) {
         const float L = luminance(c);
-        const float invL = __frcp_rn(L);  // L == 0 -> inf, 0 * inf = NaN -> 0 after sat, like 0/0 in the reference
-        if (m & (1u << RTE_TM_REINHARD_EXTENDED_LUMINANCE)) {
-            const float s = qdiv(L * fmaf(L, k.inv_wsq, 1.0f), 1.0f + L) * invL;
-            out[RTE_TM_REINHARD_EXTENDED_LUMINANCE] = pack(c.x * s, c.y * s, c.z * s);
+        const float qnan = __int_as_float(0x7fc00000);
+        if (m & (1u << RTE_TM_REINHARD_EXTENDED_LUMINANCE)) {  // x * (Ln / L), Ln = L (1 + L / w^2) / (1 + L), :143-148
+            float s = fmaf(L, k.inv_wsq, 1.0f) * rcp(1.0f + L);
+            s = (L == 0.0f) ? qnan : s;  // the reference divides 0 by 0 here: NaN -> 0 in every channel
+            put(RTE_TM_REINHARD_EXTENDED_LUMINANCE, mul_sat(c.x, s), mul_sat(c.y, s), mul_sat(c.z, s));
         }
-        if (m & (1u << RTE_TM_REINHARD_JODIE)) {  // (a / ln(2 + (L/0.85)^1.7)) * ln(1 + L), :150-154
-            const float p = exp2f(1.7f * __log2f(L * (1.0f / 0.85f)));
-            const float s = qdiv(k.jodie_a * __log2f(1.0f + L), __log2f(2.0f + p)) * invL;  // ln ratios == log2 ratios
-            out[RTE_TM_REINHARD_JODIE] = pack(c.x * s, c.y * s, c.z * s);
+        if (m & (1u << RTE_TM_REINHARD_JODIE)) {  // x * (Lm / L), Lm = (a / ln(2 + (L/0.85)^1.7)) * ln(1 + L), :150-154
+            const float q = 1.7f * lg2(L * (1.0f / 0.85f));
+            const float lgp = q > 120.0f ? q : lg2(2.0f + ex2(q));  // (L/0.85)^1.7 overflows FP32 long after the 2 stopped mattering
+            const float s = (k.jodie_a * lg2(1.0f + L)) * rcp(lgp * L);  // ln ratios == log2 ratios
+            put(RTE_TM_REINHARD_JODIE, mul_sat(c.x, s), mul_sat(c.y, s), mul_sat(c.z, s));
         }
     }
-    if (m & (1u << RTE_TM_UNCHARTED2))
-        out[RTE_TM_UNCHARTED2] = pack(u2p(c.x * 2.0f) * k.white_scale, u2p(c.y * 2.0f) * k.white_scale, u2p(c.z * 2.0f) * k.white_scale);
-    if (m & (1u << RTE_TM_ACES)) out[RTE_TM_ACES] = pack(aces1(c.x), aces1(c.y), aces1(c.z));
+    // The two rational operators square their argument: beyond 1e15 they sit on their asymptote (to 1e-15) and FP32
+    // would overflow where the FP64 reference does not.  +inf stays special: the reference evaluates inf/inf = NaN -> 0.
+    const float qn = __int_as_float(0x7fc00000), big = 1.0e15f;
+    auto lim = [&](float v) { return v == INFINITY ? qn : (v > big ? big : v); };  // NaN passes through (fminf would drop it)
+    const f3 cc = mk3(lim(c.x), lim(c.y), lim(c.z));
+    if (m & (1u << RTE_TM_UNCHARTED2)) {  // :78-87,156-163
+        auto u2 = [&](float v) {
+            const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
+            const float x = v + v;
+            const float num = fmaf(x, fmaf(x, A, C * B), D * E), den = fmaf(x, fmaf(x, A, B), D * F);
+            return mul_sat(fmaf(num, rcp(den), -(E / F)), k.white_scale);
+        };
+        put(RTE_TM_UNCHARTED2, u2(cc.x), u2(cc.y), u2(cc.z));
+    }
+    if (m & (1u << RTE_TM_ACES)) {  // :89-98
+        auto ac = [](float x) {
+            const float v = x * 0.6f;
+            return mul_sat(v * fmaf(v, 2.51f, 0.03f), rcp(fmaf(v, fmaf(v, 2.43f, 0.59f), 0.14f)));
+        };
+        put(RTE_TM_ACES, ac(cc.x), ac(cc.y), ac(cc.z));
+    }
+}
+
+// 4 pixels x RGB (bytes in bits 0..7 of twelve words) -> three packed 32-bit words
+__device__ __forceinline__ uint32_t pack4(uint32_t b0, uint32_t b1, uint32_t b2, uint32_t b3) {
+    return __byte_perm(__byte_perm(b0, b1, 0x0040), __byte_perm(b2, b3, 0x0040), 0x5410);
 }
 
 }  // namespace tm32
