@@ -574,11 +574,12 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             const int band_y = ty * TH + k * kTileH + ly;
             const int64_t oi = (int64_t)band_y * W + px[k];
             const d3 v = c[k];
-            if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[oi] = make_float4((float)v.x, (float)v.y, (float)v.z, 0.f);
-            if (P.out.hdr64) { P.out.hdr64[3 * oi] = v.x; P.out.hdr64[3 * oi + 1] = v.y; P.out.hdr64[3 * oi + 2] = v.z; }
+            // streaming stores (st.global.cs): the framebuffers are write-once and must not evict the threads' local memory from L2
+            if (P.out.hdr) __stcs(reinterpret_cast<float4*>(P.out.hdr) + oi, make_float4((float)v.x, (float)v.y, (float)v.z, 0.f));
+            if (P.out.hdr64) { __stcs(P.out.hdr64 + 3 * oi, v.x); __stcs(P.out.hdr64 + 3 * oi + 1, v.y); __stcs(P.out.hdr64 + 3 * oi + 2, v.z); }
             if (P.out.rgb8 && P.tonemap_op >= 0) {
                 const uchar3 q = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));
-                P.out.rgb8[3 * oi] = q.x; P.out.rgb8[3 * oi + 1] = q.y; P.out.rgb8[3 * oi + 2] = q.z;
+                __stcs(P.out.rgb8 + 3 * oi, q.x); __stcs(P.out.rgb8 + 3 * oi + 1, q.y); __stcs(P.out.rgb8 + 3 * oi + 2, q.z);
             }
         }
         const uint32_t v[kStatCount] = {n_in, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms, cnt.sph_exec};

@@ -16,42 +16,55 @@ constexpr int kTmThreads = 256;
 
 __device__ __forceinline__ float4 ldg_stream(const float4* p) { return __ldcs(p); }
 
+// one operator over the 4 prepared pixels of a thread -> 12 bytes = 3 aligned words: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+template <int kOp>
+__device__ __forceinline__ void store_op(const tm32::Shared (&s)[4], const tm32::Consts& K, uint8_t* rgb8, int64_t q) {
+    uint32_t b[12];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const tm32::f3 y = tm32::apply_op<kOp>(s[j], K);
+        b[3 * j] = tm32::qbyte(y.x); b[3 * j + 1] = tm32::qbyte(y.y); b[3 * j + 2] = tm32::qbyte(y.z);
+    }
+    uint32_t* dst = reinterpret_cast<uint32_t*>(rgb8 + 12 * q);
+    __stcs(dst + 0, tm32::pack4(b[0], b[1], b[2], b[3]));
+    __stcs(dst + 1, tm32::pack4(b[4], b[5], b[6], b[7]));
+    __stcs(dst + 2, tm32::pack4(b[8], b[9], b[10], b[11]));
+}
+template <int kOp>
+__device__ __forceinline__ void store_op_tail(const tm32::Shared& s, const tm32::Consts& K, uint8_t* rgb8, int64_t i) {
+    const tm32::f3 y = tm32::apply_op<kOp>(s, K);
+    uint8_t* d = rgb8 + 3 * i;
+    d[0] = (uint8_t)(tm32::qbyte(y.x) & 255u); d[1] = (uint8_t)(tm32::qbyte(y.y) & 255u); d[2] = (uint8_t)(tm32::qbyte(y.z) & 255u);
+}
+
 template <uint32_t kMask>
-__global__ void __launch_bounds__(kTmThreads) tonemap_kernel(const __grid_constant__ TonemapParams P, const tm32::Consts K) {
+__global__ void __launch_bounds__(kTmThreads, 4) tonemap_kernel(const __grid_constant__ TonemapParams P, const tm32::Consts K) {
     const int64_t n_quads = P.n_pixels >> 2;
     const uint32_t mask = kMask ? kMask : P.op_mask;
+#define RTE_TM_EACH(X) X(0) X(1) X(2) X(3) X(4) X(5) X(6)
     for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_quads; q += (int64_t)gridDim.x * blockDim.x) {
         const float4* src = P.hdr + 4 * q;
         float4 px[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) px[j] = ldg_stream(src + j);
-        tm32::Q3 c[4][RTE_TM_COUNT];
+        tm32::Shared s[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) tm32::apply_all<kMask>(tm32::mk3(px[j].x, px[j].y, px[j].z), K, mask, c[j]);
-#pragma unroll
-        for (int op = 0; op < RTE_TM_COUNT; ++op) {
-            if (!(mask & (1u << op))) continue;
-            // 4 pixels x RGB = 12 bytes = 3 aligned words: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
-            uint32_t* dst = reinterpret_cast<uint32_t*>(P.rgb8[op] + 12 * q);
-            __stcs(dst + 0, tm32::pack4(c[0][op].r, c[0][op].g, c[0][op].b, c[1][op].r));
-            __stcs(dst + 1, tm32::pack4(c[1][op].g, c[1][op].b, c[2][op].r, c[2][op].g));
-            __stcs(dst + 2, tm32::pack4(c[2][op].b, c[3][op].r, c[3][op].g, c[3][op].b));
-        }
+        for (int j = 0; j < 4; ++j) s[j] = tm32::prepare<kMask>(tm32::mk3(px[j].x, px[j].y, px[j].z), mask);
+#define RTE_TM_DO(op) if (mask & (1u << op)) store_op<op>(s, K, P.rgb8[op], q);
+        RTE_TM_EACH(RTE_TM_DO)
+#undef RTE_TM_DO
     }
     // tail (n_pixels % 4) — bytes
     const int64_t tail0 = n_quads << 2;
     const int64_t i = tail0 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < P.n_pixels) {
         const float4 v = P.hdr[i];
-        tm32::Q3 c[RTE_TM_COUNT];
-        tm32::apply_all<kMask>(tm32::mk3(v.x, v.y, v.z), K, mask, c);
-#pragma unroll
-        for (int op = 0; op < RTE_TM_COUNT; ++op) {
-            if (!(mask & (1u << op))) continue;
-            uint8_t* d = P.rgb8[op] + 3 * i;
-            d[0] = (uint8_t)(c[op].r & 255u); d[1] = (uint8_t)(c[op].g & 255u); d[2] = (uint8_t)(c[op].b & 255u);
-        }
+        const tm32::Shared s = tm32::prepare<kMask>(tm32::mk3(v.x, v.y, v.z), mask);
+#define RTE_TM_DO(op) if (mask & (1u << op)) store_op_tail<op>(s, K, P.rgb8[op], i);
+        RTE_TM_EACH(RTE_TM_DO)
+#undef RTE_TM_DO
     }
+#undef RTE_TM_EACH
 }
 
 static float u2p_host(float x) {
@@ -67,10 +80,15 @@ cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t st
     k.white_scale = 1.0f / u2p_host(11.2f);
     const int64_t n_quads = (p.n_pixels + 3) / 4;
     int64_t blocks = (n_quads + kTmThreads - 1) / kTmThreads;
-    const int64_t cap = (int64_t)sm_count * 8;  // 8 resident CTAs of 256 threads per SM
+    constexpr uint32_t kAll = (1u << RTE_TM_COUNT) - 1u;
+    const void* fn = p.op_mask == kAll ? (const void*)tonemap_kernel<kAll>
+                   : p.op_mask == (1u << RTE_TM_ACES) ? (const void*)tonemap_kernel<(1u << RTE_TM_ACES)> : (const void*)tonemap_kernel<0u>;
+    int per_sm = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kTmThreads, 0);
+    if (e != cudaSuccess) return e;
+    const int64_t cap = (int64_t)sm_count * (per_sm > 0 ? per_sm : 1);  // one resident wave, grid-stride loop
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    constexpr uint32_t kAll = (1u << RTE_TM_COUNT) - 1u;
     if (p.op_mask == kAll) tonemap_kernel<kAll><<<(unsigned)blocks, kTmThreads, 0, stream>>>(p, k);
     else if (p.op_mask == (1u << RTE_TM_ACES)) tonemap_kernel<(1u << RTE_TM_ACES)><<<(unsigned)blocks, kTmThreads, 0, stream>>>(p, k);
     else tonemap_kernel<0u><<<(unsigned)blocks, kTmThreads, 0, stream>>>(p, k);

@@ -109,57 +109,67 @@ struct Consts {
     float white_scale;  // 1 / uncharted2_partial(11.2)
 };
 
-// One pixel, all operators of `mask`: out[op] = three quantised channels with the byte in bits 0..7 each.
-struct Q3 { uint32_t r, g, b; };
+// Per-pixel values shared by several operators (computed once, kept while the operators are applied one after the
+// other so that only one operator's 12 output bytes are live at a time: 48 registers instead of 128).
+struct Shared {
+    f3 c;     // the pixel
+    f3 r1;    // 1 / (1 + c): Reinhard, Reinhard extended
+    f3 cc;    // c limited for the rational operators (see below)
+    float L;  // luminance
+};
 template <uint32_t kMask>
-__device__ __forceinline__ void apply_all(f3 c, const Consts& k, uint32_t mask, Q3 (&out)[RTE_TM_COUNT]) {
+__device__ __forceinline__ Shared prepare(f3 c, uint32_t mask) {
     const uint32_t m = kMask ? kMask : mask;
-    auto put = [&](int op, float r, float g, float b) { out[op].r = qbyte(r); out[op].g = qbyte(g); out[op].b = qbyte(b); };
-    if (m & (1u << RTE_TM_SIMPLE)) put(RTE_TM_SIMPLE, __saturatef(c.x), __saturatef(c.y), __saturatef(c.z));  // :123-131
-    if (m & ((1u << RTE_TM_REINHARD_SIMPLE) | (1u << RTE_TM_REINHARD_EXTENDED))) {
-        const f3 r1 = mk3(rcp(c.x + 1.0f), rcp(c.y + 1.0f), rcp(c.z + 1.0f));  // shared by both operators
-        if (m & (1u << RTE_TM_REINHARD_SIMPLE))  // x / (1 + x), :133-135
-            put(RTE_TM_REINHARD_SIMPLE, mul_sat(c.x, r1.x), mul_sat(c.y, r1.y), mul_sat(c.z, r1.z));
-        if (m & (1u << RTE_TM_REINHARD_EXTENDED))  // x (1 + x / w^2) / (1 + x), :137-141
-            put(RTE_TM_REINHARD_EXTENDED, mul_sat(c.x * fmaf(c.x, k.inv_wsq, 1.0f), r1.x), mul_sat(c.y * fmaf(c.y, k.inv_wsq, 1.0f), r1.y),
-                mul_sat(c.z * fmaf(c.z, k.inv_wsq, 1.0f), r1.z));
+    Shared s;
+    s.c = c;
+    if (m & ((1u << RTE_TM_REINHARD_SIMPLE) | (1u << RTE_TM_REINHARD_EXTENDED))) s.r1 = mk3(rcp(c.x + 1.0f), rcp(c.y + 1.0f), rcp(c.z + 1.0f));
+    if (m & ((1u << RTE_TM_REINHARD_EXTENDED_LUMINANCE) | (1u << RTE_TM_REINHARD_JODIE))) s.L = luminance(c);
+    if (m & ((1u << RTE_TM_UNCHARTED2) | (1u << RTE_TM_ACES))) {
+        // The two rational operators square their argument: beyond 1e15 they sit on their asymptote (to 1e-15) and FP32
+        // would overflow where the FP64 reference does not.  +inf stays special: the reference evaluates inf/inf = NaN -> 0.
+        const float qn = __int_as_float(0x7fc00000), big = 1.0e15f;
+        auto lim = [&](float v) { return v == INFINITY ? qn : (v > big ? big : v); };  // NaN passes through (fminf would drop it)
+        s.cc = mk3(lim(c.x), lim(c.y), lim(c.z));
     }
-    if (m & ((1u << RTE_TM_REINHARD_EXTENDED_LUMINANCE) | (1u << RTE_TM_REINHARD_JODIE))) {
-        const float L = luminance(c);
-        const float qnan = __int_as_float(0x7fc00000);
-        if (m & (1u << RTE_TM_REINHARD_EXTENDED_LUMINANCE)) {  // x * (Ln / L), Ln = L (1 + L / w^2) / (1 + L), :143-148
-            float s = fmaf(L, k.inv_wsq, 1.0f) * rcp(1.0f + L);
-            s = (L == 0.0f) ? qnan : s;  // the reference divides 0 by 0 here: NaN -> 0 in every channel
-            put(RTE_TM_REINHARD_EXTENDED_LUMINANCE, mul_sat(c.x, s), mul_sat(c.y, s), mul_sat(c.z, s));
-        }
-        if (m & (1u << RTE_TM_REINHARD_JODIE)) {  // x * (Lm / L), Lm = (a / ln(2 + (L/0.85)^1.7)) * ln(1 + L), :150-154
-            const float q = 1.7f * lg2(L * (1.0f / 0.85f));
-            const float lgp = q > 120.0f ? q : lg2(2.0f + ex2(q));  // (L/0.85)^1.7 overflows FP32 long after the 2 stopped mattering
-            const float s = (k.jodie_a * lg2(1.0f + L)) * rcp(lgp * L);  // ln ratios == log2 ratios
-            put(RTE_TM_REINHARD_JODIE, mul_sat(c.x, s), mul_sat(c.y, s), mul_sat(c.z, s));
-        }
+    return s;
+}
+
+// One operator on one prepared pixel -> three channels in [0,1] (NaN already mapped to 0 by .sat)
+template <int kOp>
+__device__ __forceinline__ f3 apply_op(const Shared& s, const Consts& k) {
+    const f3 c = s.c;
+    if (kOp == RTE_TM_SIMPLE) return mk3(__saturatef(c.x), __saturatef(c.y), __saturatef(c.z));  // :123-131
+    if (kOp == RTE_TM_REINHARD_SIMPLE) return mk3(mul_sat(c.x, s.r1.x), mul_sat(c.y, s.r1.y), mul_sat(c.z, s.r1.z));  // x / (1 + x), :133-135
+    if (kOp == RTE_TM_REINHARD_EXTENDED)  // x (1 + x / w^2) / (1 + x), :137-141
+        return mk3(mul_sat(c.x * fmaf(c.x, k.inv_wsq, 1.0f), s.r1.x), mul_sat(c.y * fmaf(c.y, k.inv_wsq, 1.0f), s.r1.y),
+                   mul_sat(c.z * fmaf(c.z, k.inv_wsq, 1.0f), s.r1.z));
+    if (kOp == RTE_TM_REINHARD_EXTENDED_LUMINANCE) {  // x * (Ln / L), Ln = L (1 + L / w^2) / (1 + L), :143-148
+        const float L = s.L;
+        float f = fmaf(L, k.inv_wsq, 1.0f) * rcp(1.0f + L);
+        f = (L == 0.0f) ? __int_as_float(0x7fc00000) : f;  // the reference divides 0 by 0 here: NaN -> 0 in every channel
+        return mk3(mul_sat(c.x, f), mul_sat(c.y, f), mul_sat(c.z, f));
     }
-    // The two rational operators square their argument: beyond 1e15 they sit on their asymptote (to 1e-15) and FP32
-    // would overflow where the FP64 reference does not.  +inf stays special: the reference evaluates inf/inf = NaN -> 0.
-    const float qn = __int_as_float(0x7fc00000), big = 1.0e15f;
-    auto lim = [&](float v) { return v == INFINITY ? qn : (v > big ? big : v); };  // NaN passes through (fminf would drop it)
-    const f3 cc = mk3(lim(c.x), lim(c.y), lim(c.z));
-    if (m & (1u << RTE_TM_UNCHARTED2)) {  // :78-87,156-163
+    if (kOp == RTE_TM_REINHARD_JODIE) {  // x * (Lm / L), Lm = (a / ln(2 + (L/0.85)^1.7)) * ln(1 + L), :150-154
+        const float L = s.L;
+        const float q = 1.7f * lg2(L * (1.0f / 0.85f));
+        const float lgp = q > 120.0f ? q : lg2(2.0f + ex2(q));  // (L/0.85)^1.7 overflows FP32 long after the 2 stopped mattering
+        const float f = (k.jodie_a * lg2(1.0f + L)) * rcp(lgp * L);  // ln ratios == log2 ratios
+        return mk3(mul_sat(c.x, f), mul_sat(c.y, f), mul_sat(c.z, f));
+    }
+    if (kOp == RTE_TM_UNCHARTED2) {  // :78-87,156-163
         auto u2 = [&](float v) {
             const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f;
             const float x = v + v;
             const float num = fmaf(x, fmaf(x, A, C * B), D * E), den = fmaf(x, fmaf(x, A, B), D * F);
             return mul_sat(fmaf(num, rcp(den), -(E / F)), k.white_scale);
         };
-        put(RTE_TM_UNCHARTED2, u2(cc.x), u2(cc.y), u2(cc.z));
+        return mk3(u2(s.cc.x), u2(s.cc.y), u2(s.cc.z));
     }
-    if (m & (1u << RTE_TM_ACES)) {  // :89-98
-        auto ac = [](float x) {
-            const float v = x * 0.6f;
-            return mul_sat(v * fmaf(v, 2.51f, 0.03f), rcp(fmaf(v, fmaf(v, 2.43f, 0.59f), 0.14f)));
-        };
-        put(RTE_TM_ACES, ac(cc.x), ac(cc.y), ac(cc.z));
-    }
+    auto ac = [](float x) {  // aces_approx, :89-98
+        const float v = x * 0.6f;
+        return mul_sat(v * fmaf(v, 2.51f, 0.03f), rcp(fmaf(v, fmaf(v, 2.43f, 0.59f), 0.14f)));
+    };
+    return mk3(ac(s.cc.x), ac(s.cc.y), ac(s.cc.z));
 }
 
 // 4 pixels x RGB (bytes in bits 0..7 of twelve words) -> three packed 32-bit words
