@@ -126,13 +126,21 @@ def visible_index(local_rank: int) -> int:
 
 
 # ------------------------------------------------------------------------------------------ reference arm
+def host_threads() -> int:
+    """All host cores this process may use — passed explicitly: torchrun exports OMP_NUM_THREADS=1 to its ranks."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_reference_sample(arrays, cam, target_s: float, threads: int = 0):
     """Times the CPU checker (the reference's own code when oracle/_ref was built) on every S-th row of the
     workload, S chosen so that one pass takes about `target_s`.  Returns (oracle, row_step, result dict)."""
     from oracle import pyoracle
     orc = pyoracle.load_best()
     probe_step = max(1, cam.height // 24)
-    r = orc.render(arrays, cam, row_step=probe_step, threads=threads)
+    r = orc.render(arrays, cam, row_step=probe_step, threads=threads or host_threads())
     per_row = r["render_seconds"] / max(1, r["rows"])
     rows = int(min(cam.height, max(8, target_s / max(per_row, 1e-9))))
     step = max(1, cam.height // rows)
@@ -148,7 +156,7 @@ def sample_ray_count(arrays, cam, row_step: int) -> int:
     if port is None:
         pyoracle.build("port")
         port = pyoracle.load_port()
-    r = port.render(arrays, cam, row_step=row_step)
+    r = port.render(arrays, cam, row_step=row_step, threads=host_threads())
     return int(r["primary_rays"] + r["shadow_rays"])
 
 
@@ -163,7 +171,7 @@ def run_reference(args) -> None:
     times, threads = [], 0
     rays = sample_ray_count(arrays, cam, row_step)
     for it in range(args.warmup + args.steps):
-        r = orc.render(arrays, cam, row_step=row_step)
+        r = orc.render(arrays, cam, row_step=row_step, threads=host_threads())
         t = r["render_seconds"]
         t0 = time.perf_counter()
         orc.tonemap_one(6, r["hdr"])  # tonemap() = ACES + toColor, RE/RaytracingEngine.cpp:165-174 (single-threaded upstream)
@@ -364,7 +372,7 @@ def run_gpu(args) -> None:
     }
     if not args.no_cpu_baseline and world == 1:
         orc, row_step = cpu_reference_sample(arrays, cam, args.cpu_seconds)
-        r = orc.render(arrays, cam, row_step=row_step)
+        r = orc.render(arrays, cam, row_step=row_step, threads=host_threads())
         crays = sample_ray_count(arrays, cam, row_step)
         line["cpu_baseline"] = {"value": round(crays / r["render_seconds"] / 1e6, 4), "unit": UNIT, "cores": r["threads_used"], "kind": orc.kind,
                                 "sample": f"every {row_step}th row ({r['rows']} of {H} rows, {crays} rays), RenderImage only, {r['render_seconds']:.2f} s"}

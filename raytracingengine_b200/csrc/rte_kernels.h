@@ -16,6 +16,8 @@ struct SmemPlan {
     uint32_t view_bytes, sph_bytes, tri_bytes;
     int32_t use_views;   // sphere phases of primary / shadow rays go through the per-origin views (rte_views.cuh)
     int32_t stage_sph;   // generic sph32 array is in shared memory (else read from global by the rare generic queries)
+    int32_t stream_views;  // views do not fit: view_bytes = 2 buffers of one view each, refilled by TMA while the other is scanned
+    uint32_t one_view_bytes;
     size_t total;
 };
 SmemPlan plan_smem(const DevScene& sc, size_t budget);

@@ -59,10 +59,17 @@ SmemPlan plan_smem(const DevScene& sc, size_t budget) {
     const size_t tri = (size_t)sc.nt_pad * 48, sph = (size_t)sc.ns_pad * 16;
     const size_t views = sc.ns > 0 ? (size_t)(1 + sc.nl) * view_bytes(sc.ns_pad) : 0;
     pl.tri_bytes = (uint32_t)tri;
+    pl.one_view_bytes = (uint32_t)view_bytes(sc.ns_pad);
     if (sc.views && tri + views <= budget) {
         pl.use_views = 1;
         pl.view_bytes = (uint32_t)views;
         pl.stage_sph = (sc.reflective && tri + views + sph <= budget) ? 1 : 0;
+    } else if (sc.views && !sc.reflective && sc.nt == 0 && 2 * (size_t)pl.one_view_bytes <= budget) {
+        // large diffuse sphere scenes (C5: 9 views of 64 KB): two view buffers, streamed (fast kernel only)
+        pl.use_views = 1;
+        pl.stream_views = 1;
+        pl.view_bytes = 2 * pl.one_view_bytes;
+        pl.stage_sph = 0;
     } else {
         pl.stage_sph = 1;
     }
@@ -71,6 +78,7 @@ SmemPlan plan_smem(const DevScene& sc, size_t budget) {
     return pl;
 }
 
+static SmemPlan generic_plan(const DevScene& sc);
 size_t scene_smem_bytes(const DevScene& sc) { return (size_t)sc.ns_pad * 16 + (size_t)sc.nt_pad * 48; }
 
 __device__ __forceinline__ void tma_chunks(unsigned char* dst, const void* src, uint32_t bytes, uint64_t* bar) {
@@ -87,8 +95,9 @@ __device__ __forceinline__ void stage_scene(const DevScene& sc, const SmemPlan& 
     if (threadIdx.x == 0) mbar_init(bar, 1);
     __syncthreads();
     if (threadIdx.x == 0) {
-        mbar_expect_tx(bar, pl.view_bytes + pl.sph_bytes + pl.tri_bytes);
-        tma_chunks(dyn, sc.views, pl.view_bytes, bar);
+        const uint32_t vb = pl.stream_views ? 0u : pl.view_bytes;  // streamed views are fetched by ViewStream
+        mbar_expect_tx(bar, vb + pl.sph_bytes + pl.tri_bytes);
+        tma_chunks(dyn, sc.views, vb, bar);
         tma_chunks(dyn + pl.view_bytes, sc.sph32, pl.sph_bytes, bar);
         tma_chunks(dyn + pl.view_bytes + pl.sph_bytes, sc.tri32, pl.tri_bytes, bar);
     }
@@ -222,8 +231,11 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
                     if (sr[k].cast) { T[k] = march_exact(sc, s_sph, s_tri, sr[k].o, sr[k].d, sr[k].maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
             } else {
                 OccResult r[K];
+                RayLists<K> lists;
+#pragma unroll
+                for (int k = 0; k < K; ++k) lists.n[k] = kListCap + 1;
                 if (uv) {
-                    occluded_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, s_tri, Lp, sr, bias, nf, r, cnt.confirms, cnt.sph_exec);
+                    occluded_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, s_tri, Lp, sr, bias, nf, r, lists, cnt.confirms, cnt.sph_exec);
                 } else {
 #pragma unroll
                     for (int k = 0; k < K; ++k)
@@ -233,7 +245,12 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
                 for (int k = 0; k < K; ++k) {
                     cnt.sph += r[k].sph_tests; cnt.pl += r[k].pl_tests; cnt.tri += r[k].tri_tests;
                     if (sr[k].cast) {
-                        if (r[k].near) { T[k] = march_exact(sc, s_sph, s_tri, sr[k].o, sr[k].d, sr[k].maxDist, bias, nf, cnt.confirms); cnt.marches += 1; }
+                        if (r[k].near) {
+                            // triangles (and transparent occluders) are outside march_list's scope
+                            if (lists.n[k] <= kListCap && sc.nt == 0 && !nf) T[k] = march_list(sc, lists.idx[k], lists.n[k], sr[k].o, sr[k].d, sr[k].maxDist, bias);
+                            else T[k] = march_exact(sc, s_sph, s_tri, sr[k].o, sr[k].d, sr[k].maxDist, bias, nf, cnt.confirms);
+                            cnt.marches += 1;
+                        }
                         else T[k] = r[k].occluded ? 0.0 : 1.0;
                     }
                 }
@@ -377,6 +394,53 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
     if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
 }
 
+// ------------------------------------------------------------------------------ view providers
+// Resident: all (1+nl) views sit in shared memory for the lifetime of the CTA.
+struct ViewsResident {
+    const ulonglong2* base;
+    int stride;  // ulonglong2 elements per view
+    __device__ __forceinline__ const ulonglong2* acquire(int v) const { return base + (size_t)v * stride; }
+    __device__ __forceinline__ void release() const {}
+    static constexpr bool kStream = false;
+};
+// Streamed: the views of a large scene (C5: 9 x 64 KB) pass through two shared-memory buffers.  Every warp of the CTA
+// walks the same cyclic view sequence 0,1,..,nl,0,1,.. (one tile batch per cycle); while the CTA scans the view in one
+// buffer, TMA bulk copies fill the other one with the next view of the sequence (mbarrier complete_tx), and
+// release() = __syncthreads() + refill of the buffer just left.  acquire()/release() are called by ALL threads.
+struct ViewsStream {
+    unsigned char* buf[2];
+    uint64_t* bar;  // two mbarriers
+    const unsigned char* gsrc;
+    uint32_t bytes;  // of one view
+    int nv;
+    uint32_t step;  // views consumed so far by this CTA
+    static constexpr bool kStream = true;
+    __device__ __forceinline__ void fill(uint32_t s) {  // one elected thread: view (s mod nv) -> buffer (s & 1)
+        uint64_t* b = bar + (s & 1u);
+        mbar_expect_tx(b, bytes);
+        tma_chunks(buf[s & 1u], gsrc + (size_t)(s % (uint32_t)nv) * bytes, bytes, b);
+    }
+    __device__ __forceinline__ void start() {
+        if (threadIdx.x == 0) { mbar_init(bar, 1); mbar_init(bar + 1, 1); }
+        __syncthreads();
+        if (threadIdx.x == 0) { fill(0); fill(1); }
+        step = 0;
+    }
+    __device__ __forceinline__ const ulonglong2* acquire(int) {
+        mbar_wait(bar + (step & 1u), (step >> 1) & 1u);
+        return reinterpret_cast<const ulonglong2*>(buf[step & 1u]);
+    }
+    __device__ __forceinline__ void release() {
+        __syncthreads();  // every warp has left the buffer
+        if (threadIdx.x == 0) fill(step + 2);
+        ++step;
+    }
+    __device__ __forceinline__ void drain() {  // two refills are always in flight: wait for them before the CTA exits
+        mbar_wait(bar + (step & 1u), (step >> 1) & 1u);
+        mbar_wait(bar + ((step + 1) & 1u), ((step + 1) >> 1) & 1u);
+    }
+};
+
 // ------------------------------------------------------------------------------ the fast kernel
 // Production path of diffuse sphere/plane scenes (C2/C3/C5 families): views resident in shared memory, no
 // material with specular > 0, no triangles, no validation switch, no AOV output.  Same arithmetic as
@@ -384,14 +448,13 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
 // instruction caches: everything that runs once per pixel sits in `#pragma unroll 1` loops over the K pixels of
 // the thread (one copy of the FP64 code, per-pixel state in local memory), only the two sphere scans are
 // unrolled over K.  The general kernel's per-pixel code is ~4x larger and stalls on instruction fetch.
-template <int K>
-__device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const float4* s_sph,
+template <int K, class Views>
+__device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const float4* s_sph,
                                                 const float4* s_tri, const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K],
                                                 PixelCounters& cnt, d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     const double bias = P.bias;
     const int nl = sc.nl, np = sc.np, ns = sc.ns;
-    const int view_stride = sc.ns_pad;
     d3 dir[K];
     bool alive[K], found[K];
     Hit h[K];
@@ -402,7 +465,11 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         found[k] = false;
         h[k].t = 0.0; h[k].kind = RTE_HIT_NONE; h[k].idx = 0;
     }
-    if (ns > 0) closest_spheres_view<K>(sc, s_views, cam_o, dir, alive, false, h, found, cnt.confirms);
+    {
+        const ulonglong2* v0 = views.acquire(0);
+        if (ns > 0) closest_spheres_view<K>(sc, v0, cam_o, dir, alive, false, h, found, cnt.confirms);
+        views.release();
+    }
 
     d3 Pn[K], normal[K], diffuse[K];
     int mat[K], self[K];
@@ -469,9 +536,16 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
             sr[k] = s;
             any_cast = any_cast || cast;
         }
-        if (!__any_sync(kFullMask, any_cast)) continue;
+        const bool scan = __any_sync(kFullMask, any_cast);
+        if (!Views::kStream && !scan) continue;
         OccState st[K];
-        occluded_spheres_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, Lp, sr, bias, false, st, cnt.confirms, cnt.sph_exec);
+        RayLists<K> lists;
+        {
+            const ulonglong2* vj = views.acquire(1 + j);  // streamed views: every warp of the CTA passes here, scanning or not
+            if (scan) occluded_spheres_view<K>(sc, vj, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec);
+            views.release();
+        }
+        if (!scan) continue;
         bool all_done = true;
 #pragma unroll
         for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;
@@ -480,7 +554,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         for (int k = 0; k < K; ++k) {
             OccState s = st[k];
             const ShadowRay r = sr[k];
-            if (!skip_planes && !s.done) {  // planes, any-hit in canonical order
+            if (!skip_planes && !s.done && !s.res.occluded) {  // planes, any-hit in canonical order (a `near` ray with an occluder: the march decides)
                 uint32_t firstp = (uint32_t)np;
 #pragma unroll 1
                 for (int i = 0; i < np; ++i) {
@@ -495,7 +569,12 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
             cnt.sph += s.res.sph_tests; cnt.pl += s.res.pl_tests;
             if (!r.cast) continue;
             double T;
-            if (s.res.near) { T = march_exact(sc, s_sph, s_tri, r.o, r.d, r.maxDist, bias, false, cnt.confirms); cnt.marches += 1; }
+            if (s.res.near) {
+                const int ln = lists.n[k];
+                if (ln <= kListCap) T = march_list(sc, lists.idx[k], ln, r.o, r.d, r.maxDist, bias);
+                else T = march_exact(sc, s_sph, s_tri, r.o, r.d, r.maxDist, bias, false, cnt.confirms);
+                cnt.marches += 1;
+            }
             else T = s.res.occluded ? 0.0 : 1.0;
             cnt.shadow += 1;
             if (T > bias) {
@@ -524,12 +603,14 @@ constexpr int kFastThreads = RTE_FAST_THREADS;  // block size of the fast kernel
 constexpr int kFastMinBlocks = RTE_FAST_MINB;
 
 // kBig = false: kFastThreads x kFastMinBlocks CTAs per SM; kBig = true: one 512-thread CTA per SM (views of large scenes)
-template <int K, bool kBig>
+// kStream = true (implies kBig): the views pass through two shared-memory buffers (ViewsStream), tile batches are CTA-uniform
+template <int K, bool kBig, bool kStream>
 __global__ void __launch_bounds__(kBig ? kRenderMaxThreads : kFastThreads, kBig ? 1 : kFastMinBlocks)
 render_fast_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ DevScene s_sc;
     __shared__ __align__(8) uint64_t s_bar;
+    __shared__ __align__(8) uint64_t s_vbar[2];
     __shared__ unsigned long long s_stats[kRenderMaxThreads / 32][kStatCount];
 
     if (threadIdx.x == 0) s_sc = P.sc;
@@ -539,6 +620,14 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     const ulonglong2* s_views;
     stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);
     const DevScene& sc = s_sc;
+    ViewsResident views_res{s_views, sc.ns_pad};
+    ViewsStream views_str;
+    if (kStream) {
+        views_str.buf[0] = dyn_smem; views_str.buf[1] = dyn_smem + P.plan.one_view_bytes;
+        views_str.bar = s_vbar; views_str.gsrc = reinterpret_cast<const unsigned char*>(P.sc.views);
+        views_str.bytes = P.plan.one_view_bytes; views_str.nv = 1 + P.sc.nl;
+        views_str.start();
+    }
 
     const int W = P.cam.width, rows = P.n_rows;
     const int sr = P.stripe_rows, sp = P.stripe_period;
@@ -550,9 +639,12 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     unsigned int tile = 0;
     if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
     tile = __shfl_sync(kFullMask, tile, 0);
-    while (tile < n_tiles) {
+    while (true) {
+        const bool have = tile < n_tiles;
+        if (kStream) { if (!__syncthreads_or(have ? 1 : 0)) break; }  // a batch = one tile per warp; idle warps still walk the views
+        else if (!have) break;
         unsigned int next = 0;
-        if (lane == 0) next = atomicAdd(P.tile_counter, 1u);
+        if (lane == 0) next = have ? atomicAdd(P.tile_counter, 1u) : tile;
         const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
         int px[K], py[K];
         bool inb[K];
@@ -562,12 +654,13 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             const int band_y = ty * TH + k * kTileH + ly;
             px[k] = tx * kTileW + lx;
             py[k] = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
-            inb[k] = px[k] < W && band_y < rows;
+            inb[k] = have && px[k] < W && band_y < rows;
             n_in += inb[k] ? 1u : 0u;
         }
         PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         d3 c[K];
-        trace_tile_fast<K>(P, sc, s_views, s_sph, s_tri, px, py, inb, cnt, c);
+        if (kStream) trace_tile_fast<K>(P, sc, views_str, s_sph, s_tri, px, py, inb, cnt, c);
+        else trace_tile_fast<K>(P, sc, views_res, s_sph, s_tri, px, py, inb, cnt, c);
 #pragma unroll 1
         for (int k = 0; k < K; ++k) {
             if (!inb[k]) continue;
@@ -590,6 +683,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         }
         tile = __shfl_sync(kFullMask, next, 0);
     }
+    if (kStream) views_str.drain();
     __syncwarp();
     if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
 }
@@ -637,10 +731,21 @@ bool fast_path_eligible(const RenderParams& p) {
            !f.depth64 && !f.normal && !f.albedo && !f.light_mask;
 }
 
-cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream) {
+cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t stream) {
+    RenderParams p = p0;
+    if (p.plan.stream_views && !(fast_path_eligible(p) && !p.force_general)) {
+        // only the fast kernel streams views: AOV / validation renders of a large scene use the generic filters
+        p.plan = generic_plan(p.sc);
+    }
     if (fast_path_eligible(p) && !p.force_general)
-        return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false>, (const void*)render_fast_kernel<kViewPixels, true>,
+    {
+        if (p.plan.stream_views) {
+            const void* fn = (const void*)render_fast_kernel<kViewPixels, true, true>;
+            return launch_render_fn(fn, fn, kRenderMaxThreads, 1, kViewPixels, p, sm_count, stream);
+        }
+        return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false>, (const void*)render_fast_kernel<kViewPixels, true, false>,
                                 kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream);
+    }
     const void* fn = p.sc.reflective ? (const void*)render_kernel<1, true> : (const void*)render_kernel<1, false>;
     return launch_render_fn(fn, fn, kRenderThreads, 2, 1, p, sm_count, stream);
 }

@@ -264,6 +264,16 @@ struct OccState {
             if (t <= t_safe) res.near = true;
         }
     }
+    // View scans: a ray that turned `near` keeps scanning (never `done`), so that its candidate list is complete and
+    // the exact march can run over that list instead of over every primitive (march_list, rte_views.cuh).
+    __device__ __forceinline__ void on_t_view(double t, uint32_t& firstv, uint32_t k) {
+        if (t <= bias) res.near = true;
+        else if (t < maxDist) {
+            if (!res.occluded) { res.occluded = true; firstv = k + 1u; }
+            if (t <= t_safe) res.near = true;
+            if (!res.near) done = true;
+        }
+    }
 };
 
 __device__ __forceinline__ OccState occ_begin(double maxDist, double bias, bool active) {

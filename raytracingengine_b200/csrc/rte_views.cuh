@@ -294,11 +294,55 @@ struct ShadowRay {
 //   * decided in FP32 when the interval arithmetic is conclusive: a certain occluder with t in (t_safe, maxDist),
 //     or certainly outside (behind the light / beyond the shaded point),
 //   * or confirmed in FP64 with the reference's own operation order.
+constexpr int kListCap = 24;  // in-range sphere candidates remembered per shadow ray (for march_list)
+template <int K>
+struct RayLists {
+    uint16_t idx[K][kListCap];
+    int n[K];          // > kListCap: overflow, the list is unusable
+};
+
+// Scene::computeTransmittance, RE/Scene.h:35-77, literally — but every closest-hit query of the march only looks at the
+// spheres of `list` (all spheres whose chord overlaps the ray's range: the march moves its origin along the same line, so
+// no other sphere can ever be hit) and at the planes.  Scenes of the fast path have no triangles and no transparency.
+__device__ __noinline__ double march_list(const DevScene& sc, const uint16_t* list, int n, d3 o, d3 d, double maxDist, double bias) {
+    double T = 1.0, traveled = 0.0;
+    int safety = 64;
+    while (safety-- > 0 && T > 1e-4 && traveled < maxDist) {
+        bool found = false;
+        double bt = 0.0;
+        int mat = sc.nm;
+#pragma unroll 1
+        for (int i = 0; i < n; ++i) {  // ascending sphere index, strict '<' (RE/Scene.h:218-257)
+            double t;
+            const int k = list[i];
+            if (sphere_exact(sc.sph64[k], o, d, t) && (!found || t < bt)) { found = true; bt = t; mat = sc.sph_mat[k]; }
+        }
+#pragma unroll 1
+        for (int i = 0; i < sc.np; ++i) {
+            double t;
+            if (plane_exact(sc.planes[i], o, d, t) && (!found || t < bt)) { found = true; bt = t; mat = sc.planes[i].mat; }
+        }
+        if (!found) break;
+        const double t = bt;
+        if (t <= 0.0) { o = o + d * bias; traveled += bias; continue; }
+        if (t <= bias) { o = (o + d * t) + d * bias; traveled += t + bias; continue; }
+        if (traveled + t >= maxDist) break;
+        const int m = (mat >= 0 && mat < sc.nm) ? mat : sc.nm;
+        T *= std_clamp(sc.materials[m].transparency, 0.0, 1.0);
+        const d3 newOrigin = (o + d * t) + d * bias;
+        traveled += t + bias;
+        o = newOrigin;
+    }
+    return std_clamp(T, 0.0, 1.0);
+}
+
 template <int K>
 __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, d3 Lp,
                                                       const ShadowRay (&ray)[K], double bias, bool no_filter, OccState (&st)[K],
-                                                      uint32_t& confirms, uint32_t& executed) {
+                                                      RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
     uint32_t first[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) lists.n[k] = 0;
     const int ns = sc.ns, ns_pad = sc.ns_pad;
 #pragma unroll
     for (int k = 0; k < K; ++k) { st[k] = occ_begin(ray[k].maxDist, bias, ray[k].cast); first[k] = (uint32_t)ns; }
@@ -360,6 +404,11 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
                     if (t1_hi < 0.0f || t0_lo > tmax_hi[k]) continue;  // certainly no hit in (1e-6, maxDist), none <= bias
                     certain = ch.hc_lo > 0.0f && t0_lo > tsafe_hi && t0_hi < tmax_lo[k];  // certainly t in (t_safe, maxDist)
                 }
+                {   // remember every in-range candidate of the ray (what an exact march over this ray could ever hit)
+                    const int ln = lists.n[k];
+                    if (ln < kListCap && idx < 65536) lists.idx[k][ln] = (uint16_t)idx;
+                    lists.n[k] = (ln < kListCap && idx < 65536) ? ln + 1 : kListCap + 1;
+                }
                 double t = 0.0;
                 bool hit = false;
                 if (!certain) {
@@ -369,8 +418,10 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
 #pragma unroll
                 for (int i = 0; i < K; ++i) {
                     if (i != k) continue;
-                    if (certain) { st[i].res.occluded = true; st[i].done = true; first[i] = (uint32_t)idx + 1u; }
-                    else if (hit) st[i].on_t(t, first[i], (uint32_t)idx);
+                    if (certain) {
+                        if (!st[i].res.occluded) { st[i].res.occluded = true; first[i] = (uint32_t)idx + 1u; }
+                        if (!st[i].res.near) st[i].done = true;
+                    } else if (hit) st[i].on_t_view(t, first[i], (uint32_t)idx);
                 }
             }
             qn = 0;
@@ -389,11 +440,12 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
 template <int K>
 __device__ __forceinline__ void occluded_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float4* __restrict__ s_tri,
                                               d3 Lp, const ShadowRay (&ray)[K], double bias, bool no_filter, OccResult (&out)[K],
-                                              uint32_t& confirms, uint32_t& executed) {
+                                              RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
     OccState st[K];
-    occluded_spheres_view<K>(sc, view, Lp, ray, bias, no_filter, st, confirms, executed);
+    occluded_spheres_view<K>(sc, view, Lp, ray, bias, no_filter, st, lists, confirms, executed);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
+        if (st[k].res.near && st[k].res.occluded) st[k].done = true;  // the march decides; planes/triangles are not counted after an occluder
         if (sc.np > 0 || sc.nt > 0) {
             if (!__all_sync(kFullMask, st[k].done)) {
                 const Ray32 r32 = make_ray32(sc, ray[k].o, ray[k].d, no_filter);

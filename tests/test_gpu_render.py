@@ -176,7 +176,7 @@ def test_errors(engine):
     assert engine.render_host(outputs=("prim_id",))["prim_id"].size == cam.width * cam.height
 
 
-@pytest.mark.parametrize("cfg", ["c2", "c3", "c2_band", "c2_odd"])
+@pytest.mark.parametrize("cfg", ["c2", "c3", "c2_band", "c2_odd", "c5_streamed", "c5_streamed_band", "big_resident"])
 def test_fast_kernel_is_bit_identical(engine, oracle, cfg):
     """Without AOV outputs diffuse sphere/plane scenes take the lean multi-pixel kernel (render_fast_kernel):
     same HDR bits, same fused RGB8, same algorithmic counters as the oracle and as the general kernel."""
@@ -188,6 +188,13 @@ def test_fast_kernel_is_bit_identical(engine, oracle, cfg):
     elif cfg == "c2_band":
         arrays, cam = scenes.config2(scale=0.1)
         opts = dict(row0=37, row1=150)
+    elif cfg == "c5_streamed":  # 9 views x 64 KB do not fit shared memory: streamed through two TMA-filled buffers
+        arrays, cam = scenes.config5(scale=1 / 32)
+    elif cfg == "c5_streamed_band":  # fewer tiles than warps in the last batch, odd band
+        arrays, cam = scenes.config5(scale=1 / 48)
+        opts = dict(row0=11, row1=64)
+    elif cfg == "big_resident":  # 2048 spheres x 5 views = 160 KB: resident, one 512-thread CTA per SM
+        arrays, cam = scenes.synthetic_room(240, 135, 120.0, 2048, 4, 4321)
     else:  # width / height not multiples of the 8 x 8 warp tile
         arrays, cam = scenes.synthetic_room(203, 117, 100.0, 300, 3, 77)
     engine.upload(arrays, cam)
