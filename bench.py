@@ -246,8 +246,21 @@ def run_gpu(args) -> None:
     rgb_all = torch.empty((world * rows_max * W * 3,), dtype=torch.uint8, device=dev) if world > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
+    auto_white = args.workload == "c5" and not args.fixed_white
+    white = torch.zeros(1, dtype=torch.float32, device=dev)
+    tm_ptrs = [rgb_local.data_ptr() if op == tm_op else None for op in range(_abi.TM_COUNT)]
+
     def render_step():
-        eng.render_device({"hdr": hdr.data_ptr(), "rgb8": rgb_local.data_ptr()}, tonemap_op=tm_op, **ropts)
+        if auto_white:
+            # C5's auto max-white pipeline: HDR stripes -> per-rank max luminance (device float) ->
+            # NCCL all-reduce MAX -> Reinhard-extended-luminance with that white point -> NCCL all-gather of RGB8
+            eng.render_device({"hdr": hdr.data_ptr()}, **ropts)
+            eng.max_luminance_device(hdr.data_ptr(), my_rows * W, white.data_ptr())
+            if dist is not None:
+                dist.all_reduce(white, op=dist.ReduceOp.MAX)
+            eng.tonemap_auto_white(hdr.data_ptr(), my_rows * W, tm_ptrs, white.data_ptr(), ops=[tm_op])
+        else:
+            eng.render_device({"hdr": hdr.data_ptr(), "rgb8": rgb_local.data_ptr()}, tonemap_op=tm_op, **ropts)
         if dist is not None:  # the RGB8 stripes of every rank, into the PPM writer's buffer (de-interleaved at write time)
             dist.all_gather_into_tensor(rgb_all, rgb_local)
 
@@ -349,6 +362,7 @@ def run_gpu(args) -> None:
         "dtype": "f32 filter + f64 confirm", "data": "synthetic",
         "config": {"workload": label, "width": W, "height": H, **arrays.counts(), "seed": 1234 if args.workload != "c5" else 5678,
                    "rays_per_frame": int(rays), "sharding": "single band" if world == 1 else f"interleaved {args.stripe}-row stripes + NCCL all-gather of RGB8",
+                   "tonemap": ("auto max-white: max-luminance kernel + " + ("NCCL all-reduce MAX + " if world > 1 else "") + "tonemap pass") if auto_white else "fused into the render kernel",
                    "l2": "256 MiB memset between timed steps; outputs (HDR float4 + RGB8 = 19 B/px) exceed L2",
                    "timing": "CUDA events per step on the launching stream, summed, max over ranks"},
         "ms_per_frame": round(ms_per_step, 4),
@@ -356,7 +370,8 @@ def run_gpu(args) -> None:
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "ms_per_step": round(e2e_ms, 3), "h2d_bytes_per_step": int(scene_bytes),
                 "d2h_bytes_per_step": int(my_rows * W * 3), "api": "rte_upload_scene + rte_render_host (pinned host RGB8)"},
-        "gpu_launches": args.steps,  # one rte::render_kernel launch per step and rank (the flush memset and NCCL are not ours)
+        # per step and rank: one render kernel (+ max-luminance and tonemap kernels in the auto-white pipeline); memsets and NCCL are not ours
+        "gpu_launches": args.steps * (3 if auto_white else 1),
         "roofline": {"bound": "fp32", "kernel": "rte::render_kernel", "achieved": round(achieved_tf, 3), "peak": round(fp32_peak_tf, 3),
                      "unit": "TFLOP/s", "frac": round(achieved_tf / fp32_peak_tf, 4), "traffic": None,
                      "peak_source": "FFMA micro-benchmark in this process (rte_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
@@ -392,6 +407,7 @@ def main() -> None:
     ap.add_argument("--stripe", type=int, default=8, help="rows per interleaved stripe at N>1")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU sample size per pass of the reference leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--fixed-white", action="store_true", help="c5: the reference's constant max_white = 5.0 (fused tonemap) instead of the auto max-white pipeline")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -247,6 +247,12 @@ int rte_tonemap_host(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t 
 /* Max of luminance() (RE/RaytracingEngine.cpp:100-104) over a device HDR buffer; the per-rank
  * value that an auto-max-white run all-reduces (MAX) across GPUs. Result on the host. */
 int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max);
+/* Stream-ordered variants for the multi-GPU auto-max-white pipeline: the per-rank max goes to a
+ * device float (no host round trip), the caller all-reduces it (MAX) across ranks on the same stream, and the
+ * tonemap pass reads max_white from that device float.  *max_white_dev <= 0 falls back to the reference's 5.0. */
+int rte_max_luminance_device(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max_dev);
+int rte_tonemap_auto_white(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t op_mask,
+                           const float* max_white_dev, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]);
 
 /* Measurement aid (no reference counterpart): runs a register-resident FFMA kernel on every SM of the
  * ctx device for about `target_ms` and reports the achieved FP32 rate — the measured FP32-FMA roofline

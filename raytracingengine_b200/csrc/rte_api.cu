@@ -527,9 +527,10 @@ static int check_tonemap_args(rte_ctx* ctx, const float* hdr, int64_t n, uint32_
     return RTE_OK;
 }
 
-static int do_tonemap(rte_ctx* ctx, const float* hdr, int64_t n, uint32_t mask, double max_white, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]) {
+static int do_tonemap(rte_ctx* ctx, const float* hdr, int64_t n, uint32_t mask, double max_white, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT],
+                      const float* max_white_dev = nullptr) {
     TonemapParams p{};
-    p.hdr = (const float4*)hdr; p.n_pixels = n; p.op_mask = mask;
+    p.hdr = (const float4*)hdr; p.n_pixels = n; p.op_mask = mask; p.max_white_dev = max_white_dev;
     p.max_white = (float)(max_white > 0 ? max_white : 5.0);
     p.jodie_a = (float)(jodie_a > 0 ? jodie_a : 0.18);
     if (((uintptr_t)hdr & 15u) != 0) return fail(ctx, RTE_ERR_INVALID, "hdr must be 16-byte aligned");
@@ -550,6 +551,15 @@ extern "C" int rte_tonemap(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uin
     int rc = check_tonemap_args(ctx, hdr, n_pixels, op_mask, rgb8);
     if (rc) return rc;
     return do_tonemap(ctx, hdr, n_pixels, op_mask, max_white, jodie_a, rgb8);
+}
+
+extern "C" int rte_tonemap_auto_white(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t op_mask, const float* max_white_dev, double jodie_a,
+                                      uint8_t* const rgb8[RTE_TM_COUNT]) {
+    RTE_ENTER(ctx);
+    if (!max_white_dev) return fail(ctx, RTE_ERR_INVALID, "rte_tonemap_auto_white: max_white_dev is NULL");
+    int rc = check_tonemap_args(ctx, hdr, n_pixels, op_mask, rgb8);
+    if (rc) return rc;
+    return do_tonemap(ctx, hdr, n_pixels, op_mask, 5.0, jodie_a, rgb8, max_white_dev);
 }
 
 extern "C" int rte_tonemap_host(rte_ctx* ctx, const float* hdr, int64_t n, uint32_t mask, double max_white, double jodie_a,
@@ -581,6 +591,14 @@ extern "C" int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixel
     RTE_CUDA(ctx, cudaMemcpyAsync(h, ctx->d_maxlum, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
     RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     std::memcpy(out_max, h, sizeof(float));
+    return RTE_OK;
+}
+
+extern "C" int rte_max_luminance_device(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max_dev) {
+    RTE_ENTER(ctx);
+    if (!out_max_dev || (n_pixels > 0 && !hdr) || n_pixels < 0) return fail(ctx, RTE_ERR_INVALID, "rte_max_luminance_device: bad arguments");
+    if (((uintptr_t)out_max_dev & 3u) != 0) return fail(ctx, RTE_ERR_INVALID, "rte_max_luminance_device: out_max_dev must be 4-byte aligned");
+    RTE_CUDA(ctx, launch_max_luminance((const float4*)hdr, n_pixels, (unsigned int*)out_max_dev, ctx->sm_count, ctx->stream));
     return RTE_OK;
 }
 

@@ -60,6 +60,7 @@ struct TonemapParams {
     uint32_t op_mask;
     float max_white, jodie_a;
     uint8_t* rgb8[RTE_TM_COUNT];
+    const float* max_white_dev;  // non-NULL: max_white is read from device memory (auto max-white after the all-reduce)
 };
 cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t stream);
 // max luminance (RE/RaytracingEngine.cpp:100-104) into *out (device float, bit pattern max as uint)

@@ -408,7 +408,7 @@ struct ViewsResident {
 // buffer, TMA bulk copies fill the other one with the next view of the sequence (mbarrier complete_tx), and
 // release() = __syncthreads() + refill of the buffer just left.  acquire()/release() are called by ALL threads.
 struct ViewsStream {
-    unsigned char* buf[2];
+    unsigned char* base;  // buffer b = base + b * bytes (computed, not looked up: the scans must compile to LDS, not generic LD)
     uint64_t* bar;  // two mbarriers
     const unsigned char* gsrc;
     uint32_t bytes;  // of one view
@@ -418,7 +418,7 @@ struct ViewsStream {
     __device__ __forceinline__ void fill(uint32_t s) {  // one elected thread: view (s mod nv) -> buffer (s & 1)
         uint64_t* b = bar + (s & 1u);
         mbar_expect_tx(b, bytes);
-        tma_chunks(buf[s & 1u], gsrc + (size_t)(s % (uint32_t)nv) * bytes, bytes, b);
+        tma_chunks(base + (s & 1u) * bytes, gsrc + (size_t)(s % (uint32_t)nv) * bytes, bytes, b);
     }
     __device__ __forceinline__ void start() {
         if (threadIdx.x == 0) { mbar_init(bar, 1); mbar_init(bar + 1, 1); }
@@ -428,7 +428,7 @@ struct ViewsStream {
     }
     __device__ __forceinline__ const ulonglong2* acquire(int) {
         mbar_wait(bar + (step & 1u), (step >> 1) & 1u);
-        return reinterpret_cast<const ulonglong2*>(buf[step & 1u]);
+        return reinterpret_cast<const ulonglong2*>(base + (step & 1u) * bytes);
     }
     __device__ __forceinline__ void release() {
         __syncthreads();  // every warp has left the buffer
@@ -623,7 +623,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     ViewsResident views_res{s_views, sc.ns_pad};
     ViewsStream views_str;
     if (kStream) {
-        views_str.buf[0] = dyn_smem; views_str.buf[1] = dyn_smem + P.plan.one_view_bytes;
+        views_str.base = dyn_smem;
         views_str.bar = s_vbar; views_str.gsrc = reinterpret_cast<const unsigned char*>(P.sc.views);
         views_str.bytes = P.plan.one_view_bytes; views_str.nv = 1 + P.sc.nl;
         views_str.start();

@@ -38,7 +38,12 @@ __device__ __forceinline__ void store_op_tail(const tm32::Shared& s, const tm32:
 }
 
 template <uint32_t kMask>
-__global__ void __launch_bounds__(kTmThreads, 4) tonemap_kernel(const __grid_constant__ TonemapParams P, const tm32::Consts K) {
+__global__ void __launch_bounds__(kTmThreads, 4) tonemap_kernel(const __grid_constant__ TonemapParams P, const tm32::Consts K0) {
+    tm32::Consts K = K0;
+    if (P.max_white_dev) {  // auto max-white: the (all-reduced) max luminance of the frame, produced on this stream
+        const float w = __ldg(P.max_white_dev);
+        K.inv_wsq = w > 0.0f ? 1.0f / (w * w) : K0.inv_wsq;
+    }
     const int64_t n_quads = P.n_pixels >> 2;
     const uint32_t mask = kMask ? kMask : P.op_mask;
 #define RTE_TM_EACH(X) X(0) X(1) X(2) X(3) X(4) X(5) X(6)

@@ -94,3 +94,30 @@ def test_max_luminance(engine):
     lum = hdr[:, 0].astype(np.float64) * 0.2126 + hdr[:, 1] * 0.7152 + hdr[:, 2] * 0.0722
     assert abs(got - np.nanmax(lum)) <= 1e-5 * np.nanmax(lum)
     assert engine.max_luminance(dev, 0) == 0.0
+
+
+def test_auto_white_device_path(engine, port_oracle):
+    """rte_max_luminance_device + rte_tonemap_auto_white (the stream-ordered auto max-white pair of the multi-GPU
+    pipeline) = rte_tonemap with the same max_white passed from the host."""
+    rng = np.random.default_rng(11)
+    hdr = f4(np.exp(rng.normal(0.0, 1.5, (40001, 3))))
+    n = len(hdr)
+    dev = engine.malloc(hdr.nbytes)
+    white = engine.malloc(4)
+    outs = [engine.malloc(3 * n + 16) for _ in range(2)]
+    engine.h2d(dev, hdr)
+    engine.max_luminance_device(dev, n, white)
+    w = np.zeros(1, np.float32)
+    engine.d2h(w, white)
+    assert w[0] == np.float32(engine.max_luminance(dev, n))
+    for op in (2, 3):
+        ptrs = [None] * _abi.TM_COUNT
+        ptrs[op] = outs[0]
+        engine.tonemap_auto_white(dev, n, ptrs, white, ops=[op])
+        ptrs[op] = outs[1]
+        engine.tonemap_device(dev, n, ptrs, ops=[op], max_white=float(w[0]))
+        a, b = np.zeros((n, 3), np.uint8), np.zeros((n, 3), np.uint8)
+        engine.d2h(a, outs[0]); engine.d2h(b, outs[1])
+        assert np.array_equal(a, b)
+        want = port_oracle.tonemap_one(op, hdr[:, :3].astype(np.float64), max_white=float(w[0]), jodie_a=0.18)
+        assert np.abs(a.astype(np.int16) - want.astype(np.int16)).max() <= 1
