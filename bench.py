@@ -247,6 +247,38 @@ def run_gpu(args) -> None:
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     auto_white = args.workload == "c5" and not args.fixed_white
+
+    # ---- N>1 output path.  "peer" (default): every rank's render kernel stores its RGB8 stripes straight into the
+    # full-frame buffer of EVERY rank over NVLink (rte_set_rgb8_peers; buffers exchanged as CUDA IPC handles), and a
+    # 4-byte NCCL all-reduce fences the frame.  "nccl": the stripes are all-gathered by NCCL after the kernel.
+    gather = "none" if dist is None else ("nccl" if auto_white else args.gather)
+    peer_note = ""
+    frame_all = 0
+    opened = []
+    if gather == "peer":
+        try:
+            frame_all = eng.malloc(W * H * 3)
+            mine = torch.frombuffer(bytearray(eng.ipc_export(frame_all)), dtype=torch.uint8).to(dev)
+            handles = torch.empty(world * _abi.IPC_HANDLE_BYTES, dtype=torch.uint8, device=dev)
+            dist.all_gather_into_tensor(handles, mine)
+            handles = handles.cpu().numpy().reshape(world, _abi.IPC_HANDLE_BYTES)
+            frames = []
+            for r in range(world):
+                if r == rank:
+                    frames.append(frame_all)
+                else:
+                    opened.append(eng.ipc_open(handles[r].tobytes()))
+                    frames.append(opened[-1])
+            eng.set_rgb8_peers(frames)
+            ok = torch.ones(1, device=dev)
+        except Exception as exc:  # no peer mapping on this box: say so and use the NCCL all-gather
+            peer_note = f" (peer frames unavailable: {exc})"
+            ok = torch.zeros(1, device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if ok.item() < 1:
+            eng.set_rgb8_peers([])
+            gather = "nccl"
+    fence = torch.zeros(1, dtype=torch.float32, device=dev)
     white = torch.zeros(1, dtype=torch.float32, device=dev)
     tm_ptrs = [rgb_local.data_ptr() if op == tm_op else None for op in range(_abi.TM_COUNT)]
 
@@ -259,10 +291,29 @@ def run_gpu(args) -> None:
             if dist is not None:
                 dist.all_reduce(white, op=dist.ReduceOp.MAX)
             eng.tonemap_auto_white(hdr.data_ptr(), my_rows * W, tm_ptrs, white.data_ptr(), ops=[tm_op])
+        elif gather == "peer":
+            eng.render_device({"hdr": hdr.data_ptr()}, tonemap_op=tm_op, **ropts)  # RGB8 goes to every rank's frame
+            dist.all_reduce(fence)                                                 # frame fence across ranks
+            return
         else:
             eng.render_device({"hdr": hdr.data_ptr(), "rgb8": rgb_local.data_ptr()}, tonemap_op=tm_op, **ropts)
         if dist is not None:  # the RGB8 stripes of every rank, into the PPM writer's buffer (de-interleaved at write time)
             dist.all_gather_into_tensor(rgb_all, rgb_local)
+
+    if gather == "peer":
+        # one untimed check: the frame the peer stores assemble == the frame NCCL's all-gather assembles
+        from raytracingengine_b200 import sharding
+        render_step()
+        torch.cuda.synchronize()
+        eng.render_device({"hdr": hdr.data_ptr(), "rgb8": rgb_local.data_ptr()}, tonemap_op=tm_op, **ropts)
+        dist.all_gather_into_tensor(rgb_all, rgb_local)
+        torch.cuda.synchronize()
+        if rank == 0:
+            got = np.zeros((H * W, 3), np.uint8)
+            eng.d2h(got, frame_all)
+            want = sharding.deinterleave(rgb_all.cpu().numpy().reshape(-1, 3), world, H, W, args.stripe, rows_max)
+            if not np.array_equal(got, want):
+                raise SystemExit("bench.py: peer-stored frame differs from the NCCL all-gather of the same stripes")
 
     def sync_all():
         torch.cuda.synchronize()
@@ -316,6 +367,10 @@ def run_gpu(args) -> None:
     scene_bytes = sum(a.nbytes for a in (arrays.materials, arrays.spheres, arrays.planes, arrays.triangles, arrays.models,
                                          arrays.model_vertices, arrays.model_indices, arrays.lights))
 
+    if opened or frame_all:
+        sync_all()
+        eng.set_rgb8_peers([])  # the end-to-end leg returns each rank's stripes to its own host buffer
+
     def e2e_step():
         eng.upload(arrays, cam)
         eng.render_host(outputs=("rgb8",), into={"rgb8": host_rgb}, tonemap_op=tm_op, **ropts)
@@ -345,6 +400,12 @@ def run_gpu(args) -> None:
             tm_ms.append(eng.stats()["tonemap_ms"])
     tm_med = sorted(tm_ms)[len(tm_ms) // 2]
 
+    if opened:
+        sync_all()
+        eng.set_rgb8_peers([])
+        for p in opened:
+            eng.ipc_close(p)
+        sync_all()
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -361,7 +422,9 @@ def run_gpu(args) -> None:
         "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32 filter + f64 confirm", "data": "synthetic",
         "config": {"workload": label, "width": W, "height": H, **arrays.counts(), "seed": 1234 if args.workload != "c5" else 5678,
-                   "rays_per_frame": int(rays), "sharding": "single band" if world == 1 else f"interleaved {args.stripe}-row stripes + NCCL all-gather of RGB8",
+                   "rays_per_frame": int(rays), "sharding": "single band" if world == 1 else f"interleaved {args.stripe}-row stripes; " + (
+                       "RGB8 stored by the render kernel into every rank's frame over NVLink (CUDA IPC peer frames) + 4-byte NCCL all-reduce as frame fence"
+                       if gather == "peer" else "NCCL all-gather of RGB8" + peer_note),
                    "tonemap": ("auto max-white: max-luminance kernel + " + ("NCCL all-reduce MAX + " if world > 1 else "") + "tonemap pass") if auto_white else "fused into the render kernel",
                    "l2": "256 MiB memset between timed steps; outputs (HDR float4 + RGB8 = 19 B/px) exceed L2",
                    "timing": "CUDA events per step on the launching stream, summed, max over ranks"},
@@ -406,6 +469,7 @@ def main() -> None:
     ap.add_argument("--scale", type=float, default=1.0, help="developer switch: shrink the image (not the named config)")
     ap.add_argument("--stripe", type=int, default=8, help="rows per interleaved stripe at N>1")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU sample size per pass of the reference leg")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N>1: how the RGB8 stripes reach every rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fixed-white", action="store_true", help="c5: the reference's constant max_white = 5.0 (fused tonemap) instead of the auto max-white pipeline")
     args = ap.parse_args()

@@ -271,6 +271,21 @@ int rte_intersect_any_before(rte_ctx* ctx, int64_t n_rays, const double* origins
                              const double* directions, const double* max_dist, uint8_t* out);
 
 /* Device memory helpers for callers without their own allocator. */
+/* Multi-GPU output without a separate all-gather (no reference counterpart — the reference is one
+ * process writing one std::vector): every rank registers the full-frame RGB8 buffers (W*H*3 bytes, 4-byte aligned)
+ * of all ranks of the NVSwitch domain, its own included; each render with opts.tonemap_op != RTE_TM_NONE then stores
+ * the RGB8 of every pixel it renders at 3*(y*W + x) of EVERY registered frame (peer stores over NVLink, issued by the
+ * render kernel while it computes), on top of frame.rgb8 (which may be NULL).  The caller fences the frame with
+ * any cross-rank barrier on the same stream.  n_frames = 0 unregisters.  At most RTE_MAX_PEERS frames. */
+#define RTE_MAX_PEERS 8
+int rte_set_rgb8_peers(rte_ctx* ctx, int n_frames, uint8_t* const* frames);
+/* CUDA IPC plumbing for the above when ranks are processes: export a buffer obtained from rte_malloc as an opaque
+ * 64-byte handle, map a peer's handle into this process (enables peer access), unmap it. */
+#define RTE_IPC_HANDLE_BYTES 64
+int rte_ipc_export(rte_ctx* ctx, const void* dev, uint8_t handle[RTE_IPC_HANDLE_BYTES]);
+int rte_ipc_open(rte_ctx* ctx, const uint8_t handle[RTE_IPC_HANDLE_BYTES], void** out_dev);
+int rte_ipc_close(rte_ctx* ctx, void* dev);
+
 int rte_malloc(rte_ctx* ctx, size_t bytes, void** out_dev);
 int rte_free(rte_ctx* ctx, void* dev);
 int rte_memcpy_d2h(rte_ctx* ctx, void* host, const void* dev, size_t bytes);

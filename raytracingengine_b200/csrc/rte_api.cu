@@ -48,6 +48,10 @@ struct rte_ctx {
     bool views_dirty = true;
     double views_bias = -1.0;
 
+    // rte_set_rgb8_peers
+    uint8_t* peer_rgb8[kMaxPeers] = {};
+    int n_peers = 0;
+
     // launch scratch
     unsigned int* d_tile_counter = nullptr;
     unsigned long long* d_stats = nullptr;
@@ -444,6 +448,9 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
     p.out = *frame;
     p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
     if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
+    p.n_peers = p.tonemap_op == RTE_TM_NONE ? 0 : ctx->n_peers;
+    p.rgb8_words = ((uintptr_t)p.out.rgb8 & 3u) == 0 ? 1 : 0;
+    for (int i = 0; i < p.n_peers; ++i) p.peer_rgb8[i] = ctx->peer_rgb8[i];
     RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));
     RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * kStatCount, ctx->stream));
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
@@ -679,6 +686,48 @@ extern "C" int rte_intersect_any_before(rte_ctx* ctx, int64_t n, const double* o
 }
 
 // ====================================================================================== memory helpers
+// ====================================================================================== peer frames
+extern "C" int rte_set_rgb8_peers(rte_ctx* ctx, int n_frames, uint8_t* const* frames) {
+    RTE_ENTER(ctx);
+    if (n_frames < 0 || n_frames > kMaxPeers) return fail(ctx, RTE_ERR_LIMIT, "rte_set_rgb8_peers: %d frames (at most %d)", n_frames, kMaxPeers);
+    if (n_frames > 0 && !frames) return fail(ctx, RTE_ERR_INVALID, "rte_set_rgb8_peers: frames is NULL");
+    for (int i = 0; i < n_frames; ++i)
+        if (!frames[i] || ((uintptr_t)frames[i] & 3u) != 0) return fail(ctx, RTE_ERR_INVALID, "rte_set_rgb8_peers: frame %d is NULL or not 4-byte aligned", i);
+    for (int i = 0; i < n_frames; ++i) ctx->peer_rgb8[i] = frames[i];
+    ctx->n_peers = n_frames;
+    return RTE_OK;
+}
+
+static_assert(sizeof(cudaIpcMemHandle_t) == RTE_IPC_HANDLE_BYTES, "rte.h: RTE_IPC_HANDLE_BYTES");
+extern "C" int rte_ipc_export(rte_ctx* ctx, const void* dev, uint8_t handle[RTE_IPC_HANDLE_BYTES]) {
+    RTE_ENTER(ctx);
+    if (!dev || !handle) return fail(ctx, RTE_ERR_INVALID, "rte_ipc_export: NULL argument");
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, const_cast<void*>(dev));
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, RTE_ERR_CUDA, "cudaIpcGetMemHandle: %s (the pointer must come from rte_malloc)", cudaGetErrorString(e)); }
+    std::memcpy(handle, &h, sizeof(h));
+    return RTE_OK;
+}
+extern "C" int rte_ipc_open(rte_ctx* ctx, const uint8_t handle[RTE_IPC_HANDLE_BYTES], void** out_dev) {
+    RTE_ENTER(ctx);
+    if (!handle || !out_dev) return fail(ctx, RTE_ERR_INVALID, "rte_ipc_open: NULL argument");
+    *out_dev = nullptr;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof(h));
+    cudaError_t e = cudaIpcOpenMemHandle(out_dev, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, RTE_ERR_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e)); }
+    return RTE_OK;
+}
+extern "C" int rte_ipc_close(rte_ctx* ctx, void* dev) {
+    RTE_ENTER(ctx);
+    if (!dev) return RTE_OK;
+    for (int i = 0; i < ctx->n_peers; ++i)
+        if (ctx->peer_rgb8[i] == dev) return fail(ctx, RTE_ERR_INVALID, "rte_ipc_close: the mapping is still registered with rte_set_rgb8_peers");
+    cudaError_t e = cudaIpcCloseMemHandle(dev);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, RTE_ERR_CUDA, "cudaIpcCloseMemHandle: %s", cudaGetErrorString(e)); }
+    return RTE_OK;
+}
+
 extern "C" int rte_malloc(rte_ctx* ctx, size_t bytes, void** out_dev) {
     RTE_ENTER(ctx);
     if (!out_dev) return fail(ctx, RTE_ERR_INVALID, "rte_malloc: out is NULL");

@@ -22,6 +22,8 @@ struct SmemPlan {
 };
 SmemPlan plan_smem(const DevScene& sc, size_t budget);
 
+constexpr int kMaxPeers = 8;  // GPUs of one NVSwitch domain whose frame buffers a render can store into
+
 struct RenderParams {
     DevScene sc;
     SmemPlan plan;
@@ -36,6 +38,11 @@ struct RenderParams {
     int32_t force_general;   // RTE_FLAG_GENERAL_KERNEL: never take the lean fast kernel (validation)
     double bias, max_white, jodie_a;
     rte_frame out;           // device pointers, any may be NULL
+    // rte_set_rgb8_peers: full-frame RGB8 buffers (this GPU's and its peers', mapped over NVLink) that receive every
+    // rendered pixel at 3*(y*W + x), y = image row: the all-gather of the row stripes, fused into the render kernel
+    uint8_t* peer_rgb8[kMaxPeers];
+    int32_t n_peers;
+    int32_t rgb8_words;      // out.rgb8 and every peer frame are 4-byte aligned: full tile rows leave as 32-bit words
     unsigned int* tile_counter;        // zeroed before launch
     unsigned long long* stats;         // kStatCount counters, zeroed before launch
 };

@@ -23,7 +23,7 @@ SYMBOLS = (
     "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats",
     "rte_tonemap", "rte_tonemap_host", "rte_tonemap_auto_white", "rte_max_luminance", "rte_max_luminance_device", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
     "rte_malloc", "rte_free", "rte_memcpy_d2h", "rte_memcpy_h2d", "rte_malloc_host", "rte_free_host",
-    "rte_write_ppm",
+    "rte_write_ppm", "rte_set_rgb8_peers", "rte_ipc_export", "rte_ipc_open", "rte_ipc_close",
 )
 
 _lib = None
@@ -69,6 +69,10 @@ def load_library() -> C.CDLL:
     lib.rte_intersect_closest.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rte_intersect_any_before.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rte_malloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+    lib.rte_set_rgb8_peers.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+    lib.rte_ipc_export.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p]
+    lib.rte_ipc_open.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.rte_ipc_close.argtypes = [C.c_void_p, C.c_void_p]
     lib.rte_free.argtypes = [C.c_void_p, C.c_void_p]
     lib.rte_memcpy_d2h.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
     lib.rte_memcpy_h2d.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
@@ -188,6 +192,24 @@ class Engine:
         self._ck(self.lib.rte_malloc(self.ctx, nbytes, C.byref(p)))
         self._dev_allocs.append(p)
         return p.value
+
+    # ---- peer frames (multi-GPU output fused into the render kernel)
+    def set_rgb8_peers(self, frames: Sequence[int]) -> None:
+        arr = (C.c_void_p * max(1, len(frames)))(*[C.c_void_p(p) for p in frames])
+        self._ck(self.lib.rte_set_rgb8_peers(self.ctx, len(frames), arr))
+
+    def ipc_export(self, dev: int) -> bytes:
+        buf = C.create_string_buffer(_abi.IPC_HANDLE_BYTES)
+        self._ck(self.lib.rte_ipc_export(self.ctx, C.c_void_p(dev), buf))
+        return buf.raw
+
+    def ipc_open(self, handle: bytes) -> int:
+        p = C.c_void_p()
+        self._ck(self.lib.rte_ipc_open(self.ctx, C.c_char_p(bytes(handle)), C.byref(p)))
+        return p.value
+
+    def ipc_close(self, dev: int) -> None:
+        self._ck(self.lib.rte_ipc_close(self.ctx, C.c_void_p(dev)))
 
     def d2h(self, host: np.ndarray, dev: int, nbytes: Optional[int] = None) -> None:
         self._ck(self.lib.rte_memcpy_d2h(self.ctx, C.c_void_p(host.ctypes.data), C.c_void_p(dev), host.nbytes if nbytes is None else nbytes))

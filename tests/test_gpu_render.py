@@ -226,6 +226,72 @@ def test_fast_kernel_stripes(engine):
         assert np.array_equal(part.reshape(len(rows), cam.width, 3), full[rows])
 
 
+@pytest.mark.parametrize("cfg", ["c2_fast", "c2_general", "c2_odd_width", "c4_general"])
+def test_rgb8_peer_frames_equal_the_band_output(engine, cfg):
+    """rte_set_rgb8_peers: every rank's stripes, stored by the render kernel straight into the registered full frames
+    (here two buffers of the same GPU stand in for the peers), assemble the frame a single full render produces."""
+    from raytracingengine_b200 import sharding
+    if cfg == "c4_general":
+        arrays, cam = scenes.config4("box", scale=0.1)
+    else:
+        arrays, cam = scenes.config2(scale=0.1)
+    if cfg == "c2_odd_width":  # width not a multiple of 4: rows are not word aligned, tiles overhang the right edge
+        arrays, cam = scenes.synthetic_room(203, 117, 100.0, 300, 3, 77)
+    flags = _abi.FLAG_GENERAL_KERNEL if cfg == "c2_general" else 0
+    engine.upload(arrays, cam)
+    n = cam.width * cam.height
+    full = engine.render_host(outputs=("rgb8",), tonemap_op=_abi.TM_ACES, flags=flags)["rgb8"]
+    frames = [engine.malloc(3 * n + 16) for _ in range(2)]
+    band = engine.malloc(3 * n + 16)
+    engine.h2d(frames[0], np.full(3 * n, 0xAB, np.uint8))
+    engine.h2d(frames[1], np.full(3 * n, 0xCD, np.uint8))
+    engine.set_rgb8_peers(frames)
+    try:
+        world, S = 3, 8
+        for r in range(world):
+            o = sharding.stripe_opts(r, world, cam.height, S)
+            out = {"rgb8": band} if r == 1 else {}  # with and without the local band buffer
+            if r != 1:
+                out = {"hdr": engine.malloc(16 * n)}
+            engine.render_device(out, tonemap_op=_abi.TM_ACES, flags=flags, **o)
+            if r == 1:
+                rows = sharding.stripe_row_list(r, world, cam.height, S)
+                b = np.zeros((len(rows) * cam.width, 3), np.uint8)
+                engine.d2h(b, band)
+                assert np.array_equal(b.reshape(len(rows), cam.width, 3), full.reshape(cam.height, cam.width, 3)[rows])
+        for f in frames:
+            got = np.zeros((n, 3), np.uint8)
+            engine.d2h(got, f)
+            assert np.array_equal(got, full), f"{np.count_nonzero((got != full).any(axis=1))} pixels differ"
+    finally:
+        engine.set_rgb8_peers([])
+
+
+def test_ipc_export_open_roundtrip(engine):
+    """rte_ipc_export / rte_ipc_open / rte_ipc_close: a second process maps this process' buffer and stores into it."""
+    import os, subprocess, sys, textwrap
+    n = 1 << 16
+    dev = engine.malloc(n)
+    engine.h2d(dev, np.zeros(n, np.uint8))
+    handle = engine.ipc_export(dev)
+    assert len(handle) == _abi.IPC_HANDLE_BYTES
+    child = textwrap.dedent(f"""
+        import sys, numpy as np
+        sys.path.insert(0, {os.path.dirname(os.path.dirname(os.path.abspath(__file__)))!r})
+        from raytracingengine_b200.engine import Engine
+        with Engine(0) as e:
+            p = e.ipc_open(bytes.fromhex({handle.hex()!r}))
+            e.h2d(p, (np.arange({n}) % 251).astype(np.uint8))
+            e.synchronize()
+            e.ipc_close(p)
+    """)
+    r = subprocess.run([sys.executable, "-c", child], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    got = np.zeros(n, np.uint8)
+    engine.d2h(got, dev)
+    assert np.array_equal(got, (np.arange(n) % 251).astype(np.uint8))
+
+
 def test_cpp_host_mirror_default_scene(oracle, tmp_path):
     """examples/default_scene.cpp = the reference's main() scene through include/rte/engine.hpp (C++20 over the C ABI):
     its seven PPMs must be the reference's tonemapAll of the reference's render within +-1 LSB (north_star: default scene)."""
