@@ -44,7 +44,7 @@ struct rte_ctx {
     DevScene sc{};
     DevCamera cam{};
     rte_camera cam_host{};
-    DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views;
+    DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views, b_tviews;
     bool views_dirty = true;
     double views_bias = -1.0;
 
@@ -220,7 +220,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
-                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -382,7 +382,9 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
                     smem, ns, nt, smem_budget);
 
     int rc;
+    const int nt_pad32 = (nt + 31) & ~31;
     if ((rc = reserve(ctx, ctx->b_views, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
+    if ((rc = reserve(ctx, ctx->b_tviews, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
     if ((rc = upload(ctx, ctx->b_sph32, sph32)) || (rc = upload(ctx, ctx->b_sph64, sph64)) || (rc = upload(ctx, ctx->b_sphmat, sphmat)) ||
         (rc = upload(ctx, ctx->b_planes, planes)) || (rc = upload(ctx, ctx->b_tri32, tri32)) || (rc = upload(ctx, ctx->b_tri64, tri64)) ||
         (rc = upload(ctx, ctx->b_triinfo, triinfo)) || (rc = upload(ctx, ctx->b_mats, mats)) || (rc = upload(ctx, ctx->b_lights, lights)))
@@ -392,7 +394,8 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     DevScene& sc = ctx->sc;
     sc.sph32 = (const float4*)ctx->b_sph32.p; sc.tri32 = (const float4*)ctx->b_tri32.p;
     sc.views = ns > 0 ? (const float*)ctx->b_views.p : nullptr;
-    sc.reflective = 0; sc.pad2 = 0;
+    sc.tri_views = nt > 0 ? (const float*)ctx->b_tviews.p : nullptr;
+    sc.reflective = 0; sc.nt_pad32 = nt_pad32;
     for (const rte_material& m : mats) if (m.specular > 0.0) sc.reflective = 1;
     ctx->views_dirty = true;
     sc.ns = ns; sc.ns_pad = ns_pad; sc.nt = nt; sc.nt_pad = nt_pad;
@@ -435,7 +438,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
     p.sc = ctx->sc; p.cam = ctx->cam;
     const size_t smem_budget = ctx->smem_optin > 4096 ? ctx->smem_optin - 4096 : 0;  // static smem + headroom
     p.plan = plan_smem(ctx->sc, smem_budget);
-    if (p.plan.use_views && (ctx->views_dirty || ctx->views_bias != o.bias)) {
+    if ((p.plan.use_views || p.plan.use_tri_views) && (ctx->views_dirty || ctx->views_bias != o.bias)) {
         RTE_CUDA(ctx, launch_build_views(ctx->sc, ctx->cam, o.bias, ctx->stream));
         ctx->views_dirty = false;
         ctx->views_bias = o.bias;

@@ -39,7 +39,8 @@ struct DevScene {
     const float4* sph32;  // {cx, cy, cz, r*r}; padded to a multiple of 32 with never-hit entries
     const float* views;   // (1+nl) per-origin views of the spheres (rte_views.cuh), rebuilt per camera / bias; may be NULL
     int32_t reflective;   // some material has specular > 0: reflection rays (generic closest-hit) will be traced
-    int32_t pad2;
+    int32_t nt_pad32;     // triangles padded to a multiple of 32 (one candidate mask per 32 bounding spheres)
+    const float* tri_views;  // (1+nl) per-origin views of the triangles' bounding spheres, same format as `views`; may be NULL
     const float4* tri32;  // 3 x float4 per triangle: {a0,_}, {e1,_}, {e2,_}; padded to a multiple of 2
     int32_t ns, ns_pad, nt, nt_pad;
     // FP64 exact arrays

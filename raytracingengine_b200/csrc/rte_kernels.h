@@ -18,6 +18,9 @@ struct SmemPlan {
     int32_t stage_sph;   // generic sph32 array is in shared memory (else read from global by the rare generic queries)
     int32_t stream_views;  // views do not fit: view_bytes = 2 buffers of one view each, refilled by TMA while the other is scanned
     uint32_t one_view_bytes;
+    uint32_t tview_bytes;  // triangle views (bounding spheres of the triangles), resident
+    int32_t use_tri_views; // triangle phases of primary / shadow rays go through them
+    int32_t stage_tri;     // generic tri32 array is in shared memory (else read from global by the rare generic queries)
     size_t total;
 };
 SmemPlan plan_smem(const DevScene& sc, size_t budget);

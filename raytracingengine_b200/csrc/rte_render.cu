@@ -58,9 +58,18 @@ SmemPlan plan_smem(const DevScene& sc, size_t budget) {
     SmemPlan pl{};
     const size_t tri = (size_t)sc.nt_pad * 48, sph = (size_t)sc.ns_pad * 16;
     const size_t views = sc.ns > 0 ? (size_t)(1 + sc.nl) * view_bytes(sc.ns_pad) : 0;
-    pl.tri_bytes = (uint32_t)tri;
+    const size_t tviews = (sc.nt > 0 && sc.tri_views) ? (size_t)(1 + sc.nl) * view_bytes(sc.nt_pad32) : 0;
     pl.one_view_bytes = (uint32_t)view_bytes(sc.ns_pad);
-    if (sc.views && tri + views <= budget) {
+    pl.stage_tri = 1;
+    if ((sc.views || sc.ns == 0) && tviews > 0 && views + tviews <= budget) {
+        // triangle scenes (C1/C4): sphere and triangle views resident; the generic arrays only where reflection rays use them
+        pl.use_views = sc.ns > 0 ? 1 : 0;
+        pl.use_tri_views = 1;
+        pl.view_bytes = (uint32_t)views;
+        pl.tview_bytes = (uint32_t)tviews;
+        pl.stage_tri = (sc.reflective && views + tviews + tri <= budget) ? 1 : 0;
+        pl.stage_sph = (sc.reflective && sc.ns > 0 && views + tviews + (pl.stage_tri ? tri : 0) + sph <= budget) ? 1 : 0;
+    } else if (sc.views && tri + views <= budget) {
         pl.use_views = 1;
         pl.view_bytes = (uint32_t)views;
         pl.stage_sph = (sc.reflective && tri + views + sph <= budget) ? 1 : 0;
@@ -74,7 +83,8 @@ SmemPlan plan_smem(const DevScene& sc, size_t budget) {
         pl.stage_sph = 1;
     }
     pl.sph_bytes = pl.stage_sph ? (uint32_t)sph : 0u;
-    pl.total = (size_t)pl.view_bytes + pl.sph_bytes + pl.tri_bytes;
+    pl.tri_bytes = pl.stage_tri ? (uint32_t)tri : 0u;
+    pl.total = (size_t)pl.view_bytes + pl.tview_bytes + pl.sph_bytes + pl.tri_bytes;
     return pl;
 }
 
@@ -88,18 +98,23 @@ __device__ __forceinline__ void tma_chunks(unsigned char* dst, const void* src, 
 
 // Stage the filter arrays into dynamic shared memory with TMA bulk copies.  Called by every thread of the CTA.
 __device__ __forceinline__ void stage_scene(const DevScene& sc, const SmemPlan& pl, unsigned char* dyn, uint64_t* bar,
-                                            const ulonglong2*& s_views, const float4*& s_sph, const float4*& s_tri) {
+                                            const ulonglong2*& s_views, const ulonglong2*& s_tviews, const float4*& s_sph, const float4*& s_tri) {
+    unsigned char* p_tv = dyn + pl.view_bytes;
+    unsigned char* p_sph = p_tv + pl.tview_bytes;
+    unsigned char* p_tri = p_sph + pl.sph_bytes;
     s_views = reinterpret_cast<const ulonglong2*>(dyn);
-    s_sph = pl.stage_sph ? reinterpret_cast<const float4*>(dyn + pl.view_bytes) : sc.sph32;
-    s_tri = reinterpret_cast<const float4*>(dyn + pl.view_bytes + pl.sph_bytes);
+    s_tviews = reinterpret_cast<const ulonglong2*>(p_tv);
+    s_sph = pl.stage_sph ? reinterpret_cast<const float4*>(p_sph) : sc.sph32;
+    s_tri = pl.stage_tri ? reinterpret_cast<const float4*>(p_tri) : sc.tri32;
     if (threadIdx.x == 0) mbar_init(bar, 1);
     __syncthreads();
     if (threadIdx.x == 0) {
         const uint32_t vb = pl.stream_views ? 0u : pl.view_bytes;  // streamed views are fetched by ViewStream
-        mbar_expect_tx(bar, vb + pl.sph_bytes + pl.tri_bytes);
+        mbar_expect_tx(bar, vb + pl.tview_bytes + pl.sph_bytes + pl.tri_bytes);
         tma_chunks(dyn, sc.views, vb, bar);
-        tma_chunks(dyn + pl.view_bytes, sc.sph32, pl.sph_bytes, bar);
-        tma_chunks(dyn + pl.view_bytes + pl.sph_bytes, sc.tri32, pl.tri_bytes, bar);
+        tma_chunks(p_tv, sc.tri_views, pl.tview_bytes, bar);
+        tma_chunks(p_sph, sc.sph32, pl.sph_bytes, bar);
+        tma_chunks(p_tri, sc.tri32, pl.tri_bytes, bar);
     }
     mbar_wait(bar, 0);
 }
@@ -118,8 +133,8 @@ struct PixelCounters {
 // alive = false).  kReflect = false compiles the diffuse-only path (no material has specular > 0): the depth loop,
 // Blinn-Phong and the reflection state disappear.  Per pixel the ray state is FP64, bit-identical to the reference.
 template <int K, bool kReflect>
-__device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const float4* s_sph,
-                                             const float4* s_tri, const int (&px)[K], const int (&py)[K], const bool (&inb)[K],
+__device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const ulonglong2* s_tviews,
+                                             const float4* s_sph, const float4* s_tri, const int (&px)[K], const int (&py)[K], const bool (&inb)[K],
                                              const int64_t (&out_idx)[K], PixelCounters& cnt, d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     d3 o[K], d[K], acc[K];
@@ -136,8 +151,9 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
     const double bias = P.bias;
     const int max_depth = kReflect ? P.max_depth : 1, nl = sc.nl;
     const bool nf = P.no_filter != 0;
-    const bool uv = P.plan.use_views != 0;
-    const int view_stride = sc.ns_pad;  // ulonglong2 elements per view
+    const bool utv = P.plan.use_tri_views != 0;
+    const bool uv = P.plan.use_views != 0 || utv;  // (triangle views exist only next to sphere views, or without spheres)
+    const int view_stride = sc.ns_pad, tview_stride = sc.nt_pad32;  // ulonglong2 elements per view
 #pragma unroll 1
     for (int depth = 0; depth < max_depth; ++depth) {
         bool any_alive = false;
@@ -146,7 +162,7 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
         if (!__any_sync(kFullMask, any_alive)) break;
         Hit h[K];
         if (uv && depth == 0) {
-            closest_hit_view<K>(sc, s_views, s_tri, cam_o, d, alive, nf, h, cnt.confirms);
+            closest_hit_view<K>(sc, s_views, s_tviews, utv, s_tri, cam_o, d, alive, nf, h, cnt.confirms);
 #pragma unroll
             for (int k = 0; k < K; ++k) if (alive[k]) cnt.sph_exec += (uint32_t)sc.ns_pad;
         } else {
@@ -235,7 +251,8 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
 #pragma unroll
                 for (int k = 0; k < K; ++k) lists.n[k] = kListCap + 1;
                 if (uv) {
-                    occluded_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, s_tri, Lp, sr, bias, nf, r, lists, cnt.confirms, cnt.sph_exec);
+                    occluded_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, s_tviews + (size_t)(1 + j) * tview_stride, utv, s_tri, Lp, sr,
+                                     bias, nf, r, lists, cnt.confirms, cnt.sph_exec);
                 } else {
 #pragma unroll
                     for (int k = 0; k < K; ++k)
@@ -362,8 +379,8 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
     const float4 *s_sph, *s_tri;
-    const ulonglong2* s_views;
-    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);  // contains __syncthreads: s_sc visible after it
+    const ulonglong2 *s_views, *s_tviews;
+    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_tviews, s_sph, s_tri);  // contains __syncthreads: s_sc visible after it
     const DevScene& sc = s_sc;
 
     const int W = P.cam.width, rows = P.n_rows;
@@ -395,7 +412,7 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
         }
         PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         d3 c[K];
-        trace_pixels<K, kReflect>(P, sc, s_views, s_sph, s_tri, px, py, inb, out_idx, cnt, c);
+        trace_pixels<K, kReflect>(P, sc, s_views, s_tviews, s_sph, s_tri, px, py, inb, out_idx, cnt, c);
         const bool words_ok = P.rgb8_words && (W & 3) == 0 && tx * kTileW + kTileW <= W;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -480,13 +497,15 @@ struct ViewsStream {
 // instruction caches: everything that runs once per pixel sits in `#pragma unroll 1` loops over the K pixels of
 // the thread (one copy of the FP64 code, per-pixel state in local memory), only the two sphere scans are
 // unrolled over K.  The general kernel's per-pixel code is ~4x larger and stalls on instruction fetch.
-template <int K, class Views>
-__device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const float4* s_sph,
-                                                const float4* s_tri, const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K],
-                                                PixelCounters& cnt, d3 (&result)[K]) {
+// kTris: the scene has triangles and their views are resident (s_tviews): a third scan after the planes.
+template <int K, bool kTris, class Views>
+__device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const ulonglong2* s_tviews,
+                                                const float4* s_sph, const float4* s_tri, const int (&pxs)[K], const int (&pys)[K],
+                                                const bool (&inb)[K], PixelCounters& cnt, d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     const double bias = P.bias;
-    const int nl = sc.nl, np = sc.np, ns = sc.ns;
+    const int nl = sc.nl, np = sc.np, ns = sc.ns, nt = kTris ? sc.nt : 0;
+    const int tview_stride = sc.nt_pad32;
     d3 dir[K];
     bool alive[K], found[K];
     Hit h[K];
@@ -506,15 +525,33 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
     d3 Pn[K], normal[K], diffuse[K];
     int mat[K], self[K];
     bool hitv[K];
+    if (kTris) {  // planes, then the triangles through their camera view, then (below) the hit records
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            if (!alive[k]) continue;
+            const d3 d = dir[k];
+            Hit hk = h[k];
+            bool fk = found[k];
+#pragma unroll 1
+            for (int i = 0; i < np; ++i) {
+                double t;
+                if (plane_exact(sc.planes[i], cam_o, d, t) && (!fk || t < hk.t)) {
+                    fk = true; hk.t = t; hk.kind = RTE_HIT_PLANE; hk.idx = (uint32_t)i;
+                }
+            }
+            h[k] = hk; found[k] = fk;
+        }
+        closest_spheres_view<K, true>(sc, s_tviews, cam_o, dir, alive, false, h, found, cnt.confirms);
+    }
 #pragma unroll 1
     for (int k = 0; k < K; ++k) {
         const d3 d = dir[k];
         Hit hk = h[k];
         bool fk = found[k];
         if (alive[k]) {
-            cnt.sph += (uint32_t)ns; cnt.pl += (uint32_t)np; cnt.sph_exec += (uint32_t)sc.ns_pad;
+            cnt.sph += (uint32_t)ns; cnt.pl += (uint32_t)np; cnt.tri += (uint32_t)nt; cnt.sph_exec += (uint32_t)sc.ns_pad;
 #pragma unroll 1
-            for (int i = 0; i < np; ++i) {  // planes after the spheres, strict '<' (RE/Scene.h:218-257)
+            for (int i = 0; i < (kTris ? 0 : np); ++i) {  // planes after the spheres, strict '<' (RE/Scene.h:218-257)
                 double t;
                 if (plane_exact(sc.planes[i], cam_o, d, t) && (!fk || t < hk.t)) {
                     fk = true; hk.t = t; hk.kind = RTE_HIT_PLANE; hk.idx = (uint32_t)i;
@@ -533,8 +570,10 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
             if (hk.kind == RTE_HIT_SPHERE) {
                 const double4 s = sc.sph64[hk.idx];
                 ng = normalize(P_ - mk(s.x, s.y, s.z));
-            } else {
+            } else if (!kTris || hk.kind == RTE_HIT_PLANE) {
                 ng = ld3(sc.planes[hk.idx].n);
+            } else {
+                ng = ld3(sc.tri64[hk.idx].n);
             }
         }
         const d3 incoming = normalize(d);
@@ -582,11 +621,36 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
 #pragma unroll
         for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;
         const bool skip_planes = __all_sync(kFullMask, all_done);
+        if (kTris && !skip_planes) {  // planes, then the triangles through the light's view; T is computed below
+            bool all_done2 = true;
+#pragma unroll 1
+            for (int k = 0; k < K; ++k) {
+                OccState s = st[k];
+                if (s.res.near && s.res.occluded) s.done = true;  // the march decides
+                if (!s.done) {
+                    const ShadowRay r = sr[k];
+                    uint32_t firstp = (uint32_t)np;
+#pragma unroll 1
+                    for (int i = 0; i < np; ++i) {
+                        double t;
+                        if (plane_exact(sc.planes[i], r.o, r.d, t)) {
+                            s.on_t(t, firstp, (uint32_t)i);
+                            if (s.done) break;
+                        }
+                    }
+                    s.res.pl_tests = firstp;
+                }
+                st[k] = s;
+                all_done2 = all_done2 && s.done;
+            }
+            if (!__all_sync(kFullMask, all_done2))
+                occluded_spheres_view<K, true>(sc, s_tviews + (size_t)(1 + j) * tview_stride, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec);
+        }
 #pragma unroll 1
         for (int k = 0; k < K; ++k) {
             OccState s = st[k];
             const ShadowRay r = sr[k];
-            if (!skip_planes && !s.done && !s.res.occluded) {  // planes, any-hit in canonical order (a `near` ray with an occluder: the march decides)
+            if (!kTris && !skip_planes && !s.done && !s.res.occluded) {  // planes, any-hit in canonical order (a `near` ray with an occluder: the march decides)
                 uint32_t firstp = (uint32_t)np;
 #pragma unroll 1
                 for (int i = 0; i < np; ++i) {
@@ -598,12 +662,12 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
                 }
                 s.res.pl_tests = firstp;
             }
-            cnt.sph += s.res.sph_tests; cnt.pl += s.res.pl_tests;
+            cnt.sph += s.res.sph_tests; cnt.pl += s.res.pl_tests; cnt.tri += s.res.tri_tests;
             if (!r.cast) continue;
             double T;
             if (s.res.near) {
                 const int ln = lists.n[k];
-                if (ln <= kListCap) T = march_list(sc, lists.idx[k], ln, r.o, r.d, r.maxDist, bias);
+                if (!kTris && ln <= kListCap) T = march_list(sc, lists.idx[k], ln, r.o, r.d, r.maxDist, bias);
                 else T = march_exact(sc, s_sph, s_tri, r.o, r.d, r.maxDist, bias, false, cnt.confirms);
                 cnt.marches += 1;
             }
@@ -636,7 +700,7 @@ constexpr int kFastMinBlocks = RTE_FAST_MINB;
 
 // kBig = false: kFastThreads x kFastMinBlocks CTAs per SM; kBig = true: one 512-thread CTA per SM (views of large scenes)
 // kStream = true (implies kBig): the views pass through two shared-memory buffers (ViewsStream), tile batches are CTA-uniform
-template <int K, bool kBig, bool kStream>
+template <int K, bool kBig, bool kStream, bool kTris = false>
 __global__ void __launch_bounds__(kBig ? kRenderMaxThreads : kFastThreads, kBig ? 1 : kFastMinBlocks)
 render_fast_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
@@ -649,8 +713,8 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
     const float4 *s_sph, *s_tri;
-    const ulonglong2* s_views;
-    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);
+    const ulonglong2 *s_views, *s_tviews;
+    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_tviews, s_sph, s_tri);
     const DevScene& sc = s_sc;
     ViewsResident views_res{s_views, sc.ns_pad};
     ViewsStream views_str;
@@ -691,8 +755,8 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         }
         PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         d3 c[K];
-        if (kStream) trace_tile_fast<K>(P, sc, views_str, s_sph, s_tri, px, py, inb, cnt, c);
-        else trace_tile_fast<K>(P, sc, views_res, s_sph, s_tri, px, py, inb, cnt, c);
+        if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_sph, s_tri, px, py, inb, cnt, c);
+        else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_sph, s_tri, px, py, inb, cnt, c);
         const bool words_ok = P.rgb8_words && (W & 3) == 0 && tx * kTileW + kTileW <= W;
         const bool want_rgb8 = P.tonemap_op >= 0 && (P.out.rgb8 || P.n_peers > 0);
 #pragma unroll 1
@@ -731,9 +795,14 @@ static cudaError_t ensure_smem(const void* fn, size_t bytes) {
 }
 
 cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double bias, cudaStream_t stream) {
-    if (!sc.views || sc.ns == 0) return cudaSuccess;
-    const int total = (1 + sc.nl) * sc.ns_pad;
-    build_views_kernel<<<(total + 255) / 256, 256, 0, stream>>>(sc, cam, bias, const_cast<float*>(sc.views));
+    if (sc.views && sc.ns > 0) {
+        const int total = (1 + sc.nl) * sc.ns_pad;
+        build_views_kernel<false><<<(total + 255) / 256, 256, 0, stream>>>(sc, cam, bias, const_cast<float*>(sc.views));
+    }
+    if (sc.tri_views && sc.nt > 0) {
+        const int total = (1 + sc.nl) * sc.nt_pad32;
+        build_views_kernel<true><<<(total + 255) / 256, 256, 0, stream>>>(sc, cam, bias, const_cast<float*>(sc.tri_views));
+    }
     return cudaGetLastError();
 }
 
@@ -765,8 +834,8 @@ static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int smal
 
 bool fast_path_eligible(const RenderParams& p) {
     const rte_frame& f = p.out;
-    return p.plan.use_views && !p.sc.reflective && p.sc.nt == 0 && !p.exact_shadows && !p.no_filter && !f.prim_id && !f.depth &&
-           !f.depth64 && !f.normal && !f.albedo && !f.light_mask;
+    return (p.plan.use_views || p.plan.use_tri_views) && !p.sc.reflective && (p.sc.nt == 0 || p.plan.use_tri_views) && !p.exact_shadows &&
+           !p.no_filter && !f.prim_id && !f.depth && !f.depth64 && !f.normal && !f.albedo && !f.light_mask;
 }
 
 cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t stream) {
@@ -781,6 +850,10 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
             const void* fn = (const void*)render_fast_kernel<kViewPixels, true, true>;
             return launch_render_fn(fn, fn, kRenderMaxThreads, 1, kViewPixels, p, sm_count, stream);
         }
+        if (p.sc.nt > 0)
+            return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false, true>,
+                                    (const void*)render_fast_kernel<kViewPixels, true, false, true>, kFastThreads, kFastMinBlocks, kViewPixels, p,
+                                    sm_count, stream);
         return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false>, (const void*)render_fast_kernel<kViewPixels, true, false>,
                                 kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream);
     }
@@ -807,8 +880,8 @@ __global__ void __launch_bounds__(kRenderThreads, 2) closest_kernel(const __grid
     __shared__ __align__(8) uint64_t s_bar;
     if (threadIdx.x == 0) s_sc = Q.sc;
     const float4 *s_sph, *s_tri;
-    const ulonglong2* s_views;
-    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);
+    const ulonglong2 *s_views, *s_tviews;
+    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, s_views, s_tviews, s_sph, s_tri);
     const DevScene& sc = s_sc;
     for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < Q.n; base += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = base + threadIdx.x;
@@ -848,8 +921,8 @@ __global__ void __launch_bounds__(kRenderThreads, 2) any_before_kernel(const __g
     __shared__ __align__(8) uint64_t s_bar;
     if (threadIdx.x == 0) s_sc = Q.sc;
     const float4 *s_sph, *s_tri;
-    const ulonglong2* s_views;
-    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, s_views, s_sph, s_tri);
+    const ulonglong2 *s_views, *s_tviews;
+    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, s_views, s_tviews, s_sph, s_tri);
     const DevScene& sc = s_sc;
     for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < Q.n; base += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = base + threadIdx.x;
@@ -867,6 +940,7 @@ __global__ void __launch_bounds__(kRenderThreads, 2) any_before_kernel(const __g
 static SmemPlan generic_plan(const DevScene& sc) {
     SmemPlan pl{};
     pl.stage_sph = 1;
+    pl.stage_tri = 1;
     pl.sph_bytes = (uint32_t)((size_t)sc.ns_pad * 16);
     pl.tri_bytes = (uint32_t)((size_t)sc.nt_pad * 48);
     pl.total = (size_t)pl.sph_bytes + pl.tri_bytes;

@@ -154,7 +154,7 @@ __device__ __forceinline__ void scan_triangles(const float4* __restrict__ s_tri,
 
 // Planes (exact) then triangles (FP32 filter + FP64 confirm) of a closest-hit query, after the spheres.
 __device__ __forceinline__ void closest_planes_triangles(const DevScene& sc, const float4* __restrict__ s_tri, const Ray32& r, d3 o, d3 d,
-                                                         bool alive, Hit& best, bool& found, uint32_t& confirms) {
+                                                         bool alive, Hit& best, bool& found, uint32_t& confirms, bool tris = true) {
     if (alive) {
         const int np = sc.np;
 #pragma unroll 1
@@ -165,7 +165,7 @@ __device__ __forceinline__ void closest_planes_triangles(const DevScene& sc, con
             }
         }
     }
-    if (sc.nt == 0) return;
+    if (sc.nt == 0 || !tris) return;  // !tris: the caller scans the triangles through their view (rte_views.cuh)
     CandList L;
     L.n = 0;
     auto flush = [&]() {
@@ -287,7 +287,7 @@ __device__ __forceinline__ OccState occ_begin(double maxDist, double bias, bool 
 
 // Planes (exact) and triangles (FP32 filter + FP64 confirm) of an any-hit query; all 32 lanes call it.
 __device__ __forceinline__ void occ_planes_triangles(const DevScene& sc, const float4* __restrict__ s_tri, const Ray32& r, d3 o, d3 d,
-                                                     OccState& st, uint32_t& confirms) {
+                                                     OccState& st, uint32_t& confirms, bool tris = true) {
     if (__all_sync(kFullMask, st.done)) return;
     const int np = sc.np;
     if (!st.done) {
@@ -303,7 +303,7 @@ __device__ __forceinline__ void occ_planes_triangles(const DevScene& sc, const f
         st.res.pl_tests = firstp;
     }
     const int nt_pad = sc.nt_pad, nt = sc.nt;
-    if (nt == 0) return;
+    if (nt == 0 || !tris) return;
     const bool scan_tris = !st.done;
     uint32_t firstt = (uint32_t)nt;
     CandList L;

@@ -60,26 +60,39 @@ __device__ __forceinline__ ViewEntry view_entry(const float* __restrict__ view, 
     return e;
 }
 
-// Builds view j (0 = camera, 1.. = lights) for every sphere.  One thread per (view, sphere).
+// Builds view j (0 = camera, 1.. = lights) for every sphere — or, kTri, for the bounding sphere of every triangle
+// (centroid, radius = farthest vertex: a ray that hits the triangle hits that sphere).  One thread per (view, primitive).
+template <bool kTri>
 __global__ void __launch_bounds__(256) build_views_kernel(const DevScene sc, const DevCamera cam, double bias, float* __restrict__ views) {
-    const int ns_pad = sc.ns_pad, nv = 1 + sc.nl;
-    const int total = nv * ns_pad;
+    const int n = kTri ? sc.nt : sc.ns, n_pad = kTri ? sc.nt_pad32 : sc.ns_pad, nv = 1 + sc.nl;
+    const int total = nv * n_pad;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
-        const int j = t / ns_pad, i = t - j * ns_pad;
+        const int j = t / n_pad, i = t - j * n_pad;
         float fx = 0.f, fy = 0.f, fz = 0.f, ng = -INFINITY;  // never-candidate padding: h = -inf
-        if (i < sc.ns) {
+        if (i < n) {
             const d3 O = j == 0 ? ld3(cam.pos) : ld3(sc.lights[j - 1].pos);
-            const double4 s = sc.sph64[i];
-            const d3 f = mk(s.x, s.y, s.z) - O;
+            d3 C;
+            double r;
+            if (kTri) {
+                const DevTri64 T = sc.tri64[i];
+                const d3 a = ld3(T.a0), b = a + ld3(T.e1), c = a + ld3(T.e2);
+                C = (a + b + c) * (1.0 / 3.0);
+                const d3 da = a - C, db = b - C, dc = c - C;
+                r = sqrt(fmax(dot(da, da), fmax(dot(db, db), dot(dc, dc)))) * (1.0 + 1e-9) + 1e-300;
+            } else {
+                const double4 s = sc.sph64[i];
+                C = mk(s.x, s.y, s.z);
+                r = fabs(s.w);
+            }
+            const d3 f = C - O;
             const double F2 = dot(f, f);
-            const double r = fabs(s.w);
             double M = 16.0 * (double)kEps32 * F2 + 1e-30;
             if (j > 0) M += 2.0 * r * bias + bias * bias;
             fx = (float)f.x; fy = (float)f.y; fz = (float)f.z;
             ng = __double2float_ru((r * r - F2) + M);
             if (!(ng == ng)) ng = INFINITY;  // non-finite input: always a candidate (the FP64 test decides)
         }
-        float* p = views + ((size_t)j * ns_pad + (size_t)(i & ~1)) * 4 + (i & 1);
+        float* p = views + ((size_t)j * n_pad + (size_t)(i & ~1)) * 4 + (i & 1);
         p[0] = fx; p[2] = fy; p[4] = fz; p[6] = ng;
     }
 }
@@ -137,18 +150,28 @@ __device__ __forceinline__ void view_block_masks(const ulonglong2* __restrict__ 
 __device__ __noinline__ bool confirm_sphere(const double4* __restrict__ sph64, int idx, d3 o, d3 d, double& t) {
     return sphere_exact(sph64[idx], o, d, t);
 }
+__device__ __noinline__ bool confirm_triangle(const DevTri64* __restrict__ tri64, int idx, d3 o, d3 d, double& t) {
+    return tri_exact(tri64[idx], o, d, t);
+}
+// what a view holds: the spheres of the scene, or (kTri) the bounding spheres of its triangles
+template <bool kTri> __device__ __forceinline__ int view_count(const DevScene& sc) { return kTri ? sc.nt : sc.ns; }
+template <bool kTri> __device__ __forceinline__ int view_padded(const DevScene& sc) { return kTri ? sc.nt_pad32 : sc.ns_pad; }
+template <bool kTri> __device__ __forceinline__ float view_extent(const DevScene& sc) { return kTri ? sc.tri_extent + sc.tri_edge : sc.sph_extent; }
+template <bool kTri> __device__ __forceinline__ bool confirm_prim(const DevScene& sc, int idx, d3 o, d3 d, double& t) {
+    return kTri ? confirm_triangle(sc.tri64, idx, o, d, t) : confirm_sphere(sc.sph64, idx, o, d, t);
+}
 
 // Per-view constants of the FP32 interval arithmetic on candidates.
 struct ViewBounds {
     float slack;   // absolute error bound on distances along the ray
     float m2;      // 2 * (upper bound of every M_ij of the view): h~ - m2 <= true half-chord^2 <= h~
 };
-__device__ __forceinline__ ViewBounds view_bounds(const DevScene& sc, d3 origin, double bias, bool light_view) {
-    const float S = sqrtf((float)dot(origin, origin)) * 1.0000002f + sc.sph_extent;
+__device__ __forceinline__ ViewBounds view_bounds(float extent, d3 origin, double bias, bool light_view) {  // extent >= |C_i| + r_i
+    const float S = sqrtf((float)dot(origin, origin)) * 1.0000002f + extent;
     ViewBounds vb;
     vb.slack = 24.0f * kEps32 * S + 1e-6f;
     float m = 24.0f * kEps32 * S * S + 1e-30f;
-    if (light_view) m += (float)(2.0 * bias) * sc.sph_extent + (float)(bias * bias);
+    if (light_view) m += (float)(2.0 * bias) * extent + (float)(bias * bias);
     vb.m2 = 2.0f * m * 1.0001f;
     return vb;
 }
@@ -195,18 +218,19 @@ __device__ __forceinline__ T pick(const T (&a)[K], int k) {
     return v;
 }
 
-// Scene::IntersectClosest over the spheres for K PRIMARY rays of one thread (view 0, common origin o).
-template <int K>
+// Scene::IntersectClosest over the spheres (kTri: the triangles, through their bounding spheres) for K PRIMARY rays of one
+// thread (view 0, common origin o).  best/found carry the result of the classes scanned before (canonical order, strict '<').
+template <int K, bool kTri = false>
 __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, d3 o, const d3 (&d)[K],
                                                      const bool (&alive)[K], bool no_filter, Hit (&best)[K], bool (&found)[K],
                                                      uint32_t& confirms) {
-    const ViewBounds vb = view_bounds(sc, o, 0.0, false);
+    const ViewBounds vb = view_bounds(view_extent<kTri>(sc), o, 0.0, false);
     ViewRay r[K];
     float best_f[K];
 #pragma unroll
-    for (int k = 0; k < K; ++k) { r[k] = make_view_ray(d[k]); best_f[k] = INFINITY; }
+    for (int k = 0; k < K; ++k) { r[k] = make_view_ray(d[k]); best_f[k] = found[k] ? __double2float_ru(best[k].t) : INFINITY; }
     const float* vf = reinterpret_cast<const float*>(view);
-    const int ns = sc.ns, ns_pad = sc.ns_pad;
+    const int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
     CandQueue<K> Q;
     int qn = 0;
     int base = 0;
@@ -244,11 +268,11 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
             }
             double t;
             ++confirms;
-            if (!confirm_sphere(sc.sph64, idx, o, dk, t)) continue;
+            if (!confirm_prim<kTri>(sc, idx, o, dk, t)) continue;
 #pragma unroll
             for (int i = 0; i < K; ++i) {
                 if (i == k && (!found[i] || t < best[i].t)) {  // strict '<', RE/Scene.h:223
-                    found[i] = true; best[i].t = t; best[i].kind = RTE_HIT_SPHERE; best[i].idx = (uint32_t)idx;
+                    found[i] = true; best[i].t = t; best[i].kind = kTri ? RTE_HIT_TRIANGLE : RTE_HIT_SPHERE; best[i].idx = (uint32_t)idx;
                     best_f[i] = __double2float_ru(t);
                 }
             }
@@ -257,22 +281,25 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
     }
 }
 
-// Scene::IntersectClosest for K primary rays: spheres through view 0, then planes and triangles.
+// Scene::IntersectClosest for K primary rays: spheres through view 0, planes, then triangles (through their view 0 when
+// `tri_view`, else with the generic FP32 filter).  The view pointers are always shared-memory addresses (never selected
+// against NULL: the scans must compile to LDS).
 template <int K>
-__device__ __forceinline__ void closest_hit_view(const DevScene& sc, const ulonglong2* __restrict__ view0, const float4* __restrict__ s_tri,
-                                                 d3 o, const d3 (&d)[K], const bool (&alive)[K], bool no_filter, Hit (&best)[K],
-                                                 uint32_t& confirms) {
+__device__ __forceinline__ void closest_hit_view(const DevScene& sc, const ulonglong2* __restrict__ view0, const ulonglong2* __restrict__ tview0,
+                                                 bool tri_view, const float4* __restrict__ s_tri, d3 o, const d3 (&d)[K], const bool (&alive)[K],
+                                                 bool no_filter, Hit (&best)[K], uint32_t& confirms) {
     bool found[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) { best[k].t = 0.0; best[k].kind = RTE_HIT_NONE; best[k].idx = 0; found[k] = false; }
     if (sc.ns > 0) closest_spheres_view<K>(sc, view0, o, d, alive, no_filter, best, found, confirms);
-    if (sc.np > 0 || sc.nt > 0) {
+    if (sc.np > 0 || (sc.nt > 0 && !tri_view)) {
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             const Ray32 r = make_ray32(sc, o, d[k], no_filter);
-            closest_planes_triangles(sc, s_tri, r, o, d[k], alive[k], best[k], found[k], confirms);
+            closest_planes_triangles(sc, s_tri, r, o, d[k], alive[k], best[k], found[k], confirms, !tri_view);
         }
     }
+    if (sc.nt > 0 && tri_view) closest_spheres_view<K, true>(sc, tview0, o, d, alive, no_filter, best, found, confirms);
 }
 
 // One forward shadow ray of the reference (RE/Scene.h:86-104) plus what the reversed scan needs.
@@ -336,20 +363,25 @@ __device__ __noinline__ double march_list(const DevScene& sc, const uint16_t* li
     return std_clamp(T, 0.0, 1.0);
 }
 
-template <int K>
+// kTri = true: the triangle phase of the same query, through the light's view of the triangles' bounding spheres; `st`
+// continues from the sphere and plane phases (canonical order), every candidate is confirmed in FP64 (tri_exact).
+template <int K, bool kTri = false>
 __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, d3 Lp,
                                                       const ShadowRay (&ray)[K], double bias, bool no_filter, OccState (&st)[K],
                                                       RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
     uint32_t first[K];
+    bool scanning[K];
+    const int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
 #pragma unroll
-    for (int k = 0; k < K; ++k) lists.n[k] = 0;
-    const int ns = sc.ns, ns_pad = sc.ns_pad;
-#pragma unroll
-    for (int k = 0; k < K; ++k) { st[k] = occ_begin(ray[k].maxDist, bias, ray[k].cast); first[k] = (uint32_t)ns; }
+    for (int k = 0; k < K; ++k) {
+        if (!kTri) { lists.n[k] = 0; st[k] = occ_begin(ray[k].maxDist, bias, ray[k].cast); }
+        first[k] = (uint32_t)ns;
+        scanning[k] = kTri ? !st[k].done : ray[k].cast;
+    }
     if (ns > 0) {
-        const ViewBounds vb = view_bounds(sc, Lp, bias, true);
+        const ViewBounds vb = view_bounds(view_extent<kTri>(sc), Lp, bias, true);
         const float* vf = reinterpret_cast<const float*>(view);
-        const bool skip_self = bias >= 1e-5;
+        const bool skip_self = !kTri && bias >= 1e-5;
         ViewRay r[K];
         float tref[K], tmax_lo[K], tmax_hi[K];
         const float tsafe_hi = __double2float_ru(130.0 * bias) + vb.slack;
@@ -371,7 +403,7 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
             do {
                 uint32_t cand[K];
                 view_block_masks<K>(view + base, r, cand);
-                executed += kViewBlock;
+                if (!kTri) executed += kViewBlock;
                 uint32_t any = 0;
 #pragma unroll
                 for (int k = 0; k < K; ++k) {
@@ -402,9 +434,9 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
                     const float tc = tref[k] - ch.sc;  // forward distance of the chord centre
                     const float t0_lo = tc - ch.hc_hi - vb.slack, t0_hi = tc - ch.hc_lo + vb.slack, t1_hi = tc + ch.hc_hi + vb.slack;
                     if (t1_hi < 0.0f || t0_lo > tmax_hi[k]) continue;  // certainly no hit in (1e-6, maxDist), none <= bias
-                    certain = ch.hc_lo > 0.0f && t0_lo > tsafe_hi && t0_hi < tmax_lo[k];  // certainly t in (t_safe, maxDist)
+                    certain = !kTri && ch.hc_lo > 0.0f && t0_lo > tsafe_hi && t0_hi < tmax_lo[k];  // certainly t in (t_safe, maxDist)
                 }
-                {   // remember every in-range candidate of the ray (what an exact march over this ray could ever hit)
+                if (!kTri) {  // remember every in-range candidate of the ray (what an exact march over this ray could ever hit)
                     const int ln = lists.n[k];
                     if (ln < kListCap && idx < 65536) lists.idx[k][ln] = (uint16_t)idx;
                     lists.n[k] = (ln < kListCap && idx < 65536) ? ln + 1 : kListCap + 1;
@@ -413,7 +445,7 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
                 bool hit = false;
                 if (!certain) {
                     ++confirms;
-                    hit = confirm_sphere(sc.sph64, idx, ray[k].o, ray[k].d, t);
+                    hit = confirm_prim<kTri>(sc, idx, ray[k].o, ray[k].d, t);
                 }
 #pragma unroll
                 for (int i = 0; i < K; ++i) {
@@ -421,7 +453,10 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
                     if (certain) {
                         if (!st[i].res.occluded) { st[i].res.occluded = true; first[i] = (uint32_t)idx + 1u; }
                         if (!st[i].res.near) st[i].done = true;
-                    } else if (hit) st[i].on_t_view(t, first[i], (uint32_t)idx);
+                    } else if (hit) {
+                        if (kTri) st[i].on_t(t, first[i], (uint32_t)idx);
+                        else st[i].on_t_view(t, first[i], (uint32_t)idx);
+                    }
                 }
             }
             qn = 0;
@@ -432,28 +467,40 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
         }
     }
 #pragma unroll
-    for (int k = 0; k < K; ++k)
-        if (ray[k].cast) st[k].res.sph_tests = first[k];
+    for (int k = 0; k < K; ++k) {
+        if (scanning[k]) {
+            if (kTri) st[k].res.tri_tests = first[k];
+            else st[k].res.sph_tests = first[k];
+        }
+    }
 }
 
-// Spheres through the light's view, then planes and triangles (general kernel).
+// Spheres through the light's view, then planes, then triangles (through the light's triangle view when `tri_view`,
+// else with the generic FP32 filter) — general kernel.
 template <int K>
-__device__ __forceinline__ void occluded_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float4* __restrict__ s_tri,
-                                              d3 Lp, const ShadowRay (&ray)[K], double bias, bool no_filter, OccResult (&out)[K],
-                                              RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
+__device__ __forceinline__ void occluded_view(const DevScene& sc, const ulonglong2* __restrict__ view, const ulonglong2* __restrict__ tview,
+                                              bool tri_view, const float4* __restrict__ s_tri, d3 Lp, const ShadowRay (&ray)[K], double bias,
+                                              bool no_filter, OccResult (&out)[K], RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
     OccState st[K];
-    occluded_spheres_view<K>(sc, view, Lp, ray, bias, no_filter, st, lists, confirms, executed);
+    occluded_spheres_view<K>(sc, view, Lp, ray, bias, no_filter, st, lists, confirms, executed);  // ns == 0: only initialises st
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         if (st[k].res.near && st[k].res.occluded) st[k].done = true;  // the march decides; planes/triangles are not counted after an occluder
-        if (sc.np > 0 || sc.nt > 0) {
+        if (sc.np > 0 || (sc.nt > 0 && !tri_view)) {
             if (!__all_sync(kFullMask, st[k].done)) {
                 const Ray32 r32 = make_ray32(sc, ray[k].o, ray[k].d, no_filter);
-                occ_planes_triangles(sc, s_tri, r32, ray[k].o, ray[k].d, st[k], confirms);
+                occ_planes_triangles(sc, s_tri, r32, ray[k].o, ray[k].d, st[k], confirms, !tri_view);
             }
         }
-        out[k] = st[k].res;
     }
+    if (sc.nt > 0 && tri_view) {
+        bool all_done = true;
+#pragma unroll
+        for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;
+        if (!__all_sync(kFullMask, all_done)) occluded_spheres_view<K, true>(sc, tview, Lp, ray, bias, no_filter, st, lists, confirms, executed);
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) out[k] = st[k].res;
 }
 
 }  // namespace rte

@@ -200,4 +200,23 @@ def config4(mesh="blob", scale=1.0, specular=False):
                       lights, cam)
 
 
+def mixed_scene(width, height, focal, n_spheres=200, n_lights=3, seed=4242, mesh_level=2):
+    """Every primitive class at once (diffuse): a synthetic room of spheres + planes, a mesh Model inside it and a few
+    free Triangles — the canonical order spheres, planes, triangles, models with hits in each class."""
+    arrays, cam = synthetic_room(width, height, focal, n_spheres, n_lights, seed)
+    verts, faces = blob_mesh(level=mesh_level, radius=4.0, seed=seed + 1)
+    idx = fan_triangulate(faces)
+    mats = np.concatenate([arrays.materials, np.array([_material((0.2, 0.4, 1.0)), _material((1.0, 0.5, 0.1))], dtype=_abi.material_dt)])
+    models = np.zeros(1, dtype=_abi.model_dt)
+    models[0] = (0, len(verts), 0, len(idx), (2.0, -3.0, 2.0), len(mats) - 2, 0)
+    rng = SplitMix64(seed + 2)
+    tris = np.zeros(6, dtype=_abi.triangle_dt)
+    for i in range(len(tris)):
+        c = np.array([rng.range(-10, 10), rng.range(-10, 10), rng.range(-6, 10)])
+        v = [tuple(f32(x) for x in c + np.array([rng.range(-3, 3), rng.range(-3, 3), rng.range(-3, 3)])) for _ in range(3)]
+        tris[i] = (v[0], v[1], v[2], (0.0, 0.0, 0.0), len(mats) - 1, 0)
+    return SceneArrays(materials=mats, spheres=arrays.spheres, planes=arrays.planes, triangles=tris, models=models,
+                       model_vertices=verts, model_indices=idx, lights=arrays.lights), cam
+
+
 CONFIGS = {"c1": config1, "c2": config2, "c3": config3, "c4": config4, "c5": config5}
