@@ -137,10 +137,12 @@ typedef struct rte_scene_desc {
  * Render options / outputs
  * ---------------------------------------------------------------------------------------- */
 
+/* TraceRay's recursion is evaluated on a per-pixel stack of this many frames (the reference's maxRecursion is 10). */
+#define RTE_MAX_DEPTH 24
 typedef struct rte_render_opts {
     int32_t row0, row1;     /* render rows [row0,row1) of the camera image (row band of one GPU);
                                row1 <= 0 means camera.height */
-    int32_t max_depth;      /* Scene::maxRecursion, RE/Scene.h:24; <= 0 means 10 */
+    int32_t max_depth;      /* Scene::maxRecursion, RE/Scene.h:24; <= 0 means 10; at most RTE_MAX_DEPTH */
     int32_t tonemap_op;     /* RTE_TM_* fused into the render pass (RGB8 output), or RTE_TM_NONE */
     double bias;            /* RE/Scene.h:291; <= 0 means 1e-3 */
     double max_white;       /* reinhardExtended*(…, max_white); <= 0 means 5.0 (RE/RaytracingEngine.cpp:193,195) */

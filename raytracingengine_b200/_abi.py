@@ -38,6 +38,7 @@ TM_ACES = 6
 FLAG_EXACT_SHADOWS, FLAG_NO_FILTER, FLAG_GENERAL_KERNEL = 1, 2, 4
 IPC_HANDLE_BYTES = 64  # RTE_IPC_HANDLE_BYTES
 MAX_PEERS = 8          # RTE_MAX_PEERS
+MAX_DEPTH = 24         # RTE_MAX_DEPTH
 
 # --- numpy dtypes (C layout) -------------------------------------------------------------------
 material_dt = np.dtype(  # Material, RE/Shape.h:13-19

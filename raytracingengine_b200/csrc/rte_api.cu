@@ -147,6 +147,7 @@ int resolve_opts(rte_ctx* ctx, const rte_render_opts* o, Defaults& d) {
     d.row0 = o ? o->row0 : 0;
     d.row1 = (o && o->row1 > 0) ? o->row1 : H;
     d.max_depth = (o && o->max_depth > 0) ? o->max_depth : 10;
+    if (d.max_depth > RTE_MAX_DEPTH) return fail(ctx, RTE_ERR_LIMIT, "opts.max_depth = %d exceeds RTE_MAX_DEPTH = %d", d.max_depth, RTE_MAX_DEPTH);
     d.tonemap_op = o ? o->tonemap_op : RTE_TM_NONE;
     d.bias = (o && o->bias > 0) ? o->bias : 1e-3;
     d.max_white = (o && o->max_white > 0) ? o->max_white : 5.0;
@@ -272,10 +273,6 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
 
     // materials (+ the default Material at index nm, RE/Shape.h:13-19)
     std::vector<rte_material> mats(d->materials, d->materials + d->n_materials);
-    for (int64_t i = 0; i < d->n_materials; ++i) {
-        if (mats[i].transparency > 0.0)
-            return fail(ctx, RTE_ERR_LIMIT, "material %lld has transparency > 0: refraction (RE/Scene.h:175-187) is not built yet", (long long)i);
-    }
     rte_material def{};
     def.shininess = 128.0; def.refractive_index = 1.0;
     mats.push_back(def);
@@ -396,14 +393,18 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     sc.views = ns > 0 ? (const float*)ctx->b_views.p : nullptr;
     sc.tri_views = nt > 0 ? (const float*)ctx->b_tviews.p : nullptr;
     sc.reflective = 0; sc.nt_pad32 = nt_pad32;
-    for (const rte_material& m : mats) if (m.specular > 0.0) sc.reflective = 1;
+    sc.transparent = 0;
+    for (int64_t i = 0; i < d->n_materials; ++i) {  // (the default Material appended at index nm is opaque and diffuse)
+        if (mats[i].specular > 0.0 || mats[i].transparency > 0.0) sc.reflective = 1;  // secondary rays will be traced
+        if (mats[i].transparency > 0.0) sc.transparent = 1;
+    }
     ctx->views_dirty = true;
     sc.ns = ns; sc.ns_pad = ns_pad; sc.nt = nt; sc.nt_pad = nt_pad;
     sc.sph64 = (const double4*)ctx->b_sph64.p; sc.sph_mat = (const int32_t*)ctx->b_sphmat.p;
     sc.planes = (const DevPlane*)ctx->b_planes.p; sc.tri64 = (const DevTri64*)ctx->b_tri64.p;
     sc.tri_info = (const int2*)ctx->b_triinfo.p; sc.materials = (const rte_material*)ctx->b_mats.p;
     sc.lights = (const DevLight*)ctx->b_lights.p;
-    sc.np = np; sc.nm = (int)d->n_materials; sc.nl = nl; sc.pad0 = 0;
+    sc.np = np; sc.nm = (int)d->n_materials; sc.nl = nl;
     sc.sph_extent = up((float)s_ext) * 1.000001f;
     sc.tri_extent = up((float)t_ext) * 1.000001f;
     sc.tri_edge = up((float)t_edge) * 1.000001f;

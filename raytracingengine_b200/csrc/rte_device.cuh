@@ -51,7 +51,8 @@ struct DevScene {
     const int2* tri_info; // {material, reported index (triangle index or MODEL index, RE/Shape.h:276)}
     const rte_material* materials;  // nm entries + one default Material at index nm
     const DevLight* lights;
-    int32_t np, nm, nl, pad0;
+    int32_t np, nm, nl;
+    int32_t transparent;  // some material has transparency > 0: refraction rays, transmittance marches through occluders
     // bounds used by the filter margins
     float sph_extent;  // max_i(|C_i| + r_i)
     float tri_extent;  // max |vertex|
@@ -94,6 +95,14 @@ __device__ __forceinline__ d3 reflect(d3 i, d3 n) { return i - (n * 2.0) * dot(i
 __device__ __forceinline__ double std_max(double a, double b) { return (a < b) ? b : a; }              // std::max
 __device__ __forceinline__ double std_min(double a, double b) { return (b < a) ? b : a; }              // std::min
 __device__ __forceinline__ double std_clamp(double v, double lo, double hi) { return (v < lo) ? lo : (hi < v) ? hi : v; }
+// Vec3::refract, RE/Math.h:43-52 (both arguments are normalised again, like upstream)
+__device__ __forceinline__ d3 refract(d3 self, d3 normal, double eta) {
+    const d3 I = normalize(self), N = normalize(normal);
+    const double cosi = std_clamp(dot(I, N), -1.0, 1.0);
+    const double k = 1.0 - eta * eta * (1.0 - cosi * cosi);
+    if (k < 0.0) return mk(0.0, 0.0, 0.0);
+    return I * eta - N * (eta * cosi + sqrt(k));
+}
 
 // Camera::getRay(px, py, false), RE/Math.h:99-121
 __device__ __forceinline__ d3 camera_dir(const DevCamera& c, int px, int py) {

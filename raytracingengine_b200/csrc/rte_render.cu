@@ -46,6 +46,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
 }
 
 constexpr uint32_t kTmaChunk = 32768;
+constexpr int kMaxTreeDepth = RTE_MAX_DEPTH;  // rte.h: largest opts.max_depth (frames of the per-pixel TraceRay stack)
 #ifndef RTE_VIEW_PIXELS
 #define RTE_VIEW_PIXELS 2
 #endif
@@ -154,8 +155,43 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
     const bool utv = P.plan.use_tri_views != 0;
     const bool uv = P.plan.use_views != 0 || utv;  // (triangle views exist only next to sphere views, or without spheres)
     const int view_stride = sc.ns_pad, tview_stride = sc.nt_pad32;  // ulonglong2 elements per view
+    // kReflect: TraceRay's recursion (RE/Scene.h:131-198) as an explicit per-pixel stack, evaluated in the reference's own
+    // order — local light, then the refracted subtree, then the reflected subtree, each added with its coefficient when
+    // it returns — so that the sums round exactly like the recursive calls.  One loop iteration = one TraceRay node per
+    // lane (the lanes of a warp sit at different nodes of their trees; the light views serve all of them alike).
+    struct TreeFrame {
+        d3 acc;          // finalLight of the node so far
+        d3 ro, rd;       // the reflected ray, traced after the refracted subtree has returned
+        double k_pending, k_refl;  // coefficient of the subtree being traced / of the reflected subtree
+        int has_refl;
+    };
+    TreeFrame stk[K][kReflect ? kMaxTreeDepth : 1];
+    int dep[K];  // frames on the stack = recursionAmount of the node being evaluated
+#pragma unroll
+    for (int k = 0; k < K; ++k) dep[k] = 0;
+    auto tree_return = [&](int k, d3 v) {  // the current node of pixel k returns v to its caller
+        while (true) {
+            if (dep[k] == 0) { acc[k] = v; alive[k] = false; return; }
+            TreeFrame& f = stk[k][dep[k] - 1];
+            f.acc = f.acc + v * f.k_pending;
+            if (f.has_refl) {  // next: the reflected subtree of the same node
+                f.has_refl = 0; f.k_pending = f.k_refl;
+                o[k] = f.ro; d[k] = f.rd;
+                if (dep[k] < max_depth) return;
+                v = background(d[k]);  // TraceRay(depth >= maxRecursion), RE/Scene.h:132-134
+            } else {
+                v = f.acc;
+                dep[k] -= 1;
+            }
+        }
+    };
 #pragma unroll 1
-    for (int depth = 0; depth < max_depth; ++depth) {
+    for (int depth = 0; kReflect || depth < 1; ++depth) {  // depth = iteration; all lanes are at their primary ray in iteration 0
+        if (kReflect) {
+#pragma unroll
+            for (int k = 0; k < K; ++k)
+                if (alive[k] && dep[k] >= max_depth) tree_return(k, background(d[k]));
+        }
         bool any_alive = false;
 #pragma unroll
         for (int k = 0; k < K; ++k) any_alive = any_alive || alive[k];
@@ -182,12 +218,12 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
         for (int k = 0; k < K; ++k) {
             if (alive[k]) {
                 cnt.sph += (uint32_t)sc.ns; cnt.pl += (uint32_t)sc.np; cnt.tri += (uint32_t)sc.nt;
-                if (depth > 0) cnt.secondary += 1;
+                if (dep[k] > 0) cnt.secondary += 1;
             }
             hitv[k] = alive[k] && h[k].kind != RTE_HIT_NONE;
-            if (alive[k] && !hitv[k]) {
-                acc[k] = acc[k] + background(d[k]) * w[k];
-                alive[k] = false;
+            if (alive[k] && !hitv[k]) {  // miss: sky (RE/Scene.h:137-141)
+                if (kReflect) tree_return(k, background(d[k]));
+                else { acc[k] = acc[k] + background(d[k]) * w[k]; alive[k] = false; }
             }
             Pn[k] = mk(0, 0, 0); ngeo[k] = mk(0, 0, 0);
             mat[k] = sc.nm; report[k] = 0; self[k] = -1; lmask[k] = 0;
@@ -262,9 +298,10 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
                 for (int k = 0; k < K; ++k) {
                     cnt.sph += r[k].sph_tests; cnt.pl += r[k].pl_tests; cnt.tri += r[k].tri_tests;
                     if (sr[k].cast) {
-                        if (r[k].near) {
-                            // triangles (and transparent occluders) are outside march_list's scope
-                            if (lists.n[k] <= kListCap && sc.nt == 0 && !nf) T[k] = march_list(sc, lists.idx[k], lists.n[k], sr[k].o, sr[k].d, sr[k].maxDist, bias);
+                        if (r[k].near || (sc.transparent && r[k].occluded)) {
+                            // triangles are outside march_list's scope; with transparent materials every occluded ray takes the
+                            // literal march (T *= transparency per crossing, RE/Scene.h:68-69) and its list may be incomplete
+                            if (lists.n[k] <= kListCap && sc.nt == 0 && !nf && !sc.transparent) T[k] = march_list(sc, lists.idx[k], lists.n[k], sr[k].o, sr[k].d, sr[k].maxDist, bias);
                             else T[k] = march_exact(sc, s_sph, s_tri, sr[k].o, sr[k].d, sr[k].maxDist, bias, nf, cnt.confirms);
                             cnt.marches += 1;
                         }
@@ -300,8 +337,8 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             const rte_material& M = sc.materials[mat[k]];
-            if (hitv[k]) {
-                const d3 local = ld3(M.color) * diffuseAcc[k] + specAcc[k] * M.specular;
+            const d3 local = ld3(M.color) * diffuseAcc[k] + specAcc[k] * M.specular;
+            if (hitv[k] && !kReflect) {
                 // finalLight += localLight * (1.0 - transparency), transparency == 0 (RE/Scene.h:171-173)
                 acc[k] = acc[k] + (local * (1.0 - 0.0)) * w[k];
             }
@@ -317,23 +354,55 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
                 }
                 if (P.out.light_mask) P.out.light_mask[oi] = lmask[k];
             }
-            // reflection, RE/Scene.h:189-195 (transparency == 0: reflectiveness = material.specular)
-            if (kReflect && hitv[k] && M.specular > bias) {
-                const d3 N = dot(ngeo[k], incoming[k]) < 0.0 ? ngeo[k] : -ngeo[k];
-                const d3 R = normalize(reflect(incoming[k], N));
-                w[k] = w[k] * M.specular;
-                o[k] = Pn[k] + R * bias;
-                d[k] = R;
-            } else {
+            if (!kReflect) {
                 alive[k] = false;
+            } else if (hitv[k]) {
+                // refraction and reflection, RE/Scene.h:161-195
+                const bool frontFace = dot(ngeo[k], incoming[k]) < 0.0;
+                const d3 N = frontFace ? ngeo[k] : -ngeo[k];
+                const double cosTheta = std_max(0.0, dot(N, viewDir[k]));
+                const double etaT = M.refractive_index;
+                const double f0 = pow((etaT - 1.0) / (etaT + 1.0), 2.0);
+                double fresnelAmount = f0 + (1.0 - f0) * pow(1.0 - cosTheta, 5.0);  // Scene::fresnel, RE/Scene.h:26-28
+                const double transparency = std_clamp(M.transparency, 0.0, 1.0);
+                d3 fin = mk(0.0, 0.0, 0.0);
+                if (transparency < 1.0) fin = fin + local * (1.0 - transparency);
+                bool has_t = false;
+                d3 to = mk(0, 0, 0), td = mk(0, 0, 1);
+                double kt = 0.0;
+                if (transparency > 0.0) {
+                    const double eta = frontFace ? (1.0 / etaT) : (etaT / 1.0);
+                    d3 rd = refract(incoming[k], N, eta);
+                    if (length(rd) > bias) {
+                        rd = normalize(rd);
+                        to = Pn[k] + rd * (bias * 1e2); td = rd;
+                        has_t = true;
+                        kt = transparency * (1.0 - fresnelAmount);
+                    } else {
+                        fresnelAmount = 1.0;
+                    }
+                }
+                const double reflectiveness = (transparency > 0.0) ? fresnelAmount : M.specular;
+                const bool has_r = reflectiveness > bias;
+                if (!has_t && !has_r) {
+                    tree_return(k, fin);
+                } else {
+                    TreeFrame f;
+                    f.acc = fin; f.ro = mk(0, 0, 0); f.rd = mk(0, 0, 1); f.k_refl = reflectiveness;
+                    if (has_r) {
+                        const d3 R = normalize(reflect(incoming[k], N));
+                        f.ro = Pn[k] + R * bias; f.rd = R;
+                    }
+                    if (has_t) { f.k_pending = kt; f.has_refl = has_r ? 1 : 0; o[k] = to; d[k] = td; }
+                    else { f.k_pending = reflectiveness; f.has_refl = 0; o[k] = f.ro; d[k] = f.rd; }
+                    stk[k][dep[k]] = f;
+                    dep[k] += 1;
+                }
             }
         }
     }
 #pragma unroll
-    for (int k = 0; k < K; ++k) {
-        if (alive[k]) acc[k] = acc[k] + background(d[k]) * w[k];  // TraceRay(depth >= maxRecursion), RE/Scene.h:132-134
-        result[k] = acc[k];
-    }
+    for (int k = 0; k < K; ++k) result[k] = acc[k];
 }
 
 // ------------------------------------------------------------------------------ RGB8 output

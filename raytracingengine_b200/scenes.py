@@ -219,4 +219,42 @@ def mixed_scene(width, height, focal, n_spheres=200, n_lights=3, seed=4242, mesh
                        model_vertices=verts, model_indices=idx, lights=arrays.lights), cam
 
 
+def glass_scene(width=96, height=72, focal=None, max_lights=2):
+    """Row N1: refraction, Fresnel reflection and coloured transmittance.  A 5-plane room (slightly
+    glossy floor), glass / half-transparent / mirror / diffuse spheres, a half-transparent box model and two lights:
+    every branch of TraceRay (RE/Scene.h:131-198) and computeTransmittance (RE/Scene.h:35-77) is taken."""
+    focal = float(focal if focal is not None else width * 0.75)
+    mats = np.array([
+        _material((1, 1, 1), 32.0, 0.05, 0.0, 1.0),        # 0 floor: faint mirror
+        _material((0.9, 0.3, 0.3)),                          # 1 walls
+        _material((0.3, 0.9, 0.3)),                          # 2
+        _material((1, 1, 1), 128.0, 0.0, 0.9, 1.5),        # 3 glass
+        _material((0.2, 0.6, 1.0), 64.0, 0.0, 0.5, 1.33),  # 4 half-transparent, water-like
+        _material((1, 1, 1), 256.0, 0.8, 0.0, 1.0),        # 5 mirror
+        _material((1.0, 0.8, 0.2)),                          # 6 diffuse
+        _material((0.8, 0.9, 1.0), 16.0, 0.0, 0.7, 1.1),   # 7 box: thin, weakly refracting
+        _material((1, 1, 1), 8.0, 0.0, 1.0, 2.4),          # 8 fully transparent (transparency == 1: no local light)
+    ], dtype=_abi.material_dt)
+    planes = np.zeros(5, dtype=_abi.plane_dt)
+    for i, (p, n, m) in enumerate([((0, -6, 0), (0, 1, 0), 0), ((0, 0, 14), (0, 0, -1), 1), ((-9, 0, 0), (1, 0, 0), 2),
+                                   ((9, 0, 0), (-1, 0, 0), 1), ((0, 9, 0), (0, -1, 0), 2)]):
+        planes[i] = (p, n, m, 0)
+    sph = np.zeros(7, dtype=_abi.sphere_dt)
+    for i, (c, r, m) in enumerate([((-3.0, -3.5, 4.0), 2.5, 3), ((3.5, -4.0, 2.0), 2.0, 4), ((0.5, 1.5, 9.0), 3.0, 5),
+                                   ((-5.5, 2.0, 7.0), 1.5, 6), ((5.0, 3.0, 6.0), 1.25, 8), ((0.0, -4.5, -2.0), 1.5, 3),
+                                   ((-2.5, -3.0, 4.5), 0.75, 6)]):  # the last one sits INSIDE the first glass sphere
+        sph[i] = (tuple(f32(x) for x in c), f32(r), m, 0)
+    verts, faces = box_mesh()
+    idx = fan_triangulate(faces)
+    models = np.zeros(1, dtype=_abi.model_dt)
+    models[0] = (0, len(verts), 0, len(idx), (4.0, 1.0, 1.0), 7, 0)
+    lights = np.zeros(2, dtype=_abi.light_dt)
+    lights[0] = ((-4.0, 7.0, -3.0), (1, 1, 1), 120.0)
+    lights[1] = ((5.0, 6.0, 0.0), (1.0, 0.9, 0.8), 80.0)
+    cam = Camera((0.0, 0.0, -16.0), focal, int(width), int(height), 0.0, 200.0)
+    cam.antiAliasingAmount = 1
+    return SceneArrays(materials=mats, spheres=sph, planes=planes, models=models, model_vertices=verts, model_indices=idx,
+                       lights=lights[:max_lights]), cam
+
+
 CONFIGS = {"c1": config1, "c2": config2, "c3": config3, "c4": config4, "c5": config5}

@@ -26,6 +26,8 @@ CASES = {
     "c4_blob_96x54": lambda: scenes.config4("blob", scale=0.05),
     "c4_box_specular_96x54": lambda: scenes.config4("box", scale=0.05, specular=True),
     "c5_4096_60x33": lambda: scenes.config5(scale=1 / 128),
+    "mixed_96x54": lambda: scenes.mixed_scene(96, 54, 48.0),
+    "glass_64x48": lambda: scenes.glass_scene(64, 48),   # row N1: refraction / Fresnel / transmittance
 }
 
 
@@ -39,7 +41,10 @@ def kat_scene():
 def main():
     ref = pyoracle.load_ref()
     assert ref is not None and ref.kind == "reference", "build oracle/_ref first (needs /root/reference)"
+    only_missing = "--missing" in sys.argv
     for name, make in CASES.items():
+        if only_missing and os.path.exists(os.path.join(HERE, name + ".npz")):
+            continue
         arrays, cam = make()
         r = ref.render(arrays, cam, want_aovs=True)
         rgb = ref.tonemap_all(r["hdr"])
@@ -49,6 +54,8 @@ def main():
                             primary_rays=r["primary_rays"], shadow_rays=r["shadow_rays"])
         print(name, cam.width, cam.height, r["primary_rays"], r["shadow_rays"])
 
+    if only_missing:
+        return
     kat = {}
     cam = Camera((0.0, 0.0, -25.0), 500.0, 1000, 1000, 0.0, 200.0)
     kat["camera"] = {f"{x},{y}": ref.camera_ray(cam, x, y)[1].tolist() for x, y in [(500, 500), (0, 0), (999, 999), (250, 750), (1, 998)]}

@@ -110,6 +110,28 @@ def test_mixed_scene_all_primitive_classes(engine, oracle):
     assert_parity(g, o)
 
 
+def test_glass_scene_refraction_fresnel_transmittance(engine, oracle):
+    """Row N1: transparent materials — refraction rays, Fresnel-weighted reflection, total internal reflection and the
+    transmittance march through partially transparent occluders (RE/Scene.h:35-77,161-195), evaluated on the
+    per-pixel stack in the reference's order.  libm's pow() (Fresnel, Blinn-Phong) is the only inexact step."""
+    arrays, cam = scenes.glass_scene(96, 72)
+    g, o = render_both(engine, oracle, arrays, cam)
+    assert_parity(g, o, exact_hdr=False, hdr_rtol=1e-9)
+    assert g["stats"]["secondary_rays"] > 2 * g["stats"]["primary_rays"]  # ray trees (refraction + reflection)
+    assert g["stats"]["exact_marches"] > 0
+
+
+def test_glass_scene_recursion_limits(engine, port_oracle):
+    arrays, cam = scenes.glass_scene(48, 36)
+    engine.upload(arrays, cam)
+    for md in (1, 2, 5, _abi.MAX_DEPTH):
+        g = engine.render_host(outputs=("hdr64",), max_depth=md)
+        s = engine.stats()
+        o = port_oracle.render(arrays, cam, max_depth=md)
+        np.testing.assert_allclose(g["hdr64"], o["hdr"], rtol=1e-9, atol=1e-14)
+        assert s["secondary_rays"] == o["secondary_rays"] and s["shadow_rays"] == o["shadow_rays"], md
+
+
 def test_max_depth_and_bias_options(engine, port_oracle):
     """max_depth / bias are constants in the reference (RE/Scene.h:24,291): only the port checker takes them."""
     arrays, cam = scenes.config1(96, 96)
@@ -177,10 +199,13 @@ def test_errors(engine):
         engine.render_host(outputs=("hdr",), row0=5, row1=cam.height + 1)
     with pytest.raises(RteError):
         engine.render_host(outputs=("rgb8",))  # rgb8 without an operator
-    bad = scenes.config3(scale=0.05)[0]
-    bad.materials["transparency"][0] = 0.5
     with pytest.raises(RteError):
-        engine.upload(bad, cam)
+        engine.render_host(outputs=("hdr",), max_depth=_abi.MAX_DEPTH + 1)
+    bad = scenes.config3(scale=0.05)[0]
+    bad.materials = bad.materials[:3]  # sphere materials out of range are fine (default Material), NULL arrays are not
+    bad.lights = np.zeros(17, dtype=_abi.light_dt)
+    with pytest.raises(RteError):
+        engine.upload(bad, cam)  # more lights than the light_mask AOV has bits
     engine.upload(arrays, cam)  # the ctx stays usable after argument errors
     assert engine.render_host(outputs=("prim_id",))["prim_id"].size == cam.width * cam.height
 
