@@ -117,9 +117,17 @@ typedef struct rte_camera {
     double focal;
     uint64_t width, height;
     double near_plane, far_plane;
-    int32_t anti_aliasing; /* RE/Math.h:94; only 1 is deterministic */
-    int32_t reserved;
+    int32_t anti_aliasing; /* Camera::antiAliasingAmount, RE/Math.h:94: samples per pixel, 1..RTE_MAX_AA */
+    int32_t jitter_seed;   /* seed of the jitter stream below (upstream seeds from std::random_device, RE/Math.h:109) */
 } rte_camera;
+/* GeneratePixelAt (RE/Scene.h:283-304): the pixel is the mean of anti_aliasing samples; sample 0 is unjittered, sample
+ * s >= 1 adds (jx, jy) in [0,1)^2 to the screen point (RE/Math.h:103-116, where invAA = 1/double(bool) = 1).  Upstream
+ * draws the jitter from a thread-local mt19937 seeded by random_device — not reproducible — so this library defines
+ * a counter-based stream instead (statistically equivalent, identical on every run / GPU count / tile order):
+ *   key = ((uint64)(uint32)jitter_seed << 32) ^ ((uint64)(y*W + x) * 8192 + 2*s + axis),   axis 0 = x, 1 = y
+ *   z = key + 0x9E3779B97F4A7C15; z = (z ^ z>>30) * 0xBF58476D1CE4E5B9; z = (z ^ z>>27) * 0x94D049BB133111EB; z ^= z>>31
+ *   jitter = (z >> 11) * 2^-53 */
+#define RTE_MAX_AA 4096
 
 /* The vectors a reference `Scene` owns (RE/Scene.h:17-23), flattened. */
 typedef struct rte_scene_desc {

@@ -29,7 +29,8 @@ struct Camera {  // RE/Math.h:85-97 (same member names; ctor: position, focal, w
     Vec3 position, forward{0, 0, 1};
     std::size_t width, height;
     double focal, farPlaneDistance, nearPlaneDistance;
-    std::size_t antiAliasingAmount = 32;  // only 1 is reproducible upstream; the library accepts 1
+    std::size_t antiAliasingAmount = 32;  // RE/Math.h:94; samples 1.. are jittered from the counter-based stream of rte.h
+    std::int32_t jitterSeed = 0;          // (upstream: std::random_device)
     explicit Camera(const Vec3& pos, double f = 1.0, std::size_t w = 800, std::size_t h = 600, double nearP = 1.0, double farP = 1000.0)
         : position(pos), width(w), height(h), focal(f), farPlaneDistance(farP), nearPlaneDistance(nearP) {}
 };
@@ -147,6 +148,7 @@ private:
         c.focal = camera.focal; c.width = camera.width; c.height = camera.height;
         c.near_plane = camera.nearPlaneDistance; c.far_plane = camera.farPlaneDistance;
         c.anti_aliasing = (std::int32_t)camera.antiAliasingAmount;
+        c.jitter_seed = camera.jitterSeed;
         check(rte_set_camera(ctx_, &c), ctx_);
     }
     rte_ctx* ctx_ = nullptr;

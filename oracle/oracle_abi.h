@@ -61,7 +61,9 @@ typedef struct orc_outputs {
 /* "reference" or "port" */
 const char* ORC_FN(kind)(void);
 
-/* Scene::RenderImage / GeneratePixelAt over the selected rows, camera.anti_aliasing forced to 1. */
+/* Scene::RenderImage / GeneratePixelAt over the selected rows.  camera.anti_aliasing > 1: the port uses the counter-based
+ * jitter stream of include/rte.h (bit-reproducible); the reference build uses upstream's own mt19937/random_device
+ * jitter (RE/Math.h:103-116), so its multi-sample images are a STATISTICAL reference only. */
 int ORC_FN(render)(const rte_scene_desc* scene, const rte_camera* camera, const orc_opts* opts,
                    orc_outputs* out);
 

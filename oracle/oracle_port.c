@@ -61,17 +61,34 @@ static v3 refract(v3 self, v3 normal, double eta) {                             
 typedef struct { v3 o, d; } ray_t;                                                         /* Rayon, :78-83 */
 static inline v3 point_at(ray_t r, double t) { return add(r.o, mul(r.d, t)); }            /* :82 */
 
-/* Camera::getRay(px,py,aa=false), RE/Math.h:99-121 (jitter is +0.0 when aa is false) */
-static ray_t camera_ray(const rte_camera* c, uint64_t px, uint64_t py) {
+/* the counter-based jitter stream include/rte.h defines for rte_camera (upstream: mt19937 seeded by random_device) */
+static double jitter01(uint32_t seed, uint64_t pixel, int s, int axis) {
+    uint64_t z = (((uint64_t)seed) << 32) ^ (pixel * 8192ull + (uint64_t)(2 * s + axis));
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (double)(z >> 11) * 0x1.0p-53;
+}
+/* Camera::getRay(px,py,aa), RE/Math.h:99-121: sample 0 is unjittered (jitter = 0.0); sample >= 1 adds [0,1)^2 * invAA */
+static ray_t camera_ray_sample(const rte_camera* c, uint64_t px, uint64_t py, int sample) {
     double sx = ((double)px) - (double)c->width / 2.0;
     double sy = (double)c->height / 2.0 - ((double)py);
-    sx += 0.0;
-    sy += 0.0;
+    double jx = 0.0, jy = 0.0;
+    if (sample > 0) {
+        const double invAA = 1.0 / (double)1;  /* 1.0 / static_cast<double>(bool aa), RE/Math.h:106 */
+        const uint64_t pixel = py * c->width + px;
+        jx = jitter01((uint32_t)c->jitter_seed, pixel, sample, 0) * invAA;
+        jy = jitter01((uint32_t)c->jitter_seed, pixel, sample, 1) * invAA;
+    }
+    sx += jx;
+    sy += jy;
     v3 pos = vp(c->position);
     v3 screen = V(sx, sy, pos.z + c->focal);
     ray_t r = {pos, normalize(sub(screen, pos))};
     return r;
 }
+static ray_t camera_ray(const rte_camera* c, uint64_t px, uint64_t py) { return camera_ray_sample(c, px, py, 0); }
 
 /* ---------------------------------------------------------------- flattened scene ----------- */
 typedef struct { v3 c; double r; int mat; } sph_t;
@@ -378,7 +395,7 @@ static int primary_near_tie(const scene_t* sc, ray_t ray, double best) {
     return second - best <= 1e-5 * fabs(best);
 }
 
-/* Scene::RenderImage / GeneratePixelAt with antiAliasingAmount == 1, RE/Scene.h:283-328 */
+/* Scene::RenderImage / GeneratePixelAt, RE/Scene.h:283-328 (camera.anti_aliasing samples, jitter stream of rte.h) */
 int port_render(const rte_scene_desc* scene, const rte_camera* camera, const orc_opts* opts, orc_outputs* out) {
     if (!scene || !camera || !opts || !out) return RTE_ERR_INVALID;
     scene_t* sc = scene_build(scene);
@@ -390,6 +407,7 @@ int port_render(const rte_scene_desc* scene, const rte_camera* camera, const orc
     const int max_depth = opts->max_depth > 0 ? opts->max_depth : 10;   /* RE/Scene.h:24 */
     const double bias = opts->bias > 0 ? opts->bias : 1e-3;             /* RE/Scene.h:291 */
     const int aov = opts->want_aovs;
+    const int aa = camera->anti_aliasing > 1 ? camera->anti_aliasing : 1;
 #ifdef _OPENMP
     if (opts->threads > 0) omp_set_num_threads(opts->threads);
     out->threads_used = omp_get_max_threads();
@@ -407,10 +425,14 @@ int port_render(const rte_scene_desc* scene, const rte_camera* camera, const orc
         cnt_t c; memset(&c, 0, sizeof(c)); c.count_tests = aov;
         primary_t prim; prim.have = 0;
         const ray_t ray = camera_ray(camera, (uint64_t)x, (uint64_t)y);
-        v3 color = trace(sc, ray, 0, max_depth, bias, &c, aov ? &prim : NULL);
-        /* accumulatedColor(0) += color; /= samples(1), RE/Scene.h:284-301 */
-        v3 acc = add(V(0, 0, 0), color);
-        acc = divs(acc, (double)1);
+        /* GeneratePixelAt, RE/Scene.h:283-304: accumulatedColor(0) += colour of every sample; /= samples */
+        v3 acc = V(0, 0, 0);
+        for (int s = 0; s < aa; ++s) {
+            const ray_t rs = camera_ray_sample(camera, (uint64_t)x, (uint64_t)y, s);
+            v3 color = trace(sc, rs, 0, max_depth, bias, &c, (aov && s == 0) ? &prim : NULL);
+            acc = add(acc, color);
+        }
+        acc = divs(acc, (double)aa);
         if (out->hdr) { out->hdr[3 * idx] = acc.x; out->hdr[3 * idx + 1] = acc.y; out->hdr[3 * idx + 2] = acc.z; }
         if (aov) {
             uint32_t pid = 0xFFFFFFFFu, lm = 0, tm = 0; double depth = INFINITY; v3 n = V(0, 0, 0), alb = background(ray);
@@ -429,7 +451,7 @@ int port_render(const rte_scene_desc* scene, const rte_camera* camera, const orc
         shadow += c.shadow; secondary += c.secondary; sph += c.sph; pl += c.pl; tri += c.tri; queries += c.queries;
     }
     out->render_seconds = now_s() - t0;
-    out->primary_rays = (uint64_t)total; out->shadow_rays = shadow; out->secondary_rays = secondary;
+    out->primary_rays = (uint64_t)total * (uint64_t)aa; out->shadow_rays = shadow; out->secondary_rays = secondary;
     out->sphere_tests = sph; out->plane_tests = pl; out->triangle_tests = tri; out->closest_queries = queries;
     scene_free(sc);
     return RTE_OK;

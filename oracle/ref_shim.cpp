@@ -68,7 +68,7 @@ struct Built {
 Camera to_camera(const rte_camera* c) {
     Camera cam(v3(c->position), c->focal, (size_t)c->width, (size_t)c->height, c->near_plane,
                c->far_plane);
-    cam.antiAliasingAmount = 1;  // deterministic
+    cam.antiAliasingAmount = c->anti_aliasing > 1 ? c->anti_aliasing : 1;  // 1 = deterministic; > 1: upstream's own random jitter
     return cam;
 }
 

@@ -39,6 +39,7 @@ FLAG_EXACT_SHADOWS, FLAG_NO_FILTER, FLAG_GENERAL_KERNEL = 1, 2, 4
 IPC_HANDLE_BYTES = 64  # RTE_IPC_HANDLE_BYTES
 MAX_PEERS = 8          # RTE_MAX_PEERS
 MAX_DEPTH = 24         # RTE_MAX_DEPTH
+MAX_AA = 4096          # RTE_MAX_AA
 
 # --- numpy dtypes (C layout) -------------------------------------------------------------------
 material_dt = np.dtype(  # Material, RE/Shape.h:13-19
@@ -69,7 +70,7 @@ assert hit_dt.itemsize == 64
 class Camera(C.Structure):  # Camera, RE/Math.h:85-97
     _fields_ = [("position", C.c_double * 3), ("focal", C.c_double), ("width", C.c_uint64),
                 ("height", C.c_uint64), ("near_plane", C.c_double), ("far_plane", C.c_double),
-                ("anti_aliasing", C.c_int32), ("reserved", C.c_int32)]
+                ("anti_aliasing", C.c_int32), ("jitter_seed", C.c_int32)]
 
 
 class SceneDesc(C.Structure):  # the vectors of Scene, RE/Scene.h:17-23

@@ -419,8 +419,8 @@ extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
     if (c->width == 0 || c->height == 0 || c->width > (1u << 20) || c->height > (1u << 20))
         return fail(ctx, RTE_ERR_INVALID, "camera size %llux%llu not supported", (unsigned long long)c->width, (unsigned long long)c->height);
     if (!finite3(c->position) || !std::isfinite(c->focal)) return fail(ctx, RTE_ERR_INVALID, "camera is not finite");
-    if (c->anti_aliasing != 1)
-        return fail(ctx, RTE_ERR_LIMIT, "anti_aliasing = %d: only 1 sample per pixel is built (the reference's jitter is non-reproducible, RE/Math.h:103-116)", c->anti_aliasing);
+    if (c->anti_aliasing < 1 || c->anti_aliasing > RTE_MAX_AA)
+        return fail(ctx, RTE_ERR_LIMIT, "anti_aliasing = %d: 1..%d samples per pixel", c->anti_aliasing, RTE_MAX_AA);
     ctx->cam_host = *c;
     DevCamera& dc = ctx->cam;
     dc.pos[0] = c->position[0]; dc.pos[1] = c->position[1]; dc.pos[2] = c->position[2];
@@ -428,6 +428,7 @@ extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
     dc.half_w = (double)c->width / 2.0;   // RE/Math.h:100
     dc.half_h = (double)c->height / 2.0;  // RE/Math.h:101
     dc.width = (int)c->width; dc.height = (int)c->height;
+    dc.aa = c->anti_aliasing; dc.jitter_seed = (uint32_t)c->jitter_seed;
     ctx->has_camera = true;
     ctx->views_dirty = true;
     return RTE_OK;

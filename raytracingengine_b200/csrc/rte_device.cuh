@@ -65,6 +65,8 @@ struct DevCamera {  // Camera, RE/Math.h:85-97
     double focal;
     double half_w, half_h;  // double(width)/2.0, double(height)/2.0 (RE/Math.h:100-101)
     int32_t width, height;
+    int32_t aa;             // Camera::antiAliasingAmount
+    uint32_t jitter_seed;   // rte_camera.jitter_seed
 };
 
 // ------------------------------------------------------------------------------ Vec3 (FP64)
@@ -104,10 +106,28 @@ __device__ __forceinline__ d3 refract(d3 self, d3 normal, double eta) {
     return I * eta - N * (eta * cosi + sqrt(k));
 }
 
-// Camera::getRay(px, py, false), RE/Math.h:99-121
-__device__ __forceinline__ d3 camera_dir(const DevCamera& c, int px, int py) {
+// the jitter stream of rte.h (rte_camera): sample s >= 1 of pixel y*W + x, axis 0 / 1
+__device__ __forceinline__ double jitter01(uint32_t seed, int64_t pixel, int s, int axis) {
+    unsigned long long z = (((unsigned long long)seed) << 32) ^ ((unsigned long long)pixel * 8192ull + (unsigned long long)(2 * s + axis));
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (double)(z >> 11) * 0x1.0p-53;
+}
+// Camera::getRay(px, py, aa), RE/Math.h:99-121; sample 0 is the unjittered ray (jitter = 0.0, RE/Scene.h:292)
+__device__ __forceinline__ d3 camera_dir(const DevCamera& c, int px, int py, int sample = 0) {
     double sx = (double)px - c.half_w;
     double sy = c.half_h - (double)py;
+    double jx = 0.0, jy = 0.0;
+    if (sample > 0) {
+        const double invAA = 1.0 / 1.0;  // 1.0 / static_cast<double>(bool aa), RE/Math.h:106
+        const int64_t pixel = (int64_t)py * c.width + px;
+        jx = jitter01(c.jitter_seed, pixel, sample, 0) * invAA;
+        jy = jitter01(c.jitter_seed, pixel, sample, 1) * invAA;
+    }
+    sx += jx;
+    sy += jy;
     const d3 screen = mk(sx, sy, c.pos[2] + c.focal);
     return normalize(screen - ld3(c.pos));
 }

@@ -136,7 +136,7 @@ struct PixelCounters {
 template <int K, bool kReflect>
 __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const ulonglong2* s_tviews,
                                              const float4* s_sph, const float4* s_tri, const int (&px)[K], const int (&py)[K], const bool (&inb)[K],
-                                             const int64_t (&out_idx)[K], PixelCounters& cnt, d3 (&result)[K]) {
+                                             const int64_t (&out_idx)[K], int sample, PixelCounters& cnt, d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     d3 o[K], d[K], acc[K];
     double w[K];
@@ -144,7 +144,7 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         o[k] = cam_o;
-        d[k] = camera_dir(P.cam, px[k], py[k]);
+        d[k] = camera_dir(P.cam, px[k], py[k], sample);
         acc[k] = mk(0.0, 0.0, 0.0);
         w[k] = 1.0;
         alive[k] = inb[k];
@@ -342,7 +342,7 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
                 // finalLight += localLight * (1.0 - transparency), transparency == 0 (RE/Scene.h:171-173)
                 acc[k] = acc[k] + (local * (1.0 - 0.0)) * w[k];
             }
-            if (depth == 0 && inb[k]) {  // AOVs of the primary hit
+            if (depth == 0 && sample == 0 && inb[k]) {  // AOVs of the primary hit (of the unjittered sample)
                 const int64_t oi = out_idx[k];
                 if (P.out.prim_id) P.out.prim_id[oi] = hitv[k] ? ((h[k].kind << 30) | report[k]) : kMiss;
                 if (P.out.depth) P.out.depth[oi] = hitv[k] ? (float)h[k].t : INFINITY;
@@ -481,7 +481,21 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
         }
         PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         d3 c[K];
-        trace_pixels<K, kReflect>(P, sc, s_views, s_tviews, s_sph, s_tri, px, py, inb, out_idx, cnt, c);
+        {   // GeneratePixelAt, RE/Scene.h:283-304: accumulatedColor += sample; accumulatedColor /= samples
+            const int aa = P.cam.aa;
+            d3 sum[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) sum[k] = mk(0.0, 0.0, 0.0);
+#pragma unroll 1
+            for (int s = 0; s < aa; ++s) {
+                trace_pixels<K, kReflect>(P, sc, s_views, s_tviews, s_sph, s_tri, px, py, inb, out_idx, s, cnt, c);
+#pragma unroll
+                for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
+            }
+#pragma unroll
+            for (int k = 0; k < K; ++k) c[k] = sum[k] / (double)aa;
+            n_in *= (uint32_t)aa;  // primary rays
+        }
         const bool words_ok = P.rgb8_words && (W & 3) == 0 && tx * kTileW + kTileW <= W;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -570,7 +584,7 @@ struct ViewsStream {
 template <int K, bool kTris, class Views>
 __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const ulonglong2* s_tviews,
                                                 const float4* s_sph, const float4* s_tri, const int (&pxs)[K], const int (&pys)[K],
-                                                const bool (&inb)[K], PixelCounters& cnt, d3 (&result)[K]) {
+                                                const bool (&inb)[K], int sample, PixelCounters& cnt, d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     const double bias = P.bias;
     const int nl = sc.nl, np = sc.np, ns = sc.ns, nt = kTris ? sc.nt : 0;
@@ -580,7 +594,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
     Hit h[K];
 #pragma unroll 1
     for (int k = 0; k < K; ++k) {
-        dir[k] = camera_dir(P.cam, pxs[k], pys[k]);
+        dir[k] = camera_dir(P.cam, pxs[k], pys[k], sample);
         alive[k] = inb[k];
         found[k] = false;
         h[k].t = 0.0; h[k].kind = RTE_HIT_NONE; h[k].idx = 0;
@@ -824,8 +838,22 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         }
         PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         d3 c[K];
-        if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_sph, s_tri, px, py, inb, cnt, c);
-        else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_sph, s_tri, px, py, inb, cnt, c);
+        {   // GeneratePixelAt, RE/Scene.h:283-304: accumulatedColor += sample; accumulatedColor /= samples
+            const int aa = P.cam.aa;
+            d3 sum[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) sum[k] = mk(0.0, 0.0, 0.0);
+#pragma unroll 1
+            for (int s = 0; s < aa; ++s) {
+                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_sph, s_tri, px, py, inb, s, cnt, c);
+                else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_sph, s_tri, px, py, inb, s, cnt, c);
+#pragma unroll 1
+                for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
+            }
+#pragma unroll 1
+            for (int k = 0; k < K; ++k) c[k] = sum[k] / (double)aa;
+            n_in *= (uint32_t)aa;  // primary rays
+        }
         const bool words_ok = P.rgb8_words && (W & 3) == 0 && tx * kTileW + kTileW <= W;
         const bool want_rgb8 = P.tonemap_op >= 0 && (P.out.rgb8 || P.n_peers > 0);
 #pragma unroll 1

@@ -92,6 +92,7 @@ class Camera:
     nearPlaneDistance: float = 1.0
     farPlaneDistance: float = 1000.0
     antiAliasingAmount: int = 32  # RE/Math.h:94
+    jitterSeed: int = 0           # rte_camera.jitter_seed (upstream seeds its jitter from std::random_device)
 
     def to_c(self) -> _abi.Camera:
         c = _abi.Camera()
@@ -101,6 +102,7 @@ class Camera:
         c.width, c.height = int(self.width), int(self.height)
         c.near_plane, c.far_plane = float(self.nearPlaneDistance), float(self.farPlaneDistance)
         c.anti_aliasing = int(self.antiAliasingAmount)
+        c.jitter_seed = int(self.jitterSeed)
         return c
 
 

@@ -132,6 +132,37 @@ def test_glass_scene_recursion_limits(engine, port_oracle):
         assert s["secondary_rays"] == o["secondary_rays"] and s["shadow_rays"] == o["shadow_rays"], md
 
 
+@pytest.mark.parametrize("cfg", ["c3_fast", "c3_general", "c5_streamed", "c4_mesh", "glass"])
+def test_multisample_antialiasing(engine, port_oracle, cfg):
+    """Row N2: camera.antiAliasingAmount samples per pixel (sample 0 unjittered, the others jittered by the
+    counter-based stream of rte.h) — the same samples, summed and divided like GeneratePixelAt, as the port oracle."""
+    if cfg == "c5_streamed":
+        arrays, cam = scenes.config5(scale=1 / 48)
+    elif cfg == "c4_mesh":
+        arrays, cam = scenes.config4("blob", scale=0.06)
+    elif cfg == "glass":
+        arrays, cam = scenes.glass_scene(40, 30)
+    else:
+        arrays, cam = scenes.config3(scale=0.05)
+    cam.antiAliasingAmount, cam.jitterSeed = 5, 2026
+    engine.upload(arrays, cam)
+    outs = ("hdr64", "prim_id") if cfg in ("c3_general", "glass") else ("hdr64",)
+    g = engine.render_host(outputs=outs)
+    s = engine.stats()
+    o = port_oracle.render(arrays, cam, want_aovs=True)
+    if cfg == "glass":
+        np.testing.assert_allclose(g["hdr64"], o["hdr"], rtol=1e-9, atol=1e-14)
+    else:
+        assert np.array_equal(g["hdr64"], o["hdr"]), f"max |dHDR| = {np.abs(g['hdr64'] - o['hdr']).max()}"
+    if "prim_id" in g:
+        assert np.array_equal(g["prim_id"], o["prim_id"])  # AOVs describe the unjittered sample
+    assert s["primary_rays"] == 5 * cam.width * cam.height == o["primary_rays"]
+    assert s["shadow_rays"] == o["shadow_rays"]
+    cam.jitterSeed = 2027
+    engine.upload(arrays, cam)
+    assert not np.array_equal(engine.render_host(outputs=("hdr64",))["hdr64"], g["hdr64"])
+
+
 def test_max_depth_and_bias_options(engine, port_oracle):
     """max_depth / bias are constants in the reference (RE/Scene.h:24,291): only the port checker takes them."""
     arrays, cam = scenes.config1(96, 96)

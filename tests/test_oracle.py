@@ -139,3 +139,58 @@ def test_shadow_ray_count_definition(port_oracle):
     cast = (r["light_mask"] >> 16) & 0xFFFF
     assert int(np.bitwise_count(cast).sum()) == r["shadow_rays"]
     assert r["primary_rays"] == cam.width * cam.height and r["secondary_rays"] == 0
+
+
+def _jitter01(seed, pixel, s, axis):
+    """The jitter stream include/rte.h defines for rte_camera, restated in Python integers."""
+    M = (1 << 64) - 1
+    z = ((seed & 0xFFFFFFFF) << 32) ^ ((pixel * 8192 + 2 * s + axis) & M)
+    z = (z + 0x9E3779B97F4A7C15) & M
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & M
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & M
+    z ^= z >> 31
+    return (z >> 11) * 2.0 ** -53
+
+
+def test_multisample_jitter_stream(port_oracle):
+    """Row N2: anti_aliasing = n renders the mean of n samples, sample 0 unjittered, samples 1.. jittered by the
+    counter-based stream of rte.h.  A sky-only scene makes the pixel a closed form of the ray directions."""
+    arrays = scenes.SceneArrays()
+    cam = scenes.Camera((0.0, 0.0, -25.0), 40.0, 8, 6, 0.0, 200.0)
+    cam.antiAliasingAmount, cam.jitterSeed = 3, 77
+    got = port_oracle.render(arrays, cam)
+    assert got["primary_rays"] == 3 * 8 * 6
+    want = np.zeros((6, 8, 3))
+    for y in range(6):
+        for x in range(8):
+            acc = np.zeros(3)
+            for s in range(3):
+                jx = _jitter01(77, y * 8 + x, s, 0) if s else 0.0
+                jy = _jitter01(77, y * 8 + x, s, 1) if s else 0.0
+                d = np.array([x - 4.0 + jx, 3.0 - y + jy, 40.0])
+                t = 0.5 * (d[1] / np.sqrt(d @ d) + 1.0)
+                acc = acc + (np.array([1.0, 1.0, 1.0]) * (1.0 - t) + np.array([0.5, 0.7, 1.0]) * t)
+            want[y, x] = acc / 3.0
+    np.testing.assert_allclose(got["hdr"].reshape(6, 8, 3), want, rtol=1e-14)
+    cam.jitterSeed = 78
+    assert not np.array_equal(port_oracle.render(arrays, cam)["hdr"], got["hdr"])
+    cam.antiAliasingAmount = 1
+    one = port_oracle.render(arrays, cam)["hdr"]
+    cam.jitterSeed = 77
+    assert np.array_equal(port_oracle.render(arrays, cam)["hdr"], one)  # a single sample never reads the stream
+
+
+def test_multisample_is_statistically_the_reference(port_oracle, ref_oracle):
+    """The reference's own 16-sample render (mt19937 seeded by random_device: different jitter on every run) and the
+    port's 16-sample render with the counter-based stream estimate the same image: their difference is sampling
+    noise — far smaller than the difference to the 1-sample image, and unbiased."""
+    arrays, cam = scenes.config3(scale=0.03)
+    cam.antiAliasingAmount = 16
+    a = ref_oracle.render(arrays, cam)["hdr"]
+    b = port_oracle.render(arrays, cam)["hdr"]
+    cam.antiAliasingAmount = 1
+    one = port_oracle.render(arrays, cam)["hdr"]
+    noise = np.abs(a - b).mean()
+    shift = np.abs(b - one).mean()   # the jitter is one-sided ([0,1)^2): the multi-sample image is shifted by half a pixel
+    assert noise < 0.5 * shift, (noise, shift)
+    assert abs((a - b).mean()) < 0.1 * shift
