@@ -307,6 +307,9 @@ int rte_free_host(void* host);
 /* writePPM(filename, pixels, width, height), RE/Image.cpp:11-31: "P6\n<W> <H>\n255\n" + RGB
  * bytes, one fwrite from the (pinned) host buffer. Needs no device. */
 int rte_write_ppm(const char* filename, const uint8_t* rgb8, uint64_t width, uint64_t height);
+/* What main() gets from `ffmpeg -i x.ppm x.png` + `del x.ppm` (RE/RaytracingEngine.cpp:317-327): the same pixels as an
+ * 8-bit RGB PNG (stored deflate blocks; no external tool).  Needs no GPU. */
+int rte_write_png(const char* filename, const uint8_t* rgb8, uint64_t width, uint64_t height);
 
 #ifdef __cplusplus
 }

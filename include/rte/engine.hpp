@@ -193,4 +193,9 @@ inline void writePPM(const std::string& filename, const std::vector<Color>& pixe
     check(rte_write_ppm(filename.c_str(), reinterpret_cast<const std::uint8_t*>(pixels.data()), width, height));
 }
 
+// the .png main() gets from ffmpeg + del (RE/RaytracingEngine.cpp:317-327), written directly
+inline void writePNG(const std::string& filename, const std::vector<Color>& pixels, std::size_t width, std::size_t height) {
+    check(rte_write_png(filename.c_str(), reinterpret_cast<const std::uint8_t*>(pixels.data()), width, height));
+}
+
 }  // namespace rte_host

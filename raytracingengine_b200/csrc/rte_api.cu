@@ -790,3 +790,92 @@ extern "C" int rte_write_ppm(const char* filename, const uint8_t* rgb8, uint64_t
     if (!ok) return fail(nullptr, RTE_ERR_IO, "Error occurred while writing to file");
     return RTE_OK;
 }
+
+// Row N4: the reference shells out to `ffmpeg` to turn every .ppm into a .png and to `del` to remove the
+// .ppm (RE/RaytracingEngine.cpp:317-327, Windows only).  Here the PNG is written directly: 8-bit RGB, filter 0 on every
+// scanline, zlib stream of stored (uncompressed) deflate blocks — self-contained, no zlib, no subprocess.
+namespace {
+struct PngOut {
+    FILE* f;
+    bool ok = true;
+    uint32_t crc = 0;
+    static uint32_t crc_step(uint32_t c, const uint8_t* p, size_t n) {
+        static uint32_t table[256];
+        static bool init = false;
+        if (!init) {
+            for (uint32_t i = 0; i < 256; ++i) {
+                uint32_t v = i;
+                for (int k = 0; k < 8; ++k) v = (v & 1u) ? 0xEDB88320u ^ (v >> 1) : v >> 1;
+                table[i] = v;
+            }
+            init = true;
+        }
+        for (size_t i = 0; i < n; ++i) c = table[(c ^ p[i]) & 0xFFu] ^ (c >> 8);
+        return c;
+    }
+    void raw(const void* p, size_t n) { ok = ok && (n == 0 || std::fwrite(p, 1, n, f) == n); }
+    void be32(uint32_t v) { const uint8_t b[4] = {(uint8_t)(v >> 24), (uint8_t)(v >> 16), (uint8_t)(v >> 8), (uint8_t)v}; raw(b, 4); }
+    void chunk_begin(const char* type, uint32_t len) { be32(len); crc = 0xFFFFFFFFu; data(type, 4); }
+    void data(const void* p, size_t n) { crc = crc_step(crc, (const uint8_t*)p, n); raw(p, n); }
+    void chunk_end() { be32(crc ^ 0xFFFFFFFFu); }
+};
+}  // namespace
+
+extern "C" int rte_write_png(const char* filename, const uint8_t* rgb8, uint64_t width, uint64_t height) {
+    if (!filename || !rgb8) return fail(nullptr, RTE_ERR_INVALID, "rte_write_png: NULL argument");
+    if (width == 0 || height == 0 || width > 0x7FFFFFFFull / 4 || height > 0x7FFFFFFFull)
+        return fail(nullptr, RTE_ERR_INVALID, "rte_write_png: %llux%llu is not a PNG size", (unsigned long long)width, (unsigned long long)height);
+    const uint64_t row = 1 + 3 * width, total = row * height;       // filter byte + RGB per scanline
+    const uint64_t n_blocks = (total + 65534) / 65535;
+    const uint64_t idat = 2 + total + 5 * n_blocks + 4;              // zlib header, stored blocks, adler32
+    if (idat > 0x7FFFFFFFull) return fail(nullptr, RTE_ERR_LIMIT, "rte_write_png: image too large for one IDAT chunk");
+    FILE* f = std::fopen(filename, "wb");
+    if (!f) return fail(nullptr, RTE_ERR_IO, "Could not open file for writing");
+    PngOut o{f};
+    static const uint8_t sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+    o.raw(sig, 8);
+    o.chunk_begin("IHDR", 13);
+    {
+        const uint8_t h[13] = {(uint8_t)(width >> 24), (uint8_t)(width >> 16), (uint8_t)(width >> 8), (uint8_t)width,
+                               (uint8_t)(height >> 24), (uint8_t)(height >> 16), (uint8_t)(height >> 8), (uint8_t)height,
+                               8, 2, 0, 0, 0};  // 8 bits, colour type 2 (RGB), deflate, adaptive filtering, no interlace
+        o.data(h, 13);
+    }
+    o.chunk_end();
+    o.chunk_begin("IDAT", (uint32_t)idat);
+    {
+        const uint8_t zh[2] = {0x78, 0x01};
+        o.data(zh, 2);
+        std::vector<uint8_t> line((size_t)row);
+        uint32_t a = 1, b = 0;  // adler32 of the uncompressed stream
+        uint64_t done = 0;      // bytes of the stream emitted so far
+        uint32_t left_in_block = 0;
+        for (uint64_t y = 0; y < height; ++y) {
+            line[0] = 0;
+            std::memcpy(line.data() + 1, rgb8 + (size_t)(3 * width * y), (size_t)(3 * width));
+            for (size_t i = 0; i < line.size(); ++i) { a += line[i]; if (a >= 65521u) a -= 65521u; b += a; if (b >= 65521u) b -= 65521u; }
+            size_t off = 0;
+            while (off < line.size()) {
+                if (left_in_block == 0) {
+                    const uint64_t remain = total - done;
+                    const uint32_t len = (uint32_t)(remain < 65535 ? remain : 65535);
+                    const uint8_t bh[5] = {(uint8_t)(remain <= 65535 ? 1 : 0), (uint8_t)len, (uint8_t)(len >> 8), (uint8_t)~len, (uint8_t)(~len >> 8)};
+                    o.data(bh, 5);
+                    left_in_block = len;
+                }
+                const size_t n = std::min<size_t>(line.size() - off, left_in_block);
+                o.data(line.data() + off, n);
+                off += n; done += n; left_in_block -= (uint32_t)n;
+            }
+        }
+        const uint32_t adler = (b << 16) | a;
+        const uint8_t ad[4] = {(uint8_t)(adler >> 24), (uint8_t)(adler >> 16), (uint8_t)(adler >> 8), (uint8_t)adler};
+        o.data(ad, 4);
+    }
+    o.chunk_end();
+    o.chunk_begin("IEND", 0);
+    o.chunk_end();
+    const bool ok = (std::fclose(f) == 0) && o.ok;
+    if (!ok) return fail(nullptr, RTE_ERR_IO, "Error occurred while writing to file");
+    return RTE_OK;
+}

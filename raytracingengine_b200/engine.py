@@ -23,7 +23,7 @@ SYMBOLS = (
     "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats",
     "rte_tonemap", "rte_tonemap_host", "rte_tonemap_auto_white", "rte_max_luminance", "rte_max_luminance_device", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
     "rte_malloc", "rte_free", "rte_memcpy_d2h", "rte_memcpy_h2d", "rte_malloc_host", "rte_free_host",
-    "rte_write_ppm", "rte_set_rgb8_peers", "rte_ipc_export", "rte_ipc_open", "rte_ipc_close",
+    "rte_write_ppm", "rte_write_png", "rte_set_rgb8_peers", "rte_ipc_export", "rte_ipc_open", "rte_ipc_close",
 )
 
 _lib = None
@@ -79,6 +79,7 @@ def load_library() -> C.CDLL:
     lib.rte_malloc_host.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     lib.rte_free_host.argtypes = [C.c_void_p]
     lib.rte_write_ppm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint64]
+    lib.rte_write_png.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint64]
     _lib = lib
     return lib
 
@@ -96,6 +97,15 @@ def write_ppm(path: str, rgb8: np.ndarray, width: int, height: int) -> None:
     if a.size != width * height * 3:
         raise ValueError("rgb8 must hold width*height RGB triplets")
     _check(lib, lib.rte_write_ppm(os.fsencode(path), C.c_void_p(a.ctypes.data), width, height))
+
+
+def write_png(path: str, rgb8: np.ndarray, width: int, height: int) -> None:
+    """The .png main() obtains through ffmpeg (RE/RaytracingEngine.cpp:317-327), written directly (needs no device)."""
+    lib = load_library()
+    a = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    if a.size != width * height * 3:
+        raise ValueError("rgb8 must hold width*height RGB triplets")
+    _check(lib, lib.rte_write_png(os.fsencode(path), C.c_void_p(a.ctypes.data), width, height))
 
 
 class PinnedBuffer:

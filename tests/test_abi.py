@@ -107,3 +107,32 @@ def test_product_package_never_touches_the_oracle():
                 assert "pyoracle" not in src and "oracle_port" not in src and "liboracle" not in src and "libref_oracle" not in src, f
     libs = subprocess.run(["ldd", LIB_PATH], capture_output=True, text=True).stdout
     assert "oracle" not in libs
+
+
+def test_write_png_decodes_to_the_same_pixels(tmp_path):
+    """rte_write_png (row N4: what main() gets from ffmpeg): a valid PNG — signature, IHDR, one IDAT whose zlib stream
+    inflates to filter-0 scanlines of the input pixels, IEND, all CRCs right.  Large enough for several stored blocks."""
+    import struct
+    import zlib
+    from raytracingengine_b200.engine import RteError, write_png
+    W, H = 301, 97  # 88 KB of scanlines: two 65535-byte stored blocks
+    rgb = np.random.default_rng(3).integers(0, 256, (H, W, 3), dtype=np.uint8)
+    path = tmp_path / "a.png"
+    write_png(str(path), rgb, W, H)
+    raw = path.read_bytes()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, chunks = 8, []
+    while pos < len(raw):
+        (n,), typ = struct.unpack(">I", raw[pos:pos + 4]), raw[pos + 4:pos + 8]
+        body = raw[pos + 8:pos + 8 + n]
+        (crc,) = struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])
+        assert zlib.crc32(typ + body) == crc, typ
+        chunks.append((typ, body))
+        pos += 12 + n
+    assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    assert struct.unpack(">IIBBBBB", chunks[0][1]) == (W, H, 8, 2, 0, 0, 0)
+    lines = np.frombuffer(zlib.decompress(chunks[1][1]), dtype=np.uint8).reshape(H, 1 + 3 * W)
+    assert not lines[:, 0].any()
+    assert np.array_equal(lines[:, 1:].reshape(H, W, 3), rgb)
+    with pytest.raises(RteError):
+        write_png(str(tmp_path / "no_such_dir" / "x.png"), rgb, W, H)
