@@ -440,8 +440,8 @@ def run_gpu(args) -> None:
                      "peak_source": "FFMA micro-benchmark in this process (rte_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
                      "nominal_peak_at_sampled_clock": round(nominal_tf, 2), "ffma2_peak": round(fp32x2_peak_tf, 3),
                      "algorithmic_flop_per_launch": flops / world, "kernel_ms": round(kern_ms, 4),
-                     # the view filter runs 4 FMA-pipe lane-ops (8 flop) per sphere test it really executes: the <= 1 companion of `frac`
-                     "executed_frac": round(8.0 * sph_exec / world / (kern_ms * 1e-3) / 1e12 / fp32_peak_tf, 4), "sphere_tests_executed": sph_exec,
+                     # the view filter runs 3 FMA-pipe lane-ops (6 flop) per sphere test it really executes: the <= 1 companion of `frac`
+                     "executed_frac": round(6.0 * sph_exec / world / (kern_ms * 1e-3) / 1e12 / fp32_peak_tf, 4), "sphere_tests_executed": sph_exec,
                      "tests": {"sphere": sph_t, "plane": pl_t, "triangle": tri_t}, "fp64_confirms": confirms, "exact_marches": marches},
         "roofline_tonemap": {"bound": "hbm", "kernel": "rte::tonemap_kernel<all 7 operators>", "achieved": round(n_px * 33 / (tm_med * 1e-3) / 1e9, 1),
                              "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(n_px * 33 / (tm_med * 1e-3) / 1e9 / pk["hbm_gbs"], 4),

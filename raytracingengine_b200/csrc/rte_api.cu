@@ -44,7 +44,7 @@ struct rte_ctx {
     DevScene sc{};
     DevCamera cam{};
     rte_camera cam_host{};
-    DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views, b_tviews;
+    DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views, b_tviews, b_views_cold, b_tviews_cold;
     bool views_dirty = true;
     double views_bias = -1.0;
 
@@ -221,7 +221,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
-                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -382,6 +382,8 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     const int nt_pad32 = (nt + 31) & ~31;
     if ((rc = reserve(ctx, ctx->b_views, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_tviews, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
+    if ((rc = reserve(ctx, ctx->b_views_cold, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
+    if ((rc = reserve(ctx, ctx->b_tviews_cold, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
     if ((rc = upload(ctx, ctx->b_sph32, sph32)) || (rc = upload(ctx, ctx->b_sph64, sph64)) || (rc = upload(ctx, ctx->b_sphmat, sphmat)) ||
         (rc = upload(ctx, ctx->b_planes, planes)) || (rc = upload(ctx, ctx->b_tri32, tri32)) || (rc = upload(ctx, ctx->b_tri64, tri64)) ||
         (rc = upload(ctx, ctx->b_triinfo, triinfo)) || (rc = upload(ctx, ctx->b_mats, mats)) || (rc = upload(ctx, ctx->b_lights, lights)))
@@ -392,6 +394,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     sc.sph32 = (const float4*)ctx->b_sph32.p; sc.tri32 = (const float4*)ctx->b_tri32.p;
     sc.views = ns > 0 ? (const float*)ctx->b_views.p : nullptr;
     sc.tri_views = nt > 0 ? (const float*)ctx->b_tviews.p : nullptr;
+    sc.views_cold = (const float*)ctx->b_views_cold.p; sc.tri_views_cold = (const float*)ctx->b_tviews_cold.p;
     sc.reflective = 0; sc.nt_pad32 = nt_pad32;
     sc.transparent = 0;
     for (int64_t i = 0; i < d->n_materials; ++i) {  // (the default Material appended at index nm is opaque and diffuse)

@@ -41,6 +41,8 @@ struct DevScene {
     int32_t reflective;   // some material has specular > 0: reflection rays (generic closest-hit) will be traced
     int32_t nt_pad32;     // triangles padded to a multiple of 32 (one candidate mask per 32 bounding spheres)
     const float* tri_views;  // (1+nl) per-origin views of the triangles' bounding spheres, same format as `views`; may be NULL
+    const float* views_cold;      // per view and sphere {f = C - O, ng}: read from global memory when a candidate is resolved
+    const float* tri_views_cold;  // same for the triangles' bounding spheres
     const float4* tri32;  // 3 x float4 per triangle: {a0,_}, {e1,_}, {e2,_}; padded to a multiple of 2
     int32_t ns, ns_pad, nt, nt_pad;
     // FP64 exact arrays

@@ -98,15 +98,21 @@ __device__ __forceinline__ void tma_chunks(unsigned char* dst, const void* src, 
 }
 
 // Stage the filter arrays into dynamic shared memory with TMA bulk copies.  Called by every thread of the CTA.
-__device__ __forceinline__ void stage_scene(const DevScene& sc, const SmemPlan& pl, unsigned char* dyn, uint64_t* bar,
-                                            const ulonglong2*& s_views, const ulonglong2*& s_tviews, const float4*& s_sph, const float4*& s_tri) {
+struct StagedScene {
+    const ulonglong2 *views, *tviews;   // hot views (shared memory)
+    const float *cold, *tcold;          // cold views: global memory (measured: staging them too does not pay, not even for tiny scenes)
+    const float4 *sph, *tri;            // generic filter arrays: shared or global
+};
+__device__ __forceinline__ void stage_scene(const DevScene& sc, const SmemPlan& pl, unsigned char* dyn, uint64_t* bar, StagedScene& S) {
     unsigned char* p_tv = dyn + pl.view_bytes;
     unsigned char* p_sph = p_tv + pl.tview_bytes;
     unsigned char* p_tri = p_sph + pl.sph_bytes;
-    s_views = reinterpret_cast<const ulonglong2*>(dyn);
-    s_tviews = reinterpret_cast<const ulonglong2*>(p_tv);
-    s_sph = pl.stage_sph ? reinterpret_cast<const float4*>(p_sph) : sc.sph32;
-    s_tri = pl.stage_tri ? reinterpret_cast<const float4*>(p_tri) : sc.tri32;
+    S.views = reinterpret_cast<const ulonglong2*>(dyn);
+    S.tviews = reinterpret_cast<const ulonglong2*>(p_tv);
+    S.sph = pl.stage_sph ? reinterpret_cast<const float4*>(p_sph) : sc.sph32;
+    S.tri = pl.stage_tri ? reinterpret_cast<const float4*>(p_tri) : sc.tri32;
+    S.cold = sc.views_cold;
+    S.tcold = sc.tri_views_cold;
     if (threadIdx.x == 0) mbar_init(bar, 1);
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -135,7 +141,7 @@ struct PixelCounters {
 // Blinn-Phong and the reflection state disappear.  Per pixel the ray state is FP64, bit-identical to the reference.
 template <int K, bool kReflect>
 __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevScene& sc, const ulonglong2* s_views, const ulonglong2* s_tviews,
-                                             const float4* s_sph, const float4* s_tri, const int (&px)[K], const int (&py)[K], const bool (&inb)[K],
+                                             const float* s_cold, const float* s_tcold, const float4* s_sph, const float4* s_tri, const int (&px)[K], const int (&py)[K], const bool (&inb)[K],
                                              const int64_t (&out_idx)[K], int sample, PixelCounters& cnt, d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     d3 o[K], d[K], acc[K];
@@ -198,7 +204,7 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
         if (!__any_sync(kFullMask, any_alive)) break;
         Hit h[K];
         if (uv && depth == 0) {
-            closest_hit_view<K>(sc, s_views, s_tviews, utv, s_tri, cam_o, d, alive, nf, h, cnt.confirms);
+            closest_hit_view<K>(sc, s_views, s_tviews, s_cold, s_tcold, utv, s_tri, cam_o, d, alive, nf, h, cnt.confirms);
 #pragma unroll
             for (int k = 0; k < K; ++k) if (alive[k]) cnt.sph_exec += (uint32_t)sc.ns_pad;
         } else {
@@ -287,7 +293,8 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
 #pragma unroll
                 for (int k = 0; k < K; ++k) lists.n[k] = kListCap + 1;
                 if (uv) {
-                    occluded_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, s_tviews + (size_t)(1 + j) * tview_stride, utv, s_tri, Lp, sr,
+                    occluded_view<K>(sc, s_views + (size_t)(1 + j) * view_stride, s_tviews + (size_t)(1 + j) * tview_stride,
+                                     s_cold + (size_t)(1 + j) * view_stride * 4, s_tcold + (size_t)(1 + j) * tview_stride * 4, utv, s_tri, Lp, sr,
                                      bias, nf, r, lists, cnt.confirms, cnt.sph_exec);
                 } else {
 #pragma unroll
@@ -447,9 +454,11 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
     if (threadIdx.x == 0) s_sc = P.sc;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
-    const float4 *s_sph, *s_tri;
-    const ulonglong2 *s_views, *s_tviews;
-    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_tviews, s_sph, s_tri);  // contains __syncthreads: s_sc visible after it
+    StagedScene S;
+    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, S);
+    const float4 *s_sph = S.sph, *s_tri = S.tri;
+    const ulonglong2 *s_views = S.views, *s_tviews = S.tviews;
+    const float *s_cold = S.cold, *s_tcold = S.tcold;
     const DevScene& sc = s_sc;
 
     const int W = P.cam.width, rows = P.n_rows;
@@ -488,12 +497,16 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
             for (int k = 0; k < K; ++k) sum[k] = mk(0.0, 0.0, 0.0);
 #pragma unroll 1
             for (int s = 0; s < aa; ++s) {
-                trace_pixels<K, kReflect>(P, sc, s_views, s_tviews, s_sph, s_tri, px, py, inb, out_idx, s, cnt, c);
+                trace_pixels<K, kReflect>(P, sc, s_views, s_tviews, s_cold, s_tcold, s_sph, s_tri, px, py, inb, out_idx, s, cnt, c);
+                if (aa > 1) {
 #pragma unroll
-                for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
+                    for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
+                }
             }
+            if (aa > 1) {  // (one sample: (0 + c) / 1 == c)
 #pragma unroll
-            for (int k = 0; k < K; ++k) c[k] = sum[k] / (double)aa;
+                for (int k = 0; k < K; ++k) c[k] = sum[k] / (double)aa;
+            }
             n_in *= (uint32_t)aa;  // primary rays
         }
         const bool words_ok = P.rgb8_words && (W & 3) == 0 && tx * kTileW + kTileW <= W;
@@ -583,7 +596,7 @@ struct ViewsStream {
 // kTris: the scene has triangles and their views are resident (s_tviews): a third scan after the planes.
 template <int K, bool kTris, class Views>
 __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const ulonglong2* s_tviews,
-                                                const float4* s_sph, const float4* s_tri, const int (&pxs)[K], const int (&pys)[K],
+                                                const float* s_cold, const float* s_tcold, const float4* s_sph, const float4* s_tri, const int (&pxs)[K], const int (&pys)[K],
                                                 const bool (&inb)[K], int sample, PixelCounters& cnt, d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     const double bias = P.bias;
@@ -601,7 +614,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
     }
     {
         const ulonglong2* v0 = views.acquire(0);
-        if (ns > 0) closest_spheres_view<K>(sc, v0, cam_o, dir, alive, false, h, found, cnt.confirms);
+        if (ns > 0) closest_spheres_view<K>(sc, v0, s_cold, cam_o, dir, alive, false, h, found, cnt.confirms);
         views.release();
     }
 
@@ -624,7 +637,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
             }
             h[k] = hk; found[k] = fk;
         }
-        closest_spheres_view<K, true>(sc, s_tviews, cam_o, dir, alive, false, h, found, cnt.confirms);
+        closest_spheres_view<K, true>(sc, s_tviews, s_tcold, cam_o, dir, alive, false, h, found, cnt.confirms);
     }
 #pragma unroll 1
     for (int k = 0; k < K; ++k) {
@@ -696,7 +709,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         RayLists<K> lists;
         {
             const ulonglong2* vj = views.acquire(1 + j);  // streamed views: every warp of the CTA passes here, scanning or not
-            if (scan) occluded_spheres_view<K>(sc, vj, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec);
+            if (scan) occluded_spheres_view<K>(sc, vj, s_cold + (size_t)(1 + j) * sc.ns_pad * 4, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec);
             views.release();
         }
         if (!scan) continue;
@@ -727,7 +740,8 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
                 all_done2 = all_done2 && s.done;
             }
             if (!__all_sync(kFullMask, all_done2))
-                occluded_spheres_view<K, true>(sc, s_tviews + (size_t)(1 + j) * tview_stride, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec);
+                occluded_spheres_view<K, true>(sc, s_tviews + (size_t)(1 + j) * tview_stride, s_tcold + (size_t)(1 + j) * sc.nt_pad32 * 4, Lp, sr, bias,
+                                               false, st, lists, cnt.confirms, cnt.sph_exec);
         }
 #pragma unroll 1
         for (int k = 0; k < K; ++k) {
@@ -795,9 +809,11 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     if (threadIdx.x == 0) s_sc = P.sc;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
-    const float4 *s_sph, *s_tri;
-    const ulonglong2 *s_views, *s_tviews;
-    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, s_views, s_tviews, s_sph, s_tri);
+    StagedScene S;
+    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, S);
+    const float4 *s_sph = S.sph, *s_tri = S.tri;
+    const ulonglong2 *s_views = S.views, *s_tviews = S.tviews;
+    const float *s_cold = S.cold, *s_tcold = S.tcold;
     const DevScene& sc = s_sc;
     ViewsResident views_res{s_views, sc.ns_pad};
     ViewsStream views_str;
@@ -845,13 +861,17 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             for (int k = 0; k < K; ++k) sum[k] = mk(0.0, 0.0, 0.0);
 #pragma unroll 1
             for (int s = 0; s < aa; ++s) {
-                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_sph, s_tri, px, py, inb, s, cnt, c);
-                else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_sph, s_tri, px, py, inb, s, cnt, c);
+                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, px, py, inb, s, cnt, c);
+                else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, px, py, inb, s, cnt, c);
+                if (aa > 1) {
 #pragma unroll 1
-                for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
+                    for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
+                }
             }
+            if (aa > 1) {  // (one sample: (0 + c) / 1 == c)
 #pragma unroll 1
-            for (int k = 0; k < K; ++k) c[k] = sum[k] / (double)aa;
+                for (int k = 0; k < K; ++k) c[k] = sum[k] / (double)aa;
+            }
             n_in *= (uint32_t)aa;  // primary rays
         }
         const bool words_ok = P.rgb8_words && (W & 3) == 0 && tx * kTileW + kTileW <= W;
@@ -894,11 +914,11 @@ static cudaError_t ensure_smem(const void* fn, size_t bytes) {
 cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double bias, cudaStream_t stream) {
     if (sc.views && sc.ns > 0) {
         const int total = (1 + sc.nl) * sc.ns_pad;
-        build_views_kernel<false><<<(total + 255) / 256, 256, 0, stream>>>(sc, cam, bias, const_cast<float*>(sc.views));
+        build_views_kernel<false><<<(total + 255) / 256, 256, 0, stream>>>(sc, cam, bias, const_cast<float*>(sc.views), const_cast<float*>(sc.views_cold));
     }
     if (sc.tri_views && sc.nt > 0) {
         const int total = (1 + sc.nl) * sc.nt_pad32;
-        build_views_kernel<true><<<(total + 255) / 256, 256, 0, stream>>>(sc, cam, bias, const_cast<float*>(sc.tri_views));
+        build_views_kernel<true><<<(total + 255) / 256, 256, 0, stream>>>(sc, cam, bias, const_cast<float*>(sc.tri_views), const_cast<float*>(sc.tri_views_cold));
     }
     return cudaGetLastError();
 }
@@ -976,9 +996,9 @@ __global__ void __launch_bounds__(kRenderThreads, 2) closest_kernel(const __grid
     __shared__ DevScene s_sc;
     __shared__ __align__(8) uint64_t s_bar;
     if (threadIdx.x == 0) s_sc = Q.sc;
-    const float4 *s_sph, *s_tri;
-    const ulonglong2 *s_views, *s_tviews;
-    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, s_views, s_tviews, s_sph, s_tri);
+    StagedScene S;
+    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, S);
+    const float4 *s_sph = S.sph, *s_tri = S.tri;
     const DevScene& sc = s_sc;
     for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < Q.n; base += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = base + threadIdx.x;
@@ -1017,9 +1037,9 @@ __global__ void __launch_bounds__(kRenderThreads, 2) any_before_kernel(const __g
     __shared__ DevScene s_sc;
     __shared__ __align__(8) uint64_t s_bar;
     if (threadIdx.x == 0) s_sc = Q.sc;
-    const float4 *s_sph, *s_tri;
-    const ulonglong2 *s_views, *s_tviews;
-    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, s_views, s_tviews, s_sph, s_tri);
+    StagedScene S;
+    stage_scene(Q.sc, Q.plan, dyn_smem, &s_bar, S);
+    const float4 *s_sph = S.sph, *s_tri = S.tri;
     const DevScene& sc = s_sc;
     for (int64_t base = (int64_t)blockIdx.x * blockDim.x; base < Q.n; base += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = base + threadIdx.x;

@@ -3,28 +3,33 @@
 // Every ray of the frame starts at the camera (primary rays) or ends at a light (shadow rays, RE/Scene.h:
 // 86-104; "RE/" = /root/reference/RaytracingEngine/).  A shadow ray is filtered *reversed*, from the light
 // towards the shaded point, so both families share their origin O_j across all pixels.  Everything in the
-// line–sphere test that depends only on (sphere i, origin j) is hoisted into a per-frame "view" array
+// ray-sphere test that depends only on (sphere i, origin j) is hoisted into per-frame "view" arrays.
 //
-//     f_ij  = C_i - O_j                       (FP64, rounded to FP32)
-//     ng_ij = -( |f_ij|^2 - r_i^2 ) + M_ij     (FP64, rounded UP to FP32)
+// HOT array (shared memory, scanned for every ray): seen from O_j, sphere i is a cone of directions
+//     c_ij = (C_i - O_j) / F,  F = |C_i - O_j|            (FP64, rounded to FP32)
+//     w_ij = kConeMargin - cos(theta_ij),  cos(theta_ij) = sqrt(1 - (r_i'/F)^2)   (FP64, rounded UP to FP32)
+// and a unit direction u can hit it only if  h = u.c + w >= 0  — 3 FMA per test, two spheres per instruction with
+// fma.rn.f32x2 (SASS FFMA2, sm_100+).  The sign bits of h are shifted into a 32-bit mask (1 SHF per test) and only
+// the rare clear bits are looked at again.  r_i' = r_i for the camera and r_i + bias for a light: the true shadow
+// line starts at P + N*bias (RE/Scene.h:104) and passes the light at a distance of at most `bias`.  An origin inside
+// (or on) the sphere makes it a candidate for every direction (w = 4).
 //
-// and the per-ray work left is   b = f.u  (3 FMA),  h = b*b + ng  (1 FMA):  h >= 0  <=>  the ray's LINE may
-// touch the sphere.  Two spheres are processed per instruction with fma.rn.f32x2 (SASS FFMA2, sm_100+), the
-// sign bits of h are shifted into a 32-bit mask (1 SHF per test) and only the rare set bits are looked at
-// again: FP32 interval pruning, then the FP64 confirmation in the reference's own operation order
-// (rte_device.cuh).  4 FMA-pipe lanes-ops + 1 ALU op + 1 LDS.128 per TWO tests' worth of data per test.
+// COLD array (global memory, read once per candidate): {f_ij = C_i - O_j, ng_ij = -(|f|^2 - r^2) + M_ij}, from which
+// the resolution computes the chord of the ray's line through the sphere in FP32 interval arithmetic (b = f.u,
+// h' = b^2 + ng) to prune / classify the candidate before the FP64 confirmation in the reference's own operation
+// order (rte_device.cuh).
 //
-// The filter is conservative: with u = fl32(d), |d| = 1 (FP64-normalised by the caller),
-// F = |f_ij|, eps = 2^-24:   |b~ - b| <= 5 eps F,  |b~^2 - b^2| <= 10.x eps F^2,  so with
-//     M_ij = 16 eps F^2   (+ 2 r bias + bias^2 for light views: the true shadow line starts at P + N*bias and
-//                          misses the light by at most `bias`, RE/Scene.h:104)
-// a sphere whose exact test can succeed always has h~ >= 0.  It may accept extra spheres (cost only).
+// The filter is conservative: with u = fl32(d), |d| = 1 (FP64-normalised by the caller) and
+// eps = 2^-24, the rounding of u and c perturbs u.c by at most 2 eps, the three FMAs by at most 2 eps each (partial
+// sums <= 2), w is rounded up: the computed h is at least the exact u.c - cos(theta) + kConeMargin - 8 eps, so with
+// kConeMargin = 16 eps a sphere whose exact test can succeed always has h >= 0.  It may accept extra spheres (cost only).
 #pragma once
 #include "rte_trace.cuh"
 
 namespace rte {
 
 constexpr int kViewBlock = 32;  // spheres per candidate mask (ns_pad is a multiple of this)
+constexpr double kConeMargin = 16.0 * 5.9604644775390625e-08;  // 16 * 2^-24
 
 // ------------------------------------------------------------------------------ packed f32x2 helpers
 typedef unsigned long long f32x2;  // {lo, hi} = two FP32 values in one 64-bit register pair
@@ -49,7 +54,7 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
 }
 
 // ------------------------------------------------------------------------------ view layout
-// One view = ns_pad/2 sphere pairs of 32 bytes:  {fx0,fx1, fy0,fy1} {fz0,fz1, ng0,ng1}.
+// One view = ns_pad/2 sphere pairs of 32 bytes:  hot {cx0,cx1, cy0,cy1} {cz0,cz1, w0,w1},  cold {fx0,fx1, fy0,fy1} {fz0,fz1, ng0,ng1}.
 __host__ __device__ __forceinline__ size_t view_bytes(int ns_pad) { return (size_t)ns_pad * 16; }
 
 struct ViewEntry { float fx, fy, fz, ng; };
@@ -63,12 +68,14 @@ __device__ __forceinline__ ViewEntry view_entry(const float* __restrict__ view, 
 // Builds view j (0 = camera, 1.. = lights) for every sphere — or, kTri, for the bounding sphere of every triangle
 // (centroid, radius = farthest vertex: a ray that hits the triangle hits that sphere).  One thread per (view, primitive).
 template <bool kTri>
-__global__ void __launch_bounds__(256) build_views_kernel(const DevScene sc, const DevCamera cam, double bias, float* __restrict__ views) {
+__global__ void __launch_bounds__(256) build_views_kernel(const DevScene sc, const DevCamera cam, double bias, float* __restrict__ views,
+                                                          float* __restrict__ cold) {
     const int n = kTri ? sc.nt : sc.ns, n_pad = kTri ? sc.nt_pad32 : sc.ns_pad, nv = 1 + sc.nl;
     const int total = nv * n_pad;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
         const int j = t / n_pad, i = t - j * n_pad;
-        float fx = 0.f, fy = 0.f, fz = 0.f, ng = -INFINITY;  // never-candidate padding: h = -inf
+        float fx = 0.f, fy = 0.f, fz = 0.f, ng = -INFINITY;  // cold padding: h' = -inf
+        float cx = 0.f, cy = 0.f, cz = 0.f, w = -INFINITY;   // hot padding: never a candidate
         if (i < n) {
             const d3 O = j == 0 ? ld3(cam.pos) : ld3(sc.lights[j - 1].pos);
             d3 C;
@@ -91,9 +98,22 @@ __global__ void __launch_bounds__(256) build_views_kernel(const DevScene sc, con
             fx = (float)f.x; fy = (float)f.y; fz = (float)f.z;
             ng = __double2float_ru((r * r - F2) + M);
             if (!(ng == ng)) ng = INFINITY;  // non-finite input: always a candidate (the FP64 test decides)
+            // the cone of directions from O that can touch the sphere (inflated by `bias` for a light)
+            const double ri = (j > 0 ? r + bias : r) * (1.0 + 1e-12), F = sqrt(F2);
+            w = 4.0f;  // origin inside / on the sphere, or non-finite input: every direction is a candidate
+            if (F > ri && F < 1e150) {
+                const double q = ri / F;
+                const d3 c = f / F;
+                cx = (float)c.x; cy = (float)c.y; cz = (float)c.z;
+                w = __double2float_ru(kConeMargin - sqrt(fmax(0.0, 1.0 - q * q)));
+                if (!(w == w) || !(cx == cx) || !(cy == cy) || !(cz == cz)) { cx = cy = cz = 0.f; w = 4.0f; }
+            }
         }
-        float* p = views + ((size_t)j * n_pad + (size_t)(i & ~1)) * 4 + (i & 1);
-        p[0] = fx; p[2] = fy; p[4] = fz; p[6] = ng;
+        const size_t at = ((size_t)j * n_pad + (size_t)(i & ~1)) * 4 + (i & 1);
+        float* p = views + at;
+        p[0] = cx; p[2] = cy; p[4] = cz; p[6] = w;
+        float* q = cold + at;
+        q[0] = fx; q[2] = fy; q[4] = fz; q[6] = ng;
     }
 }
 
@@ -110,8 +130,8 @@ __device__ __forceinline__ ViewRay make_view_ray(d3 u) {
     return r;
 }
 
-// Filters spheres [base, base+32) of one view against K directions; cand[k] bit (31-i) <-> sphere base+i.
-// The 16 sphere pairs are walked in chunks of kPairs unrolled pairs: the loop body (kPairs * (2 LDS + 6K) SASS
+// Filters spheres [base, base+32) of one (hot) view against K unit directions; cand[k] bit (31-i) <-> sphere base+i.
+// The 16 sphere pairs are walked in chunks of kPairs unrolled pairs: the loop body (kPairs * (2 LDS + 5K) SASS
 // instructions) has to stay well inside the ~6 KB L0 instruction cache, or the warps of an SMSP starve on fetch.
 template <int K>
 __device__ __forceinline__ void view_block_masks(const ulonglong2* __restrict__ v, const ViewRay (&r)[K], uint32_t (&cand)[K]) {
@@ -130,10 +150,9 @@ __device__ __forceinline__ void view_block_masks(const ulonglong2* __restrict__ 
             const ulonglong2 A = v[2 * (c + p)], B = v[2 * (c + p) + 1];
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                f32x2 b = mul2(A.x, ux2[k]);
-                b = fma2(A.y, uy2[k], b);
-                b = fma2(B.x, uz2[k], b);
-                const f32x2 h = fma2(b, b, B.y);
+                f32x2 h = fma2(B.x, uz2[k], B.y);  // h = u.c + w
+                h = fma2(A.y, uy2[k], h);
+                h = fma2(A.x, ux2[k], h);
                 uint32_t h0, h1;
                 unpack2_bits(h, h0, h1);
                 m[k] = __funnelshift_l(h0, m[k], 1);  // m = (m << 1) | sign(h0)
@@ -177,13 +196,14 @@ __device__ __forceinline__ ViewBounds view_bounds(float extent, d3 origin, doubl
 }
 
 // Centre parameter and half-chord bounds of candidate `idx` along the scan line.
-struct ViewChord { float sc, hc_lo, hc_hi; };
+struct ViewChord { float sc, hc_lo, hc_hi; bool miss; };  // miss: the line certainly passes outside the sphere
 __device__ __forceinline__ ViewChord view_chord(const float* __restrict__ view, int idx, const ViewRay& r, const ViewBounds& vb) {
     const ViewEntry e = view_entry(view, idx);
     const float b = __fmaf_rn(e.fz, r.uz, __fmaf_rn(e.fy, r.uy, e.fx * r.ux));
     const float h = __fmaf_rn(b, b, e.ng);
     ViewChord c;
     c.sc = b;
+    c.miss = h < 0.0f;
     c.hc_hi = sqrtf(fmaxf(h, 0.0f)) * 1.000001f;
     c.hc_lo = sqrtf(fmaxf(h - vb.m2, 0.0f)) * 0.999999f;
     return c;
@@ -200,11 +220,16 @@ template <int K>
 struct CandQueue {
     uint16_t q[kWindow * K];  // (ray k << 8) | (sphere index - window start); local memory, only written entries are touched
     // `n` is passed in and out so that it stays in a register (the dynamically indexed array lives in local memory)
-    __device__ __forceinline__ int push_block(uint32_t c, int rel, int k, int left, int n) {  // rel = base - window start, left = ns - base
+    // rel = base - window start, left = ns - base; `cold_w` = cold entries of the window start: the candidate's entry is
+    // prefetched into L1 now, the resolution at the end of the window reads it some hundred cycles later
+    __device__ __forceinline__ int push_block(uint32_t c, int rel, int k, int left, int n, const float* __restrict__ cold_w) {
         while (c) {  // short, divergent
             const int i = __clz(c);
             c &= ~(0x80000000u >> i);
-            if (i < left) q[n++] = (uint16_t)((k << 8) | (rel + i));
+            if (i < left) {
+                q[n++] = (uint16_t)((k << 8) | (rel + i));
+                if (cold_w) asm volatile("prefetch.global.L1 [%0];" ::"l"(cold_w + (size_t)((rel + i) >> 1) * 8));
+            }
         }
         return n;
     }
@@ -221,15 +246,15 @@ __device__ __forceinline__ T pick(const T (&a)[K], int k) {
 // Scene::IntersectClosest over the spheres (kTri: the triangles, through their bounding spheres) for K PRIMARY rays of one
 // thread (view 0, common origin o).  best/found carry the result of the classes scanned before (canonical order, strict '<').
 template <int K, bool kTri = false>
-__device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, d3 o, const d3 (&d)[K],
-                                                     const bool (&alive)[K], bool no_filter, Hit (&best)[K], bool (&found)[K],
-                                                     uint32_t& confirms) {
+__device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float* __restrict__ vf, d3 o,
+                                                     const d3 (&d)[K], const bool (&alive)[K], bool no_filter, Hit (&best)[K], bool (&found)[K],
+                                                     uint32_t& confirms) {  // view: hot array (shared), vf: cold array (global or shared)
+    const bool prefetch = true;  // vf is global memory
     const ViewBounds vb = view_bounds(view_extent<kTri>(sc), o, 0.0, false);
     ViewRay r[K];
     float best_f[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) { r[k] = make_view_ray(d[k]); best_f[k] = found[k] ? __double2float_ru(best[k].t) : INFINITY; }
-    const float* vf = reinterpret_cast<const float*>(view);
     const int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
     CandQueue<K> Q;
     int qn = 0;
@@ -250,7 +275,7 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
             }
             if (any) {  // ~5 % of the blocks
 #pragma unroll
-                for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn);
+                for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn, prefetch ? vf + (size_t)wbase * 4 : nullptr);
             }
             base += kViewBlock;
         } while (base < stop);
@@ -263,8 +288,8 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
             const d3 dk = d[k];  // FP64 ray data is indexed dynamically: it lives in local memory, not in K selects
             if (!no_filter) {
                 const ViewChord ch = view_chord(vf, idx, pick<K>(r, k), vb);
-                // behind the camera, or its near root cannot beat the best so far
-                if (ch.sc + ch.hc_hi + vb.slack < 0.0f || ch.sc - ch.hc_hi - vb.slack > pick<K>(best_f, k)) continue;
+                // the line misses it, it lies behind the camera, or its near root cannot beat the best so far
+                if (ch.miss || ch.sc + ch.hc_hi + vb.slack < 0.0f || ch.sc - ch.hc_hi - vb.slack > pick<K>(best_f, k)) continue;
             }
             double t;
             ++confirms;
@@ -286,12 +311,12 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
 // against NULL: the scans must compile to LDS).
 template <int K>
 __device__ __forceinline__ void closest_hit_view(const DevScene& sc, const ulonglong2* __restrict__ view0, const ulonglong2* __restrict__ tview0,
-                                                 bool tri_view, const float4* __restrict__ s_tri, d3 o, const d3 (&d)[K], const bool (&alive)[K],
+                                                 const float* cold0, const float* tcold0, bool tri_view, const float4* __restrict__ s_tri, d3 o, const d3 (&d)[K], const bool (&alive)[K],
                                                  bool no_filter, Hit (&best)[K], uint32_t& confirms) {
     bool found[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) { best[k].t = 0.0; best[k].kind = RTE_HIT_NONE; best[k].idx = 0; found[k] = false; }
-    if (sc.ns > 0) closest_spheres_view<K>(sc, view0, o, d, alive, no_filter, best, found, confirms);
+    if (sc.ns > 0) closest_spheres_view<K>(sc, view0, cold0, o, d, alive, no_filter, best, found, confirms);
     if (sc.np > 0 || (sc.nt > 0 && !tri_view)) {
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -299,7 +324,7 @@ __device__ __forceinline__ void closest_hit_view(const DevScene& sc, const ulong
             closest_planes_triangles(sc, s_tri, r, o, d[k], alive[k], best[k], found[k], confirms, !tri_view);
         }
     }
-    if (sc.nt > 0 && tri_view) closest_spheres_view<K, true>(sc, tview0, o, d, alive, no_filter, best, found, confirms);
+    if (sc.nt > 0 && tri_view) closest_spheres_view<K, true>(sc, tview0, tcold0, o, d, alive, no_filter, best, found, confirms);
 }
 
 // One forward shadow ray of the reference (RE/Scene.h:86-104) plus what the reversed scan needs.
@@ -366,9 +391,10 @@ __device__ __noinline__ double march_list(const DevScene& sc, const uint16_t* li
 // kTri = true: the triangle phase of the same query, through the light's view of the triangles' bounding spheres; `st`
 // continues from the sphere and plane phases (canonical order), every candidate is confirmed in FP64 (tri_exact).
 template <int K, bool kTri = false>
-__device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, d3 Lp,
+__device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float* __restrict__ vf, d3 Lp,
                                                       const ShadowRay (&ray)[K], double bias, bool no_filter, OccState (&st)[K],
                                                       RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
+    const bool prefetch = true;  // vf is global memory
     uint32_t first[K];
     bool scanning[K];
     const int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
@@ -380,7 +406,6 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
     }
     if (ns > 0) {
         const ViewBounds vb = view_bounds(view_extent<kTri>(sc), Lp, bias, true);
-        const float* vf = reinterpret_cast<const float*>(view);
         const bool skip_self = !kTri && bias >= 1e-5;
         ViewRay r[K];
         float tref[K], tmax_lo[K], tmax_hi[K];
@@ -413,7 +438,7 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
                 }
                 if (any) {  // ~5 % of the blocks
 #pragma unroll
-                    for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn);
+                    for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn, prefetch ? vf + (size_t)wbase * 4 : nullptr);
                 }
                 base += kViewBlock;
             } while (base < stop);
@@ -431,6 +456,7 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
                 if (!no_filter) {
                     if (skip_self && idx == ray[k].self) continue;
                     const ViewChord ch = view_chord(vf, idx, pick<K>(r, k), vb);
+                    if (ch.miss) continue;
                     const float tc = tref[k] - ch.sc;  // forward distance of the chord centre
                     const float t0_lo = tc - ch.hc_hi - vb.slack, t0_hi = tc - ch.hc_lo + vb.slack, t1_hi = tc + ch.hc_hi + vb.slack;
                     if (t1_hi < 0.0f || t0_lo > tmax_hi[k]) continue;  // certainly no hit in (1e-6, maxDist), none <= bias
@@ -479,10 +505,10 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
 // else with the generic FP32 filter) — general kernel.
 template <int K>
 __device__ __forceinline__ void occluded_view(const DevScene& sc, const ulonglong2* __restrict__ view, const ulonglong2* __restrict__ tview,
-                                              bool tri_view, const float4* __restrict__ s_tri, d3 Lp, const ShadowRay (&ray)[K], double bias,
+                                              const float* cold, const float* tcold, bool tri_view, const float4* __restrict__ s_tri, d3 Lp, const ShadowRay (&ray)[K], double bias,
                                               bool no_filter, OccResult (&out)[K], RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
     OccState st[K];
-    occluded_spheres_view<K>(sc, view, Lp, ray, bias, no_filter, st, lists, confirms, executed);  // ns == 0: only initialises st
+    occluded_spheres_view<K>(sc, view, cold, Lp, ray, bias, no_filter, st, lists, confirms, executed);  // ns == 0: only initialises st
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         if (st[k].res.near && st[k].res.occluded) st[k].done = true;  // the march decides; planes/triangles are not counted after an occluder
@@ -497,7 +523,8 @@ __device__ __forceinline__ void occluded_view(const DevScene& sc, const ulonglon
         bool all_done = true;
 #pragma unroll
         for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;
-        if (!__all_sync(kFullMask, all_done)) occluded_spheres_view<K, true>(sc, tview, Lp, ray, bias, no_filter, st, lists, confirms, executed);
+        if (!__all_sync(kFullMask, all_done))
+            occluded_spheres_view<K, true>(sc, tview, tcold, Lp, ray, bias, no_filter, st, lists, confirms, executed);
     }
 #pragma unroll
     for (int k = 0; k < K; ++k) out[k] = st[k].res;
