@@ -167,8 +167,9 @@ typedef struct rte_render_opts {
 /* Validation switches for rte_render_opts.flags.  Both must leave every output bit-identical:
  *   EXACT_SHADOWS  every shadow ray takes the literal RE/Scene.h:35-77 march instead of the any-hit query;
  *   NO_FILTER      the FP32 filters accept everything, i.e. every primitive is tested in FP64;
- *   GENERAL_KERNEL never take the lean kernel specialised for diffuse sphere/plane scenes without AOVs. */
-enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4 };
+ *   GENERAL_KERNEL never take the lean kernel specialised for diffuse scenes without AOVs;
+ *   NO_CULL        the lean kernel scans every view in full instead of the per-tile culled copy. */
+enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4, RTE_FLAG_NO_CULL = 8 };
 
 /* Output buffers of one render call.  Every pointer is optional (NULL = not wanted) and is a
  * DEVICE pointer for rte_render() and a HOST pointer for rte_render_host().  Each buffer holds

@@ -452,6 +452,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
     p.exact_shadows = (o.flags & RTE_FLAG_EXACT_SHADOWS) ? 1 : 0;
     p.no_filter = (o.flags & RTE_FLAG_NO_FILTER) ? 1 : 0;
     p.force_general = (o.flags & RTE_FLAG_GENERAL_KERNEL) ? 1 : 0;
+    p.no_cull = (o.flags & RTE_FLAG_NO_CULL) ? 1 : 0;
     p.bias = o.bias; p.max_white = o.max_white; p.jodie_a = o.jodie_a;
     p.out = *frame;
     p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;

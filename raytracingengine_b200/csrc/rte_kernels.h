@@ -46,6 +46,8 @@ struct RenderParams {
     uint8_t* peer_rgb8[kMaxPeers];
     int32_t n_peers;
     int32_t rgb8_words;      // out.rgb8 and every peer frame are 4-byte aligned: full tile rows leave as 32-bit words
+    int32_t cull;            // fast kernel: per-warp cull scratch follows the staged arrays in dynamic shared memory (rte_views.cuh)
+    int32_t no_cull;         // RTE_FLAG_NO_CULL: never use it (validation / A-B)
     unsigned int* tile_counter;        // zeroed before launch
     unsigned long long* stats;         // kStatCount counters, zeroed before launch
 };

@@ -596,8 +596,9 @@ struct ViewsStream {
 // kTris: the scene has triangles and their views are resident (s_tviews): a third scan after the planes.
 template <int K, bool kTris, class Views>
 __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const ulonglong2* s_tviews,
-                                                const float* s_cold, const float* s_tcold, const float4* s_sph, const float4* s_tri, const int (&pxs)[K], const int (&pys)[K],
-                                                const bool (&inb)[K], int sample, PixelCounters& cnt, d3 (&result)[K]) {
+                                                const float* s_cold, const float* s_tcold, const float4* s_sph, const float4* s_tri, const CullScratch* cull,
+                                                const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K], int sample, PixelCounters& cnt,
+                                                d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     const double bias = P.bias;
     const int nl = sc.nl, np = sc.np, ns = sc.ns, nt = kTris ? sc.nt : 0;
@@ -614,7 +615,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
     }
     {
         const ulonglong2* v0 = views.acquire(0);
-        if (ns > 0) closest_spheres_view<K>(sc, v0, s_cold, cam_o, dir, alive, false, h, found, cnt.confirms);
+        if (ns > 0) closest_spheres_view<K>(sc, v0, s_cold, cam_o, dir, alive, false, h, found, cnt.confirms, cull, &cnt.sph_exec);
         views.release();
     }
 
@@ -637,7 +638,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
             }
             h[k] = hk; found[k] = fk;
         }
-        closest_spheres_view<K, true>(sc, s_tviews, s_tcold, cam_o, dir, alive, false, h, found, cnt.confirms);
+        closest_spheres_view<K, true>(sc, s_tviews, s_tcold, cam_o, dir, alive, false, h, found, cnt.confirms, cull);
     }
 #pragma unroll 1
     for (int k = 0; k < K; ++k) {
@@ -645,7 +646,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         Hit hk = h[k];
         bool fk = found[k];
         if (alive[k]) {
-            cnt.sph += (uint32_t)ns; cnt.pl += (uint32_t)np; cnt.tri += (uint32_t)nt; cnt.sph_exec += (uint32_t)sc.ns_pad;
+            cnt.sph += (uint32_t)ns; cnt.pl += (uint32_t)np; cnt.tri += (uint32_t)nt;
 #pragma unroll 1
             for (int i = 0; i < (kTris ? 0 : np); ++i) {  // planes after the spheres, strict '<' (RE/Scene.h:218-257)
                 double t;
@@ -709,7 +710,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         RayLists<K> lists;
         {
             const ulonglong2* vj = views.acquire(1 + j);  // streamed views: every warp of the CTA passes here, scanning or not
-            if (scan) occluded_spheres_view<K>(sc, vj, s_cold + (size_t)(1 + j) * sc.ns_pad * 4, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec);
+            if (scan) occluded_spheres_view<K>(sc, vj, s_cold + (size_t)(1 + j) * sc.ns_pad * 4, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec, cull);
             views.release();
         }
         if (!scan) continue;
@@ -741,7 +742,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
             }
             if (!__all_sync(kFullMask, all_done2))
                 occluded_spheres_view<K, true>(sc, s_tviews + (size_t)(1 + j) * tview_stride, s_tcold + (size_t)(1 + j) * sc.nt_pad32 * 4, Lp, sr, bias,
-                                               false, st, lists, cnt.confirms, cnt.sph_exec);
+                                               false, st, lists, cnt.confirms, cnt.sph_exec, cull);
         }
 #pragma unroll 1
         for (int k = 0; k < K; ++k) {
@@ -816,6 +817,13 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     const float *s_cold = S.cold, *s_tcold = S.tcold;
     const DevScene& sc = s_sc;
     ViewsResident views_res{s_views, sc.ns_pad};
+    CullScratch cull_scratch{nullptr, nullptr};
+    if (P.cull) {
+        unsigned char* base = dyn_smem + ((P.plan.total + 15) & ~(size_t)15) + (size_t)warp * kCullBytesPerWarp;
+        cull_scratch.mini = reinterpret_cast<ulonglong2*>(base);
+        cull_scratch.map = reinterpret_cast<uint16_t*>(base + kCullCap * 16);
+    }
+    const CullScratch* cull = P.cull ? &cull_scratch : nullptr;
     ViewsStream views_str;
     if (kStream) {
         views_str.base = dyn_smem;
@@ -861,8 +869,8 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             for (int k = 0; k < K; ++k) sum[k] = mk(0.0, 0.0, 0.0);
 #pragma unroll 1
             for (int s = 0; s < aa; ++s) {
-                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, px, py, inb, s, cnt, c);
-                else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, px, py, inb, s, cnt, c);
+                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, px, py, inb, s, cnt, c);
+                else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, px, py, inb, s, cnt, c);
                 if (aa > 1) {
 #pragma unroll 1
                     for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
@@ -923,9 +931,13 @@ cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double 
     return cudaGetLastError();
 }
 
+// `cull_ok`: the kernel can use per-warp cull scratch (the fast kernel); it is granted when it fits next to the staged arrays
+// without lowering the number of CTAs per SM.
 static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int small_threads, int small_min_blocks, int K,
-                                    const RenderParams& p, int sm_count, cudaStream_t stream) {
-    const size_t smem = p.plan.total;
+                                    const RenderParams& p0, int sm_count, cudaStream_t stream, bool cull_ok = false, size_t smem_limit = 0) {
+    RenderParams p = p0;
+    p.cull = 0;
+    size_t smem = p.plan.total;
     cudaError_t e = ensure_smem(fn, smem);
     if (e != cudaSuccess) return e;
     // several CTAs per SM when the staged arrays fit that often, else one CTA of 512 threads
@@ -940,6 +952,15 @@ static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int smal
         if (e != cudaSuccess) return e;
     }
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
+    if (cull_ok && !p.no_cull) {
+        const size_t with_cull = ((smem + 15) & ~(size_t)15) + (size_t)(threads / 32) * kCullBytesPerWarp;
+        int per_sm2 = 0;
+        if (with_cull <= smem_limit && ensure_smem(fn, with_cull) == cudaSuccess &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, fn, threads, with_cull) == cudaSuccess && per_sm2 >= per_sm) {
+            smem = with_cull;
+            p.cull = 1;
+        }
+    }
     const int W = p.cam.width, rows = p.n_rows;
     const long long n_tiles = (long long)((W + kTileW - 1) / kTileW) * ((rows + kTileH * K - 1) / (kTileH * K));
     long long blocks = (long long)sm_count * per_sm;  // persistent: a multiple of the SM count
@@ -963,16 +984,20 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
     }
     if (fast_path_eligible(p) && !p.force_general)
     {
+        int dev = 0, optin = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        const size_t limit = optin > 2048 ? (size_t)optin - 2048 : 0;  // static shared memory of the kernel
         if (p.plan.stream_views) {
             const void* fn = (const void*)render_fast_kernel<kViewPixels, true, true>;
-            return launch_render_fn(fn, fn, kRenderMaxThreads, 1, kViewPixels, p, sm_count, stream);
+            return launch_render_fn(fn, fn, kRenderMaxThreads, 1, kViewPixels, p, sm_count, stream, true, limit);
         }
         if (p.sc.nt > 0)
             return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false, true>,
                                     (const void*)render_fast_kernel<kViewPixels, true, false, true>, kFastThreads, kFastMinBlocks, kViewPixels, p,
-                                    sm_count, stream);
+                                    sm_count, stream, true, limit);
         return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false>, (const void*)render_fast_kernel<kViewPixels, true, false>,
-                                kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream);
+                                kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream, true, limit);
     }
     const void* fn = p.sc.reflective ? (const void*)render_kernel<1, true> : (const void*)render_kernel<1, false>;
     return launch_render_fn(fn, fn, kRenderThreads, 2, 1, p, sm_count, stream);

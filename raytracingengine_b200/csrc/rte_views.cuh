@@ -209,6 +209,121 @@ __device__ __forceinline__ ViewChord view_chord(const float* __restrict__ view, 
     return c;
 }
 
+// ------------------------------------------------------------------------------ warp-level culling
+// The K*32 rays a warp sends through one view (its 8 x 4K pixel tile from the camera, or the shadow rays of those pixels
+// from one light) are coherent: they lie in a narrow cone around their mean direction.  Before the per-ray scan the warp
+// tests every sphere of the view ONCE against that tile cone — lanes take different spheres, coalesced LDS.128 — and
+// packs the survivors (typically a few percent) into a private mini-view of the same layout, which the per-ray scan then
+// walks instead of the whole view.  Cone-cone test on the unit sphere: sphere cone (axis c, half-angle ts) and tile cone
+// (axis a, half-angle tt) can share a direction only if  angle(c, a) <= ts + tt,  i.e.  c.a >= cos ts cos tt - sin ts sin tt.
+// Conservative like the per-ray test (bounds rounded outwards); the survivors keep their ascending index order, so the
+// resolution still sees candidates in canonical order.  Tiles whose rays diverge (silhouettes: cos tt < kCullMinCos) or
+// with more than kCullCap survivors scan the full view as before.
+constexpr int kCullCap = 128;         // survivors per (tile, view)
+constexpr int kCullMin = 128;         // views with fewer entries are scanned directly
+constexpr float kCullMinCos = 0.5f;   // tile cones wider than 60 degrees are not worth testing
+constexpr int kCullBytesPerWarp = kCullCap * 16 + kCullCap * 2;
+struct CullScratch {
+    ulonglong2* mini;  // kCullCap entries in pair layout (shared memory, private to the warp)
+    uint16_t* map;     // position in the mini-view -> index in the view
+};
+
+// Tests the n_pad entries of `view` against the tile cone (ax,ay,az | ct = lower bound of cos tt, st2 = upper bound of
+// sin^2 tt) and packs the survivors.  All 32 lanes; returns the survivor count (> kCullCap: overflow, scratch unusable).
+// No square root: with x = c.a - cos ts cos tt (+ slack), the entry survives iff x >= 0 or x^2 <= sin^2 ts sin^2 tt.
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool cull_keep(float cx, float cy, float cz, float w, float ax, float ay, float az, float ct, float st2) {
+    const float cs = -w;  // = cos ts - kConeMargin: a lower bound of cos ts
+    const float d = __fmaf_rn(cz, az, __fmaf_rn(cy, ay, cx * ax));
+    const float x = __fmaf_rn(-cs, ct, d) + 4e-6f;                       // >= the exact c.a - cos ts cos tt
+    const float rhs = __fmaf_rn(-cs * cs, st2, st2) * 1.00001f + 1e-12f;  // >= sin^2 ts sin^2 tt
+    const bool hit = (x >= 0.0f) | (x * x <= rhs);
+    return (w >= 2.0f) | (hit & (w > -2.0f));  // w = 4: origin inside the sphere, always; w = -inf: padding, never
+}
+__device__ __forceinline__ void cull_store(float* __restrict__ mf, uint16_t* __restrict__ map, int pos, float cx, float cy, float cz, float w, int idx) {
+    float* e = mf + (size_t)(pos >> 1) * 8 + (pos & 1);
+    e[0] = cx; e[2] = cy; e[4] = cz; e[6] = w;
+    map[pos] = (uint16_t)idx;
+}
+__device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float ct, float st2,
+                                      ulonglong2* __restrict__ mini, uint16_t* __restrict__ map) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt = (1u << lane) - 1u;
+    const int n_pairs = n_pad >> 1;
+    float* mf = reinterpret_cast<float*>(mini);
+    const uint32_t v0 = (uint32_t)__cvta_generic_to_shared(view);  // the views live in shared memory
+    int count = 0;
+#pragma unroll 1
+    for (int p0 = 0; p0 < n_pairs; p0 += 32) {
+        const int p = p0 + lane;
+        bool k0 = false, k1 = false;
+        float4 A = make_float4(0.f, 0.f, 0.f, 0.f), B = A;  // A = {cx0,cx1,cy0,cy1}, B = {cz0,cz1,w0,w1}
+        if (p < n_pairs) {
+            A = lds_f4(v0 + 32u * (uint32_t)p);
+            B = lds_f4(v0 + 32u * (uint32_t)p + 16u);
+            k0 = cull_keep(A.x, A.z, B.x, B.z, ax, ay, az, ct, st2);
+            k1 = cull_keep(A.y, A.w, B.y, B.w, ax, ay, az, ct, st2);
+        }
+        const uint32_t m0 = __ballot_sync(kFullMask, k0), m1 = __ballot_sync(kFullMask, k1);
+        if ((m0 | m1) != 0u) {  // warp-uniform; most groups of 64 spheres have no survivor
+            const int pos = count + __popc(m0 & lt) + __popc(m1 & lt);
+            if (k0 && pos < kCullCap) cull_store(mf, map, pos, A.x, A.z, B.x, B.z, 2 * p);
+            const int pos1 = pos + (k0 ? 1 : 0);
+            if (k1 && pos1 < kCullCap) cull_store(mf, map, pos1, A.y, A.w, B.y, B.w, 2 * p + 1);
+            count += __popc(m0) + __popc(m1);
+            if (count > kCullCap) return count;
+        }
+    }
+    // pad to a multiple of 32 with never-candidate entries
+    const int padded = (count + 31) & ~31;
+    const int q = count + lane;
+    if (q < padded) {
+        float* e = mf + (size_t)(q >> 1) * 8 + (q & 1);
+        e[0] = 0.f; e[2] = 0.f; e[4] = 0.f; e[6] = -INFINITY;
+    }
+    __syncwarp();
+    return count;
+}
+
+// Tile cone of the active rays of the warp, then cull_pack.  Returns true when `cs` holds a usable mini-view of `count`
+// entries.  All 32 lanes call it.
+template <int K>
+__device__ __forceinline__ bool cull_view(const ulonglong2* __restrict__ view, int n_pad, const ViewRay (&r)[K], const bool (&active)[K],
+                                          const CullScratch& cs, int& count) {
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (active[k]) { sx += r[k].ux; sy += r[k].uy; sz += r[k].uz; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sx += __shfl_xor_sync(kFullMask, sx, o); sy += __shfl_xor_sync(kFullMask, sy, o); sz += __shfl_xor_sync(kFullMask, sz, o);
+    }
+    const float l2 = __fmaf_rn(sz, sz, __fmaf_rn(sy, sy, sx * sx));
+    if (!(l2 > 1e-6f)) return false;  // no active ray, or directions that cancel
+    const float inv = 1.0f / sqrtf(l2);
+    const float ax = sx * inv, ay = sy * inv, az = sz * inv;  // |a| = 1 +- 3e-7
+    float md = 1.0f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (active[k]) md = fminf(md, __fmaf_rn(r[k].uz, az, __fmaf_rn(r[k].uy, ay, r[k].ux * ax)));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) md = fminf(md, __shfl_xor_sync(kFullMask, md, o));
+    const float ct = md * 0.999999f - 1e-6f;  // lower bound of cos(tile half-angle): |a|, |u| and the dot are off by < 1e-6
+#ifdef RTE_CULL_DEBUG
+    if (!(ct >= kCullMinCos)) { count = -1; return false; }
+#endif
+    if (!(ct >= kCullMinCos)) return false;
+    const float st2 = fmaxf(1.0f - ct * ct, 0.0f) * 1.00001f + 1e-12f;  // upper bound of sin^2(tile half-angle)
+    count = cull_pack(view, n_pad, ax, ay, az, ct, st2, cs.mini, cs.map);
+    return count <= kCullCap;
+}
+
 // ------------------------------------------------------------------------------ candidate queue
 // With ~2 line candidates per ray and 32 lanes, almost every 32-sphere block has a candidate in SOME lane:
 // resolving candidates where they are found runs the divergent path ~30 times per scan with 1-2 lanes active.
@@ -220,15 +335,18 @@ template <int K>
 struct CandQueue {
     uint16_t q[kWindow * K];  // (ray k << 8) | (sphere index - window start); local memory, only written entries are touched
     // `n` is passed in and out so that it stays in a register (the dynamically indexed array lives in local memory)
-    // rel = base - window start, left = ns - base; `cold_w` = cold entries of the window start: the candidate's entry is
-    // prefetched into L1 now, the resolution at the end of the window reads it some hundred cycles later
-    __device__ __forceinline__ int push_block(uint32_t c, int rel, int k, int left, int n, const float* __restrict__ cold_w) {
+    // rel = base - window start, left = ns - base; the candidate's cold entry is prefetched into L1 now, the resolution at
+    // the end of the window reads it some hundred cycles later
+    // (`map`: the scan walks a culled mini-view, positions translate to view indices)
+    __device__ __forceinline__ int push_block(uint32_t c, int rel, int k, int left, int n, int wbase, const float* __restrict__ cold,
+                                              const uint16_t* __restrict__ map) {
         while (c) {  // short, divergent
             const int i = __clz(c);
             c &= ~(0x80000000u >> i);
             if (i < left) {
                 q[n++] = (uint16_t)((k << 8) | (rel + i));
-                if (cold_w) asm volatile("prefetch.global.L1 [%0];" ::"l"(cold_w + (size_t)((rel + i) >> 1) * 8));
+                const int idx = map ? (int)map[wbase + rel + i] : wbase + rel + i;
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(cold + (size_t)(idx >> 1) * 8));
             }
         }
         return n;
@@ -248,14 +366,24 @@ __device__ __forceinline__ T pick(const T (&a)[K], int k) {
 template <int K, bool kTri = false>
 __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float* __restrict__ vf, d3 o,
                                                      const d3 (&d)[K], const bool (&alive)[K], bool no_filter, Hit (&best)[K], bool (&found)[K],
-                                                     uint32_t& confirms) {  // view: hot array (shared), vf: cold array (global or shared)
-    const bool prefetch = true;  // vf is global memory
+                                                     uint32_t& confirms, const CullScratch* cull = nullptr, uint32_t* executed = nullptr) {
+    // view: hot array (shared), vf: cold array (global); executed: per-lane count of FP32 tests really run (optional)
     const ViewBounds vb = view_bounds(view_extent<kTri>(sc), o, 0.0, false);
     ViewRay r[K];
     float best_f[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) { r[k] = make_view_ray(d[k]); best_f[k] = found[k] ? __double2float_ru(best[k].t) : INFINITY; }
-    const int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
+    int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
+    const uint16_t* map = nullptr;  // culled: positions of the mini-view -> indices of the view
+    if (cull && !no_filter && ns_pad >= kCullMin) {
+        int cnt = 0;
+        if (executed) *executed += (uint32_t)(ns_pad >> 4);  // the warp's cull pass: ns_pad/32 cone-cone tests per lane, ~2x a ray test
+        if (cull_view<K>(view, ns_pad, r, alive, *cull, cnt)) { view = cull->mini; map = cull->map; ns = cnt; ns_pad = (cnt + 31) & ~31; }
+    }
+    uint32_t n_alive = 0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) n_alive += alive[k] ? 1u : 0u;
+    if (executed) *executed += n_alive * (uint32_t)ns_pad;
     CandQueue<K> Q;
     int qn = 0;
     int base = 0;
@@ -275,7 +403,7 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
             }
             if (any) {  // ~5 % of the blocks
 #pragma unroll
-                for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn, prefetch ? vf + (size_t)wbase * 4 : nullptr);
+                for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn, wbase, vf, map);
             }
             base += kViewBlock;
         } while (base < stop);
@@ -284,7 +412,8 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
         for (int e = 0; e < nmax; ++e) {  // lane-parallel resolution, ascending index per ray
             if (e >= qn) continue;
             const uint32_t ent = Q.q[e];
-            const int k = (int)(ent >> 8), idx = wbase + (int)(ent & 0xFFu);
+            const int k = (int)(ent >> 8), pos = wbase + (int)(ent & 0xFFu);
+            const int idx = map ? (int)map[pos] : pos;
             const d3 dk = d[k];  // FP64 ray data is indexed dynamically: it lives in local memory, not in K selects
             if (!no_filter) {
                 const ViewChord ch = view_chord(vf, idx, pick<K>(r, k), vb);
@@ -393,15 +522,16 @@ __device__ __noinline__ double march_list(const DevScene& sc, const uint16_t* li
 template <int K, bool kTri = false>
 __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float* __restrict__ vf, d3 Lp,
                                                       const ShadowRay (&ray)[K], double bias, bool no_filter, OccState (&st)[K],
-                                                      RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
-    const bool prefetch = true;  // vf is global memory
+                                                      RayLists<K>& lists, uint32_t& confirms, uint32_t& executed,
+                                                      const CullScratch* cull = nullptr) {
     uint32_t first[K];
     bool scanning[K];
-    const int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
+    const int ns_view = view_count<kTri>(sc);
+    int ns = ns_view, ns_pad = view_padded<kTri>(sc);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         if (!kTri) { lists.n[k] = 0; st[k] = occ_begin(ray[k].maxDist, bias, ray[k].cast); }
-        first[k] = (uint32_t)ns;
+        first[k] = (uint32_t)ns_view;
         scanning[k] = kTri ? !st[k].done : ray[k].cast;
     }
     if (ns > 0) {
@@ -417,6 +547,23 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
             tref[k] = (float)(ray[k].dist - bias * ray[k].ndl);
             tmax_lo[k] = __double2float_rd(ray[k].maxDist) - vb.slack;
             tmax_hi[k] = fmaxf(__double2float_ru(ray[k].maxDist) + vb.slack, bias_hi);  // also keeps every t <= bias (`near`)
+        }
+        const uint16_t* map = nullptr;  // culled: positions of the mini-view -> indices of the view
+        if (cull && !no_filter && ns_pad >= kCullMin) {
+            bool act[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) act[k] = !st[k].done;
+            int cnt = 0;
+            if (!kTri) executed += (uint32_t)(ns_pad >> 4);  // the warp's cull pass: ns_pad/32 cone-cone tests per lane, ~2x a ray test
+            if (cull_view<K>(view, ns_pad, r, act, *cull, cnt)) { view = cull->mini; map = cull->map; ns = cnt; ns_pad = (cnt + 31) & ~31; }
+#ifdef RTE_CULL_DEBUG
+            if ((threadIdx.x & 31) == 0) {
+                if (RTE_CULL_DEBUG == 1 && cnt == -1) confirms += 1;                 // tile cone too wide
+                if (RTE_CULL_DEBUG == 2 && cnt > kCullCap) confirms += 1;            // too many survivors
+                if (RTE_CULL_DEBUG == 3 && cnt >= 0 && cnt <= kCullCap) confirms += 1;  // culled
+                if (RTE_CULL_DEBUG == 4 && cnt >= 0 && cnt <= kCullCap) confirms += (uint32_t)cnt;  // survivors of culled scans
+            }
+#endif
         }
         CandQueue<K> Q;
         int qn = 0;
@@ -438,7 +585,7 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
                 }
                 if (any) {  // ~5 % of the blocks
 #pragma unroll
-                    for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn, prefetch ? vf + (size_t)wbase * 4 : nullptr);
+                    for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn, wbase, vf, map);
                 }
                 base += kViewBlock;
             } while (base < stop);
@@ -447,7 +594,8 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
             for (int e = 0; e < nmax; ++e) {  // lane-parallel resolution, canonical order per ray
                 if (e >= qn) continue;
                 const uint32_t ent = Q.q[e];
-                const int k = (int)(ent >> 8), idx = wbase + (int)(ent & 0xFFu);
+                const int k = (int)(ent >> 8), pos = wbase + (int)(ent & 0xFFu);
+                const int idx = map ? (int)map[pos] : pos;
                 bool dn = false;
 #pragma unroll
                 for (int i = 0; i < K; ++i) if (i == k) dn = st[i].done;

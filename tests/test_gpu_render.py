@@ -283,6 +283,30 @@ def test_fast_kernel_is_bit_identical(engine, oracle, cfg):
     assert sf["sphere_tests_executed"] > 0 or arrays.counts()["spheres"] == 0
 
 
+@pytest.mark.parametrize("cfg", ["c2", "c5_streamed", "c4_blob", "mixed"])
+def test_tile_culling_changes_nothing(engine, cfg):
+    """The lean kernel's per-tile culled mini-views (cone-cone test of every sphere against the warp's rays) against
+    RTE_FLAG_NO_CULL (every ray scans the full view): identical bits and counters, fewer executed tests."""
+    if cfg == "c2":
+        arrays, cam = scenes.config2(scale=0.2)
+    elif cfg == "c5_streamed":
+        arrays, cam = scenes.config5(scale=1 / 24)
+    elif cfg == "c4_blob":
+        arrays, cam = scenes.config4("blob", scale=0.15)
+    else:
+        arrays, cam = scenes.mixed_scene(256, 144, 128.0, n_spheres=400)
+    engine.upload(arrays, cam)
+    a = engine.render_host(outputs=("hdr64", "rgb8"), tonemap_op=_abi.TM_ACES)
+    sa = engine.stats()
+    b = engine.render_host(outputs=("hdr64", "rgb8"), tonemap_op=_abi.TM_ACES, flags=_abi.FLAG_NO_CULL)
+    sb = engine.stats()
+    assert np.array_equal(a["hdr64"], b["hdr64"]) and np.array_equal(a["rgb8"], b["rgb8"])
+    for k in COUNTERS:
+        assert sa[k] == sb[k], k
+    if arrays.counts()["spheres"] >= 128:  # (tiles of a small image span wide cones: the saving grows with the resolution)
+        assert sa["sphere_tests_executed"] < sb["sphere_tests_executed"], (sa["sphere_tests_executed"], sb["sphere_tests_executed"])
+
+
 def test_fast_kernel_stripes(engine):
     """Interleaved stripes through the fast kernel == the same rows of the full frame."""
     from raytracingengine_b200 import sharding
