@@ -114,6 +114,22 @@ class ClockSampler:
                 "samples": len(s), "power_w_max": round(self.power, 1)}
 
 
+def ncu_traffic(kernel_prefix: str):
+    """DRAM bytes (read + write) of one launch of a kernel from the newest committed `ncu --set full` capture
+    (profiles/*_traffic.json, written by tools/profile_summary.py for THIS workload), or None."""
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")), reverse=True):
+        try:
+            with open(path) as f:
+                d = json.load(f)
+        except (OSError, ValueError):
+            continue
+        for name, v in d.items():
+            if kernel_prefix in name:
+                return {"bytes": int(v["dram_bytes_read"] + v["dram_bytes_write"]), "source": os.path.relpath(path, ROOT), "kernel": name}
+    return None
+
+
 def visible_index(local_rank: int) -> int:
     """NVML index of cuda:local_rank (CUDA_VISIBLE_DEVICES may remap)."""
     vis = os.environ.get("CUDA_VISIBLE_DEVICES")
@@ -413,6 +429,7 @@ def run_gpu(args) -> None:
 
     pk, pk_src = peaks()
     clocks = sampler.summary()
+    tr_render, tr_tm = ncu_traffic("render_fast_kernel"), ncu_traffic("tonemap_kernel")
     flops = _abi.algorithmic_flops(sph_t, pl_t, tri_t)           # 20 / 14 / 46 flop per test
     achieved_tf = flops / world / (kern_ms * 1e-3) / 1e12       # per GPU: per-rank flops / slowest rank's kernel time
     clk = clocks.get("sm_mhz") or pk.get("sm_max_mhz", 1965.0)
@@ -436,7 +453,8 @@ def run_gpu(args) -> None:
         # per step and rank: one render kernel (+ max-luminance and tonemap kernels in the auto-white pipeline); memsets and NCCL are not ours
         "gpu_launches": args.steps * (3 if auto_white else 1),
         "roofline": {"bound": "fp32", "kernel": "rte::render_kernel", "achieved": round(achieved_tf, 3), "peak": round(fp32_peak_tf, 3),
-                     "unit": "TFLOP/s", "frac": round(achieved_tf / fp32_peak_tf, 4), "traffic": None,
+                     "unit": "TFLOP/s", "frac": round(achieved_tf / fp32_peak_tf, 4),
+                     "traffic": (tr_render or {}).get("bytes") if args.workload == "c2" and world == 1 else None, "traffic_capture": tr_render,
                      "peak_source": "FFMA micro-benchmark in this process (rte_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
                      "nominal_peak_at_sampled_clock": round(nominal_tf, 2), "ffma2_peak": round(fp32x2_peak_tf, 3),
                      "algorithmic_flop_per_launch": flops / world, "kernel_ms": round(kern_ms, 4),
@@ -445,7 +463,8 @@ def run_gpu(args) -> None:
                      "tests": {"sphere": sph_t, "plane": pl_t, "triangle": tri_t}, "fp64_confirms": confirms, "exact_marches": marches},
         "roofline_tonemap": {"bound": "hbm", "kernel": "rte::tonemap_kernel<all 7 operators>", "achieved": round(n_px * 33 / (tm_med * 1e-3) / 1e9, 1),
                              "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(n_px * 33 / (tm_med * 1e-3) / 1e9 / pk["hbm_gbs"], 4),
-                             "traffic": None, "peak_source": pk_src, "algorithmic_bytes_per_launch": n_px * 33, "kernel_ms": round(tm_med, 4),
+                             "traffic": (tr_tm or {}).get("bytes") if args.workload in ("c2", "c3") and world == 1 else None, "traffic_capture": tr_tm,
+                             "peak_source": pk_src, "algorithmic_bytes_per_launch": n_px * 33, "kernel_ms": round(tm_med, 4),
                              "l2": "input (16 B/px float4, two rotating buffers) and output (21 B/px) exceed L2; no flush"},
     }
     if not args.no_cpu_baseline and world == 1:

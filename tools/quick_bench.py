@@ -6,7 +6,7 @@ from raytracingengine_b200 import _abi, scenes
 from raytracingengine_b200.engine import Engine
 
 def main():
-    which = sys.argv[1:] or ["c2", "c3", "c4", "c5", "c1"]
+    which = [a for a in sys.argv[1:] if not a.startswith("--")] or ["c2", "c3", "c4", "c5", "c1"]
     e = Engine(0)
     for name in which:
         arrays, cam = {"c2": lambda: scenes.config2(), "c3": lambda: scenes.config3(), "c4": lambda: scenes.config4("blob"),
@@ -15,8 +15,9 @@ def main():
         n = cam.width * cam.height
         hdr = e.malloc(n * 16)
         rgb = [e.malloc(n * 3 + 16) for _ in range(7)]
+        full = "--rgb8" in sys.argv
         for it in range(3):
-            e.render_device({"hdr": hdr})
+            e.render_device({"hdr": hdr, "rgb8": rgb[0]} if full else {"hdr": hdr}, **({"tonemap_op": _abi.TM_ACES} if full else {}))
             s = e.stats()
         flops = _abi.algorithmic_flops(s["sphere_tests"], s["plane_tests"], s["triangle_tests"])
         rays = s["primary_rays"] + s["shadow_rays"] + s["secondary_rays"]
