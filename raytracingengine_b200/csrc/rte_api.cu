@@ -62,7 +62,7 @@ struct rte_ctx {
     rte_stats stats{};
 
     // staging for the *_host variants (grow-only)
-    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask;
+    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64;
     DevBuf s_tm_in, s_tm_out[RTE_TM_COUNT], s_q_o, s_q_d, s_q_m, s_q_out;
 };
 
@@ -221,7 +221,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
-                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -457,13 +457,32 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame) {
     p.out = *frame;
     p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
     if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
-    p.n_peers = p.tonemap_op == RTE_TM_NONE ? 0 : ctx->n_peers;
-    p.rgb8_words = ((uintptr_t)p.out.rgb8 & 3u) == 0 ? 1 : 0;
-    for (int i = 0; i < p.n_peers; ++i) p.peer_rgb8[i] = ctx->peer_rgb8[i];
+    // RGB8 (band buffer and / or registered peer frames) = the exact FP64 operator over the FP64 HDR of the render kernel, as
+    // a second, HBM-bound pass (rte_tonemap.cu: tonemap64_kernel) — the render kernels themselves only write HDR
+    Tonemap64Params tp{};
+    tp.n_peers = p.tonemap_op == RTE_TM_NONE ? 0 : ctx->n_peers;
+    const bool want_rgb8 = p.tonemap_op != RTE_TM_NONE && (p.out.rgb8 || tp.n_peers > 0) && o.n_rows > 0;
+    if (want_rgb8) {
+        const int64_t n_px = (int64_t)o.n_rows * ctx->cam.width;
+        if (!p.out.hdr64) {
+            int rc = reserve(ctx, ctx->s_tm64, (size_t)n_px * 24);
+            if (rc) return rc;
+            p.out.hdr64 = (double*)ctx->s_tm64.p;
+        }
+        if (p.out.rgb8 && ((uintptr_t)p.out.rgb8 & 3u) != 0 && (ctx->cam.width & 3) == 0)
+            return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 must be 4-byte aligned");
+        tp.hdr64 = p.out.hdr64; tp.n_pixels = n_px; tp.op = p.tonemap_op; tp.max_white = o.max_white; tp.jodie_a = o.jodie_a;
+        tp.rgb8 = p.out.rgb8;
+        for (int i = 0; i < tp.n_peers; ++i) tp.peer_rgb8[i] = ctx->peer_rgb8[i];
+        tp.W = ctx->cam.width; tp.row0 = o.row0; tp.stripe_rows = o.stripe_rows; tp.stripe_period = o.stripe_period;
+    }
+    p.out.rgb8 = nullptr;
+    p.tonemap_op = RTE_TM_NONE;
     RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));
     RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * kStatCount, ctx->stream));
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
     if (o.n_rows > 0) RTE_CUDA(ctx, launch_render(p, ctx->sm_count, ctx->stream));
+    if (want_rgb8) RTE_CUDA(ctx, launch_tonemap64(tp, ctx->sm_count, ctx->stream));
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
     RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));
     ctx->render_timed = true;

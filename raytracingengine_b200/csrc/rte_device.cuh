@@ -80,8 +80,12 @@ __device__ __forceinline__ d3 operator+(d3 a, d3 b) { return mk(a.x + b.x, a.y +
 __device__ __forceinline__ d3 operator-(d3 a, d3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }   // :16
 __device__ __forceinline__ d3 operator*(d3 a, double s) { return mk(a.x * s, a.y * s, a.z * s); }      // :18
 __device__ __forceinline__ d3 operator*(d3 a, d3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }   // :19
+// (measured: out-of-line copies of the FP64 division / square root shrink the kernels by 12 % but lose more in calls than
+// they win in instruction fetch on every config but one — they stay inline)
+__device__ __forceinline__ double div64(double a, double b) { return a / b; }
+__device__ __forceinline__ double sqrt64(double a) { return sqrt(a); }
 __device__ __forceinline__ d3 operator/(d3 a, double s) { return mk(a.x / s, a.y / s, a.z / s); }      // :21
-__device__ __forceinline__ d3 operator/(d3 a, d3 b) { return mk(a.x / b.x, a.y / b.y, a.z / b.z); }   // :20
+__device__ __forceinline__ d3 operator/(d3 a, d3 b) { return mk(div64(a.x, b.x), div64(a.y, b.y), div64(a.z, b.z)); }   // :20
 __device__ __forceinline__ d3 operator-(d3 a) { return mk(-a.x, -a.y, -a.z); }                         // :23
 __device__ __forceinline__ d3 adds(d3 a, double s) { return mk(a.x + s, a.y + s, a.z + s); }           // :15
 __device__ __forceinline__ d3 subs(d3 a, double s) { return mk(a.x - s, a.y - s, a.z - s); }           // :17
@@ -89,7 +93,7 @@ __device__ __forceinline__ double dot(d3 a, d3 b) { return a.x * b.x + a.y * b.y
 __device__ __forceinline__ d3 cross(d3 a, d3 b) {                                                       // :28
     return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
-__device__ __forceinline__ double length(d3 a) { return sqrt(dot(a, a)); }                             // :30
+__device__ __forceinline__ double length(d3 a) { return sqrt64(dot(a, a)); }                           // :30
 __device__ __forceinline__ d3 normalize(d3 a) {                                                         // :31-37
     const double len = length(a);
     if (len <= 1e-12) return mk(0.0, 0.0, 0.0);
@@ -105,7 +109,7 @@ __device__ __forceinline__ d3 refract(d3 self, d3 normal, double eta) {
     const double cosi = std_clamp(dot(I, N), -1.0, 1.0);
     const double k = 1.0 - eta * eta * (1.0 - cosi * cosi);
     if (k < 0.0) return mk(0.0, 0.0, 0.0);
-    return I * eta - N * (eta * cosi + sqrt(k));
+    return I * eta - N * (eta * cosi + sqrt64(k));
 }
 
 // the jitter stream of rte.h (rte_camera): sample s >= 1 of pixel y*W + x, axis 0 / 1
@@ -143,9 +147,9 @@ __device__ __forceinline__ bool sphere_exact(const double4 s, d3 o, d3 d, double
     const double c = dot(oc, oc) - s.w * s.w;
     const double disc = b * b - 4.0 * a * c;
     if (disc < 0.0) return false;
-    const double sq = sqrt(disc);
-    double t0 = (-b - sq) / (2.0 * a);
-    double t1 = (-b + sq) / (2.0 * a);
+    const double sq = sqrt64(disc);
+    double t0 = div64(-b - sq, 2.0 * a);
+    double t1 = div64(-b + sq, 2.0 * a);
     if (t0 > t1) { const double tmp = t0; t0 = t1; t1 = tmp; }
     double t = t0;
     if (t < 1e-6) { t = t1; if (t < 1e-6) return false; }
@@ -158,7 +162,7 @@ __device__ __forceinline__ bool plane_exact(const DevPlane& p, d3 o, d3 d, doubl
     const double denom = dot(n, d);
     if (fabs(denom) > 1e-6) {
         const d3 p0l0 = ld3(p.p0) - o;
-        const double t = dot(p0l0, n) / denom;
+        const double t = div64(dot(p0l0, n), denom);
         if (t >= 0.0) { t_out = t; return true; }
     }
     return false;
@@ -169,7 +173,7 @@ __device__ __forceinline__ bool tri_exact(const DevTri64& tr, d3 o, d3 d, double
     const d3 h = cross(d, e2);
     const double a = dot(e1, h);
     if (a > -1e-6 && a < 1e-6) return false;
-    const double f = 1.0 / a;
+    const double f = div64(1.0, a);
     const d3 s = o - ld3(tr.a0);
     const double u = f * dot(s, h);
     if (u < 0.0 || u > 1.0) return false;

@@ -41,11 +41,6 @@ struct RenderParams {
     int32_t force_general;   // RTE_FLAG_GENERAL_KERNEL: never take the lean fast kernel (validation)
     double bias, max_white, jodie_a;
     rte_frame out;           // device pointers, any may be NULL
-    // rte_set_rgb8_peers: full-frame RGB8 buffers (this GPU's and its peers', mapped over NVLink) that receive every
-    // rendered pixel at 3*(y*W + x), y = image row: the all-gather of the row stripes, fused into the render kernel
-    uint8_t* peer_rgb8[kMaxPeers];
-    int32_t n_peers;
-    int32_t rgb8_words;      // out.rgb8 and every peer frame are 4-byte aligned: full tile rows leave as 32-bit words
     int32_t cull;            // fast kernel: per-warp cull scratch follows the staged arrays in dynamic shared memory (rte_views.cuh)
     int32_t no_cull;         // RTE_FLAG_NO_CULL: never use it (validation / A-B)
     unsigned int* tile_counter;        // zeroed before launch
@@ -64,6 +59,21 @@ cudaError_t launch_intersect_closest(const DevScene& sc, int64_t n, const double
                                      rte_hit* hits, int sm_count, cudaStream_t stream);
 cudaError_t launch_intersect_any_before(const DevScene& sc, int64_t n, const double* origins, const double* dirs,
                                         const double* max_dist, uint8_t* out, int sm_count, cudaStream_t stream);
+
+// The exact (FP64) operator + quantiser of a render call: hdr64 (3 doubles per band pixel, written by the render kernel) ->
+// RGB8 in the band buffer and in every registered peer frame (rte_set_rgb8_peers: this GPU's and its peers' full frames,
+// mapped over NVLink; pixel (x, y) goes to 3*(y*W + x) — the all-gather of the row stripes, fused into this pass).
+struct Tonemap64Params {
+    const double* hdr64;
+    int64_t n_pixels;        // band pixels = n_rows * W
+    int32_t op;              // RTE_TM_*
+    double max_white, jodie_a;
+    uint8_t* rgb8;           // band-local, may be NULL
+    uint8_t* peer_rgb8[kMaxPeers];
+    int32_t n_peers;
+    int32_t W, row0, stripe_rows, stripe_period;  // band row -> image row (rte_render_opts)
+};
+cudaError_t launch_tonemap64(const Tonemap64Params& p, int sm_count, cudaStream_t stream);
 
 // tonemapAll / tonemap over a float4 HDR buffer (stand-alone HBM-bound pass)
 struct TonemapParams {

@@ -325,7 +325,7 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
                     if (j < 16) lmask[k] |= 1u << j;
                     const d3 emitted = ld3(sc.lights[j].E);
                     const double dist = sr[k].dist;
-                    const d3 contribution = (emitted * (1.0 / (dist * dist))) * sr[k].ndl;
+                    const d3 contribution = (emitted * div64(1.0, dist * dist)) * sr[k].ndl;
                     diffuseAcc[k] = diffuseAcc[k] + contribution * T[k];
                     if (kReflect) {
                         const rte_material& M = sc.materials[mat[k]];
@@ -334,7 +334,7 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
                             const double ndh = std_max(0.0, dot(normal[k], H));
                             if (ndh > 0.0) {
                                 const double specFactor = pow(ndh, M.shininess);
-                                specAcc[k] = specAcc[k] + ((emitted * (1.0 / (dist * dist))) * specFactor) * T[k];
+                                specAcc[k] = specAcc[k] + ((emitted * div64(1.0, dist * dist)) * specFactor) * T[k];
                             }
                         }
                     }
@@ -412,32 +412,6 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
     for (int k = 0; k < K; ++k) result[k] = acc[k];
 }
 
-// ------------------------------------------------------------------------------ RGB8 output
-// The 8 pixels of one tile row are 24 contiguous bytes.  Lanes exchange their packed pixels (q = r | g<<8 | b<<16)
-// so that the row leaves as six aligned 32-bit words (three of every four lanes store one word) instead of 24 byte
-// stores: fewer, fuller write sectors — which matters most for the stores that cross NVLink into the peers' frames.
-// Called by all 32 lanes.  words_ok is warp-uniform: the tile lies inside the image in x and rows are word aligned.
-__device__ __forceinline__ void store_rgb8(uint8_t* __restrict__ dst, uint32_t q, bool in_image, bool words_ok, int lx, int64_t pixel) {
-    const uint32_t qn = __shfl_down_sync(kFullMask, q, 1);
-    if (!in_image) return;
-    if (words_ok) {
-        const int j = lx & 3;
-        if (j < 3) {
-            const uint32_t w = __funnelshift_r(q | (qn << 24), qn >> 8, 8 * j);
-            __stcs(reinterpret_cast<uint32_t*>(dst + 3 * (pixel - lx)) + (lx >> 2) * 3 + j, w);
-        }
-    } else {
-        uint8_t* d = dst + 3 * pixel;
-        __stcs(d, (uint8_t)(q & 255u)); __stcs(d + 1, (uint8_t)((q >> 8) & 255u)); __stcs(d + 2, (uint8_t)(q >> 16));
-    }
-}
-// local band buffer (pixel index within the rendered rows) + every registered peer frame (index within the image)
-__device__ __forceinline__ void store_rgb8_all(const RenderParams& P, uint32_t q, bool in_image, bool words_ok, int lx, int64_t band_pixel, int64_t image_pixel) {
-    if (P.out.rgb8) store_rgb8(P.out.rgb8, q, in_image, words_ok, lx, band_pixel);
-#pragma unroll 1
-    for (int i = 0; i < P.n_peers; ++i) store_rgb8(P.peer_rgb8[i], q, in_image, words_ok, lx, image_pixel);
-}
-
 // ------------------------------------------------------------------------------ the kernel
 constexpr int kRenderThreads = 256;     // block size of the query kernels and of the render kernel at 2 CTAs/SM
 constexpr int kRenderMaxThreads = 512;  // render kernel at 1 CTA/SM (large scenes: more shared memory per CTA)
@@ -509,22 +483,12 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
             }
             n_in *= (uint32_t)aa;  // primary rays
         }
-        const bool words_ok = P.rgb8_words && (W & 3) == 0 && tx * kTileW + kTileW <= W;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
+            if (!inb[k]) continue;
             const int64_t oi = out_idx[k];
-            if (inb[k]) {
-                if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[oi] = make_float4((float)c[k].x, (float)c[k].y, (float)c[k].z, 0.f);
-                if (P.out.hdr64) { P.out.hdr64[3 * oi] = c[k].x; P.out.hdr64[3 * oi + 1] = c[k].y; P.out.hdr64[3 * oi + 2] = c[k].z; }
-            }
-            if (P.tonemap_op >= 0 && (P.out.rgb8 || P.n_peers > 0)) {
-                uint32_t q = 0;
-                if (inb[k]) {
-                    const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, c[k], P.max_white, P.jodie_a));
-                    q = (uint32_t)u.x | ((uint32_t)u.y << 8) | ((uint32_t)u.z << 16);
-                }
-                store_rgb8_all(P, q, inb[k], words_ok, lx, oi, (int64_t)py[k] * W + px[k]);
-            }
+            if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[oi] = make_float4((float)c[k].x, (float)c[k].y, (float)c[k].z, 0.f);
+            if (P.out.hdr64) { P.out.hdr64[3 * oi] = c[k].x; P.out.hdr64[3 * oi + 1] = c[k].y; P.out.hdr64[3 * oi + 2] = c[k].z; }
         }
         // per-warp statistics: one REDUX per counter, lane 0 accumulates in shared memory
         const uint32_t v[kStatCount] = {n_in, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms, cnt.sph_exec};
@@ -773,7 +737,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
             cnt.shadow += 1;
             if (T > bias) {
                 const d3 emitted = ld3(sc.lights[j].E);
-                const d3 contribution = (emitted * (1.0 / (r.dist * r.dist))) * r.ndl;
+                const d3 contribution = (emitted * div64(1.0, r.dist * r.dist)) * r.ndl;
                 diffuse[k] = diffuse[k] + contribution * T;
             }
         }
@@ -882,25 +846,15 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             }
             n_in *= (uint32_t)aa;  // primary rays
         }
-        const bool words_ok = P.rgb8_words && (W & 3) == 0 && tx * kTileW + kTileW <= W;
-        const bool want_rgb8 = P.tonemap_op >= 0 && (P.out.rgb8 || P.n_peers > 0);
 #pragma unroll 1
         for (int k = 0; k < K; ++k) {
+            if (!inb[k]) continue;
             const int band_y = ty * TH + k * kTileH + ly;
             const int64_t oi = (int64_t)band_y * W + px[k];
             const d3 v = c[k];
-            const bool in = inb[k];
             // streaming stores (st.global.cs): the framebuffers are write-once and must not evict the threads' local memory from L2
-            if (in && P.out.hdr) __stcs(reinterpret_cast<float4*>(P.out.hdr) + oi, make_float4((float)v.x, (float)v.y, (float)v.z, 0.f));
-            if (in && P.out.hdr64) { __stcs(P.out.hdr64 + 3 * oi, v.x); __stcs(P.out.hdr64 + 3 * oi + 1, v.y); __stcs(P.out.hdr64 + 3 * oi + 2, v.z); }
-            if (want_rgb8) {
-                uint32_t q = 0;
-                if (in) {
-                    const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));
-                    q = (uint32_t)u.x | ((uint32_t)u.y << 8) | ((uint32_t)u.z << 16);
-                }
-                store_rgb8_all(P, q, in, words_ok, lx, oi, (int64_t)py[k] * W + px[k]);
-            }
+            if (P.out.hdr) __stcs(reinterpret_cast<float4*>(P.out.hdr) + oi, make_float4((float)v.x, (float)v.y, (float)v.z, 0.f));
+            if (P.out.hdr64) { __stcs(P.out.hdr64 + 3 * oi, v.x); __stcs(P.out.hdr64 + 3 * oi + 1, v.y); __stcs(P.out.hdr64 + 3 * oi + 2, v.z); }
         }
         const uint32_t v[kStatCount] = {n_in, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms, cnt.sph_exec};
 #pragma unroll

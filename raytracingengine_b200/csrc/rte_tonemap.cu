@@ -100,6 +100,59 @@ cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t st
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------ exact pass of a render call
+// One thread = 4 consecutive band pixels: 12 doubles in (streaming loads), tm64 (the reference's FP64 evaluation order),
+// 12 bytes = 3 aligned words out — to the band buffer and to every peer frame.  HBM-bound: 96 B read + 12 B written per
+// thread; kept out of the render kernel because that kernel is bound by instruction fetch.
+__global__ void __launch_bounds__(kTmThreads) tonemap64_kernel(const __grid_constant__ Tonemap64Params P) {
+    const int64_t n = P.n_pixels;
+    const int W = P.W;
+    const bool words = (W & 3) == 0;  // a quad never straddles two rows, rows are word aligned
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; 4 * q < n; q += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t p0 = 4 * q;
+        const int cnt = (int)(n - p0 < 4 ? n - p0 : 4);
+        uint32_t px[4] = {0, 0, 0, 0};
+        for (int j = 0; j < cnt; ++j) {
+            const double* h = P.hdr64 + 3 * (p0 + j);
+            const d3 v = mk(__ldcs(h), __ldcs(h + 1), __ldcs(h + 2));
+            const uchar3 u = tm64::to_color(tm64::apply(P.op, v, P.max_white, P.jodie_a));
+            px[j] = (uint32_t)u.x | ((uint32_t)u.y << 8) | ((uint32_t)u.z << 16);
+        }
+        const uint32_t w0 = px[0] | (px[1] << 24), w1 = (px[1] >> 8) | (px[2] << 16), w2 = (px[2] >> 16) | (px[3] << 8);
+        // image position of the quad's first pixel (peer frames hold the whole image)
+        const int64_t band_y = p0 / W;
+        const int x = (int)(p0 - band_y * W);
+        const int sr = P.stripe_rows, sp = P.stripe_period;
+        const int64_t y = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
+        const int64_t ip0 = y * W + x;
+        if (words && cnt == 4) {
+            if (P.rgb8) { uint32_t* d = reinterpret_cast<uint32_t*>(P.rgb8 + 3 * p0); __stcs(d, w0); __stcs(d + 1, w1); __stcs(d + 2, w2); }
+            for (int i = 0; i < P.n_peers; ++i) {
+                uint32_t* d = reinterpret_cast<uint32_t*>(P.peer_rgb8[i] + 3 * ip0);
+                __stcs(d, w0); __stcs(d + 1, w1); __stcs(d + 2, w2);
+            }
+        } else {
+            for (int j = 0; j < cnt; ++j) {
+                const int64_t pj = p0 + j, by = pj / W;
+                const int64_t ipj = (P.row0 + (sr > 0 ? (by / sr) * sp + by % sr : by)) * W + (pj - by * W);
+                const uint8_t b0 = (uint8_t)(px[j] & 255u), b1 = (uint8_t)((px[j] >> 8) & 255u), b2 = (uint8_t)(px[j] >> 16);
+                if (P.rgb8) { uint8_t* d = P.rgb8 + 3 * pj; d[0] = b0; d[1] = b1; d[2] = b2; }
+                for (int i = 0; i < P.n_peers; ++i) { uint8_t* d = P.peer_rgb8[i] + 3 * ipj; d[0] = b0; d[1] = b1; d[2] = b2; }
+            }
+        }
+    }
+}
+
+cudaError_t launch_tonemap64(const Tonemap64Params& p, int sm_count, cudaStream_t stream) {
+    if (p.n_pixels <= 0 || (!p.rgb8 && p.n_peers == 0)) return cudaSuccess;
+    const int64_t quads = (p.n_pixels + 3) / 4;
+    int64_t blocks = (quads + kTmThreads - 1) / kTmThreads;
+    const int64_t cap = (int64_t)sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    tonemap64_kernel<<<(unsigned)blocks, kTmThreads, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
 // max over pixels of luminance() (RE/RaytracingEngine.cpp:100-104); non-negative floats order like their bits
 __global__ void __launch_bounds__(kTmThreads) max_luminance_kernel(const float4* __restrict__ hdr, int64_t n, unsigned int* out_bits) {
     float m = 0.0f;

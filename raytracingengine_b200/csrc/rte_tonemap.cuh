@@ -63,7 +63,9 @@ __device__ __forceinline__ d3 uncharted2(d3 c) {
     const d3 whiteScale = mk(1.0, 1.0, 1.0) / uncharted2_partial(mk(11.2, 11.2, 11.2));
     return curr * whiteScale;
 }
-__device__ __forceinline__ d3 apply(int op, d3 c, double max_white, double a) {
+// one out-of-line copy: the fused epilogue runs it once per pixel, and inlining seven operators (pow / log included)
+// into the render kernels only adds to their instruction footprint
+static __device__ __noinline__ d3 apply(int op, d3 c, double max_white, double a) {
     switch (op) {
         case RTE_TM_SIMPLE: return simple(c);
         case RTE_TM_REINHARD_SIMPLE: return reinhard(c);
@@ -75,9 +77,14 @@ __device__ __forceinline__ d3 apply(int op, d3 c, double max_white, double a) {
     }
 }
 // toColor, :113-121: clamp to [0,1], * 255.0, truncate
+// static_cast<uint8_t>(c * 255.0) for c in [0,1] without a double -> integer conversion instruction: adding 2^52 with
+// round-towards-zero leaves floor(c * 255.0) in the low mantissa bits
+__device__ __forceinline__ unsigned char trunc_byte(double c01) {
+    return (unsigned char)(__double2loint(__dadd_rz(c01 * 255.0, 4503599627370496.0)) & 0xFF);
+}
 __device__ __forceinline__ uchar3 to_color(d3 p) {
     const d3 c = clamp3(p, 0.0, 1.0);
-    return make_uchar3((unsigned char)(c.x * 255.0), (unsigned char)(c.y * 255.0), (unsigned char)(c.z * 255.0));
+    return make_uchar3(trunc_byte(c.x), trunc_byte(c.y), trunc_byte(c.z));
 }
 
 }  // namespace tm64
