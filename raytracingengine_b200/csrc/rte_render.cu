@@ -47,10 +47,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
 
 constexpr uint32_t kTmaChunk = 32768;
 constexpr int kMaxTreeDepth = RTE_MAX_DEPTH;  // rte.h: largest opts.max_depth (frames of the per-pixel TraceRay stack)
+// Pixels per thread of the view-mode render kernel (a warp's tile is 8 x 4K pixels).  Measured on B200: with resident views one
+// pixel per thread is fastest (fewer live registers, tighter ray cones for the tile cull: C2 4.78 -> 4.60 ms, C4 1.40 -> 0.95 ms);
+// with streamed views every tile pays one pass over ALL view blocks, so two pixels per thread halve that cost (C5 19.1 -> 15.8 ms).
 #ifndef RTE_VIEW_PIXELS
-#define RTE_VIEW_PIXELS 2
+#define RTE_VIEW_PIXELS 1
 #endif
-constexpr int kViewPixels = RTE_VIEW_PIXELS;  // pixels per thread of the view-mode render kernel
+#ifndef RTE_STREAM_PIXELS
+#define RTE_STREAM_PIXELS 2
+#endif
+constexpr int kViewPixels = RTE_VIEW_PIXELS;
+constexpr int kStreamPixels = RTE_STREAM_PIXELS;
 
 // Dynamic shared memory layout of the render kernel: [views (1+nl) x ns_pad x 16 B][generic sph32][tri32].
 // The generic sphere array is only staged when something can use it often (reflection rays, or no views);
@@ -751,25 +758,33 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
     }
 }
 
+// Block shape of the fast kernel with resident views, measured on B200 (C2 at 4K, one pixel per thread): 320 x 2 CTAs 4.59 ms,
+// 512 x 1 4.11, 768 x 1 4.17, 1024 x 1 3.82.  The kernel waits on instruction fetch and local-memory latency, so 32 resident
+// warps at 64 registers beat 16-20 warps at 96-128 registers despite the extra spills, and one CTA stages the views once per SM.
 #ifndef RTE_FAST_THREADS
-#define RTE_FAST_THREADS 320
+#define RTE_FAST_THREADS 1024
 #endif
 #ifndef RTE_FAST_MINB
-#define RTE_FAST_MINB 2
+#define RTE_FAST_MINB 1
 #endif
 constexpr int kFastThreads = RTE_FAST_THREADS;  // block size of the fast kernel when kFastMinBlocks CTAs fit one SM
 constexpr int kFastMinBlocks = RTE_FAST_MINB;
+#ifndef RTE_BIG_THREADS
+#define RTE_BIG_THREADS 512
+#endif
+constexpr int kBigThreads = RTE_BIG_THREADS;  // block size of the streamed-view variant (two pixels per thread: 512 x 128 registers
+                                              // 15.7 ms on C5 at 4K, 768 x 80 17.5, 1024 x 64 17.9)
 
 // kBig = false: kFastThreads x kFastMinBlocks CTAs per SM; kBig = true: one 512-thread CTA per SM (views of large scenes)
 // kStream = true (implies kBig): the views pass through two shared-memory buffers (ViewsStream), tile batches are CTA-uniform
 template <int K, bool kBig, bool kStream, bool kTris = false>
-__global__ void __launch_bounds__(kBig ? kRenderMaxThreads : kFastThreads, kBig ? 1 : kFastMinBlocks)
+__global__ void __launch_bounds__(kBig ? kBigThreads : kFastThreads, kBig ? 1 : kFastMinBlocks)
 render_fast_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ DevScene s_sc;
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ __align__(8) uint64_t s_vbar[2];
-    __shared__ unsigned long long s_stats[kRenderMaxThreads / 32][kStatCount];
+    __shared__ unsigned long long s_stats[(kBig ? kBigThreads : kFastThreads) / 32][kStatCount];
 
     if (threadIdx.x == 0) s_sc = P.sc;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -888,7 +903,8 @@ cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double 
 // `cull_ok`: the kernel can use per-warp cull scratch (the fast kernel); it is granted when it fits next to the staged arrays
 // without lowering the number of CTAs per SM.
 static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int small_threads, int small_min_blocks, int K,
-                                    const RenderParams& p0, int sm_count, cudaStream_t stream, bool cull_ok = false, size_t smem_limit = 0) {
+                                    const RenderParams& p0, int sm_count, cudaStream_t stream, bool cull_ok = false, size_t smem_limit = 0,
+                                    int big_threads = kRenderMaxThreads) {
     RenderParams p = p0;
     p.cull = 0;
     size_t smem = p.plan.total;
@@ -900,7 +916,7 @@ static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int smal
     if (e != cudaSuccess) return e;
     if (per_sm < small_min_blocks) {
         fn = fn_big;
-        threads = kRenderMaxThreads;
+        threads = big_threads;
         if ((e = ensure_smem(fn, smem)) != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, threads, smem);
         if (e != cudaSuccess) return e;
@@ -941,17 +957,17 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
         int dev = 0, optin = 0;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-        const size_t limit = optin > 2048 ? (size_t)optin - 2048 : 0;  // static shared memory of the kernel
+        const size_t limit = optin > 4096 ? (size_t)optin - 4096 : 0;  // static shared memory of the kernel
         if (p.plan.stream_views) {
-            const void* fn = (const void*)render_fast_kernel<kViewPixels, true, true>;
-            return launch_render_fn(fn, fn, kRenderMaxThreads, 1, kViewPixels, p, sm_count, stream, true, limit);
+            const void* fn = (const void*)render_fast_kernel<kStreamPixels, true, true>;
+            return launch_render_fn(fn, fn, kBigThreads, 1, kStreamPixels, p, sm_count, stream, true, limit, kBigThreads);
         }
         if (p.sc.nt > 0)
             return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false, true>,
                                     (const void*)render_fast_kernel<kViewPixels, true, false, true>, kFastThreads, kFastMinBlocks, kViewPixels, p,
-                                    sm_count, stream, true, limit);
+                                    sm_count, stream, true, limit, kBigThreads);
         return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false>, (const void*)render_fast_kernel<kViewPixels, true, false>,
-                                kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream, true, limit);
+                                kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream, true, limit, kBigThreads);
     }
     const void* fn = p.sc.reflective ? (const void*)render_kernel<1, true> : (const void*)render_kernel<1, false>;
     return launch_render_fn(fn, fn, kRenderThreads, 2, 1, p, sm_count, stream);

@@ -22,4 +22,6 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:rend
 echo "exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:tonemap_kernel -c 1 -f -o $OUT/${TAG}_tonemap $CMD > $OUT/${TAG}_ncu_full_tm.log 2>&1
 echo "exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:tonemap64 -s 3 -c 1 -f -o $OUT/${TAG}_tonemap64 $CMD > $OUT/${TAG}_ncu_full_tm64.log 2>&1
+echo "exit $?"
 ls -la $OUT
