@@ -94,10 +94,26 @@ __device__ __forceinline__ d3 cross(d3 a, d3 b) {                               
     return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
 __device__ __forceinline__ double length(d3 a) { return sqrt64(dot(a, a)); }                           // :30
+// {a / |a|, |a|} — optionally as ONE out-of-line copy (RTE_UNIT_OL): a square root and three divisions are ~100 SASS
+// instructions, and the render kernels normalise at five places per ray
+struct d4 { double x, y, z, w; };
+#ifndef RTE_UNIT_OL
+#define RTE_UNIT_OL 1
+#endif
+#if RTE_UNIT_OL
+static __device__ __noinline__ d4 unit_len(d3 a) {
+#else
+__device__ __forceinline__ d4 unit_len(d3 a) {
+#endif
+    d4 r;
+    r.w = length(a);
+    r.x = a.x / r.w; r.y = a.y / r.w; r.z = a.z / r.w;
+    return r;
+}
 __device__ __forceinline__ d3 normalize(d3 a) {                                                         // :31-37
-    const double len = length(a);
-    if (len <= 1e-12) return mk(0.0, 0.0, 0.0);
-    return a / len;
+    const d4 u = unit_len(a);
+    if (u.w <= 1e-12) return mk(0.0, 0.0, 0.0);
+    return mk(u.x, u.y, u.z);
 }
 __device__ __forceinline__ d3 reflect(d3 i, d3 n) { return i - (n * 2.0) * dot(i, n); }                // :39-41
 __device__ __forceinline__ double std_max(double a, double b) { return (a < b) ? b : a; }              // std::max
@@ -157,7 +173,14 @@ __device__ __forceinline__ bool sphere_exact(const double4 s, d3 o, d3 d, double
     return true;
 }
 // Plane::Intersect, RE/Shape.h:149-159
+#ifndef RTE_PLANE_OL
+#define RTE_PLANE_OL 0
+#endif
+#if RTE_PLANE_OL
+static __device__ __noinline__ bool plane_exact(const DevPlane& p, d3 o, d3 d, double& t_out) {
+#else
 __device__ __forceinline__ bool plane_exact(const DevPlane& p, d3 o, d3 d, double& t_out) {
+#endif
     const d3 n = ld3(p.n);
     const double denom = dot(n, d);
     if (fabs(denom) > 1e-6) {

@@ -660,12 +660,13 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
 #pragma unroll 1
         for (int k = 0; k < K; ++k) {
             const d3 vecToLight = Lp - Pn[k];
-            const double dist = length(vecToLight);
+            const d4 vl = unit_len(vecToLight);
+            const double dist = vl.w;
             bool cast = hitv[k] && dist > 0.0;
             d3 L = mk(0, 0, 1);
             double ndl = 0.0;
             if (cast) {
-                L = vecToLight / dist;
+                L = mk(vl.x, vl.y, vl.z);  // vecToLight / dist
                 ndl = std_max(0.0, dot(normal[k], L));
                 cast = ndl > 0.0 && dist > bias;
             }
@@ -766,6 +767,9 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
 #endif
 #ifndef RTE_FAST_MINB
 #define RTE_FAST_MINB 1
+#endif
+#ifndef RTE_STATS_SEL
+#define RTE_STATS_SEL 1
 #endif
 constexpr int kFastThreads = RTE_FAST_THREADS;  // block size of the fast kernel when kFastMinBlocks CTAs fit one SM
 constexpr int kFastMinBlocks = RTE_FAST_MINB;
@@ -872,11 +876,21 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             if (P.out.hdr64) { __stcs(P.out.hdr64 + 3 * oi, v.x); __stcs(P.out.hdr64 + 3 * oi + 1, v.y); __stcs(P.out.hdr64 + 3 * oi + 2, v.z); }
         }
         const uint32_t v[kStatCount] = {n_in, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms, cnt.sph_exec};
+#if RTE_STATS_SEL
+        uint32_t mine = 0;  // lane k keeps the warp's sum of counter k: one shared-memory update per tile instead of kStatCount
+#pragma unroll
+        for (int k = 0; k < kStatCount; ++k) {
+            const uint32_t s = __reduce_add_sync(kFullMask, v[k]);
+            if (lane == k) mine = s;
+        }
+        if (lane < kStatCount) s_stats[warp][lane] += mine;
+#else
 #pragma unroll
         for (int k = 0; k < kStatCount; ++k) {
             const uint32_t s = __reduce_add_sync(kFullMask, v[k]);
             if (lane == 0) s_stats[warp][k] += s;
         }
+#endif
         tile = __shfl_sync(kFullMask, next, 0);
     }
     if (kStream) views_str.drain();

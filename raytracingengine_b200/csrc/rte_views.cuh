@@ -219,6 +219,13 @@ __device__ __forceinline__ ViewChord view_chord(const float* __restrict__ view, 
 // Conservative like the per-ray test (bounds rounded outwards); the survivors keep their ascending index order, so the
 // resolution still sees candidates in canonical order.  Tiles whose rays diverge (silhouettes: cos tt < kCullMinCos) or
 // with more than kCullCap survivors scan the full view as before.
+#ifndef RTE_CULL_UNROLL
+#define RTE_CULL_UNROLL 1  // measured: 1 -> 3.68 ms, 2 -> 4.07, 4 -> 4.29 on C2 (the kernel waits on instruction fetch)
+#endif
+constexpr int kCullUnroll = RTE_CULL_UNROLL;
+#ifndef RTE_CULL_PF
+#define RTE_CULL_PF 0
+#endif
 constexpr int kCullCap = 128;         // survivors per (tile, view)
 constexpr int kCullMin = 128;         // views with fewer entries are scanned directly
 constexpr float kCullMinCos = 0.5f;   // tile cones wider than 60 degrees are not worth testing
@@ -231,49 +238,95 @@ struct CullScratch {
 // Tests the n_pad entries of `view` against the tile cone (ax,ay,az | ct = lower bound of cos tt, st2 = upper bound of
 // sin^2 tt) and packs the survivors.  All 32 lanes; returns the survivor count (> kCullCap: overflow, scratch unusable).
 // No square root: with x = c.a - cos ts cos tt (+ slack), the entry survives iff x >= 0 or x^2 <= sin^2 ts sin^2 tt.
-__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
-    return v;
+// Both spheres of a pair at once (packed FP32x2, SASS FFMA2): with cs = -w (a lower bound of cos ts),
+//     x   = c.a + 4e-6 + w ct            >= the exact c.a - cos ts cos tt
+//     rhs = st2' (1 - w^2) + 1e-12       >= sin^2 ts sin^2 tt          (st2' = st2 * 1.00001)
+//     y   = x^2 - rhs
+// and the entry survives iff x >= 0 or y < 0, i.e. iff sign(x) is clear or sign(y) is set.  (y == 0 may be rejected: rhs is
+// inflated by 1e-5 relative, far more than the rounding of x^2.)  The special entries need no test of their own: the origin
+// inside a sphere (w = 4) gives x >= 4 ct - 1 > 0 because ct >= kCullMinCos = 0.5, padding (w = -inf) gives x = -inf, y = +inf.
+struct CullCone {
+    f32x2 ax, ay, az, ct, slack, st2p, nrc;  // nrc = -(st2' + 1e-12)
+};
+__device__ __forceinline__ CullCone make_cull_cone(float ax, float ay, float az, float ct, float st2) {
+    const float st2p = st2 * 1.00001f, nrc = -(st2p + 1e-12f);
+    CullCone c;
+    c.ax = pack2(ax, ax); c.ay = pack2(ay, ay); c.az = pack2(az, az); c.ct = pack2(ct, ct);
+    c.slack = pack2(4e-6f, 4e-6f); c.st2p = pack2(st2p, st2p); c.nrc = pack2(nrc, nrc);
+    return c;
 }
-__device__ __forceinline__ bool cull_keep(float cx, float cy, float cz, float w, float ax, float ay, float az, float ct, float st2) {
-    const float cs = -w;  // = cos ts - kConeMargin: a lower bound of cos ts
-    const float d = __fmaf_rn(cz, az, __fmaf_rn(cy, ay, cx * ax));
-    const float x = __fmaf_rn(-cs, ct, d) + 4e-6f;                       // >= the exact c.a - cos ts cos tt
-    const float rhs = __fmaf_rn(-cs * cs, st2, st2) * 1.00001f + 1e-12f;  // >= sin^2 ts sin^2 tt
-    const bool hit = (x >= 0.0f) | (x * x <= rhs);
-    return (w >= 2.0f) | (hit & (w > -2.0f));  // w = 4: origin inside the sphere, always; w = -inf: padding, never
+// A = {cx0,cx1 | cy0,cy1}, B = {cz0,cz1 | w0,w1}; the sign bit of k0 / k1 says "keep"
+__device__ __forceinline__ void cull_keep2(const ulonglong2& A, const ulonglong2& B, const CullCone& c, uint32_t& k0, uint32_t& k1) {
+    f32x2 x = fma2(A.x, c.ax, c.slack);
+    x = fma2(A.y, c.ay, x);
+    x = fma2(B.x, c.az, x);
+    x = fma2(B.y, c.ct, x);
+    const f32x2 nrhs = fma2(mul2(B.y, B.y), c.st2p, c.nrc);  // -(st2' (1 - w^2) + 1e-12)
+    const f32x2 y = fma2(x, x, nrhs);
+    uint32_t x0, x1, y0, y1;
+    unpack2_bits(x, x0, x1);
+    unpack2_bits(y, y0, y1);
+    k0 = ~x0 | y0;
+    k1 = ~x1 | y1;
+}
+__device__ __forceinline__ ulonglong2 lds_u2(uint32_t addr) {
+    ulonglong2 v;
+    asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr) : "memory");
+    return v;
 }
 __device__ __forceinline__ void cull_store(float* __restrict__ mf, uint16_t* __restrict__ map, int pos, float cx, float cy, float cz, float w, int idx) {
     float* e = mf + (size_t)(pos >> 1) * 8 + (pos & 1);
     e[0] = cx; e[2] = cy; e[4] = cz; e[6] = w;
     map[pos] = (uint16_t)idx;
 }
-__device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float ct, float st2,
+// `md`: this lane's smallest u.a over its active rays (1 if it has none).  Returns -1 when the tile cone is too wide to be worth testing.
+__device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float md,
                                       ulonglong2* __restrict__ mini, uint16_t* __restrict__ map) {
+    // min over the warp with one REDUX: non-negative floats order like their bit patterns (a negative dot clamps to 0: too wide anyway)
+    md = __uint_as_float(__reduce_min_sync(kFullMask, __float_as_uint(fmaxf(md, 0.0f))));
+    const float ct = md * 0.999998f - 2e-6f;  // lower bound of cos(tile half-angle): |a|, |u| and the dots are off by < 1e-6
+    if (!(ct >= kCullMinCos)) return -1;
+    const float st2 = fmaxf(1.0f - ct * ct, 0.0f) * 1.00001f + 1e-12f;  // upper bound of sin^2(tile half-angle)
     const int lane = threadIdx.x & 31;
     const uint32_t lt = (1u << lane) - 1u;
-    const int n_pairs = n_pad >> 1;
+    const int n_pairs = n_pad >> 1;  // a multiple of 16
     float* mf = reinterpret_cast<float*>(mini);
     const uint32_t v0 = (uint32_t)__cvta_generic_to_shared(view);  // the views live in shared memory
+    const CullCone cone = make_cull_cone(ax, ay, az, ct, st2);
     int count = 0;
-#pragma unroll 1
+#if RTE_CULL_PF
+    // software pipelining: the pair of the next group is loaded before this one is tested (the loop is latency bound: one LDS,
+    // then a chain of five dependent FFMA2)
+    ulonglong2 An, Bn;
+    {
+        const int p = min(lane, n_pairs - 1);
+        An = lds_u2(v0 + 32u * (uint32_t)p); Bn = lds_u2(v0 + 32u * (uint32_t)p + 16u);
+    }
+#endif
+#pragma unroll kCullUnroll
     for (int p0 = 0; p0 < n_pairs; p0 += 32) {
-        const int p = p0 + lane;
-        bool k0 = false, k1 = false;
-        float4 A = make_float4(0.f, 0.f, 0.f, 0.f), B = A;  // A = {cx0,cx1,cy0,cy1}, B = {cz0,cz1,w0,w1}
-        if (p < n_pairs) {
-            A = lds_f4(v0 + 32u * (uint32_t)p);
-            B = lds_f4(v0 + 32u * (uint32_t)p + 16u);
-            k0 = cull_keep(A.x, A.z, B.x, B.z, ax, ay, az, ct, st2);
-            k1 = cull_keep(A.y, A.w, B.y, B.w, ax, ay, az, ct, st2);
+        const int p = min(p0 + lane, n_pairs - 1);  // (the last group of a view of 32 (mod 64) entries: the upper lanes repeat its last pair)
+#if RTE_CULL_PF
+        const ulonglong2 A = An, B = Bn;
+        {
+            const int pn = min(p0 + 32 + lane, n_pairs - 1);
+            An = lds_u2(v0 + 32u * (uint32_t)pn); Bn = lds_u2(v0 + 32u * (uint32_t)pn + 16u);
         }
-        const uint32_t m0 = __ballot_sync(kFullMask, k0), m1 = __ballot_sync(kFullMask, k1);
-        if ((m0 | m1) != 0u) {  // warp-uniform; most groups of 64 spheres have no survivor
+#else
+        const ulonglong2 A = lds_u2(v0 + 32u * (uint32_t)p), B = lds_u2(v0 + 32u * (uint32_t)p + 16u);
+#endif
+        uint32_t kw0, kw1;
+        cull_keep2(A, B, cone, kw0, kw1);
+        if (p0 + lane >= n_pairs) kw0 = kw1 = 0u;
+        if (__any_sync(kFullMask, (int)(kw0 | kw1) < 0)) {  // warp-uniform; ~10 % of the groups of 64 spheres have a survivor
+            const bool k0 = (int)kw0 < 0, k1 = (int)kw1 < 0;
+            const uint32_t m0 = __ballot_sync(kFullMask, k0), m1 = __ballot_sync(kFullMask, k1);
+            uint32_t a0, a1, a2, a3, b0, b1, b2, b3;  // A = {cx0,cx1,cy0,cy1}, B = {cz0,cz1,w0,w1}
+            unpack2_bits(A.x, a0, a1); unpack2_bits(A.y, a2, a3); unpack2_bits(B.x, b0, b1); unpack2_bits(B.y, b2, b3);
             const int pos = count + __popc(m0 & lt) + __popc(m1 & lt);
-            if (k0 && pos < kCullCap) cull_store(mf, map, pos, A.x, A.z, B.x, B.z, 2 * p);
+            if (k0 && pos < kCullCap) cull_store(mf, map, pos, __uint_as_float(a0), __uint_as_float(a2), __uint_as_float(b0), __uint_as_float(b2), 2 * p);
             const int pos1 = pos + (k0 ? 1 : 0);
-            if (k1 && pos1 < kCullCap) cull_store(mf, map, pos1, A.y, A.w, B.y, B.w, 2 * p + 1);
+            if (k1 && pos1 < kCullCap) cull_store(mf, map, pos1, __uint_as_float(a1), __uint_as_float(a3), __uint_as_float(b1), __uint_as_float(b3), 2 * p + 1);
             count += __popc(m0) + __popc(m1);
             if (count > kCullCap) return count;
         }
@@ -289,6 +342,20 @@ __device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n
     return count;
 }
 
+// Axis of the tile cone: the normalised sum of the active rays' directions (any unit vector would do: the half-angle is
+// measured against it afterwards).  The three sums go through integer REDUX (fixed point, 2^-22: exact enough for an axis)
+// instead of 15 shuffles.  One out-of-line copy; returns w = 0 when there is no active ray or the directions cancel.
+__device__ __noinline__ float4 cull_axis(float sx, float sy, float sz) {
+    const float kScale = 4194304.0f, kInv = 1.0f / 4194304.0f;  // |sum over the warp| <= 32 K <= 2^7: fits 2^29
+    const float fx = (float)__reduce_add_sync(kFullMask, __float2int_rn(sx * kScale)) * kInv;
+    const float fy = (float)__reduce_add_sync(kFullMask, __float2int_rn(sy * kScale)) * kInv;
+    const float fz = (float)__reduce_add_sync(kFullMask, __float2int_rn(sz * kScale)) * kInv;
+    const float l2 = __fmaf_rn(fz, fz, __fmaf_rn(fy, fy, fx * fx));
+    if (!(l2 > 1e-6f)) return make_float4(0.f, 0.f, 0.f, 0.f);
+    const float inv = rsqrtf(l2);
+    return make_float4(fx * inv, fy * inv, fz * inv, 1.0f);  // |a| = 1 +- 5e-7
+}
+
 // Tile cone of the active rays of the warp, then cull_pack.  Returns true when `cs` holds a usable mini-view of `count`
 // entries.  All 32 lanes call it.
 template <int K>
@@ -299,29 +366,15 @@ __device__ __forceinline__ bool cull_view(const ulonglong2* __restrict__ view, i
     for (int k = 0; k < K; ++k) {
         if (active[k]) { sx += r[k].ux; sy += r[k].uy; sz += r[k].uz; }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        sx += __shfl_xor_sync(kFullMask, sx, o); sy += __shfl_xor_sync(kFullMask, sy, o); sz += __shfl_xor_sync(kFullMask, sz, o);
-    }
-    const float l2 = __fmaf_rn(sz, sz, __fmaf_rn(sy, sy, sx * sx));
-    if (!(l2 > 1e-6f)) return false;  // no active ray, or directions that cancel
-    const float inv = 1.0f / sqrtf(l2);
-    const float ax = sx * inv, ay = sy * inv, az = sz * inv;  // |a| = 1 +- 3e-7
+    const float4 a = cull_axis(sx, sy, sz);
+    if (a.w == 0.0f) return false;
     float md = 1.0f;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-        if (active[k]) md = fminf(md, __fmaf_rn(r[k].uz, az, __fmaf_rn(r[k].uy, ay, r[k].ux * ax)));
+        if (active[k]) md = fminf(md, __fmaf_rn(r[k].uz, a.z, __fmaf_rn(r[k].uy, a.y, r[k].ux * a.x)));
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) md = fminf(md, __shfl_xor_sync(kFullMask, md, o));
-    const float ct = md * 0.999999f - 1e-6f;  // lower bound of cos(tile half-angle): |a|, |u| and the dot are off by < 1e-6
-#ifdef RTE_CULL_DEBUG
-    if (!(ct >= kCullMinCos)) { count = -1; return false; }
-#endif
-    if (!(ct >= kCullMinCos)) return false;
-    const float st2 = fmaxf(1.0f - ct * ct, 0.0f) * 1.00001f + 1e-12f;  // upper bound of sin^2(tile half-angle)
-    count = cull_pack(view, n_pad, ax, ay, az, ct, st2, cs.mini, cs.map);
-    return count <= kCullCap;
+    count = cull_pack(view, n_pad, a.x, a.y, a.z, md, cs.mini, cs.map);  // -1: tile cone too wide
+    return count >= 0 && count <= kCullCap;
 }
 
 // ------------------------------------------------------------------------------ candidate queue
