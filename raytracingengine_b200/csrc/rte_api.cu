@@ -278,7 +278,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     mats.push_back(def);
 
     // spheres
-    const int ns = (int)d->n_spheres, ns_pad = (ns + 31) & ~31;  // kViewBlock (a multiple of kSphUnroll)
+    const int ns = (int)d->n_spheres, ns_pad = ns > 96 ? (ns + 63) & ~63 : (ns + 31) & ~31;  // kViewBlock; views that get culled (>= kCullMin): whole groups of 64
     std::vector<float4> sph32((size_t)ns_pad);
     std::vector<double4> sph64((size_t)ns_pad);
     std::vector<int32_t> sphmat((size_t)ns_pad, -1);
@@ -379,7 +379,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
                     smem, ns, nt, smem_budget);
 
     int rc;
-    const int nt_pad32 = (nt + 31) & ~31;
+    const int nt_pad32 = nt > 96 ? (nt + 63) & ~63 : (nt + 31) & ~31;  // like ns_pad
     if ((rc = reserve(ctx, ctx->b_views, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_tviews, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_views_cold, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;

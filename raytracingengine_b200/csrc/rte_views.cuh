@@ -223,10 +223,10 @@ __device__ __forceinline__ ViewChord view_chord(const float* __restrict__ view, 
 #define RTE_CULL_UNROLL 1  // measured: 1 -> 3.68 ms, 2 -> 4.07, 4 -> 4.29 on C2 (the kernel waits on instruction fetch)
 #endif
 constexpr int kCullUnroll = RTE_CULL_UNROLL;
-#ifndef RTE_CULL_PF
-#define RTE_CULL_PF 0
+#ifndef RTE_CULL_CAP
+#define RTE_CULL_CAP 128
 #endif
-constexpr int kCullCap = 128;         // survivors per (tile, view)
+constexpr int kCullCap = RTE_CULL_CAP;  // survivors per (tile, view); a multiple of 32
 constexpr int kCullMin = 128;         // views with fewer entries are scanned directly
 constexpr float kCullMinCos = 0.5f;   // tile cones wider than 60 degrees are not worth testing
 constexpr int kCullBytesPerWarp = kCullCap * 16 + kCullCap * 2;
@@ -294,30 +294,13 @@ __device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n
     const uint32_t v0 = (uint32_t)__cvta_generic_to_shared(view);  // the views live in shared memory
     const CullCone cone = make_cull_cone(ax, ay, az, ct, st2);
     int count = 0;
-#if RTE_CULL_PF
-    // software pipelining: the pair of the next group is loaded before this one is tested (the loop is latency bound: one LDS,
-    // then a chain of five dependent FFMA2)
-    ulonglong2 An, Bn;
-    {
-        const int p = min(lane, n_pairs - 1);
-        An = lds_u2(v0 + 32u * (uint32_t)p); Bn = lds_u2(v0 + 32u * (uint32_t)p + 16u);
-    }
-#endif
+    uint32_t va = v0 + 32u * (uint32_t)lane;
 #pragma unroll kCullUnroll
-    for (int p0 = 0; p0 < n_pairs; p0 += 32) {
-        const int p = min(p0 + lane, n_pairs - 1);  // (the last group of a view of 32 (mod 64) entries: the upper lanes repeat its last pair)
-#if RTE_CULL_PF
-        const ulonglong2 A = An, B = Bn;
-        {
-            const int pn = min(p0 + 32 + lane, n_pairs - 1);
-            An = lds_u2(v0 + 32u * (uint32_t)pn); Bn = lds_u2(v0 + 32u * (uint32_t)pn + 16u);
-        }
-#else
-        const ulonglong2 A = lds_u2(v0 + 32u * (uint32_t)p), B = lds_u2(v0 + 32u * (uint32_t)p + 16u);
-#endif
+    for (int p0 = 0; p0 < n_pairs; p0 += 32, va += 1024u) {  // n_pairs is a multiple of 32 (views of >= kCullMin entries are padded to 64)
+        const int p = p0 + lane;
+        const ulonglong2 A = lds_u2(va), B = lds_u2(va + 16u);
         uint32_t kw0, kw1;
         cull_keep2(A, B, cone, kw0, kw1);
-        if (p0 + lane >= n_pairs) kw0 = kw1 = 0u;
         if (__any_sync(kFullMask, (int)(kw0 | kw1) < 0)) {  // warp-uniform; ~10 % of the groups of 64 spheres have a survivor
             const bool k0 = (int)kw0 < 0, k1 = (int)kw1 < 0;
             const uint32_t m0 = __ballot_sync(kFullMask, k0), m1 = __ballot_sync(kFullMask, k1);
@@ -414,29 +397,18 @@ __device__ __forceinline__ T pick(const T (&a)[K], int k) {
     return v;
 }
 
-// Scene::IntersectClosest over the spheres (kTri: the triangles, through their bounding spheres) for K PRIMARY rays of one
-// thread (view 0, common origin o).  best/found carry the result of the classes scanned before (canonical order, strict '<').
-template <int K, bool kTri = false>
-__device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float* __restrict__ vf, d3 o,
-                                                     const d3 (&d)[K], const bool (&alive)[K], bool no_filter, Hit (&best)[K], bool (&found)[K],
-                                                     uint32_t& confirms, const CullScratch* cull = nullptr, uint32_t* executed = nullptr) {
-    // view: hot array (shared), vf: cold array (global); executed: per-lane count of FP32 tests really run (optional)
-    const ViewBounds vb = view_bounds(view_extent<kTri>(sc), o, 0.0, false);
-    ViewRay r[K];
-    float best_f[K];
-#pragma unroll
-    for (int k = 0; k < K; ++k) { r[k] = make_view_ray(d[k]); best_f[k] = found[k] ? __double2float_ru(best[k].t) : INFINITY; }
-    int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
-    const uint16_t* map = nullptr;  // culled: positions of the mini-view -> indices of the view
-    if (cull && !no_filter && ns_pad >= kCullMin) {
-        int cnt = 0;
-        if (executed) *executed += (uint32_t)(ns_pad >> 4);  // the warp's cull pass: ns_pad/32 cone-cone tests per lane, ~2x a ray test
-        if (cull_view<K>(view, ns_pad, r, alive, *cull, cnt)) { view = cull->mini; map = cull->map; ns = cnt; ns_pad = (cnt + 31) & ~31; }
-    }
-    uint32_t n_alive = 0;
-#pragma unroll
-    for (int k = 0; k < K; ++k) n_alive += alive[k] ? 1u : 0u;
-    if (executed) *executed += n_alive * (uint32_t)ns_pad;
+// More than two pixels per thread: the K rays of a thread share the tile cull (one pass over the view for 32 K rays) but are
+// scanned one after the other by the single-ray code (one copy, in a loop): no K-fold registers, no K-fold code.
+// Measured on B200 (C2 at 4K, -DRTE_VIEW_PIXELS=4 / 8): bit-identical, but 4.72 / 5.29 ms against 2.95 ms with one pixel per
+// thread — the per-pixel FP64 state of K pixels lives in local memory (2.6 / 4.1 KB stack) and that costs more than three
+// quarters of the cull passes save.  Kept as an option, not the default.
+template <int K> struct SeqScan { static constexpr bool value = K > 2; };
+
+// The window loop of closest_spheres_view: scan (FP32, K rays share every LDS), queue, lane-parallel resolution.
+template <int K, bool kTri>
+__device__ __forceinline__ void closest_scan(const DevScene& sc, const ulonglong2* __restrict__ view, const uint16_t* __restrict__ map, int ns, int ns_pad,
+                                             const float* __restrict__ vf, const ViewBounds& vb, d3 o, const d3 (&d)[K], const ViewRay (&r)[K],
+                                             const bool (&alive)[K], bool no_filter, Hit (&best)[K], float (&best_f)[K], bool (&found)[K], uint32_t& confirms) {
     CandQueue<K> Q;
     int qn = 0;
     int base = 0;
@@ -485,6 +457,47 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
             }
         }
         qn = 0;
+    }
+}
+
+// Scene::IntersectClosest over the spheres (kTri: the triangles, through their bounding spheres) for K PRIMARY rays of one
+// thread (view 0, common origin o).  best/found carry the result of the classes scanned before (canonical order, strict '<').
+template <int K, bool kTri = false>
+__device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float* __restrict__ vf, d3 o,
+                                                     const d3 (&d)[K], const bool (&alive)[K], bool no_filter, Hit (&best)[K], bool (&found)[K],
+                                                     uint32_t& confirms, const CullScratch* cull = nullptr, uint32_t* executed = nullptr) {
+    // view: hot array (shared), vf: cold array (global); executed: per-lane count of FP32 tests really run (optional)
+    const ViewBounds vb = view_bounds(view_extent<kTri>(sc), o, 0.0, false);
+    ViewRay r[K];
+    float best_f[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) { r[k] = make_view_ray(d[k]); best_f[k] = found[k] ? __double2float_ru(best[k].t) : INFINITY; }
+    int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
+    const uint16_t* map = nullptr;  // culled: positions of the mini-view -> indices of the view
+    if (cull && !no_filter && ns_pad >= kCullMin && (ns_pad & 63) == 0) {
+        int cnt = 0;
+        if (executed) *executed += (uint32_t)(ns_pad >> 4);  // the warp's cull pass: ns_pad/32 cone-cone tests per lane, ~2x a ray test
+        if (cull_view<K>(view, ns_pad, r, alive, *cull, cnt)) { view = cull->mini; map = cull->map; ns = cnt; ns_pad = (cnt + 31) & ~31; }
+    }
+    uint32_t n_alive = 0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) n_alive += alive[k] ? 1u : 0u;
+    if (executed) *executed += n_alive * (uint32_t)ns_pad;
+    if (SeqScan<K>::value) {
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            const bool a1[1] = {alive[k]};
+            if (!__any_sync(kFullMask, a1[0])) continue;
+            const d3 d1[1] = {d[k]};
+            const ViewRay r1[1] = {r[k]};
+            Hit b1[1] = {best[k]};
+            bool f1[1] = {found[k]};
+            float bf1[1] = {best_f[k]};
+            closest_scan<1, kTri>(sc, view, map, ns, ns_pad, vf, vb, o, d1, r1, a1, no_filter, b1, bf1, f1, confirms);
+            best[k] = b1[0]; found[k] = f1[0];
+        }
+    } else {
+        closest_scan<K, kTri>(sc, view, map, ns, ns_pad, vf, vb, o, d, r, alive, no_filter, best, best_f, found, confirms);
     }
 }
 
@@ -570,6 +583,91 @@ __device__ __noinline__ double march_list(const DevScene& sc, const uint16_t* li
     return std_clamp(T, 0.0, 1.0);
 }
 
+// Per-ray FP32 constants of a reversed shadow scan.
+struct OccRay32 { float tref, tmax_lo, tmax_hi; };
+
+// The window loop of occluded_spheres_view: scan, queue, lane-parallel resolution in canonical order per ray, warp vote per window.
+template <int K, bool kTri>
+__device__ __forceinline__ void occluded_scan(const DevScene& sc, const ulonglong2* __restrict__ view, const uint16_t* __restrict__ map, int ns, int ns_pad,
+                                              const float* __restrict__ vf, const ViewBounds& vb, const ShadowRay (&ray)[K], const ViewRay (&r)[K],
+                                              const OccRay32 (&q32)[K], float tsafe_hi, bool skip_self, bool no_filter, OccState (&st)[K], uint32_t (&first)[K],
+                                              RayLists<K>& lists, uint32_t& confirms, uint32_t& executed) {
+    CandQueue<K> Q;
+    int qn = 0;
+    int base = 0;
+#pragma unroll 1
+    while (base < ns_pad) {
+        const int wbase = base, stop = min(base + kWindow, ns_pad);
+#pragma unroll 1
+        do {
+            uint32_t cand[K];
+            view_block_masks<K>(view + base, r, cand);
+            if (!kTri) executed += kViewBlock;
+            uint32_t any = 0;
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                cand[k] = no_filter ? 0xFFFFFFFFu : cand[k];
+                if (st[k].done) cand[k] = 0u;
+                any |= cand[k];
+            }
+            if (any) {  // ~5 % of the blocks
+#pragma unroll
+                for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn, wbase, vf, map);
+            }
+            base += kViewBlock;
+        } while (base < stop);
+        const int nmax = __reduce_max_sync(kFullMask, qn);
+#pragma unroll 1
+        for (int e = 0; e < nmax; ++e) {  // lane-parallel resolution, canonical order per ray
+            if (e >= qn) continue;
+            const uint32_t ent = Q.q[e];
+            const int k = (int)(ent >> 8), pos = wbase + (int)(ent & 0xFFu);
+            const int idx = map ? (int)map[pos] : pos;
+            bool dn = false;
+#pragma unroll
+            for (int i = 0; i < K; ++i) if (i == k) dn = st[i].done;
+            if (dn) continue;  // decided by an earlier entry of this window
+            bool certain = false;
+            if (!no_filter) {
+                if (skip_self && idx == ray[k].self) continue;
+                const ViewChord ch = view_chord(vf, idx, pick<K>(r, k), vb);
+                if (ch.miss) continue;
+                const float tc = q32[k].tref - ch.sc;  // forward distance of the chord centre
+                const float t0_lo = tc - ch.hc_hi - vb.slack, t0_hi = tc - ch.hc_lo + vb.slack, t1_hi = tc + ch.hc_hi + vb.slack;
+                if (t1_hi < 0.0f || t0_lo > q32[k].tmax_hi) continue;  // certainly no hit in (1e-6, maxDist), none <= bias
+                certain = !kTri && ch.hc_lo > 0.0f && t0_lo > tsafe_hi && t0_hi < q32[k].tmax_lo;  // certainly t in (t_safe, maxDist)
+            }
+            if (!kTri) {  // remember every in-range candidate of the ray (what an exact march over this ray could ever hit)
+                const int ln = lists.n[k];
+                if (ln < kListCap && idx < 65536) lists.idx[k][ln] = (uint16_t)idx;
+                lists.n[k] = (ln < kListCap && idx < 65536) ? ln + 1 : kListCap + 1;
+            }
+            double t = 0.0;
+            bool hit = false;
+            if (!certain) {
+                ++confirms;
+                hit = confirm_prim<kTri>(sc, idx, ray[k].o, ray[k].d, t);
+            }
+#pragma unroll
+            for (int i = 0; i < K; ++i) {
+                if (i != k) continue;
+                if (certain) {
+                    if (!st[i].res.occluded) { st[i].res.occluded = true; first[i] = (uint32_t)idx + 1u; }
+                    if (!st[i].res.near) st[i].done = true;
+                } else if (hit) {
+                    if (kTri) st[i].on_t(t, first[i], (uint32_t)idx);
+                    else st[i].on_t_view(t, first[i], (uint32_t)idx);
+                }
+            }
+        }
+        qn = 0;
+        bool all_done = true;
+#pragma unroll
+        for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;
+        if (__all_sync(kFullMask, all_done)) break;
+    }
+}
+
 // kTri = true: the triangle phase of the same query, through the light's view of the triangles' bounding spheres; `st`
 // continues from the sphere and plane phases (canonical order), every candidate is confirmed in FP64 (tri_exact).
 template <int K, bool kTri = false>
@@ -591,18 +689,18 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
         const ViewBounds vb = view_bounds(view_extent<kTri>(sc), Lp, bias, true);
         const bool skip_self = !kTri && bias >= 1e-5;
         ViewRay r[K];
-        float tref[K], tmax_lo[K], tmax_hi[K];
+        OccRay32 q32[K];
         const float tsafe_hi = __double2float_ru(130.0 * bias) + vb.slack;
         const float bias_hi = __double2float_ru(bias) + vb.slack;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             r[k] = make_view_ray(-ray[k].d);
-            tref[k] = (float)(ray[k].dist - bias * ray[k].ndl);
-            tmax_lo[k] = __double2float_rd(ray[k].maxDist) - vb.slack;
-            tmax_hi[k] = fmaxf(__double2float_ru(ray[k].maxDist) + vb.slack, bias_hi);  // also keeps every t <= bias (`near`)
+            q32[k].tref = (float)(ray[k].dist - bias * ray[k].ndl);
+            q32[k].tmax_lo = __double2float_rd(ray[k].maxDist) - vb.slack;
+            q32[k].tmax_hi = fmaxf(__double2float_ru(ray[k].maxDist) + vb.slack, bias_hi);  // also keeps every t <= bias (`near`)
         }
         const uint16_t* map = nullptr;  // culled: positions of the mini-view -> indices of the view
-        if (cull && !no_filter && ns_pad >= kCullMin) {
+        if (cull && !no_filter && ns_pad >= kCullMin && (ns_pad & 63) == 0) {
             bool act[K];
 #pragma unroll
             for (int k = 0; k < K; ++k) act[k] = !st[k].done;
@@ -618,79 +716,27 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
             }
 #endif
         }
-        CandQueue<K> Q;
-        int qn = 0;
-        int base = 0;
+        if (SeqScan<K>::value) {
 #pragma unroll 1
-        while (base < ns_pad) {
-            const int wbase = base, stop = min(base + kWindow, ns_pad);
-#pragma unroll 1
-            do {
-                uint32_t cand[K];
-                view_block_masks<K>(view + base, r, cand);
-                if (!kTri) executed += kViewBlock;
-                uint32_t any = 0;
-#pragma unroll
-                for (int k = 0; k < K; ++k) {
-                    cand[k] = no_filter ? 0xFFFFFFFFu : cand[k];
-                    if (st[k].done) cand[k] = 0u;
-                    any |= cand[k];
-                }
-                if (any) {  // ~5 % of the blocks
-#pragma unroll
-                    for (int k = 0; k < K; ++k) qn = Q.push_block(cand[k], base - wbase, k, ns - base, qn, wbase, vf, map);
-                }
-                base += kViewBlock;
-            } while (base < stop);
-            const int nmax = __reduce_max_sync(kFullMask, qn);
-#pragma unroll 1
-            for (int e = 0; e < nmax; ++e) {  // lane-parallel resolution, canonical order per ray
-                if (e >= qn) continue;
-                const uint32_t ent = Q.q[e];
-                const int k = (int)(ent >> 8), pos = wbase + (int)(ent & 0xFFu);
-                const int idx = map ? (int)map[pos] : pos;
-                bool dn = false;
-#pragma unroll
-                for (int i = 0; i < K; ++i) if (i == k) dn = st[i].done;
-                if (dn) continue;  // decided by an earlier entry of this window
-                bool certain = false;
-                if (!no_filter) {
-                    if (skip_self && idx == ray[k].self) continue;
-                    const ViewChord ch = view_chord(vf, idx, pick<K>(r, k), vb);
-                    if (ch.miss) continue;
-                    const float tc = tref[k] - ch.sc;  // forward distance of the chord centre
-                    const float t0_lo = tc - ch.hc_hi - vb.slack, t0_hi = tc - ch.hc_lo + vb.slack, t1_hi = tc + ch.hc_hi + vb.slack;
-                    if (t1_hi < 0.0f || t0_lo > tmax_hi[k]) continue;  // certainly no hit in (1e-6, maxDist), none <= bias
-                    certain = !kTri && ch.hc_lo > 0.0f && t0_lo > tsafe_hi && t0_hi < tmax_lo[k];  // certainly t in (t_safe, maxDist)
-                }
-                if (!kTri) {  // remember every in-range candidate of the ray (what an exact march over this ray could ever hit)
-                    const int ln = lists.n[k];
-                    if (ln < kListCap && idx < 65536) lists.idx[k][ln] = (uint16_t)idx;
-                    lists.n[k] = (ln < kListCap && idx < 65536) ? ln + 1 : kListCap + 1;
-                }
-                double t = 0.0;
-                bool hit = false;
-                if (!certain) {
-                    ++confirms;
-                    hit = confirm_prim<kTri>(sc, idx, ray[k].o, ray[k].d, t);
-                }
-#pragma unroll
-                for (int i = 0; i < K; ++i) {
-                    if (i != k) continue;
-                    if (certain) {
-                        if (!st[i].res.occluded) { st[i].res.occluded = true; first[i] = (uint32_t)idx + 1u; }
-                        if (!st[i].res.near) st[i].done = true;
-                    } else if (hit) {
-                        if (kTri) st[i].on_t(t, first[i], (uint32_t)idx);
-                        else st[i].on_t_view(t, first[i], (uint32_t)idx);
-                    }
+            for (int k = 0; k < K; ++k) {
+                OccState s1[1] = {st[k]};
+                if (__all_sync(kFullMask, s1[0].done)) continue;
+                const ShadowRay y1[1] = {ray[k]};
+                const ViewRay r1[1] = {r[k]};
+                const OccRay32 q1[1] = {q32[k]};
+                uint32_t f1[1] = {first[k]};
+                RayLists<1> l1;
+                l1.n[0] = lists.n[k];
+                occluded_scan<1, kTri>(sc, view, map, ns, ns_pad, vf, vb, y1, r1, q1, tsafe_hi, skip_self, no_filter, s1, f1, l1, confirms, executed);
+                st[k] = s1[0]; first[k] = f1[0];
+                if (!kTri) {
+                    const int n1 = l1.n[0];
+                    lists.n[k] = n1;
+                    for (int i = 0; i < n1 && i < kListCap; ++i) lists.idx[k][i] = l1.idx[0][i];
                 }
             }
-            qn = 0;
-            bool all_done = true;
-#pragma unroll
-            for (int k = 0; k < K; ++k) all_done = all_done && st[k].done;
-            if (__all_sync(kFullMask, all_done)) break;
+        } else {
+            occluded_scan<K, kTri>(sc, view, map, ns, ns_pad, vf, vb, ray, r, q32, tsafe_hi, skip_self, no_filter, st, first, lists, confirms, executed);
         }
     }
 #pragma unroll
