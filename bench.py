@@ -30,6 +30,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+_OUT = sys.stdout
 METRIC = "Mrays/s (primary+shadow) at 3840x2160"
 UNIT = "Mrays/s"
 
@@ -210,7 +211,7 @@ def run_reference(args) -> None:
         "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
@@ -473,7 +474,7 @@ def run_gpu(args) -> None:
         crays = sample_ray_count(arrays, cam, row_step)
         line["cpu_baseline"] = {"value": round(crays / r["render_seconds"] / 1e6, 4), "unit": UNIT, "cores": r["threads_used"], "kind": orc.kind,
                                 "sample": f"every {row_step}th row ({r['rows']} of {H} rows, {crays} rays), RenderImage only, {r['render_seconds']:.2f} s"}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_OUT, flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -492,6 +493,11 @@ def main() -> None:
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fixed-white", action="store_true", help="c5: the reference's constant max_white = 5.0 (fused tonemap) instead of the auto max-white pipeline")
     args = ap.parse_args()
+    # stdout carries exactly ONE line (the JSON); libraries that print to fd 1 (NCCL's version banner) go to stderr
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
