@@ -321,6 +321,45 @@ def test_fast_kernel_stripes(engine):
         assert np.array_equal(part.reshape(len(rows), cam.width, 3), full[rows])
 
 
+@pytest.mark.parametrize("cfg", ["rows", "stripes", "aovs"])
+def test_render_host_bands_equal_one_launch(engine, cfg):
+    """rte_render_host renders calls of >= 1024 rows as two bands (device->host copy of the first under the kernels of the
+    second): outputs and statistics must equal those of the same rows rendered band by band in single-launch calls."""
+    arrays, cam = scenes.config2(scale=0.25)
+    cam.height = 1288 if cfg != "stripes" else 2600   # >= 1024 rows per call; not a multiple of the band unit
+    engine.upload(arrays, cam)
+    outs = ("hdr64", "rgb8") if cfg != "aovs" else AOVS
+    opts = dict(tonemap_op=_abi.TM_ACES) if cfg != "aovs" else {}
+    if cfg == "stripes":
+        from raytracingengine_b200 import sharding
+        o = sharding.stripe_opts(1, 2, cam.height, 8)
+        rows = sharding.stripe_row_list(1, 2, cam.height, 8)
+        assert len(rows) >= 1024
+        got = engine.render_host(outputs=outs, **o, **opts)
+        st = engine.stats()
+        assert st["primary_rays"] == len(rows) * cam.width
+        for k in outs:  # the same rows out of the full frame, rendered 500 rows per (single-launch) call
+            full = np.concatenate([engine.render_host(outputs=(k,), row0=a, row1=min(a + 500, cam.height), **opts)[k] for a in range(0, cam.height, 500)])
+            full = full.reshape(cam.height, cam.width, -1)
+            assert np.array_equal(got[k].reshape(len(rows), cam.width, -1), full[rows]), k
+        return
+    got = engine.render_host(outputs=outs, **opts)
+    st = engine.stats()
+    want = {k: [] for k in outs}
+    tot = {k: 0 for k in COUNTERS}
+    for a in range(0, cam.height, 500):
+        part = engine.render_host(outputs=outs, row0=a, row1=min(a + 500, cam.height), **opts)
+        s1 = engine.stats()
+        for k in outs:
+            want[k].append(part[k])
+        for k in COUNTERS:
+            tot[k] += s1[k]
+    for k in outs:
+        assert np.array_equal(got[k], np.concatenate(want[k]), equal_nan=(got[k].dtype.kind == "f")), k
+    for k in COUNTERS:
+        assert st[k] == tot[k], k
+
+
 @pytest.mark.parametrize("cfg", ["c2_fast", "c2_general", "c2_odd_width", "c4_general"])
 def test_rgb8_peer_frames_equal_the_band_output(engine, cfg):
     """rte_set_rgb8_peers: every rank's stripes, stored by the render kernel straight into the registered full frames
