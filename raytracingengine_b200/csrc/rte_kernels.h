@@ -43,6 +43,7 @@ struct RenderParams {
     rte_frame out;           // device pointers, any may be NULL
     int32_t cull;            // fast kernel: per-warp cull scratch follows the staged arrays in dynamic shared memory (rte_views.cuh)
     int32_t no_cull;         // RTE_FLAG_NO_CULL: never use it (validation / A-B)
+    int32_t cta_cull;        // streamed views: the CTA-level cull scratch follows the per-warp scratch (rte_views.cuh)
     unsigned int* tile_counter;        // zeroed before launch
     unsigned long long* stats;         // kStatCount counters, zeroed before launch
 };

@@ -49,12 +49,19 @@ constexpr uint32_t kTmaChunk = 32768;
 constexpr int kMaxTreeDepth = RTE_MAX_DEPTH;  // rte.h: largest opts.max_depth (frames of the per-pixel TraceRay stack)
 // Pixels per thread of the view-mode render kernel (a warp's tile is 8 x 4K pixels).  Measured on B200: with resident views one
 // pixel per thread is fastest (fewer live registers, tighter ray cones for the tile cull: C2 4.78 -> 4.60 ms, C4 1.40 -> 0.95 ms);
-// with streamed views every tile pays one pass over ALL view blocks, so two pixels per thread halve that cost (C5 19.1 -> 15.8 ms).
+// with streamed views two pixels per thread used to halve the per-tile pass over ALL view blocks (C5 19.1 -> 15.8 ms); since the
+// CTA-level cull (rte_views.cuh) that pass walks a few hundred survivors and one pixel per thread wins there too (C5 10.5 -> 9.6 ms).
 #ifndef RTE_VIEW_PIXELS
 #define RTE_VIEW_PIXELS 1
 #endif
 #ifndef RTE_STREAM_PIXELS
-#define RTE_STREAM_PIXELS 2
+#define RTE_STREAM_PIXELS 1
+#endif
+#ifndef RTE_BATCH_W
+#define RTE_BATCH_W 4
+#endif
+#ifndef RTE_FORCE_STREAM
+#define RTE_FORCE_STREAM 0  // A/B: stream the views (lock-step CTA, CTA-level cull) even when they would fit shared memory
 #endif
 constexpr int kViewPixels = RTE_VIEW_PIXELS;
 constexpr int kStreamPixels = RTE_STREAM_PIXELS;
@@ -77,7 +84,7 @@ SmemPlan plan_smem(const DevScene& sc, size_t budget) {
         pl.tview_bytes = (uint32_t)tviews;
         pl.stage_tri = (sc.reflective && views + tviews + tri <= budget) ? 1 : 0;
         pl.stage_sph = (sc.reflective && sc.ns > 0 && views + tviews + (pl.stage_tri ? tri : 0) + sph <= budget) ? 1 : 0;
-    } else if (sc.views && tri + views <= budget) {
+    } else if (sc.views && tri + views <= budget && !(RTE_FORCE_STREAM && !sc.reflective && sc.nt == 0 && sc.ns_pad >= 128)) {
         pl.use_views = 1;
         pl.view_bytes = (uint32_t)views;
         pl.stage_sph = (sc.reflective && tri + views + sph <= budget) ? 1 : 0;
@@ -568,7 +575,7 @@ struct ViewsStream {
 template <int K, bool kTris, class Views>
 __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const ulonglong2* s_tviews,
                                                 const float* s_cold, const float* s_tcold, const float4* s_sph, const float4* s_tri, const CullScratch* cull,
-                                                const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K], int sample, PixelCounters& cnt,
+                                                const CtaCull* cc, const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K], int sample, PixelCounters& cnt,
                                                 d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     const double bias = P.bias;
@@ -586,7 +593,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
     }
     {
         const ulonglong2* v0 = views.acquire(0);
-        if (ns > 0) closest_spheres_view<K>(sc, v0, s_cold, cam_o, dir, alive, false, h, found, cnt.confirms, cull, &cnt.sph_exec);
+        if (ns > 0) closest_spheres_view<K>(sc, v0, s_cold, cam_o, dir, alive, false, h, found, cnt.confirms, cull, &cnt.sph_exec, cc);
         views.release();
     }
 
@@ -682,7 +689,8 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         RayLists<K> lists;
         {
             const ulonglong2* vj = views.acquire(1 + j);  // streamed views: every warp of the CTA passes here, scanning or not
-            if (scan) occluded_spheres_view<K>(sc, vj, s_cold + (size_t)(1 + j) * sc.ns_pad * 4, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec, cull);
+            // (with a CTA-level cull every warp of the CTA takes part, casting or not)
+            if (scan || cc) occluded_spheres_view<K>(sc, vj, s_cold + (size_t)(1 + j) * sc.ns_pad * 4, Lp, sr, bias, false, st, lists, cnt.confirms, cnt.sph_exec, cull, cc);
             views.release();
         }
         if (!scan) continue;
@@ -776,8 +784,8 @@ constexpr int kFastMinBlocks = RTE_FAST_MINB;
 #ifndef RTE_BIG_THREADS
 #define RTE_BIG_THREADS 512
 #endif
-constexpr int kBigThreads = RTE_BIG_THREADS;  // block size of the streamed-view variant (two pixels per thread: 512 x 128 registers
-                                              // 15.7 ms on C5 at 4K, 768 x 80 17.5, 1024 x 64 17.9)
+constexpr int kBigThreads = RTE_BIG_THREADS;  // block size of the streamed-view variant (one pixel per thread, CTA-level cull, C5 at 4K:
+                                              // 384 x 128 registers 10.4 ms, 512 x 128 9.6, 768 x 80 10.5, 1024 x 64 9.9)
 
 // kBig = false: kFastThreads x kFastMinBlocks CTAs per SM; kBig = true: one 512-thread CTA per SM (views of large scenes)
 // kStream = true (implies kBig): the views pass through two shared-memory buffers (ViewsStream), tile batches are CTA-uniform
@@ -807,6 +815,14 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         cull_scratch.map = reinterpret_cast<uint16_t*>(base + kCullCap * 16);
     }
     const CullScratch* cull = P.cull ? &cull_scratch : nullptr;
+    CtaCull cta_scratch{nullptr, nullptr, nullptr};
+    if (kStream && P.cta_cull) {
+        unsigned char* base = dyn_smem + ((P.plan.total + 15) & ~(size_t)15) + (size_t)(blockDim.x >> 5) * kCullBytesPerWarp;
+        cta_scratch.mini = reinterpret_cast<ulonglong2*>(base);
+        cta_scratch.map = reinterpret_cast<uint16_t*>(base + kCtaCap * 16);
+        cta_scratch.part = reinterpret_cast<int*>(base + kCtaCap * 18);
+    }
+    const CtaCull* cc = (kStream && P.cta_cull) ? &cta_scratch : nullptr;
     ViewsStream views_str;
     if (kStream) {
         views_str.base = dyn_smem;
@@ -822,16 +838,38 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
     const int lx = lane & (kTileW - 1), ly = lane >> 3;
 
+    // Resident views: every warp pulls its next tile from the global counter.  Streamed views: the CTA pulls a BATCH (one tile
+    // per warp; the warps walk the views together) whose tiles lie side by side, 4 wide (a strip of tiles when the rows are
+    // striped: stripes are one tile high), so that the CTA-level cull sees a narrow cone.
+    __shared__ unsigned int s_batch;
+    const int nw = (int)(blockDim.x >> 5);
+    const int bw = sr > 0 ? nw : RTE_BATCH_W, bh = nw / bw;
+    const int batches_x = (tiles_x + bw - 1) / bw, batches_y = (tiles_y + bh - 1) / bh;
+    const unsigned int n_batches = (unsigned int)(batches_x * batches_y);
     unsigned int tile = 0;
-    if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
-    tile = __shfl_sync(kFullMask, tile, 0);
+    if (!kStream) {
+        if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
+        tile = __shfl_sync(kFullMask, tile, 0);
+    }
     while (true) {
-        const bool have = tile < n_tiles;
-        if (kStream) { if (!__syncthreads_or(have ? 1 : 0)) break; }  // a batch = one tile per warp; idle warps still walk the views
-        else if (!have) break;
+        bool have;
+        int tx, ty;
         unsigned int next = 0;
-        if (lane == 0) next = have ? atomicAdd(P.tile_counter, 1u) : tile;
-        const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
+        if (kStream) {
+            if (threadIdx.x == 0) s_batch = atomicAdd(P.tile_counter, 1u);
+            __syncthreads();
+            const unsigned int b = s_batch;
+            __syncthreads();
+            if (b >= n_batches) break;
+            tx = (int)(b % (unsigned)batches_x) * bw + warp % bw;
+            ty = (int)(b / (unsigned)batches_x) * bh + warp / bw;
+            have = tx < tiles_x && ty < tiles_y;  // idle warps still walk the views
+        } else {
+            have = tile < n_tiles;
+            if (!have) break;
+            if (lane == 0) next = atomicAdd(P.tile_counter, 1u);
+            ty = (int)(tile / (unsigned)tiles_x); tx = (int)(tile % (unsigned)tiles_x);
+        }
         int px[K], py[K];
         bool inb[K];
         uint32_t n_in = 0;
@@ -852,8 +890,8 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             for (int k = 0; k < K; ++k) sum[k] = mk(0.0, 0.0, 0.0);
 #pragma unroll 1
             for (int s = 0; s < aa; ++s) {
-                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, px, py, inb, s, cnt, c);
-                else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, px, py, inb, s, cnt, c);
+                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, cc, px, py, inb, s, cnt, c);
+                else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, nullptr, px, py, inb, s, cnt, c);
                 if (aa > 1) {
 #pragma unroll 1
                     for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
@@ -921,6 +959,7 @@ static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int smal
                                     int big_threads = kRenderMaxThreads) {
     RenderParams p = p0;
     p.cull = 0;
+    p.cta_cull = 0;
     size_t smem = p.plan.total;
     cudaError_t e = ensure_smem(fn, smem);
     if (e != cudaSuccess) return e;
@@ -943,6 +982,13 @@ static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int smal
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, fn, threads, with_cull) == cudaSuccess && per_sm2 >= per_sm) {
             smem = with_cull;
             p.cull = 1;
+            // streamed views: the CTA-level cull scratch behind the per-warp scratch, when it fits as well
+            const size_t with_cta = with_cull + kCtaCullBytes;
+            if (p.plan.stream_views && with_cta <= smem_limit && ensure_smem(fn, with_cta) == cudaSuccess &&
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, fn, threads, with_cta) == cudaSuccess && per_sm2 >= per_sm) {
+                smem = with_cta;
+                p.cta_cull = 1;
+            }
         }
     }
     const int W = p.cam.width, rows = p.n_rows;

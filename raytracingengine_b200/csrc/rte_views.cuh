@@ -280,8 +280,9 @@ __device__ __forceinline__ void cull_store(float* __restrict__ mf, uint16_t* __r
     map[pos] = (uint16_t)idx;
 }
 // `md`: this lane's smallest u.a over its active rays (1 if it has none).  Returns -1 when the tile cone is too wide to be worth testing.
+// `src`: the view is itself a culled one (CTA level): position -> index in the full view, or NULL.
 __device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float md,
-                                      ulonglong2* __restrict__ mini, uint16_t* __restrict__ map) {
+                                      ulonglong2* __restrict__ mini, uint16_t* __restrict__ map, const uint16_t* __restrict__ src) {
     // min over the warp with one REDUX: non-negative floats order like their bit patterns (a negative dot clamps to 0: too wide anyway)
     md = __uint_as_float(__reduce_min_sync(kFullMask, __float_as_uint(fmaxf(md, 0.0f))));
     const float ct = md * 0.999998f - 2e-6f;  // lower bound of cos(tile half-angle): |a|, |u| and the dots are off by < 1e-6
@@ -307,9 +308,9 @@ __device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n
             uint32_t a0, a1, a2, a3, b0, b1, b2, b3;  // A = {cx0,cx1,cy0,cy1}, B = {cz0,cz1,w0,w1}
             unpack2_bits(A.x, a0, a1); unpack2_bits(A.y, a2, a3); unpack2_bits(B.x, b0, b1); unpack2_bits(B.y, b2, b3);
             const int pos = count + __popc(m0 & lt) + __popc(m1 & lt);
-            if (k0 && pos < kCullCap) cull_store(mf, map, pos, __uint_as_float(a0), __uint_as_float(a2), __uint_as_float(b0), __uint_as_float(b2), 2 * p);
+            if (k0 && pos < kCullCap) cull_store(mf, map, pos, __uint_as_float(a0), __uint_as_float(a2), __uint_as_float(b0), __uint_as_float(b2), src ? (int)src[2 * p] : 2 * p);
             const int pos1 = pos + (k0 ? 1 : 0);
-            if (k1 && pos1 < kCullCap) cull_store(mf, map, pos1, __uint_as_float(a1), __uint_as_float(a3), __uint_as_float(b1), __uint_as_float(b3), 2 * p + 1);
+            if (k1 && pos1 < kCullCap) cull_store(mf, map, pos1, __uint_as_float(a1), __uint_as_float(a3), __uint_as_float(b1), __uint_as_float(b3), src ? (int)src[2 * p + 1] : 2 * p + 1);
             count += __popc(m0) + __popc(m1);
             if (count > kCullCap) return count;
         }
@@ -343,7 +344,7 @@ __device__ __noinline__ float4 cull_axis(float sx, float sy, float sz) {
 // entries.  All 32 lanes call it.
 template <int K>
 __device__ __forceinline__ bool cull_view(const ulonglong2* __restrict__ view, int n_pad, const ViewRay (&r)[K], const bool (&active)[K],
-                                          const CullScratch& cs, int& count) {
+                                          const CullScratch& cs, int& count, const uint16_t* __restrict__ src = nullptr) {
     float sx = 0.f, sy = 0.f, sz = 0.f;
 #pragma unroll
     for (int k = 0; k < K; ++k) {
@@ -356,8 +357,125 @@ __device__ __forceinline__ bool cull_view(const ulonglong2* __restrict__ view, i
     for (int k = 0; k < K; ++k) {
         if (active[k]) md = fminf(md, __fmaf_rn(r[k].uz, a.z, __fmaf_rn(r[k].uy, a.y, r[k].ux * a.x)));
     }
-    count = cull_pack(view, n_pad, a.x, a.y, a.z, md, cs.mini, cs.map);  // -1: tile cone too wide
+    count = cull_pack(view, n_pad, a.x, a.y, a.z, md, cs.mini, cs.map, src);  // -1: tile cone too wide
     return count >= 0 && count <= kCullCap;
+}
+
+// ------------------------------------------------------------------------------ CTA-level culling (streamed views)
+// A scene whose views are streamed (C5: 4096 spheres, 9 views of 64 KB) pays one per-warp cull pass over the WHOLE view
+// per (tile, view): 64 groups of 64 spheres.  In that kernel every warp of the CTA walks the same view at the same time
+// and the CTA's tiles lie side by side (one batch = 4 x 4 tiles, or one strip of tiles when the rows are striped), so the
+// CTA first culls the view ONCE against the bounding cone of all its rays — every warp tests its share of the view,
+// two passes (count, then pack behind the lower warps' counts: ascending index) — and the per-warp culls then walk the
+// CTA's survivors (a few hundred) instead of the view.  Same test, same conservativeness as the warp level.
+#ifndef RTE_CTA_CAP
+#define RTE_CTA_CAP 1024
+#endif
+constexpr int kCtaCap = RTE_CTA_CAP;  // survivors of the CTA-level cull; more: the warps cull the whole view as before
+constexpr int kCtaCullBytes = kCtaCap * 16 + kCtaCap * 2 + 32 * 4 * 4;
+struct CtaCull {
+    ulonglong2* mini;  // kCtaCap entries in pair layout (shared memory, one per CTA)
+    uint16_t* map;     // position -> index in the view
+    int* part;         // [32 warps][4]: exchange of per-warp partial results
+};
+
+// Axis of the CTA's cone.  Called by every thread of the CTA; sx,sy,sz: this lane's sum of active directions.
+__device__ __noinline__ float4 cta_cull_axis(float sx, float sy, float sz, int* __restrict__ part) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const float kScale = 262144.0f, kInv = 1.0f / 262144.0f;  // |sum over the CTA| <= 1024 K <= 2^11: fits 2^29
+    const int ix = __reduce_add_sync(kFullMask, __float2int_rn(sx * kScale));
+    const int iy = __reduce_add_sync(kFullMask, __float2int_rn(sy * kScale));
+    const int iz = __reduce_add_sync(kFullMask, __float2int_rn(sz * kScale));
+    if (lane == 0) { part[warp * 4] = ix; part[warp * 4 + 1] = iy; part[warp * 4 + 2] = iz; }
+    __syncthreads();
+    const bool in = lane < nw;
+    const float fx = (float)__reduce_add_sync(kFullMask, in ? part[lane * 4] : 0) * kInv;
+    const float fy = (float)__reduce_add_sync(kFullMask, in ? part[lane * 4 + 1] : 0) * kInv;
+    const float fz = (float)__reduce_add_sync(kFullMask, in ? part[lane * 4 + 2] : 0) * kInv;
+    const float l2 = __fmaf_rn(fz, fz, __fmaf_rn(fy, fy, fx * fx));
+    if (!(l2 > 1e-4f)) return make_float4(0.f, 0.f, 0.f, 0.f);  // (CTA-uniform)
+    const float inv = rsqrtf(l2);
+    return make_float4(fx * inv, fy * inv, fz * inv, 1.0f);
+}
+
+// Called by every thread of the CTA.  Returns the survivor count (CTA-uniform): -1 cone too wide, > kCtaCap overflow.
+__device__ __noinline__ int cta_cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float md,
+                                          ulonglong2* __restrict__ mini, uint16_t* __restrict__ map, int* __restrict__ part) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const uint32_t mdw = __reduce_min_sync(kFullMask, __float_as_uint(fmaxf(md, 0.0f)));
+    if (lane == 0) part[warp * 4 + 3] = (int)mdw;
+    __syncthreads();
+    md = __uint_as_float(__reduce_min_sync(kFullMask, lane < nw ? (uint32_t)part[lane * 4 + 3] : 0x3f800000u));
+    const float ct = md * 0.999998f - 2e-6f;
+    if (!(ct >= kCullMinCos)) return -1;
+    const float st2 = fmaxf(1.0f - ct * ct, 0.0f) * 1.00001f + 1e-12f;
+    const CullCone cone = make_cull_cone(ax, ay, az, ct, st2);
+    const uint32_t lt = (1u << lane) - 1u;
+    const int groups = n_pad >> 6;  // of 32 pairs (n_pad is a multiple of 64)
+    const int per = (groups + nw - 1) / nw, g0 = min(warp * per, groups), g1 = min(g0 + per, groups);
+    const uint32_t v0 = (uint32_t)__cvta_generic_to_shared(view) + 32u * (uint32_t)lane;
+    int cnt = 0;
+#pragma unroll 1
+    for (int g = g0; g < g1; ++g) {  // pass 1: count
+        const uint32_t va = v0 + 1024u * (uint32_t)g;
+        const ulonglong2 A = lds_u2(va), B = lds_u2(va + 16u);
+        uint32_t kw0, kw1;
+        cull_keep2(A, B, cone, kw0, kw1);
+        cnt += __popc(__ballot_sync(kFullMask, (int)kw0 < 0)) + __popc(__ballot_sync(kFullMask, (int)kw1 < 0));
+    }
+    if (lane == 0) part[warp * 4] = cnt;
+    __syncthreads();
+    const int c = lane < nw ? part[lane * 4] : 0;
+    const int total = __reduce_add_sync(kFullMask, c);
+    if (total > kCtaCap) return total;
+    int count = __reduce_add_sync(kFullMask, lane < warp ? c : 0);  // behind the survivors of the lower warps
+    float* mf = reinterpret_cast<float*>(mini);
+#pragma unroll 1
+    for (int g = g0; g < g1 && cnt > 0; ++g) {  // pass 2: pack
+        const uint32_t va = v0 + 1024u * (uint32_t)g;
+        const ulonglong2 A = lds_u2(va), B = lds_u2(va + 16u);
+        uint32_t kw0, kw1;
+        cull_keep2(A, B, cone, kw0, kw1);
+        const bool k0 = (int)kw0 < 0, k1 = (int)kw1 < 0;
+        const uint32_t m0 = __ballot_sync(kFullMask, k0), m1 = __ballot_sync(kFullMask, k1);
+        if ((m0 | m1) == 0u) continue;
+        uint32_t a0, a1, a2, a3, b0, b1, b2, b3;
+        unpack2_bits(A.x, a0, a1); unpack2_bits(A.y, a2, a3); unpack2_bits(B.x, b0, b1); unpack2_bits(B.y, b2, b3);
+        const int p = g * 32 + lane;
+        const int pos = count + __popc(m0 & lt) + __popc(m1 & lt);
+        if (k0) cull_store(mf, map, pos, __uint_as_float(a0), __uint_as_float(a2), __uint_as_float(b0), __uint_as_float(b2), 2 * p);
+        if (k1) cull_store(mf, map, pos + (k0 ? 1 : 0), __uint_as_float(a1), __uint_as_float(a3), __uint_as_float(b1), __uint_as_float(b3), 2 * p + 1);
+        count += __popc(m0) + __popc(m1);
+    }
+    if (warp == 0) {  // pad to a multiple of 64 with never-candidate entries
+        const int padded = (total + 63) & ~63;
+        for (int q = total + lane; q < padded; q += 32) {
+            float* e = mf + (size_t)(q >> 1) * 8 + (q & 1);
+            e[0] = 0.f; e[2] = 0.f; e[4] = 0.f; e[6] = -INFINITY;
+        }
+    }
+    __syncthreads();
+    return total;
+}
+
+// CTA cone of the active rays, then cta_cull_pack.  Every thread of the CTA calls it (warps without work pass no active ray).
+template <int K>
+__device__ __forceinline__ bool cta_cull_view(const ulonglong2* __restrict__ view, int n_pad, const ViewRay (&r)[K], const bool (&active)[K],
+                                              const CtaCull& cc, int& count) {
+    float sx = 0.f, sy = 0.f, sz = 0.f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (active[k]) { sx += r[k].ux; sy += r[k].uy; sz += r[k].uz; }
+    }
+    const float4 a = cta_cull_axis(sx, sy, sz, cc.part);
+    if (a.w == 0.0f) return false;
+    float md = 1.0f;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        if (active[k]) md = fminf(md, __fmaf_rn(r[k].uz, a.z, __fmaf_rn(r[k].uy, a.y, r[k].ux * a.x)));
+    }
+    count = cta_cull_pack(view, n_pad, a.x, a.y, a.z, md, cc.mini, cc.map, cc.part);
+    return count >= 0 && count <= kCtaCap;
 }
 
 // ------------------------------------------------------------------------------ candidate queue
@@ -465,8 +583,10 @@ __device__ __forceinline__ void closest_scan(const DevScene& sc, const ulonglong
 template <int K, bool kTri = false>
 __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float* __restrict__ vf, d3 o,
                                                      const d3 (&d)[K], const bool (&alive)[K], bool no_filter, Hit (&best)[K], bool (&found)[K],
-                                                     uint32_t& confirms, const CullScratch* cull = nullptr, uint32_t* executed = nullptr) {
+                                                     uint32_t& confirms, const CullScratch* cull = nullptr, uint32_t* executed = nullptr,
+                                                     const CtaCull* cc = nullptr) {
     // view: hot array (shared), vf: cold array (global); executed: per-lane count of FP32 tests really run (optional)
+    // cc: CTA-level cull first (streamed views; then EVERY thread of the CTA is here)
     const ViewBounds vb = view_bounds(view_extent<kTri>(sc), o, 0.0, false);
     ViewRay r[K];
     float best_f[K];
@@ -474,10 +594,15 @@ __device__ __forceinline__ void closest_spheres_view(const DevScene& sc, const u
     for (int k = 0; k < K; ++k) { r[k] = make_view_ray(d[k]); best_f[k] = found[k] ? __double2float_ru(best[k].t) : INFINITY; }
     int ns = view_count<kTri>(sc), ns_pad = view_padded<kTri>(sc);
     const uint16_t* map = nullptr;  // culled: positions of the mini-view -> indices of the view
+    if (cc && !no_filter && (ns_pad & 63) == 0) {
+        int cnt = 0;
+        if (executed) *executed += (uint32_t)(ns_pad >> 3) / (blockDim.x >> 5);  // two passes over this warp's share of the view
+        if (cta_cull_view<K>(view, ns_pad, r, alive, *cc, cnt)) { view = cc->mini; map = cc->map; ns = cnt; ns_pad = (cnt + 63) & ~63; }
+    }
     if (cull && !no_filter && ns_pad >= kCullMin && (ns_pad & 63) == 0) {
         int cnt = 0;
         if (executed) *executed += (uint32_t)(ns_pad >> 4);  // the warp's cull pass: ns_pad/32 cone-cone tests per lane, ~2x a ray test
-        if (cull_view<K>(view, ns_pad, r, alive, *cull, cnt)) { view = cull->mini; map = cull->map; ns = cnt; ns_pad = (cnt + 31) & ~31; }
+        if (cull_view<K>(view, ns_pad, r, alive, *cull, cnt, map)) { view = cull->mini; map = cull->map; ns = cnt; ns_pad = (cnt + 31) & ~31; }
     }
     uint32_t n_alive = 0;
 #pragma unroll
@@ -674,7 +799,7 @@ template <int K, bool kTri = false>
 __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const ulonglong2* __restrict__ view, const float* __restrict__ vf, d3 Lp,
                                                       const ShadowRay (&ray)[K], double bias, bool no_filter, OccState (&st)[K],
                                                       RayLists<K>& lists, uint32_t& confirms, uint32_t& executed,
-                                                      const CullScratch* cull = nullptr) {
+                                                      const CullScratch* cull = nullptr, const CtaCull* cc = nullptr) {
     uint32_t first[K];
     bool scanning[K];
     const int ns_view = view_count<kTri>(sc);
@@ -700,13 +825,21 @@ __device__ __forceinline__ void occluded_spheres_view(const DevScene& sc, const 
             q32[k].tmax_hi = fmaxf(__double2float_ru(ray[k].maxDist) + vb.slack, bias_hi);  // also keeps every t <= bias (`near`)
         }
         const uint16_t* map = nullptr;  // culled: positions of the mini-view -> indices of the view
+        if (cc && !no_filter && (ns_pad & 63) == 0) {  // CTA-level cull first (every thread of the CTA is here)
+            bool act[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) act[k] = !st[k].done;
+            int cnt = 0;
+            if (!kTri) executed += (uint32_t)(ns_pad >> 3) / (blockDim.x >> 5);
+            if (cta_cull_view<K>(view, ns_pad, r, act, *cc, cnt)) { view = cc->mini; map = cc->map; ns = cnt; ns_pad = (cnt + 63) & ~63; }
+        }
         if (cull && !no_filter && ns_pad >= kCullMin && (ns_pad & 63) == 0) {
             bool act[K];
 #pragma unroll
             for (int k = 0; k < K; ++k) act[k] = !st[k].done;
             int cnt = 0;
             if (!kTri) executed += (uint32_t)(ns_pad >> 4);  // the warp's cull pass: ns_pad/32 cone-cone tests per lane, ~2x a ray test
-            if (cull_view<K>(view, ns_pad, r, act, *cull, cnt)) { view = cull->mini; map = cull->map; ns = cnt; ns_pad = (cnt + 31) & ~31; }
+            if (cull_view<K>(view, ns_pad, r, act, *cull, cnt, map)) { view = cull->mini; map = cull->map; ns = cnt; ns_pad = (cnt + 31) & ~31; }
 #ifdef RTE_CULL_DEBUG
             if ((threadIdx.x & 31) == 0) {
                 if (RTE_CULL_DEBUG == 1 && cnt == -1) confirms += 1;                 // tile cone too wide
