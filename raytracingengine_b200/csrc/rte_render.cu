@@ -57,6 +57,10 @@ constexpr int kMaxTreeDepth = RTE_MAX_DEPTH;  // rte.h: largest opts.max_depth (
 #ifndef RTE_STREAM_PIXELS
 #define RTE_STREAM_PIXELS 1
 #endif
+#ifndef RTE_SMEM_CONSTS
+#define RTE_SMEM_CONSTS 1
+#endif
+constexpr int kSmemPlanes = 8, kSmemLights = 16;
 #ifndef RTE_BATCH_W
 #define RTE_BATCH_W 4
 #endif
@@ -798,7 +802,19 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     __shared__ __align__(8) uint64_t s_vbar[2];
     __shared__ unsigned long long s_stats[(kBig ? kBigThreads : kFastThreads) / 32][kStatCount];
 
+#if RTE_SMEM_CONSTS
+    // the planes and lights every ray reads (a few hundred bytes) live in shared memory: the L1 is busy with local memory
+    __shared__ DevPlane s_planes[kSmemPlanes];
+    __shared__ DevLight s_lights[kSmemLights];
+    if (threadIdx.x == 0) {
+        DevScene t = P.sc;
+        if (t.np <= kSmemPlanes) { for (int i = 0; i < t.np; ++i) s_planes[i] = P.sc.planes[i]; t.planes = s_planes; }
+        if (t.nl <= kSmemLights) { for (int i = 0; i < t.nl; ++i) s_lights[i] = P.sc.lights[i]; t.lights = s_lights; }
+        s_sc = t;
+    }
+#else
     if (threadIdx.x == 0) s_sc = P.sc;
+#endif
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
     StagedScene S;
