@@ -212,8 +212,8 @@ extern "C" int rte_create(int device, rte_ctx** out) {
 #define CK(call) do { cudaError_t e2 = (call); if (e2 != cudaSuccess) { int rc = cuda_fail(nullptr, e2, #call); rte_destroy(ctx); return rc; } } while (0)
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    CK(cudaMalloc(&ctx->d_tile_counter, sizeof(unsigned int)));
-    CK(cudaMalloc(&ctx->d_stats, sizeof(unsigned long long) * kStatCount));
+    CK(cudaMalloc(&ctx->d_stats, sizeof(unsigned long long) * (kStatCount + 1)));
+    ctx->d_tile_counter = reinterpret_cast<unsigned int*>(ctx->d_stats + kStatCount);
     CK(cudaMalloc(&ctx->d_maxlum, sizeof(unsigned int)));
     CK(cudaMallocHost(&ctx->h_stats, sizeof(unsigned long long) * (kStatCount + 1)));
     CK(cudaEventCreate(&ctx->ev_r0)); CK(cudaEventCreate(&ctx->ev_r1));
@@ -236,7 +236,6 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     for (DevBuf& b : ctx->s_tm_out) if (b.p) cudaFree(b.p);
-    if (ctx->d_tile_counter) cudaFree(ctx->d_tile_counter);
     if (ctx->d_stats) cudaFree(ctx->d_stats);
     if (ctx->d_maxlum) cudaFree(ctx->d_maxlum);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
@@ -493,10 +492,12 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     }
     p.out.rgb8 = nullptr;
     p.tonemap_op = RTE_TM_NONE;
-    RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));
+    // (d_tile_counter sits right behind d_stats: one memset clears both)
     if (first) {
-        RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * kStatCount, ctx->stream));
+        RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * (kStatCount + 1), ctx->stream));
         RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
+    } else {
+        RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));
     }
     if (o.n_rows > 0) RTE_CUDA(ctx, launch_render(p, ctx->sm_count, ctx->stream));
     if (want_rgb8) RTE_CUDA(ctx, launch_tonemap64(tp, ctx->sm_count, ctx->stream));

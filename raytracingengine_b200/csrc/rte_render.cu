@@ -10,6 +10,8 @@
 //  * per pixel the ray state is FP64 (bit-identical to the reference's doubles), the O(primitives)
 //    loops are FP32 FMA filters (rte_trace.cuh);
 //  * reflection (material.specular) is an iterative loop; refraction is rejected at upload time.
+#include <vector>
+
 #include "rte_kernels.h"
 #include "rte_tonemap.cuh"
 #include "rte_trace.cuh"
@@ -968,14 +970,23 @@ cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double 
     return cudaGetLastError();
 }
 
+// Launch configuration of one (kernel pair, staged bytes, flags) on one device.  The occupancy queries and attribute calls
+// behind it take tens of microseconds of host time, during which an otherwise empty stream idles inside the caller's
+// timed region — they run once per configuration, not once per frame.
+struct LaunchCfg {
+    const void *key_fn, *key_big;
+    size_t key_smem, key_limit;
+    int key_dev, key_threads, key_minb, key_bigt, key_flags;
+    const void* fn;
+    int threads, per_sm, cull, cta_cull;
+    size_t smem;
+};
+static thread_local std::vector<LaunchCfg> t_launch_cfgs;
+
 // `cull_ok`: the kernel can use per-warp cull scratch (the fast kernel); it is granted when it fits next to the staged arrays
 // without lowering the number of CTAs per SM.
-static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int small_threads, int small_min_blocks, int K,
-                                    const RenderParams& p0, int sm_count, cudaStream_t stream, bool cull_ok = false, size_t smem_limit = 0,
-                                    int big_threads = kRenderMaxThreads) {
-    RenderParams p = p0;
-    p.cull = 0;
-    p.cta_cull = 0;
+static cudaError_t resolve_launch(LaunchCfg& c, const void* fn, const void* fn_big, int small_threads, int small_min_blocks, const RenderParams& p,
+                                  bool cull_ok, size_t smem_limit, int big_threads) {
     size_t smem = p.plan.total;
     cudaError_t e = ensure_smem(fn, smem);
     if (e != cudaSuccess) return e;
@@ -991,29 +1002,61 @@ static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int smal
         if (e != cudaSuccess) return e;
     }
     if (per_sm < 1) return cudaErrorInvalidConfiguration;
+    c.cull = 0; c.cta_cull = 0;
     if (cull_ok && !p.no_cull) {
         const size_t with_cull = ((smem + 15) & ~(size_t)15) + (size_t)(threads / 32) * kCullBytesPerWarp;
         int per_sm2 = 0;
         if (with_cull <= smem_limit && ensure_smem(fn, with_cull) == cudaSuccess &&
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, fn, threads, with_cull) == cudaSuccess && per_sm2 >= per_sm) {
             smem = with_cull;
-            p.cull = 1;
+            c.cull = 1;
             // streamed views: the CTA-level cull scratch behind the per-warp scratch, when it fits as well
             const size_t with_cta = with_cull + kCtaCullBytes;
             if (p.plan.stream_views && with_cta <= smem_limit && ensure_smem(fn, with_cta) == cudaSuccess &&
                 cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, fn, threads, with_cta) == cudaSuccess && per_sm2 >= per_sm) {
                 smem = with_cta;
-                p.cta_cull = 1;
+                c.cta_cull = 1;
             }
         }
+        if ((e = ensure_smem(fn, smem)) != cudaSuccess) return e;  // (a failed probe above may have left a larger request)
     }
+    c.fn = fn; c.threads = threads; c.per_sm = per_sm; c.smem = smem;
+    return cudaSuccess;
+}
+
+static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int small_threads, int small_min_blocks, int K,
+                                    const RenderParams& p0, int sm_count, cudaStream_t stream, bool cull_ok = false, size_t smem_limit = 0,
+                                    int big_threads = kRenderMaxThreads) {
+    RenderParams p = p0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const int flags = (cull_ok ? 1 : 0) | (p.no_cull ? 2 : 0) | (p.plan.stream_views ? 4 : 0);
+    const LaunchCfg* cfg = nullptr;
+    for (const LaunchCfg& c : t_launch_cfgs)
+        if (c.key_fn == fn && c.key_big == fn_big && c.key_smem == p.plan.total && c.key_limit == smem_limit && c.key_dev == dev &&
+            c.key_threads == small_threads && c.key_minb == small_min_blocks && c.key_bigt == big_threads && c.key_flags == flags) { cfg = &c; break; }
+    if (!cfg) {
+        LaunchCfg c{};
+        c.key_fn = fn; c.key_big = fn_big; c.key_smem = p.plan.total; c.key_limit = smem_limit; c.key_dev = dev;
+        c.key_threads = small_threads; c.key_minb = small_min_blocks; c.key_bigt = big_threads; c.key_flags = flags;
+        const cudaError_t e = resolve_launch(c, fn, fn_big, small_threads, small_min_blocks, p, cull_ok, smem_limit, big_threads);
+        if (e != cudaSuccess) return e;
+        if (t_launch_cfgs.size() >= 64) t_launch_cfgs.clear();
+        t_launch_cfgs.push_back(c);
+        cfg = &t_launch_cfgs.back();
+    }
+    p.cull = cfg->cull;
+    p.cta_cull = cfg->cta_cull;
+    const int threads = cfg->threads;
     const int W = p.cam.width, rows = p.n_rows;
     const long long n_tiles = (long long)((W + kTileW - 1) / kTileW) * ((rows + kTileH * K - 1) / (kTileH * K));
-    long long blocks = (long long)sm_count * per_sm;  // persistent: a multiple of the SM count
+    long long blocks = (long long)sm_count * cfg->per_sm;  // persistent: a multiple of the SM count
     const long long needed = (n_tiles + threads / 32 - 1) / (threads / 32);
     if (blocks > needed) blocks = needed > 0 ? needed : 1;
+    const cudaError_t e = ensure_smem(cfg->fn, cfg->smem);  // (per function and device, and other configurations of this kernel lower it)
+    if (e != cudaSuccess) return e;
     void* args[] = {(void*)&p};
-    return cudaLaunchKernel(fn, dim3((unsigned)blocks), dim3((unsigned)threads), args, smem, stream);
+    return cudaLaunchKernel(cfg->fn, dim3((unsigned)blocks), dim3((unsigned)threads), args, cfg->smem, stream);
 }
 
 bool fast_path_eligible(const RenderParams& p) {
