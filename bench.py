@@ -487,12 +487,14 @@ def main() -> None:
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c5"])
     ap.add_argument("--scale", type=float, default=1.0, help="developer switch: shrink the image (not the named config)")
-    ap.add_argument("--stripe", type=int, default=8, help="rows per interleaved stripe at N>1")
+    ap.add_argument("--stripe", type=int, default=0, help="rows per interleaved stripe at N>1 (0: 8 for c2/c3, 16 for c5 whose streamed-view kernel works on 32x16 pixel batches)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU sample size per pass of the reference leg")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N>1: how the RGB8 stripes reach every rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fixed-white", action="store_true", help="c5: the reference's constant max_white = 5.0 (fused tonemap) instead of the auto max-white pipeline")
     args = ap.parse_args()
+    if args.stripe <= 0:
+        args.stripe = 16 if args.workload == "c5" else 8
     # stdout carries exactly ONE line (the JSON); libraries that print to fd 1 (NCCL's version banner) go to stderr
     global _OUT
     sys.stdout.flush()

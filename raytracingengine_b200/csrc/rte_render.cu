@@ -857,11 +857,14 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     const int lx = lane & (kTileW - 1), ly = lane >> 3;
 
     // Resident views: every warp pulls its next tile from the global counter.  Streamed views: the CTA pulls a BATCH (one tile
-    // per warp; the warps walk the views together) whose tiles lie side by side, 4 wide (a strip of tiles when the rows are
-    // striped: stripes are one tile high), so that the CTA-level cull sees a narrow cone.
+    // per warp; the warps walk the views together) whose tiles lie side by side, 4 x 4 (flatter when the rows are striped: a batch
+    // stays inside one stripe), so that the CTA-level cull sees a narrow cone.
     __shared__ unsigned int s_batch;
     const int nw = (int)(blockDim.x >> 5);
-    const int bw = sr > 0 ? nw : RTE_BATCH_W, bh = nw / bw;
+    int bh = nw / RTE_BATCH_W;                                  // rows of tiles per batch ...
+    if (sr > 0) bh = min(bh, max(1, sr / TH));                   // ... within one stripe of rows (stripe_rows is a multiple of 4)
+    while (bh > 1 && (nw % bh != 0 || (sr > 0 && (sr / TH) % bh != 0))) --bh;
+    const int bw = nw / bh;
     const int batches_x = (tiles_x + bw - 1) / bw, batches_y = (tiles_y + bh - 1) / bh;
     const unsigned int n_batches = (unsigned int)(batches_x * batches_y);
     unsigned int tile = 0;

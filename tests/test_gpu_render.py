@@ -307,13 +307,15 @@ def test_tile_culling_changes_nothing(engine, cfg):
         assert sa["sphere_tests_executed"] < sb["sphere_tests_executed"], (sa["sphere_tests_executed"], sb["sphere_tests_executed"])
 
 
-def test_fast_kernel_stripes(engine):
-    """Interleaved stripes through the fast kernel == the same rows of the full frame."""
+@pytest.mark.parametrize("cfg", ["c2_stripe8", "c5_streamed_stripe8", "c5_streamed_stripe16", "c5_streamed_stripe4"])
+def test_fast_kernel_stripes(engine, cfg):
+    """Interleaved stripes through the fast kernel == the same rows of the full frame (streamed views: the CTA's batch of
+    tiles stays inside one stripe, 16 x 1, 8 x 2 or 4 x 4 tiles)."""
     from raytracingengine_b200 import sharding
-    arrays, cam = scenes.config2(scale=0.1)
+    arrays, cam = scenes.config2(scale=0.1) if cfg == "c2_stripe8" else scenes.config5(scale=1 / 24)
     engine.upload(arrays, cam)
     full = engine.render_host(outputs=("hdr64",))["hdr64"].reshape(cam.height, cam.width, 3)
-    world, S = 3, 8
+    world, S = 3, int(cfg.split("stripe")[1])
     for r in range(world):
         o = sharding.stripe_opts(r, world, cam.height, S)
         part = engine.render_host(outputs=("hdr64",), **o)["hdr64"]
