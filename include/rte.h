@@ -168,8 +168,10 @@ typedef struct rte_render_opts {
  *   EXACT_SHADOWS  every shadow ray takes the literal RE/Scene.h:35-77 march instead of the any-hit query;
  *   NO_FILTER      the FP32 filters accept everything, i.e. every primitive is tested in FP64;
  *   GENERAL_KERNEL never take the lean kernel specialised for diffuse scenes without AOVs;
- *   NO_CULL        the lean kernel scans every view in full instead of the per-tile culled copy. */
-enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4, RTE_FLAG_NO_CULL = 8 };
+ *   NO_CULL        the lean kernel scans every view in full instead of the per-tile culled copy;
+ *   SINGLE_PASS /  the lean kernel traces primary rays and shades in one launch / in two launches (primary hits, then
+ *   TWO_PASS       shading); without either flag large frames of heavy scenes take two launches, everything else one. */
+enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4, RTE_FLAG_NO_CULL = 8, RTE_FLAG_SINGLE_PASS = 16, RTE_FLAG_TWO_PASS = 32 };
 
 /* Output buffers of one render call.  Every pointer is optional (NULL = not wanted) and is a
  * DEVICE pointer for rte_render() and a HOST pointer for rte_render_host().  Each buffer holds

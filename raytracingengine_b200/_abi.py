@@ -36,6 +36,7 @@ TM_COUNT = 7
 TM_NONE = -1
 TM_ACES = 6
 FLAG_EXACT_SHADOWS, FLAG_NO_FILTER, FLAG_GENERAL_KERNEL, FLAG_NO_CULL = 1, 2, 4, 8
+FLAG_SINGLE_PASS, FLAG_TWO_PASS = 16, 32
 IPC_HANDLE_BYTES = 64  # RTE_IPC_HANDLE_BYTES
 MAX_PEERS = 8          # RTE_MAX_PEERS
 MAX_DEPTH = 24         # RTE_MAX_DEPTH

@@ -69,7 +69,7 @@ struct rte_ctx {
     rte_stats stats{};
 
     // staging for the *_host variants (grow-only)
-    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64;
+    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64, s_hits;
     DevBuf s_tm_in, s_tm_out[RTE_TM_COUNT], s_q_o, s_q_d, s_q_m, s_q_out;
 };
 
@@ -231,7 +231,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
-                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->s_hits, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -469,6 +469,12 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     p.no_cull = (o.flags & RTE_FLAG_NO_CULL) ? 1 : 0;
     p.bias = o.bias; p.max_white = o.max_white; p.jodie_a = o.jodie_a;
     p.out = *frame;
+    p.pass_mode = (o.flags & RTE_FLAG_SINGLE_PASS) ? 1 : (o.flags & RTE_FLAG_TWO_PASS) ? 2 : 0;
+    if (p.pass_mode != 1 && o.n_rows > 0 && two_pass_wanted(p)) {  // nearest hits between the two launches of the fast path (16 B per pixel)
+        int rc = reserve(ctx, ctx->s_hits, (size_t)o.n_rows * (size_t)ctx->cam.width * sizeof(double2));
+        if (rc) return rc;
+        p.hits = (double2*)ctx->s_hits.p;
+    }
     p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
     if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
     // RGB8 (band buffer and / or registered peer frames) = the exact FP64 operator over the FP64 HDR of the render kernel, as

@@ -44,6 +44,8 @@ struct RenderParams {
     int32_t cull;            // fast kernel: per-warp cull scratch follows the staged arrays in dynamic shared memory (rte_views.cuh)
     int32_t no_cull;         // RTE_FLAG_NO_CULL: never use it (validation / A-B)
     int32_t cta_cull;        // streamed views: the CTA-level cull scratch follows the per-warp scratch (rte_views.cuh)
+    int32_t pass_mode;       // fast kernel: 0 = auto, 1 = RTE_FLAG_SINGLE_PASS, 2 = RTE_FLAG_TWO_PASS (primary-ray launch + shading launch)
+    double2* hits;           // two-pass fast path: {t, (kind << 30 | index) as the low word of the second double} per band pixel
     unsigned int* tile_counter;        // zeroed before launch
     unsigned long long* stats;         // kStatCount counters, zeroed before launch
 };
@@ -52,6 +54,8 @@ struct RenderParams {
 size_t scene_smem_bytes(const DevScene& sc);
 // largest dynamic shared memory size the device allows per block (opt-in)
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream);
+// would launch_render split this call into a primary-ray launch and a shading launch (it then needs p.hits)?
+bool two_pass_wanted(const RenderParams& p);
 // (re)builds sc.views for this camera / bias (rte_views.cuh); a no-op for scenes without spheres
 cudaError_t launch_build_views(const DevScene& sc, const DevCamera& cam, double bias, cudaStream_t stream);
 

@@ -578,11 +578,13 @@ struct ViewsStream {
 // the thread (one copy of the FP64 code, per-pixel state in local memory), only the two sphere scans are
 // unrolled over K.  The general kernel's per-pixel code is ~4x larger and stalls on instruction fetch.
 // kTris: the scene has triangles and their views are resident (s_tviews): a third scan after the planes.
-template <int K, bool kTris, class Views>
+// kPhase: 0 = the whole of TraceRay; 1 = primary rays only (nearest hit of every pixel -> P.hits[pix]); 2 = everything after the
+// nearest hit (reads P.hits[pix]).  Two launches of half the code each: the kernel waits on instruction fetch.
+template <int K, bool kTris, class Views, int kPhase = 0>
 __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const ulonglong2* s_tviews,
                                                 const float* s_cold, const float* s_tcold, const float4* s_sph, const float4* s_tri, const CullScratch* cull,
-                                                const CtaCull* cc, const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K], int sample, PixelCounters& cnt,
-                                                d3 (&result)[K]) {
+                                                const CtaCull* cc, const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K], const int64_t (&pix)[K], int sample,
+                                                PixelCounters& cnt, d3 (&result)[K]) {
     const d3 cam_o = ld3(P.cam.pos);
     const double bias = P.bias;
     const int nl = sc.nl, np = sc.np, ns = sc.ns, nt = kTris ? sc.nt : 0;
@@ -597,10 +599,39 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         found[k] = false;
         h[k].t = 0.0; h[k].kind = RTE_HIT_NONE; h[k].idx = 0;
     }
-    {
+    if (kPhase != 2) {
         const ulonglong2* v0 = views.acquire(0);
         if (ns > 0) closest_spheres_view<K>(sc, v0, s_cold, cam_o, dir, alive, false, h, found, cnt.confirms, cull, &cnt.sph_exec, cc);
         views.release();
+    }
+    if (kPhase == 1) {  // planes after the spheres, strict '<' (RE/Scene.h:218-257); the hit goes to the shading launch
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            if (!alive[k]) continue;
+            const d3 d = dir[k];
+            Hit hk = h[k];
+            bool fk = found[k];
+#pragma unroll 1
+            for (int i = 0; i < np; ++i) {
+                double t;
+                if (plane_exact(sc.planes[i], cam_o, d, t) && (!fk || t < hk.t)) {
+                    fk = true; hk.t = t; hk.kind = RTE_HIT_PLANE; hk.idx = (uint32_t)i;
+                }
+            }
+            const unsigned long long packed = fk ? (((unsigned long long)hk.kind << 32) | hk.idx) : 0ull;  // RTE_HIT_NONE = 0
+            P.hits[pix[k]] = make_double2(hk.t, __longlong_as_double((long long)packed));
+        }
+        return;
+    }
+    if (kPhase == 2) {
+#pragma unroll 1
+        for (int k = 0; k < K; ++k) {
+            if (!alive[k]) continue;
+            const double2 v = P.hits[pix[k]];
+            const unsigned long long packed = (unsigned long long)__double_as_longlong(v.y);
+            h[k].t = v.x; h[k].kind = (uint32_t)(packed >> 32); h[k].idx = (uint32_t)packed;
+            found[k] = h[k].kind != RTE_HIT_NONE;
+        }
     }
 
     d3 Pn[K], normal[K], diffuse[K];
@@ -632,7 +663,7 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         if (alive[k]) {
             cnt.sph += (uint32_t)ns; cnt.pl += (uint32_t)np; cnt.tri += (uint32_t)nt;
 #pragma unroll 1
-            for (int i = 0; i < (kTris ? 0 : np); ++i) {  // planes after the spheres, strict '<' (RE/Scene.h:218-257)
+            for (int i = 0; i < ((kTris || kPhase == 2) ? 0 : np); ++i) {  // planes after the spheres, strict '<' (RE/Scene.h:218-257)
                 double t;
                 if (plane_exact(sc.planes[i], cam_o, d, t) && (!fk || t < hk.t)) {
                     fk = true; hk.t = t; hk.kind = RTE_HIT_PLANE; hk.idx = (uint32_t)i;
@@ -795,7 +826,8 @@ constexpr int kBigThreads = RTE_BIG_THREADS;  // block size of the streamed-view
 
 // kBig = false: kFastThreads x kFastMinBlocks CTAs per SM; kBig = true: one 512-thread CTA per SM (views of large scenes)
 // kStream = true (implies kBig): the views pass through two shared-memory buffers (ViewsStream), tile batches are CTA-uniform
-template <int K, bool kBig, bool kStream, bool kTris = false>
+// kPhase (resident sphere views, one sample per pixel): 0 = one launch; 1 / 2 = the primary-ray launch and the shading launch
+template <int K, bool kBig, bool kStream, bool kTris = false, int kPhase = 0>
 __global__ void __launch_bounds__(kBig ? kBigThreads : kFastThreads, kBig ? 1 : kFastMinBlocks)
 render_fast_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
@@ -893,6 +925,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         }
         int px[K], py[K];
         bool inb[K];
+        int64_t pix[K];  // band-local pixel index
         uint32_t n_in = 0;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -900,7 +933,8 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             px[k] = tx * kTileW + lx;
             py[k] = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
             inb[k] = have && px[k] < W && band_y < rows;
-            n_in += inb[k] ? 1u : 0u;
+            pix[k] = (int64_t)band_y * W + px[k];
+            n_in += (inb[k] && kPhase != 2) ? 1u : 0u;
         }
         PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
         d3 c[K];
@@ -911,8 +945,8 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             for (int k = 0; k < K; ++k) sum[k] = mk(0.0, 0.0, 0.0);
 #pragma unroll 1
             for (int s = 0; s < aa; ++s) {
-                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, cc, px, py, inb, s, cnt, c);
-                else trace_tile_fast<K, kTris>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, nullptr, px, py, inb, s, cnt, c);
+                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, cc, px, py, inb, pix, s, cnt, c);
+                else trace_tile_fast<K, kTris, ViewsResident, kPhase>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, nullptr, px, py, inb, pix, s, cnt, c);
                 if (aa > 1) {
 #pragma unroll 1
                     for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
@@ -926,9 +960,8 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         }
 #pragma unroll 1
         for (int k = 0; k < K; ++k) {
-            if (!inb[k]) continue;
-            const int band_y = ty * TH + k * kTileH + ly;
-            const int64_t oi = (int64_t)band_y * W + px[k];
+            if (!inb[k] || kPhase == 1) continue;
+            const int64_t oi = pix[k];
             const d3 v = c[k];
             // streaming stores (st.global.cs): the framebuffers are write-once and must not evict the threads' local memory from L2
             if (P.out.hdr) __stcs(reinterpret_cast<float4*>(P.out.hdr) + oi, make_float4((float)v.x, (float)v.y, (float)v.z, 0.f));
@@ -1068,6 +1101,17 @@ bool fast_path_eligible(const RenderParams& p) {
            !p.no_filter && !f.prim_id && !f.depth && !f.depth64 && !f.normal && !f.albedo && !f.light_mask;
 }
 
+// Two launches of half the code each pay on big frames of heavy scenes (C2 at 4K: 2.93 -> 2.68 ms); every launch of the
+// persistent kernel has a floor of ~0.1 ms (ramp-up + the tail of 50 us tiles), which light scenes (C3: 0.85 -> 0.91 ms) and
+// small row bands do not earn back.
+bool two_pass_wanted(const RenderParams& p) {
+    if (!fast_path_eligible(p) || p.force_general || p.plan.stream_views || p.sc.nt > 0 || p.cam.aa != 1 || kViewPixels != 1) return false;
+    if (p.pass_mode == 1) return false;
+    if (p.pass_mode == 2) return true;
+    const long long entries = (long long)(1 + p.sc.nl) * p.sc.ns_pad, pixels = (long long)p.n_rows * p.cam.width;
+    return entries >= 2048 && pixels >= (3ll << 20);
+}
+
 cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t stream) {
     RenderParams p = p0;
     if (p.plan.stream_views && !(fast_path_eligible(p) && !p.force_general)) {
@@ -1088,6 +1132,15 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
             return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false, true>,
                                     (const void*)render_fast_kernel<kViewPixels, true, false, true>, kFastThreads, kFastMinBlocks, kViewPixels, p,
                                     sm_count, stream, true, limit, kBigThreads);
+        if (p.hits && two_pass_wanted(p)) {
+            // two launches of half the code each: primary rays (nearest hit -> p.hits), then shading
+            const void* f1 = (const void*)render_fast_kernel<1, false, false, false, 1>;
+            const void* f2 = (const void*)render_fast_kernel<1, false, false, false, 2>;
+            cudaError_t e = launch_render_fn(f1, f1, kFastThreads, kFastMinBlocks, 1, p, sm_count, stream, true, limit, kFastThreads);
+            if (e != cudaSuccess) return e;
+            if ((e = cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
+            return launch_render_fn(f2, f2, kFastThreads, kFastMinBlocks, 1, p, sm_count, stream, true, limit, kFastThreads);
+        }
         return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false>, (const void*)render_fast_kernel<kViewPixels, true, false>,
                                 kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream, true, limit, kBigThreads);
     }

@@ -281,6 +281,15 @@ def test_fast_kernel_is_bit_identical(engine, oracle, cfg):
     for k in COUNTERS:
         assert sf[k] == o[k] == sg[k], f"counter {k}: fast {sf[k]}, general {sg[k]}, oracle {o[k]}"
     assert sf["sphere_tests_executed"] > 0 or arrays.counts()["spheres"] == 0
+    # one launch (primary rays + shading) and two launches (nearest hits through a device buffer, then shading): same bits.
+    # Where the two-launch path does not apply (streamed views, triangles) RTE_FLAG_TWO_PASS is ignored.
+    for flag in (_abi.FLAG_SINGLE_PASS, _abi.FLAG_TWO_PASS):
+        alt = engine.render_host(outputs=("hdr64", "hdr", "rgb8"), tonemap_op=_abi.TM_ACES, flags=flag, **opts)
+        sa = engine.stats()
+        for k in ("hdr64", "hdr", "rgb8"):
+            assert np.array_equal(fast[k], alt[k]), (flag, k)
+        for k in COUNTERS:
+            assert sa[k] == sf[k], (flag, k)
 
 
 @pytest.mark.parametrize("cfg", ["c2", "c5_streamed", "c4_blob", "mixed"])

@@ -1,5 +1,5 @@
 """Developer probe (not the bench contract): device time of the render / tonemap kernels per config."""
-import sys, time, json
+import os, sys, time, json
 import numpy as np
 sys.path.insert(0, ".")
 from raytracingengine_b200 import _abi, scenes
@@ -17,7 +17,7 @@ def main():
         rgb = [e.malloc(n * 3 + 16) for _ in range(7)]
         full = "--rgb8" in sys.argv
         for it in range(3):
-            e.render_device({"hdr": hdr, "rgb8": rgb[0]} if full else {"hdr": hdr}, **({"tonemap_op": _abi.TM_ACES} if full else {}))
+            e.render_device({"hdr": hdr, "rgb8": rgb[0]} if full else {"hdr": hdr}, flags=int(os.environ.get("RTE_FLAGS", "0")), **({"tonemap_op": _abi.TM_ACES} if full else {}))
             s = e.stats()
         flops = _abi.algorithmic_flops(s["sphere_tests"], s["plane_tests"], s["triangle_tests"])
         rays = s["primary_rays"] + s["shadow_rays"] + s["secondary_rays"]
