@@ -125,9 +125,10 @@ def ncu_traffic(kernel_prefix: str):
                 d = json.load(f)
         except (OSError, ValueError):
             continue
-        for name, v in d.items():
-            if kernel_prefix in name:
-                return {"bytes": int(v["dram_bytes_read"] + v["dram_bytes_write"]), "source": os.path.relpath(path, ROOT), "kernel": name}
+        hit = {name: v for name, v in d.items() if kernel_prefix in name}  # (the render step is two launches: <..., 1> and <..., 2>)
+        if hit:
+            return {"bytes": int(sum(v["dram_bytes_read"] + v["dram_bytes_write"] for v in hit.values())), "source": os.path.relpath(path, ROOT),
+                    "kernel": " + ".join(sorted(hit))}
     return None
 
 
@@ -362,6 +363,7 @@ def run_gpu(args) -> None:
                 kernel_ms.append(eng.stats()["kernel_ms"])  # syncs; per-launch time of the render kernel alone
         sync_all()
     wall = time.perf_counter() - wall0
+    launches_per_render = eng.last_render_launches()  # rte_render of the last timed step: render launch(es) + the RGB8 pass
     step_ms = [a.elapsed_time(b) for a, b in ev]
     my_ms = sum(step_ms)
     st = eng.stats()
@@ -452,8 +454,8 @@ def run_gpu(args) -> None:
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "ms_per_step": round(e2e_ms, 3), "h2d_bytes_per_step": int(scene_bytes),
                 "d2h_bytes_per_step": int(my_rows * W * 3), "api": "rte_upload_scene + rte_render_host (pinned host RGB8)"},
         # per step and rank: render kernel + exact tonemap pass (auto-white pipeline: render, max-luminance, tonemap); memsets and NCCL are not ours
-        "gpu_launches": args.steps * (3 if auto_white else 2),
-        "roofline": {"bound": "fp32", "kernel": "rte::render_fast_kernel (+ rte::tonemap64_kernel, ~1 % of the call)", "achieved": round(achieved_tf, 3), "peak": round(fp32_peak_tf, 3),
+        "gpu_launches": args.steps * (launches_per_render + (2 if auto_white else 0)),  # render call (+ max luminance + tonemap for c5); NCCL kernels not counted
+        "roofline": {"bound": "fp32", "kernel": "rte::render_fast_kernel (primary-ray launch + shading launch on big frames; + rte::tonemap64_kernel, ~1 % of the call)", "achieved": round(achieved_tf, 3), "peak": round(fp32_peak_tf, 3),
                      "unit": "TFLOP/s", "frac": round(achieved_tf / fp32_peak_tf, 4),
                      "traffic": (tr_render or {}).get("bytes") if args.workload == "c2" and world == 1 else None, "traffic_capture": tr_render,
                      "peak_source": "FFMA micro-benchmark in this process (rte_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",

@@ -250,6 +250,9 @@ int rte_render(rte_ctx* ctx, const rte_render_opts* opts, const rte_frame* frame
  * call the end-to-end number is measured through. */
 int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const rte_frame* host_frame);
 int rte_get_stats(rte_ctx* ctx, rte_stats* out);
+/* Kernel launches of this library that the last rte_render / rte_render_host call enqueued (view build, render
+ * launches, RGB8 pass), for callers that account for them (bench.py gpu_launches); negative on error. */
+int rte_last_render_launches(const rte_ctx* ctx);
 
 /* tonemap() / tonemapAll(), RE/RaytracingEngine.cpp:165-214: `hdr` = float4 per pixel (device),
  * rgb8[op] = 3 bytes per pixel (device) for every op whose bit is set in op_mask. */

@@ -66,6 +66,7 @@ struct rte_ctx {
     cudaEvent_t ev_band[kHostBandsMax] = {};
     cudaEvent_t ev_copied = nullptr;
     bool render_timed = false, tonemap_timed = false;
+    int render_launches = 0;  // kernels enqueued by the last render call
     rte_stats stats{};
 
     // staging for the *_host variants (grow-only)
@@ -457,8 +458,10 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     p.sc = ctx->sc; p.cam = ctx->cam;
     const size_t smem_budget = ctx->smem_optin > 4096 ? ctx->smem_optin - 4096 : 0;  // static smem + headroom
     p.plan = plan_smem(ctx->sc, smem_budget);
+    if (first) ctx->render_launches = 0;
     if ((p.plan.use_views || p.plan.use_tri_views) && (ctx->views_dirty || ctx->views_bias != o.bias)) {
         RTE_CUDA(ctx, launch_build_views(ctx->sc, ctx->cam, o.bias, ctx->stream));
+        ctx->render_launches += (ctx->sc.ns > 0 ? 1 : 0) + ((ctx->sc.nt > 0 && ctx->sc.tri_views) ? 1 : 0);
         ctx->views_dirty = false;
         ctx->views_bias = o.bias;
     }
@@ -506,7 +509,9 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
         RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));
     }
     if (o.n_rows > 0) RTE_CUDA(ctx, launch_render(p, ctx->sm_count, ctx->stream));
+    if (o.n_rows > 0) ctx->render_launches += (p.hits && two_pass_wanted(p)) ? 2 : 1;
     if (want_rgb8) RTE_CUDA(ctx, launch_tonemap64(tp, ctx->sm_count, ctx->stream));
+    if (want_rgb8) ctx->render_launches += 1;
     if (last) {
         RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
         RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));
@@ -588,6 +593,8 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
     RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return RTE_OK;
 }
+
+extern "C" int rte_last_render_launches(const rte_ctx* ctx) { return ctx ? ctx->render_launches : -1; }
 
 extern "C" int rte_get_stats(rte_ctx* ctx, rte_stats* out) {
     RTE_ENTER(ctx);

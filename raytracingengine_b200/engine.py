@@ -20,7 +20,7 @@ LIB_PATH = os.environ.get("RTE_B200_LIB") or os.path.join(os.path.dirname(os.pat
 # every symbol include/rte.h declares (tests/test_abi.py checks the header against this list)
 SYMBOLS = (
     "rte_version", "rte_device_count", "rte_last_error", "rte_create", "rte_destroy", "rte_set_stream",
-    "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats",
+    "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats", "rte_last_render_launches",
     "rte_tonemap", "rte_tonemap_host", "rte_tonemap_auto_white", "rte_max_luminance", "rte_max_luminance_device", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
     "rte_malloc", "rte_free", "rte_memcpy_d2h", "rte_memcpy_h2d", "rte_malloc_host", "rte_free_host",
     "rte_write_ppm", "rte_write_png", "rte_set_rgb8_peers", "rte_ipc_export", "rte_ipc_open", "rte_ipc_close",
@@ -58,6 +58,8 @@ def load_library() -> C.CDLL:
     lib.rte_render.argtypes = [C.c_void_p, C.POINTER(_abi.RenderOpts), C.POINTER(_abi.Frame)]
     lib.rte_render_host.argtypes = [C.c_void_p, C.POINTER(_abi.RenderOpts), C.POINTER(_abi.Frame)]
     lib.rte_get_stats.argtypes = [C.c_void_p, C.POINTER(_abi.Stats)]
+    lib.rte_last_render_launches.argtypes = [C.c_void_p]
+    lib.rte_last_render_launches.restype = C.c_int
     tm_args = [C.c_void_p, C.c_void_p, C.c_int64, C.c_uint32, C.c_double, C.c_double, C.POINTER(C.c_void_p)]
     lib.rte_tonemap.argtypes = tm_args
     lib.rte_tonemap_host.argtypes = tm_args
@@ -277,6 +279,10 @@ class Engine:
         s = _abi.Stats()
         self._ck(self.lib.rte_get_stats(self.ctx, C.byref(s)))
         return s.as_dict()
+
+    def last_render_launches(self) -> int:
+        """rte_last_render_launches: kernels the last render call enqueued."""
+        return int(self.lib.rte_last_render_launches(self.ctx))
 
     # ---- tonemap
     @staticmethod

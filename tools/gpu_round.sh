@@ -18,7 +18,7 @@ timeout 600 $CMD > $OUT/${TAG}_plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/${TAG}_ncu_list.log 2>&1
 echo "exit $?"
 echo "== ncu full (render kernel)"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:render_ -s 3 -c 1 -f -o $OUT/${TAG}_render $CMD > $OUT/${TAG}_ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:render_ -s 6 -c 2 -f -o $OUT/${TAG}_render $CMD > $OUT/${TAG}_ncu_full.log 2>&1
 echo "exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:tonemap_kernel -c 1 -f -o $OUT/${TAG}_tonemap $CMD > $OUT/${TAG}_ncu_full_tm.log 2>&1
 echo "exit $?"

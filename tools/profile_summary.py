@@ -74,7 +74,7 @@ if os.path.exists(ll):
     for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
         lines.append(f"| `{k}` | {n} | {t:.0f} | {100 * t / tot:.1f}% |")
     lines += ["", "(`at::` kernels are torch's L2-flush memsets / clones of the harness, not part of the step; `ffma*_peak_kernel` is the",
-              "FP32-peak micro-benchmark; the step itself is one `render_fast_kernel` launch.)", ""]
+              "FP32-peak micro-benchmark; the step itself is the primary-ray launch `render_fast_kernel<..., 1>`, the shading launch `<..., 2>` and `tonemap64_kernel`.)", ""]
     import shutil
     shutil.copy(ll, f"{P}/{name}_launches.csv")
 for f in ("bench.json", "bench_ref.json", "quick.txt", "gpu.txt", "pytest_gpu.txt"):
