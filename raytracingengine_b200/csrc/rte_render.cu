@@ -59,6 +59,9 @@ constexpr int kMaxTreeDepth = RTE_MAX_DEPTH;  // rte.h: largest opts.max_depth (
 #ifndef RTE_STREAM_PIXELS
 #define RTE_STREAM_PIXELS 1
 #endif
+#ifndef RTE_P2_BIG
+#define RTE_P2_BIG 0  // A/B: the shading launch of the two-launch path at kBigThreads (more registers per thread)
+#endif
 #ifndef RTE_SMEM_CONSTS
 #define RTE_SMEM_CONSTS 1
 #endif
@@ -1135,11 +1138,12 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
         if (p.hits && two_pass_wanted(p)) {
             // two launches of half the code each: primary rays (nearest hit -> p.hits), then shading
             const void* f1 = (const void*)render_fast_kernel<1, false, false, false, 1>;
-            const void* f2 = (const void*)render_fast_kernel<1, false, false, false, 2>;
+            const void* f2 = (const void*)render_fast_kernel<1, RTE_P2_BIG != 0, false, false, 2>;
+            const int t2 = RTE_P2_BIG ? kBigThreads : kFastThreads;
             cudaError_t e = launch_render_fn(f1, f1, kFastThreads, kFastMinBlocks, 1, p, sm_count, stream, true, limit, kFastThreads);
             if (e != cudaSuccess) return e;
             if ((e = cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
-            return launch_render_fn(f2, f2, kFastThreads, kFastMinBlocks, 1, p, sm_count, stream, true, limit, kFastThreads);
+            return launch_render_fn(f2, f2, t2, 1, 1, p, sm_count, stream, true, limit, t2);
         }
         return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false>, (const void*)render_fast_kernel<kViewPixels, true, false>,
                                 kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream, true, limit, kBigThreads);
