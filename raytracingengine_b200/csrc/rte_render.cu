@@ -59,6 +59,9 @@ constexpr int kMaxTreeDepth = RTE_MAX_DEPTH;  // rte.h: largest opts.max_depth (
 #ifndef RTE_STREAM_PIXELS
 #define RTE_STREAM_PIXELS 1
 #endif
+#ifndef RTE_P2_STATE
+#define RTE_P2_STATE 0  // A/B: hit point + normal of the shading launch in shared memory (kSt); measured 2.69 -> 2.78 ms on C2: off
+#endif
 #ifndef RTE_P2_BIG
 #define RTE_P2_BIG 0  // A/B: the shading launch of the two-launch path at kBigThreads (more registers per thread)
 #endif
@@ -583,11 +586,13 @@ struct ViewsStream {
 // kTris: the scene has triangles and their views are resident (s_tviews): a third scan after the planes.
 // kPhase: 0 = the whole of TraceRay; 1 = primary rays only (nearest hit of every pixel -> P.hits[pix]); 2 = everything after the
 // nearest hit (reads P.hits[pix]).  Two launches of half the code each: the kernel waits on instruction fetch.
-template <int K, bool kTris, class Views, int kPhase = 0>
+// kSt: hit point and normal of the pixel (six doubles that live across the whole light loop, and across every out-of-line call
+// in it) sit in shared memory, st[c * blockDim.x + threadIdx.x], instead of registers / local memory (K = 1 only).
+template <int K, bool kTris, class Views, int kPhase = 0, bool kSt = false>
 __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const DevScene& sc, Views& views, const ulonglong2* s_tviews,
                                                 const float* s_cold, const float* s_tcold, const float4* s_sph, const float4* s_tri, const CullScratch* cull,
                                                 const CtaCull* cc, const int (&pxs)[K], const int (&pys)[K], const bool (&inb)[K], const int64_t (&pix)[K], int sample,
-                                                PixelCounters& cnt, d3 (&result)[K]) {
+                                                PixelCounters& cnt, d3 (&result)[K], double* __restrict__ st = nullptr) {
     const d3 cam_o = ld3(P.cam.pos);
     const double bias = P.bias;
     const int nl = sc.nl, np = sc.np, ns = sc.ns, nt = kTris ? sc.nt : 0;
@@ -695,7 +700,15 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         const bool frontFace = dot(ng, incoming) < 0.0;
         const d3 N = frontFace ? ng : -ng;
         if (hv && hk.kind == RTE_HIT_SPHERE && frontFace) sf = (int)hk.idx;
-        Pn[k] = P_; normal[k] = normalize(N); mat[k] = m; self[k] = sf;
+        if (kSt) {
+            const d3 nn = normalize(N);
+            const int T = (int)blockDim.x, tid = (int)threadIdx.x;
+            st[tid] = P_.x; st[T + tid] = P_.y; st[2 * T + tid] = P_.z;
+            st[3 * T + tid] = nn.x; st[4 * T + tid] = nn.y; st[5 * T + tid] = nn.z;
+        } else {
+            Pn[k] = P_; normal[k] = normalize(N);
+        }
+        mat[k] = m; self[k] = sf;
         diffuse[k] = mk(0.0, 0.0, 0.0);
     }
     // directLightning, RE/Scene.h:79-129 (diffuse term; specAcc stays 0 without specular materials)
@@ -706,7 +719,15 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
         bool any_cast = false;
 #pragma unroll 1
         for (int k = 0; k < K; ++k) {
-            const d3 vecToLight = Lp - Pn[k];
+            d3 Pk, Nk;
+            if (kSt) {
+                const int T = (int)blockDim.x, tid = (int)threadIdx.x;
+                Pk = mk(st[tid], st[T + tid], st[2 * T + tid]);
+                Nk = mk(st[3 * T + tid], st[4 * T + tid], st[5 * T + tid]);
+            } else {
+                Pk = Pn[k]; Nk = normal[k];
+            }
+            const d3 vecToLight = Lp - Pk;
             const d4 vl = unit_len(vecToLight);
             const double dist = vl.w;
             bool cast = hitv[k] && dist > 0.0;
@@ -714,11 +735,11 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
             double ndl = 0.0;
             if (cast) {
                 L = mk(vl.x, vl.y, vl.z);  // vecToLight / dist
-                ndl = std_max(0.0, dot(normal[k], L));
+                ndl = std_max(0.0, dot(Nk, L));
                 cast = ndl > 0.0 && dist > bias;
             }
             ShadowRay s;
-            s.o = Pn[k] + normal[k] * bias;
+            s.o = Pk + Nk * bias;
             s.d = L; s.dist = dist; s.maxDist = dist - bias; s.ndl = ndl; s.self = self[k]; s.cast = cast;
             sr[k] = s;
             any_cast = any_cast || cast;
@@ -830,7 +851,7 @@ constexpr int kBigThreads = RTE_BIG_THREADS;  // block size of the streamed-view
 // kBig = false: kFastThreads x kFastMinBlocks CTAs per SM; kBig = true: one 512-thread CTA per SM (views of large scenes)
 // kStream = true (implies kBig): the views pass through two shared-memory buffers (ViewsStream), tile batches are CTA-uniform
 // kPhase (resident sphere views, one sample per pixel): 0 = one launch; 1 / 2 = the primary-ray launch and the shading launch
-template <int K, bool kBig, bool kStream, bool kTris = false, int kPhase = 0>
+template <int K, bool kBig, bool kStream, bool kTris = false, int kPhase = 0, bool kSt = false>
 __global__ void __launch_bounds__(kBig ? kBigThreads : kFastThreads, kBig ? 1 : kFastMinBlocks)
 render_fast_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
@@ -876,6 +897,8 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         cta_scratch.part = reinterpret_cast<int*>(base + kCtaCap * 18);
     }
     const CtaCull* cc = (kStream && P.cta_cull) ? &cta_scratch : nullptr;
+    // kSt: six doubles per thread behind the per-warp cull scratch (the launch grants kernel variants with kSt only when they fit)
+    double* px_state = kSt ? reinterpret_cast<double*>(dyn_smem + ((P.plan.total + 15) & ~(size_t)15) + (size_t)(blockDim.x >> 5) * kCullBytesPerWarp) : nullptr;
     ViewsStream views_str;
     if (kStream) {
         views_str.base = dyn_smem;
@@ -949,7 +972,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
 #pragma unroll 1
             for (int s = 0; s < aa; ++s) {
                 if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, cc, px, py, inb, pix, s, cnt, c);
-                else trace_tile_fast<K, kTris, ViewsResident, kPhase>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, nullptr, px, py, inb, pix, s, cnt, c);
+                else trace_tile_fast<K, kTris, ViewsResident, kPhase, kSt>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, nullptr, px, py, inb, pix, s, cnt, c, px_state);
                 if (aa > 1) {
 #pragma unroll 1
                     for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
@@ -1024,8 +1047,10 @@ static thread_local std::vector<LaunchCfg> t_launch_cfgs;
 
 // `cull_ok`: the kernel can use per-warp cull scratch (the fast kernel); it is granted when it fits next to the staged arrays
 // without lowering the number of CTAs per SM.
+// `state_bytes`: shared memory behind the cull scratch that this kernel variant cannot do without (kSt); when it does not fit,
+// the configuration is recorded as unusable (c.fn = NULL) and the caller launches the plain variant.
 static cudaError_t resolve_launch(LaunchCfg& c, const void* fn, const void* fn_big, int small_threads, int small_min_blocks, const RenderParams& p,
-                                  bool cull_ok, size_t smem_limit, int big_threads) {
+                                  bool cull_ok, size_t smem_limit, int big_threads, size_t state_bytes) {
     size_t smem = p.plan.total;
     cudaError_t e = ensure_smem(fn, smem);
     if (e != cudaSuccess) return e;
@@ -1060,12 +1085,23 @@ static cudaError_t resolve_launch(LaunchCfg& c, const void* fn, const void* fn_b
         if ((e = ensure_smem(fn, smem)) != cudaSuccess) return e;  // (a failed probe above may have left a larger request)
     }
     c.fn = fn; c.threads = threads; c.per_sm = per_sm; c.smem = smem;
+    if (state_bytes) {
+        int per_sm2 = 0;
+        const size_t with_state = smem + state_bytes;
+        if (!c.cull || with_state > smem_limit || ensure_smem(fn, with_state) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, fn, threads, with_state) != cudaSuccess || per_sm2 < per_sm) {
+            cudaGetLastError();
+            c.fn = nullptr;
+        } else {
+            c.smem = with_state;
+        }
+    }
     return cudaSuccess;
 }
 
 static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int small_threads, int small_min_blocks, int K,
                                     const RenderParams& p0, int sm_count, cudaStream_t stream, bool cull_ok = false, size_t smem_limit = 0,
-                                    int big_threads = kRenderMaxThreads) {
+                                    int big_threads = kRenderMaxThreads, size_t state_bytes = 0) {
     RenderParams p = p0;
     int dev = 0;
     cudaGetDevice(&dev);
@@ -1078,12 +1114,13 @@ static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int smal
         LaunchCfg c{};
         c.key_fn = fn; c.key_big = fn_big; c.key_smem = p.plan.total; c.key_limit = smem_limit; c.key_dev = dev;
         c.key_threads = small_threads; c.key_minb = small_min_blocks; c.key_bigt = big_threads; c.key_flags = flags;
-        const cudaError_t e = resolve_launch(c, fn, fn_big, small_threads, small_min_blocks, p, cull_ok, smem_limit, big_threads);
+        const cudaError_t e = resolve_launch(c, fn, fn_big, small_threads, small_min_blocks, p, cull_ok, smem_limit, big_threads, state_bytes);
         if (e != cudaSuccess) return e;
         if (t_launch_cfgs.size() >= 64) t_launch_cfgs.clear();
         t_launch_cfgs.push_back(c);
         cfg = &t_launch_cfgs.back();
     }
+    if (!cfg->fn) return cudaErrorInvalidConfiguration;  // (a kSt variant that does not fit: not an error of the device)
     p.cull = cfg->cull;
     p.cta_cull = cfg->cta_cull;
     const int threads = cfg->threads;
@@ -1143,6 +1180,13 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
             cudaError_t e = launch_render_fn(f1, f1, kFastThreads, kFastMinBlocks, 1, p, sm_count, stream, true, limit, kFastThreads);
             if (e != cudaSuccess) return e;
             if ((e = cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
+#if RTE_P2_STATE
+            if (!RTE_P2_BIG) {  // hit point and normal in shared memory when 48 B per thread fit behind the cull scratch
+                const void* f2s = (const void*)render_fast_kernel<1, false, false, false, 2, true>;
+                e = launch_render_fn(f2s, f2s, t2, 1, 1, p, sm_count, stream, true, limit, t2, (size_t)t2 * 48);
+                if (e != cudaErrorInvalidConfiguration) return e;
+            }
+#endif
             return launch_render_fn(f2, f2, t2, 1, 1, p, sm_count, stream, true, limit, t2);
         }
         return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false>, (const void*)render_fast_kernel<kViewPixels, true, false>,
