@@ -270,6 +270,7 @@ def run_gpu(args) -> None:
     # full-frame buffer of EVERY rank over NVLink (rte_set_rgb8_peers; buffers exchanged as CUDA IPC handles), and a
     # 4-byte NCCL all-reduce fences the frame.  "nccl": the stripes are all-gathered by NCCL after the kernel.
     gather = "none" if dist is None else ("nccl" if auto_white else args.gather)
+    use_flag_fence = False
     peer_note = ""
     frame_all = 0
     opened = []
@@ -288,6 +289,22 @@ def run_gpu(args) -> None:
                     opened.append(eng.ipc_open(handles[r].tobytes()))
                     frames.append(opened[-1])
             eng.set_rgb8_peers(frames)
+            if args.fence == "flags":
+                # frame fence without NCCL: every rank's flag array mapped into every rank like the frames (rte_set_fence_peers)
+                my_flags = eng.malloc(4 * _abi.MAX_PEERS)
+                mine = torch.frombuffer(bytearray(eng.ipc_export(my_flags)), dtype=torch.uint8).to(dev)
+                fh = torch.empty(world * _abi.IPC_HANDLE_BYTES, dtype=torch.uint8, device=dev)
+                dist.all_gather_into_tensor(fh, mine)
+                fh = fh.cpu().numpy().reshape(world, _abi.IPC_HANDLE_BYTES)
+                flags = []
+                for r in range(world):
+                    if r == rank:
+                        flags.append(my_flags)
+                    else:
+                        opened.append(eng.ipc_open(fh[r].tobytes()))
+                        flags.append(opened[-1])
+                eng.set_fence_peers(rank, flags)
+                use_flag_fence = True
             ok = torch.ones(1, device=dev)
         except Exception as exc:  # no peer mapping on this box: say so and use the NCCL all-gather
             peer_note = f" (peer frames unavailable: {exc})"
@@ -295,7 +312,11 @@ def run_gpu(args) -> None:
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         if ok.item() < 1:
             eng.set_rgb8_peers([])
+            if use_flag_fence:
+                eng.set_fence_peers(rank, [])
+            use_flag_fence = False
             gather = "nccl"
+        dist.barrier()  # every rank has zeroed its flags before anybody renders
     fence = torch.zeros(1, dtype=torch.float32, device=dev)
     white = torch.zeros(1, dtype=torch.float32, device=dev)
     tm_ptrs = [rgb_local.data_ptr() if op == tm_op else None for op in range(_abi.TM_COUNT)]
@@ -311,7 +332,10 @@ def run_gpu(args) -> None:
             eng.tonemap_auto_white(hdr.data_ptr(), my_rows * W, tm_ptrs, white.data_ptr(), ops=[tm_op])
         elif gather == "peer":
             eng.render_device({"hdr": hdr.data_ptr()}, tonemap_op=tm_op, **ropts)  # RGB8 goes to every rank's frame
-            dist.all_reduce(fence)                                                 # frame fence across ranks
+            if use_flag_fence:
+                eng.frame_fence()            # device-side wait for every rank's "frame delivered" flag (written over NVLink)
+            else:
+                dist.all_reduce(fence)       # frame fence across ranks through NCCL
             return
         else:
             eng.render_device({"hdr": hdr.data_ptr(), "rgb8": rgb_local.data_ptr()}, tonemap_op=tm_op, **ropts)
@@ -389,6 +413,8 @@ def run_gpu(args) -> None:
     if opened or frame_all:
         sync_all()
         eng.set_rgb8_peers([])  # the end-to-end leg returns each rank's stripes to its own host buffer
+        if use_flag_fence:
+            eng.set_fence_peers(rank, [])
 
     def e2e_step():
         eng.upload(arrays, cam)
@@ -443,7 +469,7 @@ def run_gpu(args) -> None:
         "dtype": "f32 filter + f64 confirm", "data": "synthetic",
         "config": {"workload": label, "width": W, "height": H, **arrays.counts(), "seed": 1234 if args.workload != "c5" else 5678,
                    "rays_per_frame": int(rays), "sharding": "single band" if world == 1 else f"interleaved {args.stripe}-row stripes; " + (
-                       "RGB8 stored by the render call's tonemap pass into every rank's frame over NVLink (CUDA IPC peer frames) + 4-byte NCCL all-reduce as frame fence"
+                       ("RGB8 stored by the render call's tonemap pass into every rank's frame over NVLink (CUDA IPC peer frames) + " + ("frame fence through NVLink flags written by the same kernel (rte_frame_fence), no collective" if use_flag_fence else "4-byte NCCL all-reduce as frame fence"))
                        if gather == "peer" else "NCCL all-gather of RGB8" + peer_note),
                    "tonemap": ("auto max-white: max-luminance kernel + " + ("NCCL all-reduce MAX + " if world > 1 else "") + "tonemap pass") if auto_white else "exact FP64 ACES pass over the render kernel's FP64 HDR, inside the same rte_render call",
                    "l2": "256 MiB memset between timed steps; outputs (HDR float4 + RGB8 = 19 B/px) exceed L2",
@@ -492,6 +518,7 @@ def main() -> None:
     ap.add_argument("--stripe", type=int, default=0, help="rows per interleaved stripe at N>1 (0: 8 for c2/c3, 16 for c5 whose streamed-view kernel works on 32x16 pixel batches)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU sample size per pass of the reference leg")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N>1: how the RGB8 stripes reach every rank")
+    ap.add_argument("--fence", default="flags", choices=["flags", "nccl"], help="N>1, --gather peer: frame fence through NVLink flags (rte_frame_fence) or a 4-byte NCCL all-reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fixed-white", action="store_true", help="c5: the reference's constant max_white = 5.0 (fused tonemap) instead of the auto max-white pipeline")
     args = ap.parse_args()

@@ -34,7 +34,8 @@ typedef enum rte_status {
     RTE_ERR_CUDA = -2,      /* CUDA runtime error (sticky for the ctx) */
     RTE_ERR_NO_DEVICE = -3, /* no usable CUDA device: there is no CPU path */
     RTE_ERR_IO = -4,        /* file open / write failure (RE/Image.cpp:14-16,26-28) */
-    RTE_ERR_LIMIT = -5      /* scene exceeds a documented capacity */
+    RTE_ERR_LIMIT = -5,     /* scene exceeds a documented capacity */
+    RTE_ERR_TIMEOUT = -6    /* rte_frame_fence: a peer did not deliver its frame in time */
 } rte_status;
 
 /* HitType, RE/Shape.h:21-26 */
@@ -292,9 +293,20 @@ int rte_intersect_any_before(rte_ctx* ctx, int64_t n_rays, const double* origins
  * of all ranks of the NVSwitch domain, its own included; each render with opts.tonemap_op != RTE_TM_NONE then stores
  * the RGB8 of every pixel it renders at 3*(y*W + x) of EVERY registered frame (peer stores over NVLink, issued by the
  * render kernel while it computes), on top of frame.rgb8 (which may be NULL).  The caller fences the frame with
- * any cross-rank barrier on the same stream.  n_frames = 0 unregisters.  At most RTE_MAX_PEERS frames. */
+ * rte_frame_fence() (below) or any cross-rank barrier on the same stream.  n_frames = 0 unregisters.  At most RTE_MAX_PEERS frames. */
 #define RTE_MAX_PEERS 8
 int rte_set_rgb8_peers(rte_ctx* ctx, int n_frames, uint8_t* const* frames);
+/* Frame fence for the above without a collective library.  Every rank owns an array of RTE_MAX_PEERS uint32 flags
+ * (rte_malloc; mapped into the peers like the frames) and registers the arrays of all ranks, flags[r] = rank r's array,
+ * flags[rank] its own (zeroed by this call; follow it with one cross-rank barrier before the first render).  From then on
+ * the kernel that performs a render's peer stores ends by writing the render's sequence number to flags[r][rank] of every
+ * rank r (system-scope release store over NVLink, after its stores), and rte_frame_fence() enqueues a device-side wait on
+ * the context's stream until every rank has delivered the frame of the last render call: work enqueued behind it sees the
+ * complete frame.  A peer that does not deliver within timeout_ms (<= 0: 2000) makes the NEXT rte_synchronize /
+ * rte_get_stats of this context fail with RTE_ERR_TIMEOUT.  Ranks must issue the same sequence of render calls.
+ * n_ranks = 0 unregisters. */
+int rte_set_fence_peers(rte_ctx* ctx, int rank, int n_ranks, uint32_t* const* flags);
+int rte_frame_fence(rte_ctx* ctx, double timeout_ms);
 /* CUDA IPC plumbing for the above when ranks are processes: export a buffer obtained from rte_malloc as an opaque
  * 64-byte handle, map a peer's handle into this process (enables peer access), unmap it. */
 #define RTE_IPC_HANDLE_BYTES 64

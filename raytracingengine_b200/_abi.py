@@ -18,6 +18,7 @@ RTE_ERR_CUDA = -2
 RTE_ERR_NO_DEVICE = -3
 RTE_ERR_IO = -4
 RTE_ERR_LIMIT = -5
+RTE_ERR_TIMEOUT = -6
 
 HIT_NONE, HIT_SPHERE, HIT_PLANE, HIT_TRIANGLE = 0, 1, 2, 3  # RE/Shape.h:21-26
 PRIM_MISS = 0xFFFFFFFF

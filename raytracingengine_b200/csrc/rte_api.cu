@@ -54,6 +54,12 @@ struct rte_ctx {
     // rte_set_rgb8_peers
     uint8_t* peer_rgb8[kMaxPeers] = {};
     int n_peers = 0;
+    // rte_set_fence_peers
+    uint32_t* fence_flags[kMaxPeers] = {};
+    int n_fence = 0, fence_rank = 0;
+    uint32_t fence_seq = 0;
+    unsigned int* d_fence_counter = nullptr;
+    unsigned int* h_fence_timeout = nullptr;  // mapped pinned word, set by the wait kernel
 
     // launch scratch
     unsigned int* d_tile_counter = nullptr;
@@ -216,6 +222,10 @@ extern "C" int rte_create(int device, rte_ctx** out) {
     CK(cudaMalloc(&ctx->d_stats, sizeof(unsigned long long) * (kStatCount + 1)));
     ctx->d_tile_counter = reinterpret_cast<unsigned int*>(ctx->d_stats + kStatCount);
     CK(cudaMalloc(&ctx->d_maxlum, sizeof(unsigned int)));
+    CK(cudaMalloc(&ctx->d_fence_counter, sizeof(unsigned int)));
+    CK(cudaMemset(ctx->d_fence_counter, 0, sizeof(unsigned int)));
+    CK(cudaHostAlloc(&ctx->h_fence_timeout, sizeof(unsigned int), cudaHostAllocMapped));
+    *ctx->h_fence_timeout = 0u;
     CK(cudaMallocHost(&ctx->h_stats, sizeof(unsigned long long) * (kStatCount + 1)));
     CK(cudaEventCreate(&ctx->ev_r0)); CK(cudaEventCreate(&ctx->ev_r1));
     CK(cudaEventCreate(&ctx->ev_t0)); CK(cudaEventCreate(&ctx->ev_t1));
@@ -239,6 +249,8 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     for (DevBuf& b : ctx->s_tm_out) if (b.p) cudaFree(b.p);
     if (ctx->d_stats) cudaFree(ctx->d_stats);
     if (ctx->d_maxlum) cudaFree(ctx->d_maxlum);
+    if (ctx->d_fence_counter) cudaFree(ctx->d_fence_counter);
+    if (ctx->h_fence_timeout) cudaFreeHost(ctx->h_fence_timeout);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     cudaEvent_t evs[] = {ctx->ev_r0, ctx->ev_r1, ctx->ev_t0, ctx->ev_t1};
     for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
@@ -264,10 +276,18 @@ extern "C" int rte_set_stream(rte_ctx* ctx, void* cuda_stream) {
     return RTE_OK;
 }
 
+static int check_fence_timeout(rte_ctx* ctx) {
+    if (ctx->h_fence_timeout && *ctx->h_fence_timeout) {
+        *ctx->h_fence_timeout = 0u;
+        return fail(ctx, RTE_ERR_TIMEOUT, "rte_frame_fence: a peer did not deliver frame %u in time", ctx->fence_seq);
+    }
+    return RTE_OK;
+}
+
 extern "C" int rte_synchronize(rte_ctx* ctx) {
     RTE_ENTER(ctx);
     RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    return RTE_OK;
+    return check_fence_timeout(ctx);
 }
 
 // ====================================================================================== scene
@@ -485,6 +505,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     Tonemap64Params tp{};
     tp.n_peers = p.tonemap_op == RTE_TM_NONE ? 0 : ctx->n_peers;
     const bool want_rgb8 = p.tonemap_op != RTE_TM_NONE && (p.out.rgb8 || tp.n_peers > 0) && o.n_rows > 0;
+    const bool fence = ctx->n_fence > 0 && tp.n_peers > 0;  // this render delivers a frame to the peers: it also signals them
     if (want_rgb8) {
         const int64_t n_px = (int64_t)o.n_rows * ctx->cam.width;
         if (!p.out.hdr64) {
@@ -510,8 +531,14 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     }
     if (o.n_rows > 0) RTE_CUDA(ctx, launch_render(p, ctx->sm_count, ctx->stream));
     if (o.n_rows > 0) ctx->render_launches += (p.hits && two_pass_wanted(p)) ? 2 : 1;
-    if (want_rgb8) RTE_CUDA(ctx, launch_tonemap64(tp, ctx->sm_count, ctx->stream));
-    if (want_rgb8) ctx->render_launches += 1;
+    if (fence) {
+        ctx->fence_seq += 1;
+        for (int i = 0; i < ctx->n_fence; ++i) tp.fence_flags[i] = ctx->fence_flags[i];
+        tp.n_fence = ctx->n_fence; tp.fence_rank = ctx->fence_rank; tp.fence_seq = ctx->fence_seq; tp.fence_counter = ctx->d_fence_counter;
+        if (!want_rgb8) { tp.n_pixels = 0; tp.rgb8 = nullptr; tp.n_peers = 0; tp.W = ctx->cam.width > 0 ? ctx->cam.width : 1; }  // a rank without rows still signals
+    }
+    if (want_rgb8 || fence) RTE_CUDA(ctx, launch_tonemap64(tp, ctx->sm_count, ctx->stream));
+    if (want_rgb8 || fence) ctx->render_launches += 1;
     if (last) {
         RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
         RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));
@@ -600,6 +627,7 @@ extern "C" int rte_get_stats(rte_ctx* ctx, rte_stats* out) {
     RTE_ENTER(ctx);
     if (!out) return fail(ctx, RTE_ERR_INVALID, "rte_get_stats: out is NULL");
     RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (int rc = check_fence_timeout(ctx)) return rc;
     rte_stats& s = ctx->stats;
     if (ctx->render_timed) {
         const unsigned long long* h = ctx->h_stats;
@@ -792,6 +820,33 @@ extern "C" int rte_set_rgb8_peers(rte_ctx* ctx, int n_frames, uint8_t* const* fr
         if (!frames[i] || ((uintptr_t)frames[i] & 3u) != 0) return fail(ctx, RTE_ERR_INVALID, "rte_set_rgb8_peers: frame %d is NULL or not 4-byte aligned", i);
     for (int i = 0; i < n_frames; ++i) ctx->peer_rgb8[i] = frames[i];
     ctx->n_peers = n_frames;
+    return RTE_OK;
+}
+
+extern "C" int rte_set_fence_peers(rte_ctx* ctx, int rank, int n_ranks, uint32_t* const* flags) {
+    RTE_ENTER(ctx);
+    if (n_ranks < 0 || n_ranks > kMaxPeers) return fail(ctx, RTE_ERR_LIMIT, "rte_set_fence_peers: %d ranks (at most %d)", n_ranks, kMaxPeers);
+    if (n_ranks > 0 && (!flags || rank < 0 || rank >= n_ranks)) return fail(ctx, RTE_ERR_INVALID, "rte_set_fence_peers: flags is NULL or rank %d outside [0,%d)", rank, n_ranks);
+    for (int i = 0; i < n_ranks; ++i)
+        if (!flags[i] || ((uintptr_t)flags[i] & 3u) != 0) return fail(ctx, RTE_ERR_INVALID, "rte_set_fence_peers: flags[%d] is NULL or misaligned", i);
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < n_ranks; ++i) ctx->fence_flags[i] = flags[i];
+    ctx->n_fence = n_ranks; ctx->fence_rank = rank; ctx->fence_seq = 0;
+    if (n_ranks > 0) {
+        RTE_CUDA(ctx, cudaMemsetAsync(flags[rank], 0, sizeof(uint32_t) * kMaxPeers, ctx->stream));
+        RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_fence_counter, 0, sizeof(unsigned int), ctx->stream));
+        RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return RTE_OK;
+}
+
+extern "C" int rte_frame_fence(rte_ctx* ctx, double timeout_ms) {
+    RTE_ENTER(ctx);
+    if (ctx->n_fence <= 0) return fail(ctx, RTE_ERR_INVALID, "rte_frame_fence: no fence peers registered (rte_set_fence_peers)");
+    const double ms = timeout_ms > 0 ? timeout_ms : 2000.0;
+    unsigned int* dev_word = nullptr;
+    RTE_CUDA(ctx, cudaHostGetDevicePointer((void**)&dev_word, ctx->h_fence_timeout, 0));
+    RTE_CUDA(ctx, launch_fence_wait(ctx->fence_flags[ctx->fence_rank], ctx->n_fence, ctx->fence_seq, (unsigned long long)(ms * 1e6), dev_word, ctx->stream));
     return RTE_OK;
 }
 

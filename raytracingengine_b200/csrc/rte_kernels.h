@@ -77,7 +77,14 @@ struct Tonemap64Params {
     uint8_t* peer_rgb8[kMaxPeers];
     int32_t n_peers;
     int32_t W, row0, stripe_rows, stripe_period;  // band row -> image row (rte_render_opts)
+    // frame fence (rte_set_fence_peers): when this launch's peer stores are done, flags[r][rank] = seq on every rank r
+    uint32_t* fence_flags[kMaxPeers];
+    int32_t n_fence, fence_rank;
+    uint32_t fence_seq;
+    unsigned int* fence_counter;  // CTAs of this launch that are done (self-resetting)
 };
+// waits (device side, on `stream`) until flags[r] >= seq for every r < n; after timeout_ns writes 1 to *timed_out (mapped host word)
+cudaError_t launch_fence_wait(const uint32_t* flags, int n, uint32_t seq, unsigned long long timeout_ns, unsigned int* timed_out, cudaStream_t stream);
 cudaError_t launch_tonemap64(const Tonemap64Params& p, int sm_count, cudaStream_t stream);
 
 // tonemapAll / tonemap over a float4 HDR buffer (stand-alone HBM-bound pass)

@@ -141,14 +141,56 @@ __global__ void __launch_bounds__(kTmThreads) tonemap64_kernel(const __grid_cons
             }
         }
     }
+    // Frame fence over NVLink, fused into the kernel that does the peer stores: every thread makes its stores visible
+    // system-wide, the last CTA of the launch to get here tells every rank "rank `fence_rank` has delivered frame `seq`".
+    if (P.n_fence > 0) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned int done = atomicAdd(P.fence_counter, 1u);
+            if (done == gridDim.x - 1) {
+                *P.fence_counter = 0u;  // for the next launch (stream order)
+                __threadfence_system();
+                for (int r = 0; r < P.n_fence; ++r)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.fence_flags[r] + P.fence_rank), "r"(P.fence_seq) : "memory");
+            }
+        }
+    }
+}
+
+// One warp: lane r polls flags[r] (this rank's own memory, written by rank r over NVLink) until it reaches `seq`.
+__global__ void fence_wait_kernel(const uint32_t* flags, int n, uint32_t seq, unsigned long long timeout_ns, unsigned int* timed_out) {
+    const int r = (int)threadIdx.x;
+    if (r >= n) return;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (true) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + r) : "memory");
+        if ((int32_t)(v - seq) >= 0) return;  // (sequence numbers wrap)
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t - t0 > timeout_ns) { *timed_out = 1u; return; }
+        __nanosleep(200);
+    }
+}
+
+cudaError_t launch_fence_wait(const uint32_t* flags, int n, uint32_t seq, unsigned long long timeout_ns, unsigned int* timed_out, cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    fence_wait_kernel<<<1, 32, 0, stream>>>(flags, n, seq, timeout_ns, timed_out);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_tonemap64(const Tonemap64Params& p, int sm_count, cudaStream_t stream) {
-    if (p.n_pixels <= 0 || (!p.rgb8 && p.n_peers == 0)) return cudaSuccess;
+    if (p.n_pixels <= 0 || (!p.rgb8 && p.n_peers == 0)) {
+        if (p.n_fence <= 0) return cudaSuccess;
+        // nothing to store (a rank without rows), but the peers wait for this rank's flag: an empty launch signals
+    }
     const int64_t quads = (p.n_pixels + 3) / 4;
     int64_t blocks = (quads + kTmThreads - 1) / kTmThreads;
     const int64_t cap = (int64_t)sm_count * 8;
     if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
     tonemap64_kernel<<<(unsigned)blocks, kTmThreads, 0, stream>>>(p);
     return cudaGetLastError();
 }

@@ -23,7 +23,7 @@ SYMBOLS = (
     "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats", "rte_last_render_launches",
     "rte_tonemap", "rte_tonemap_host", "rte_tonemap_auto_white", "rte_max_luminance", "rte_max_luminance_device", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
     "rte_malloc", "rte_free", "rte_memcpy_d2h", "rte_memcpy_h2d", "rte_malloc_host", "rte_free_host",
-    "rte_write_ppm", "rte_write_png", "rte_set_rgb8_peers", "rte_ipc_export", "rte_ipc_open", "rte_ipc_close",
+    "rte_write_ppm", "rte_write_png", "rte_set_rgb8_peers", "rte_set_fence_peers", "rte_frame_fence", "rte_ipc_export", "rte_ipc_open", "rte_ipc_close",
 )
 
 _lib = None
@@ -72,6 +72,8 @@ def load_library() -> C.CDLL:
     lib.rte_intersect_any_before.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.rte_malloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
     lib.rte_set_rgb8_peers.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p)]
+    lib.rte_set_fence_peers.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+    lib.rte_frame_fence.argtypes = [C.c_void_p, C.c_double]
     lib.rte_ipc_export.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p]
     lib.rte_ipc_open.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_void_p)]
     lib.rte_ipc_close.argtypes = [C.c_void_p, C.c_void_p]
@@ -209,6 +211,15 @@ class Engine:
     def set_rgb8_peers(self, frames: Sequence[int]) -> None:
         arr = (C.c_void_p * max(1, len(frames)))(*[C.c_void_p(p) for p in frames])
         self._ck(self.lib.rte_set_rgb8_peers(self.ctx, len(frames), arr))
+
+    def set_fence_peers(self, rank: int, flags: Sequence[int]) -> None:
+        """rte_set_fence_peers: flags[r] = device pointer of rank r's flag array (RTE_MAX_PEERS uint32); [] unregisters."""
+        arr = (C.c_void_p * max(1, len(flags)))(*[C.c_void_p(p) for p in flags])
+        self._ck(self.lib.rte_set_fence_peers(self.ctx, int(rank), len(flags), arr))
+
+    def frame_fence(self, timeout_ms: float = 0.0) -> None:
+        """rte_frame_fence: device-side wait (on the context's stream) until every rank delivered the last rendered frame."""
+        self._ck(self.lib.rte_frame_fence(self.ctx, float(timeout_ms)))
 
     def ipc_export(self, dev: int) -> bytes:
         buf = C.create_string_buffer(_abi.IPC_HANDLE_BYTES)

@@ -412,6 +412,54 @@ def test_rgb8_peer_frames_equal_the_band_output(engine, cfg):
         engine.set_rgb8_peers([])
 
 
+def test_frame_fence_flags(engine):
+    """rte_set_fence_peers / rte_frame_fence: the kernel that does a render's peer stores ends by writing the render's
+    sequence number into every rank's flag array; the fence waits (device side) for all ranks and times out when one is
+    missing.  One process, one GPU: "rank 1" is a second flag array whose flag this test writes itself."""
+    from raytracingengine_b200.engine import RteError
+    arrays, cam = scenes.config2(scale=0.05)
+    engine.upload(arrays, cam)
+    n = cam.width * cam.height
+    frame = engine.malloc(n * 3)
+    f0, f1 = engine.malloc(4 * _abi.MAX_PEERS), engine.malloc(4 * _abi.MAX_PEERS)
+    engine.h2d(f1, np.zeros(_abi.MAX_PEERS, np.uint32))
+    engine.set_rgb8_peers([frame])
+    try:
+        # one rank: its own flag arrives with the frame
+        engine.set_fence_peers(0, [f0])
+        for seq in (1, 2):
+            engine.render_device({}, tonemap_op=_abi.TM_ACES)
+            engine.frame_fence()
+            engine.synchronize()
+            got = np.zeros(_abi.MAX_PEERS, np.uint32)
+            engine.d2h(got, f0)
+            assert got[0] == seq and not got[1:].any()
+        ref = engine.render_host(outputs=("rgb8",), tonemap_op=_abi.TM_ACES)["rgb8"]
+        out = np.zeros((n, 3), np.uint8)
+        engine.d2h(out, frame)
+        assert np.array_equal(out, ref)
+        # two ranks, rank 1 silent: both arrays get rank 0's flag, the fence times out
+        engine.set_fence_peers(0, [f0, f1])
+        engine.render_device({}, tonemap_op=_abi.TM_ACES)
+        engine.frame_fence(50.0)
+        with pytest.raises(RteError, match="did not deliver"):
+            engine.synchronize()
+        got0, got1 = np.zeros(_abi.MAX_PEERS, np.uint32), np.zeros(_abi.MAX_PEERS, np.uint32)
+        engine.d2h(got0, f0); engine.d2h(got1, f1)
+        assert got0[0] == 1 and got1[0] == 1 and got0[1] == 0
+        # "rank 1" delivers frame 2 before this rank asks: no wait, no error; an empty band still signals
+        two = np.zeros(_abi.MAX_PEERS, np.uint32); two[0] = 1; two[1] = 2
+        engine.h2d(f0, two)
+        engine.render_device({}, tonemap_op=_abi.TM_ACES, row0=cam.height, row1=cam.height)
+        engine.frame_fence(50.0)
+        engine.synchronize()
+        engine.d2h(got0, f0)
+        assert got0[0] == 2 and got0[1] == 2
+    finally:
+        engine.set_fence_peers(0, [])
+        engine.set_rgb8_peers([])
+
+
 def test_ipc_export_open_roundtrip(engine):
     """rte_ipc_export / rte_ipc_open / rte_ipc_close: a second process maps this process' buffer and stores into it."""
     import os, subprocess, sys, textwrap
