@@ -296,22 +296,28 @@ __device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n
     const CullCone cone = make_cull_cone(ax, ay, az, ct, st2);
     int count = 0;
     uint32_t va = v0 + 32u * (uint32_t)lane;
+    // survivors of one group of 32 pairs (pair p of this lane), packed behind `count` in ascending index
+    auto emit = [&](const ulonglong2& A, const ulonglong2& B, uint32_t kw0, uint32_t kw1, int p) {
+        const bool k0 = (int)kw0 < 0, k1 = (int)kw1 < 0;
+        const uint32_t m0 = __ballot_sync(kFullMask, k0), m1 = __ballot_sync(kFullMask, k1);
+        if ((m0 | m1) == 0u) return;
+        uint32_t a0, a1, a2, a3, b0, b1, b2, b3;  // A = {cx0,cx1,cy0,cy1}, B = {cz0,cz1,w0,w1}
+        unpack2_bits(A.x, a0, a1); unpack2_bits(A.y, a2, a3); unpack2_bits(B.x, b0, b1); unpack2_bits(B.y, b2, b3);
+        const int pos = count + __popc(m0 & lt) + __popc(m1 & lt);
+        if (k0 && pos < kCullCap) cull_store(mf, map, pos, __uint_as_float(a0), __uint_as_float(a2), __uint_as_float(b0), __uint_as_float(b2), src ? (int)src[2 * p] : 2 * p);
+        const int pos1 = pos + (k0 ? 1 : 0);
+        if (k1 && pos1 < kCullCap) cull_store(mf, map, pos1, __uint_as_float(a1), __uint_as_float(a3), __uint_as_float(b1), __uint_as_float(b3), src ? (int)src[2 * p + 1] : 2 * p + 1);
+        count += __popc(m0) + __popc(m1);
+    };
+    int p0 = 0;
+    // (two groups per iteration — two independent FFMA2 chains, one vote — measured slower: 2.70 -> 2.78 ms on C2)
 #pragma unroll kCullUnroll
-    for (int p0 = 0; p0 < n_pairs; p0 += 32, va += 1024u) {  // n_pairs is a multiple of 32 (views of >= kCullMin entries are padded to 64)
-        const int p = p0 + lane;
+    for (; p0 < n_pairs; p0 += 32, va += 1024u) {  // n_pairs is a multiple of 32 (views of >= kCullMin entries are padded to 64)
         const ulonglong2 A = lds_u2(va), B = lds_u2(va + 16u);
         uint32_t kw0, kw1;
         cull_keep2(A, B, cone, kw0, kw1);
         if (__any_sync(kFullMask, (int)(kw0 | kw1) < 0)) {  // warp-uniform; ~10 % of the groups of 64 spheres have a survivor
-            const bool k0 = (int)kw0 < 0, k1 = (int)kw1 < 0;
-            const uint32_t m0 = __ballot_sync(kFullMask, k0), m1 = __ballot_sync(kFullMask, k1);
-            uint32_t a0, a1, a2, a3, b0, b1, b2, b3;  // A = {cx0,cx1,cy0,cy1}, B = {cz0,cz1,w0,w1}
-            unpack2_bits(A.x, a0, a1); unpack2_bits(A.y, a2, a3); unpack2_bits(B.x, b0, b1); unpack2_bits(B.y, b2, b3);
-            const int pos = count + __popc(m0 & lt) + __popc(m1 & lt);
-            if (k0 && pos < kCullCap) cull_store(mf, map, pos, __uint_as_float(a0), __uint_as_float(a2), __uint_as_float(b0), __uint_as_float(b2), src ? (int)src[2 * p] : 2 * p);
-            const int pos1 = pos + (k0 ? 1 : 0);
-            if (k1 && pos1 < kCullCap) cull_store(mf, map, pos1, __uint_as_float(a1), __uint_as_float(a3), __uint_as_float(b1), __uint_as_float(b3), src ? (int)src[2 * p + 1] : 2 * p + 1);
-            count += __popc(m0) + __popc(m1);
+            emit(A, B, kw0, kw1, p0 + lane);
             if (count > kCullCap) return count;
         }
     }
