@@ -30,6 +30,9 @@ struct DevBuf {
 
 }  // namespace
 
+#ifndef RTE_HOST_TAIL_DIV
+#define RTE_HOST_TAIL_DIV 8  // the second band = the last 1/8 of the rows (measured on C2 at 4K: 1/4 3.19 ms, 1/6 3.13, 1/8 3.07, 1/12 3.11, 1/16 3.17)
+#endif
 constexpr int kHostBandsMax = 2;    // row bands of one rte_render_host call
 constexpr int kHostBandRows = 1024;  // calls of fewer rows are one band
 
@@ -579,14 +582,14 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
         if ((rc = reserve(ctx, *it.buf, n * it.px_bytes))) return rc;
         *it.dev = it.buf->p;
     }
-    // Two row bands: the second (the last quarter of the rows) is rendered and tonemapped on the context's stream while the
+    // Two row bands: the second (the last eighth of the rows) is rendered and tonemapped on the context's stream while the
     // outputs of the first travel to the host on the copy stream.  Measured on B200 (C2 at 4K, 24.9 MB of RGB8): every extra
     // launch of the persistent render kernel costs ~0.1 ms (ramp-up plus the tail of ~50 us tiles), the copy 0.48 ms: four
-    // equal bands lose more than they hide (3.64 ms against 3.56 ms unsplit), 3/4 + 1/4 hides three quarters of the copy.
+    // equal bands lose more than they hide (3.64 ms against 3.56 ms unsplit), 7/8 + 1/8 hides most of the copy.
     // Bands are whole stripes when the rows are striped; registered peer frames (multi-GPU output exchange) keep one launch.
     const int unit = o.stripe_rows > 0 ? o.stripe_rows : 4;
     int rows_per = o.n_rows;
-    if (o.n_rows >= kHostBandRows && ctx->n_peers == 0) rows_per = (o.n_rows - o.n_rows / 4 + unit - 1) / unit * unit;
+    if (o.n_rows >= kHostBandRows && ctx->n_peers == 0) rows_per = (o.n_rows - o.n_rows / RTE_HOST_TAIL_DIV + unit - 1) / unit * unit;
     if (rows_per < 1) rows_per = 1;
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_copied, ctx->stream));
     RTE_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_copied, 0));  // the copy stream starts behind earlier work of the context
