@@ -1143,13 +1143,13 @@ bool fast_path_eligible(const RenderParams& p) {
 
 // Two launches of half the code each pay on big frames of heavy scenes (C2 at 4K: 2.93 -> 2.68 ms); every launch of the
 // persistent kernel has a floor of ~0.1 ms (ramp-up + the tail of 50 us tiles), which light scenes (C3: 0.85 -> 0.91 ms) and
-// small row bands do not earn back.
+// small row bands (C2: under ~1.3 Mpx) do not earn back.
 bool two_pass_wanted(const RenderParams& p) {
     if (!fast_path_eligible(p) || p.force_general || p.plan.stream_views || p.sc.nt > 0 || p.cam.aa != 1 || kViewPixels != 1) return false;
     if (p.pass_mode == 1) return false;
     if (p.pass_mode == 2) return true;
     const long long entries = (long long)(1 + p.sc.nl) * p.sc.ns_pad, pixels = (long long)p.n_rows * p.cam.width;
-    return entries >= 2048 && pixels >= (3ll << 20);
+    return entries >= 2048 && pixels >= (5ll << 18);  // C2, 1/N of the 4K frame (tools/pass_probe.py): two launches win down to 1/6 (1.4 Mpx), lose at 1/8
 }
 
 cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t stream) {
