@@ -842,6 +842,10 @@ __device__ __forceinline__ void trace_tile_fast(const RenderParams& P, const Dev
 #endif
 constexpr int kFastThreads = RTE_FAST_THREADS;  // block size of the fast kernel when kFastMinBlocks CTAs fit one SM
 constexpr int kFastMinBlocks = RTE_FAST_MINB;
+#ifndef RTE_TRIS_THREADS
+#define RTE_TRIS_THREADS 768
+#endif
+constexpr int kTrisThreads = RTE_TRIS_THREADS;  // scenes with triangle views (C4 at 1080p: 1024 x 64 registers 0.96 ms, 768 x 80 0.84 ms)
 #ifndef RTE_BIG_THREADS
 #define RTE_BIG_THREADS 512
 #endif
@@ -852,13 +856,13 @@ constexpr int kBigThreads = RTE_BIG_THREADS;  // block size of the streamed-view
 // kStream = true (implies kBig): the views pass through two shared-memory buffers (ViewsStream), tile batches are CTA-uniform
 // kPhase (resident sphere views, one sample per pixel): 0 = one launch; 1 / 2 = the primary-ray launch and the shading launch
 template <int K, bool kBig, bool kStream, bool kTris = false, int kPhase = 0, bool kSt = false>
-__global__ void __launch_bounds__(kBig ? kBigThreads : kFastThreads, kBig ? 1 : kFastMinBlocks)
+__global__ void __launch_bounds__(kBig ? kBigThreads : (kTris ? kTrisThreads : kFastThreads), kBig ? 1 : kFastMinBlocks)
 render_fast_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ DevScene s_sc;
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ __align__(8) uint64_t s_vbar[2];
-    __shared__ unsigned long long s_stats[(kBig ? kBigThreads : kFastThreads) / 32][kStatCount];
+    __shared__ unsigned long long s_stats[(kBig ? kBigThreads : (kTris ? kTrisThreads : kFastThreads)) / 32][kStatCount];
 
 #if RTE_SMEM_CONSTS
     // the planes and lights every ray reads (a few hundred bytes) live in shared memory: the L1 is busy with local memory
@@ -1170,7 +1174,7 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
         }
         if (p.sc.nt > 0)
             return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false, true>,
-                                    (const void*)render_fast_kernel<kViewPixels, true, false, true>, kFastThreads, kFastMinBlocks, kViewPixels, p,
+                                    (const void*)render_fast_kernel<kViewPixels, true, false, true>, kTrisThreads, kFastMinBlocks, kViewPixels, p,
                                     sm_count, stream, true, limit, kBigThreads);
         if (p.hits && two_pass_wanted(p)) {
             // two launches of half the code each: primary rays (nearest hit -> p.hits), then shading
