@@ -63,6 +63,10 @@ struct rte_ctx {
     uint32_t fence_seq = 0;
     unsigned int* d_fence_counter = nullptr;
     unsigned int* h_fence_timeout = nullptr;  // mapped pinned word, set by the wait kernel
+    // rte_upload_scene: pinned staging of the flattened scene arrays (the H2D copies are asynchronous, no stream sync at the end)
+    unsigned char* h_stage = nullptr;
+    size_t h_stage_cap = 0, h_stage_off = 0;
+    cudaEvent_t ev_stage = nullptr;
 
     // launch scratch
     unsigned int* d_tile_counter = nullptr;
@@ -128,11 +132,37 @@ int reserve(rte_ctx* ctx, DevBuf& b, size_t bytes) {
     return RTE_OK;
 }
 
+// The staging buffer holds `bytes` more (grow-only); waits for the copies of the previous upload that still read it.
+int stage_begin(rte_ctx* ctx, size_t bytes) {
+    if (!ctx->ev_stage) RTE_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_stage, cudaEventDisableTiming));
+    else RTE_CUDA(ctx, cudaEventSynchronize(ctx->ev_stage));
+    if (ctx->h_stage_cap < bytes) {
+        if (ctx->h_stage) RTE_CUDA(ctx, cudaFreeHost(ctx->h_stage));
+        ctx->h_stage = nullptr; ctx->h_stage_cap = 0;
+        RTE_CUDA(ctx, cudaMallocHost(&ctx->h_stage, bytes + bytes / 2));
+        ctx->h_stage_cap = bytes + bytes / 2;
+    }
+    ctx->h_stage_off = 0;
+    return RTE_OK;
+}
+template <class T>
+size_t stage_bytes(const std::vector<T>& v) { return (v.size() * sizeof(T) + 255) & ~(size_t)255; }
+
 template <class T>
 int upload(rte_ctx* ctx, DevBuf& b, const std::vector<T>& v) {
     int rc = reserve(ctx, b, v.size() * sizeof(T));
     if (rc) return rc;
-    if (!v.empty()) RTE_CUDA(ctx, cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    if (v.empty()) return RTE_OK;
+    const size_t bytes = v.size() * sizeof(T);
+    if (ctx->h_stage && ctx->h_stage_off + bytes <= ctx->h_stage_cap) {  // through the pinned staging buffer: truly asynchronous
+        unsigned char* h = ctx->h_stage + ctx->h_stage_off;
+        memcpy(h, v.data(), bytes);
+        ctx->h_stage_off += (bytes + 255) & ~(size_t)255;
+        RTE_CUDA(ctx, cudaMemcpyAsync(b.p, h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    } else {
+        RTE_CUDA(ctx, cudaMemcpyAsync(b.p, v.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
+        RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // pageable source about to go out of scope
+    }
     return RTE_OK;
 }
 
@@ -254,6 +284,8 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     if (ctx->d_maxlum) cudaFree(ctx->d_maxlum);
     if (ctx->d_fence_counter) cudaFree(ctx->d_fence_counter);
     if (ctx->h_fence_timeout) cudaFreeHost(ctx->h_fence_timeout);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    if (ctx->ev_stage) cudaEventDestroy(ctx->ev_stage);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     cudaEvent_t evs[] = {ctx->ev_r0, ctx->ev_r1, ctx->ev_t0, ctx->ev_t1};
     for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
@@ -420,11 +452,14 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     if ((rc = reserve(ctx, ctx->b_tviews, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_views_cold, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_tviews_cold, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
+    if ((rc = stage_begin(ctx, stage_bytes(sph32) + stage_bytes(sph64) + stage_bytes(sphmat) + stage_bytes(planes) + stage_bytes(tri32) + stage_bytes(tri64) +
+                               stage_bytes(triinfo) + stage_bytes(mats) + stage_bytes(lights))))
+        return rc;
     if ((rc = upload(ctx, ctx->b_sph32, sph32)) || (rc = upload(ctx, ctx->b_sph64, sph64)) || (rc = upload(ctx, ctx->b_sphmat, sphmat)) ||
         (rc = upload(ctx, ctx->b_planes, planes)) || (rc = upload(ctx, ctx->b_tri32, tri32)) || (rc = upload(ctx, ctx->b_tri64, tri64)) ||
         (rc = upload(ctx, ctx->b_triinfo, triinfo)) || (rc = upload(ctx, ctx->b_mats, mats)) || (rc = upload(ctx, ctx->b_lights, lights)))
         return rc;
-    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the host vectors go out of scope
+    RTE_CUDA(ctx, cudaEventRecord(ctx->ev_stage, ctx->stream));  // (the copies read the staging buffer, not the host vectors: no sync)
 
     DevScene& sc = ctx->sc;
     sc.sph32 = (const float4*)ctx->b_sph32.p; sc.tri32 = (const float4*)ctx->b_tri32.p;
