@@ -283,13 +283,18 @@ def test_fast_kernel_is_bit_identical(engine, oracle, cfg):
     assert sf["sphere_tests_executed"] > 0 or arrays.counts()["spheres"] == 0
     # one launch (primary rays + shading) and two launches (nearest hits through a device buffer, then shading): same bits.
     # Where the two-launch path does not apply (streamed views, triangles) RTE_FLAG_TWO_PASS is ignored.
+    launches = {}
     for flag in (_abi.FLAG_SINGLE_PASS, _abi.FLAG_TWO_PASS):
         alt = engine.render_host(outputs=("hdr64", "hdr", "rgb8"), tonemap_op=_abi.TM_ACES, flags=flag, **opts)
+        launches[flag] = engine.last_render_launches()  # (views are built already: render launch(es) + the RGB8 pass)
         sa = engine.stats()
         for k in ("hdr64", "hdr", "rgb8"):
             assert np.array_equal(fast[k], alt[k]), (flag, k)
         for k in COUNTERS:
             assert sa[k] == sf[k], (flag, k)
+    two_pass_applies = cfg in ("c2", "c2_band", "c2_odd", "c3", "big_resident")  # resident sphere views, no triangles
+    assert launches[_abi.FLAG_SINGLE_PASS] == 2
+    assert launches[_abi.FLAG_TWO_PASS] == (3 if two_pass_applies else 2), launches
 
 
 @pytest.mark.parametrize("cfg", ["c2", "c5_streamed", "c4_blob", "mixed"])
