@@ -908,6 +908,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         views_str.base = dyn_smem;
         views_str.bar = s_vbar; views_str.gsrc = reinterpret_cast<const unsigned char*>(P.sc.views);
         views_str.bytes = P.plan.one_view_bytes; views_str.nv = 1 + P.sc.nl;
+        if (kPhase == 2) { views_str.gsrc += P.plan.one_view_bytes; views_str.nv = P.sc.nl; }  // the shading launch walks the lights' views only
         views_str.start();
     }
 
@@ -975,7 +976,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
             for (int k = 0; k < K; ++k) sum[k] = mk(0.0, 0.0, 0.0);
 #pragma unroll 1
             for (int s = 0; s < aa; ++s) {
-                if (kStream) trace_tile_fast<K, false>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, cc, px, py, inb, pix, s, cnt, c);
+                if (kStream) trace_tile_fast<K, false, ViewsStream, kPhase>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, cc, px, py, inb, pix, s, cnt, c);
                 else trace_tile_fast<K, kTris, ViewsResident, kPhase, kSt>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, nullptr, px, py, inb, pix, s, cnt, c, px_state);
                 if (aa > 1) {
 #pragma unroll 1
@@ -1149,9 +1150,13 @@ bool fast_path_eligible(const RenderParams& p) {
 // persistent kernel has a floor of ~0.1 ms (ramp-up + the tail of 50 us tiles), which light scenes (C3: 0.85 -> 0.91 ms) and
 // small row bands (C2: under ~1.3 Mpx) do not earn back.
 bool two_pass_wanted(const RenderParams& p) {
-    if (!fast_path_eligible(p) || p.force_general || p.plan.stream_views || p.sc.nt > 0 || p.cam.aa != 1 || kViewPixels != 1) return false;
+    if (!fast_path_eligible(p) || p.force_general || p.sc.nt > 0 || p.cam.aa != 1 || kViewPixels != 1) return false;
+    if (p.plan.stream_views && (kStreamPixels != 1 || p.sc.nl < 1)) return false;  // (streamed views: the primary launch keeps view 0 resident)
     if (p.pass_mode == 1) return false;
     if (p.pass_mode == 2) return true;
+    // streamed views: a primary launch with the camera's view resident has no lock step, but no CTA-level cull either (every
+    // tile culls all of the view): C5 at 4K 9.35 -> 9.72 ms.  Only on request.
+    if (p.plan.stream_views) return false;
     const long long entries = (long long)(1 + p.sc.nl) * p.sc.ns_pad, pixels = (long long)p.n_rows * p.cam.width;
     return entries >= 2048 && pixels >= (5ll << 18);  // C2, 1/N of the 4K frame (tools/pass_probe.py): two launches win down to 1/6 (1.4 Mpx), lose at 1/8
 }
@@ -1169,6 +1174,21 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
         cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
         const size_t limit = optin > 4096 ? (size_t)optin - 4096 : 0;  // static shared memory of the kernel
         if (p.plan.stream_views) {
+            if (p.hits && two_pass_wanted(p)) {
+                // primary rays need the camera's view only: it stays resident in a launch of its own (no lock step), and the
+                // shading launch streams the views of the lights
+                RenderParams p1 = p;
+                p1.plan = SmemPlan{};
+                p1.plan.use_views = 1;
+                p1.plan.view_bytes = p.plan.one_view_bytes; p1.plan.one_view_bytes = p.plan.one_view_bytes;
+                p1.plan.total = p.plan.one_view_bytes;
+                const void* f1 = (const void*)render_fast_kernel<1, false, false, false, 1>;
+                cudaError_t e = launch_render_fn(f1, f1, kFastThreads, kFastMinBlocks, 1, p1, sm_count, stream, true, limit, kFastThreads);
+                if (e != cudaSuccess) return e;
+                if ((e = cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
+                const void* f2 = (const void*)render_fast_kernel<1, true, true, false, 2>;
+                return launch_render_fn(f2, f2, kBigThreads, 1, 1, p, sm_count, stream, true, limit, kBigThreads);
+            }
             const void* fn = (const void*)render_fast_kernel<kStreamPixels, true, true>;
             return launch_render_fn(fn, fn, kBigThreads, 1, kStreamPixels, p, sm_count, stream, true, limit, kBigThreads);
         }

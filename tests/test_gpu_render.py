@@ -292,7 +292,7 @@ def test_fast_kernel_is_bit_identical(engine, oracle, cfg):
             assert np.array_equal(fast[k], alt[k]), (flag, k)
         for k in COUNTERS:
             assert sa[k] == sf[k], (flag, k)
-    two_pass_applies = cfg in ("c2", "c2_band", "c2_odd", "c3", "big_resident")  # resident sphere views, no triangles
+    two_pass_applies = cfg in ("c2", "c2_band", "c2_odd", "c3", "big_resident", "c5_streamed", "c5_streamed_band")  # sphere views, no triangles
     assert launches[_abi.FLAG_SINGLE_PASS] == 2
     assert launches[_abi.FLAG_TWO_PASS] == (3 if two_pass_applies else 2), launches
 
