@@ -59,6 +59,9 @@ constexpr int kMaxTreeDepth = RTE_MAX_DEPTH;  // rte.h: largest opts.max_depth (
 #ifndef RTE_STREAM_PIXELS
 #define RTE_STREAM_PIXELS 1
 #endif
+#ifndef RTE_P1_BATCH
+#define RTE_P1_BATCH 1  // primary-ray launch of scenes with streamed views: CTA batches of 4 x 8 tiles + CTA-level cull of the camera's view
+#endif
 #ifndef RTE_P2_STATE
 #define RTE_P2_STATE 0  // A/B: hit point + normal of the shading launch in shared memory (kSt); measured 2.69 -> 2.78 ms on C2: off
 #endif
@@ -894,13 +897,16 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     }
     const CullScratch* cull = P.cull ? &cull_scratch : nullptr;
     CtaCull cta_scratch{nullptr, nullptr, nullptr};
-    if (kStream && P.cta_cull) {
+    // kBatch: the CTA works on batches of adjacent tiles and culls a view once per CTA (streamed views; the primary-ray launch)
+    constexpr bool kBatch = kStream || (kPhase == 1 && RTE_P1_BATCH != 0);
+    if (kBatch && P.cta_cull) {
         unsigned char* base = dyn_smem + ((P.plan.total + 15) & ~(size_t)15) + (size_t)(blockDim.x >> 5) * kCullBytesPerWarp;
         cta_scratch.mini = reinterpret_cast<ulonglong2*>(base);
         cta_scratch.map = reinterpret_cast<uint16_t*>(base + kCtaCap * 16);
         cta_scratch.part = reinterpret_cast<int*>(base + kCtaCap * 18);
     }
-    const CtaCull* cc = (kStream && P.cta_cull) ? &cta_scratch : nullptr;
+    const CtaCull* cc = (kBatch && P.cta_cull) ? &cta_scratch : nullptr;
+    const bool batched = kStream || (kBatch && P.cta_cull);  // (the primary-ray launch without CTA scratch keeps per-warp tiles)
     // kSt: six doubles per thread behind the per-warp cull scratch (the launch grants kernel variants with kSt only when they fit)
     double* px_state = kSt ? reinterpret_cast<double*>(dyn_smem + ((P.plan.total + 15) & ~(size_t)15) + (size_t)(blockDim.x >> 5) * kCullBytesPerWarp) : nullptr;
     ViewsStream views_str;
@@ -931,7 +937,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
     const int batches_x = (tiles_x + bw - 1) / bw, batches_y = (tiles_y + bh - 1) / bh;
     const unsigned int n_batches = (unsigned int)(batches_x * batches_y);
     unsigned int tile = 0;
-    if (!kStream) {
+    if (!batched) {
         if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
         tile = __shfl_sync(kFullMask, tile, 0);
     }
@@ -939,7 +945,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
         bool have;
         int tx, ty;
         unsigned int next = 0;
-        if (kStream) {
+        if (batched) {
             if (threadIdx.x == 0) s_batch = atomicAdd(P.tile_counter, 1u);
             __syncthreads();
             const unsigned int b = s_batch;
@@ -977,7 +983,7 @@ render_fast_kernel(const __grid_constant__ RenderParams P) {
 #pragma unroll 1
             for (int s = 0; s < aa; ++s) {
                 if (kStream) trace_tile_fast<K, false, ViewsStream, kPhase>(P, sc, views_str, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, cc, px, py, inb, pix, s, cnt, c);
-                else trace_tile_fast<K, kTris, ViewsResident, kPhase, kSt>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, nullptr, px, py, inb, pix, s, cnt, c, px_state);
+                else trace_tile_fast<K, kTris, ViewsResident, kPhase, kSt>(P, sc, views_res, s_tviews, s_cold, s_tcold, s_sph, s_tri, cull, kBatch ? cc : nullptr, px, py, inb, pix, s, cnt, c, px_state);
                 if (aa > 1) {
 #pragma unroll 1
                     for (int k = 0; k < K; ++k) sum[k] = sum[k] + c[k];
@@ -1055,7 +1061,7 @@ static thread_local std::vector<LaunchCfg> t_launch_cfgs;
 // `state_bytes`: shared memory behind the cull scratch that this kernel variant cannot do without (kSt); when it does not fit,
 // the configuration is recorded as unusable (c.fn = NULL) and the caller launches the plain variant.
 static cudaError_t resolve_launch(LaunchCfg& c, const void* fn, const void* fn_big, int small_threads, int small_min_blocks, const RenderParams& p,
-                                  bool cull_ok, size_t smem_limit, int big_threads, size_t state_bytes) {
+                                  bool cull_ok, size_t smem_limit, int big_threads, size_t state_bytes, bool cta_ok) {
     size_t smem = p.plan.total;
     cudaError_t e = ensure_smem(fn, smem);
     if (e != cudaSuccess) return e;
@@ -1081,7 +1087,7 @@ static cudaError_t resolve_launch(LaunchCfg& c, const void* fn, const void* fn_b
             c.cull = 1;
             // streamed views: the CTA-level cull scratch behind the per-warp scratch, when it fits as well
             const size_t with_cta = with_cull + kCtaCullBytes;
-            if (p.plan.stream_views && with_cta <= smem_limit && ensure_smem(fn, with_cta) == cudaSuccess &&
+            if ((p.plan.stream_views || cta_ok) && with_cta <= smem_limit && ensure_smem(fn, with_cta) == cudaSuccess &&
                 cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, fn, threads, with_cta) == cudaSuccess && per_sm2 >= per_sm) {
                 smem = with_cta;
                 c.cta_cull = 1;
@@ -1106,11 +1112,11 @@ static cudaError_t resolve_launch(LaunchCfg& c, const void* fn, const void* fn_b
 
 static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int small_threads, int small_min_blocks, int K,
                                     const RenderParams& p0, int sm_count, cudaStream_t stream, bool cull_ok = false, size_t smem_limit = 0,
-                                    int big_threads = kRenderMaxThreads, size_t state_bytes = 0) {
+                                    int big_threads = kRenderMaxThreads, size_t state_bytes = 0, bool cta_ok = false) {
     RenderParams p = p0;
     int dev = 0;
     cudaGetDevice(&dev);
-    const int flags = (cull_ok ? 1 : 0) | (p.no_cull ? 2 : 0) | (p.plan.stream_views ? 4 : 0);
+    const int flags = (cull_ok ? 1 : 0) | (p.no_cull ? 2 : 0) | (p.plan.stream_views ? 4 : 0) | (cta_ok ? 8 : 0);
     const LaunchCfg* cfg = nullptr;
     for (const LaunchCfg& c : t_launch_cfgs)
         if (c.key_fn == fn && c.key_big == fn_big && c.key_smem == p.plan.total && c.key_limit == smem_limit && c.key_dev == dev &&
@@ -1119,7 +1125,7 @@ static cudaError_t launch_render_fn(const void* fn, const void* fn_big, int smal
         LaunchCfg c{};
         c.key_fn = fn; c.key_big = fn_big; c.key_smem = p.plan.total; c.key_limit = smem_limit; c.key_dev = dev;
         c.key_threads = small_threads; c.key_minb = small_min_blocks; c.key_bigt = big_threads; c.key_flags = flags;
-        const cudaError_t e = resolve_launch(c, fn, fn_big, small_threads, small_min_blocks, p, cull_ok, smem_limit, big_threads, state_bytes);
+        const cudaError_t e = resolve_launch(c, fn, fn_big, small_threads, small_min_blocks, p, cull_ok, smem_limit, big_threads, state_bytes, cta_ok);
         if (e != cudaSuccess) return e;
         if (t_launch_cfgs.size() >= 64) t_launch_cfgs.clear();
         t_launch_cfgs.push_back(c);
@@ -1154,9 +1160,8 @@ bool two_pass_wanted(const RenderParams& p) {
     if (p.plan.stream_views && (kStreamPixels != 1 || p.sc.nl < 1)) return false;  // (streamed views: the primary launch keeps view 0 resident)
     if (p.pass_mode == 1) return false;
     if (p.pass_mode == 2) return true;
-    // streamed views: a primary launch with the camera's view resident has no lock step, but no CTA-level cull either (every
-    // tile culls all of the view): C5 at 4K 9.35 -> 9.72 ms.  Only on request.
-    if (p.plan.stream_views) return false;
+    // (streamed views: the primary launch keeps the camera's view resident and culls it per CTA batch: C5 at 4K 9.35 -> 9.19 ms;
+    // with per-warp culls of the whole view it was 9.72 ms)
     const long long entries = (long long)(1 + p.sc.nl) * p.sc.ns_pad, pixels = (long long)p.n_rows * p.cam.width;
     return entries >= 2048 && pixels >= (5ll << 18);  // C2, 1/N of the 4K frame (tools/pass_probe.py): two launches win down to 1/6 (1.4 Mpx), lose at 1/8
 }
@@ -1183,7 +1188,7 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
                 p1.plan.view_bytes = p.plan.one_view_bytes; p1.plan.one_view_bytes = p.plan.one_view_bytes;
                 p1.plan.total = p.plan.one_view_bytes;
                 const void* f1 = (const void*)render_fast_kernel<1, false, false, false, 1>;
-                cudaError_t e = launch_render_fn(f1, f1, kFastThreads, kFastMinBlocks, 1, p1, sm_count, stream, true, limit, kFastThreads);
+                cudaError_t e = launch_render_fn(f1, f1, kFastThreads, kFastMinBlocks, 1, p1, sm_count, stream, true, limit, kFastThreads, 0, RTE_P1_BATCH != 0);
                 if (e != cudaSuccess) return e;
                 if ((e = cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
                 const void* f2 = (const void*)render_fast_kernel<1, true, true, false, 2>;
@@ -1201,7 +1206,7 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
             const void* f1 = (const void*)render_fast_kernel<1, false, false, false, 1>;
             const void* f2 = (const void*)render_fast_kernel<1, RTE_P2_BIG != 0, false, false, 2>;
             const int t2 = RTE_P2_BIG ? kBigThreads : kFastThreads;
-            cudaError_t e = launch_render_fn(f1, f1, kFastThreads, kFastMinBlocks, 1, p, sm_count, stream, true, limit, kFastThreads);
+            cudaError_t e = launch_render_fn(f1, f1, kFastThreads, kFastMinBlocks, 1, p, sm_count, stream, true, limit, kFastThreads);  // (CTA batches + CTA-level cull measured 2.69 -> 2.73 ms here)
             if (e != cudaSuccess) return e;
             if ((e = cudaMemsetAsync(p.tile_counter, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
 #if RTE_P2_STATE
