@@ -332,9 +332,10 @@ def test_fast_kernel_stripes(engine, cfg):
     world, S = 3, int(cfg.split("stripe")[1])
     for r in range(world):
         o = sharding.stripe_opts(r, world, cam.height, S)
-        part = engine.render_host(outputs=("hdr64",), **o)["hdr64"]
         rows = sharding.stripe_row_list(r, world, cam.height, S)
-        assert np.array_equal(part.reshape(len(rows), cam.width, 3), full[rows])
+        for flag in (0, _abi.FLAG_TWO_PASS):  # (two launches: the primary launch of streamed views works on CTA batches inside a stripe)
+            part = engine.render_host(outputs=("hdr64",), flags=flag, **o)["hdr64"]
+            assert np.array_equal(part.reshape(len(rows), cam.width, 3), full[rows]), flag
 
 
 @pytest.mark.parametrize("cfg", ["rows", "stripes", "aovs"])
