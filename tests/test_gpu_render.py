@@ -418,6 +418,36 @@ def test_rgb8_peer_frames_equal_the_band_output(engine, cfg):
         engine.set_rgb8_peers([])
 
 
+@pytest.mark.parametrize("cfg", ["c2_4k", "c5_4k"])
+def test_full_size_properties(engine, oracle, cfg):
+    """BASELINE.json configs[1] at its full size (3840x2160, 1024 spheres, 4 lights) and the C5 scene (4096 spheres, 8
+    lights, streamed views) at 3840x2160: the production path (two launches, tile / CTA culling, two-band host copy)
+    against size-independent properties — the frame equals its row bands rendered by the single-launch kernel (one of
+    them without culling), the counters add up, and sampled rows equal the CPU oracle bit for bit."""
+    arrays, cam = scenes.config2() if cfg == "c2_4k" else scenes.config5(0.5)
+    engine.upload(arrays, cam)
+    full = engine.render_host(outputs=("hdr64", "rgb8"), tonemap_op=_abi.TM_ACES)
+    sf = engine.stats()
+    assert engine.last_render_launches() >= 3  # primary-ray launch + shading launch + RGB8 pass (per band of the host copy)
+    assert sf["primary_rays"] == cam.width * cam.height
+    H, W = cam.height, cam.width
+    tot = {k: 0 for k in COUNTERS}
+    for a in range(0, H, 540):
+        flags = _abi.FLAG_SINGLE_PASS | (_abi.FLAG_NO_CULL if a == 540 else 0)
+        part = engine.render_host(outputs=("hdr64", "rgb8"), tonemap_op=_abi.TM_ACES, row0=a, row1=a + 540, flags=flags)
+        sp = engine.stats()
+        for k in COUNTERS:
+            tot[k] += sp[k]
+        for k in ("hdr64", "rgb8"):
+            assert np.array_equal(full[k][a * W:(a + 540) * W], part[k]), (a, k)
+    for k in COUNTERS:
+        assert sf[k] == tot[k], k
+    for r0 in (0, 1079, 2158):  # top, middle, bottom rows against the oracle
+        o = oracle.render(arrays, cam, row0=r0, row1=r0 + 2, want_aovs=False)
+        assert np.array_equal(full["hdr64"][r0 * W:(r0 + 2) * W], o["hdr"]), r0
+        assert np.array_equal(full["rgb8"][r0 * W:(r0 + 2) * W], oracle.tonemap_all(o["hdr"])[_abi.TM_ACES]), r0
+
+
 def test_frame_fence_flags(engine):
     """rte_set_fence_peers / rte_frame_fence: the kernel that does a render's peer stores ends by writing the render's
     sequence number into every rank's flag array; the fence waits (device side) for all ranks and times out when one is
