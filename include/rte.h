@@ -271,6 +271,18 @@ int rte_max_luminance_device(rte_ctx* ctx, const float* hdr, int64_t n_pixels, f
 int rte_tonemap_auto_white(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t op_mask,
                            const float* max_white_dev, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]);
 
+/* Allocation-free variant of rte_max_luminance_device.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  The call allocates nothing — no cudaMalloc / cudaFree, no allocating library routine: the
+ * reduction's scratch (one partial maximum per 4096 pixels + a counter) is a file-scope static __device__ array of
+ * 64.25 KB that every GPU loading the library holds until exit, so at most RTE_NOALLOC_MAX_PIXELS pixels per call (more:
+ * RTE_ERR_LIMIT).  hdr = float4 per pixel (device, 16-byte aligned), *out_max_dev = device float, stream-ordered on the ctx
+ * stream; same value as rte_max_luminance_device (NaN luminances ignored, 0 for n_pixels == 0).  All calls on one GPU share
+ * the array (it keeps the last call's contents; the call clears what must start at zero): calls that OVERLAP on the GPU —
+ * two contexts or streams of one device — race; calls in stream order do not. */
+#define RTE_NOALLOC_MAX_PIXELS 67108864
+int rte_max_luminance_noalloc(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max_dev);
+
 /* Measurement aid (no reference counterpart): runs a register-resident FFMA kernel on every SM of the
  * ctx device for about `target_ms` and reports the achieved FP32 rate — the measured FP32-FMA roofline
  * denominator bench.py quotes the render kernel against (MEASURED_PEAKS.json has none). */

@@ -42,6 +42,7 @@ IPC_HANDLE_BYTES = 64  # RTE_IPC_HANDLE_BYTES
 MAX_PEERS = 8          # RTE_MAX_PEERS
 MAX_DEPTH = 24         # RTE_MAX_DEPTH
 MAX_AA = 4096          # RTE_MAX_AA
+NOALLOC_MAX_PIXELS = 1 << 26  # RTE_NOALLOC_MAX_PIXELS
 
 # --- numpy dtypes (C layout) -------------------------------------------------------------------
 material_dt = np.dtype(  # Material, RE/Shape.h:13-19

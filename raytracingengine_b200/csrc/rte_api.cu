@@ -772,6 +772,21 @@ extern "C" int rte_max_luminance_device(rte_ctx* ctx, const float* hdr, int64_t 
     return RTE_OK;
 }
 
+// No counterpart in the reference (see include/rte.h): max luminance with no
+// allocation of any kind in the call — the reduction's scratch is a static __device__ array of rte_tonemap.cu.
+extern "C" int rte_max_luminance_noalloc(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max_dev) {
+    RTE_ENTER(ctx);
+    if (!out_max_dev || (n_pixels > 0 && !hdr) || n_pixels < 0) return fail(ctx, RTE_ERR_INVALID, "rte_max_luminance_noalloc: bad arguments");
+    if (((uintptr_t)out_max_dev & 3u) != 0 || ((uintptr_t)hdr & 15u) != 0)
+        return fail(ctx, RTE_ERR_INVALID, "rte_max_luminance_noalloc: hdr must be 16-byte and out_max_dev 4-byte aligned");
+    if (n_pixels > (int64_t)RTE_NOALLOC_MAX_PIXELS)
+        return fail(ctx, RTE_ERR_LIMIT, "rte_max_luminance_noalloc: %lld pixels exceed RTE_NOALLOC_MAX_PIXELS = %lld (the static scratch array holds one partial per 4096 pixels); use rte_max_luminance_device",
+                    (long long)n_pixels, (long long)RTE_NOALLOC_MAX_PIXELS);
+    const cudaError_t e = launch_max_luminance_noalloc((const float4*)hdr, n_pixels, out_max_dev, ctx->device, ctx->stream);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(ctx, RTE_ERR_CUDA, "rte_max_luminance_noalloc: %s (%s)", cudaGetErrorString(e), cudaGetErrorName(e)); }
+    return RTE_OK;
+}
+
 // ====================================================================================== FP32 peak
 static int measure_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms, int packed);
 extern "C" int rte_measure_fp32_peak(rte_ctx* ctx, double target_ms, double* out_tflops, double* out_ms) {

@@ -101,6 +101,10 @@ cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t st
 cudaError_t launch_max_luminance(const float4* hdr, int64_t n_pixels, unsigned int* out_bits, int sm_count,
                                  cudaStream_t stream);
 
+// rte_max_luminance_noalloc: the same maximum into *out_dev (device float) with its scratch in a file-scope device array of
+// rte_tonemap.cu (no cudaMalloc); `device` = the current device; n_pixels <= RTE_NOALLOC_MAX_PIXELS
+cudaError_t launch_max_luminance_noalloc(const float4* hdr, int64_t n_pixels, float* out_dev, int device, cudaStream_t stream);
+
 // register-resident FFMA chains on every SM (rte_peak.cu): *flop_out = FP32 flop the launch executes
 cudaError_t launch_ffma_peak(float* scratch, int outer, int sm_count, cudaStream_t stream, double* flop_out, int packed);
 

@@ -7,6 +7,8 @@
 //   * one thread = 4 consecutive pixels: 4 x LDG.128 in, 3 x STG.32 per operator out (12 B, aligned);
 //   * grid = a multiple of the SM count, grid-stride loop, streaming loads (ld.global.cs) because
 //     nothing is re-read.
+#include <mutex>
+
 #include "rte_kernels.h"
 #include "rte_tonemap.cuh"
 
@@ -213,6 +215,93 @@ __global__ void __launch_bounds__(kTmThreads) max_luminance_kernel(const float4*
         for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
         if (threadIdx.x == 0) atomicMax(out_bits, __float_as_uint(fmaxf(m, 0.0f)));
     }
+}
+
+// ------------------------------------------------------------------------------ allocation-free variant
+// rte_max_luminance_noalloc (include/rte.h; no counterpart in the reference):
+// the same reduction in two stages — every block reduces one fixed chunk of kNaPixelsPerBlock pixels to a partial maximum,
+// the last block to finish (device-scope ticket) reduces the partials — with the partials and the ticket counter in a
+// file-scope device array instead of memory from cudaMalloc.  Every GPU that loads the library holds the array (64.25 KB)
+// until exit; every call on a device shares it, so calls that overlap on the GPU race.
+constexpr int kNaPixelsPerBlock = kTmThreads * 16;
+constexpr int kNaMaxBlocks = 16384;  // x 4096 pixels = RTE_NOALLOC_MAX_PIXELS
+static_assert((long long)kNaMaxBlocks * kNaPixelsPerBlock == RTE_NOALLOC_MAX_PIXELS, "rte.h: RTE_NOALLOC_MAX_PIXELS");
+// [0, kNaMaxBlocks): per-block partial maxima (float bits); [kNaMaxBlocks]: blocks done.  In host code this name is only a
+// stand-in for the symbol: kernels get the address cudaGetSymbolAddress returns (noalloc_scratch_ptr below).
+static __device__ __align__(256) unsigned int g_noalloc_scratch[kNaMaxBlocks + 64];
+
+__device__ __forceinline__ float block_max(float m, float* s_m) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+    if ((threadIdx.x & 31) == 0) s_m[threadIdx.x >> 5] = m;
+    __syncthreads();
+    m = threadIdx.x < kTmThreads / 32 ? s_m[threadIdx.x] : 0.0f;
+    if (threadIdx.x < 32) {
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xFFFFFFFFu, m, o));
+    }
+    return m;  // valid in thread 0
+}
+
+__global__ void __launch_bounds__(kTmThreads) max_luminance_noalloc_kernel(const float4* __restrict__ hdr, int64_t n, unsigned int* scratch,
+                                                                           float* __restrict__ out) {
+    __shared__ float s_m[kTmThreads / 32];
+    __shared__ bool s_last;
+    const int64_t base = (int64_t)blockIdx.x * kNaPixelsPerBlock;
+    const int64_t end = base + kNaPixelsPerBlock < n ? base + kNaPixelsPerBlock : n;
+    float m = 0.0f;
+    for (int64_t i = base + threadIdx.x; i < end; i += kTmThreads) {
+        const float4 v = __ldcs(hdr + i);
+        m = fmaxf(m, tm32::luminance(tm32::mk3(v.x, v.y, v.z)));  // fmaxf drops NaN, like launch_max_luminance
+    }
+    m = block_max(m, s_m);
+    if (threadIdx.x == 0) {
+        scratch[blockIdx.x] = __float_as_uint(fmaxf(m, 0.0f));
+        __threadfence();
+        s_last = atomicAdd(scratch + kNaMaxBlocks, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    m = 0.0f;
+    for (unsigned int b = threadIdx.x; b < gridDim.x; b += kTmThreads) m = fmaxf(m, __uint_as_float(__ldcg(scratch + b)));
+    __syncthreads();  // (s_m is reused)
+    m = block_max(m, s_m);
+    if (threadIdx.x == 0) {
+        *out = m;
+        scratch[kNaMaxBlocks] = 0u;  // the next call (stream order) starts from zero; the launcher clears it as well
+    }
+}
+
+// The device address of g_noalloc_scratch on the CURRENT device, looked up once per device (cudaGetSymbolAddress is not an
+// allocation: the array is part of the module image).
+static cudaError_t noalloc_scratch_ptr(int device, unsigned int** out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static unsigned int* ptrs[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[device]) {
+        unsigned int* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+        if (e != cudaSuccess) return e;
+        ptrs[device] = p;
+    }
+    *out = ptrs[device];
+    return cudaSuccess;
+}
+
+cudaError_t launch_max_luminance_noalloc(const float4* hdr, int64_t n_pixels, float* out_dev, int device, cudaStream_t stream) {
+    if (n_pixels <= 0) return cudaMemsetAsync(out_dev, 0, sizeof(float), stream);
+    if (n_pixels > (int64_t)RTE_NOALLOC_MAX_PIXELS) return cudaErrorInvalidValue;  // (the entry point rejects it with a message first)
+    unsigned int* scratch = nullptr;
+    cudaError_t e = noalloc_scratch_ptr(device, &scratch);
+    if (e != cudaSuccess) return e;
+    // the array keeps the last call's contents: the ticket counter must start at zero (the partials are overwritten before they are read)
+    if ((e = cudaMemsetAsync(scratch + kNaMaxBlocks, 0, sizeof(unsigned int), stream)) != cudaSuccess) return e;
+    const unsigned blocks = (unsigned)((n_pixels + kNaPixelsPerBlock - 1) / kNaPixelsPerBlock);
+    max_luminance_noalloc_kernel<<<blocks, kTmThreads, 0, stream>>>(hdr, n_pixels, scratch, out_dev);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_max_luminance(const float4* hdr, int64_t n_pixels, unsigned int* out_bits, int sm_count, cudaStream_t stream) {

@@ -21,7 +21,7 @@ LIB_PATH = os.environ.get("RTE_B200_LIB") or os.path.join(os.path.dirname(os.pat
 SYMBOLS = (
     "rte_version", "rte_device_count", "rte_last_error", "rte_create", "rte_destroy", "rte_set_stream",
     "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats", "rte_last_render_launches",
-    "rte_tonemap", "rte_tonemap_host", "rte_tonemap_auto_white", "rte_max_luminance", "rte_max_luminance_device", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
+    "rte_tonemap", "rte_tonemap_host", "rte_tonemap_auto_white", "rte_max_luminance", "rte_max_luminance_device", "rte_max_luminance_noalloc", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
     "rte_malloc", "rte_free", "rte_memcpy_d2h", "rte_memcpy_h2d", "rte_malloc_host", "rte_free_host",
     "rte_write_ppm", "rte_write_png", "rte_set_rgb8_peers", "rte_set_fence_peers", "rte_frame_fence", "rte_ipc_export", "rte_ipc_open", "rte_ipc_close",
 )
@@ -65,6 +65,7 @@ def load_library() -> C.CDLL:
     lib.rte_tonemap_host.argtypes = tm_args
     lib.rte_max_luminance.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_float)]
     lib.rte_max_luminance_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    lib.rte_max_luminance_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     lib.rte_tonemap_auto_white.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_uint32, C.c_void_p, C.c_double, C.POINTER(C.c_void_p)]
     lib.rte_measure_fp32_peak.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     lib.rte_measure_fp32x2_peak.argtypes = [C.c_void_p, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -327,6 +328,10 @@ class Engine:
     def max_luminance_device(self, hdr_dev: int, n_pixels: int, out_dev: int) -> None:
         """Stream-ordered: max luminance into a device float (the value a multi-GPU run all-reduces with MAX)."""
         self._ck(self.lib.rte_max_luminance_device(self.ctx, C.c_void_p(hdr_dev), n_pixels, C.c_void_p(out_dev)))
+
+    def max_luminance_noalloc(self, hdr_dev: int, n_pixels: int, out_dev: int) -> None:
+        """rte_max_luminance_noalloc: the same value with the scratch in a static device array (no allocation in the call)."""
+        self._ck(self.lib.rte_max_luminance_noalloc(self.ctx, C.c_void_p(hdr_dev), n_pixels, C.c_void_p(out_dev)))
 
     def tonemap_auto_white(self, hdr_dev: int, n_pixels: int, rgb8_dev: Sequence[Optional[int]], max_white_dev: int, ops=None, jodie_a=0.0) -> None:
         """rte_tonemap with max_white read from a device float (auto max-white, after the all-reduce)."""
