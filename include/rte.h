@@ -171,8 +171,15 @@ typedef struct rte_render_opts {
  *   GENERAL_KERNEL never take the lean kernel specialised for diffuse scenes without AOVs;
  *   NO_CULL        the lean kernel scans every view in full instead of the per-tile culled copy;
  *   SINGLE_PASS /  the lean kernel traces primary rays and shades in one launch / in two launches (primary hits, then
- *   TWO_PASS       shading); without either flag large frames of heavy scenes take two launches, everything else one. */
-enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4, RTE_FLAG_NO_CULL = 8, RTE_FLAG_SINGLE_PASS = 16, RTE_FLAG_TWO_PASS = 32 };
+ *   TWO_PASS       shading); without either flag large frames of heavy scenes take two launches, everything else one.
+ * And one switch that selects the numerics of the PRODUCTION path:
+ *   EXACT_FP64     never take the FP32 production path.  Without it, a call that asks for hdr / rgb8 / prim_id / light_mask
+ *                  only, on a diffuse sphere / plane scene, is shaded in FP32 (hit index and shadow visibility bit-exact — every
+ *                  FP32 decision is certain within its error bound or the pixel is re-rendered in FP64 —, HDR to ~1e-6 relative,
+ *                  RGB8 within +-1 LSB of the reference: the bars BASELINE.json states).  Every FP64 output (hdr64, depth64), the
+ *                  other AOVs and every flag above select the exact FP64 path, whose results are the reference's own bits. */
+enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4, RTE_FLAG_NO_CULL = 8, RTE_FLAG_SINGLE_PASS = 16, RTE_FLAG_TWO_PASS = 32,
+       RTE_FLAG_EXACT_FP64 = 64 };
 
 /* Output buffers of one render call.  Every pointer is optional (NULL = not wanted) and is a
  * DEVICE pointer for rte_render() and a HOST pointer for rte_render_host().  Each buffer holds
@@ -201,7 +208,7 @@ typedef struct rte_stats {
     uint64_t plane_tests;      /*   every primitive, shadow rays count canonical-order tests up  */
     uint64_t triangle_tests;   /*   to and including the first occluder                           */
     uint64_t exact_marches;    /* shadow rays resolved by the exact RE/Scene.h:35-77 march */
-    uint64_t fp64_confirms;    /* FP64 re-evaluations triggered by the FP32 filter */
+    uint64_t fp64_confirms;    /* FP64 re-evaluations triggered by the FP32 filter; FP32 production path: pixel samples re-rendered in FP64 */
     double kernel_ms;          /* device time of the render kernel (CUDA events on the ctx stream) */
     double tonemap_ms;         /* device time of the last tonemap kernel */
     uint64_t sphere_tests_executed; /* ray-sphere filter evaluations the kernel really ran (any-hit rays stop

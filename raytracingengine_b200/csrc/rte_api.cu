@@ -83,7 +83,7 @@ struct rte_ctx {
     rte_stats stats{};
 
     // staging for the *_host variants (grow-only)
-    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64, s_hits;
+    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64, s_hits, s_fix;
     DevBuf s_tm_in, s_tm_out[RTE_TM_COUNT], s_q_o, s_q_d, s_q_m, s_q_out;
 };
 
@@ -252,7 +252,7 @@ extern "C" int rte_create(int device, rte_ctx** out) {
 #define CK(call) do { cudaError_t e2 = (call); if (e2 != cudaSuccess) { int rc = cuda_fail(nullptr, e2, #call); rte_destroy(ctx); return rc; } } while (0)
     CK(cudaSetDevice(device));
     CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    CK(cudaMalloc(&ctx->d_stats, sizeof(unsigned long long) * (kStatCount + 1)));
+    CK(cudaMalloc(&ctx->d_stats, sizeof(unsigned long long) * (kStatCount + 2)));  // counters, tile counter, fix-up list length
     ctx->d_tile_counter = reinterpret_cast<unsigned int*>(ctx->d_stats + kStatCount);
     CK(cudaMalloc(&ctx->d_maxlum, sizeof(unsigned int)));
     CK(cudaMalloc(&ctx->d_fence_counter, sizeof(unsigned int)));
@@ -275,7 +275,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
-                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->s_hits, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -531,13 +531,40 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     p.bias = o.bias; p.max_white = o.max_white; p.jodie_a = o.jodie_a;
     p.out = *frame;
     p.pass_mode = (o.flags & RTE_FLAG_SINGLE_PASS) ? 1 : (o.flags & RTE_FLAG_TWO_PASS) ? 2 : 0;
+    p.exact_fp64 = (o.flags & RTE_FLAG_EXACT_FP64) ? 1 : 0;
+    p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
+    if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
+    // FP32 production path (rte_render32.cu): diffuse sphere / plane scenes with resident views, outputs hdr / rgb8 / prim_id /
+    // light_mask.  The operator runs in the kernel; pixels with an inconclusive FP32 decision go through the exact fix-up launch.
+    // (Registered peer frames / fences keep the exact path: its RGB8 pass performs the peer stores.)
+    if (o.n_rows > 0 && ctx->n_peers == 0 && ctx->n_fence == 0 && fp32_path_eligible(p)) {
+        const size_t n_px = (size_t)o.n_rows * (size_t)ctx->cam.width;
+        if (p.out.rgb8 && ((uintptr_t)p.out.rgb8 & 3u) != 0 && (ctx->cam.width & 3) == 0) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 must be 4-byte aligned");
+        int rc = reserve(ctx, ctx->s_fix, n_px * sizeof(unsigned int));
+        if (rc) return rc;
+        p.fix_list = (unsigned int*)ctx->s_fix.p;
+        p.fix_count = reinterpret_cast<unsigned int*>(ctx->d_stats + kStatCount + 1);
+        if (first) {
+            RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * (kStatCount + 2), ctx->stream));
+            RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
+        } else {
+            RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned long long) * 2, ctx->stream));
+        }
+        RTE_CUDA(ctx, launch_render32(p, ctx->sm_count, ctx->stream));
+        RTE_CUDA(ctx, launch_fixup(p, ctx->sm_count, ctx->stream));
+        ctx->render_launches += 2;
+        if (last) {
+            RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
+            RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));
+            ctx->render_timed = true;
+        }
+        return RTE_OK;
+    }
     if (p.pass_mode != 1 && o.n_rows > 0 && two_pass_wanted(p)) {  // nearest hits between the two launches of the fast path (16 B per pixel)
         int rc = reserve(ctx, ctx->s_hits, (size_t)o.n_rows * (size_t)ctx->cam.width * sizeof(double2));
         if (rc) return rc;
         p.hits = (double2*)ctx->s_hits.p;
     }
-    p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
-    if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
     // RGB8 (band buffer and / or registered peer frames) = the exact FP64 operator over the FP64 HDR of the render kernel, as
     // a second, HBM-bound pass (rte_tonemap.cu: tonemap64_kernel) — the render kernels themselves only write HDR
     Tonemap64Params tp{};
@@ -562,7 +589,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     p.tonemap_op = RTE_TM_NONE;
     // (d_tile_counter sits right behind d_stats: one memset clears both)
     if (first) {
-        RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * (kStatCount + 1), ctx->stream));
+        RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * (kStatCount + 2), ctx->stream));
         RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
     } else {
         RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));

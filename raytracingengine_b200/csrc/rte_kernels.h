@@ -46,6 +46,9 @@ struct RenderParams {
     int32_t cta_cull;        // streamed views: the CTA-level cull scratch follows the per-warp scratch (rte_views.cuh)
     int32_t pass_mode;       // fast kernel: 0 = auto, 1 = RTE_FLAG_SINGLE_PASS, 2 = RTE_FLAG_TWO_PASS (primary-ray launch + shading launch)
     double2* hits;           // two-pass fast path: {t, (kind << 30 | index) as the low word of the second double} per band pixel
+    int32_t exact_fp64;      // RTE_FLAG_EXACT_FP64: never take the FP32 production path (rte_render32.cu)
+    unsigned int* fix_list;  // FP32 path: band-local indices of the pixels with an inconclusive decision (capacity: band pixels) ...
+    unsigned int* fix_count; // ... and their number (zeroed before the launch); the fix-up launch renders them exactly
     unsigned int* tile_counter;        // zeroed before launch
     unsigned long long* stats;         // kStatCount counters, zeroed before launch
 };
@@ -54,6 +57,10 @@ struct RenderParams {
 size_t scene_smem_bytes(const DevScene& sc);
 // largest dynamic shared memory size the device allows per block (opt-in)
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream);
+// FP32 production path (rte_render32.cu) and the exact fix-up of its flagged pixels (rte_render.cu)
+bool fp32_path_eligible(const RenderParams& p);
+cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream);
+cudaError_t launch_fixup(const RenderParams& p, int sm_count, cudaStream_t stream);
 // would launch_render split this call into a primary-ray launch and a shading launch (it then needs p.hits)?
 bool two_pass_wanted(const RenderParams& p);
 // (re)builds sc.views for this camera / bias (rte_views.cuh); a no-op for scenes without spheres

@@ -13,41 +13,13 @@
 #include <vector>
 
 #include "rte_kernels.h"
+#include "rte_stage.cuh"
 #include "rte_tonemap.cuh"
 #include "rte_trace.cuh"
 #include "rte_views.cuh"
 
 namespace rte {
 
-// ------------------------------------------------------------------------------ TMA / mbarrier
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
-    uint32_t ok = 0;
-    while (!ok) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok)
-            : "r"(smem_u32(bar)), "r"(phase)
-            : "memory");
-    }
-}
-
-constexpr uint32_t kTmaChunk = 32768;
 constexpr int kMaxTreeDepth = RTE_MAX_DEPTH;  // rte.h: largest opts.max_depth (frames of the per-pixel TraceRay stack)
 // Pixels per thread of the view-mode render kernel (a warp's tile is 8 x 4K pixels).  Measured on B200: with resident views one
 // pixel per thread is fastest (fewer live registers, tighter ray cones for the tile cull: C2 4.78 -> 4.60 ms, C4 1.40 -> 0.95 ms);
@@ -120,40 +92,6 @@ SmemPlan plan_smem(const DevScene& sc, size_t budget) {
 
 static SmemPlan generic_plan(const DevScene& sc);
 size_t scene_smem_bytes(const DevScene& sc) { return (size_t)sc.ns_pad * 16 + (size_t)sc.nt_pad * 48; }
-
-__device__ __forceinline__ void tma_chunks(unsigned char* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    for (uint32_t off = 0; off < bytes; off += kTmaChunk)
-        tma_bulk_g2s(dst + off, reinterpret_cast<const unsigned char*>(src) + off, min(kTmaChunk, bytes - off), bar);
-}
-
-// Stage the filter arrays into dynamic shared memory with TMA bulk copies.  Called by every thread of the CTA.
-struct StagedScene {
-    const ulonglong2 *views, *tviews;   // hot views (shared memory)
-    const float *cold, *tcold;          // cold views: global memory (measured: staging them too does not pay, not even for tiny scenes)
-    const float4 *sph, *tri;            // generic filter arrays: shared or global
-};
-__device__ __forceinline__ void stage_scene(const DevScene& sc, const SmemPlan& pl, unsigned char* dyn, uint64_t* bar, StagedScene& S) {
-    unsigned char* p_tv = dyn + pl.view_bytes;
-    unsigned char* p_sph = p_tv + pl.tview_bytes;
-    unsigned char* p_tri = p_sph + pl.sph_bytes;
-    S.views = reinterpret_cast<const ulonglong2*>(dyn);
-    S.tviews = reinterpret_cast<const ulonglong2*>(p_tv);
-    S.sph = pl.stage_sph ? reinterpret_cast<const float4*>(p_sph) : sc.sph32;
-    S.tri = pl.stage_tri ? reinterpret_cast<const float4*>(p_tri) : sc.tri32;
-    S.cold = sc.views_cold;
-    S.tcold = sc.tri_views_cold;
-    if (threadIdx.x == 0) mbar_init(bar, 1);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const uint32_t vb = pl.stream_views ? 0u : pl.view_bytes;  // streamed views are fetched by ViewStream
-        mbar_expect_tx(bar, vb + pl.tview_bytes + pl.sph_bytes + pl.tri_bytes);
-        tma_chunks(dyn, sc.views, vb, bar);
-        tma_chunks(p_tv, sc.tri_views, pl.tview_bytes, bar);
-        tma_chunks(p_sph, sc.sph32, pl.sph_bytes, bar);
-        tma_chunks(p_tri, sc.tri32, pl.tri_bytes, bar);
-    }
-    mbar_wait(bar, 0);
-}
 
 // Scene::backgroundColor, RE/Scene.h:30-33
 __device__ __forceinline__ d3 background(d3 dir) {
@@ -530,6 +468,63 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
     }
     __syncwarp();
     if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
+}
+
+// ------------------------------------------------------------------------------ fix-up launch of the FP32 path
+// The FP32 production kernel (rte_render32.cu) shades a pixel only when every decision of it is certain within FP32 error
+// bounds; the others (~1e-3 of a frame: grazing rays, N.L ~ 0, contact shadows within `bias`) arrive here as a list of
+// band-local pixel indices and are rendered by the exact FP64 code above (generic filters: the pixels are incoherent, so
+// views and tile culls would not pay), operator included (tm64: the reference's own bytes).  One pixel per lane.
+__global__ void __launch_bounds__(kRenderThreads, 2) fixup_kernel(const __grid_constant__ RenderParams P) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ DevScene s_sc;
+    __shared__ __align__(8) uint64_t s_bar;
+    if (threadIdx.x == 0) s_sc = P.sc;
+    StagedScene S;
+    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, S);  // P.plan = generic arrays only
+    const DevScene& sc = s_sc;
+    const unsigned int n = *P.fix_count;
+    const int lane = threadIdx.x & 31;
+    const int W = P.cam.width, sr = P.stripe_rows, sp = P.stripe_period, aa = P.cam.aa;
+    PixelCounters tot = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t n_prim = 0;
+    for (unsigned int base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; base < n; base += gridDim.x * blockDim.x) {
+        const unsigned int i = base + (unsigned)lane;
+        const bool inb1 = i < n;
+        const int64_t pix = inb1 ? (int64_t)P.fix_list[i] : 0;
+        const int band_y = (int)(pix / W);
+        const int px[1] = {(int)(pix - (int64_t)band_y * W)};
+        const int py[1] = {P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y)};
+        const bool inb[1] = {inb1};
+        const int64_t out_idx[1] = {pix};
+        PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
+        d3 c[1], sum = mk(0.0, 0.0, 0.0);
+#pragma unroll 1
+        for (int s = 0; s < aa; ++s) {  // GeneratePixelAt, RE/Scene.h:283-304
+            trace_pixels<1, false>(P, sc, S.views, S.tviews, S.cold, S.tcold, S.sph, S.tri, px, py, inb, out_idx, s, cnt, c);
+            if (aa > 1) sum = sum + c[0];
+        }
+        if (aa > 1) c[0] = sum / (double)aa;
+        if (inb1) {
+            const d3 v = c[0];
+            if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[pix] = make_float4((float)v.x, (float)v.y, (float)v.z, 0.f);
+            if (P.out.rgb8) {
+                const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));
+                uint8_t* d = P.out.rgb8 + 3 * pix;
+                d[0] = u.x; d[1] = u.y; d[2] = u.z;
+            }
+            n_prim += (uint32_t)aa;
+        }
+        tot.shadow += cnt.shadow; tot.sph += cnt.sph; tot.pl += cnt.pl; tot.tri += cnt.tri; tot.marches += cnt.marches; tot.confirms += cnt.confirms;
+        tot.sph_exec += cnt.sph_exec;
+    }
+    // (fp64_confirms of an FP32-path call = the number of pixel samples re-rendered here)
+    const uint32_t v[kStatCount] = {n_prim, tot.shadow, 0u, tot.sph, tot.pl, tot.tri, tot.marches, n_prim, tot.sph_exec};
+#pragma unroll
+    for (int k = 0; k < kStatCount; ++k) {
+        const uint32_t t = __reduce_add_sync(kFullMask, v[k]);
+        if (lane == 0 && t) atomicAdd(&P.stats[k], (unsigned long long)t);
+    }
 }
 
 // ------------------------------------------------------------------------------ view providers
@@ -1223,6 +1218,17 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
     }
     const void* fn = p.sc.reflective ? (const void*)render_kernel<1, true> : (const void*)render_kernel<1, false>;
     return launch_render_fn(fn, fn, kRenderThreads, 2, 1, p, sm_count, stream);
+}
+
+cudaError_t launch_fixup(const RenderParams& p0, int sm_count, cudaStream_t stream) {
+    RenderParams p = p0;
+    p.plan = generic_plan(p.sc);
+    const void* fn = (const void*)fixup_kernel;
+    const cudaError_t e = ensure_smem(fn, p.plan.total);
+    if (e != cudaSuccess) return e;
+    void* args[] = {(void*)&p};
+    // the list's length lives on the device: a fixed grid walks it (an empty list costs an empty launch)
+    return cudaLaunchKernel(fn, dim3((unsigned)(2 * sm_count)), dim3(kRenderThreads), args, p.plan.total, stream);
 }
 
 // ------------------------------------------------------------------------------ ray queries

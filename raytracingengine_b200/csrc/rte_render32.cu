@@ -1,0 +1,557 @@
+// rte_render32.cu — the FP32 production path of the render call (sm_100a): diffuse sphere / plane scenes whose views are
+// resident in shared memory, outputs HDR float4 / RGB8 (+ the integer AOVs prim_id, light_mask).
+//
+// Replaces Scene::RenderImage / TraceRay / directLightning + tonemap()/toColor for those scenes (RE/Scene.h:311-328, 131-198,
+// 79-129; RE/RaytracingEngine.cpp:113-121,165-174; "RE/" = /root/reference/RaytracingEngine/) to the bar BASELINE.json states:
+// nearest-hit index and shadow visibility bit-exact, depth / normals 1e-5, RGB8 +-1 LSB.  (The FP64 path of rte_render.cu,
+// bit-identical to the reference, stays behind RTE_FLAG_EXACT_FP64 and every FP64 output.)
+//
+//  * Values (hit point, normal, N.L, 1/d^2, the light sum, the operator) are FP32; the few places where FP32 would cancel
+//    (hit point, C - origin of a candidate) take a handful of FP64 adds / FMAs — never an FP64 division or square root
+//    (those are ~25 / ~40 SASS instructions each): reciprocal square roots come from MUFU + Newton steps.
+//  * DECISIONS (which primitive is nearest, is a shadow ray cast, is it occluded) are taken from FP32 INTERVALS with explicit
+//    error bounds.  A pixel with any inconclusive decision is not shaded here: its index goes to a device list and the
+//    fix-up launch (rte_render.cu: fixup_kernel) renders it with the exact FP64 code.  So every decision that reaches an
+//    output is either certain or exact, and flagged pixels (~1e-3 of a frame) are the reference's own bits.
+//  * The operator + toColor run in the kernel (tm32, rte_tonemap.cuh) and a tile row of 8 pixels leaves as six aligned
+//    32-bit words: no FP64 HDR scratch, no second pass.
+#include "rte_kernels.h"
+#include "rte_stage.cuh"
+#include "rte_tonemap.cuh"
+#include "rte_views.cuh"
+
+namespace rte {
+
+constexpr int kR32Threads = 1024;  // one CTA per SM (the views of C2 are 80 KB)
+constexpr int kR32Planes = 8, kR32Lights = 16;  // scenes with more take the exact path
+
+// ------------------------------------------------------------------------------ cheap FP64 (no DDIV / DSQRT sequences)
+// 1/sqrt(x) to ~1e-16 relative for normal positive x: MUFU.RSQ seed (1e-7) + two Newton steps in FP64.
+__device__ __forceinline__ double rsqrt64_fast(double x) {
+    double y = (double)rsqrtf((float)x);
+    const double hx = 0.5 * x;
+    y = y * fma(-hx * y, y, 1.5);
+    y = y * fma(-hx * y, y, 1.5);
+    return y;
+}
+// 1/x to ~1e-16 relative: MUFU.RCP seed + two Newton steps.
+__device__ __forceinline__ double rcp64_fast(double x) {
+    double y = (double)__frcp_rn((float)x);
+    y = y * fma(-x, y, 2.0);
+    y = y * fma(-x, y, 2.0);
+    return y;
+}
+__device__ __forceinline__ float sqrt_approx(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+// ------------------------------------------------------------------------------ scene constants in shared memory
+struct Plane32 {
+    float nx, ny, nz, d;  // n (FP64 normalised, rounded), d = n.p0 (FP64 dot, rounded)
+    int mat;
+};
+struct Scene32 {
+    Plane32 pl[kR32Planes];
+    double li_pos[kR32Lights][3];
+    float li_E[kR32Lights][3];
+    double cam[3];
+    int np, nl;
+};
+
+// ------------------------------------------------------------------------------ one sphere candidate against one ray
+// The ray is {origin o (FP64), unit direction L (FP32, |L| = 1 +- 4 eps, within 4 eps of the reference's direction)}.
+//   g = fl32(C - o)  (FP64 subtraction: relative error eps),  b = g.L,  l = g - b L,  l2 = |l|^2  — no cancellation between
+//   quantities of the size of the scene; every absolute error below is bounded by  dl = 20 eps (|b| + |l|) + 1e-7
+//   (direction error 4 eps |b| + roundings ~5 eps |g| + parameter scale 4 eps |b|, |g| <= |b| + |l|).
+// Returns the class of the candidate and, for a certain hit, bounds of the near root t0 and of the far root t1.
+enum { kCandMiss = 0, kCandHit = 1, kCandUnsure = 2 };
+struct Cand32 {
+    int cls;
+    float t0_lo, t0_hi, t1_lo, t1_hi;  // kCandHit: t0 in [t0_lo, t0_hi], t1 in [t1_lo, t1_hi]; kCandUnsure: the chord, if any, lies in [t0_lo, t1_hi]
+};
+__device__ __forceinline__ Cand32 classify_sphere(const double4 s, double ox, double oy, double oz, float Lx, float Ly, float Lz, float r_pad) {
+    const float gx = (float)(s.x - ox), gy = (float)(s.y - oy), gz = (float)(s.z - oz);
+    const float b = __fmaf_rn(gz, Lz, __fmaf_rn(gy, Ly, gx * Lx));
+    const float lx = __fmaf_rn(-b, Lx, gx), ly = __fmaf_rn(-b, Ly, gy), lz = __fmaf_rn(-b, Lz, gz);
+    const float l2 = __fmaf_rn(lz, lz, __fmaf_rn(ly, ly, lx * lx));
+    const float l = sqrt_approx(l2) * 1.000001f;
+    const float dl = __fmaf_rn(20.0f * kEps32, fabsf(b) + l, 1e-7f);
+    const float r = (float)s.w;  // |r| is what the reference squares
+    const float ra = fabsf(r);
+    const float r_hi = ra * 1.0000002f + r_pad, r_lo = ra * 0.9999998f - r_pad;
+    Cand32 c;
+    const float lm = fmaxf(l * 0.999998f - dl, 0.0f), lp = l + dl;   // lower / upper bound of the true distance line - centre
+    if (lm > r_hi) { c.cls = kCandMiss; c.t0_lo = c.t0_hi = c.t1_lo = c.t1_hi = 0.0f; return c; }
+    const float hc_hi = sqrt_approx(fmaxf(__fmaf_rn(r_hi, r_hi, -lm * lm), 0.0f)) * 1.000002f + dl;
+    const float h_lo2 = __fmaf_rn(r_lo, r_lo, -lp * lp);
+    c.t0_lo = b - hc_hi - dl;
+    c.t1_hi = b + hc_hi + dl;
+    if (!(r_lo > 0.0f) || !(h_lo2 > 0.0f)) { c.cls = kCandUnsure; c.t0_hi = c.t1_hi; c.t1_lo = c.t0_lo; return c; }  // grazing: hit or miss
+    const float hc_lo = fmaxf(sqrt_approx(h_lo2) * 0.999998f - dl, 0.0f);
+    c.cls = kCandHit;
+    c.t0_hi = b - hc_lo + dl;
+    c.t1_lo = b + hc_lo - dl;
+    return c;
+}
+
+// Sphere::Intersect's reported distance (RE/Shape.h:89-97: t0 unless t0 < 1e-6, then t1 unless t1 < 1e-6) as an interval.
+// Returns kCandMiss / kCandHit ([lo, hi]) / kCandUnsure (a hit, if any, reports a distance >= lo).
+__device__ __forceinline__ int reported_t(const Cand32& c, float& lo, float& hi) {
+    const float kRefEps = 1e-6f;
+    lo = 0.0f; hi = 0.0f;
+    if (c.cls == kCandMiss || c.t1_hi < kRefEps) return kCandMiss;         // no root can reach 1e-6
+    if (c.cls == kCandHit) {
+        if (c.t0_lo > kRefEps) { lo = c.t0_lo; hi = c.t0_hi; return kCandHit; }
+        if (c.t0_hi < kRefEps && c.t1_lo > kRefEps) { lo = c.t1_lo; hi = c.t1_hi; return kCandHit; }  // origin inside: far root
+    }
+    lo = fmaxf(c.t0_lo, 0.0f); hi = c.t1_hi;
+    return kCandUnsure;
+}
+
+// ------------------------------------------------------------------------------ nearest hit from intervals
+struct Near32 {
+    int kind, idx;        // RTE_HIT_*; best certain hit so far
+    float lo, hi;         // its distance interval
+    float amb_lo;         // the smallest distance anything ambiguous (overlapping interval, grazing sphere) could report
+};
+__device__ __forceinline__ void near_hit(Near32& n, int kind, int idx, float lo, float hi) {
+    if (n.kind == RTE_HIT_NONE || hi < n.lo) { n.kind = kind; n.idx = idx; n.lo = lo; n.hi = hi; return; }  // certainly closer
+    if (lo > n.hi) return;                                                                                  // certainly farther
+    n.amb_lo = fminf(n.amb_lo, fminf(lo, n.lo));  // overlap: canonical order / strict '<' (RE/Scene.h:223) would have to decide
+    if (lo < n.lo) { n.kind = kind; n.idx = idx; n.lo = lo; n.hi = hi; }
+}
+__device__ __forceinline__ void near_unsure(Near32& n, float lo) {
+    if (n.kind != RTE_HIT_NONE && lo > n.hi) return;  // whatever it is, it is farther than the best (which only gets closer)
+    n.amb_lo = fminf(n.amb_lo, lo);
+}
+__device__ __forceinline__ bool near_ambiguous(const Near32& n) { return n.kind == RTE_HIT_NONE ? n.amb_lo < INFINITY : n.amb_lo <= n.hi; }
+
+// ------------------------------------------------------------------------------ one plane against one ray
+// Plane::Intersect, RE/Shape.h:149-159: denom = n.d; |denom| > 1e-6; t = ((p0 - o).n) / denom; hit iff t >= 0.
+// FP32: den = n.L (error <= 6 eps), num = d - n.o (error <= en = 4 eps (|d| + |o|_1) + 1e-9).
+// Returns kCandMiss / kCandHit with t in [lo, hi] / kCandUnsure.
+__device__ __forceinline__ int plane_interval(const Plane32& p, float ox, float oy, float oz, float o1, float Lx, float Ly, float Lz, float& lo, float& hi,
+                                              float& den_out) {
+    const float den = __fmaf_rn(p.nz, Lz, __fmaf_rn(p.ny, Ly, p.nx * Lx));
+    const float num = p.d - __fmaf_rn(p.nz, oz, __fmaf_rn(p.ny, oy, p.nx * ox));
+    const float ed = 8.0f * kEps32, en = __fmaf_rn(4.0f * kEps32, fabsf(p.d) + o1, 1e-9f);
+    const float ad = fabsf(den), an = fabsf(num);
+    den_out = den;
+    lo = 0.0f; hi = 0.0f;
+    if (ad < 1e-6f - ed) return kCandMiss;          // parallel: rejected by the reference
+    if (ad < 1e-6f + ed) return kCandUnsure;
+    if (an <= en) return kCandUnsure;               // origin on the plane: t = 0 is a hit upstream, its sign is not decidable here
+    if ((num < 0.0f) != (den < 0.0f)) return kCandMiss;  // t < 0
+    const float t = an * __frcp_rn(ad);
+    const float rel = en * __frcp_rn(an) + ed * __frcp_rn(ad) + 4.0f * kEps32;
+    lo = t * (1.0f - rel); hi = t * (1.0f + rel);
+    return rel < 0.25f ? kCandHit : kCandUnsure;
+}
+
+// ------------------------------------------------------------------------------ the scan of one view by one ray per lane
+// Nomination by the view's cone test (rte_views.cuh: view_block_masks, 3 packed FMAs per sphere pair), candidates queued
+// per lane and resolved lane-parallel per window, in ascending index per ray.  `on_cand(idx)` may clear `active`.
+template <class Fn>
+__device__ __forceinline__ void scan32(const ulonglong2* __restrict__ view, const uint16_t* __restrict__ map, int ns, int ns_pad, const ViewRay& r,
+                                       bool& active, const double4* __restrict__ sph64, uint32_t& executed, Fn&& on_cand) {
+    uint16_t q[kWindow];  // local memory; only written entries are touched
+    int qn = 0, base = 0;
+    const ViewRay rr[1] = {r};
+#pragma unroll 1
+    while (base < ns_pad) {
+        const int wbase = base, stop = min(base + kWindow, ns_pad);
+#pragma unroll 1
+        do {
+            uint32_t cand[1];
+            view_block_masks<1>(view + base, rr, cand);
+            executed += kViewBlock;
+            uint32_t c = active ? cand[0] : 0u;
+            while (c) {  // short, divergent
+                const int i = __clz(c);
+                c &= ~(0x80000000u >> i);
+                if (base + i < ns) {
+                    q[qn++] = (uint16_t)(base - wbase + i);
+                    const int idx = map ? (int)map[base + i] : base + i;
+                    asm volatile("prefetch.global.L1 [%0];" ::"l"(sph64 + idx));
+                }
+            }
+            base += kViewBlock;
+        } while (base < stop);
+        const int nmax = __reduce_max_sync(kFullMask, qn);
+#pragma unroll 1
+        for (int e = 0; e < nmax; ++e) {
+            if (e >= qn || !active) continue;
+            const int pos = wbase + (int)q[e];
+            on_cand(map ? (int)map[pos] : pos);
+        }
+        qn = 0;
+        if (__all_sync(kFullMask, !active)) break;
+    }
+}
+
+// ------------------------------------------------------------------------------ operator + toColor for one pixel
+__device__ __forceinline__ uint32_t tonemap_rgb24(int op, float x, float y, float z, const tm32::Consts& K) {
+    const tm32::Shared s = tm32::prepare<0u>(tm32::mk3(x, y, z), 1u << op);
+    tm32::f3 c;
+    switch (op) {
+        case RTE_TM_SIMPLE: c = tm32::apply_op<RTE_TM_SIMPLE>(s, K); break;
+        case RTE_TM_REINHARD_SIMPLE: c = tm32::apply_op<RTE_TM_REINHARD_SIMPLE>(s, K); break;
+        case RTE_TM_REINHARD_EXTENDED: c = tm32::apply_op<RTE_TM_REINHARD_EXTENDED>(s, K); break;
+        case RTE_TM_REINHARD_EXTENDED_LUMINANCE: c = tm32::apply_op<RTE_TM_REINHARD_EXTENDED_LUMINANCE>(s, K); break;
+        case RTE_TM_REINHARD_JODIE: c = tm32::apply_op<RTE_TM_REINHARD_JODIE>(s, K); break;
+        case RTE_TM_UNCHARTED2: c = tm32::apply_op<RTE_TM_UNCHARTED2>(s, K); break;
+        default: c = tm32::apply_op<RTE_TM_ACES>(s, K); break;
+    }
+    return (tm32::qbyte(c.x) & 255u) | ((tm32::qbyte(c.y) & 255u) << 8) | ((tm32::qbyte(c.z) & 255u) << 16);
+}
+
+// One sample of one pixel per lane, all 32 lanes of the warp in lock step.  Returns false when some decision of the pixel
+// was inconclusive (the pixel then belongs to the fix-up launch and nothing else of the result is meaningful).
+struct Px32 {
+    float r, g, b;       // linear HDR of the sample
+    uint32_t prim, lmask;
+    uint32_t c_shadow, c_sph, c_pl;  // statistics of this sample (SURVEY §8(d) algorithmic counts)
+};
+__device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S, const ulonglong2* __restrict__ s_views, const CullScratch* cull, int px, int py,
+                                        bool alive, int sample, Px32& out, uint32_t& executed) {
+    const DevScene& sc = P.sc;
+    const int ns = sc.ns, ns_pad = sc.ns_pad, np = S.np, nl = S.nl;
+    const float bias = (float)P.bias;
+    bool ok = true;
+    out.r = out.g = out.b = 0.0f;
+    out.prim = kMiss; out.lmask = 0u; out.c_shadow = 0u; out.c_sph = (uint32_t)ns; out.c_pl = (uint32_t)np;
+    // ---- Camera::getRay, RE/Math.h:99-121 (the reference's FP64 operations up to the normalisation)
+    double dx, dy, dz;
+    {
+        double sx = (double)px - P.cam.half_w, sy = P.cam.half_h - (double)py;
+        if (sample > 0) {
+            const int64_t pixel = (int64_t)py * P.cam.width + px;
+            sx += jitter01(P.cam.jitter_seed, pixel, sample, 0);
+            sy += jitter01(P.cam.jitter_seed, pixel, sample, 1);
+        }
+        const double vx = sx - S.cam[0], vy = sy - S.cam[1], vz = (S.cam[2] + P.cam.focal) - S.cam[2];
+        const double len2 = vx * vx + vy * vy + vz * vz;
+        if (!(len2 > 1e-20) || !(len2 < 1e30)) ok = false;  // (normalize() returns 0 below 1e-12: leave it to the exact code)
+        const double inv = rsqrt64_fast(len2);
+        dx = vx * inv; dy = vy * inv; dz = vz * inv;
+    }
+    ViewRay r;
+    r.ux = (float)dx; r.uy = (float)dy; r.uz = (float)dz;
+    // ---- Scene::IntersectClosest, RE/Scene.h:218-257, from intervals
+    Near32 nr;
+    nr.kind = RTE_HIT_NONE; nr.idx = 0; nr.lo = 0.0f; nr.hi = 0.0f; nr.amb_lo = INFINITY;
+    if (ns > 0) {
+        const ulonglong2* view = s_views;
+        const uint16_t* map = nullptr;
+        int n = ns, n_pad = ns_pad;
+        if (cull && n_pad >= kCullMin && (n_pad & 63) == 0) {
+            int cnt = 0;
+            const ViewRay rr[1] = {r};
+            const bool act[1] = {alive};
+            executed += (uint32_t)(n_pad >> 4);
+            if (cull_view<1>(view, n_pad, rr, act, *cull, cnt)) { view = cull->mini; map = cull->map; n = cnt; n_pad = (cnt + 31) & ~31; }
+        }
+        bool active = alive;
+        scan32(view, map, n, n_pad, r, active, sc.sph64, executed, [&](int idx) {
+            const Cand32 c = classify_sphere(sc.sph64[idx], S.cam[0], S.cam[1], S.cam[2], r.ux, r.uy, r.uz, 0.0f);
+            float lo, hi;
+            const int cls = reported_t(c, lo, hi);
+            if (cls == kCandHit) near_hit(nr, RTE_HIT_SPHERE, idx, lo, hi);
+            else if (cls == kCandUnsure) near_unsure(nr, lo);
+        });
+    }
+    const float cam32x = (float)S.cam[0], cam32y = (float)S.cam[1], cam32z = (float)S.cam[2];
+    const float cam1 = fabsf(cam32x) + fabsf(cam32y) + fabsf(cam32z);
+#pragma unroll 1
+    for (int i = 0; i < np; ++i) {  // planes after the spheres: a plane wins only when it is certainly closer
+        float lo, hi, den;
+        const int cls = plane_interval(S.pl[i], cam32x, cam32y, cam32z, cam1, r.ux, r.uy, r.uz, lo, hi, den);
+        if (cls == kCandHit) near_hit(nr, RTE_HIT_PLANE, i, lo, hi);
+        else if (cls == kCandUnsure) near_unsure(nr, 0.0f);
+    }
+    if (near_ambiguous(nr)) ok = false;
+    // (no early exit: the culls and scans of the light loop are warp-synchronous, every lane walks them)
+    const bool hitv = alive && ok && nr.kind != RTE_HIT_NONE;
+    if (!alive) { out.c_sph = 0u; out.c_pl = 0u; }
+    if (alive && nr.kind == RTE_HIT_NONE) {  // Scene::backgroundColor, RE/Scene.h:30-33
+        const float t = 0.5f * (r.uy + 1.0f);
+        out.r = __fmaf_rn(0.5f, t, 1.0f - t); out.g = __fmaf_rn(0.7f, t, 1.0f - t); out.b = 1.0f;
+    }
+    // ---- the hit: distance in cheap FP64 (no DDIV / DSQRT), point, viewer-facing unit normal
+    double Px = 0.0, Py = 0.0, Pz = 0.0;
+    float Nx = 0.0f, Ny = 0.0f, Nz = 1.0f;
+    int mat = sc.nm, self = -1;
+    if (hitv && nr.kind == RTE_HIT_SPHERE) {
+        const double4 s = sc.sph64[nr.idx];
+        const double ocx = S.cam[0] - s.x, ocy = S.cam[1] - s.y, ocz = S.cam[2] - s.z;
+        const double bq = ocx * dx + ocy * dy + ocz * dz;            // oc.d, |d| = 1
+        const double cq = fma(ocx, ocx, fma(ocy, ocy, ocz * ocz)) - s.w * s.w;
+        const double disc = fma(bq, bq, -cq);
+        const bool far_root = cq < 0.0;                              // origin inside the sphere: the far root was reported
+        const double sq = disc > 0.0 ? disc * rsqrt64_fast(disc) : 0.0;
+        const double t = far_root ? -bq + sq : -bq - sq;
+        Px = fma(dx, t, S.cam[0]); Py = fma(dy, t, S.cam[1]); Pz = fma(dz, t, S.cam[2]);
+        const float ir = __frcp_rn((float)fabs(s.w));
+        float nx = (float)(Px - s.x) * ir, ny = (float)(Py - s.y) * ir, nz = (float)(Pz - s.z) * ir;  // outward
+        if (far_root) { nx = -nx; ny = -ny; nz = -nz; } else if (bias >= 1e-5f) self = nr.idx;       // frontFace = n.d < 0
+        Nx = nx; Ny = ny; Nz = nz;
+        mat = sc.sph_mat[nr.idx];
+        out.prim = ((uint32_t)RTE_HIT_SPHERE << 30) | (uint32_t)nr.idx;
+    } else if (hitv) {
+        const DevPlane& pl = sc.planes[nr.idx];
+        const double num = (pl.p0[0] - S.cam[0]) * pl.n[0] + (pl.p0[1] - S.cam[1]) * pl.n[1] + (pl.p0[2] - S.cam[2]) * pl.n[2];
+        const double den = pl.n[0] * dx + pl.n[1] * dy + pl.n[2] * dz;
+        const double t = num * rcp64_fast(den);
+        Px = fma(dx, t, S.cam[0]); Py = fma(dy, t, S.cam[1]); Pz = fma(dz, t, S.cam[2]);
+        const float sg = den < 0.0 ? 1.0f : -1.0f;  // frontFace = n.d < 0 (|n.d| > 1e-6 is certain here)
+        Nx = sg * S.pl[nr.idx].nx; Ny = sg * S.pl[nr.idx].ny; Nz = sg * S.pl[nr.idx].nz;
+        mat = S.pl[nr.idx].mat;
+        out.prim = ((uint32_t)RTE_HIT_PLANE << 30) | (uint32_t)nr.idx;
+    }
+    mat = (mat >= 0 && mat < sc.nm) ? mat : sc.nm;
+    // shadow origin so = P + N * bias (RE/Scene.h:104)
+    const double sox = fma((double)Nx, (double)bias, Px), soy = fma((double)Ny, (double)bias, Py), soz = fma((double)Nz, (double)bias, Pz);
+    const float so32x = (float)sox, so32y = (float)soy, so32z = (float)soz;
+    const float so1 = fabsf(so32x) + fabsf(so32y) + fabsf(so32z);
+    float ar = 0.0f, ag = 0.0f, ab = 0.0f;
+    // ---- Scene::directLightning, RE/Scene.h:79-129 (diffuse term)
+#pragma unroll 1
+    for (int j = 0; j < nl; ++j) {
+        const float vx = (float)(S.li_pos[j][0] - Px), vy = (float)(S.li_pos[j][1] - Py), vz = (float)(S.li_pos[j][2] - Pz);
+        const float d2 = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, vx * vx));
+        float inv = rsqrtf(d2);
+        inv = inv * __fmaf_rn(-0.5f * d2 * inv, inv, 1.5f);  // one Newton step: <= 1.5 ulp
+        const float dist = d2 * inv;
+        const float Lx = vx * inv, Ly = vy * inv, Lz = vz * inv;
+        const float ndl = __fmaf_rn(Nz, Lz, __fmaf_rn(Ny, Ly, Nx * Lx));
+        bool cast = hitv && ok && d2 > 0.0f;
+        if (cast) {
+            // guards of RE/Scene.h:89-101: ndl > 0, dist > bias — certain, or the pixel is flagged
+            if (fabsf(ndl) < 32.0f * kEps32 || fabsf(dist - bias) < 1e-5f * bias + 1e-30f) { ok = false; cast = false; }
+            else cast = ndl > 0.0f && dist > bias;
+        }
+        if (!__any_sync(kFullMask, cast)) continue;
+        const float maxDist = dist - bias;
+        const float dt = 24.0f * kEps32 * (dist + so1) + 1e-7f;  // slack of the range ends (maxDist, bias) against the candidate bounds
+        const float tmax_lo = maxDist - dt, tmax_hi = maxDist + dt, bias_hi = bias + dt, tsafe_hi = 130.0f * bias + dt;
+        bool occl = false, unsure = false;
+        uint32_t first = (uint32_t)ns;
+        if (ns > 0) {
+            ViewRay rv;
+            rv.ux = -Lx; rv.uy = -Ly; rv.uz = -Lz;  // the light's view is scanned from the light towards the shaded point
+            const ulonglong2* view = s_views + (size_t)(1 + j) * ns_pad;
+            const uint16_t* map = nullptr;
+            int n = ns, n_pad = ns_pad;
+            if (cull && n_pad >= kCullMin && (n_pad & 63) == 0) {
+                int cnt = 0;
+                const ViewRay rr[1] = {rv};
+                const bool act[1] = {cast};
+                executed += (uint32_t)(n_pad >> 4);
+                if (cull_view<1>(view, n_pad, rr, act, *cull, cnt)) { view = cull->mini; map = cull->map; n = cnt; n_pad = (cnt + 31) & ~31; }
+            }
+            bool active = cast;
+            scan32(view, map, n, n_pad, rv, active, sc.sph64, executed, [&](int idx) {
+                if (idx == self) return;  // so lies outside the sphere the point is on, the ray leaves it: both roots < 0
+                const Cand32 c = classify_sphere(sc.sph64[idx], sox, soy, soz, Lx, Ly, Lz, 0.0f);
+                float lo, hi;
+                const int cls = reported_t(c, lo, hi);
+                if (cls == kCandMiss) return;
+                if (lo > tmax_hi) return;  // behind the light: not an occluder, not `near`
+                if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) {  // certainly bias < t < maxDist
+                    if (!occl) first = (uint32_t)idx;
+                    occl = true;
+                    if (lo > tsafe_hi) active = false;  // beyond the reach of the march's bias steps: decided
+                    return;
+                }
+                unsure = true; active = false;
+            });
+        }
+        if (unsure) ok = false;
+        uint32_t firstp = (uint32_t)np;
+        if (cast && !occl && !unsure) {  // planes, any-hit in canonical order
+#pragma unroll 1
+            for (int i = 0; i < np; ++i) {
+                float lo, hi, den;
+                const int cls = plane_interval(S.pl[i], so32x, so32y, so32z, so1, Lx, Ly, Lz, lo, hi, den);
+                if (cls == kCandMiss) continue;
+                if (cls == kCandHit && lo > tmax_hi) continue;
+                if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; firstp = (uint32_t)i; break; }
+                ok = false; break;
+            }
+        }
+        if (cast) {
+            out.c_shadow += 1u;
+            out.c_sph += first < (uint32_t)ns ? first + 1u : (uint32_t)ns;
+            out.c_pl += first < (uint32_t)ns ? 0u : (firstp < (uint32_t)np ? firstp + 1u : (uint32_t)np);
+            if (j < 16) out.lmask |= 1u << (16 + j);
+            if (!occl) {
+                if (j < 16) out.lmask |= 1u << j;
+                const float w = inv * inv * ndl;  // (1 / d^2) * N.L
+                ar = __fmaf_rn(S.li_E[j][0], w, ar); ag = __fmaf_rn(S.li_E[j][1], w, ag); ab = __fmaf_rn(S.li_E[j][2], w, ab);
+            }
+        }
+    }
+    if (hitv) {
+        const rte_material& M = sc.materials[mat];
+        out.r = (float)M.color[0] * ar; out.g = (float)M.color[1] * ag; out.b = (float)M.color[2] * ab;
+    }
+    return ok || !alive;
+}
+
+// ------------------------------------------------------------------------------ the kernel
+// Persistent CTAs, one 8 x 4 pixel tile per warp at a time from a global counter (like the exact kernels), one pixel per lane.
+constexpr int kTile32W = 8, kTile32H = 4;
+
+template <bool kAov>
+__global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_constant__ RenderParams P) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __shared__ Scene32 s32;
+    __shared__ __align__(8) uint64_t s_bar;
+    __shared__ unsigned long long s_stats[kR32Threads / 32][kStatCount];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        const DevScene& g = P.sc;
+        s32.np = g.np; s32.nl = g.nl;
+        for (int i = 0; i < g.np; ++i) {
+            const DevPlane p = g.planes[i];
+            s32.pl[i].nx = (float)p.n[0]; s32.pl[i].ny = (float)p.n[1]; s32.pl[i].nz = (float)p.n[2];
+            s32.pl[i].d = (float)(p.n[0] * p.p0[0] + p.n[1] * p.p0[1] + p.n[2] * p.p0[2]);
+            s32.pl[i].mat = p.mat;
+        }
+        for (int j = 0; j < g.nl; ++j) {
+            const DevLight l = g.lights[j];
+            for (int c = 0; c < 3; ++c) { s32.li_pos[j][c] = l.pos[c]; s32.li_E[j][c] = (float)l.E[c]; }
+        }
+        for (int c = 0; c < 3; ++c) s32.cam[c] = P.cam.pos[c];
+    }
+    if (lane < kStatCount) s_stats[warp][lane] = 0ull;
+    StagedScene S;
+    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, S);  // (its __syncthreads also publishes s32)
+    CullScratch cull_scratch{nullptr, nullptr};
+    if (P.cull) {
+        unsigned char* base = dyn_smem + ((P.plan.total + 15) & ~(size_t)15) + (size_t)warp * kCullBytesPerWarp;
+        cull_scratch.mini = reinterpret_cast<ulonglong2*>(base);
+        cull_scratch.map = reinterpret_cast<uint16_t*>(base + kCullCap * 16);
+    }
+    const CullScratch* cull = P.cull ? &cull_scratch : nullptr;
+    tm32::Consts K;
+    {
+        const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f, x = 11.2f;  // 1 / uncharted2_tonemap_partial(11.2)
+        K.white_scale = 1.0f / (((x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F)) - E / F);
+        K.inv_wsq = (float)(1.0 / (P.max_white * P.max_white));
+        K.jodie_a = (float)P.jodie_a;
+    }
+    const int W = P.cam.width, rows = P.n_rows;
+    const int sr = P.stripe_rows, sp = P.stripe_period;
+    const int tiles_x = (W + kTile32W - 1) / kTile32W, tiles_y = (rows + kTile32H - 1) / kTile32H;
+    const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
+    const int lx = lane & (kTile32W - 1), ly = lane >> 3;
+    const int aa = P.cam.aa;
+    const bool words = (W & 3) == 0;  // rows of RGB8 are word aligned: a tile row of 8 pixels is six aligned words
+
+    unsigned int tile = 0;
+    if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
+    tile = __shfl_sync(kFullMask, tile, 0);
+    while (tile < n_tiles) {
+        unsigned int next = 0;
+        if (lane == 0) next = atomicAdd(P.tile_counter, 1u);  // the next tile id arrives behind the work
+        const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
+        const int band_y = ty * kTile32H + ly, px = tx * kTile32W + lx;
+        const int py = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
+        const bool inb = px < W && band_y < rows;
+        const int64_t pix = (int64_t)band_y * W + px;
+        // GeneratePixelAt, RE/Scene.h:283-304: mean of the samples
+        float cr = 0.0f, cg = 0.0f, cb = 0.0f;
+        uint32_t prim = kMiss, lmask = 0u, n_shadow = 0u, n_sph = 0u, n_pl = 0u, executed = 0u;
+        bool ok = true;
+#pragma unroll 1
+        for (int s = 0; s < aa; ++s) {
+            Px32 o;
+            ok = trace32(P, s32, S.views, cull, px, py, inb, s, o, executed) && ok;
+            cr += o.r; cg += o.g; cb += o.b;
+            n_shadow += o.c_shadow; n_sph += o.c_sph; n_pl += o.c_pl;
+            if (s == 0) { prim = o.prim; lmask = o.lmask; }
+        }
+        if (aa > 1) { const float ia = 1.0f / (float)aa; cr *= ia; cg *= ia; cb *= ia; }
+        const bool mine = inb && ok;    // this kernel owns the pixel; flagged pixels go to the fix-up launch
+        const bool flagged = inb && !ok;
+        // ---- outputs
+        if (mine) {
+            if (P.out.hdr) __stcs(reinterpret_cast<float4*>(P.out.hdr) + pix, make_float4(cr, cg, cb, 0.f));
+            if (kAov) {
+                if (P.out.prim_id) P.out.prim_id[pix] = prim;
+                if (P.out.light_mask) P.out.light_mask[pix] = lmask;
+            }
+        }
+        if (P.out.rgb8) {
+            const uint32_t rgb = tonemap_rgb24(P.tonemap_op, cr, cg, cb, K);
+            const bool row_full = (tx + 1) * kTile32W <= W && band_y < rows;  // (uniform over the 8 lanes of a tile row)
+            if (words) {
+                // bytes 4 lx .. 4 lx + 3 of the row's 24: pixel q = 4 lx / 3 from its byte o = 4 lx % 3 on, then pixel q + 1
+                const int q = lx < 6 ? (4 * lx) / 3 : 6, o = lx < 6 ? (4 * lx) % 3 : 0;
+                const uint32_t a = __shfl_sync(kFullMask, rgb, (lane & ~7) + q), b = __shfl_sync(kFullMask, rgb, (lane & ~7) + q + 1);
+                const uint32_t word = o == 0 ? (a | (b << 24)) : o == 1 ? ((a >> 8) | (b << 16)) : ((a >> 16) | (b << 8));
+                if (row_full) {
+                    if (lx < 6) __stcs(reinterpret_cast<uint32_t*>(P.out.rgb8 + 3 * ((int64_t)band_y * W + tx * kTile32W)) + lx, word);
+                } else if (mine) {
+                    uint8_t* d = P.out.rgb8 + 3 * pix;
+                    d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+                }
+            } else if (mine) {
+                uint8_t* d = P.out.rgb8 + 3 * pix;
+                d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+            }
+        }
+        // ---- pixels with an inconclusive decision: appended to the fix-up list (one atomic per tile that has any)
+        const uint32_t fm = __ballot_sync(kFullMask, flagged);
+        if (fm) {
+            unsigned int at = 0;
+            if (lane == 0) at = atomicAdd(P.fix_count, (unsigned int)__popc(fm));
+            at = __shfl_sync(kFullMask, at, 0);
+            if (flagged) P.fix_list[at + __popc(fm & ((1u << lane) - 1u))] = (unsigned int)pix;
+        }
+        // ---- statistics of the pixels this kernel owns (the fix-up launch counts its own)
+        const uint32_t v[kStatCount] = {mine ? (uint32_t)aa : 0u, mine ? n_shadow : 0u, 0u, mine ? n_sph : 0u, mine ? n_pl : 0u, 0u, 0u, 0u, executed};
+        uint32_t sum_mine = 0;
+#pragma unroll
+        for (int k = 0; k < kStatCount; ++k) {
+            const uint32_t t = __reduce_add_sync(kFullMask, v[k]);
+            if (lane == k) sum_mine = t;
+        }
+        if (lane < kStatCount) s_stats[warp][lane] += sum_mine;
+        tile = __shfl_sync(kFullMask, next, 0);
+    }
+    __syncwarp();
+    if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
+}
+
+// Can this render call take the FP32 path?  (rte_render.cu decides with it; everything else takes the exact kernels.)
+bool fp32_path_eligible(const RenderParams& p) {
+    const rte_frame& f = p.out;
+    return p.plan.use_views && !p.plan.stream_views && !p.plan.use_tri_views && !p.sc.reflective && !p.sc.transparent && p.sc.nt == 0 && p.sc.ns > 0 &&
+           p.sc.np <= kR32Planes && p.sc.nl <= kR32Lights && !p.exact_shadows && !p.no_filter && !p.force_general && !p.exact_fp64 &&
+           !f.hdr64 && !f.depth && !f.depth64 && !f.normal && !f.albedo && p.bias >= 1e-6 && p.bias <= 1e-1;
+}
+
+cudaError_t launch_render32(const RenderParams& p0, int sm_count, cudaStream_t stream) {
+    RenderParams p = p0;
+    const bool aov = p.out.prim_id || p.out.light_mask;
+    const void* fn = aov ? (const void*)render32_kernel<true> : (const void*)render32_kernel<false>;
+    int dev = 0, optin = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    const size_t limit = optin > 4096 ? (size_t)optin - 4096 : 0;  // static shared memory of the kernel
+    size_t smem = p.plan.total;
+    const size_t with_cull = ((smem + 15) & ~(size_t)15) + (size_t)(kR32Threads / 32) * kCullBytesPerWarp;
+    p.cull = 0;
+    if (!p.no_cull && with_cull <= limit) { smem = with_cull; p.cull = 1; }
+    if (smem > limit) return cudaErrorInvalidConfiguration;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const long long n_tiles = (long long)((p.cam.width + kTile32W - 1) / kTile32W) * ((p.n_rows + kTile32H - 1) / kTile32H);
+    long long blocks = sm_count;
+    const long long needed = (n_tiles + kR32Threads / 32 - 1) / (kR32Threads / 32);
+    if (blocks > needed) blocks = needed > 0 ? needed : 1;
+    void* args[] = {(void*)&p};
+    return cudaLaunchKernel(fn, dim3((unsigned)blocks), dim3(kR32Threads), args, smem, stream);
+}
+
+}  // namespace rte

@@ -212,7 +212,7 @@ __device__ __forceinline__ void closest_hit_body(const DevScene& sc, const float
     closest_planes_triangles(sc, s_tri, r, o, d, alive, best, found, confirms);
 }
 
-__device__ __noinline__ void closest_hit_cold(const DevScene& sc, const float4* s_sph, const float4* s_tri, d3 o,
+static __device__ __noinline__ void closest_hit_cold(const DevScene& sc, const float4* s_sph, const float4* s_tri, d3 o,
                                               d3 d, bool no_filter, Hit& best, uint32_t& confirms) {
     closest_hit_body(sc, s_sph, s_tri, o, d, true, no_filter, best, confirms);
 }
@@ -225,7 +225,7 @@ __device__ __forceinline__ int material_of(const DevScene& sc, const Hit& h) {
 }
 
 // Scene::computeTransmittance, RE/Scene.h:35-77, literally (transparent occluders included).
-__device__ __noinline__ double march_exact(const DevScene& sc, const float4* s_sph, const float4* s_tri, d3 o, d3 d,
+static __device__ __noinline__ double march_exact(const DevScene& sc, const float4* s_sph, const float4* s_tri, d3 o, d3 d,
                                            double maxDist, double bias, bool no_filter, uint32_t& confirms) {
     double T = 1.0, traveled = 0.0;
     int safety = 64;

@@ -166,10 +166,10 @@ __device__ __forceinline__ void view_block_masks(const ulonglong2* __restrict__ 
 
 // The FP64 confirmation as ONE out-of-line copy: it is the rare path of every scan site, and inlining it K times
 // per site bloats the kernel far beyond the instruction caches.
-__device__ __noinline__ bool confirm_sphere(const double4* __restrict__ sph64, int idx, d3 o, d3 d, double& t) {
+static __device__ __noinline__ bool confirm_sphere(const double4* __restrict__ sph64, int idx, d3 o, d3 d, double& t) {
     return sphere_exact(sph64[idx], o, d, t);
 }
-__device__ __noinline__ bool confirm_triangle(const DevTri64* __restrict__ tri64, int idx, d3 o, d3 d, double& t) {
+static __device__ __noinline__ bool confirm_triangle(const DevTri64* __restrict__ tri64, int idx, d3 o, d3 d, double& t) {
     return tri_exact(tri64[idx], o, d, t);
 }
 // what a view holds: the spheres of the scene, or (kTri) the bounding spheres of its triangles
@@ -281,7 +281,7 @@ __device__ __forceinline__ void cull_store(float* __restrict__ mf, uint16_t* __r
 }
 // `md`: this lane's smallest u.a over its active rays (1 if it has none).  Returns -1 when the tile cone is too wide to be worth testing.
 // `src`: the view is itself a culled one (CTA level): position -> index in the full view, or NULL.
-__device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float md,
+static __device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float md,
                                       ulonglong2* __restrict__ mini, uint16_t* __restrict__ map, const uint16_t* __restrict__ src) {
     // min over the warp with one REDUX: non-negative floats order like their bit patterns (a negative dot clamps to 0: too wide anyway)
     md = __uint_as_float(__reduce_min_sync(kFullMask, __float_as_uint(fmaxf(md, 0.0f))));
@@ -335,7 +335,7 @@ __device__ __noinline__ int cull_pack(const ulonglong2* __restrict__ view, int n
 // Axis of the tile cone: the normalised sum of the active rays' directions (any unit vector would do: the half-angle is
 // measured against it afterwards).  The three sums go through integer REDUX (fixed point, 2^-22: exact enough for an axis)
 // instead of 15 shuffles.  One out-of-line copy; returns w = 0 when there is no active ray or the directions cancel.
-__device__ __noinline__ float4 cull_axis(float sx, float sy, float sz) {
+static __device__ __noinline__ float4 cull_axis(float sx, float sy, float sz) {
     const float kScale = 4194304.0f, kInv = 1.0f / 4194304.0f;  // |sum over the warp| <= 32 K <= 2^7: fits 2^29
     const float fx = (float)__reduce_add_sync(kFullMask, __float2int_rn(sx * kScale)) * kInv;
     const float fy = (float)__reduce_add_sync(kFullMask, __float2int_rn(sy * kScale)) * kInv;
@@ -386,7 +386,7 @@ struct CtaCull {
 };
 
 // Axis of the CTA's cone.  Called by every thread of the CTA; sx,sy,sz: this lane's sum of active directions.
-__device__ __noinline__ float4 cta_cull_axis(float sx, float sy, float sz, int* __restrict__ part) {
+static __device__ __noinline__ float4 cta_cull_axis(float sx, float sy, float sz, int* __restrict__ part) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     const float kScale = 262144.0f, kInv = 1.0f / 262144.0f;  // |sum over the CTA| <= 1024 K <= 2^11: fits 2^29
     const int ix = __reduce_add_sync(kFullMask, __float2int_rn(sx * kScale));
@@ -405,7 +405,7 @@ __device__ __noinline__ float4 cta_cull_axis(float sx, float sy, float sz, int* 
 }
 
 // Called by every thread of the CTA.  Returns the survivor count (CTA-uniform): -1 cone too wide, > kCtaCap overflow.
-__device__ __noinline__ int cta_cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float md,
+static __device__ __noinline__ int cta_cull_pack(const ulonglong2* __restrict__ view, int n_pad, float ax, float ay, float az, float md,
                                           ulonglong2* __restrict__ mini, uint16_t* __restrict__ map, int* __restrict__ part) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     const uint32_t mdw = __reduce_min_sync(kFullMask, __float_as_uint(fmaxf(md, 0.0f)));
@@ -682,7 +682,7 @@ struct RayLists {
 // Scene::computeTransmittance, RE/Scene.h:35-77, literally — but every closest-hit query of the march only looks at the
 // spheres of `list` (all spheres whose chord overlaps the ray's range: the march moves its origin along the same line, so
 // no other sphere can ever be hit) and at the planes.  Scenes of the fast path have no triangles and no transparency.
-__device__ __noinline__ double march_list(const DevScene& sc, const uint16_t* list, int n, d3 o, d3 d, double maxDist, double bias) {
+static __device__ __noinline__ double march_list(const DevScene& sc, const uint16_t* list, int n, d3 o, d3 d, double maxDist, double bias) {
     double T = 1.0, traveled = 0.0;
     int safety = 64;
     while (safety-- > 0 && T > 1e-4 && traveled < maxDist) {

@@ -1,0 +1,108 @@
+"""GPU parity of the FP32 PRODUCTION path (csrc/rte_render32.cu + the exact fix-up launch): calls that ask for hdr / rgb8 /
+prim_id / light_mask only, on diffuse sphere / plane scenes.
+
+Bars (BASELINE.json north_star): nearest-hit (type, index) and shadow visibility bit-exact, RGB8 within +-1 LSB of the
+reference; here also: HDR to 2e-5 relative, ray / test counters identical to the exact path's (which equal the oracle's)."""
+import numpy as np
+import pytest
+
+from raytracingengine_b200 import _abi, scenes
+
+pytestmark = pytest.mark.gpu
+COUNTERS = ("primary_rays", "shadow_rays", "sphere_tests", "plane_tests")
+OUTS = ("hdr", "rgb8", "prim_id", "light_mask")
+
+
+def both_paths(engine, op=_abi.TM_ACES, outs=OUTS, **opts):
+    fast = engine.render_host(outputs=outs, tonemap_op=op, **opts)
+    sf, lf = engine.stats(), engine.last_render_launches()
+    exact = engine.render_host(outputs=outs, tonemap_op=op, flags=_abi.FLAG_EXACT_FP64, **opts)
+    se = engine.stats()
+    return fast, sf, lf, exact, se
+
+
+def check(fast, sf, exact, se, n_px):
+    assert np.array_equal(fast["prim_id"], exact["prim_id"]), f"{np.count_nonzero(fast['prim_id'] != exact['prim_id'])} nearest-hit mismatches"
+    assert np.array_equal(fast["light_mask"], exact["light_mask"]), f"{np.count_nonzero(fast['light_mask'] != exact['light_mask'])} visibility mismatches"
+    d = np.abs(fast["rgb8"].astype(np.int16) - exact["rgb8"].astype(np.int16))
+    assert d.max() <= 1, f"{np.count_nonzero(d > 1)} bytes differ by more than 1 LSB"
+    np.testing.assert_allclose(fast["hdr"][:, :3], exact["hdr"][:, :3], rtol=2e-5, atol=1e-7)
+    for k in COUNTERS:
+        assert sf[k] == se[k], f"counter {k}: fp32 path {sf[k]}, exact path {se[k]}"
+    assert sf["fp64_confirms"] <= 0.02 * n_px, f"{sf['fp64_confirms']} of {n_px} pixels went through the fix-up launch"
+
+
+@pytest.mark.parametrize("cfg", ["c2", "c2_quarter", "c3", "odd", "big_resident", "camera_inside"])
+def test_fp32_path_against_exact_path_and_oracle(engine, oracle, cfg):
+    if cfg == "c2":
+        arrays, cam = scenes.config2(scale=0.125)
+    elif cfg == "c2_quarter":
+        arrays, cam = scenes.config2(scale=0.25)
+    elif cfg == "c3":
+        arrays, cam = scenes.config3(scale=0.125)
+    elif cfg == "big_resident":  # 2048 spheres x 5 views = 160 KB resident, no room for the cull scratch
+        arrays, cam = scenes.synthetic_room(240, 135, 120.0, 2048, 4, 4321)
+    elif cfg == "camera_inside":  # the camera sits inside a big sphere: far roots, inward normals
+        arrays, cam = scenes.synthetic_room(160, 90, 80.0, 200, 3, 99)
+        arrays.spheres[7] = ((0.0, 0.0, -25.0), 60.0, 7, 0)
+    else:  # width / height not multiples of the tile, width not a multiple of 4 (byte stores)
+        arrays, cam = scenes.synthetic_room(203, 117, 100.0, 300, 3, 77)
+    engine.upload(arrays, cam)
+    fast, sf, lf, exact, se = both_paths(engine)
+    assert lf in (2, 3), lf  # (view build +) FP32 kernel + fix-up launch
+    n = cam.width * cam.height
+    check(fast, sf, exact, se, n)
+    o = oracle.render(arrays, cam, want_aovs=True)
+    assert np.array_equal(fast["prim_id"], o["prim_id"]) and np.array_equal(fast["light_mask"], o["light_mask"])
+    want = oracle.tonemap_one(_abi.TM_ACES, o["hdr"])
+    assert np.abs(fast["rgb8"].astype(np.int16) - want.astype(np.int16)).max() <= 1
+    assert sf["primary_rays"] == o["primary_rays"] and sf["shadow_rays"] == o["shadow_rays"]
+    assert sf["sphere_tests"] == o["sphere_tests"] and sf["plane_tests"] == o["plane_tests"]
+
+
+def test_fp32_path_all_operators_bands_stripes(engine, oracle):
+    from raytracingengine_b200 import sharding
+    arrays, cam = scenes.config3(scale=0.1)
+    engine.upload(arrays, cam)
+    o = oracle.render(arrays, cam)
+    want = oracle.tonemap_all(o["hdr"])
+    full = {}
+    for op in range(_abi.TM_COUNT):
+        g = engine.render_host(outputs=("rgb8",), tonemap_op=op)
+        assert engine.last_render_launches() == 2
+        assert np.abs(g["rgb8"].astype(np.int16) - want[op].astype(np.int16)).max() <= 1, _abi.TM_NAMES[op]
+        full[op] = g["rgb8"]
+    H, W = cam.height, cam.width
+    ref = engine.render_host(outputs=("hdr", "rgb8"), tonemap_op=_abi.TM_ACES)
+    cuts = [0, H // 3, H // 3 + 1, H - 5, H]
+    parts = [engine.render_host(outputs=("hdr", "rgb8"), tonemap_op=_abi.TM_ACES, row0=a, row1=b) for a, b in zip(cuts[:-1], cuts[1:])]
+    for k in ("hdr", "rgb8"):
+        assert np.array_equal(np.concatenate([p[k] for p in parts]), ref[k]), k
+    for r in range(3):
+        so = sharding.stripe_opts(r, 3, H, 8)
+        rows = sharding.stripe_row_list(r, 3, H, 8)
+        part = engine.render_host(outputs=("rgb8",), tonemap_op=_abi.TM_ACES, **so)["rgb8"]
+        assert np.array_equal(part.reshape(len(rows), W, 3), ref["rgb8"].reshape(H, W, 3)[rows])
+
+
+def test_fp32_path_multisample(engine, port_oracle):
+    arrays, cam = scenes.config3(scale=0.05)
+    cam.antiAliasingAmount, cam.jitterSeed = 4, 2026
+    engine.upload(arrays, cam)
+    g = engine.render_host(outputs=("hdr", "rgb8"), tonemap_op=_abi.TM_ACES)
+    s = engine.stats()
+    o = port_oracle.render(arrays, cam)
+    np.testing.assert_allclose(g["hdr"][:, :3], o["hdr"], rtol=2e-5, atol=1e-7)
+    assert s["primary_rays"] == 4 * cam.width * cam.height == o["primary_rays"] and s["shadow_rays"] == o["shadow_rays"]
+    want = port_oracle.tonemap_one(_abi.TM_ACES, o["hdr"])
+    assert np.abs(g["rgb8"].astype(np.int16) - want.astype(np.int16)).max() <= 1
+
+
+def test_exact_flag_and_fp64_outputs_keep_the_exact_path(engine, oracle):
+    arrays, cam = scenes.config2(scale=0.05)
+    engine.upload(arrays, cam)
+    o = oracle.render(arrays, cam)
+    want = oracle.tonemap_one(_abi.TM_ACES, o["hdr"])
+    a = engine.render_host(outputs=("rgb8",), tonemap_op=_abi.TM_ACES, flags=_abi.FLAG_EXACT_FP64)["rgb8"]
+    b = engine.render_host(outputs=("rgb8", "hdr64"), tonemap_op=_abi.TM_ACES)
+    assert np.array_equal(a, want) and np.array_equal(b["rgb8"], want) and np.array_equal(b["hdr64"], o["hdr"])
