@@ -10,6 +10,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -53,6 +54,12 @@ struct rte_ctx {
     DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views, b_tviews, b_views_cold, b_tviews_cold;
     bool views_dirty = true;
     double views_bias = -1.0;
+    // FP32 production path: per-origin direction grids (rte_grid.cuh), rebuilt when the scene, the camera or the bias changes
+    DevBuf b_grid_count, b_grid_start, b_grid_entries;
+    bool grid_dirty = true;
+    double grid_bias = -1.0;
+    int grid_G = 0;
+    unsigned int* h_grid_total = nullptr;  // pinned: number of (sphere, cell) entries of the last build
 
     // rte_set_rgb8_peers
     uint8_t* peer_rgb8[kMaxPeers] = {};
@@ -260,6 +267,7 @@ extern "C" int rte_create(int device, rte_ctx** out) {
     CK(cudaHostAlloc(&ctx->h_fence_timeout, sizeof(unsigned int), cudaHostAllocMapped));
     *ctx->h_fence_timeout = 0u;
     CK(cudaMallocHost(&ctx->h_stats, sizeof(unsigned long long) * (kStatCount + 1)));
+    CK(cudaMallocHost(&ctx->h_grid_total, sizeof(unsigned int)));
     CK(cudaEventCreate(&ctx->ev_r0)); CK(cudaEventCreate(&ctx->ev_r1));
     CK(cudaEventCreate(&ctx->ev_t0)); CK(cudaEventCreate(&ctx->ev_t1));
     CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
@@ -275,7 +283,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
-                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->b_grid_count, &ctx->b_grid_start, &ctx->b_grid_entries, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -287,6 +295,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     if (ctx->ev_stage) cudaEventDestroy(ctx->ev_stage);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
+    if (ctx->h_grid_total) cudaFreeHost(ctx->h_grid_total);
     cudaEvent_t evs[] = {ctx->ev_r0, ctx->ev_r1, ctx->ev_t0, ctx->ev_t1};
     for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->ev_band) if (e) cudaEventDestroy(e);
@@ -473,6 +482,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
         if (mats[i].transparency > 0.0) sc.transparent = 1;
     }
     ctx->views_dirty = true;
+    ctx->grid_dirty = true;
     sc.ns = ns; sc.ns_pad = ns_pad; sc.nt = nt; sc.nt_pad = nt_pad;
     sc.sph64 = (const double4*)ctx->b_sph64.p; sc.sph_mat = (const int32_t*)ctx->b_sphmat.p;
     sc.planes = (const DevPlane*)ctx->b_planes.p; sc.tri64 = (const DevTri64*)ctx->b_tri64.p;
@@ -505,10 +515,38 @@ extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
     dc.aa = c->anti_aliasing; dc.jitter_seed = (uint32_t)c->jitter_seed;
     ctx->has_camera = true;
     ctx->views_dirty = true;
+    ctx->grid_dirty = true;
     return RTE_OK;
 }
 
 // ====================================================================================== render
+// Direction grids of the FP32 path: count + scan on the device, one read-back of the entry count (the only synchronisation,
+// once per scene / camera / bias), fill.  RTE_GRID_G (environment, developer knob): cells per cube-face edge.
+static int ensure_grid(rte_ctx* ctx, double bias, DevGrid& out) {
+    int G = 64;
+    if (const char* e = std::getenv("RTE_GRID_G")) { const int v = std::atoi(e); if (v >= 4 && v <= 512) G = v; }
+    const int n_views = 1 + ctx->sc.nl, cpv = 6 * G * G + 1;
+    const size_t n_cells = (size_t)n_views * (size_t)cpv;
+    if (ctx->grid_dirty || ctx->grid_bias != bias || ctx->grid_G != G) {
+        int rc;
+        if ((rc = reserve(ctx, ctx->b_grid_count, n_cells * 4)) || (rc = reserve(ctx, ctx->b_grid_start, (n_cells + 1) * 4))) return rc;
+        RTE_CUDA(ctx, cudaMemsetAsync(ctx->b_grid_count.p, 0, n_cells * 4, ctx->stream));
+        RTE_CUDA(ctx, launch_grid_count_scan(ctx->sc, ctx->cam, bias, G, (uint32_t*)ctx->b_grid_count.p, (uint32_t*)ctx->b_grid_start.p, ctx->stream));
+        RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_grid_total, (uint32_t*)ctx->b_grid_start.p + n_cells, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        const size_t total = *ctx->h_grid_total;
+        if ((rc = reserve(ctx, ctx->b_grid_entries, (total + total / 8 + 64) * 4))) return rc;
+        RTE_CUDA(ctx, launch_grid_fill(ctx->sc, ctx->cam, bias, G, (uint32_t*)ctx->b_grid_count.p, (uint32_t*)ctx->b_grid_start.p,
+                                       (uint32_t*)ctx->b_grid_entries.p, (uint32_t)(ctx->b_grid_entries.cap / 4), ctx->stream));
+        ctx->grid_dirty = false; ctx->grid_bias = bias; ctx->grid_G = G;
+        ctx->render_launches += 3;
+    }
+    out.cell_start = (const uint32_t*)ctx->b_grid_start.p;
+    out.entries = (const uint32_t*)ctx->b_grid_entries.p;
+    out.G = G; out.cells_per_view = cpv;
+    return RTE_OK;
+}
+
 // `first` / `last`: one API call may render its rows as several bands (rte_render_host); the statistics and the
 // ev_r0..ev_r1 interval then cover all of them.
 static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bool first = true, bool last = true) {
@@ -517,12 +555,6 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     const size_t smem_budget = ctx->smem_optin > 4096 ? ctx->smem_optin - 4096 : 0;  // static smem + headroom
     p.plan = plan_smem(ctx->sc, smem_budget);
     if (first) ctx->render_launches = 0;
-    if ((p.plan.use_views || p.plan.use_tri_views) && (ctx->views_dirty || ctx->views_bias != o.bias)) {
-        RTE_CUDA(ctx, launch_build_views(ctx->sc, ctx->cam, o.bias, ctx->stream));
-        ctx->render_launches += (ctx->sc.ns > 0 ? 1 : 0) + ((ctx->sc.nt > 0 && ctx->sc.tri_views) ? 1 : 0);
-        ctx->views_dirty = false;
-        ctx->views_bias = o.bias;
-    }
     p.row0 = o.row0; p.row1 = o.row1; p.n_rows = o.n_rows; p.stripe_rows = o.stripe_rows; p.stripe_period = o.stripe_period; p.max_depth = o.max_depth; p.tonemap_op = o.tonemap_op;
     p.exact_shadows = (o.flags & RTE_FLAG_EXACT_SHADOWS) ? 1 : 0;
     p.no_filter = (o.flags & RTE_FLAG_NO_FILTER) ? 1 : 0;
@@ -542,6 +574,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
         if (p.out.rgb8 && ((uintptr_t)p.out.rgb8 & 3u) != 0 && (ctx->cam.width & 3) == 0) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 must be 4-byte aligned");
         int rc = reserve(ctx, ctx->s_fix, n_px * sizeof(unsigned int));
         if (rc) return rc;
+        if ((rc = ensure_grid(ctx, o.bias, p.grid))) return rc;
         p.fix_list = (unsigned int*)ctx->s_fix.p;
         p.fix_count = reinterpret_cast<unsigned int*>(ctx->d_stats + kStatCount + 1);
         if (first) {
@@ -564,6 +597,12 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
         int rc = reserve(ctx, ctx->s_hits, (size_t)o.n_rows * (size_t)ctx->cam.width * sizeof(double2));
         if (rc) return rc;
         p.hits = (double2*)ctx->s_hits.p;
+    }
+    if ((p.plan.use_views || p.plan.use_tri_views) && (ctx->views_dirty || ctx->views_bias != o.bias)) {
+        RTE_CUDA(ctx, launch_build_views(ctx->sc, ctx->cam, o.bias, ctx->stream));
+        ctx->render_launches += (ctx->sc.ns > 0 ? 1 : 0) + ((ctx->sc.nt > 0 && ctx->sc.tri_views) ? 1 : 0);
+        ctx->views_dirty = false;
+        ctx->views_bias = o.bias;
     }
     // RGB8 (band buffer and / or registered peer frames) = the exact FP64 operator over the FP64 HDR of the render kernel, as
     // a second, HBM-bound pass (rte_tonemap.cu: tonemap64_kernel) — the render kernels themselves only write HDR

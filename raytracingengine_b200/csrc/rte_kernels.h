@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include "rte_device.cuh"
+#include "rte_grid.cuh"
 
 namespace rte {
 
@@ -47,6 +48,7 @@ struct RenderParams {
     int32_t pass_mode;       // fast kernel: 0 = auto, 1 = RTE_FLAG_SINGLE_PASS, 2 = RTE_FLAG_TWO_PASS (primary-ray launch + shading launch)
     double2* hits;           // two-pass fast path: {t, (kind << 30 | index) as the low word of the second double} per band pixel
     int32_t exact_fp64;      // RTE_FLAG_EXACT_FP64: never take the FP32 production path (rte_render32.cu)
+    DevGrid grid;            // FP32 path: per-origin direction grids (rte_grid.cuh), built per camera / bias
     unsigned int* fix_list;  // FP32 path: band-local indices of the pixels with an inconclusive decision (capacity: band pixels) ...
     unsigned int* fix_count; // ... and their number (zeroed before the launch); the fix-up launch renders them exactly
     unsigned int* tile_counter;        // zeroed before launch
@@ -59,6 +61,10 @@ size_t scene_smem_bytes(const DevScene& sc);
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream);
 // FP32 production path (rte_render32.cu) and the exact fix-up of its flagged pixels (rte_render.cu)
 bool fp32_path_eligible(const RenderParams& p);
+// direction grids: count + scan (cell_start[n_cells] = number of entries), then — with `entries` of at least that capacity — fill
+cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, cudaStream_t stream);
+cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
+                             uint32_t capacity, cudaStream_t stream);
 cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream);
 cudaError_t launch_fixup(const RenderParams& p, int sm_count, cudaStream_t stream);
 // would launch_render split this call into a primary-ray launch and a shading launch (it then needs p.hits)?

@@ -15,10 +15,10 @@
 //    output is either certain or exact, and flagged pixels (~1e-3 of a frame) are the reference's own bits.
 //  * The operator + toColor run in the kernel (tm32, rte_tonemap.cuh) and a tile row of 8 pixels leaves as six aligned
 //    32-bit words: no FP64 HDR scratch, no second pass.
+#include "rte_grid.cuh"
 #include "rte_kernels.h"
-#include "rte_stage.cuh"
 #include "rte_tonemap.cuh"
-#include "rte_views.cuh"
+#include "rte_trace.cuh"
 
 namespace rte {
 
@@ -146,44 +146,112 @@ __device__ __forceinline__ int plane_interval(const Plane32& p, float ox, float 
     return rel < 0.25f ? kCandHit : kCandUnsure;
 }
 
-// ------------------------------------------------------------------------------ the scan of one view by one ray per lane
-// Nomination by the view's cone test (rte_views.cuh: view_block_masks, 3 packed FMAs per sphere pair), candidates queued
-// per lane and resolved lane-parallel per window, in ascending index per ray.  `on_cand(idx)` may clear `active`.
-template <class Fn>
-__device__ __forceinline__ void scan32(const ulonglong2* __restrict__ view, const uint16_t* __restrict__ map, int ns, int ns_pad, const ViewRay& r,
-                                       bool& active, const double4* __restrict__ sph64, uint32_t& executed, Fn&& on_cand) {
-    uint16_t q[kWindow];  // local memory; only written entries are touched
-    int qn = 0, base = 0;
-    const ViewRay rr[1] = {r};
-#pragma unroll 1
-    while (base < ns_pad) {
-        const int wbase = base, stop = min(base + kWindow, ns_pad);
-#pragma unroll 1
-        do {
-            uint32_t cand[1];
-            view_block_masks<1>(view + base, rr, cand);
-            executed += kViewBlock;
-            uint32_t c = active ? cand[0] : 0u;
-            while (c) {  // short, divergent
-                const int i = __clz(c);
-                c &= ~(0x80000000u >> i);
-                if (base + i < ns) {
-                    q[qn++] = (uint16_t)(base - wbase + i);
-                    const int idx = map ? (int)map[base + i] : base + i;
-                    asm volatile("prefetch.global.L1 [%0];" ::"l"(sph64 + idx));
-                }
-            }
-            base += kViewBlock;
-        } while (base < stop);
-        const int nmax = __reduce_max_sync(kFullMask, qn);
-#pragma unroll 1
-        for (int e = 0; e < nmax; ++e) {
-            if (e >= qn || !active) continue;
-            const int pos = wbase + (int)q[e];
-            on_cand(map ? (int)map[pos] : pos);
+// ------------------------------------------------------------------------------ building the direction grids (rte_grid.cuh)
+// Per frame (camera, lights or bias changed): count the (sphere, cell) incidences, exclusive scan, fill.  One thread per
+// (view, sphere); the count pass leaves its counters at zero again after the fill pass has consumed them.
+struct GridBuildParams {
+    DevScene sc;
+    double cam[3];
+    double bias;
+    int32_t G, cells_per_view, n_views;
+    uint32_t* count;       // n_cells counters (zero before the count pass and after the fill pass)
+    uint32_t* cell_start;  // n_cells + 1
+    uint32_t* entries;
+    uint32_t capacity;     // of `entries`
+};
+__device__ __forceinline__ void grid_view_sphere(const GridBuildParams& B, int j, int i, double& fx, double& fy, double& fz, double& r) {
+    const double4 s = B.sc.sph64[i];
+    const double ox = j == 0 ? B.cam[0] : B.sc.lights[j - 1].pos[0], oy = j == 0 ? B.cam[1] : B.sc.lights[j - 1].pos[1],
+                 oz = j == 0 ? B.cam[2] : B.sc.lights[j - 1].pos[2];
+    fx = s.x - ox; fy = s.y - oy; fz = s.z - oz;
+    const double F = sqrt(fx * fx + fy * fy + fz * fz);
+    // |r| (+ bias for a light's grid: the shadow line passes the light within `bias`), + the lateral reach of an FP32 direction
+    r = (fabs(s.w) + (j > 0 ? B.bias : 0.0)) * (1.0 + 1e-9) + 4e-6 * F + 1e-12;
+}
+template <bool kFill>
+__global__ void __launch_bounds__(256) grid_build_kernel(const GridBuildParams B) {
+    const int total = B.n_views * B.sc.ns;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        const int j = t / B.sc.ns, i = t - j * B.sc.ns;
+        double fx, fy, fz, r;
+        grid_view_sphere(B, j, i, fx, fy, fz, r);
+        const uint32_t base = (uint32_t)j * (uint32_t)B.cells_per_view;
+        auto add = [&](uint32_t cell) {
+            if (!kFill) { atomicAdd(B.count + cell, 1u); return; }
+            const uint32_t pos = B.cell_start[cell] + (atomicSub(B.count + cell, 1u) - 1u);
+            if (pos < B.capacity) B.entries[pos] = (uint32_t)i;
+        };
+        if (grid_sphere_is_near(fx, fy, fz, r)) { add(base + (uint32_t)(6 * B.G * B.G)); continue; }
+        for (int face = 0; face < 6; ++face) {
+            GridRect rc;
+            if (!grid_rect(B.G, face, fx, fy, fz, r, rc)) continue;
+            for (int iv = rc.iv0; iv <= rc.iv1; ++iv)
+                for (int iu = rc.iu0; iu <= rc.iu1; ++iu) add(base + (uint32_t)(face * B.G * B.G + iv * B.G + iu));
         }
-        qn = 0;
-        if (__all_sync(kFullMask, !active)) break;
+    }
+}
+// Exclusive scan of `count` into `cell_start` (one CTA; n_cells is a few hundred thousand); cell_start[n] = total.
+__global__ void __launch_bounds__(1024) grid_scan_kernel(const uint32_t* __restrict__ count, uint32_t* __restrict__ cell_start, int n) {
+    __shared__ uint32_t s_part[1024];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0u;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024 * 4) {  // 4 consecutive cells per thread: coalesced enough, n / 4096 rounds
+        const int i0 = base + threadIdx.x * 4;
+        uint32_t v[4], sum = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { v[k] = i0 + k < n ? count[i0 + k] : 0u; sum += v[k]; }
+        s_part[threadIdx.x] = sum;
+        __syncthreads();
+        for (int off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan of the per-thread sums
+            const uint32_t add = threadIdx.x >= (unsigned)off ? s_part[threadIdx.x - off] : 0u;
+            __syncthreads();
+            s_part[threadIdx.x] += add;
+            __syncthreads();
+        }
+        uint32_t run = s_carry + s_part[threadIdx.x] - sum;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { if (i0 + k < n) cell_start[i0 + k] = run; run += v[k]; }
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry += s_part[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) cell_start[n] = s_carry;
+}
+
+cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, cudaStream_t stream) {
+    GridBuildParams B{};
+    B.sc = sc; B.cam[0] = cam.pos[0]; B.cam[1] = cam.pos[1]; B.cam[2] = cam.pos[2]; B.bias = bias;
+    B.G = G; B.cells_per_view = 6 * G * G + 1; B.n_views = 1 + sc.nl;
+    B.count = count; B.cell_start = cell_start; B.entries = nullptr; B.capacity = 0;
+    const int total = B.n_views * sc.ns, n_cells = B.n_views * B.cells_per_view;
+    if (total > 0) grid_build_kernel<false><<<(total + 255) / 256, 256, 0, stream>>>(B);
+    grid_scan_kernel<<<1, 1024, 0, stream>>>(count, cell_start, n_cells);
+    return cudaGetLastError();
+}
+cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
+                             uint32_t capacity, cudaStream_t stream) {
+    GridBuildParams B{};
+    B.sc = sc; B.cam[0] = cam.pos[0]; B.cam[1] = cam.pos[1]; B.cam[2] = cam.pos[2]; B.bias = bias;
+    B.G = G; B.cells_per_view = 6 * G * G + 1; B.n_views = 1 + sc.nl;
+    B.count = count; B.cell_start = cell_start; B.entries = entries; B.capacity = capacity;
+    const int total = B.n_views * sc.ns;
+    if (total > 0) grid_build_kernel<true><<<(total + 255) / 256, 256, 0, stream>>>(B);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------ the candidates of one ray
+// The spheres of the ray's cell, then the view's near list.  `on_cand(idx)` may clear `go` to stop early.
+template <class Fn>
+__device__ __forceinline__ void grid_candidates(const DevGrid& g, int view, float dx, float dy, float dz, bool& go, Fn&& on_cand) {
+    if (!go) return;
+    uint32_t cell = grid_cell(g, view, dx, dy, dz);
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        const uint32_t e0 = __ldg(g.cell_start + cell), e1 = __ldg(g.cell_start + cell + 1);
+#pragma unroll 1
+        for (uint32_t e = e0; e < e1 && go; ++e) on_cand((int)__ldg(g.entries + e));
+        cell = grid_near_cell(g, view);
     }
 }
 
@@ -210,10 +278,10 @@ struct Px32 {
     uint32_t prim, lmask;
     uint32_t c_shadow, c_sph, c_pl;  // statistics of this sample (SURVEY §8(d) algorithmic counts)
 };
-__device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S, const ulonglong2* __restrict__ s_views, const CullScratch* cull, int px, int py,
-                                        bool alive, int sample, Px32& out, uint32_t& executed) {
+__device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S, int px, int py, bool alive, int sample, Px32& out, uint32_t& executed) {
     const DevScene& sc = P.sc;
-    const int ns = sc.ns, ns_pad = sc.ns_pad, np = S.np, nl = S.nl;
+    const DevGrid& grid = P.grid;
+    const int ns = sc.ns, np = S.np, nl = S.nl;
     const float bias = (float)P.bias;
     bool ok = true;
     out.r = out.g = out.b = 0.0f;
@@ -233,31 +301,20 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         const double inv = rsqrt64_fast(len2);
         dx = vx * inv; dy = vy * inv; dz = vz * inv;
     }
-    ViewRay r;
+    struct { float ux, uy, uz; } r;  // fl32 of the unit direction
     r.ux = (float)dx; r.uy = (float)dy; r.uz = (float)dz;
     // ---- Scene::IntersectClosest, RE/Scene.h:218-257, from intervals
     Near32 nr;
     nr.kind = RTE_HIT_NONE; nr.idx = 0; nr.lo = 0.0f; nr.hi = 0.0f; nr.amb_lo = INFINITY;
-    if (ns > 0) {
-        const ulonglong2* view = s_views;
-        const uint16_t* map = nullptr;
-        int n = ns, n_pad = ns_pad;
-        if (cull && n_pad >= kCullMin && (n_pad & 63) == 0) {
-            int cnt = 0;
-            const ViewRay rr[1] = {r};
-            const bool act[1] = {alive};
-            executed += (uint32_t)(n_pad >> 4);
-            if (cull_view<1>(view, n_pad, rr, act, *cull, cnt)) { view = cull->mini; map = cull->map; n = cnt; n_pad = (cnt + 31) & ~31; }
-        }
-        bool active = alive;
-        scan32(view, map, n, n_pad, r, active, sc.sph64, executed, [&](int idx) {
-            const Cand32 c = classify_sphere(sc.sph64[idx], S.cam[0], S.cam[1], S.cam[2], r.ux, r.uy, r.uz, 0.0f);
-            float lo, hi;
-            const int cls = reported_t(c, lo, hi);
-            if (cls == kCandHit) near_hit(nr, RTE_HIT_SPHERE, idx, lo, hi);
-            else if (cls == kCandUnsure) near_unsure(nr, lo);
-        });
-    }
+    bool go0 = alive;
+    grid_candidates(grid, 0, r.ux, r.uy, r.uz, go0, [&](int idx) {
+        const Cand32 c = classify_sphere(sc.sph64[idx], S.cam[0], S.cam[1], S.cam[2], r.ux, r.uy, r.uz, 0.0f);
+        float lo, hi;
+        const int cls = reported_t(c, lo, hi);
+        executed += 1u;
+        if (cls == kCandHit) near_hit(nr, RTE_HIT_SPHERE, idx, lo, hi);
+        else if (cls == kCandUnsure) near_unsure(nr, lo);
+    });
     const float cam32x = (float)S.cam[0], cam32y = (float)S.cam[1], cam32z = (float)S.cam[2];
     const float cam1 = fabsf(cam32x) + fabsf(cam32y) + fabsf(cam32z);
 #pragma unroll 1
@@ -268,7 +325,6 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         else if (cls == kCandUnsure) near_unsure(nr, 0.0f);
     }
     if (near_ambiguous(nr)) ok = false;
-    // (no early exit: the culls and scans of the light loop are warp-synchronous, every lane walks them)
     const bool hitv = alive && ok && nr.kind != RTE_HIT_NONE;
     if (!alive) { out.c_sph = 0u; out.c_pl = 0u; }
     if (alive && nr.kind == RTE_HIT_NONE) {  // Scene::backgroundColor, RE/Scene.h:30-33
@@ -331,39 +387,27 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         if (!__any_sync(kFullMask, cast)) continue;
         const float maxDist = dist - bias;
         const float dt = 24.0f * kEps32 * (dist + so1) + 1e-7f;  // slack of the range ends (maxDist, bias) against the candidate bounds
-        const float tmax_lo = maxDist - dt, tmax_hi = maxDist + dt, bias_hi = bias + dt, tsafe_hi = 130.0f * bias + dt;
+        const float tmax_lo = maxDist - dt, tmax_hi = maxDist + dt, bias_hi = bias + dt;
         bool occl = false, unsure = false;
         uint32_t first = (uint32_t)ns;
-        if (ns > 0) {
-            ViewRay rv;
-            rv.ux = -Lx; rv.uy = -Ly; rv.uz = -Lz;  // the light's view is scanned from the light towards the shaded point
-            const ulonglong2* view = s_views + (size_t)(1 + j) * ns_pad;
-            const uint16_t* map = nullptr;
-            int n = ns, n_pad = ns_pad;
-            if (cull && n_pad >= kCullMin && (n_pad & 63) == 0) {
-                int cnt = 0;
-                const ViewRay rr[1] = {rv};
-                const bool act[1] = {cast};
-                executed += (uint32_t)(n_pad >> 4);
-                if (cull_view<1>(view, n_pad, rr, act, *cull, cnt)) { view = cull->mini; map = cull->map; n = cnt; n_pad = (cnt + 31) & ~31; }
+        bool go = cast;
+        // the light's grid is looked up along the reversed ray (from the light towards the shaded point); the candidates
+        // are tested against the ray itself: origin so, direction L
+        grid_candidates(grid, 1 + j, -Lx, -Ly, -Lz, go, [&](int idx) {
+            if (idx == self) return;  // so lies outside the sphere the point is on, the ray leaves it: both roots < 0
+            const Cand32 c = classify_sphere(sc.sph64[idx], sox, soy, soz, Lx, Ly, Lz, 0.0f);
+            float lo, hi;
+            const int cls = reported_t(c, lo, hi);
+            executed += 1u;
+            if (cls == kCandMiss) return;
+            if (lo > tmax_hi) return;  // behind the light: not an occluder, not `near`
+            if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) {  // certainly bias < t < maxDist
+                first = min(first, (uint32_t)idx);  // (the lists are unordered: the first occluder in canonical order is the smallest index)
+                occl = true;
+                return;
             }
-            bool active = cast;
-            scan32(view, map, n, n_pad, rv, active, sc.sph64, executed, [&](int idx) {
-                if (idx == self) return;  // so lies outside the sphere the point is on, the ray leaves it: both roots < 0
-                const Cand32 c = classify_sphere(sc.sph64[idx], sox, soy, soz, Lx, Ly, Lz, 0.0f);
-                float lo, hi;
-                const int cls = reported_t(c, lo, hi);
-                if (cls == kCandMiss) return;
-                if (lo > tmax_hi) return;  // behind the light: not an occluder, not `near`
-                if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) {  // certainly bias < t < maxDist
-                    if (!occl) first = (uint32_t)idx;
-                    occl = true;
-                    if (lo > tsafe_hi) active = false;  // beyond the reach of the march's bias steps: decided
-                    return;
-                }
-                unsure = true; active = false;
-            });
-        }
+            unsure = true; go = false;
+        });
         if (unsure) ok = false;
         uint32_t firstp = (uint32_t)np;
         if (cast && !occl && !unsure) {  // planes, any-hit in canonical order
@@ -402,9 +446,7 @@ constexpr int kTile32W = 8, kTile32H = 4;
 
 template <bool kAov>
 __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_constant__ RenderParams P) {
-    extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ Scene32 s32;
-    __shared__ __align__(8) uint64_t s_bar;
     __shared__ unsigned long long s_stats[kR32Threads / 32][kStatCount];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
@@ -423,15 +465,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
         for (int c = 0; c < 3; ++c) s32.cam[c] = P.cam.pos[c];
     }
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
-    StagedScene S;
-    stage_scene(P.sc, P.plan, dyn_smem, &s_bar, S);  // (its __syncthreads also publishes s32)
-    CullScratch cull_scratch{nullptr, nullptr};
-    if (P.cull) {
-        unsigned char* base = dyn_smem + ((P.plan.total + 15) & ~(size_t)15) + (size_t)warp * kCullBytesPerWarp;
-        cull_scratch.mini = reinterpret_cast<ulonglong2*>(base);
-        cull_scratch.map = reinterpret_cast<uint16_t*>(base + kCullCap * 16);
-    }
-    const CullScratch* cull = P.cull ? &cull_scratch : nullptr;
+    __syncthreads();
     tm32::Consts K;
     {
         const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f, x = 11.2f;  // 1 / uncharted2_tonemap_partial(11.2)
@@ -465,7 +499,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
 #pragma unroll 1
         for (int s = 0; s < aa; ++s) {
             Px32 o;
-            ok = trace32(P, s32, S.views, cull, px, py, inb, s, o, executed) && ok;
+            ok = trace32(P, s32, px, py, inb, s, o, executed) && ok;
             cr += o.r; cg += o.g; cb += o.b;
             n_shadow += o.c_shadow; n_sph += o.c_sph; n_pl += o.c_pl;
             if (s == 0) { prim = o.prim; lmask = o.lmask; }
@@ -523,35 +557,23 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
 }
 
-// Can this render call take the FP32 path?  (rte_render.cu decides with it; everything else takes the exact kernels.)
+// Can this render call take the FP32 path?  (rte_api.cu decides with it; everything else takes the exact kernels.)
 bool fp32_path_eligible(const RenderParams& p) {
     const rte_frame& f = p.out;
-    return p.plan.use_views && !p.plan.stream_views && !p.plan.use_tri_views && !p.sc.reflective && !p.sc.transparent && p.sc.nt == 0 && p.sc.ns > 0 &&
-           p.sc.np <= kR32Planes && p.sc.nl <= kR32Lights && !p.exact_shadows && !p.no_filter && !p.force_general && !p.exact_fp64 &&
+    return !p.sc.reflective && !p.sc.transparent && p.sc.nt == 0 && p.sc.ns > 0 && p.sc.np <= kR32Planes && p.sc.nl <= kR32Lights &&
+           !p.exact_shadows && !p.no_filter && !p.force_general && !p.no_cull && p.pass_mode == 0 && !p.exact_fp64 &&
            !f.hdr64 && !f.depth && !f.depth64 && !f.normal && !f.albedo && p.bias >= 1e-6 && p.bias <= 1e-1;
 }
 
-cudaError_t launch_render32(const RenderParams& p0, int sm_count, cudaStream_t stream) {
-    RenderParams p = p0;
+cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream) {
     const bool aov = p.out.prim_id || p.out.light_mask;
     const void* fn = aov ? (const void*)render32_kernel<true> : (const void*)render32_kernel<false>;
-    int dev = 0, optin = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
-    const size_t limit = optin > 4096 ? (size_t)optin - 4096 : 0;  // static shared memory of the kernel
-    size_t smem = p.plan.total;
-    const size_t with_cull = ((smem + 15) & ~(size_t)15) + (size_t)(kR32Threads / 32) * kCullBytesPerWarp;
-    p.cull = 0;
-    if (!p.no_cull && with_cull <= limit) { smem = with_cull; p.cull = 1; }
-    if (smem > limit) return cudaErrorInvalidConfiguration;
-    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
     const long long n_tiles = (long long)((p.cam.width + kTile32W - 1) / kTile32W) * ((p.n_rows + kTile32H - 1) / kTile32H);
-    long long blocks = sm_count;
+    long long blocks = sm_count;  // persistent: one CTA of 32 warps per SM (64 registers per thread fill the register file)
     const long long needed = (n_tiles + kR32Threads / 32 - 1) / (kR32Threads / 32);
     if (blocks > needed) blocks = needed > 0 ? needed : 1;
     void* args[] = {(void*)&p};
-    return cudaLaunchKernel(fn, dim3((unsigned)blocks), dim3(kR32Threads), args, smem, stream);
+    return cudaLaunchKernel(fn, dim3((unsigned)blocks), dim3(kR32Threads), args, 0, stream);
 }
 
 }  // namespace rte
