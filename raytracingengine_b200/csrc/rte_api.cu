@@ -55,7 +55,10 @@ struct rte_ctx {
     bool views_dirty = true;
     double views_bias = -1.0;
     // FP32 production path: per-origin direction grids (rte_grid.cuh), rebuilt when the scene, the camera or the bias changes
-    DevBuf b_grid_count, b_grid_start, b_grid_entries;
+    DevBuf b_grid_count, b_grid_start, b_grid_entries, b_grid_aggr;
+    uint32_t grid_epoch = 0;
+    long long grid_shape = -1;        // (ns, nl, G) of the build the entries buffer was sized for
+    bool grid_check_pending = false;  // the last build was not followed by a read-back of its entry count yet
     bool grid_dirty = true;
     double grid_bias = -1.0;
     int grid_G = 0;
@@ -283,7 +286,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
-                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->b_grid_count, &ctx->b_grid_start, &ctx->b_grid_entries, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
+                      &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->b_grid_count, &ctx->b_grid_start, &ctx->b_grid_entries, &ctx->b_grid_aggr, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
@@ -320,6 +323,7 @@ extern "C" int rte_set_stream(rte_ctx* ctx, void* cuda_stream) {
     return RTE_OK;
 }
 
+static int check_grid_overflow(rte_ctx* ctx);
 static int check_fence_timeout(rte_ctx* ctx) {
     if (ctx->h_fence_timeout && *ctx->h_fence_timeout) {
         *ctx->h_fence_timeout = 0u;
@@ -331,6 +335,7 @@ static int check_fence_timeout(rte_ctx* ctx) {
 extern "C" int rte_synchronize(rte_ctx* ctx) {
     RTE_ENTER(ctx);
     RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (int rc = check_grid_overflow(ctx)) return rc;
     return check_fence_timeout(ctx);
 }
 
@@ -520,8 +525,11 @@ extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
 }
 
 // ====================================================================================== render
-// Direction grids of the FP32 path: count + scan on the device, one read-back of the entry count (the only synchronisation,
-// once per scene / camera / bias), fill.  RTE_GRID_G (environment, developer knob): cells per cube-face edge.
+// Direction grids of the FP32 path: count + scan on the device, then fill.  The entry count is only known on the device:
+// the first build of a scene shape (sphere / light count, G) reads it back (one synchronisation) and sizes the buffer at
+// twice that; later builds of the same shape (a re-uploaded or moved scene) reuse the buffer without synchronising — the fill
+// pass never writes beyond it, the count travels to a pinned word and is checked at the next synchronisation point
+// (check_grid_overflow).  RTE_GRID_G (environment, developer knob): cells per cube-face edge.
 static int ensure_grid(rte_ctx* ctx, double bias, DevGrid& out) {
     int G = 64;
     if (const char* e = std::getenv("RTE_GRID_G")) { const int v = std::atoi(e); if (v >= 4 && v <= 512) G = v; }
@@ -529,13 +537,27 @@ static int ensure_grid(rte_ctx* ctx, double bias, DevGrid& out) {
     const size_t n_cells = (size_t)n_views * (size_t)cpv;
     if (ctx->grid_dirty || ctx->grid_bias != bias || ctx->grid_G != G) {
         int rc;
+        const size_t aggr_bytes = (size_t)grid_scan_blocks((int)n_cells) * 8;
         if ((rc = reserve(ctx, ctx->b_grid_count, n_cells * 4)) || (rc = reserve(ctx, ctx->b_grid_start, (n_cells + 1) * 4))) return rc;
+        if (ctx->b_grid_aggr.cap < aggr_bytes) {
+            if ((rc = reserve(ctx, ctx->b_grid_aggr, aggr_bytes))) return rc;
+            RTE_CUDA(ctx, cudaMemsetAsync(ctx->b_grid_aggr.p, 0, ctx->b_grid_aggr.cap, ctx->stream));  // (epoch 0 is never used)
+        }
+        ctx->grid_epoch = ctx->grid_epoch == 0xFFFFFFFFu ? 1u : ctx->grid_epoch + 1u;
         RTE_CUDA(ctx, cudaMemsetAsync(ctx->b_grid_count.p, 0, n_cells * 4, ctx->stream));
-        RTE_CUDA(ctx, launch_grid_count_scan(ctx->sc, ctx->cam, bias, G, (uint32_t*)ctx->b_grid_count.p, (uint32_t*)ctx->b_grid_start.p, ctx->stream));
+        RTE_CUDA(ctx, launch_grid_count_scan(ctx->sc, ctx->cam, bias, G, (uint32_t*)ctx->b_grid_count.p, (uint32_t*)ctx->b_grid_start.p,
+                                             (unsigned long long*)ctx->b_grid_aggr.p, ctx->grid_epoch, ctx->stream));
         RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_grid_total, (uint32_t*)ctx->b_grid_start.p + n_cells, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        const size_t total = *ctx->h_grid_total;
-        if ((rc = reserve(ctx, ctx->b_grid_entries, (total + total / 8 + 64) * 4))) return rc;
+        const long long shape = ((long long)ctx->sc.ns << 24) ^ ((long long)ctx->sc.nl << 12) ^ (long long)G;
+        if (ctx->grid_shape != shape || ctx->b_grid_entries.cap == 0) {
+            RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            const size_t total = *ctx->h_grid_total;
+            if ((rc = reserve(ctx, ctx->b_grid_entries, (2 * total + 1024) * 4))) return rc;
+            ctx->grid_shape = shape;
+            ctx->grid_check_pending = false;
+        } else {
+            ctx->grid_check_pending = true;
+        }
         RTE_CUDA(ctx, launch_grid_fill(ctx->sc, ctx->cam, bias, G, (uint32_t*)ctx->b_grid_count.p, (uint32_t*)ctx->b_grid_start.p,
                                        (uint32_t*)ctx->b_grid_entries.p, (uint32_t)(ctx->b_grid_entries.cap / 4), ctx->stream));
         ctx->grid_dirty = false; ctx->grid_bias = bias; ctx->grid_G = G;
@@ -545,6 +567,16 @@ static int ensure_grid(rte_ctx* ctx, double bias, DevGrid& out) {
     out.entries = (const uint32_t*)ctx->b_grid_entries.p;
     out.G = G; out.cells_per_view = cpv;
     return RTE_OK;
+}
+// After a stream synchronisation: did the last unsynchronised grid build fit its buffer?  If not, the frames rendered with it
+// are invalid: the next build sizes the buffer anew, and the caller is told (rte_render_host renders again by itself).
+static int check_grid_overflow(rte_ctx* ctx) {
+    if (!ctx->grid_check_pending) return RTE_OK;
+    ctx->grid_check_pending = false;
+    if ((size_t)*ctx->h_grid_total * 4 <= ctx->b_grid_entries.cap) return RTE_OK;
+    ctx->grid_dirty = true; ctx->grid_shape = -1;
+    return fail(ctx, RTE_ERR_LIMIT, "the direction grid of the last render outgrew its buffer (%u entries): that frame is incomplete, render it again",
+                *ctx->h_grid_total);
 }
 
 // `first` / `last`: one API call may render its rows as several bands (rte_render_host); the statistics and the
@@ -568,13 +600,20 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
     // FP32 production path (rte_render32.cu): diffuse sphere / plane scenes with resident views, outputs hdr / rgb8 / prim_id /
     // light_mask.  The operator runs in the kernel; pixels with an inconclusive FP32 decision go through the exact fix-up launch.
-    // (Registered peer frames / fences keep the exact path: its RGB8 pass performs the peer stores.)
-    if (o.n_rows > 0 && ctx->n_peers == 0 && ctx->n_fence == 0 && fp32_path_eligible(p)) {
+    // With registered peer frames the kernel stores its RGB8 into every rank's frame itself; the fix-up launch signals the fence.
+    if (o.n_rows > 0 && fp32_path_eligible(p)) {
         const size_t n_px = (size_t)o.n_rows * (size_t)ctx->cam.width;
         if (p.out.rgb8 && ((uintptr_t)p.out.rgb8 & 3u) != 0 && (ctx->cam.width & 3) == 0) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 must be 4-byte aligned");
         int rc = reserve(ctx, ctx->s_fix, n_px * sizeof(unsigned int));
         if (rc) return rc;
         if ((rc = ensure_grid(ctx, o.bias, p.grid))) return rc;
+        p.n_peers = p.tonemap_op == RTE_TM_NONE ? 0 : ctx->n_peers;
+        for (int i = 0; i < p.n_peers; ++i) p.peer_rgb8[i] = ctx->peer_rgb8[i];
+        if (ctx->n_fence > 0 && p.n_peers > 0) {
+            ctx->fence_seq += 1;
+            for (int i = 0; i < ctx->n_fence; ++i) p.fence_flags[i] = ctx->fence_flags[i];
+            p.n_fence = ctx->n_fence; p.fence_rank = ctx->fence_rank; p.fence_seq = ctx->fence_seq; p.fence_counter = ctx->d_fence_counter;
+        }
         p.fix_list = (unsigned int*)ctx->s_fix.p;
         p.fix_count = reinterpret_cast<unsigned int*>(ctx->d_stats + kStatCount + 1);
         if (first) {
@@ -722,6 +761,11 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
     RTE_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copied, 0));  // later work of the context must not overwrite the staging buffers
     RTE_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
     RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (int rc = check_grid_overflow(ctx)) {  // the reused grid buffer was too small for this scene: it is sized anew, the frame rendered again
+        static thread_local int depth = 0;
+        if (depth == 0) { ++depth; rc = rte_render_host(ctx, opts, hf); --depth; }
+        return rc;
+    }
     return RTE_OK;
 }
 
@@ -731,6 +775,7 @@ extern "C" int rte_get_stats(rte_ctx* ctx, rte_stats* out) {
     RTE_ENTER(ctx);
     if (!out) return fail(ctx, RTE_ERR_INVALID, "rte_get_stats: out is NULL");
     RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (int rc = check_grid_overflow(ctx)) return rc;
     if (int rc = check_fence_timeout(ctx)) return rc;
     rte_stats& s = ctx->stats;
     if (ctx->render_timed) {

@@ -49,6 +49,15 @@ struct RenderParams {
     double2* hits;           // two-pass fast path: {t, (kind << 30 | index) as the low word of the second double} per band pixel
     int32_t exact_fp64;      // RTE_FLAG_EXACT_FP64: never take the FP32 production path (rte_render32.cu)
     DevGrid grid;            // FP32 path: per-origin direction grids (rte_grid.cuh), built per camera / bias
+    // FP32 path, multi-GPU output (rte_set_rgb8_peers / rte_set_fence_peers): the render kernel stores every tile row it finishes
+    // into every registered full frame at its image position (peer stores over NVLink while the SMs keep tracing); the fix-up
+    // launch stores its pixels and then signals the frame fence (its last CTA), see Tonemap64Params below
+    uint8_t* peer_rgb8[8];
+    int32_t n_peers;
+    uint32_t* fence_flags[8];
+    int32_t n_fence, fence_rank;
+    uint32_t fence_seq;
+    unsigned int* fence_counter;
     unsigned int* fix_list;  // FP32 path: band-local indices of the pixels with an inconclusive decision (capacity: band pixels) ...
     unsigned int* fix_count; // ... and their number (zeroed before the launch); the fix-up launch renders them exactly
     unsigned int* tile_counter;        // zeroed before launch
@@ -62,7 +71,10 @@ cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stre
 // FP32 production path (rte_render32.cu) and the exact fix-up of its flagged pixels (rte_render.cu)
 bool fp32_path_eligible(const RenderParams& p);
 // direction grids: count + scan (cell_start[n_cells] = number of entries), then — with `entries` of at least that capacity — fill
-cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, cudaStream_t stream);
+// (`aggregates`: grid_scan_blocks(n_cells) 64-bit words of scratch; `epoch`: a number that differs from build to build)
+int grid_scan_blocks(int n_cells);
+cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start,
+                                   unsigned long long* aggregates, uint32_t epoch, cudaStream_t stream);
 cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
                              uint32_t capacity, cudaStream_t stream);
 cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream);

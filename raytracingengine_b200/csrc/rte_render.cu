@@ -602,7 +602,12 @@ __global__ void __launch_bounds__(kRenderThreads) fixup_kernel(const __grid_cons
     const int W = P.cam.width, sr = P.stripe_rows, sp = P.stripe_period, aa = P.cam.aa;
     PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
     uint32_t n_prim = 0;
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    // Each pixel is a long serial FP64 chain and there are few of them: only every kFixSpread-th lane takes one, so that the
+    // list spreads over kFixSpread times as many warps (latency-bound work: more warps in flight, not fewer instructions).
+    constexpr unsigned int kFixSpread = 4;
+    for (unsigned int vi = blockIdx.x * blockDim.x + threadIdx.x; vi < n * kFixSpread; vi += gridDim.x * blockDim.x) {
+        if (vi % kFixSpread) continue;
+        const unsigned int i = vi / kFixSpread;
         const int64_t pix = (int64_t)P.fix_list[i];
         const int band_y = (int)(pix / W);
         const int px = (int)(pix - (int64_t)band_y * W);
@@ -623,6 +628,10 @@ __global__ void __launch_bounds__(kRenderThreads) fixup_kernel(const __grid_cons
             uint8_t* dst = P.out.rgb8 + 3 * pix;
             dst[0] = u.x; dst[1] = u.y; dst[2] = u.z;
         }
+        if (P.n_peers > 0) {
+            const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));
+            for (int r = 0; r < P.n_peers; ++r) { uint8_t* dst = P.peer_rgb8[r] + 3 * ((int64_t)py * W + px); dst[0] = u.x; dst[1] = u.y; dst[2] = u.z; }
+        }
         if (P.out.prim_id) P.out.prim_id[pix] = prim0;
         if (P.out.light_mask) P.out.light_mask[pix] = lmask0;
         n_prim += (uint32_t)aa;
@@ -633,6 +642,22 @@ __global__ void __launch_bounds__(kRenderThreads) fixup_kernel(const __grid_cons
     for (int k = 0; k < kStatCount; ++k) {
         const uint32_t t = __reduce_add_sync(kFullMask, v[k]);
         if (lane == 0 && t) atomicAdd(&P.stats[k], (unsigned long long)t);
+    }
+    // Frame fence over NVLink (rte_set_fence_peers): this launch runs after the render kernel of the call, whose peer stores
+    // are complete at its end; every thread here makes its own stores visible system-wide, and the last CTA to get here tells
+    // every rank "rank `fence_rank` has delivered frame `seq`" (same protocol as tonemap64_kernel, rte_tonemap.cu).
+    if (P.n_fence > 0) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned int done = atomicAdd(P.fence_counter, 1u);
+            if (done == gridDim.x - 1) {
+                *P.fence_counter = 0u;  // for the next launch (stream order)
+                __threadfence_system();
+                for (int r = 0; r < P.n_fence; ++r)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.fence_flags[r] + P.fence_rank), "r"(P.fence_seq) : "memory");
+            }
+        }
     }
 }
 

@@ -168,10 +168,13 @@ __device__ __forceinline__ void grid_view_sphere(const GridBuildParams& B, int j
     // |r| (+ bias for a light's grid: the shadow line passes the light within `bias`), + the lateral reach of an FP32 direction
     r = (fabs(s.w) + (j > 0 ? B.bias : 0.0)) * (1.0 + 1e-9) + 4e-6 * F + 1e-12;
 }
+// One WARP per (view, sphere): the lanes walk the cells of the sphere's rectangles together (a sphere close to a light covers
+// hundreds of cells; one thread issuing that many dependent atomics was 0.4 ms of tail).
 template <bool kFill>
 __global__ void __launch_bounds__(256) grid_build_kernel(const GridBuildParams B) {
-    const int total = B.n_views * B.sc.ns;
-    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+    const int total = B.n_views * B.sc.ns, lane = threadIdx.x & 31;
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < total; t += warps) {
         const int j = t / B.sc.ns, i = t - j * B.sc.ns;
         double fx, fy, fz, r;
         grid_view_sphere(B, j, i, fx, fy, fz, r);
@@ -181,62 +184,92 @@ __global__ void __launch_bounds__(256) grid_build_kernel(const GridBuildParams B
             const uint32_t pos = B.cell_start[cell] + (atomicSub(B.count + cell, 1u) - 1u);
             if (pos < B.capacity) B.entries[pos] = (uint32_t)i;
         };
-        if (grid_sphere_is_near(fx, fy, fz, r)) { add(base + (uint32_t)(6 * B.G * B.G)); continue; }
+        if (grid_sphere_is_near(fx, fy, fz, r)) { if (lane == 0) add(base + (uint32_t)(6 * B.G * B.G)); continue; }
         for (int face = 0; face < 6; ++face) {
             GridRect rc;
-            if (!grid_rect(B.G, face, fx, fy, fz, r, rc)) continue;
-            for (int iv = rc.iv0; iv <= rc.iv1; ++iv)
-                for (int iu = rc.iu0; iu <= rc.iu1; ++iu) add(base + (uint32_t)(face * B.G * B.G + iv * B.G + iu));
+            if (!grid_rect(B.G, face, fx, fy, fz, r, rc)) continue;  // (warp-uniform: every lane computes the same rectangle)
+            const int w = rc.iu1 - rc.iu0 + 1, n = w * (rc.iv1 - rc.iv0 + 1);
+            for (int c = lane; c < n; c += 32) {
+                const int iv = rc.iv0 + c / w, iu = rc.iu0 + c % w;
+                add(base + (uint32_t)(face * B.G * B.G + iv * B.G + iu));
+            }
         }
     }
-}
-// Exclusive scan of `count` into `cell_start` (one CTA; n_cells is a few hundred thousand); cell_start[n] = total.
-__global__ void __launch_bounds__(1024) grid_scan_kernel(const uint32_t* __restrict__ count, uint32_t* __restrict__ cell_start, int n) {
-    __shared__ uint32_t s_part[1024];
-    __shared__ uint32_t s_carry;
-    if (threadIdx.x == 0) s_carry = 0u;
-    __syncthreads();
-    for (int base = 0; base < n; base += 1024 * 4) {  // 4 consecutive cells per thread: coalesced enough, n / 4096 rounds
-        const int i0 = base + threadIdx.x * 4;
-        uint32_t v[4], sum = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { v[k] = i0 + k < n ? count[i0 + k] : 0u; sum += v[k]; }
-        s_part[threadIdx.x] = sum;
-        __syncthreads();
-        for (int off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan of the per-thread sums
-            const uint32_t add = threadIdx.x >= (unsigned)off ? s_part[threadIdx.x - off] : 0u;
-            __syncthreads();
-            s_part[threadIdx.x] += add;
-            __syncthreads();
-        }
-        uint32_t run = s_carry + s_part[threadIdx.x] - sum;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { if (i0 + k < n) cell_start[i0 + k] = run; run += v[k]; }
-        __syncthreads();
-        if (threadIdx.x == 1023) s_carry += s_part[1023];
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) cell_start[n] = s_carry;
 }
 
-cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, cudaStream_t stream) {
-    GridBuildParams B{};
-    B.sc = sc; B.cam[0] = cam.pos[0]; B.cam[1] = cam.pos[1]; B.cam[2] = cam.pos[2]; B.bias = bias;
-    B.G = G; B.cells_per_view = 6 * G * G + 1; B.n_views = 1 + sc.nl;
-    B.count = count; B.cell_start = cell_start; B.entries = nullptr; B.capacity = 0;
-    const int total = B.n_views * sc.ns, n_cells = B.n_views * B.cells_per_view;
-    if (total > 0) grid_build_kernel<false><<<(total + 255) / 256, 256, 0, stream>>>(B);
-    grid_scan_kernel<<<1, 1024, 0, stream>>>(count, cell_start, n_cells);
-    return cudaGetLastError();
+// Exclusive scan of `count` into `cell_start`, cell_start[n] = total.  Block b scans cells [b, b + 1) * kScanChunk locally,
+// publishes its total tagged with the build's epoch (no reset between builds), adds the totals of the blocks before it
+// (they all run at the same time: the grid is far smaller than one wave) and writes its offsets.
+constexpr int kScanThreads = 256, kScanPer = 16, kScanChunk = kScanThreads * kScanPer;
+__global__ void __launch_bounds__(kScanThreads) grid_scan_kernel(const uint32_t* __restrict__ count, uint32_t* __restrict__ cell_start, int n,
+                                                                 unsigned long long* aggregates, uint32_t epoch) {
+    __shared__ uint32_t s_warp[kScanThreads / 32];
+    __shared__ uint32_t s_prefix;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int i0 = blockIdx.x * kScanChunk + threadIdx.x * kScanPer;
+    uint32_t v[kScanPer], sum = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPer; k += 4) {
+        uint4 q = make_uint4(0u, 0u, 0u, 0u);
+        if (i0 + k + 3 < n) q = *reinterpret_cast<const uint4*>(count + i0 + k);
+        else { if (i0 + k < n) q.x = count[i0 + k]; if (i0 + k + 1 < n) q.y = count[i0 + k + 1]; if (i0 + k + 2 < n) q.z = count[i0 + k + 2]; }
+        v[k] = q.x; v[k + 1] = q.y; v[k + 2] = q.z; v[k + 3] = q.w;
+        sum += q.x + q.y + q.z + q.w;
+    }
+    uint32_t inc = sum;  // inclusive scan of the per-thread sums: warp shuffles, then the warp totals
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    uint32_t woff = 0, btotal = 0;
+#pragma unroll
+    for (int k = 0; k < kScanThreads / 32; ++k) { const uint32_t t = s_warp[k]; if (k < warp) woff += t; btotal += t; }
+    if (threadIdx.x == 0) {
+        const unsigned long long tagged = ((unsigned long long)epoch << 32) | btotal;
+        asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(aggregates + blockIdx.x), "l"(tagged) : "memory");
+        s_prefix = 0u;
+    }
+    __syncthreads();
+    uint32_t part = 0;  // totals of the blocks before this one
+    for (int k = threadIdx.x; k < (int)blockIdx.x; k += kScanThreads) {
+        unsigned long long a;
+        do {  // (volatile: a plain load may legally be read once and the loop assumed to end)
+            asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(a) : "l"(aggregates + k) : "memory");
+        } while ((uint32_t)(a >> 32) != epoch);
+        part += (uint32_t)a;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xFFFFFFFFu, part, o);
+    if (lane == 0 && part) atomicAdd(&s_prefix, part);
+    __syncthreads();
+    uint32_t run = s_prefix + woff + inc - sum;
+#pragma unroll
+    for (int k = 0; k < kScanPer; ++k) { if (i0 + k < n) cell_start[i0 + k] = run; run += v[k]; }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == kScanThreads - 1) cell_start[n] = s_prefix + btotal;
 }
-cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
-                             uint32_t capacity, cudaStream_t stream) {
+
+static GridBuildParams grid_params(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
+                                   uint32_t capacity) {
     GridBuildParams B{};
     B.sc = sc; B.cam[0] = cam.pos[0]; B.cam[1] = cam.pos[1]; B.cam[2] = cam.pos[2]; B.bias = bias;
     B.G = G; B.cells_per_view = 6 * G * G + 1; B.n_views = 1 + sc.nl;
     B.count = count; B.cell_start = cell_start; B.entries = entries; B.capacity = capacity;
+    return B;
+}
+int grid_scan_blocks(int n_cells) { return (n_cells + kScanChunk - 1) / kScanChunk; }
+cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start,
+                                   unsigned long long* aggregates, uint32_t epoch, cudaStream_t stream) {
+    const GridBuildParams B = grid_params(sc, cam, bias, G, count, cell_start, nullptr, 0);
+    const int total = B.n_views * sc.ns, n_cells = B.n_views * B.cells_per_view;
+    if (total > 0) grid_build_kernel<false><<<(total + 7) / 8, 256, 0, stream>>>(B);
+    grid_scan_kernel<<<grid_scan_blocks(n_cells), kScanThreads, 0, stream>>>(count, cell_start, n_cells, aggregates, epoch);
+    return cudaGetLastError();
+}
+cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
+                             uint32_t capacity, cudaStream_t stream) {
+    const GridBuildParams B = grid_params(sc, cam, bias, G, count, cell_start, entries, capacity);
     const int total = B.n_views * sc.ns;
-    if (total > 0) grid_build_kernel<true><<<(total + 255) / 256, 256, 0, stream>>>(B);
+    if (total > 0) grid_build_kernel<true><<<(total + 7) / 8, 256, 0, stream>>>(B);
     return cudaGetLastError();
 }
 
@@ -515,23 +548,25 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
                 if (P.out.light_mask) P.out.light_mask[pix] = lmask;
             }
         }
-        if (P.out.rgb8) {
+        if (P.out.rgb8 || P.n_peers > 0) {
             const uint32_t rgb = tonemap_rgb24(P.tonemap_op, cr, cg, cb, K);
             const bool row_full = (tx + 1) * kTile32W <= W && band_y < rows;  // (uniform over the 8 lanes of a tile row)
+            const int64_t ipix = (int64_t)py * W + px;                           // position in a full frame (peer frames hold the whole image)
             if (words) {
                 // bytes 4 lx .. 4 lx + 3 of the row's 24: pixel q = 4 lx / 3 from its byte o = 4 lx % 3 on, then pixel q + 1
                 const int q = lx < 6 ? (4 * lx) / 3 : 6, o = lx < 6 ? (4 * lx) % 3 : 0;
                 const uint32_t a = __shfl_sync(kFullMask, rgb, (lane & ~7) + q), b = __shfl_sync(kFullMask, rgb, (lane & ~7) + q + 1);
                 const uint32_t word = o == 0 ? (a | (b << 24)) : o == 1 ? ((a >> 8) | (b << 16)) : ((a >> 16) | (b << 8));
-                if (row_full) {
-                    if (lx < 6) __stcs(reinterpret_cast<uint32_t*>(P.out.rgb8 + 3 * ((int64_t)band_y * W + tx * kTile32W)) + lx, word);
-                } else if (mine) {
-                    uint8_t* d = P.out.rgb8 + 3 * pix;
-                    d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+                if (row_full && lx < 6) {
+                    if (P.out.rgb8) __stcs(reinterpret_cast<uint32_t*>(P.out.rgb8 + 3 * ((int64_t)band_y * W + tx * kTile32W)) + lx, word);
+                    for (int i = 0; i < P.n_peers; ++i)
+                        __stcs(reinterpret_cast<uint32_t*>(P.peer_rgb8[i] + 3 * ((int64_t)py * W + tx * kTile32W)) + lx, word);
                 }
-            } else if (mine) {
-                uint8_t* d = P.out.rgb8 + 3 * pix;
-                d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
+            }
+            if (mine && !(words && row_full)) {
+                const uint8_t b0 = (uint8_t)rgb, b1 = (uint8_t)(rgb >> 8), b2 = (uint8_t)(rgb >> 16);
+                if (P.out.rgb8) { uint8_t* d = P.out.rgb8 + 3 * pix; d[0] = b0; d[1] = b1; d[2] = b2; }
+                for (int i = 0; i < P.n_peers; ++i) { uint8_t* d = P.peer_rgb8[i] + 3 * ipix; d[0] = b0; d[1] = b1; d[2] = b2; }
             }
         }
         // ---- pixels with an inconclusive decision: appended to the fix-up list (one atomic per tile that has any)
