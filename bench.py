@@ -31,7 +31,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 _OUT = sys.stdout
-METRIC = "Mrays/s (primary+shadow) at 3840x2160"
+METRIC = "Mrays/s (primary+shadow) at 3840x2160"  # (the reference arm; the GPU arm names its own frame size)
 UNIT = "Mrays/s"
 
 
@@ -202,7 +202,7 @@ def run_reference(args) -> None:
     frame_rays_est = rays * (cam.height / max(1, r["rows"]))
     sample = f"every {row_step}th row ({r['rows']} of {cam.height} rows, {rays} rays) per step; RenderImage (OpenMP, all host threads) + ACES tonemap (serial, as upstream)"
     line = {
-        "impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": f"Mrays/s (primary+shadow) at {cam.width}x{cam.height}", "value": round(value, 4), "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(total / len(times) * 1e3, 3), "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": label, "width": cam.width, "height": cam.height, **arrays.counts(), "seed": 1234,
@@ -216,12 +216,256 @@ def run_reference(args) -> None:
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
+def frame_crc_golden(name: str):
+    """CRC-32 of the reference build's RGB8 frame of a workload at its named size (tools/make_frame_crc.py), or None."""
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "frame_crc.json")) as f:
+            return json.load(f).get(name)
+    except (OSError, ValueError):
+        return None
+
+
+def ncu_kernels():
+    """Per-kernel hardware figures of the newest committed ncu capture (profiles/*_kernels.json, tools/profile_summary.py)."""
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_kernels.json")), reverse=True):
+        try:
+            with open(path) as f:
+                return json.load(f), os.path.relpath(path, ROOT)
+        except (OSError, ValueError):
+            continue
+    return None, None
+
+
+class Pipeline:
+    """One workload on this rank: engine, row assignment, output buffers, N>1 output exchange, one `step()`."""
+
+    def __init__(self, args, name, torch, dist, dev, rank, world, local_rank, stream):
+        import numpy as np
+        from raytracingengine_b200 import _abi
+        from raytracingengine_b200.engine import Engine
+        self.np, self.torch, self.dist, self.abi = np, torch, dist, _abi
+        self.args, self.name, self.rank, self.world, self.dev = args, name, rank, world, dev
+        self.arrays, self.cam, self.label = workload(name, args.scale)
+        W, H = self.cam.width, self.cam.height
+        self.W, self.H = W, H
+        self.tm_op = _abi.TM_ACES if name != "c5" else _abi.TM_REINHARD_EXT_LUM
+        self.stripe = args.stripe if args.stripe > 0 else (16 if name == "c5" else 8)
+        self.eng = Engine(local_rank)
+        self.eng.set_stream(stream.cuda_stream)  # the library enqueues on torch's current stream: torch events and NCCL see its work
+        self.eng.upload(self.arrays, self.cam)
+        if world == 1:
+            self.ropts = dict(row0=0, row1=H)
+        else:
+            self.ropts = dict(row0=rank * self.stripe, row1=H, stripe_rows=self.stripe, stripe_period=world * self.stripe)
+        self.my_rows = Engine.striped_rows(self.ropts["row0"], H, self.ropts.get("stripe_rows", 0), self.ropts.get("stripe_period", 0)) if self.ropts["row0"] < H else 0
+        self.rows_max = self.my_rows
+        if dist is not None:
+            t = torch.tensor([self.my_rows], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            self.rows_max = int(t.item())
+        self.hdr = torch.empty((max(self.my_rows, 1) * W, 4), dtype=torch.float32, device=dev)
+        self.rgb_local = torch.zeros((self.rows_max * W * 3,), dtype=torch.uint8, device=dev)
+        self.rgb_all = torch.empty((world * self.rows_max * W * 3,), dtype=torch.uint8, device=dev) if world > 1 else None
+        self.auto_white = name == "c5" and args.auto_white
+        self.gather = "none" if dist is None else ("nccl" if self.auto_white else args.gather)
+        self.use_flag_fence, self.peer_note, self.frame_all, self.opened = False, "", 0, []
+        if self.gather == "peer":
+            self._setup_peers()
+        self.fence = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.white = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.tm_ptrs = [self.rgb_local.data_ptr() if op == self.tm_op else None for op in range(_abi.TM_COUNT)]
+
+    def _exchange(self, ptr):
+        """Every rank's device buffer `ptr` mapped into this process: list of device pointers by rank (CUDA IPC)."""
+        torch, dist, _abi = self.torch, self.dist, self.abi
+        mine = torch.frombuffer(bytearray(self.eng.ipc_export(ptr)), dtype=torch.uint8).to(self.dev)
+        handles = torch.empty(self.world * _abi.IPC_HANDLE_BYTES, dtype=torch.uint8, device=self.dev)
+        dist.all_gather_into_tensor(handles, mine)
+        handles = handles.cpu().numpy().reshape(self.world, _abi.IPC_HANDLE_BYTES)
+        out = []
+        for r in range(self.world):
+            if r == self.rank:
+                out.append(ptr)
+            else:
+                self.opened.append(self.eng.ipc_open(handles[r].tobytes()))
+                out.append(self.opened[-1])
+        return out
+
+    def _setup_peers(self):
+        # "peer": every rank's render call stores its RGB8 stripes straight into the full-frame buffer of EVERY rank over NVLink
+        # (rte_set_rgb8_peers; buffers exchanged as CUDA IPC handles); the frame is fenced by flags written over NVLink by the
+        # same call (rte_frame_fence) or by a 4-byte NCCL all-reduce
+        torch, dist, _abi = self.torch, self.dist, self.abi
+        try:
+            self._peer_frames, self._peer_flags = None, None
+            self.frame_all = self.eng.malloc(self.W * self.H * 3)
+            self._peer_frames = self._exchange(self.frame_all)
+            self.eng.set_rgb8_peers(self._peer_frames)
+            if self.args.fence == "flags":
+                self._peer_flags = self._exchange(self.eng.malloc(4 * _abi.MAX_PEERS))
+                self.eng.set_fence_peers(self.rank, self._peer_flags)
+                self.use_flag_fence = True
+            ok = torch.ones(1, device=self.dev)
+        except Exception as exc:  # no peer mapping on this box: say so and use the NCCL all-gather
+            self.peer_note = f" (peer frames unavailable: {exc})"
+            ok = torch.zeros(1, device=self.dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if ok.item() < 1:
+            self.eng.set_rgb8_peers([])
+            if self.use_flag_fence:
+                self.eng.set_fence_peers(self.rank, [])
+            self.use_flag_fence = False
+            self.gather = "nccl"
+        dist.barrier()  # every rank has zeroed its flags before anybody renders
+
+    def step(self, flags=0):
+        eng, dist, W = self.eng, self.dist, self.W
+        if self.auto_white:
+            # C5's auto max-white pipeline (SURVEY §8(e)): HDR stripes -> per-rank max luminance (device float) ->
+            # NCCL all-reduce MAX -> Reinhard-extended-luminance with that white point -> NCCL all-gather of RGB8
+            eng.render_device({"hdr": self.hdr.data_ptr()}, flags=flags, **self.ropts)
+            eng.max_luminance_device(self.hdr.data_ptr(), self.my_rows * W, self.white.data_ptr())
+            if dist is not None:
+                dist.all_reduce(self.white, op=dist.ReduceOp.MAX)
+            eng.tonemap_auto_white(self.hdr.data_ptr(), self.my_rows * W, self.tm_ptrs, self.white.data_ptr(), ops=[self.tm_op])
+        elif self.gather == "peer":
+            eng.render_device({"hdr": self.hdr.data_ptr()}, tonemap_op=self.tm_op, flags=flags, **self.ropts)  # RGB8 goes to every rank's frame
+            if self.use_flag_fence:
+                eng.frame_fence()            # device-side wait for every rank's "frame delivered" flag (written over NVLink)
+            else:
+                dist.all_reduce(self.fence)  # frame fence across ranks through NCCL
+            return
+        else:
+            eng.render_device({"hdr": self.hdr.data_ptr(), "rgb8": self.rgb_local.data_ptr()}, tonemap_op=self.tm_op, flags=flags, **self.ropts)
+        if dist is not None:  # the RGB8 stripes of every rank, into the PPM writer's buffer (de-interleaved at write time)
+            dist.all_gather_into_tensor(self.rgb_all, self.rgb_local)
+
+    def frame_check(self):
+        """Untimed: (1) the frame of the EXACT path (RTE_FLAG_EXACT_FP64, fixed max_white) assembled from all ranks has the CRC-32
+        of the reference build's frame (tests/golden/frame_crc.json); (2) the production path's frame is within 1 LSB of it;
+        (3) N>1: what the peer stores assemble is what an all-gather of the same stripes assembles."""
+        import zlib
+        np, torch, dist, eng, _abi = self.np, self.torch, self.dist, self.eng, self.abi
+        from raytracingengine_b200 import sharding
+        W, H = self.W, self.H
+        res = {"frame_ok": None, "frame_lsb_max": None}
+
+        def assembled(flags):
+            eng.render_device({"rgb8": self.rgb_local.data_ptr()}, tonemap_op=self.tm_op, flags=flags, **self.ropts)
+            if dist is None:
+                torch.cuda.synchronize()
+                return self.rgb_local[:self.my_rows * W * 3].cpu().numpy().reshape(-1, 3)
+            dist.all_gather_into_tensor(self.rgb_all, self.rgb_local)
+            torch.cuda.synchronize()
+            if self.rank != 0:
+                return None
+            return sharding.deinterleave(self.rgb_all.cpu().numpy().reshape(-1, 3), self.world, H, W, self.stripe, self.rows_max)
+
+        if self.gather == "peer":
+            eng.set_rgb8_peers([])  # the checks below want each rank's stripes in its own buffer
+            if self.use_flag_fence:
+                eng.set_fence_peers(self.rank, [])
+        exact = assembled(_abi.FLAG_EXACT_FP64)
+        prod = assembled(0)
+        if self.gather == "peer":
+            self._reregister()
+            self.step()
+            torch.cuda.synchronize()
+            dist.barrier()
+        if self.rank == 0:
+            gold = frame_crc_golden(self.name) if self.args.scale == 1.0 else None
+            if gold and (gold["width"], gold["height"]) == (W, H):
+                res["frame_ok"] = bool(zlib.crc32(exact.tobytes()) == gold["crc32"])
+                res["frame_crc32"] = zlib.crc32(exact.tobytes())
+            res["frame_lsb_max"] = int(np.abs(prod.astype(np.int16) - exact.astype(np.int16)).max())
+            if self.gather == "peer":
+                got = np.zeros((H * W, 3), np.uint8)
+                eng.d2h(got, self.frame_all)
+                res["peer_frame_equals_gather"] = bool(np.array_equal(got, prod))
+        return res
+
+    def _reregister(self):
+        """Peer frames / flags again after frame_check() or the e2e leg unregistered them (pointers are still mapped)."""
+        self.eng.set_rgb8_peers(self._peer_frames)
+        if self._peer_flags:
+            self.eng.set_fence_peers(self.rank, self._peer_flags)
+            self.dist.barrier()
+
+    def close(self):
+        if self.opened:
+            self.eng.set_rgb8_peers([])
+            if self.use_flag_fence:
+                self.eng.set_fence_peers(self.rank, [])
+            for p in self.opened:
+                self.eng.ipc_close(p)
+        self.eng.close()
+
+
+def measure(pipe, steps, warmup, flush, stream):
+    """W warm-ups, then K timed steps: CUDA events per step on the launching stream (L2 flushed between steps, outside the
+    event pair), barrier + synchronize on both sides, max over ranks."""
+    torch, dist, eng = pipe.torch, pipe.dist, pipe.eng
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    for _ in range(max(warmup, 3)):
+        flush.zero_()
+        pipe.step()
+    sync_all()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    kernel_ms = []
+    wall0 = time.perf_counter()
+    for i in range(steps):
+        flush.zero_()
+        ev[i][0].record(stream)
+        pipe.step()
+        ev[i][1].record(stream)
+        if pipe.world == 1:
+            kernel_ms.append(eng.stats()["kernel_ms"])  # (synchronises) device time of the library's own launches of this step
+    sync_all()
+    wall = time.perf_counter() - wall0
+    launches = eng.last_render_launches()
+    st = eng.stats()
+    if pipe.world > 1:
+        kernel_ms = [st["kernel_ms"]]
+    my_ms = sum(a.elapsed_time(b) for a, b in ev)
+    k_mean = sum(kernel_ms) / len(kernel_ms)
+    counters = torch.tensor([st["primary_rays"] + st["shadow_rays"], st["sphere_tests"], st["plane_tests"], st["triangle_tests"],
+                             st["fp64_confirms"], st["exact_marches"], st["sphere_tests_executed"]], dtype=torch.float64, device=pipe.dev)
+    tmax = torch.tensor([my_ms, k_mean, -k_mean], dtype=torch.float64, device=pipe.dev)
+    if dist is not None:
+        dist.all_reduce(counters, op=dist.ReduceOp.SUM)
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    rays, sph_t, pl_t, tri_t, confirms, marches, sph_exec = [float(x) for x in counters.tolist()]
+    total_ms, k_max, k_min_neg = [float(x) for x in tmax.tolist()]
+    ms = total_ms / steps
+    return {"ms_per_step": ms, "value": rays / (ms * 1e-3) / 1e6, "rays": rays, "tests": (sph_t, pl_t, tri_t), "fixup_pixels": confirms,
+            "marches": marches, "candidates": sph_exec, "kernel_ms_max": k_max, "kernel_ms_min": -k_min_neg, "launches": launches,
+            "wall_ms": wall / steps * 1e3}
+
+
+def sharding_text(pipe):
+    if pipe.world == 1:
+        return "single band"
+    s = f"interleaved {pipe.stripe}-row stripes; "
+    if pipe.gather == "peer":
+        return s + "RGB8 stored by the render kernel into every rank's frame over NVLink while it traces (CUDA IPC peer frames) + " + (
+            "frame fence through NVLink flags written by the call's last launch (rte_frame_fence), no collective" if pipe.use_flag_fence
+            else "4-byte NCCL all-reduce as frame fence")
+    return s + "NCCL all-gather of RGB8" + pipe.peer_note
+
+
 def run_gpu(args) -> None:
     import numpy as np
     import torch
 
     from raytracingengine_b200 import _abi
-    from raytracingengine_b200.engine import Engine, PinnedBuffer
+    from raytracingengine_b200.engine import PinnedBuffer
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -238,219 +482,75 @@ def run_gpu(args) -> None:
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
-
-    arrays, cam, label = workload(args.workload, args.scale)
-    W, H = cam.width, cam.height
-    tm_op = _abi.TM_ACES if args.workload != "c5" else 3
-    eng = Engine(local_rank)
     stream = torch.cuda.Stream(device=dev)  # a real (non-default) stream: handle 0 would mean "ctx-private" to the library
     torch.cuda.set_stream(stream)
-    eng.set_stream(stream.cuda_stream)  # the library enqueues on torch's current stream: torch events and NCCL see its work
-    eng.upload(arrays, cam)
-
-    # ---- row assignment: the whole frame at N=1; interleaved stripes of `--stripe` rows at N>1, one launch per rank
-    if world == 1:
-        ropts = dict(row0=0, row1=H)
-    else:
-        ropts = dict(row0=rank * args.stripe, row1=H, stripe_rows=args.stripe, stripe_period=world * args.stripe)
-    my_rows = Engine.striped_rows(ropts["row0"], H, ropts.get("stripe_rows", 0), ropts.get("stripe_period", 0)) if ropts["row0"] < H else 0
-    rows_max = my_rows
-    if dist is not None:
-        t = torch.tensor([my_rows], device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        rows_max = int(t.item())
-    hdr = torch.empty((max(my_rows, 1) * W, 4), dtype=torch.float32, device=dev)
-    rgb_local = torch.zeros((rows_max * W * 3,), dtype=torch.uint8, device=dev)
-    rgb_all = torch.empty((world * rows_max * W * 3,), dtype=torch.uint8, device=dev) if world > 1 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
-    auto_white = args.workload == "c5" and not args.fixed_white
-
-    # ---- N>1 output path.  "peer" (default): every rank's render kernel stores its RGB8 stripes straight into the
-    # full-frame buffer of EVERY rank over NVLink (rte_set_rgb8_peers; buffers exchanged as CUDA IPC handles), and a
-    # 4-byte NCCL all-reduce fences the frame.  "nccl": the stripes are all-gathered by NCCL after the kernel.
-    gather = "none" if dist is None else ("nccl" if auto_white else args.gather)
-    use_flag_fence = False
-    peer_note = ""
-    frame_all = 0
-    opened = []
-    if gather == "peer":
-        try:
-            frame_all = eng.malloc(W * H * 3)
-            mine = torch.frombuffer(bytearray(eng.ipc_export(frame_all)), dtype=torch.uint8).to(dev)
-            handles = torch.empty(world * _abi.IPC_HANDLE_BYTES, dtype=torch.uint8, device=dev)
-            dist.all_gather_into_tensor(handles, mine)
-            handles = handles.cpu().numpy().reshape(world, _abi.IPC_HANDLE_BYTES)
-            frames = []
-            for r in range(world):
-                if r == rank:
-                    frames.append(frame_all)
-                else:
-                    opened.append(eng.ipc_open(handles[r].tobytes()))
-                    frames.append(opened[-1])
-            eng.set_rgb8_peers(frames)
-            if args.fence == "flags":
-                # frame fence without NCCL: every rank's flag array mapped into every rank like the frames (rte_set_fence_peers)
-                my_flags = eng.malloc(4 * _abi.MAX_PEERS)
-                mine = torch.frombuffer(bytearray(eng.ipc_export(my_flags)), dtype=torch.uint8).to(dev)
-                fh = torch.empty(world * _abi.IPC_HANDLE_BYTES, dtype=torch.uint8, device=dev)
-                dist.all_gather_into_tensor(fh, mine)
-                fh = fh.cpu().numpy().reshape(world, _abi.IPC_HANDLE_BYTES)
-                flags = []
-                for r in range(world):
-                    if r == rank:
-                        flags.append(my_flags)
-                    else:
-                        opened.append(eng.ipc_open(fh[r].tobytes()))
-                        flags.append(opened[-1])
-                eng.set_fence_peers(rank, flags)
-                use_flag_fence = True
-            ok = torch.ones(1, device=dev)
-        except Exception as exc:  # no peer mapping on this box: say so and use the NCCL all-gather
-            peer_note = f" (peer frames unavailable: {exc})"
-            ok = torch.zeros(1, device=dev)
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        if ok.item() < 1:
-            eng.set_rgb8_peers([])
-            if use_flag_fence:
-                eng.set_fence_peers(rank, [])
-            use_flag_fence = False
-            gather = "nccl"
-        dist.barrier()  # every rank has zeroed its flags before anybody renders
-    fence = torch.zeros(1, dtype=torch.float32, device=dev)
-    white = torch.zeros(1, dtype=torch.float32, device=dev)
-    tm_ptrs = [rgb_local.data_ptr() if op == tm_op else None for op in range(_abi.TM_COUNT)]
-
-    def render_step():
-        if auto_white:
-            # C5's auto max-white pipeline: HDR stripes -> per-rank max luminance (device float) ->
-            # NCCL all-reduce MAX -> Reinhard-extended-luminance with that white point -> NCCL all-gather of RGB8
-            eng.render_device({"hdr": hdr.data_ptr()}, **ropts)
-            eng.max_luminance_device(hdr.data_ptr(), my_rows * W, white.data_ptr())
-            if dist is not None:
-                dist.all_reduce(white, op=dist.ReduceOp.MAX)
-            eng.tonemap_auto_white(hdr.data_ptr(), my_rows * W, tm_ptrs, white.data_ptr(), ops=[tm_op])
-        elif gather == "peer":
-            eng.render_device({"hdr": hdr.data_ptr()}, tonemap_op=tm_op, **ropts)  # RGB8 goes to every rank's frame
-            if use_flag_fence:
-                eng.frame_fence()            # device-side wait for every rank's "frame delivered" flag (written over NVLink)
-            else:
-                dist.all_reduce(fence)       # frame fence across ranks through NCCL
-            return
-        else:
-            eng.render_device({"hdr": hdr.data_ptr(), "rgb8": rgb_local.data_ptr()}, tonemap_op=tm_op, **ropts)
-        if dist is not None:  # the RGB8 stripes of every rank, into the PPM writer's buffer (de-interleaved at write time)
-            dist.all_gather_into_tensor(rgb_all, rgb_local)
-
-    if gather == "peer":
-        # one untimed check: the frame the peer stores assemble == the frame NCCL's all-gather assembles
-        from raytracingengine_b200 import sharding
-        render_step()
-        torch.cuda.synchronize()
-        eng.render_device({"hdr": hdr.data_ptr(), "rgb8": rgb_local.data_ptr()}, tonemap_op=tm_op, **ropts)
-        dist.all_gather_into_tensor(rgb_all, rgb_local)
-        torch.cuda.synchronize()
-        if rank == 0:
-            got = np.zeros((H * W, 3), np.uint8)
-            eng.d2h(got, frame_all)
-            want = sharding.deinterleave(rgb_all.cpu().numpy().reshape(-1, 3), world, H, W, args.stripe, rows_max)
-            if not np.array_equal(got, want):
-                raise SystemExit("bench.py: peer-stored frame differs from the NCCL all-gather of the same stripes")
-
-    def sync_all():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-            torch.cuda.synchronize()
-
+    pipe = Pipeline(args, args.workload, torch, dist, dev, rank, world, local_rank, stream)
+    arrays, cam, W, H, eng = pipe.arrays, pipe.cam, pipe.W, pipe.H, pipe.eng
+    check = pipe.frame_check()
     fp32_peak_tf, _ = eng.measure_fp32_peak(15.0)
-    fp32x2_peak_tf, _ = eng.measure_fp32_peak(15.0, packed=True)
-
-    for _ in range(max(args.warmup, 3)):
-        flush.zero_()
-        render_step()
-    sync_all()
-    st0 = eng.stats()
-
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    kernel_ms = []
     sampler = ClockSampler(visible_index(local_rank))
-    sync_all()
-    wall0 = time.perf_counter()
     with sampler:
-        for i in range(args.steps):
-            flush.zero_()              # L2 flush between timed iterations (outside the event pair)
-            ev[i][0].record(stream)
-            render_step()
-            ev[i][1].record(stream)
-            if world == 1:
-                kernel_ms.append(eng.stats()["kernel_ms"])  # syncs; per-launch time of the render kernel alone
-        sync_all()
-    wall = time.perf_counter() - wall0
-    launches_per_render = eng.last_render_launches()  # rte_render of the last timed step: render launch(es) + the RGB8 pass
-    step_ms = [a.elapsed_time(b) for a, b in ev]
-    my_ms = sum(step_ms)
-    st = eng.stats()
-    if world > 1:
-        kernel_ms = [st["kernel_ms"]]
-    counters = torch.tensor([st["primary_rays"] + st["shadow_rays"], st["sphere_tests"], st["plane_tests"], st["triangle_tests"],
-                             st["fp64_confirms"], st["exact_marches"], st["sphere_tests_executed"]], dtype=torch.float64, device=dev)
-    tmax = torch.tensor([my_ms, sum(kernel_ms) / len(kernel_ms)], dtype=torch.float64, device=dev)
-    if dist is not None:
-        dist.all_reduce(counters, op=dist.ReduceOp.SUM)
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-    rays, sph_t, pl_t, tri_t, confirms, marches, sph_exec = [float(x) for x in counters.tolist()]
-    total_ms, kern_ms = [float(x) for x in tmax.tolist()]
-    ms_per_step = total_ms / args.steps
-    value = rays / (ms_per_step * 1e-3) / 1e6
+        m = measure(pipe, args.steps, args.warmup, flush, stream)
 
     # ---- e2e: C-ABI with HOST buffers — scene description H2D (rte_upload_scene) + render + RGB8 D2H, wall clock
-    pin = PinnedBuffer(max(my_rows, 1) * W * 3)
-    host_rgb = pin.view(np.uint8, (max(my_rows, 1) * W, 3))
+    pin = PinnedBuffer(max(pipe.my_rows, 1) * W * 3)
+    host_rgb = pin.view(np.uint8, (max(pipe.my_rows, 1) * W, 3))
     scene_bytes = sum(a.nbytes for a in (arrays.materials, arrays.spheres, arrays.planes, arrays.triangles, arrays.models,
                                          arrays.model_vertices, arrays.model_indices, arrays.lights))
-
-    if opened or frame_all:
-        sync_all()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    if pipe.gather == "peer":
         eng.set_rgb8_peers([])  # the end-to-end leg returns each rank's stripes to its own host buffer
-        if use_flag_fence:
+        if pipe.use_flag_fence:
             eng.set_fence_peers(rank, [])
 
     def e2e_step():
         eng.upload(arrays, cam)
-        eng.render_host(outputs=("rgb8",), into={"rgb8": host_rgb}, tonemap_op=tm_op, **ropts)
+        eng.render_host(outputs=("rgb8",), into={"rgb8": host_rgb}, tonemap_op=pipe.tm_op, **pipe.ropts)
 
-    for _ in range(2):
+    for _ in range(3):
         e2e_step()
-    sync_all()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
     e0 = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
     torch.cuda.synchronize()
-    e_ms = (time.perf_counter() - e0) * 1e3
-    te = torch.tensor([e_ms], dtype=torch.float64, device=dev)
+    te = torch.tensor([(time.perf_counter() - e0) * 1e3], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_ms = float(te.item()) / args.steps
-    e2e_value = rays / (e2e_ms * 1e-3) / 1e6
+    e2e_value = m["rays"] / (e2e_ms * 1e-3) / 1e6
 
     # ---- the HBM-bound pass of the path: all seven tonemap operators over the (band) HDR buffer (C3's pass)
-    n_px = my_rows * W
+    n_px = pipe.my_rows * W
     tm_out = [torch.empty(n_px * 3 + 16, dtype=torch.uint8, device=dev) for _ in range(_abi.TM_COUNT)]
     tm_ms = []
-    hdr2 = hdr.clone()  # two rotating inputs: 2 x 133 MB in + 174 MB out per launch stream through the 126 MB L2 (no flush needed)
+    hdr2 = pipe.hdr.clone()  # two rotating inputs: 2 x 133 MB in + 174 MB out per launch stream through the 126 MB L2 (no flush needed)
     for i in range(3 + 20):
-        eng.tonemap_device((hdr if i % 2 else hdr2).data_ptr(), n_px, [t.data_ptr() for t in tm_out])
+        eng.tonemap_device((pipe.hdr if i % 2 else hdr2).data_ptr(), n_px, [t.data_ptr() for t in tm_out])
         if i >= 3:
             tm_ms.append(eng.stats()["tonemap_ms"])
     tm_med = sorted(tm_ms)[len(tm_ms) // 2]
+    del tm_out, hdr2
+    pipe.close()
 
-    if opened:
-        sync_all()
-        eng.set_rgb8_peers([])
-        for p in opened:
-            eng.ipc_close(p)
-        sync_all()
+    # ---- the north star's scaling target in the same run: C5 at 7680x4320 (4096 spheres, 8 lights, Reinhard-extended-luminance
+    # with the reference's constant max_white = 5.0), fewer steps
+    c5 = None
+    if args.workload != "c5" and not args.no_c5 and args.scale == 1.0:
+        p5 = Pipeline(args, "c5", torch, dist, dev, rank, world, local_rank, stream)
+        chk5 = p5.frame_check()
+        m5 = measure(p5, max(3, args.steps // 4), 3, flush, stream)
+        c5 = {"workload": p5.label, "ms_per_step": round(m5["ms_per_step"], 4), "value": round(m5["value"], 2), "unit": UNIT,
+              "rays_per_frame": int(m5["rays"]), "kernel_ms_max": round(m5["kernel_ms_max"], 4), "kernel_ms_min": round(m5["kernel_ms_min"], 4),
+              "steps": max(3, args.steps // 4), "sharding": sharding_text(p5), "fixup_pixels": int(m5["fixup_pixels"]), **chk5}
+        p5.close()
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -458,44 +558,49 @@ def run_gpu(args) -> None:
 
     pk, pk_src = peaks()
     clocks = sampler.summary()
-    tr_render, tr_tm = ncu_traffic("render_fast_kernel"), ncu_traffic("tonemap_kernel")
+    kern, kern_src = ncu_kernels()
+    tr_tm = ncu_traffic("tonemap_kernel")
+    sph_t, pl_t, tri_t = m["tests"]
     flops = _abi.algorithmic_flops(sph_t, pl_t, tri_t)           # 20 / 14 / 46 flop per test
-    achieved_tf = flops / world / (kern_ms * 1e-3) / 1e12       # per GPU: per-rank flops / slowest rank's kernel time
-    clk = clocks.get("sm_mhz") or pk.get("sm_max_mhz", 1965.0)
-    nominal_tf = 148 * 128 * 2 * clk * 1e6 / 1e12
+    achieved_tf = flops / world / (m["kernel_ms_max"] * 1e-3) / 1e12   # per GPU: per-rank flops / slowest rank's device time
+    r32 = (kern or {}).get("render32_kernel", {})
     line = {
-        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f32 filter + f64 confirm", "data": "synthetic",
-        "config": {"workload": label, "width": W, "height": H, **arrays.counts(), "seed": 1234 if args.workload != "c5" else 5678,
-                   "rays_per_frame": int(rays), "sharding": "single band" if world == 1 else f"interleaved {args.stripe}-row stripes; " + (
-                       ("RGB8 stored by the render call's tonemap pass into every rank's frame over NVLink (CUDA IPC peer frames) + " + ("frame fence through NVLink flags written by the same kernel (rte_frame_fence), no collective" if use_flag_fence else "4-byte NCCL all-reduce as frame fence"))
-                       if gather == "peer" else "NCCL all-gather of RGB8" + peer_note),
-                   "tonemap": ("auto max-white: max-luminance kernel + " + ("NCCL all-reduce MAX + " if world > 1 else "") + "tonemap pass") if auto_white else "exact FP64 ACES pass over the render kernel's FP64 HDR, inside the same rte_render call",
+        "metric": f"Mrays/s (primary+shadow) at {W}x{H}", "value": round(m["value"], 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(m["ms_per_step"], 4), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32 values, decisions from f32 intervals with an exact f64 fix-up", "data": "synthetic",
+        "config": {"workload": pipe.label, "width": W, "height": H, **arrays.counts(), "seed": 1234 if args.workload != "c5" else 5678,
+                   "rays_per_frame": int(m["rays"]), "sharding": sharding_text(pipe),
+                   "tonemap": ("auto max-white: max-luminance kernel + " + ("NCCL all-reduce MAX + " if world > 1 else "") + "tonemap pass") if pipe.auto_white
+                   else "operator + toColor inside the render kernel (FP32, +-1 LSB of the reference); exact FP64 for the fix-up pixels",
                    "l2": "256 MiB memset between timed steps; outputs (HDR float4 + RGB8 = 19 B/px) exceed L2",
                    "timing": "CUDA events per step on the launching stream, summed, max over ranks"},
-        "ms_per_frame": round(ms_per_step, 4),
-        "wall_ms_per_step_incl_flush": round(wall / args.steps * 1e3, 3),
-        "clocks": clocks,
+        "ms_per_frame": round(m["ms_per_step"], 4), "wall_ms_per_step_incl_flush": round(m["wall_ms"], 3), "clocks": clocks,
+        **check,
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "ms_per_step": round(e2e_ms, 3), "h2d_bytes_per_step": int(scene_bytes),
-                "d2h_bytes_per_step": int(my_rows * W * 3), "api": "rte_upload_scene + rte_render_host (pinned host RGB8)"},
-        # per step and rank: render kernel + exact tonemap pass (auto-white pipeline: render, max-luminance, tonemap); memsets and NCCL are not ours
-        "gpu_launches": args.steps * (launches_per_render + (2 if auto_white else 0)),  # render call (+ max luminance + tonemap for c5); NCCL kernels not counted
-        "roofline": {"bound": "fp32", "kernel": "rte::render_fast_kernel (primary-ray launch + shading launch on big frames; + rte::tonemap64_kernel, ~1 % of the call)", "achieved": round(achieved_tf, 3), "peak": round(fp32_peak_tf, 3),
-                     "unit": "TFLOP/s", "frac": round(achieved_tf / fp32_peak_tf, 4),
-                     "traffic": (tr_render or {}).get("bytes") if args.workload == "c2" and world == 1 else None, "traffic_capture": tr_render,
+                "d2h_bytes_per_step": int(pipe.my_rows * W * 3), "api": "rte_upload_scene + rte_render_host (pinned host RGB8)"},
+        # per step and rank: the library's launches of one render call (render kernel + fix-up launch; + max luminance + tonemap for the
+        # auto-white pipeline); memsets and NCCL are not ours
+        "gpu_launches": args.steps * (m["launches"] + (2 if pipe.auto_white else 0)),
+        "roofline": {"bound": "fp32", "kernel": "rte::render32_kernel (+ rte::fixup_kernel, the exact FP64 re-render of the flagged pixels)",
+                     "achieved": round(achieved_tf, 3), "peak": round(fp32_peak_tf, 3), "unit": "TFLOP/s", "frac": round(achieved_tf / fp32_peak_tf, 4),
+                     "frac_note": "ALGORITHMIC: the reference's 20 flop per ray-sphere test over ALL spheres (SURVEY §8(d)) / time / measured FFMA peak; the "
+                                  "direction grids test ~3 of 1024 spheres per ray, so this is a speed-up over brute force, not a hardware utilisation — "
+                                  "the bounded hardware figures are issue_active_pct / pipe_*_pct below (ncu)",
+                     "algorithmic_tflops": round(achieved_tf, 3), "algorithmic_flop_per_launch": flops / world,
+                     "traffic": r32.get("dram_bytes"), "kernel_ms": round(m["kernel_ms_max"], 4), "kernel_ms_min_rank": round(m["kernel_ms_min"], 4),
+                     "issue_active_pct": r32.get("issue_active_pct"), "pipe_fma_pct": r32.get("pipe_fma_pct"), "pipe_fp64_pct": r32.get("pipe_fp64_pct"),
+                     "pipe_alu_pct": r32.get("pipe_alu_pct"), "pipe_xu_pct": r32.get("pipe_xu_pct"), "ncu_kernels": kern, "ncu_source": kern_src,
                      "peak_source": "FFMA micro-benchmark in this process (rte_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
-                     "nominal_peak_at_sampled_clock": round(nominal_tf, 2), "ffma2_peak": round(fp32x2_peak_tf, 3),
-                     "algorithmic_flop_per_launch": flops / world, "kernel_ms": round(kern_ms, 4),
-                     # the view filter runs 3 FMA-pipe lane-ops (6 flop) per sphere test it really executes: the <= 1 companion of `frac`
-                     "executed_frac": round(6.0 * sph_exec / world / (kern_ms * 1e-3) / 1e12 / fp32_peak_tf, 4), "sphere_tests_executed": sph_exec,
-                     "tests": {"sphere": sph_t, "plane": pl_t, "triangle": tri_t}, "fp64_confirms": confirms, "exact_marches": marches},
+                     "candidates_tested": m["candidates"], "candidates_per_ray": round(m["candidates"] / max(1.0, m["rays"]), 3),
+                     "fixup_pixels": int(m["fixup_pixels"]), "tests": {"sphere": sph_t, "plane": pl_t, "triangle": tri_t}, "exact_marches": m["marches"]},
         "roofline_tonemap": {"bound": "hbm", "kernel": "rte::tonemap_kernel<all 7 operators>", "achieved": round(n_px * 33 / (tm_med * 1e-3) / 1e9, 1),
                              "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(n_px * 33 / (tm_med * 1e-3) / 1e9 / pk["hbm_gbs"], 4),
                              "traffic": (tr_tm or {}).get("bytes") if args.workload in ("c2", "c3") and world == 1 else None, "traffic_capture": tr_tm,
                              "peak_source": pk_src, "algorithmic_bytes_per_launch": n_px * 33, "kernel_ms": round(tm_med, 4),
                              "l2": "input (16 B/px float4, two rotating buffers) and output (21 B/px) exceed L2; no flush"},
     }
+    if c5 is not None:
+        line["c5_8k"] = c5
     if not args.no_cpu_baseline and world == 1:
         orc, row_step = cpu_reference_sample(arrays, cam, args.cpu_seconds)
         r = orc.render(arrays, cam, row_step=row_step, threads=host_threads())
@@ -520,10 +625,9 @@ def main() -> None:
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N>1: how the RGB8 stripes reach every rank")
     ap.add_argument("--fence", default="flags", choices=["flags", "nccl"], help="N>1, --gather peer: frame fence through NVLink flags (rte_frame_fence) or a 4-byte NCCL all-reduce")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--fixed-white", action="store_true", help="c5: the reference's constant max_white = 5.0 (fused tonemap) instead of the auto max-white pipeline")
+    ap.add_argument("--auto-white", action="store_true", help="--workload c5: the auto max-white pipeline (max-luminance kernel + NCCL all-reduce MAX + tonemap pass; no reference counterpart, SURVEY D6) instead of the reference's constant max_white = 5.0")
+    ap.add_argument("--no-c5", action="store_true", help="skip the c5_8k leg (C5 at 7680x4320, the north star's scaling target)")
     args = ap.parse_args()
-    if args.stripe <= 0:
-        args.stripe = 16 if args.workload == "c5" else 8
     # stdout carries exactly ONE line (the JSON); libraries that print to fd 1 (NCCL's version banner) go to stderr
     global _OUT
     sys.stdout.flush()
