@@ -602,10 +602,8 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     // light_mask.  The operator runs in the kernel; pixels with an inconclusive FP32 decision go through the exact fix-up launch.
     // With registered peer frames the kernel stores its RGB8 into every rank's frame itself; the fix-up launch signals the fence.
     if (o.n_rows > 0 && fp32_path_eligible(p)) {
-        const size_t n_px = (size_t)o.n_rows * (size_t)ctx->cam.width;
         if (p.out.rgb8 && ((uintptr_t)p.out.rgb8 & 3u) != 0 && (ctx->cam.width & 3) == 0) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 must be 4-byte aligned");
-        int rc = reserve(ctx, ctx->s_fix, n_px * sizeof(unsigned int));
-        if (rc) return rc;
+        int rc;
         if ((rc = ensure_grid(ctx, o.bias, p.grid))) return rc;
         p.n_peers = p.tonemap_op == RTE_TM_NONE ? 0 : ctx->n_peers;
         for (int i = 0; i < p.n_peers; ++i) p.peer_rgb8[i] = ctx->peer_rgb8[i];
@@ -614,8 +612,6 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
             for (int i = 0; i < ctx->n_fence; ++i) p.fence_flags[i] = ctx->fence_flags[i];
             p.n_fence = ctx->n_fence; p.fence_rank = ctx->fence_rank; p.fence_seq = ctx->fence_seq; p.fence_counter = ctx->d_fence_counter;
         }
-        p.fix_list = (unsigned int*)ctx->s_fix.p;
-        p.fix_count = reinterpret_cast<unsigned int*>(ctx->d_stats + kStatCount + 1);
         if (first) {
             RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * (kStatCount + 2), ctx->stream));
             RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
@@ -623,8 +619,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
             RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned long long) * 2, ctx->stream));
         }
         RTE_CUDA(ctx, launch_render32(p, ctx->sm_count, ctx->stream));
-        RTE_CUDA(ctx, launch_fixup(p, ctx->sm_count, ctx->stream));
-        ctx->render_launches += 2;
+        ctx->render_launches += 1;
         if (last) {
             RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
             RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));

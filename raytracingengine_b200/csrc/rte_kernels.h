@@ -50,16 +50,14 @@ struct RenderParams {
     int32_t exact_fp64;      // RTE_FLAG_EXACT_FP64: never take the FP32 production path (rte_render32.cu)
     DevGrid grid;            // FP32 path: per-origin direction grids (rte_grid.cuh), built per camera / bias
     // FP32 path, multi-GPU output (rte_set_rgb8_peers / rte_set_fence_peers): the render kernel stores every tile row it finishes
-    // into every registered full frame at its image position (peer stores over NVLink while the SMs keep tracing); the fix-up
-    // launch stores its pixels and then signals the frame fence (its last CTA), see Tonemap64Params below
+    // into every registered full frame at its image position (peer stores over NVLink while the SMs keep tracing); its last
+    // CTA signals the frame fence, see Tonemap64Params below
     uint8_t* peer_rgb8[8];
     int32_t n_peers;
     uint32_t* fence_flags[8];
     int32_t n_fence, fence_rank;
     uint32_t fence_seq;
     unsigned int* fence_counter;
-    unsigned int* fix_list;  // FP32 path: band-local indices of the pixels with an inconclusive decision (capacity: band pixels) ...
-    unsigned int* fix_count; // ... and their number (zeroed before the launch); the fix-up launch renders them exactly
     unsigned int* tile_counter;        // zeroed before launch
     unsigned long long* stats;         // kStatCount counters, zeroed before launch
 };
@@ -78,7 +76,6 @@ cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, dou
 cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
                              uint32_t capacity, cudaStream_t stream);
 cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream);
-cudaError_t launch_fixup(const RenderParams& p, int sm_count, cudaStream_t stream);
 // would launch_render split this call into a primary-ray launch and a shading launch (it then needs p.hits)?
 bool two_pass_wanted(const RenderParams& p);
 // (re)builds sc.views for this camera / bias (rte_views.cuh); a no-op for scenes without spheres

@@ -12,6 +12,7 @@
 //  * reflection (material.specular) is an iterative loop; refraction is rejected at upload time.
 #include <vector>
 
+#include "rte_exact_grid.cuh"
 #include "rte_kernels.h"
 #include "rte_stage.cuh"
 #include "rte_tonemap.cuh"
@@ -92,16 +93,6 @@ SmemPlan plan_smem(const DevScene& sc, size_t budget) {
 
 static SmemPlan generic_plan(const DevScene& sc);
 size_t scene_smem_bytes(const DevScene& sc) { return (size_t)sc.ns_pad * 16 + (size_t)sc.nt_pad * 48; }
-
-// Scene::backgroundColor, RE/Scene.h:30-33
-__device__ __forceinline__ d3 background(d3 dir) {
-    const double t = 0.5 * (normalize(dir).y + 1.0);
-    return mk(1.0, 1.0, 1.0) * (1.0 - t) + mk(0.5, 0.7, 1.0) * t;
-}
-
-struct PixelCounters {
-    uint32_t shadow, secondary, sph, pl, tri, marches, confirms, sph_exec;
-};
 
 // TraceRay for the K pixels of one thread, all 32 lanes of the warp in lock step (pixels outside the image:
 // alive = false).  kReflect = false compiles the diffuse-only path (no material has specular > 0): the depth loop,
@@ -468,197 +459,6 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
     }
     __syncwarp();
     if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
-}
-
-// ------------------------------------------------------------------------------ fix-up launch of the FP32 path
-// The FP32 production kernel (rte_render32.cu) shades a pixel only when every decision of it is certain within FP32 error
-// bounds; the others (~1e-3 of a frame: grazing rays, N.L ~ 0, contact shadows within `bias`) arrive here as a list of
-// band-local pixel indices and are rendered with the reference's exact FP64 operations, in the reference's order — over the
-// candidates of the ray's grid cell (rte_grid.cuh) instead of over all spheres.  One pixel per lane, no warp-level step.
-
-// Scene::IntersectClosest (RE/Scene.h:218-257) over {spheres of the cell + near list of `view`} and all planes.  The lists are
-// unordered, so "the first of equal distances wins" (strict '<' in canonical order) is applied by index.
-__device__ __forceinline__ void closest_hit_grid(const DevScene& sc, const DevGrid& g, int view, float ux, float uy, float uz, d3 o, d3 d, Hit& best) {
-    best.t = 0.0; best.kind = RTE_HIT_NONE; best.idx = 0;
-    uint32_t cell = grid_cell(g, view, ux, uy, uz);
-#pragma unroll 1
-    for (int pass = 0; pass < 2; ++pass) {
-        const uint32_t e0 = g.cell_start[cell], e1 = g.cell_start[cell + 1];
-#pragma unroll 1
-        for (uint32_t e = e0; e < e1; ++e) {
-            const uint32_t k = g.entries[e];
-            double t;
-            if (sphere_exact(sc.sph64[k], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t || (t == best.t && k < best.idx))) {
-                best.t = t; best.kind = RTE_HIT_SPHERE; best.idx = k;
-            }
-        }
-        cell = grid_near_cell(g, view);
-    }
-#pragma unroll 1
-    for (int i = 0; i < sc.np; ++i) {
-        double t;
-        if (plane_exact(sc.planes[i], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t)) { best.t = t; best.kind = RTE_HIT_PLANE; best.idx = (uint32_t)i; }
-    }
-}
-
-// One pixel sample, exactly: TraceRay + directLightning + computeTransmittance (RE/Scene.h:131-198, 79-129, 35-77) for scenes
-// without specular / transparent materials and without triangles (what the FP32 path accepts).
-__device__ __noinline__ d3 exact_pixel_grid(const RenderParams& P, const DevScene& sc, int px, int py, int sample, uint32_t& prim, uint32_t& lmask,
-                                            PixelCounters& cnt) {
-    const DevGrid& g = P.grid;
-    const d3 cam_o = ld3(P.cam.pos);
-    const d3 d = camera_dir(P.cam, px, py, sample);
-    const double bias = P.bias;
-    Hit h;
-    closest_hit_grid(sc, g, 0, (float)d.x, (float)d.y, (float)d.z, cam_o, d, h);
-    cnt.sph += (uint32_t)sc.ns; cnt.pl += (uint32_t)sc.np;
-    prim = kMiss; lmask = 0u;
-    if (h.kind == RTE_HIT_NONE) return mk(0.0, 0.0, 0.0) + background(d) * 1.0;  // sky (RE/Scene.h:137-141)
-    const d3 Pn = cam_o + d * h.t;
-    d3 ng;
-    if (h.kind == RTE_HIT_SPHERE) { const double4 s = sc.sph64[h.idx]; ng = normalize(Pn - mk(s.x, s.y, s.z)); }
-    else ng = ld3(sc.planes[h.idx].n);
-    prim = (h.kind << 30) | h.idx;
-    const int mat = material_of(sc, h);
-    const d3 incoming = normalize(d);
-    const bool frontFace = dot(ng, incoming) < 0.0;
-    const d3 normal = normalize(frontFace ? ng : -ng);  // directLightning re-normalises, RE/Scene.h:81
-    d3 diffuse = mk(0.0, 0.0, 0.0);
-#pragma unroll 1
-    for (int j = 0; j < sc.nl; ++j) {
-        const d3 Lp = ld3(sc.lights[j].pos);
-        const d3 vecToLight = Lp - Pn;
-        const double dist = length(vecToLight);
-        if (!(dist > 0.0)) continue;
-        const d3 L = vecToLight / dist;
-        const double ndl = std_max(0.0, dot(normal, L));
-        if (!(ndl > 0.0) || !(dist > bias)) continue;
-        cnt.shadow += 1;
-        if (j < 16) lmask |= 1u << (16 + j);
-        // computeTransmittance, literally; every closest-hit query of the march looks at the spheres of the light's cell in the
-        // direction of this ray (the march moves its origin along the same line: no other sphere can be hit before the light)
-        d3 o = Pn + normal * bias;
-        const double maxDist = dist - bias;
-        const float ux = (float)(-L.x), uy = (float)(-L.y), uz = (float)(-L.z);
-        {   // algorithmic test counts: canonical order up to and including the first occluder
-            uint32_t first = (uint32_t)sc.ns;
-            uint32_t cell = grid_cell(g, 1 + j, ux, uy, uz);
-            for (int pass = 0; pass < 2; ++pass) {
-                for (uint32_t e = g.cell_start[cell]; e < g.cell_start[cell + 1]; ++e) {
-                    const uint32_t k = g.entries[e];
-                    double t;
-                    if (sphere_exact(sc.sph64[k], o, L, t) && t > bias && t < maxDist && k < first) first = k;
-                }
-                cell = grid_near_cell(g, 1 + j);
-            }
-            if (first < (uint32_t)sc.ns) cnt.sph += first + 1u;
-            else {
-                cnt.sph += (uint32_t)sc.ns;
-                uint32_t firstp = (uint32_t)sc.np;
-                for (int i = 0; i < sc.np; ++i) {
-                    double t;
-                    if (plane_exact(sc.planes[i], o, L, t) && t > bias && t < maxDist) { firstp = (uint32_t)i; break; }
-                }
-                cnt.pl += firstp < (uint32_t)sc.np ? firstp + 1u : (uint32_t)sc.np;
-            }
-        }
-        double T = 1.0, traveled = 0.0;
-        int safety = 64;
-        bool stepped = false;
-        while (safety-- > 0 && T > 1e-4 && traveled < maxDist) {
-            Hit sh;
-            closest_hit_grid(sc, g, 1 + j, ux, uy, uz, o, L, sh);
-            if (sh.kind == RTE_HIT_NONE) break;
-            const double t = sh.t;
-            if (t <= 0.0) { o = o + L * bias; traveled += bias; stepped = true; continue; }
-            if (t <= bias) { o = (o + L * t) + L * bias; traveled += t + bias; stepped = true; continue; }
-            if (traveled + t >= maxDist) break;
-            T *= std_clamp(sc.materials[material_of(sc, sh)].transparency, 0.0, 1.0);
-            const d3 newOrigin = (o + L * t) + L * bias;
-            traveled += t + bias;
-            o = newOrigin;
-        }
-        T = std_clamp(T, 0.0, 1.0);
-        if (stepped) cnt.marches += 1;
-        if (T > bias) {
-            if (j < 16) lmask |= 1u << j;
-            const d3 emitted = ld3(sc.lights[j].E);
-            const d3 contribution = (emitted * div64(1.0, dist * dist)) * ndl;
-            diffuse = diffuse + contribution * T;
-        }
-    }
-    const rte_material& M = sc.materials[mat];
-    const d3 local = ld3(M.color) * diffuse + mk(0.0, 0.0, 0.0) * M.specular;
-    return mk(0.0, 0.0, 0.0) + (local * (1.0 - 0.0)) * 1.0;  // finalLight += localLight * (1 - transparency)
-}
-
-__global__ void __launch_bounds__(kRenderThreads) fixup_kernel(const __grid_constant__ RenderParams P) {
-    __shared__ DevScene s_sc;
-    if (threadIdx.x == 0) s_sc = P.sc;
-    __syncthreads();
-    const DevScene& sc = s_sc;
-    const unsigned int n = *P.fix_count;
-    const int lane = threadIdx.x & 31;
-    const int W = P.cam.width, sr = P.stripe_rows, sp = P.stripe_period, aa = P.cam.aa;
-    PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
-    uint32_t n_prim = 0;
-    // Each pixel is a long serial FP64 chain and there are few of them: only every kFixSpread-th lane takes one, so that the
-    // list spreads over kFixSpread times as many warps (latency-bound work: more warps in flight, not fewer instructions).
-    constexpr unsigned int kFixSpread = 4;
-    for (unsigned int vi = blockIdx.x * blockDim.x + threadIdx.x; vi < n * kFixSpread; vi += gridDim.x * blockDim.x) {
-        if (vi % kFixSpread) continue;
-        const unsigned int i = vi / kFixSpread;
-        const int64_t pix = (int64_t)P.fix_list[i];
-        const int band_y = (int)(pix / W);
-        const int px = (int)(pix - (int64_t)band_y * W);
-        const int py = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
-        d3 v = mk(0.0, 0.0, 0.0);
-        uint32_t prim0 = kMiss, lmask0 = 0u;
-#pragma unroll 1
-        for (int s = 0; s < aa; ++s) {  // GeneratePixelAt, RE/Scene.h:283-304
-            uint32_t prim, lmask;
-            const d3 c = exact_pixel_grid(P, sc, px, py, s, prim, lmask, cnt);
-            if (aa > 1) v = v + c; else v = c;
-            if (s == 0) { prim0 = prim; lmask0 = lmask; }
-        }
-        if (aa > 1) v = v / (double)aa;
-        if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[pix] = make_float4((float)v.x, (float)v.y, (float)v.z, 0.f);
-        if (P.out.rgb8) {
-            const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));
-            uint8_t* dst = P.out.rgb8 + 3 * pix;
-            dst[0] = u.x; dst[1] = u.y; dst[2] = u.z;
-        }
-        if (P.n_peers > 0) {
-            const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));
-            for (int r = 0; r < P.n_peers; ++r) { uint8_t* dst = P.peer_rgb8[r] + 3 * ((int64_t)py * W + px); dst[0] = u.x; dst[1] = u.y; dst[2] = u.z; }
-        }
-        if (P.out.prim_id) P.out.prim_id[pix] = prim0;
-        if (P.out.light_mask) P.out.light_mask[pix] = lmask0;
-        n_prim += (uint32_t)aa;
-    }
-    // (fp64_confirms of an FP32-path call = the number of pixel samples re-rendered here)
-    const uint32_t v[kStatCount] = {n_prim, cnt.shadow, 0u, cnt.sph, cnt.pl, 0u, cnt.marches, n_prim, 0u};
-#pragma unroll
-    for (int k = 0; k < kStatCount; ++k) {
-        const uint32_t t = __reduce_add_sync(kFullMask, v[k]);
-        if (lane == 0 && t) atomicAdd(&P.stats[k], (unsigned long long)t);
-    }
-    // Frame fence over NVLink (rte_set_fence_peers): this launch runs after the render kernel of the call, whose peer stores
-    // are complete at its end; every thread here makes its own stores visible system-wide, and the last CTA to get here tells
-    // every rank "rank `fence_rank` has delivered frame `seq`" (same protocol as tonemap64_kernel, rte_tonemap.cu).
-    if (P.n_fence > 0) {
-        __threadfence_system();
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            const unsigned int done = atomicAdd(P.fence_counter, 1u);
-            if (done == gridDim.x - 1) {
-                *P.fence_counter = 0u;  // for the next launch (stream order)
-                __threadfence_system();
-                for (int r = 0; r < P.n_fence; ++r)
-                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.fence_flags[r] + P.fence_rank), "r"(P.fence_seq) : "memory");
-            }
-        }
-    }
 }
 
 // ------------------------------------------------------------------------------ view providers
@@ -1352,12 +1152,6 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
     }
     const void* fn = p.sc.reflective ? (const void*)render_kernel<1, true> : (const void*)render_kernel<1, false>;
     return launch_render_fn(fn, fn, kRenderThreads, 2, 1, p, sm_count, stream);
-}
-
-cudaError_t launch_fixup(const RenderParams& p, int sm_count, cudaStream_t stream) {
-    void* args[] = {(void*)&p};
-    // the list's length lives on the device: a fixed grid walks it (an empty list costs an empty launch)
-    return cudaLaunchKernel((const void*)fixup_kernel, dim3((unsigned)(2 * sm_count)), dim3(kRenderThreads), args, 0, stream);
 }
 
 // ------------------------------------------------------------------------------ ray queries

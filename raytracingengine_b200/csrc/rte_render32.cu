@@ -10,11 +10,12 @@
 //    (hit point, C - origin of a candidate) take a handful of FP64 adds / FMAs — never an FP64 division or square root
 //    (those are ~25 / ~40 SASS instructions each): reciprocal square roots come from MUFU + Newton steps.
 //  * DECISIONS (which primitive is nearest, is a shadow ray cast, is it occluded) are taken from FP32 INTERVALS with explicit
-//    error bounds.  A pixel with any inconclusive decision is not shaded here: its index goes to a device list and the
-//    fix-up launch (rte_render.cu: fixup_kernel) renders it with the exact FP64 code.  So every decision that reaches an
-//    output is either certain or exact, and flagged pixels (~1e-3 of a frame) are the reference's own bits.
+//    error bounds.  A pixel with any inconclusive decision is rendered again on the spot with the reference's exact FP64
+//    operations (rte_exact_grid.cuh) by the lane that owns it.  So every decision that reaches an output is either certain
+//    or exact, and those pixels (~1e-3 of a frame) are the reference's own bits.
 //  * The operator + toColor run in the kernel (tm32, rte_tonemap.cuh) and a tile row of 8 pixels leaves as six aligned
 //    32-bit words: no FP64 HDR scratch, no second pass.
+#include "rte_exact_grid.cuh"
 #include "rte_grid.cuh"
 #include "rte_kernels.h"
 #include "rte_tonemap.cuh"
@@ -473,6 +474,72 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
     return ok || !alive;
 }
 
+// ------------------------------------------------------------------------------ deferred exact pixels
+// A warp queues the (band-local) indices of its pixels with an inconclusive FP32 decision and renders them in batches with the
+// reference's exact FP64 operations (rte_exact_grid.cuh).  Lanes = (pixel, light): every lane of a pixel's group evaluates the
+// primary hit, lane j the shadow ray of light j, and the contributions are added in the lights' order (RE/Scene.h:86,113) —
+// all 32 lanes busy, and the dependent FP64 chain of a pixel is 1 + 1 rays long instead of 1 + nl.
+constexpr int kFixCap = 64;  // per-warp queue
+static __device__ __noinline__ void fix_batch(const RenderParams& P, const uint32_t* __restrict__ q, int n, unsigned long long* __restrict__ stats_row) {
+    const int lane = threadIdx.x & 31;
+    const DevScene& sc = P.sc;
+    const int nl = sc.nl, W = P.cam.width, sr = P.stripe_rows, sp = P.stripe_period, aa = P.cam.aa;
+    int lpp = 1;
+    while (lpp < nl) lpp <<= 1;  // lanes per pixel (nl <= 16)
+    const int per = 32 / lpp, slot = lane / lpp, j = lane % lpp, lead = lane & ~(lpp - 1);
+    uint32_t st[kStatCount] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+    for (int base = 0; base < n; base += per) {
+        const bool act = base + slot < n;
+        const int64_t pix = act ? (int64_t)q[base + slot] : 0;
+        const int band_y = (int)(pix / W), px = (int)(pix - (int64_t)band_y * W);
+        const int py = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
+        d3 v = mk(0.0, 0.0, 0.0);
+        uint32_t prim0 = kMiss, lmask0 = 0u;
+#pragma unroll 1
+        for (int s = 0; s < aa; ++s) {  // GeneratePixelAt, RE/Scene.h:283-304
+            ExactHit H;
+            H.hit = false; H.sky = mk(0.0, 0.0, 0.0); H.prim = kMiss; H.mat = sc.nm; H.Pn = mk(0.0, 0.0, 0.0); H.normal = mk(0.0, 0.0, 1.0);
+            if (act) exact_primary(P, sc, px, py, s, H);
+            PixelCounters c = {0, 0, 0, 0, 0, 0, 0, 0};
+            d3 contrib = mk(0.0, 0.0, 0.0);
+            uint32_t bits = 0u;
+            if (act && j < nl) contrib = exact_light(P, sc, H, j, bits, c);
+            d3 diffuse = mk(0.0, 0.0, 0.0);
+            uint32_t lm = 0u;
+            for (int k = 0; k < nl; ++k) {  // (warp-uniform) diffuseAccumulation += contribution * transmittance, in the lights' order
+                const double cx = __shfl_sync(kFullMask, contrib.x, lead + k), cy = __shfl_sync(kFullMask, contrib.y, lead + k),
+                             cz = __shfl_sync(kFullMask, contrib.z, lead + k);
+                const uint32_t b = __shfl_sync(kFullMask, bits, lead + k);
+                if (b & 1u) diffuse = diffuse + mk(cx, cy, cz);
+                if (k < 16) lm |= (((b >> 16) & 1u) << (16 + k)) | ((b & 1u) << k);
+            }
+            const d3 e = exact_finish(sc, H, diffuse);
+            if (aa > 1) v = v + e; else v = e;
+            if (s == 0) { prim0 = H.prim; lmask0 = lm; }
+            st[kStatShadow] += c.shadow; st[kStatSphTests] += c.sph; st[kStatPlTests] += c.pl; st[kStatMarches] += c.marches;
+            if (act && j == 0) { st[kStatPrimary] += 1u; st[kStatSphTests] += (uint32_t)sc.ns; st[kStatPlTests] += (uint32_t)sc.np; st[kStatConfirms] += 1u; }
+        }
+        if (aa > 1) v = v / (double)aa;
+        if (act && j == 0) {
+            if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[pix] = make_float4((float)v.x, (float)v.y, (float)v.z, 0.f);
+            if (P.out.prim_id) P.out.prim_id[pix] = prim0;
+            if (P.out.light_mask) P.out.light_mask[pix] = lmask0;
+            if (P.out.rgb8 || P.n_peers > 0) {
+                const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));  // the reference's own bytes
+                if (P.out.rgb8) { uint8_t* d = P.out.rgb8 + 3 * pix; d[0] = u.x; d[1] = u.y; d[2] = u.z; }
+                for (int r = 0; r < P.n_peers; ++r) { uint8_t* d = P.peer_rgb8[r] + 3 * ((int64_t)py * W + px); d[0] = u.x; d[1] = u.y; d[2] = u.z; }
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < kStatCount; ++k) {
+        const uint32_t t = __reduce_add_sync(kFullMask, st[k]);
+        if (lane == 0 && t) stats_row[k] += t;
+    }
+    __syncwarp();
+}
+
 // ------------------------------------------------------------------------------ the kernel
 // Persistent CTAs, one 8 x 4 pixel tile per warp at a time from a global counter (like the exact kernels), one pixel per lane.
 constexpr int kTile32W = 8, kTile32H = 4;
@@ -481,7 +548,9 @@ template <bool kAov>
 __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_constant__ RenderParams P) {
     __shared__ Scene32 s32;
     __shared__ unsigned long long s_stats[kR32Threads / 32][kStatCount];
+    __shared__ uint32_t s_fixq[kR32Threads / 32][kFixCap];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int fix_n = 0;  // (warp-uniform) pixels waiting in s_fixq[warp]
     if (threadIdx.x == 0) {
         const DevScene& g = P.sc;
         s32.np = g.np; s32.nl = g.nl;
@@ -538,8 +607,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
             if (s == 0) { prim = o.prim; lmask = o.lmask; }
         }
         if (aa > 1) { const float ia = 1.0f / (float)aa; cr *= ia; cg *= ia; cb *= ia; }
-        const bool mine = inb && ok;    // this kernel owns the pixel; flagged pixels go to the fix-up launch
-        const bool flagged = inb && !ok;
+        const bool flagged = inb && !ok, mine = inb && ok;  // flagged pixels wait in the warp's queue for an exact batch (fix_batch)
         // ---- outputs
         if (mine) {
             if (P.out.hdr) __stcs(reinterpret_cast<float4*>(P.out.hdr) + pix, make_float4(cr, cg, cb, 0.f));
@@ -549,7 +617,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
             }
         }
         if (P.out.rgb8 || P.n_peers > 0) {
-            const uint32_t rgb = tonemap_rgb24(P.tonemap_op, cr, cg, cb, K);
+            const uint32_t rgb = tonemap_rgb24(P.tonemap_op, cr, cg, cb, K);  // (a flagged pixel's bytes are overwritten by fix_batch)
             const bool row_full = (tx + 1) * kTile32W <= W && band_y < rows;  // (uniform over the 8 lanes of a tile row)
             const int64_t ipix = (int64_t)py * W + px;                           // position in a full frame (peer frames hold the whole image)
             if (words) {
@@ -569,15 +637,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
                 for (int i = 0; i < P.n_peers; ++i) { uint8_t* d = P.peer_rgb8[i] + 3 * ipix; d[0] = b0; d[1] = b1; d[2] = b2; }
             }
         }
-        // ---- pixels with an inconclusive decision: appended to the fix-up list (one atomic per tile that has any)
-        const uint32_t fm = __ballot_sync(kFullMask, flagged);
-        if (fm) {
-            unsigned int at = 0;
-            if (lane == 0) at = atomicAdd(P.fix_count, (unsigned int)__popc(fm));
-            at = __shfl_sync(kFullMask, at, 0);
-            if (flagged) P.fix_list[at + __popc(fm & ((1u << lane) - 1u))] = (unsigned int)pix;
-        }
-        // ---- statistics of the pixels this kernel owns (the fix-up launch counts its own)
+        // ---- statistics of the pixels shaded here (fix_batch counts its own; fp64_confirms = pixel samples rendered again in FP64)
         const uint32_t v[kStatCount] = {mine ? (uint32_t)aa : 0u, mine ? n_shadow : 0u, 0u, mine ? n_sph : 0u, mine ? n_pl : 0u, 0u, 0u, 0u, executed};
         uint32_t sum_mine = 0;
 #pragma unroll
@@ -586,10 +646,34 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
             if (lane == k) sum_mine = t;
         }
         if (lane < kStatCount) s_stats[warp][lane] += sum_mine;
+        // ---- queue the flagged pixels; a full batch (every lane a (pixel, light) pair) is rendered exactly right away
+        const uint32_t fm = __ballot_sync(kFullMask, flagged);
+        if (fm) {
+            if (flagged) s_fixq[warp][fix_n + __popc(fm & ((1u << lane) - 1u))] = (uint32_t)pix;
+            fix_n += __popc(fm);
+            __syncwarp();
+            if (fix_n > kFixCap - 32) { fix_batch(P, s_fixq[warp], fix_n, s_stats[warp]); fix_n = 0; }
+        }
         tile = __shfl_sync(kFullMask, next, 0);
     }
+    if (fix_n > 0) fix_batch(P, s_fixq[warp], fix_n, s_stats[warp]);  // what is left of the warp's queue
     __syncwarp();
     if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
+    // Frame fence over NVLink (rte_set_fence_peers), fused into the kernel that does the peer stores: every thread makes its
+    // stores visible system-wide, the last CTA to get here tells every rank "rank `fence_rank` has delivered frame `seq`".
+    if (P.n_fence > 0) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned int done = atomicAdd(P.fence_counter, 1u);
+            if (done == gridDim.x - 1) {
+                *P.fence_counter = 0u;  // for the next launch (stream order)
+                __threadfence_system();
+                for (int r = 0; r < P.n_fence; ++r)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.fence_flags[r] + P.fence_rank), "r"(P.fence_seq) : "memory");
+            }
+        }
+    }
 }
 
 // Can this render call take the FP32 path?  (rte_api.cu decides with it; everything else takes the exact kernels.)
