@@ -51,7 +51,7 @@ struct rte_ctx {
     DevScene sc{};
     DevCamera cam{};
     rte_camera cam_host{};
-    DevBuf b_sph32, b_tri32, b_sph64, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views, b_tviews, b_views_cold, b_tviews_cold;
+    DevBuf b_sph32, b_tri32, b_sph64, b_sphhl, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views, b_tviews, b_views_cold, b_tviews_cold;
     bool views_dirty = true;
     double views_bias = -1.0;
     // FP32 production path: per-origin direction grids (rte_grid.cuh), rebuilt when the scene, the camera or the bias changes
@@ -285,7 +285,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
+    DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphhl, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
                       &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->b_grid_count, &ctx->b_grid_start, &ctx->b_grid_entries, &ctx->b_grid_aggr, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
@@ -364,6 +364,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     std::vector<float4> sph32((size_t)ns_pad);
     std::vector<double4> sph64((size_t)ns_pad);
     std::vector<int32_t> sphmat((size_t)ns_pad, -1);
+    std::vector<float4> sphhl((size_t)ns_pad * 2, make_float4(0.f, 0.f, 0.f, 0.f));
     double s_ext = 0.0;
     for (int i = 0; i < ns; ++i) {
         const rte_sphere& s = d->spheres[i];
@@ -372,6 +373,11 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
         const float r = up((float)std::fabs(s.radius));
         sph32[i] = make_float4((float)s.center[0], (float)s.center[1], (float)s.center[2], up(r * r));
         sphmat[i] = s.material;
+        {   // centre as hi + lo floats (FP32 production path, rte_render32.cu)
+            const float hx = (float)s.center[0], hy = (float)s.center[1], hz = (float)s.center[2];
+            sphhl[2 * (size_t)i] = make_float4(hx, hy, hz, (float)std::fabs(s.radius));
+            sphhl[2 * (size_t)i + 1] = make_float4((float)(s.center[0] - (double)hx), (float)(s.center[1] - (double)hy), (float)(s.center[2] - (double)hz), 0.f);
+        }
         s_ext = std::fmax(s_ext, hlen(h3(s.center)) + std::fabs(s.radius));
     }
     for (int i = ns; i < ns_pad; ++i) {  // never-hit padding: q = +inf
@@ -466,10 +472,10 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     if ((rc = reserve(ctx, ctx->b_tviews, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_views_cold, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_tviews_cold, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
-    if ((rc = stage_begin(ctx, stage_bytes(sph32) + stage_bytes(sph64) + stage_bytes(sphmat) + stage_bytes(planes) + stage_bytes(tri32) + stage_bytes(tri64) +
+    if ((rc = stage_begin(ctx, stage_bytes(sph32) + stage_bytes(sph64) + stage_bytes(sphhl) + stage_bytes(sphmat) + stage_bytes(planes) + stage_bytes(tri32) + stage_bytes(tri64) +
                                stage_bytes(triinfo) + stage_bytes(mats) + stage_bytes(lights))))
         return rc;
-    if ((rc = upload(ctx, ctx->b_sph32, sph32)) || (rc = upload(ctx, ctx->b_sph64, sph64)) || (rc = upload(ctx, ctx->b_sphmat, sphmat)) ||
+    if ((rc = upload(ctx, ctx->b_sph32, sph32)) || (rc = upload(ctx, ctx->b_sph64, sph64)) || (rc = upload(ctx, ctx->b_sphhl, sphhl)) || (rc = upload(ctx, ctx->b_sphmat, sphmat)) ||
         (rc = upload(ctx, ctx->b_planes, planes)) || (rc = upload(ctx, ctx->b_tri32, tri32)) || (rc = upload(ctx, ctx->b_tri64, tri64)) ||
         (rc = upload(ctx, ctx->b_triinfo, triinfo)) || (rc = upload(ctx, ctx->b_mats, mats)) || (rc = upload(ctx, ctx->b_lights, lights)))
         return rc;
@@ -489,7 +495,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     ctx->views_dirty = true;
     ctx->grid_dirty = true;
     sc.ns = ns; sc.ns_pad = ns_pad; sc.nt = nt; sc.nt_pad = nt_pad;
-    sc.sph64 = (const double4*)ctx->b_sph64.p; sc.sph_mat = (const int32_t*)ctx->b_sphmat.p;
+    sc.sph64 = (const double4*)ctx->b_sph64.p; sc.sph_hl = (const float4*)ctx->b_sphhl.p; sc.sph_mat = (const int32_t*)ctx->b_sphmat.p;
     sc.planes = (const DevPlane*)ctx->b_planes.p; sc.tri64 = (const DevTri64*)ctx->b_tri64.p;
     sc.tri_info = (const int2*)ctx->b_triinfo.p; sc.materials = (const rte_material*)ctx->b_mats.p;
     sc.lights = (const DevLight*)ctx->b_lights.p;

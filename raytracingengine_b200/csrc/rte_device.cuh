@@ -47,6 +47,7 @@ struct DevScene {
     int32_t ns, ns_pad, nt, nt_pad;
     // FP64 exact arrays
     const double4* sph64; // {cx, cy, cz, r}
+    const float4* sph_hl; // FP32 path: two float4 per sphere, {hi(C), |r|} and {lo(C), 0} with C = hi + lo to ~2^-48 (no FP64 -> FP32 conversion per candidate)
     const int32_t* sph_mat;
     const DevPlane* planes;
     const DevTri64* tri64;

@@ -40,7 +40,8 @@ __device__ __forceinline__ uint32_t grid_cell(const DevGrid& g, int view, float 
     else if (ay >= az)        { axis = 1; w = dy; p = dz; q = dx; }
     else                      { axis = 2; w = dz; p = dx; q = dy; }
     const int face = 2 * axis + (w < 0.0f ? 1 : 0);
-    const float inv = __frcp_rn(fabsf(w));
+    float inv;  // (approximate reciprocal: the rectangles of the build carry a margin of 1e-5 in u, v)
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(fabsf(w)));
     const float half = 0.5f * (float)g.G;
     // (u + 1) * G / 2 with u = p / |w| in [-1, 1]
     int iu = (int)__fmaf_rn(p * inv, half, half), iv = (int)__fmaf_rn(q * inv, half, half);

@@ -51,15 +51,16 @@ struct Plane32 {
 };
 struct Scene32 {
     Plane32 pl[kR32Planes];
-    double li_pos[kR32Lights][3];
+    float li_hi[kR32Lights][3], li_lo[kR32Lights][3];  // light position = hi + lo
     float li_E[kR32Lights][3];
     double cam[3];
+    float cam_hi[3], cam_lo[3];
     int np, nl;
 };
 
 // ------------------------------------------------------------------------------ one sphere candidate against one ray
 // The ray is {origin o (FP64), unit direction L (FP32, |L| = 1 +- 4 eps, within 4 eps of the reference's direction)}.
-//   g = fl32(C - o)  (FP64 subtraction: relative error eps),  b = g.L,  l = g - b L,  l2 = |l|^2  — no cancellation between
+//   g = C - o to a relative error of ~2 eps (see below),  b = g.L,  l = g - b L,  l2 = |l|^2  — no cancellation between
 //   quantities of the size of the scene; every absolute error below is bounded by  dl = 20 eps (|b| + |l|) + 1e-7
 //   (direction error 4 eps |b| + roundings ~5 eps |g| + parameter scale 4 eps |b|, |g| <= |b| + |l|).
 // Returns the class of the candidate and, for a certain hit, bounds of the near root t0 and of the far root t1.
@@ -68,16 +69,19 @@ struct Cand32 {
     int cls;
     float t0_lo, t0_hi, t1_lo, t1_hi;  // kCandHit: t0 in [t0_lo, t0_hi], t1 in [t1_lo, t1_hi]; kCandUnsure: the chord, if any, lies in [t0_lo, t1_hi]
 };
-__device__ __forceinline__ Cand32 classify_sphere(const double4 s, double ox, double oy, double oz, float Lx, float Ly, float Lz, float r_pad) {
-    const float gx = (float)(s.x - ox), gy = (float)(s.y - oy), gz = (float)(s.z - oz);
+__device__ __forceinline__ Cand32 classify_sphere(const float4 hi, const float4 lo, float ohx, float ohy, float ohz, float olx, float oly, float olz,
+                                                  float Lx, float Ly, float Lz) {
+    // g = C - o from the hi + lo halves: (hi_C - hi_o) is one correctly rounded FP32 subtraction (relative error eps of |g|), the
+    // lo halves carry what the roundings of C and o to FP32 lost — the same accuracy as rounding the FP64 difference, without
+    // an FP64 -> FP32 conversion per candidate (those issue on the XU pipe, like MUFU)
+    const float gx = (hi.x - ohx) + (lo.x - olx), gy = (hi.y - ohy) + (lo.y - oly), gz = (hi.z - ohz) + (lo.z - olz);
     const float b = __fmaf_rn(gz, Lz, __fmaf_rn(gy, Ly, gx * Lx));
     const float lx = __fmaf_rn(-b, Lx, gx), ly = __fmaf_rn(-b, Ly, gy), lz = __fmaf_rn(-b, Lz, gz);
     const float l2 = __fmaf_rn(lz, lz, __fmaf_rn(ly, ly, lx * lx));
     const float l = sqrt_approx(l2) * 1.000001f;
     const float dl = __fmaf_rn(20.0f * kEps32, fabsf(b) + l, 1e-7f);
-    const float r = (float)s.w;  // |r| is what the reference squares
-    const float ra = fabsf(r);
-    const float r_hi = ra * 1.0000002f + r_pad, r_lo = ra * 0.9999998f - r_pad;
+    const float ra = hi.w;  // |r| rounded to FP32 (what the reference squares)
+    const float r_hi = ra * 1.0000002f, r_lo = ra * 0.9999998f;
     Cand32 c;
     const float lm = fmaxf(l * 0.999998f - dl, 0.0f), lp = l + dl;   // lower / upper bound of the true distance line - centre
     if (lm > r_hi) { c.cls = kCandMiss; c.t0_lo = c.t0_hi = c.t1_lo = c.t1_hi = 0.0f; return c; }
@@ -127,24 +131,40 @@ __device__ __forceinline__ bool near_ambiguous(const Near32& n) { return n.kind 
 
 // ------------------------------------------------------------------------------ one plane against one ray
 // Plane::Intersect, RE/Shape.h:149-159: denom = n.d; |denom| > 1e-6; t = ((p0 - o).n) / denom; hit iff t >= 0.
-// FP32: den = n.L (error <= 6 eps), num = d - n.o (error <= en = 4 eps (|d| + |o|_1) + 1e-9).
-// Returns kCandMiss / kCandHit with t in [lo, hi] / kCandUnsure.
-__device__ __forceinline__ int plane_interval(const Plane32& p, float ox, float oy, float oz, float o1, float Lx, float Ly, float Lz, float& lo, float& hi,
-                                              float& den_out) {
+// FP32: den = n.L (error <= ed = 8 eps), num = d - n.o (error <= en = 4 eps (|d| + |o|_1) + 1e-9), so
+//   t = |num| / |den|  lies in  [(|num| - en) / (|den| + ed), (|num| + en) / (|den| - ed)].
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+struct PlaneND { float ad, an, ed, en; int cls; };  // cls: kCandMiss (no hit), kCandUnsure, kCandHit (t = an / ad >= 0 for certain)
+__device__ __forceinline__ PlaneND plane_nd(const Plane32& p, float ox, float oy, float oz, float o1, float Lx, float Ly, float Lz) {
     const float den = __fmaf_rn(p.nz, Lz, __fmaf_rn(p.ny, Ly, p.nx * Lx));
     const float num = p.d - __fmaf_rn(p.nz, oz, __fmaf_rn(p.ny, oy, p.nx * ox));
-    const float ed = 8.0f * kEps32, en = __fmaf_rn(4.0f * kEps32, fabsf(p.d) + o1, 1e-9f);
-    const float ad = fabsf(den), an = fabsf(num);
-    den_out = den;
+    PlaneND r;
+    r.ed = 8.0f * kEps32; r.en = __fmaf_rn(4.0f * kEps32, fabsf(p.d) + o1, 1e-9f);
+    r.ad = fabsf(den); r.an = fabsf(num);
+    if (r.ad < 1e-6f - r.ed) r.cls = kCandMiss;                          // parallel: rejected by the reference
+    else if (r.ad < 1e-6f + r.ed || r.an <= r.en) r.cls = kCandUnsure;    // |denom| ~ 1e-6, or the origin on the plane (t = 0 is a hit upstream)
+    else r.cls = ((num < 0.0f) != (den < 0.0f)) ? kCandMiss : kCandHit;  // t < 0: miss
+    return r;
+}
+// Primary rays: the distance as an interval.
+__device__ __forceinline__ int plane_interval(const Plane32& p, float ox, float oy, float oz, float o1, float Lx, float Ly, float Lz, float& lo, float& hi) {
+    const PlaneND r = plane_nd(p, ox, oy, oz, o1, Lx, Ly, Lz);
     lo = 0.0f; hi = 0.0f;
-    if (ad < 1e-6f - ed) return kCandMiss;          // parallel: rejected by the reference
-    if (ad < 1e-6f + ed) return kCandUnsure;
-    if (an <= en) return kCandUnsure;               // origin on the plane: t = 0 is a hit upstream, its sign is not decidable here
-    if ((num < 0.0f) != (den < 0.0f)) return kCandMiss;  // t < 0
-    const float t = an * __frcp_rn(ad);
-    const float rel = en * __frcp_rn(an) + ed * __frcp_rn(ad) + 4.0f * kEps32;
-    lo = t * (1.0f - rel); hi = t * (1.0f + rel);
-    return rel < 0.25f ? kCandHit : kCandUnsure;
+    if (r.cls != kCandHit) return r.cls;
+    lo = (r.an - r.en) * rcp_approx(r.ad + r.ed) * 0.999999f;
+    hi = (r.an + r.en) * rcp_approx(r.ad - r.ed) * 1.000001f;
+    return hi < 1.5f * lo + 1e-6f ? kCandHit : kCandUnsure;  // (a uselessly wide interval: leave the pixel to the exact code)
+}
+// Shadow rays: only the position of t against (bias, maxDist) matters — no division.
+//   kCandMiss: no effect (no hit, t < 0, or certainly beyond the light); kCandHit: certainly bias < t < maxDist; else kCandUnsure.
+__device__ __forceinline__ int plane_shadow(const Plane32& p, float ox, float oy, float oz, float o1, float Lx, float Ly, float Lz, float bias_hi,
+                                            float tmax_lo, float tmax_hi) {
+    const PlaneND r = plane_nd(p, ox, oy, oz, o1, Lx, Ly, Lz);
+    if (r.cls != kCandHit) return r.cls;
+    const float n_lo = r.an - r.en, n_hi = r.an + r.en, d_lo = r.ad - r.ed, d_hi = r.ad + r.ed;
+    if (n_lo > tmax_hi * d_hi) return kCandMiss;
+    if (n_lo > bias_hi * d_hi && n_hi < tmax_lo * d_lo) return kCandHit;
+    return kCandUnsure;
 }
 
 // ------------------------------------------------------------------------------ building the direction grids (rte_grid.cuh)
@@ -342,19 +362,20 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
     nr.kind = RTE_HIT_NONE; nr.idx = 0; nr.lo = 0.0f; nr.hi = 0.0f; nr.amb_lo = INFINITY;
     bool go0 = alive;
     grid_candidates(grid, 0, r.ux, r.uy, r.uz, go0, [&](int idx) {
-        const Cand32 c = classify_sphere(sc.sph64[idx], S.cam[0], S.cam[1], S.cam[2], r.ux, r.uy, r.uz, 0.0f);
+        const Cand32 c = classify_sphere(__ldg(sc.sph_hl + 2 * idx), __ldg(sc.sph_hl + 2 * idx + 1), S.cam_hi[0], S.cam_hi[1], S.cam_hi[2], S.cam_lo[0], S.cam_lo[1],
+                                         S.cam_lo[2], r.ux, r.uy, r.uz);
         float lo, hi;
         const int cls = reported_t(c, lo, hi);
         executed += 1u;
         if (cls == kCandHit) near_hit(nr, RTE_HIT_SPHERE, idx, lo, hi);
         else if (cls == kCandUnsure) near_unsure(nr, lo);
     });
-    const float cam32x = (float)S.cam[0], cam32y = (float)S.cam[1], cam32z = (float)S.cam[2];
+    const float cam32x = S.cam_hi[0], cam32y = S.cam_hi[1], cam32z = S.cam_hi[2];
     const float cam1 = fabsf(cam32x) + fabsf(cam32y) + fabsf(cam32z);
 #pragma unroll 1
     for (int i = 0; i < np; ++i) {  // planes after the spheres: a plane wins only when it is certainly closer
-        float lo, hi, den;
-        const int cls = plane_interval(S.pl[i], cam32x, cam32y, cam32z, cam1, r.ux, r.uy, r.uz, lo, hi, den);
+        float lo, hi;
+        const int cls = plane_interval(S.pl[i], cam32x, cam32y, cam32z, cam1, r.ux, r.uy, r.uz, lo, hi);
         if (cls == kCandHit) near_hit(nr, RTE_HIT_PLANE, i, lo, hi);
         else if (cls == kCandUnsure) near_unsure(nr, 0.0f);
     }
@@ -397,15 +418,23 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         out.prim = ((uint32_t)RTE_HIT_PLANE << 30) | (uint32_t)nr.idx;
     }
     mat = (mat >= 0 && mat < sc.nm) ? mat : sc.nm;
-    // shadow origin so = P + N * bias (RE/Scene.h:104)
-    const double sox = fma((double)Nx, (double)bias, Px), soy = fma((double)Ny, (double)bias, Py), soz = fma((double)Nz, (double)bias, Pz);
-    const float so32x = (float)sox, so32y = (float)soy, so32z = (float)soz;
+    // hit point as hi + lo floats; shadow origin so = P + N * bias (RE/Scene.h:104) as hi + lo floats through an error-free FP32 sum
+    const float Phx = (float)Px, Phy = (float)Py, Phz = (float)Pz;
+    const float Plx = (float)(Px - (double)Phx), Ply = (float)(Py - (double)Phy), Plz = (float)(Pz - (double)Phz);
+    float so32x, so32y, so32z, solx, soly, solz;
+    {
+        const float bx = Nx * bias, by = Ny * bias, bz = Nz * bias;
+        so32x = Phx + bx; so32y = Phy + by; so32z = Phz + bz;
+        // TwoSum: s = a + b exactly equals fl(s) + err
+        const float tx = so32x - Phx, ty = so32y - Phy, tz = so32z - Phz;
+        solx = Plx + ((Phx - (so32x - tx)) + (bx - tx)); soly = Ply + ((Phy - (so32y - ty)) + (by - ty)); solz = Plz + ((Phz - (so32z - tz)) + (bz - tz));
+    }
     const float so1 = fabsf(so32x) + fabsf(so32y) + fabsf(so32z);
     float ar = 0.0f, ag = 0.0f, ab = 0.0f;
     // ---- Scene::directLightning, RE/Scene.h:79-129 (diffuse term)
 #pragma unroll 1
     for (int j = 0; j < nl; ++j) {
-        const float vx = (float)(S.li_pos[j][0] - Px), vy = (float)(S.li_pos[j][1] - Py), vz = (float)(S.li_pos[j][2] - Pz);
+        const float vx = (S.li_hi[j][0] - Phx) + (S.li_lo[j][0] - Plx), vy = (S.li_hi[j][1] - Phy) + (S.li_lo[j][1] - Ply), vz = (S.li_hi[j][2] - Phz) + (S.li_lo[j][2] - Plz);
         const float d2 = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, vx * vx));
         float inv = rsqrtf(d2);
         inv = inv * __fmaf_rn(-0.5f * d2 * inv, inv, 1.5f);  // one Newton step: <= 1.5 ulp
@@ -429,7 +458,7 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         // are tested against the ray itself: origin so, direction L
         grid_candidates(grid, 1 + j, -Lx, -Ly, -Lz, go, [&](int idx) {
             if (idx == self) return;  // so lies outside the sphere the point is on, the ray leaves it: both roots < 0
-            const Cand32 c = classify_sphere(sc.sph64[idx], sox, soy, soz, Lx, Ly, Lz, 0.0f);
+            const Cand32 c = classify_sphere(__ldg(sc.sph_hl + 2 * idx), __ldg(sc.sph_hl + 2 * idx + 1), so32x, so32y, so32z, solx, soly, solz, Lx, Ly, Lz);
             float lo, hi;
             const int cls = reported_t(c, lo, hi);
             executed += 1u;
@@ -447,11 +476,9 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         if (cast && !occl && !unsure) {  // planes, any-hit in canonical order
 #pragma unroll 1
             for (int i = 0; i < np; ++i) {
-                float lo, hi, den;
-                const int cls = plane_interval(S.pl[i], so32x, so32y, so32z, so1, Lx, Ly, Lz, lo, hi, den);
+                const int cls = plane_shadow(S.pl[i], so32x, so32y, so32z, so1, Lx, Ly, Lz, bias_hi, tmax_lo, tmax_hi);
                 if (cls == kCandMiss) continue;
-                if (cls == kCandHit && lo > tmax_hi) continue;
-                if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; firstp = (uint32_t)i; break; }
+                if (cls == kCandHit) { occl = true; firstp = (uint32_t)i; break; }
                 ok = false; break;
             }
         }
@@ -562,9 +589,15 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
         }
         for (int j = 0; j < g.nl; ++j) {
             const DevLight l = g.lights[j];
-            for (int c = 0; c < 3; ++c) { s32.li_pos[j][c] = l.pos[c]; s32.li_E[j][c] = (float)l.E[c]; }
+            for (int c = 0; c < 3; ++c) {
+                s32.li_hi[j][c] = (float)l.pos[c]; s32.li_lo[j][c] = (float)(l.pos[c] - (double)s32.li_hi[j][c]);
+                s32.li_E[j][c] = (float)l.E[c];
+            }
         }
-        for (int c = 0; c < 3; ++c) s32.cam[c] = P.cam.pos[c];
+        for (int c = 0; c < 3; ++c) {
+            s32.cam[c] = P.cam.pos[c];
+            s32.cam_hi[c] = (float)P.cam.pos[c]; s32.cam_lo[c] = (float)(P.cam.pos[c] - (double)s32.cam_hi[c]);
+        }
     }
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
     __syncthreads();

@@ -356,7 +356,8 @@ def test_render_host_bands_equal_one_launch(engine, cfg):
         st = engine.stats()
         assert st["primary_rays"] == len(rows) * cam.width
         for k in outs:  # the same rows out of the full frame, rendered 500 rows per (single-launch) call
-            full = np.concatenate([engine.render_host(outputs=(k,), row0=a, row1=min(a + 500, cam.height), **opts)[k] for a in range(0, cam.height, 500)])
+            full = np.concatenate([engine.render_host(outputs=(k,), row0=a, row1=min(a + 500, cam.height), flags=_abi.FLAG_EXACT_FP64, **opts)[k]
+                                       for a in range(0, cam.height, 500)])  # (the striped call asked for hdr64: the exact path on both sides)
             full = full.reshape(cam.height, cam.width, -1)
             assert np.array_equal(got[k].reshape(len(rows), cam.width, -1), full[rows]), k
         return
