@@ -53,6 +53,7 @@ struct Scene32 {
     Plane32 pl[kR32Planes];
     float li_hi[kR32Lights][3], li_lo[kR32Lights][3];  // light position = hi + lo
     float li_E[kR32Lights][3];
+    float plA[kR32Lights][kR32Planes];  // n_i . Lp_j - d_i: the part of (n_i . L) * dist that does not depend on the pixel
     double cam[3];
     float cam_hi[3], cam_lo[3];
     int np, nl;
@@ -95,6 +96,21 @@ __device__ __forceinline__ Cand32 classify_sphere(const float4 hi, const float4 
     c.t0_hi = b - hc_lo + dl;
     c.t1_lo = b + hc_lo - dl;
     return c;
+}
+
+// Cheap rejection of a cell's candidate before the interval classification: with the hi halves only (absolute error of g up
+// to d = 2 eps (|o|_1 + |g|)), the squared distance line - centre  l2 = |g|^2 - (g.L)^2  carries an error of at most
+// E = 4 eps |g|^2 (cancellation, |L| = 1 +- 4 eps) + 2 |g| d + d^2; certainly a miss when l2 - E > (1.001 r)^2.
+// (sqrt-free: |g| <= (|g|^2 + 1) / 2.)  Most entries of a cell are spheres the ray passes at a distance.
+__device__ __forceinline__ bool far_miss(const float4 hi, float ox, float oy, float oz, float o1, float Lx, float Ly, float Lz) {
+    const float gx = hi.x - ox, gy = hi.y - oy, gz = hi.z - oz;
+    const float b = __fmaf_rn(gz, Lz, __fmaf_rn(gy, Ly, gx * Lx));
+    const float gg = __fmaf_rn(gz, gz, __fmaf_rn(gy, gy, gx * gx));
+    const float l2 = __fmaf_rn(-b, b, gg);
+    const float gn = 0.5f * gg + 0.5f;                                  // >= |g|
+    const float E = kEps32 * __fmaf_rn(4.0f * gn, o1 + gn, 16.0f * gg) + 1e-12f;  // >= 4 eps gg + 2 gn d + d^2 with d = 2 eps (o1 + gn)
+    const float r = hi.w * 1.001f;
+    return l2 - E > r * r;
 }
 
 // Sphere::Intersect's reported distance (RE/Shape.h:89-97: t0 unless t0 < 1e-6, then t1 unless t1 < 1e-6) as an interval.
@@ -155,13 +171,20 @@ __device__ __forceinline__ int plane_interval(const Plane32& p, float ox, float 
     hi = (r.an + r.en) * rcp_approx(r.ad - r.ed) * 1.000001f;
     return hi < 1.5f * lo + 1e-6f ? kCandHit : kCandUnsure;  // (a uselessly wide interval: leave the pixel to the exact code)
 }
-// Shadow rays: only the position of t against (bias, maxDist) matters — no division.
+// Shadow rays: only the position of t against (bias, maxDist) matters — no division, and no dot product per light either:
+//   den * dist = n . (Lp - so) = (n . Lp - d) + (d - n . so) = A + num,
+// A a constant of (plane, light) (Scene32::plA), num = d - n . so a value of (plane, pixel) that the caller computes once per pixel.
+//   t = num * dist / (A + num);   errors: num <= en, A + num <= e2 = eps |A| + en + eps |A + num|, dist relative 6 eps.
 //   kCandMiss: no effect (no hit, t < 0, or certainly beyond the light); kCandHit: certainly bias < t < maxDist; else kCandUnsure.
-__device__ __forceinline__ int plane_shadow(const Plane32& p, float ox, float oy, float oz, float o1, float Lx, float Ly, float Lz, float bias_hi,
-                                            float tmax_lo, float tmax_hi) {
-    const PlaneND r = plane_nd(p, ox, oy, oz, o1, Lx, Ly, Lz);
-    if (r.cls != kCandHit) return r.cls;
-    const float n_lo = r.an - r.en, n_hi = r.an + r.en, d_lo = r.ad - r.ed, d_hi = r.ad + r.ed;
+__device__ __forceinline__ int plane_shadow(float num, float en, float A, float dist, float bias_hi, float tmax_lo, float tmax_hi) {
+    const float den2 = A + num;
+    const float ad = fabsf(den2), an = fabsf(num);
+    const float e2 = __fmaf_rn(kEps32, fabsf(A) + ad, en);
+    const float par = 1e-6f * dist;                 // |denom| > 1e-6 of the reference, scaled by dist
+    if (ad + e2 < par * 0.99999f) return kCandMiss;  // parallel: rejected upstream
+    if (ad - e2 < par * 1.00001f || an <= en) return kCandUnsure;
+    if ((num < 0.0f) != (den2 < 0.0f)) return kCandMiss;  // t < 0
+    const float n_lo = (an - en) * dist * 0.999999f, n_hi = (an + en) * dist * 1.000001f, d_lo = ad - e2, d_hi = ad + e2;
     if (n_lo > tmax_hi * d_hi) return kCandMiss;
     if (n_lo > bias_hi * d_hi && n_hi < tmax_lo * d_lo) return kCandHit;
     return kCandUnsure;
@@ -332,7 +355,8 @@ struct Px32 {
     uint32_t prim, lmask;
     uint32_t c_shadow, c_sph, c_pl;  // statistics of this sample (SURVEY §8(d) algorithmic counts)
 };
-__device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S, int px, int py, bool alive, int sample, Px32& out, uint32_t& executed) {
+__device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S, float* __restrict__ pl_num, int px, int py, bool alive, int sample, Px32& out,
+                                        uint32_t& executed) {
     const DevScene& sc = P.sc;
     const DevGrid& grid = P.grid;
     const int ns = sc.ns, np = S.np, nl = S.nl;
@@ -360,18 +384,19 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
     // ---- Scene::IntersectClosest, RE/Scene.h:218-257, from intervals
     Near32 nr;
     nr.kind = RTE_HIT_NONE; nr.idx = 0; nr.lo = 0.0f; nr.hi = 0.0f; nr.amb_lo = INFINITY;
+    const float cam32x = S.cam_hi[0], cam32y = S.cam_hi[1], cam32z = S.cam_hi[2];
+    const float cam1 = fabsf(cam32x) + fabsf(cam32y) + fabsf(cam32z);
     bool go0 = alive;
     grid_candidates(grid, 0, r.ux, r.uy, r.uz, go0, [&](int idx) {
-        const Cand32 c = classify_sphere(__ldg(sc.sph_hl + 2 * idx), __ldg(sc.sph_hl + 2 * idx + 1), S.cam_hi[0], S.cam_hi[1], S.cam_hi[2], S.cam_lo[0], S.cam_lo[1],
-                                         S.cam_lo[2], r.ux, r.uy, r.uz);
+        const float4 shi = __ldg(sc.sph_hl + 2 * idx);
+        executed += 1u;
+        if (far_miss(shi, cam32x, cam32y, cam32z, cam1, r.ux, r.uy, r.uz)) return;
+        const Cand32 c = classify_sphere(shi, __ldg(sc.sph_hl + 2 * idx + 1), cam32x, cam32y, cam32z, S.cam_lo[0], S.cam_lo[1], S.cam_lo[2], r.ux, r.uy, r.uz);
         float lo, hi;
         const int cls = reported_t(c, lo, hi);
-        executed += 1u;
         if (cls == kCandHit) near_hit(nr, RTE_HIT_SPHERE, idx, lo, hi);
         else if (cls == kCandUnsure) near_unsure(nr, lo);
     });
-    const float cam32x = S.cam_hi[0], cam32y = S.cam_hi[1], cam32z = S.cam_hi[2];
-    const float cam1 = fabsf(cam32x) + fabsf(cam32y) + fabsf(cam32z);
 #pragma unroll 1
     for (int i = 0; i < np; ++i) {  // planes after the spheres: a plane wins only when it is certainly closer
         float lo, hi;
@@ -430,6 +455,10 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         solx = Plx + ((Phx - (so32x - tx)) + (bx - tx)); soly = Ply + ((Phy - (so32y - ty)) + (by - ty)); solz = Plz + ((Phz - (so32z - tz)) + (bz - tz));
     }
     const float so1 = fabsf(so32x) + fabsf(so32y) + fabsf(so32z);
+    // num_i = d_i - n_i . so of every plane, once per pixel (this thread's slots of pl_num: [plane][thread])
+#pragma unroll 1
+    for (int i = 0; i < np; ++i)
+        pl_num[i * kR32Threads] = S.pl[i].d - __fmaf_rn(S.pl[i].nz, so32z, __fmaf_rn(S.pl[i].ny, so32y, S.pl[i].nx * so32x));
     float ar = 0.0f, ag = 0.0f, ab = 0.0f;
     // ---- Scene::directLightning, RE/Scene.h:79-129 (diffuse term)
 #pragma unroll 1
@@ -458,13 +487,15 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         // are tested against the ray itself: origin so, direction L
         grid_candidates(grid, 1 + j, -Lx, -Ly, -Lz, go, [&](int idx) {
             if (idx == self) return;  // so lies outside the sphere the point is on, the ray leaves it: both roots < 0
-            const Cand32 c = classify_sphere(__ldg(sc.sph_hl + 2 * idx), __ldg(sc.sph_hl + 2 * idx + 1), so32x, so32y, so32z, solx, soly, solz, Lx, Ly, Lz);
-            float lo, hi;
-            const int cls = reported_t(c, lo, hi);
+            const float4 hi = __ldg(sc.sph_hl + 2 * idx);
             executed += 1u;
+            if (far_miss(hi, so32x, so32y, so32z, so1, Lx, Ly, Lz)) return;
+            const Cand32 c = classify_sphere(hi, __ldg(sc.sph_hl + 2 * idx + 1), so32x, so32y, so32z, solx, soly, solz, Lx, Ly, Lz);
+            float lo, hi2;
+            const int cls = reported_t(c, lo, hi2);
             if (cls == kCandMiss) return;
             if (lo > tmax_hi) return;  // behind the light: not an occluder, not `near`
-            if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) {  // certainly bias < t < maxDist
+            if (cls == kCandHit && lo > bias_hi && hi2 < tmax_lo) {  // certainly bias < t < maxDist
                 first = min(first, (uint32_t)idx);  // (the lists are unordered: the first occluder in canonical order is the smallest index)
                 occl = true;
                 return;
@@ -476,7 +507,8 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         if (cast && !occl && !unsure) {  // planes, any-hit in canonical order
 #pragma unroll 1
             for (int i = 0; i < np; ++i) {
-                const int cls = plane_shadow(S.pl[i], so32x, so32y, so32z, so1, Lx, Ly, Lz, bias_hi, tmax_lo, tmax_hi);
+                const float en = __fmaf_rn(4.0f * kEps32, fabsf(S.pl[i].d) + so1, 1e-9f);
+                const int cls = plane_shadow(pl_num[i * kR32Threads], en, S.plA[j][i], dist, bias_hi, tmax_lo, tmax_hi);
                 if (cls == kCandMiss) continue;
                 if (cls == kCandHit) { occl = true; firstp = (uint32_t)i; break; }
                 ok = false; break;
@@ -576,6 +608,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     __shared__ Scene32 s32;
     __shared__ unsigned long long s_stats[kR32Threads / 32][kStatCount];
     __shared__ uint32_t s_fixq[kR32Threads / 32][kFixCap];
+    __shared__ float s_plnum[kR32Planes][kR32Threads];  // per pixel: d_i - n_i . so of every plane (trace32)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int fix_n = 0;  // (warp-uniform) pixels waiting in s_fixq[warp]
     if (threadIdx.x == 0) {
@@ -594,6 +627,13 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
                 s32.li_E[j][c] = (float)l.E[c];
             }
         }
+        for (int j = 0; j < g.nl; ++j)
+            for (int i = 0; i < g.np; ++i) {
+                const DevPlane p = g.planes[i];
+                const DevLight l = g.lights[j];
+                const double d = p.n[0] * p.p0[0] + p.n[1] * p.p0[1] + p.n[2] * p.p0[2];
+                s32.plA[j][i] = (float)((p.n[0] * l.pos[0] + p.n[1] * l.pos[1] + p.n[2] * l.pos[2]) - d);
+            }
         for (int c = 0; c < 3; ++c) {
             s32.cam[c] = P.cam.pos[c];
             s32.cam_hi[c] = (float)P.cam.pos[c]; s32.cam_lo[c] = (float)(P.cam.pos[c] - (double)s32.cam_hi[c]);
@@ -612,6 +652,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     const int sr = P.stripe_rows, sp = P.stripe_period;
     const int tiles_x = (W + kTile32W - 1) / kTile32W, tiles_y = (rows + kTile32H - 1) / kTile32H;
     const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
+    const float inv_tiles_x = 1.0f / (float)tiles_x;
     const int lx = lane & (kTile32W - 1), ly = lane >> 3;
     const int aa = P.cam.aa;
     const bool words = (W & 3) == 0;  // rows of RGB8 are word aligned: a tile row of 8 pixels is six aligned words
@@ -622,7 +663,9 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     while (tile < n_tiles) {
         unsigned int next = 0;
         if (lane == 0) next = atomicAdd(P.tile_counter, 1u);  // the next tile id arrives behind the work
-        const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
+        int ty = (int)((float)tile * inv_tiles_x);  // tile / tiles_x without the integer-division sequence (tile < 2^24 for every frame <= 16K x 16K)
+        if ((unsigned)(ty * tiles_x) > tile) --ty; else if ((unsigned)((ty + 1) * tiles_x) <= tile) ++ty;
+        const int tx = (int)tile - ty * tiles_x;
         const int band_y = ty * kTile32H + ly, px = tx * kTile32W + lx;
         const int py = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
         const bool inb = px < W && band_y < rows;
@@ -634,7 +677,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
 #pragma unroll 1
         for (int s = 0; s < aa; ++s) {
             Px32 o;
-            ok = trace32(P, s32, px, py, inb, s, o, executed) && ok;
+            ok = trace32(P, s32, &s_plnum[0][threadIdx.x], px, py, inb, s, o, executed) && ok;
             cr += o.r; cg += o.g; cb += o.b;
             n_shadow += o.c_shadow; n_sph += o.c_sph; n_pl += o.c_pl;
             if (s == 0) { prim = o.prim; lmask = o.lmask; }
