@@ -5,7 +5,7 @@
  * boundary is the public C++ API of `Scene` plus the free functions of RaytracingEngine.cpp and
  * Image.cpp.  Each entry point below names the reference interface it replaces (file:line).
  * The C++20 host mirror (include/rte/engine.hpp) and the Python binding
- * (raytracingengine_b200/binding.py) are thin layers over exactly these symbols.
+ * (raytracingengine_b200/engine.py, struct mirrors in _abi.py) are thin layers over exactly these symbols.
  *
  * Conventions
  *   - plain pointers and sizes only; no C++/torch types cross this boundary;
@@ -268,6 +268,14 @@ int rte_tonemap(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t op_ma
                 double max_white, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]);
 int rte_tonemap_host(rte_ctx* ctx, const float* hdr, int64_t n_pixels, uint32_t op_mask,
                      double max_white, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]);
+/* tonemap() / tonemapAll() over the FP64 HDR the reference's functions take (std::vector<Vec3>, RE/RaytracingEngine.cpp:165,176):
+ * hdr64 = 3 doubles per pixel (HOST), rgb8[op] = 3 bytes per pixel (HOST).  The exact FP64 operators in the reference's
+ * evaluation order: the bytes are the reference's own (rte_tonemap / rte_tonemap_host are the fast FP32 pass, +-1 LSB). */
+int rte_tonemap_exact_host(rte_ctx* ctx, const double* hdr64, int64_t n_pixels, uint32_t op_mask,
+                           double max_white, double jodie_a, uint8_t* const rgb8[RTE_TM_COUNT]);
+/* The operator functions themselves — simple, reinhardSimple, reinhardExtended(max_white), reinhardExtendedLuminance(max_white),
+ * reinhardJodie(a), uncharted2, aces_approx (RE/RaytracingEngine.cpp:89-163) — on n FP64 colours: in3 / out3 = xyz triples (HOST). */
+int rte_tonemap_values_host(rte_ctx* ctx, int op, double max_white, double jodie_a, const double* in3, int64_t n, double* out3);
 /* Max of luminance() (RE/RaytracingEngine.cpp:100-104) over a device HDR buffer; the per-rank
  * value that an auto-max-white run all-reduces (MAX) across GPUs. Result on the host. */
 int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max);

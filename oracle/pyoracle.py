@@ -137,6 +137,19 @@ class Oracle:
         assert rc == 0
         return out
 
+    def load_obj(self, path):
+        """LoadObject(path) of the reference (tinyobjloader, RE/RaytracingEngine.cpp:15-65): (vertices (n,3) float64, indices int32).
+        Reference-built checker only."""
+        f = self._fn("load_obj")
+        nv, ni = C.c_int64(), C.c_int64()
+        if f(path.encode(), C.byref(nv), C.byref(ni), None, None) != 0:
+            raise RuntimeError("ref_load_obj failed")
+        v = np.zeros((nv.value, 3), dtype=np.float64)
+        i = np.zeros(ni.value, dtype=np.int32)
+        if f(path.encode(), C.byref(nv), C.byref(ni), C.c_void_p(v.ctypes.data), C.c_void_p(i.ctypes.data)) != 0:
+            raise RuntimeError("ref_load_obj failed")
+        return v, i
+
     def write_ppm(self, path, rgb8, width, height) -> int:
         a = np.ascontiguousarray(rgb8, dtype=np.uint8)
         return self._fn("write_ppm")(path.encode(), C.c_void_p(a.ctypes.data), C.c_uint64(width), C.c_uint64(height))

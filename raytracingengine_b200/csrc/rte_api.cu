@@ -865,6 +865,47 @@ extern "C" int rte_tonemap_host(rte_ctx* ctx, const float* hdr, int64_t n, uint3
     return RTE_OK;
 }
 
+// tonemap() / tonemapAll() over the FP64 HDR the reference's functions take (std::vector<Vec3>): the exact FP64 operators
+// (tm64), byte-identical to the reference's output.
+extern "C" int rte_tonemap_exact_host(rte_ctx* ctx, const double* hdr64, int64_t n, uint32_t mask, double max_white, double jodie_a,
+                                      uint8_t* const rgb8[RTE_TM_COUNT]) {
+    RTE_ENTER(ctx);
+    if (n < 0) return fail(ctx, RTE_ERR_INVALID, "n_pixels is negative");
+    if (mask == 0 || mask >= (1u << RTE_TM_COUNT)) return fail(ctx, RTE_ERR_INVALID, "op_mask 0x%x selects no / unknown operators", mask);
+    if ((n > 0 && !hdr64) || !rgb8) return fail(ctx, RTE_ERR_INVALID, "rte_tonemap_exact_host: NULL argument");
+    for (int op = 0; op < RTE_TM_COUNT; ++op)
+        if ((mask & (1u << op)) && n > 0 && !rgb8[op]) return fail(ctx, RTE_ERR_INVALID, "rgb8[%d] is NULL but its bit is set in op_mask", op);
+    if (n == 0) return RTE_OK;
+    int rc;
+    if ((rc = reserve(ctx, ctx->s_hdr64, (size_t)n * 24))) return rc;
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->s_hdr64.p, hdr64, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+    const double mw = max_white > 0 ? max_white : 5.0, ja = jodie_a > 0 ? jodie_a : 0.18;
+    for (int op = 0; op < RTE_TM_COUNT; ++op) {
+        if (!(mask & (1u << op))) continue;
+        if ((rc = reserve(ctx, ctx->s_tm_out[op], (size_t)n * 3 + 16))) return rc;
+        RTE_CUDA(ctx, launch_tonemap64_values((const double*)ctx->s_hdr64.p, n, op, mw, ja, nullptr, (uint8_t*)ctx->s_tm_out[op].p, ctx->sm_count, ctx->stream));
+        RTE_CUDA(ctx, cudaMemcpyAsync(rgb8[op], ctx->s_tm_out[op].p, (size_t)n * 3, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+
+// The operator functions themselves (simple ... aces_approx, RE/RaytracingEngine.cpp:89-163) on FP64 values: Vec3 -> Vec3.
+extern "C" int rte_tonemap_values_host(rte_ctx* ctx, int op, double max_white, double jodie_a, const double* in3, int64_t n, double* out3) {
+    RTE_ENTER(ctx);
+    if (op < 0 || op >= RTE_TM_COUNT) return fail(ctx, RTE_ERR_INVALID, "tonemap op %d is not an RTE_TM_* value", op);
+    if (n < 0 || (n > 0 && (!in3 || !out3))) return fail(ctx, RTE_ERR_INVALID, "rte_tonemap_values_host: bad arguments");
+    if (n == 0) return RTE_OK;
+    int rc;
+    if ((rc = reserve(ctx, ctx->s_hdr64, (size_t)n * 24)) || (rc = reserve(ctx, ctx->s_tm64, (size_t)n * 24))) return rc;
+    RTE_CUDA(ctx, cudaMemcpyAsync(ctx->s_hdr64.p, in3, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+    RTE_CUDA(ctx, launch_tonemap64_values((const double*)ctx->s_hdr64.p, n, op, max_white > 0 ? max_white : 5.0, jodie_a > 0 ? jodie_a : 0.18,
+                                          (double*)ctx->s_tm64.p, nullptr, ctx->sm_count, ctx->stream));
+    RTE_CUDA(ctx, cudaMemcpyAsync(out3, ctx->s_tm64.p, (size_t)n * 24, cudaMemcpyDeviceToHost, ctx->stream));
+    RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RTE_OK;
+}
+
 extern "C" int rte_max_luminance(rte_ctx* ctx, const float* hdr, int64_t n_pixels, float* out_max) {
     RTE_ENTER(ctx);
     if (!out_max || (n_pixels > 0 && !hdr) || n_pixels < 0) return fail(ctx, RTE_ERR_INVALID, "rte_max_luminance: bad arguments");

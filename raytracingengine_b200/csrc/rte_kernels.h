@@ -123,6 +123,9 @@ cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t st
 cudaError_t launch_max_luminance(const float4* hdr, int64_t n_pixels, unsigned int* out_bits, int sm_count,
                                  cudaStream_t stream);
 
+// tm64 over 3 doubles per pixel: the operator's FP64 result (out3) and / or its toColor bytes (rgb8)
+cudaError_t launch_tonemap64_values(const double* in3, int64_t n, int op, double max_white, double jodie_a, double* out3, uint8_t* rgb8, int sm_count,
+                                    cudaStream_t stream);
 // rte_max_luminance_noalloc: the same maximum into *out_dev (device float) with its scratch in a file-scope device array of
 // rte_tonemap.cu (no cudaMalloc); `device` = the current device; n_pixels <= RTE_NOALLOC_MAX_PIXELS
 cudaError_t launch_max_luminance_noalloc(const float4* hdr, int64_t n_pixels, float* out_dev, int device, cudaStream_t stream);

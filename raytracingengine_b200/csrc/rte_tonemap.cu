@@ -217,6 +217,27 @@ __global__ void __launch_bounds__(kTmThreads) max_luminance_kernel(const float4*
     }
 }
 
+// ------------------------------------------------------------------------------ exact operators over FP64 values
+// rte_tonemap_exact_host / rte_tonemap_values_host: tm64 (the reference's FP64 evaluation order, RE/RaytracingEngine.cpp:70-163)
+// over 3 doubles per pixel; `out3` receives the operator's Vec3 result, `rgb8` its toColor bytes (either may be NULL).
+__global__ void __launch_bounds__(kTmThreads) tonemap64_values_kernel(const double* __restrict__ in3, int64_t n, int op, double max_white, double jodie_a,
+                                                                      double* __restrict__ out3, uint8_t* __restrict__ rgb8) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const d3 v = mk(in3[3 * i], in3[3 * i + 1], in3[3 * i + 2]);
+        const d3 m = tm64::apply(op, v, max_white, jodie_a);
+        if (out3) { out3[3 * i] = m.x; out3[3 * i + 1] = m.y; out3[3 * i + 2] = m.z; }
+        if (rgb8) { const uchar3 u = tm64::to_color(m); rgb8[3 * i] = u.x; rgb8[3 * i + 1] = u.y; rgb8[3 * i + 2] = u.z; }
+    }
+}
+cudaError_t launch_tonemap64_values(const double* in3, int64_t n, int op, double max_white, double jodie_a, double* out3, uint8_t* rgb8, int sm_count,
+                                    cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    int64_t blocks = (n + kTmThreads - 1) / kTmThreads;
+    if (blocks > (int64_t)sm_count * 8) blocks = (int64_t)sm_count * 8;
+    tonemap64_values_kernel<<<(unsigned)blocks, kTmThreads, 0, stream>>>(in3, n, op, max_white, jodie_a, out3, rgb8);
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------ allocation-free variant
 // rte_max_luminance_noalloc (include/rte.h; no counterpart in the reference):
 // the same reduction in two stages — every block reduces one fixed chunk of kNaPixelsPerBlock pixels to a partial maximum,

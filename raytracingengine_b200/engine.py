@@ -21,7 +21,7 @@ LIB_PATH = os.environ.get("RTE_B200_LIB") or os.path.join(os.path.dirname(os.pat
 SYMBOLS = (
     "rte_version", "rte_device_count", "rte_last_error", "rte_create", "rte_destroy", "rte_set_stream",
     "rte_synchronize", "rte_upload_scene", "rte_set_camera", "rte_render", "rte_render_host", "rte_get_stats", "rte_last_render_launches",
-    "rte_tonemap", "rte_tonemap_host", "rte_tonemap_auto_white", "rte_max_luminance", "rte_max_luminance_device", "rte_max_luminance_noalloc", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
+    "rte_tonemap", "rte_tonemap_host", "rte_tonemap_exact_host", "rte_tonemap_values_host", "rte_tonemap_auto_white", "rte_max_luminance", "rte_max_luminance_device", "rte_max_luminance_noalloc", "rte_measure_fp32_peak", "rte_measure_fp32x2_peak", "rte_intersect_closest", "rte_intersect_any_before",
     "rte_malloc", "rte_free", "rte_memcpy_d2h", "rte_memcpy_h2d", "rte_malloc_host", "rte_free_host",
     "rte_write_ppm", "rte_write_png", "rte_set_rgb8_peers", "rte_set_fence_peers", "rte_frame_fence", "rte_ipc_export", "rte_ipc_open", "rte_ipc_close",
 )
@@ -63,6 +63,8 @@ def load_library() -> C.CDLL:
     tm_args = [C.c_void_p, C.c_void_p, C.c_int64, C.c_uint32, C.c_double, C.c_double, C.POINTER(C.c_void_p)]
     lib.rte_tonemap.argtypes = tm_args
     lib.rte_tonemap_host.argtypes = tm_args
+    lib.rte_tonemap_exact_host.argtypes = tm_args
+    lib.rte_tonemap_values_host.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_void_p, C.c_int64, C.c_void_p]
     lib.rte_max_luminance.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_float)]
     lib.rte_max_luminance_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     lib.rte_max_luminance_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
@@ -318,6 +320,23 @@ class Engine:
         out = {op: np.empty((n, 3), dtype=np.uint8) for op in range(_abi.TM_COUNT) if mask & (1 << op)}
         ptrs = (C.c_void_p * _abi.TM_COUNT)(*[C.c_void_p(out[op].ctypes.data) if op in out else None for op in range(_abi.TM_COUNT)])
         self._ck(self.lib.rte_tonemap_host(self.ctx, C.c_void_p(h.ctypes.data), n, mask, max_white, jodie_a, ptrs))
+        return out
+
+    def tonemap_exact_host(self, hdr64: np.ndarray, ops=None, max_white=0.0, jodie_a=0.0) -> Dict[int, np.ndarray]:
+        """tonemapAll / tonemap over the FP64 HDR (n,3) float64 — the exact FP64 operators: the reference's own bytes."""
+        h = np.ascontiguousarray(hdr64, dtype=np.float64).reshape(-1, 3)
+        n = len(h)
+        mask = self._mask(ops)
+        out = {op: np.empty((n, 3), dtype=np.uint8) for op in range(_abi.TM_COUNT) if mask & (1 << op)}
+        ptrs = (C.c_void_p * _abi.TM_COUNT)(*[C.c_void_p(out[op].ctypes.data) if op in out else None for op in range(_abi.TM_COUNT)])
+        self._ck(self.lib.rte_tonemap_exact_host(self.ctx, C.c_void_p(h.ctypes.data), n, mask, max_white, jodie_a, ptrs))
+        return out
+
+    def tonemap_values_host(self, op: int, colors: np.ndarray, max_white=0.0, jodie_a=0.0) -> np.ndarray:
+        """One operator function (simple ... aces_approx) on (n,3) float64 colours -> (n,3) float64."""
+        c = np.ascontiguousarray(colors, dtype=np.float64).reshape(-1, 3)
+        out = np.empty_like(c)
+        self._ck(self.lib.rte_tonemap_values_host(self.ctx, int(op), max_white, jodie_a, C.c_void_p(c.ctypes.data), len(c), C.c_void_p(out.ctypes.data)))
         return out
 
     def max_luminance(self, hdr_dev: int, n_pixels: int) -> float:

@@ -121,3 +121,26 @@ def test_auto_white_device_path(engine, port_oracle):
         assert np.array_equal(a, b)
         want = port_oracle.tonemap_one(op, hdr[:, :3].astype(np.float64), max_white=float(w[0]), jodie_a=0.18)
         assert np.abs(a.astype(np.int16) - want.astype(np.int16)).max() <= 1
+
+
+def test_exact_host_tonemap_is_byte_exact(engine, oracle):
+    """rte_tonemap_exact_host (what tonemap() / tonemapAll() of the host mirrors call): the FP64 operators over the FP64 HDR —
+    the reference's own bytes, on ordinary radiance, on the KAT vectors and on the edge values (0/0, negatives, inf, NaN)."""
+    with open(os.path.join(GOLD, "kat.json")) as f:
+        kat = json.load(f)["tonemap"]
+    rng = np.random.default_rng(3)
+    vals = [0.0, -0.0, 1e-30, -0.5, -1.0, 1.0, 5.0, 25.0, 1e10, 1e30, np.inf, -np.inf, np.nan]
+    hdr = np.concatenate([np.exp(rng.normal(-1.0, 2.0, (50001, 3))),
+                          np.array([[np.nan if v is None else v for v in row] for row in kat["hdr"]], dtype=np.float64),
+                          np.array([[a, b, c] for a in vals for b in vals[::3] for c in vals[1::4]], dtype=np.float64)])
+    got = engine.tonemap_exact_host(hdr)
+    want = oracle.tonemap_all(hdr)
+    for op in range(_abi.TM_COUNT):
+        assert np.array_equal(got[op], want[op]), f"{_abi.TM_NAMES[op]}: {np.count_nonzero(got[op] != want[op])} bytes differ"
+    part = engine.tonemap_exact_host(hdr, ops=[_abi.TM_ACES])
+    assert sorted(part) == [_abi.TM_ACES] and np.array_equal(part[_abi.TM_ACES], want[_abi.TM_ACES])
+    # the operator functions themselves: Vec3 -> Vec3 in FP64
+    _, fl = oracle.tonemap_all(hdr[:50001], want_float=True)
+    for op in range(_abi.TM_COUNT):
+        v = engine.tonemap_values_host(op, hdr[:50001], max_white=5.0, jodie_a=0.18)
+        np.testing.assert_allclose(v, fl[op], rtol=1e-13, atol=1e-300, equal_nan=True)

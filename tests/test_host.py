@@ -1,4 +1,6 @@
 """CPU suite: host-side logic — the reference-shaped scene API, scene fixtures, sharding index math."""
+import os
+
 import numpy as np
 import pytest
 
@@ -120,3 +122,55 @@ def test_algorithmic_flop_accounting():
     """20 / 14 / 46 flop per sphere / plane / triangle test; C2 primary pass = 170.3 GFLOP."""
     assert _abi.algorithmic_flops(1, 1, 1) == 80
     assert abs(8294400 * _abi.algorithmic_flops(1024, 4, 0) / 1e9 - 170.3) < 0.05
+
+
+TRICKY_OBJ = """# comments, blank lines, CRLF line ends, exponents, many digits, relative indices, polygons, slashes
+o first
+
+v 0.1 0.2 0.3
+v  -1.25e1   +3.5E-2  7
+v 0.333333333333333333 1234567.890123 -0.000001
+v 1e-3 2.e1 .5\r
+v 16777217 0.1000000014901161 -12.000000000000001
+vn 0 1 0
+vt 0.5 0.5
+g grp
+f 1 2 3
+f 1/1/1 2/1/1 3/1/1 4/1/1
+f 1//1 -1//1 -2//1 -3//1 2//1
+usemtl whatever
+o second
+v 9 8 7
+f -1 1 2 3 4 5
+f 2/1 3/1 6/1
+"""
+
+
+def test_load_object_reader_equals_tinyobjloader(tmp_path, ref_oracle):
+    """LoadObject of include/rte/engine.hpp (own OBJ reader) == the reference's LoadObject (vendored tinyobjloader 1.0.6,
+    RE/RaytracingEngine.cpp:15-65): same float-exact vertices, same flat index list (fan triangulation, relative indices)."""
+    import subprocess
+    import __graft_entry__ as ge
+    exe = os.path.join(ge.ROOT, "examples", "obj_probe")
+    if not os.path.exists(exe):
+        ge.build_obj_probe()
+    from raytracingengine_b200 import scenes
+    files = {"tricky.obj": TRICKY_OBJ}
+    p = tmp_path / "blob.obj"
+    v, faces = scenes.blob_mesh(level=2)
+    scenes.write_obj(str(p), v, faces)
+    files["blob.obj"] = None
+    for name, text in files.items():
+        path = tmp_path / name
+        if text is not None:
+            path.write_bytes(text.encode())
+        want_v, want_i = ref_oracle.load_obj(str(path))
+        out = subprocess.run([exe, str(path)], capture_output=True, text=True, check=True).stdout.split("\n")
+        nv, ni = map(int, out[0].split())
+        got_v = np.array([[float(x) for x in l.split()] for l in out[1:1 + nv]]).reshape(nv, 3)
+        got_i = np.array([int(l) for l in out[1 + nv:1 + nv + ni]], dtype=np.int32)
+        assert (nv, ni) == (len(want_v), len(want_i)), name
+        assert np.array_equal(got_v, want_v), name
+        assert np.array_equal(got_i, want_i), name
+    missing = subprocess.run([exe, str(tmp_path / "nope.obj")], capture_output=True, text=True)
+    assert missing.returncode == 1 and "Failed to load/parse .obj." in missing.stdout
