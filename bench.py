@@ -454,7 +454,7 @@ def sharding_text(pipe):
         return "single band"
     s = f"interleaved {pipe.stripe}-row stripes; "
     if pipe.gather == "peer":
-        return s + "RGB8 stored by the render kernel into every rank's frame over NVLink while it traces (CUDA IPC peer frames) + " + (
+        return s + "RGB8 band copied into every rank's frame over NVLink by the exchange launch behind the render kernel (16-byte peer stores, CUDA IPC peer frames) + " + (
             "frame fence through NVLink flags written by the call's last launch (rte_frame_fence), no collective" if pipe.use_flag_fence
             else "4-byte NCCL all-reduce as frame fence")
     return s + "NCCL all-gather of RGB8" + pipe.peer_note

@@ -606,17 +606,28 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
     // FP32 production path (rte_render32.cu): diffuse sphere / plane scenes with resident views, outputs hdr / rgb8 / prim_id /
     // light_mask.  The operator runs in the kernel; pixels with an inconclusive FP32 decision go through the exact fix-up launch.
-    // With registered peer frames the kernel stores its RGB8 into every rank's frame itself; the fix-up launch signals the fence.
     if (o.n_rows > 0 && fp32_path_eligible(p)) {
         if (p.out.rgb8 && ((uintptr_t)p.out.rgb8 & 3u) != 0 && (ctx->cam.width & 3) == 0) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 must be 4-byte aligned");
         int rc;
         if ((rc = ensure_grid(ctx, o.bias, p.grid))) return rc;
-        p.n_peers = p.tonemap_op == RTE_TM_NONE ? 0 : ctx->n_peers;
-        for (int i = 0; i < p.n_peers; ++i) p.peer_rgb8[i] = ctx->peer_rgb8[i];
-        if (ctx->n_fence > 0 && p.n_peers > 0) {
-            ctx->fence_seq += 1;
-            for (int i = 0; i < ctx->n_fence; ++i) p.fence_flags[i] = ctx->fence_flags[i];
-            p.n_fence = ctx->n_fence; p.fence_rank = ctx->fence_rank; p.fence_seq = ctx->fence_seq; p.fence_counter = ctx->d_fence_counter;
+        // multi-GPU output: the kernel writes RGB8 to a band buffer (the caller's, or scratch); the exchange launch behind it
+        // copies the band into every registered frame and signals the fence
+        Tonemap64Params xp{};
+        xp.n_peers = p.tonemap_op == RTE_TM_NONE ? 0 : ctx->n_peers;
+        if (xp.n_peers > 0) {
+            const size_t n_px = (size_t)o.n_rows * (size_t)ctx->cam.width;
+            if (!p.out.rgb8) {
+                if ((rc = reserve(ctx, ctx->s_rgb8, n_px * 3 + 16))) return rc;
+                p.out.rgb8 = (uint8_t*)ctx->s_rgb8.p;
+            }
+            xp.rgb8 = p.out.rgb8; xp.n_pixels = (int64_t)n_px;
+            for (int i = 0; i < xp.n_peers; ++i) xp.peer_rgb8[i] = ctx->peer_rgb8[i];
+            xp.W = ctx->cam.width; xp.row0 = o.row0; xp.stripe_rows = o.stripe_rows; xp.stripe_period = o.stripe_period;
+            if (ctx->n_fence > 0) {
+                ctx->fence_seq += 1;
+                for (int i = 0; i < ctx->n_fence; ++i) xp.fence_flags[i] = ctx->fence_flags[i];
+                xp.n_fence = ctx->n_fence; xp.fence_rank = ctx->fence_rank; xp.fence_seq = ctx->fence_seq; xp.fence_counter = ctx->d_fence_counter;
+            }
         }
         if (first) {
             RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * (kStatCount + 2), ctx->stream));
@@ -626,6 +637,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
         }
         RTE_CUDA(ctx, launch_render32(p, ctx->sm_count, ctx->stream));
         ctx->render_launches += 1;
+        if (xp.n_peers > 0) { RTE_CUDA(ctx, launch_exchange_rgb8(xp, ctx->sm_count, ctx->stream)); ctx->render_launches += 1; }
         if (last) {
             RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
             RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));

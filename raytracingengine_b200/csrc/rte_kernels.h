@@ -49,15 +49,6 @@ struct RenderParams {
     double2* hits;           // two-pass fast path: {t, (kind << 30 | index) as the low word of the second double} per band pixel
     int32_t exact_fp64;      // RTE_FLAG_EXACT_FP64: never take the FP32 production path (rte_render32.cu)
     DevGrid grid;            // FP32 path: per-origin direction grids (rte_grid.cuh), built per camera / bias
-    // FP32 path, multi-GPU output (rte_set_rgb8_peers / rte_set_fence_peers): the render kernel stores every tile row it finishes
-    // into every registered full frame at its image position (peer stores over NVLink while the SMs keep tracing); its last
-    // CTA signals the frame fence, see Tonemap64Params below
-    uint8_t* peer_rgb8[8];
-    int32_t n_peers;
-    uint32_t* fence_flags[8];
-    int32_t n_fence, fence_rank;
-    uint32_t fence_seq;
-    unsigned int* fence_counter;
     unsigned int* tile_counter;        // zeroed before launch
     unsigned long long* stats;         // kStatCount counters, zeroed before launch
 };
@@ -108,6 +99,8 @@ struct Tonemap64Params {
 // waits (device side, on `stream`) until flags[r] >= seq for every r < n; after timeout_ns writes 1 to *timed_out (mapped host word)
 cudaError_t launch_fence_wait(const uint32_t* flags, int n, uint32_t seq, unsigned long long timeout_ns, unsigned int* timed_out, cudaStream_t stream);
 cudaError_t launch_tonemap64(const Tonemap64Params& p, int sm_count, cudaStream_t stream);
+// FP32 path, multi-GPU: copies the band's RGB8 (p.rgb8, p.n_pixels, band row -> image row like above) into every p.peer_rgb8 frame and signals the fence
+cudaError_t launch_exchange_rgb8(const Tonemap64Params& p, int sm_count, cudaStream_t stream);
 
 // tonemapAll / tonemap over a float4 HDR buffer (stand-alone HBM-bound pass)
 struct TonemapParams {

@@ -584,10 +584,10 @@ static __device__ __noinline__ void fix_batch(const RenderParams& P, const uint3
             if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[pix] = make_float4((float)v.x, (float)v.y, (float)v.z, 0.f);
             if (P.out.prim_id) P.out.prim_id[pix] = prim0;
             if (P.out.light_mask) P.out.light_mask[pix] = lmask0;
-            if (P.out.rgb8 || P.n_peers > 0) {
+            if (P.out.rgb8) {
                 const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, v, P.max_white, P.jodie_a));  // the reference's own bytes
-                if (P.out.rgb8) { uint8_t* d = P.out.rgb8 + 3 * pix; d[0] = u.x; d[1] = u.y; d[2] = u.z; }
-                for (int r = 0; r < P.n_peers; ++r) { uint8_t* d = P.peer_rgb8[r] + 3 * ((int64_t)py * W + px); d[0] = u.x; d[1] = u.y; d[2] = u.z; }
+                uint8_t* d = P.out.rgb8 + 3 * pix;
+                d[0] = u.x; d[1] = u.y; d[2] = u.z;
             }
         }
     }
@@ -611,32 +611,32 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     __shared__ float s_plnum[kR32Planes][kR32Threads];  // per pixel: d_i - n_i . so of every plane (trace32)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int fix_n = 0;  // (warp-uniform) pixels waiting in s_fixq[warp]
-    if (threadIdx.x == 0) {
+    {   // scene constants: one thread per plane / light / (light, plane) pair (one thread doing all of it was ~15 us of serial loads)
         const DevScene& g = P.sc;
-        s32.np = g.np; s32.nl = g.nl;
-        for (int i = 0; i < g.np; ++i) {
+        const int t = (int)threadIdx.x;
+        if (t == 0) { s32.np = g.np; s32.nl = g.nl; }
+        if (t < 3) { s32.cam[t] = P.cam.pos[t]; s32.cam_hi[t] = (float)P.cam.pos[t]; s32.cam_lo[t] = (float)(P.cam.pos[t] - (double)s32.cam_hi[t]); }
+        if (t >= 32 && t < 32 + g.np) {
+            const int i = t - 32;
             const DevPlane p = g.planes[i];
             s32.pl[i].nx = (float)p.n[0]; s32.pl[i].ny = (float)p.n[1]; s32.pl[i].nz = (float)p.n[2];
             s32.pl[i].d = (float)(p.n[0] * p.p0[0] + p.n[1] * p.p0[1] + p.n[2] * p.p0[2]);
             s32.pl[i].mat = p.mat;
         }
-        for (int j = 0; j < g.nl; ++j) {
+        if (t >= 64 && t < 64 + g.nl) {
+            const int j = t - 64;
             const DevLight l = g.lights[j];
             for (int c = 0; c < 3; ++c) {
                 s32.li_hi[j][c] = (float)l.pos[c]; s32.li_lo[j][c] = (float)(l.pos[c] - (double)s32.li_hi[j][c]);
                 s32.li_E[j][c] = (float)l.E[c];
             }
         }
-        for (int j = 0; j < g.nl; ++j)
-            for (int i = 0; i < g.np; ++i) {
-                const DevPlane p = g.planes[i];
-                const DevLight l = g.lights[j];
-                const double d = p.n[0] * p.p0[0] + p.n[1] * p.p0[1] + p.n[2] * p.p0[2];
-                s32.plA[j][i] = (float)((p.n[0] * l.pos[0] + p.n[1] * l.pos[1] + p.n[2] * l.pos[2]) - d);
-            }
-        for (int c = 0; c < 3; ++c) {
-            s32.cam[c] = P.cam.pos[c];
-            s32.cam_hi[c] = (float)P.cam.pos[c]; s32.cam_lo[c] = (float)(P.cam.pos[c] - (double)s32.cam_hi[c]);
+        if (t >= 128 && t < 128 + g.nl * g.np) {
+            const int j = (t - 128) / g.np, i = (t - 128) - j * g.np;
+            const DevPlane p = g.planes[i];
+            const DevLight l = g.lights[j];
+            const double d = p.n[0] * p.p0[0] + p.n[1] * p.p0[1] + p.n[2] * p.p0[2];
+            s32.plA[j][i] = (float)((p.n[0] * l.pos[0] + p.n[1] * l.pos[1] + p.n[2] * l.pos[2]) - d);
         }
     }
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
@@ -692,25 +692,19 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
                 if (P.out.light_mask) P.out.light_mask[pix] = lmask;
             }
         }
-        if (P.out.rgb8 || P.n_peers > 0) {
+        if (P.out.rgb8) {
             const uint32_t rgb = tonemap_rgb24(P.tonemap_op, cr, cg, cb, K);  // (a flagged pixel's bytes are overwritten by fix_batch)
             const bool row_full = (tx + 1) * kTile32W <= W && band_y < rows;  // (uniform over the 8 lanes of a tile row)
-            const int64_t ipix = (int64_t)py * W + px;                           // position in a full frame (peer frames hold the whole image)
             if (words) {
                 // bytes 4 lx .. 4 lx + 3 of the row's 24: pixel q = 4 lx / 3 from its byte o = 4 lx % 3 on, then pixel q + 1
                 const int q = lx < 6 ? (4 * lx) / 3 : 6, o = lx < 6 ? (4 * lx) % 3 : 0;
                 const uint32_t a = __shfl_sync(kFullMask, rgb, (lane & ~7) + q), b = __shfl_sync(kFullMask, rgb, (lane & ~7) + q + 1);
                 const uint32_t word = o == 0 ? (a | (b << 24)) : o == 1 ? ((a >> 8) | (b << 16)) : ((a >> 16) | (b << 8));
-                if (row_full && lx < 6) {
-                    if (P.out.rgb8) __stcs(reinterpret_cast<uint32_t*>(P.out.rgb8 + 3 * ((int64_t)band_y * W + tx * kTile32W)) + lx, word);
-                    for (int i = 0; i < P.n_peers; ++i)
-                        __stcs(reinterpret_cast<uint32_t*>(P.peer_rgb8[i] + 3 * ((int64_t)py * W + tx * kTile32W)) + lx, word);
-                }
+                if (row_full && lx < 6) __stcs(reinterpret_cast<uint32_t*>(P.out.rgb8 + 3 * ((int64_t)band_y * W + tx * kTile32W)) + lx, word);
             }
             if (mine && !(words && row_full)) {
-                const uint8_t b0 = (uint8_t)rgb, b1 = (uint8_t)(rgb >> 8), b2 = (uint8_t)(rgb >> 16);
-                if (P.out.rgb8) { uint8_t* d = P.out.rgb8 + 3 * pix; d[0] = b0; d[1] = b1; d[2] = b2; }
-                for (int i = 0; i < P.n_peers; ++i) { uint8_t* d = P.peer_rgb8[i] + 3 * ipix; d[0] = b0; d[1] = b1; d[2] = b2; }
+                uint8_t* d = P.out.rgb8 + 3 * pix;
+                d[0] = (uint8_t)rgb; d[1] = (uint8_t)(rgb >> 8); d[2] = (uint8_t)(rgb >> 16);
             }
         }
         // ---- statistics of the pixels shaded here (fix_batch counts its own; fp64_confirms = pixel samples rendered again in FP64)
@@ -735,21 +729,6 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     if (fix_n > 0) fix_batch(P, s_fixq[warp], fix_n, s_stats[warp]);  // what is left of the warp's queue
     __syncwarp();
     if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
-    // Frame fence over NVLink (rte_set_fence_peers), fused into the kernel that does the peer stores: every thread makes its
-    // stores visible system-wide, the last CTA to get here tells every rank "rank `fence_rank` has delivered frame `seq`".
-    if (P.n_fence > 0) {
-        __threadfence_system();
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            const unsigned int done = atomicAdd(P.fence_counter, 1u);
-            if (done == gridDim.x - 1) {
-                *P.fence_counter = 0u;  // for the next launch (stream order)
-                __threadfence_system();
-                for (int r = 0; r < P.n_fence; ++r)
-                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.fence_flags[r] + P.fence_rank), "r"(P.fence_seq) : "memory");
-            }
-        }
-    }
 }
 
 // Can this render call take the FP32 path?  (rte_api.cu decides with it; everything else takes the exact kernels.)

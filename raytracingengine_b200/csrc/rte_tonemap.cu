@@ -177,6 +177,59 @@ __global__ void fence_wait_kernel(const uint32_t* flags, int n, uint32_t seq, un
     }
 }
 
+// ------------------------------------------------------------------------------ multi-GPU output exchange of the FP32 path
+// The FP32 render kernel writes its RGB8 to the band buffer of its own GPU; this launch, right behind it on the stream, copies
+// the band's rows into every registered full frame at their image rows (this GPU's and its peers', mapped over NVLink) with
+// 16-byte stores — the all-gather of the row stripes as plain wide peer stores — and signals the frame fence like
+// tonemap64_kernel does.  (Measured on 2 x B200: storing from the render kernel itself, 24 bytes per tile row and frame, costs the
+// kernel ~60 us; counting finished tiles to send whole segments needs a __threadfence per tile and costs more.)
+__global__ void __launch_bounds__(kTmThreads) exchange_rgb8_kernel(const __grid_constant__ Tonemap64Params P) {
+    const int64_t row_bytes = (int64_t)P.W * 3;
+    const int64_t n_rows = P.W > 0 ? P.n_pixels / P.W : 0;
+    const int sr = P.stripe_rows, sp = P.stripe_period;
+    bool v16 = ((row_bytes | (int64_t)(uintptr_t)P.rgb8) & 15) == 0;
+    for (int i = 0; i < P.n_peers; ++i) v16 = v16 && ((uintptr_t)P.peer_rgb8[i] & 15) == 0;
+    if (v16) {
+        const int64_t per_row = row_bytes >> 4, total = per_row * n_rows;
+        for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t br = k / per_row, c = k - br * per_row;
+            const int64_t iy = P.row0 + (sr > 0 ? (br / sr) * sp + br % sr : br);
+            const uint4 v = __ldcs(reinterpret_cast<const uint4*>(P.rgb8 + br * row_bytes) + c);
+            for (int i = 0; i < P.n_peers; ++i) __stcs(reinterpret_cast<uint4*>(P.peer_rgb8[i] + iy * row_bytes) + c, v);
+        }
+    } else {
+        const int64_t total = row_bytes * n_rows;
+        for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+            const int64_t br = k / row_bytes, c = k - br * row_bytes;
+            const int64_t iy = P.row0 + (sr > 0 ? (br / sr) * sp + br % sr : br);
+            const uint8_t v = P.rgb8[br * row_bytes + c];
+            for (int i = 0; i < P.n_peers; ++i) P.peer_rgb8[i][iy * row_bytes + c] = v;
+        }
+    }
+    if (P.n_fence > 0) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned int done = atomicAdd(P.fence_counter, 1u);
+            if (done == gridDim.x - 1) {
+                *P.fence_counter = 0u;  // for the next launch (stream order)
+                __threadfence_system();
+                for (int r = 0; r < P.n_fence; ++r)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.fence_flags[r] + P.fence_rank), "r"(P.fence_seq) : "memory");
+            }
+        }
+    }
+}
+cudaError_t launch_exchange_rgb8(const Tonemap64Params& p, int sm_count, cudaStream_t stream) {
+    const int64_t units = (p.n_pixels * 3 + 15) / 16;
+    int64_t blocks = (units + kTmThreads - 1) / kTmThreads;
+    const int64_t cap = (int64_t)sm_count * 4;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    exchange_rgb8_kernel<<<(unsigned)blocks, kTmThreads, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_fence_wait(const uint32_t* flags, int n, uint32_t seq, unsigned long long timeout_ns, unsigned int* timed_out, cudaStream_t stream) {
     if (n <= 0) return cudaSuccess;
     fence_wait_kernel<<<1, 32, 0, stream>>>(flags, n, seq, timeout_ns, timed_out);
