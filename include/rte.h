@@ -34,7 +34,7 @@ typedef enum rte_status {
     RTE_ERR_CUDA = -2,      /* CUDA runtime error (sticky for the ctx) */
     RTE_ERR_NO_DEVICE = -3, /* no usable CUDA device: there is no CPU path */
     RTE_ERR_IO = -4,        /* file open / write failure (RE/Image.cpp:14-16,26-28) */
-    RTE_ERR_LIMIT = -5,     /* scene exceeds a documented capacity */
+    RTE_ERR_LIMIT = -5,     /* a documented capacity is exceeded (2^30 primitives per class, 4096 lights, RTE_MAX_AA, RTE_MAX_DEPTH, ...) */
     RTE_ERR_TIMEOUT = -6    /* rte_frame_fence: a peer did not deliver its frame in time */
 } rte_status;
 
@@ -172,6 +172,8 @@ typedef struct rte_render_opts {
  *   NO_CULL        the lean kernel scans every view in full instead of the per-tile culled copy;
  *   SINGLE_PASS /  the lean kernel traces primary rays and shades in one launch / in two launches (primary hits, then
  *   TWO_PASS       shading); without either flag large frames of heavy scenes take two launches, everything else one.
+ *   EXACT_GRID     the exact path of a diffuse scene walks the per-origin direction grids (one pixel per thread, no shared-memory
+ *                  staging) even where the view-based kernels apply; it is what scenes too large for those kernels take anyway.
  * And one switch that selects the numerics of the PRODUCTION path:
  *   EXACT_FP64     never take the FP32 production path.  Without it, a call that asks for hdr / rgb8 / prim_id / light_mask
  *                  only, on a diffuse sphere / plane scene, is shaded in FP32 (hit index and shadow visibility bit-exact — every
@@ -179,7 +181,7 @@ typedef struct rte_render_opts {
  *                  RGB8 within +-1 LSB of the reference: the bars BASELINE.json states).  Every FP64 output (hdr64, depth64), the
  *                  other AOVs and every flag above select the exact FP64 path, whose results are the reference's own bits. */
 enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4, RTE_FLAG_NO_CULL = 8, RTE_FLAG_SINGLE_PASS = 16, RTE_FLAG_TWO_PASS = 32,
-       RTE_FLAG_EXACT_FP64 = 64 };
+       RTE_FLAG_EXACT_FP64 = 64, RTE_FLAG_EXACT_GRID = 128 };
 
 /* Output buffers of one render call.  Every pointer is optional (NULL = not wanted) and is a
  * DEVICE pointer for rte_render() and a HOST pointer for rte_render_host().  Each buffer holds

@@ -39,6 +39,7 @@ TM_SIMPLE, TM_REINHARD_SIMPLE, TM_REINHARD_EXT, TM_REINHARD_EXT_LUM, TM_REINHARD
 FLAG_EXACT_SHADOWS, FLAG_NO_FILTER, FLAG_GENERAL_KERNEL, FLAG_NO_CULL = 1, 2, 4, 8
 FLAG_SINGLE_PASS, FLAG_TWO_PASS = 16, 32
 FLAG_EXACT_FP64 = 64
+FLAG_EXACT_GRID = 128
 IPC_HANDLE_BYTES = 64  # RTE_IPC_HANDLE_BYTES
 MAX_PEERS = 8          # RTE_MAX_PEERS
 MAX_DEPTH = 24         # RTE_MAX_DEPTH

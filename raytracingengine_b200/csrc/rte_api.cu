@@ -350,7 +350,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
         if (counts[i] < 0) return fail(ctx, RTE_ERR_INVALID, "n_%s is negative", names[i]);
         if (counts[i] > 0 && !ptrs[i]) return fail(ctx, RTE_ERR_INVALID, "%s is NULL with n_%s = %lld", names[i], names[i], (long long)counts[i]);
     }
-    if (d->n_lights > 16) return fail(ctx, RTE_ERR_LIMIT, "at most 16 lights (light_mask AOV is 16+16 bits), got %lld", (long long)d->n_lights);
+    if (d->n_lights > 4096) return fail(ctx, RTE_ERR_LIMIT, "at most 4096 lights, got %lld", (long long)d->n_lights);  // (light_mask covers the first 16)
     if (d->n_spheres >= (1ll << 30) || d->n_planes >= (1ll << 30)) return fail(ctx, RTE_ERR_LIMIT, "primitive index does not fit 30 bits");
 
     // materials (+ the default Material at index nm, RE/Shape.h:13-19)
@@ -460,12 +460,6 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
         put3(lights[i].E, hmul(h3(d->lights[i].color), d->lights[i].intensity));
     }
 
-    const size_t smem = (size_t)ns_pad * 16 + (size_t)nt_pad * 48;
-    const size_t smem_budget = ctx->smem_optin > 4096 ? ctx->smem_optin - 4096 : 0;  // static smem + headroom
-    if (smem > smem_budget)
-        return fail(ctx, RTE_ERR_LIMIT, "scene filter arrays need %zu B of shared memory (%d spheres, %d triangles); the per-CTA limit is %zu B",
-                    smem, ns, nt, smem_budget);
-
     int rc;
     const int nt_pad32 = nt > 96 ? (nt + 63) & ~63 : (nt + 31) & ~31;  // like ns_pad
     if ((rc = reserve(ctx, ctx->b_views, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
@@ -554,7 +548,7 @@ static int ensure_grid(rte_ctx* ctx, double bias, DevGrid& out) {
         RTE_CUDA(ctx, launch_grid_count_scan(ctx->sc, ctx->cam, bias, G, (uint32_t*)ctx->b_grid_count.p, (uint32_t*)ctx->b_grid_start.p,
                                              (unsigned long long*)ctx->b_grid_aggr.p, ctx->grid_epoch, ctx->stream));
         RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_grid_total, (uint32_t*)ctx->b_grid_start.p + n_cells, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        const long long shape = ((long long)ctx->sc.ns << 24) ^ ((long long)ctx->sc.nl << 12) ^ (long long)G;
+        const long long shape = ((long long)(ctx->sc.ns + ctx->sc.nt) << 24) ^ ((long long)ctx->sc.nl << 12) ^ (long long)G;
         if (ctx->grid_shape != shape || ctx->b_grid_entries.cap == 0) {
             RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
             const size_t total = *ctx->h_grid_total;
@@ -602,6 +596,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     p.out = *frame;
     p.pass_mode = (o.flags & RTE_FLAG_SINGLE_PASS) ? 1 : (o.flags & RTE_FLAG_TWO_PASS) ? 2 : 0;
     p.exact_fp64 = (o.flags & RTE_FLAG_EXACT_FP64) ? 1 : 0;
+    p.exact_grid = (o.flags & RTE_FLAG_EXACT_GRID) ? 1 : 0;
     p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
     if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
     // FP32 production path (rte_render32.cu): diffuse sphere / plane scenes with resident views, outputs hdr / rgb8 / prim_id /
@@ -644,6 +639,11 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
             ctx->render_timed = true;
         }
         return RTE_OK;
+    }
+    if (o.n_rows > 0 && exact_grid_wanted(p)) {  // the exact path on the direction grids (any scene size): needs the grids, not the views
+        int rc = ensure_grid(ctx, o.bias, p.grid);
+        if (rc) return rc;
+        p.plan.use_views = 0; p.plan.use_tri_views = 0;
     }
     if (p.pass_mode != 1 && o.n_rows > 0 && two_pass_wanted(p)) {  // nearest hits between the two launches of the fast path (16 B per pixel)
         int rc = reserve(ctx, ctx->s_hits, (size_t)o.n_rows * (size_t)ctx->cam.width * sizeof(double2));

@@ -18,10 +18,13 @@ struct PixelCounters {
     uint32_t shadow, secondary, sph, pl, tri, marches, confirms, sph_exec;
 };
 
-// Scene::IntersectClosest (RE/Scene.h:218-257) over {spheres of the cell + near list of `view`} and all planes.  The lists are
-// unordered, so "the first of equal distances wins" (strict '<' in canonical order) is applied by index.
+// Scene::IntersectClosest (RE/Scene.h:218-257) over {primitives of the cell + near list of `view`} and all planes.  The lists are
+// unordered, so the reference's rule — canonical order spheres, planes, triangles (each by ascending index), replace only when
+// strictly closer, i.e. of equal distances the FIRST wins — is applied explicitly: a sphere beats everything it ties with except a
+// sphere of lower index, a plane beats the triangles it ties with, a triangle only triangles of higher index.
 __device__ __forceinline__ void closest_hit_grid(const DevScene& sc, const DevGrid& g, int view, float ux, float uy, float uz, d3 o, d3 d, Hit& best) {
     best.t = 0.0; best.kind = RTE_HIT_NONE; best.idx = 0;
+    const uint32_t ns = (uint32_t)sc.ns;
     uint32_t cell = grid_cell(g, view, ux, uy, uz);
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
@@ -30,8 +33,16 @@ __device__ __forceinline__ void closest_hit_grid(const DevScene& sc, const DevGr
         for (uint32_t e = e0; e < e1; ++e) {
             const uint32_t k = g.entries[e];
             double t;
-            if (sphere_exact(sc.sph64[k], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t || (t == best.t && k < best.idx))) {
-                best.t = t; best.kind = RTE_HIT_SPHERE; best.idx = k;
+            if (k < ns) {
+                if (sphere_exact(sc.sph64[k], o, d, t) &&
+                    (best.kind == RTE_HIT_NONE || t < best.t || (t == best.t && (best.kind != RTE_HIT_SPHERE || k < best.idx)))) {
+                    best.t = t; best.kind = RTE_HIT_SPHERE; best.idx = k;
+                }
+            } else {
+                const uint32_t ti = k - ns;
+                if (tri_exact(sc.tri64[ti], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t || (t == best.t && best.kind == RTE_HIT_TRIANGLE && ti < best.idx))) {
+                    best.t = t; best.kind = RTE_HIT_TRIANGLE; best.idx = ti;
+                }
             }
         }
         cell = grid_near_cell(g, view);
@@ -39,19 +50,23 @@ __device__ __forceinline__ void closest_hit_grid(const DevScene& sc, const DevGr
 #pragma unroll 1
     for (int i = 0; i < sc.np; ++i) {
         double t;
-        if (plane_exact(sc.planes[i], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t)) { best.t = t; best.kind = RTE_HIT_PLANE; best.idx = (uint32_t)i; }
+        if (plane_exact(sc.planes[i], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t || (t == best.t && best.kind == RTE_HIT_TRIANGLE))) {
+            best.t = t; best.kind = RTE_HIT_PLANE; best.idx = (uint32_t)i;
+        }
     }
 }
 
 // One pixel sample, exactly: TraceRay + directLightning + computeTransmittance (RE/Scene.h:131-198, 79-129, 35-77) for scenes
-// without specular / transparent materials and without triangles (what the FP32 path accepts) — in two parts, so that the
+// without specular materials (no secondary rays; transparent occluders are handled by the literal march) — in two parts, so that the
 // lanes of a warp can share one pixel: every lane evaluates the primary hit, lane j the light j (rte_render32.cu: fix_batch).
 struct ExactHit {
     bool hit;
     d3 Pn, normal;   // hit point, viewer-facing unit normal (directLightning re-normalises, RE/Scene.h:81)
     d3 sky;          // Scene::backgroundColor of a miss
+    d3 ngeo;         // HitInfo.normal (geometric, un-flipped)
+    double t;        // HitInfo.distance
     int mat;
-    uint32_t prim;   // (type << 30) | index, kMiss
+    uint32_t prim;   // (type << 30) | reported index (triangles of a model report the MODEL index, RE/Shape.h:276), kMiss
 };
 static __device__ __noinline__ void exact_primary(const RenderParams& P, const DevScene& sc, int px, int py, int sample, ExactHit& out) {
     const d3 cam_o = ld3(P.cam.pos);
@@ -60,14 +75,18 @@ static __device__ __noinline__ void exact_primary(const RenderParams& P, const D
     closest_hit_grid(sc, P.grid, 0, (float)d.x, (float)d.y, (float)d.z, cam_o, d, h);
     out.hit = h.kind != RTE_HIT_NONE;
     out.prim = kMiss; out.mat = sc.nm;
-    out.Pn = mk(0.0, 0.0, 0.0); out.normal = mk(0.0, 0.0, 1.0);
+    out.Pn = mk(0.0, 0.0, 0.0); out.normal = mk(0.0, 0.0, 1.0); out.ngeo = mk(0.0, 0.0, 0.0); out.t = 0.0;
     out.sky = mk(0.0, 0.0, 0.0);
     if (!out.hit) { out.sky = mk(0.0, 0.0, 0.0) + background(d) * 1.0; return; }  // sky (RE/Scene.h:137-141)
+    out.t = h.t;
     out.Pn = cam_o + d * h.t;
     d3 ng;
+    uint32_t report = h.idx;
     if (h.kind == RTE_HIT_SPHERE) { const double4 s = sc.sph64[h.idx]; ng = normalize(out.Pn - mk(s.x, s.y, s.z)); }
-    else ng = ld3(sc.planes[h.idx].n);
-    out.prim = (h.kind << 30) | h.idx;
+    else if (h.kind == RTE_HIT_PLANE) ng = ld3(sc.planes[h.idx].n);
+    else { ng = ld3(sc.tri64[h.idx].n); report = (uint32_t)sc.tri_info[h.idx].y; }
+    out.ngeo = ng;
+    out.prim = (h.kind << 30) | report;
     out.mat = material_of(sc, h);
     const d3 incoming = normalize(d);
     const bool frontFace = dot(ng, incoming) < 0.0;
@@ -95,26 +114,29 @@ static __device__ __noinline__ d3 exact_light(const RenderParams& P, const DevSc
     d3 o = H.Pn + H.normal * bias;
     const double maxDist = dist - bias;
     const float ux = (float)(-L.x), uy = (float)(-L.y), uz = (float)(-L.z);
-    {   // algorithmic test counts: canonical order up to and including the first occluder
-        uint32_t first = (uint32_t)sc.ns;
+    {   // algorithmic test counts: canonical order (spheres, planes, triangles) up to and including the first occluder
+        const uint32_t ns = (uint32_t)sc.ns, nt = (uint32_t)sc.nt;
+        uint32_t first = ns, first_t = nt;
         uint32_t cell = grid_cell(g, 1 + j, ux, uy, uz);
         for (int pass = 0; pass < 2; ++pass) {
             for (uint32_t e = g.cell_start[cell]; e < g.cell_start[cell + 1]; ++e) {
                 const uint32_t k = g.entries[e];
                 double t;
-                if (sphere_exact(sc.sph64[k], o, L, t) && t > bias && t < maxDist && k < first) first = k;
+                if (k < ns) { if (k < first && sphere_exact(sc.sph64[k], o, L, t) && t > bias && t < maxDist) first = k; }
+                else if (k - ns < first_t && tri_exact(sc.tri64[k - ns], o, L, t) && t > bias && t < maxDist) first_t = k - ns;
             }
             cell = grid_near_cell(g, 1 + j);
         }
-        if (first < (uint32_t)sc.ns) cnt.sph += first + 1u;
+        if (first < ns) cnt.sph += first + 1u;
         else {
-            cnt.sph += (uint32_t)sc.ns;
+            cnt.sph += ns;
             uint32_t firstp = (uint32_t)sc.np;
             for (int i = 0; i < sc.np; ++i) {
                 double t;
                 if (plane_exact(sc.planes[i], o, L, t) && t > bias && t < maxDist) { firstp = (uint32_t)i; break; }
             }
-            cnt.pl += firstp < (uint32_t)sc.np ? firstp + 1u : (uint32_t)sc.np;
+            if (firstp < (uint32_t)sc.np) cnt.pl += firstp + 1u;
+            else { cnt.pl += (uint32_t)sc.np; cnt.tri += first_t < nt ? first_t + 1u : nt; }
         }
     }
     double T = 1.0, traveled = 0.0;

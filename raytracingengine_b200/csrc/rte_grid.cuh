@@ -17,7 +17,8 @@
 // still decides every candidate itself (rte_render32.cu: FP32 intervals; rte_render.cu fixup_kernel: the exact FP64 tests).
 //
 // Layout (CSR): cells of view j start at j * cells_per_view; cell = face * G*G + iv * G + iu; the view's near list is its
-// last cell (index 6 G*G).  cell_start[c] .. cell_start[c + 1] index `entries` (sphere indices, unordered).
+// last cell (index 6 G*G).  cell_start[c] .. cell_start[c + 1] index `entries` (unordered primitive indices: spheres first,
+// then the triangles — standalone ones and every model's — through their bounding spheres).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -26,7 +27,7 @@ namespace rte {
 
 struct DevGrid {
     const uint32_t* cell_start;  // n_views * cells_per_view + 1 offsets
-    const uint32_t* entries;     // sphere indices
+    const uint32_t* entries;     // primitive indices: spheres [0, ns), triangles ns + (flattened triangle index)
     int32_t G;                   // cells per edge of a cube face
     int32_t cells_per_view;      // 6 G^2 + 1
 };

@@ -47,6 +47,7 @@ struct RenderParams {
     int32_t cta_cull;        // streamed views: the CTA-level cull scratch follows the per-warp scratch (rte_views.cuh)
     int32_t pass_mode;       // fast kernel: 0 = auto, 1 = RTE_FLAG_SINGLE_PASS, 2 = RTE_FLAG_TWO_PASS (primary-ray launch + shading launch)
     double2* hits;           // two-pass fast path: {t, (kind << 30 | index) as the low word of the second double} per band pixel
+    int32_t exact_grid;      // RTE_FLAG_EXACT_GRID: the exact path walks the direction grids (render_exact_grid_kernel) even where the views fit
     int32_t exact_fp64;      // RTE_FLAG_EXACT_FP64: never take the FP32 production path (rte_render32.cu)
     DevGrid grid;            // FP32 path: per-origin direction grids (rte_grid.cuh), built per camera / bias
     unsigned int* tile_counter;        // zeroed before launch
@@ -59,6 +60,7 @@ size_t scene_smem_bytes(const DevScene& sc);
 cudaError_t launch_render(const RenderParams& p, int sm_count, cudaStream_t stream);
 // FP32 production path (rte_render32.cu) and the exact fix-up of its flagged pixels (rte_render.cu)
 bool fp32_path_eligible(const RenderParams& p);
+bool exact_grid_wanted(const RenderParams& p);  // exact path: render_exact_grid_kernel (needs p.grid)
 // direction grids: count + scan (cell_start[n_cells] = number of entries), then — with `entries` of at least that capacity — fill
 // (`aggregates`: grid_scan_blocks(n_cells) 64-bit words of scratch; `epoch`: a number that differs from build to build)
 int grid_scan_blocks(int n_cells);

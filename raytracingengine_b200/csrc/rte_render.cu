@@ -85,6 +85,9 @@ SmemPlan plan_smem(const DevScene& sc, size_t budget) {
     } else {
         pl.stage_sph = 1;
     }
+    // the generic arrays are staged only while they fit next to the views: what does not fit is read from global memory (L1 / L2)
+    if (pl.stage_tri && (size_t)pl.view_bytes + pl.tview_bytes + tri > budget) pl.stage_tri = 0;
+    if (pl.stage_sph && (size_t)pl.view_bytes + pl.tview_bytes + (pl.stage_tri ? tri : 0) + sph > budget) pl.stage_sph = 0;
     pl.sph_bytes = pl.stage_sph ? (uint32_t)sph : 0u;
     pl.tri_bytes = pl.stage_tri ? (uint32_t)tri : 0u;
     pl.total = (size_t)pl.view_bytes + pl.tview_bytes + pl.sph_bytes + pl.tri_bytes;
@@ -454,6 +457,84 @@ __global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __gr
         for (int k = 0; k < kStatCount; ++k) {
             const uint32_t s = __reduce_add_sync(kFullMask, v[k]);
             if (lane == 0) s_stats[warp][k] += s;
+        }
+        tile = __shfl_sync(kFullMask, next, 0);
+    }
+    __syncwarp();
+    if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
+}
+
+// ------------------------------------------------------------------------------ the exact path on the direction grids
+// Diffuse scenes (no specular / transparent material: no secondary rays) of ANY size: every primary and shadow ray looks up one
+// cell of its origin's direction grid (rte_grid.cuh) and runs the reference's exact FP64 tests, in the reference's order with its
+// tie rule, over that cell's spheres and triangles (rte_exact_grid.cuh) — O(cell) instead of O(primitives) per ray, nothing staged
+// in shared memory, so there is no capacity limit (the view-based kernels above need (1 + lights) x primitives x 16 B per CTA).
+// One pixel per lane; all outputs of rte_frame except rgb8 (the FP64 operator pass follows, like behind the other exact kernels).
+__global__ void __launch_bounds__(kRenderThreads, 2) render_exact_grid_kernel(const __grid_constant__ RenderParams P) {
+    __shared__ DevScene s_sc;
+    __shared__ unsigned long long s_stats[kRenderThreads / 32][kStatCount];
+    if (threadIdx.x == 0) s_sc = P.sc;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane < kStatCount) s_stats[warp][lane] = 0ull;
+    __syncthreads();
+    const DevScene& sc = s_sc;
+    const int W = P.cam.width, rows = P.n_rows, sr = P.stripe_rows, sp = P.stripe_period, aa = P.cam.aa, nl = sc.nl;
+    const int tiles_x = (W + kTileW - 1) / kTileW, tiles_y = (rows + kTileH - 1) / kTileH;
+    const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
+    const int lx = lane & (kTileW - 1), ly = lane >> 3;
+    unsigned int tile = 0;
+    if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
+    tile = __shfl_sync(kFullMask, tile, 0);
+    while (tile < n_tiles) {
+        unsigned int next = 0;
+        if (lane == 0) next = atomicAdd(P.tile_counter, 1u);
+        const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
+        const int band_y = ty * kTileH + ly, px = tx * kTileW + lx;
+        const int py = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
+        const bool inb = px < W && band_y < rows;
+        const int64_t oi = (int64_t)band_y * W + px;
+        PixelCounters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
+        uint32_t n_prim = 0;
+        if (inb) {
+            d3 v = mk(0.0, 0.0, 0.0);
+#pragma unroll 1
+            for (int s = 0; s < aa; ++s) {  // GeneratePixelAt, RE/Scene.h:283-304
+                ExactHit H;
+                exact_primary(P, sc, px, py, s, H);
+                cnt.sph += (uint32_t)sc.ns; cnt.pl += (uint32_t)sc.np; cnt.tri += (uint32_t)sc.nt;
+                d3 diffuse = mk(0.0, 0.0, 0.0);
+                uint32_t lmask = 0u;
+#pragma unroll 1
+                for (int j = 0; j < nl; ++j) {  // directLightning, RE/Scene.h:86-127
+                    uint32_t bits;
+                    const d3 c = exact_light(P, sc, H, j, bits, cnt);
+                    if (bits & 1u) diffuse = diffuse + c;
+                    if (j < 16) lmask |= (((bits >> 16) & 1u) << (16 + j)) | ((bits & 1u) << j);
+                }
+                const d3 e = exact_finish(sc, H, diffuse);
+                if (aa > 1) v = v + e; else v = e;
+                if (s == 0) {  // AOVs of the primary hit of the unjittered sample
+                    if (P.out.prim_id) P.out.prim_id[oi] = H.prim;
+                    if (P.out.depth) P.out.depth[oi] = H.hit ? (float)H.t : INFINITY;
+                    if (P.out.depth64) P.out.depth64[oi] = H.hit ? H.t : (double)INFINITY;
+                    if (P.out.normal) reinterpret_cast<float4*>(P.out.normal)[oi] = make_float4((float)H.ngeo.x, (float)H.ngeo.y, (float)H.ngeo.z, 0.f);
+                    if (P.out.albedo) {
+                        const d3 a = H.hit ? ld3(sc.materials[H.mat].color) : H.sky;
+                        reinterpret_cast<float4*>(P.out.albedo)[oi] = make_float4((float)a.x, (float)a.y, (float)a.z, 0.f);
+                    }
+                    if (P.out.light_mask) P.out.light_mask[oi] = lmask;
+                }
+                n_prim += 1u;
+            }
+            if (aa > 1) v = v / (double)aa;
+            if (P.out.hdr) __stcs(reinterpret_cast<float4*>(P.out.hdr) + oi, make_float4((float)v.x, (float)v.y, (float)v.z, 0.f));
+            if (P.out.hdr64) { __stcs(P.out.hdr64 + 3 * oi, v.x); __stcs(P.out.hdr64 + 3 * oi + 1, v.y); __stcs(P.out.hdr64 + 3 * oi + 2, v.z); }
+        }
+        const uint32_t st[kStatCount] = {n_prim, cnt.shadow, 0u, cnt.sph, cnt.pl, cnt.tri, cnt.marches, 0u, 0u};
+#pragma unroll
+        for (int k = 0; k < kStatCount; ++k) {
+            const uint32_t t = __reduce_add_sync(kFullMask, st[k]);
+            if (lane == 0) s_stats[warp][k] += t;
         }
         tile = __shfl_sync(kFullMask, next, 0);
     }
@@ -1095,8 +1176,27 @@ bool two_pass_wanted(const RenderParams& p) {
     return entries >= 2048 && pixels >= (5ll << 18);  // C2, 1/N of the 4K frame (tools/pass_probe.py): two launches win down to 1/6 (1.4 Mpx), lose at 1/8
 }
 
+// Does this exact-path call take the grid kernel?  Diffuse scenes when asked for (RTE_FLAG_EXACT_GRID), when the per-origin views
+// do not fit one CTA's shared memory, or with more lights than the view kernels keep in shared memory.
+bool exact_grid_wanted(const RenderParams& p) {
+    if (p.sc.reflective || p.exact_shadows || p.no_filter || p.sc.ns + p.sc.nt == 0) return false;
+    if (p.exact_grid) return true;
+    if (p.sc.nl > kSmemLights) return true;
+    if (p.sc.ns > 0 && !p.plan.use_views) return true;
+    if (p.sc.nt > 0 && !p.plan.use_tri_views) return true;
+    return false;
+}
+
 cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t stream) {
     RenderParams p = p0;
+    if (p.grid.cell_start && exact_grid_wanted(p)) {
+        const long long n_tiles = (long long)((p.cam.width + kTileW - 1) / kTileW) * ((p.n_rows + kTileH - 1) / kTileH);
+        long long blocks = (long long)sm_count * 2;
+        const long long needed = (n_tiles + kRenderThreads / 32 - 1) / (kRenderThreads / 32);
+        if (blocks > needed) blocks = needed > 0 ? needed : 1;
+        void* args[] = {(void*)&p};
+        return cudaLaunchKernel((const void*)render_exact_grid_kernel, dim3((unsigned)blocks), dim3(kRenderThreads), args, 0, stream);
+    }
     if (p.plan.stream_views && !(fast_path_eligible(p) && !p.force_general)) {
         // only the fast kernel streams views: AOV / validation renders of a large scene use the generic filters
         p.plan = generic_plan(p.sc);
@@ -1230,12 +1330,27 @@ __global__ void __launch_bounds__(kRenderThreads, 2) any_before_kernel(const __g
     }
 }
 
+static size_t smem_budget() {  // dynamic shared memory one CTA of this device may have (minus the kernels' static part)
+    static thread_local int dev_cached = -1;
+    static thread_local size_t budget = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev != dev_cached) {
+        int optin = 0;
+        cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+        budget = optin > 8192 ? (size_t)optin - 8192 : 0;
+        dev_cached = dev;
+    }
+    return budget;
+}
+// generic FP32 filter arrays only: staged when they fit (two CTAs per SM: half the budget), else read from global memory
 static SmemPlan generic_plan(const DevScene& sc) {
     SmemPlan pl{};
-    pl.stage_sph = 1;
-    pl.stage_tri = 1;
-    pl.sph_bytes = (uint32_t)((size_t)sc.ns_pad * 16);
-    pl.tri_bytes = (uint32_t)((size_t)sc.nt_pad * 48);
+    const size_t sph = (size_t)sc.ns_pad * 16, tri = (size_t)sc.nt_pad * 48, budget = smem_budget();
+    pl.stage_tri = tri <= budget ? 1 : 0;
+    pl.stage_sph = (pl.stage_tri ? tri : 0) + sph <= budget ? 1 : 0;
+    pl.sph_bytes = pl.stage_sph ? (uint32_t)sph : 0u;
+    pl.tri_bytes = pl.stage_tri ? (uint32_t)tri : 0u;
     pl.total = (size_t)pl.sph_bytes + pl.tri_bytes;
     return pl;
 }

@@ -15,6 +15,8 @@
 //    or exact, and those pixels (~1e-3 of a frame) are the reference's own bits.
 //  * The operator + toColor run in the kernel (tm32, rte_tonemap.cuh) and a tile row of 8 pixels leaves as six aligned
 //    32-bit words: no FP64 HDR scratch, no second pass.
+#include <algorithm>
+
 #include "rte_exact_grid.cuh"
 #include "rte_grid.cuh"
 #include "rte_kernels.h"
@@ -203,25 +205,40 @@ struct GridBuildParams {
     uint32_t* entries;
     uint32_t capacity;     // of `entries`
 };
-__device__ __forceinline__ void grid_view_sphere(const GridBuildParams& B, int j, int i, double& fx, double& fy, double& fz, double& r) {
-    const double4 s = B.sc.sph64[i];
+// Primitive i of the grid: spheres [0, ns), then the triangles [ns, ns + nt) through their bounding spheres (centroid, farthest
+// vertex: a ray that hits the triangle hits that sphere).
+__device__ __forceinline__ void grid_view_prim(const GridBuildParams& B, int j, int i, double& fx, double& fy, double& fz, double& r) {
+    double cx, cy, cz, rad;
+    if (i < B.sc.ns) {
+        const double4 s = B.sc.sph64[i];
+        cx = s.x; cy = s.y; cz = s.z; rad = fabs(s.w);
+    } else {
+        const DevTri64 T = B.sc.tri64[i - B.sc.ns];
+        const double ax = T.a0[0], ay = T.a0[1], az = T.a0[2];
+        const double bx = ax + T.e1[0], by = ay + T.e1[1], bz = az + T.e1[2], qx = ax + T.e2[0], qy = ay + T.e2[1], qz = az + T.e2[2];
+        cx = (ax + bx + qx) * (1.0 / 3.0); cy = (ay + by + qy) * (1.0 / 3.0); cz = (az + bz + qz) * (1.0 / 3.0);
+        const double da = (ax - cx) * (ax - cx) + (ay - cy) * (ay - cy) + (az - cz) * (az - cz);
+        const double db = (bx - cx) * (bx - cx) + (by - cy) * (by - cy) + (bz - cz) * (bz - cz);
+        const double dc = (qx - cx) * (qx - cx) + (qy - cy) * (qy - cy) + (qz - cz) * (qz - cz);
+        rad = sqrt(fmax(da, fmax(db, dc))) * (1.0 + 1e-9) + 1e-300;
+    }
     const double ox = j == 0 ? B.cam[0] : B.sc.lights[j - 1].pos[0], oy = j == 0 ? B.cam[1] : B.sc.lights[j - 1].pos[1],
                  oz = j == 0 ? B.cam[2] : B.sc.lights[j - 1].pos[2];
-    fx = s.x - ox; fy = s.y - oy; fz = s.z - oz;
+    fx = cx - ox; fy = cy - oy; fz = cz - oz;
     const double F = sqrt(fx * fx + fy * fy + fz * fz);
-    // |r| (+ bias for a light's grid: the shadow line passes the light within `bias`), + the lateral reach of an FP32 direction
-    r = (fabs(s.w) + (j > 0 ? B.bias : 0.0)) * (1.0 + 1e-9) + 4e-6 * F + 1e-12;
+    // radius (+ bias for a light's grid: the shadow line passes the light within `bias`), + the lateral reach of an FP32 direction
+    r = (rad + (j > 0 ? B.bias : 0.0)) * (1.0 + 1e-9) + 4e-6 * F + 1e-12;
 }
-// One WARP per (view, sphere): the lanes walk the cells of the sphere's rectangles together (a sphere close to a light covers
+// One WARP per (view, primitive): the lanes walk the cells of the sphere's rectangles together (a sphere close to a light covers
 // hundreds of cells; one thread issuing that many dependent atomics was 0.4 ms of tail).
 template <bool kFill>
 __global__ void __launch_bounds__(256) grid_build_kernel(const GridBuildParams B) {
-    const int total = B.n_views * B.sc.ns, lane = threadIdx.x & 31;
+    const int n_prims = B.sc.ns + B.sc.nt, total = B.n_views * n_prims, lane = threadIdx.x & 31;
     const int warps = (gridDim.x * blockDim.x) >> 5;
     for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < total; t += warps) {
-        const int j = t / B.sc.ns, i = t - j * B.sc.ns;
+        const int j = t / n_prims, i = t - j * n_prims;
         double fx, fy, fz, r;
-        grid_view_sphere(B, j, i, fx, fy, fz, r);
+        grid_view_prim(B, j, i, fx, fy, fz, r);
         const uint32_t base = (uint32_t)j * (uint32_t)B.cells_per_view;
         auto add = [&](uint32_t cell) {
             if (!kFill) { atomicAdd(B.count + cell, 1u); return; }
@@ -304,16 +321,17 @@ int grid_scan_blocks(int n_cells) { return (n_cells + kScanChunk - 1) / kScanChu
 cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start,
                                    unsigned long long* aggregates, uint32_t epoch, cudaStream_t stream) {
     const GridBuildParams B = grid_params(sc, cam, bias, G, count, cell_start, nullptr, 0);
-    const int total = B.n_views * sc.ns, n_cells = B.n_views * B.cells_per_view;
-    if (total > 0) grid_build_kernel<false><<<(total + 7) / 8, 256, 0, stream>>>(B);
+    const long long total = (long long)B.n_views * (sc.ns + sc.nt);
+    const int n_cells = B.n_views * B.cells_per_view;
+    if (total > 0) grid_build_kernel<false><<<(unsigned)std::min<long long>((total + 7) / 8, 1 << 20), 256, 0, stream>>>(B);
     grid_scan_kernel<<<grid_scan_blocks(n_cells), kScanThreads, 0, stream>>>(count, cell_start, n_cells, aggregates, epoch);
     return cudaGetLastError();
 }
 cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
                              uint32_t capacity, cudaStream_t stream) {
     const GridBuildParams B = grid_params(sc, cam, bias, G, count, cell_start, entries, capacity);
-    const int total = B.n_views * sc.ns;
-    if (total > 0) grid_build_kernel<true><<<(total + 7) / 8, 256, 0, stream>>>(B);
+    const long long total = (long long)B.n_views * (sc.ns + sc.nt);
+    if (total > 0) grid_build_kernel<true><<<(unsigned)std::min<long long>((total + 7) / 8, 1 << 20), 256, 0, stream>>>(B);
     return cudaGetLastError();
 }
 
@@ -559,6 +577,7 @@ static __device__ __noinline__ void fix_batch(const RenderParams& P, const uint3
         for (int s = 0; s < aa; ++s) {  // GeneratePixelAt, RE/Scene.h:283-304
             ExactHit H;
             H.hit = false; H.sky = mk(0.0, 0.0, 0.0); H.prim = kMiss; H.mat = sc.nm; H.Pn = mk(0.0, 0.0, 0.0); H.normal = mk(0.0, 0.0, 1.0);
+            H.ngeo = mk(0.0, 0.0, 0.0); H.t = 0.0;
             if (act) exact_primary(P, sc, px, py, s, H);
             PixelCounters c = {0, 0, 0, 0, 0, 0, 0, 0};
             d3 contrib = mk(0.0, 0.0, 0.0);

@@ -234,9 +234,9 @@ def test_errors(engine):
         engine.render_host(outputs=("hdr",), max_depth=_abi.MAX_DEPTH + 1)
     bad = scenes.config3(scale=0.05)[0]
     bad.materials = bad.materials[:3]  # sphere materials out of range are fine (default Material), NULL arrays are not
-    bad.lights = np.zeros(17, dtype=_abi.light_dt)
+    bad.lights = np.zeros(4097, dtype=_abi.light_dt)
     with pytest.raises(RteError):
-        engine.upload(bad, cam)  # more lights than the light_mask AOV has bits
+        engine.upload(bad, cam)  # more lights than the documented capacity (4096; light_mask covers the first 16)
     engine.upload(arrays, cam)  # the ctx stays usable after argument errors
     assert engine.render_host(outputs=("prim_id",))["prim_id"].size == cam.width * cam.height
 
