@@ -60,6 +60,7 @@ struct rte_ctx {
     long long grid_shape = -1;        // (ns, nl, G) of the build the entries buffer was sized for
     bool grid_check_pending = false;  // the last build was not followed by a read-back of its entry count yet
     bool grid_dirty = true;
+    size_t grid_call_px = 0;  // pixels of the API call being served (ensure_grid sizes the cells by it)
     double grid_bias = -1.0;
     int grid_G = 0;
     unsigned int* h_grid_total = nullptr;  // pinned: number of (sphere, cell) entries of the last build
@@ -531,23 +532,29 @@ extern "C" int rte_set_camera(rte_ctx* ctx, const rte_camera* c) {
 // pass never writes beyond it, the count travels to a pinned word and is checked at the next synchronisation point
 // (check_grid_overflow).  RTE_GRID_G (environment, developer knob): cells per cube-face edge.
 static int ensure_grid(rte_ctx* ctx, double bias, DevGrid& out) {
-    int G = 128;  // measured on B200 (C2 / C5 at 4K): 32: 1.01 / 3.34 ms, 64: 0.89 / 2.59, 96: 0.86 / 2.40, 128: 0.84 / 2.30, 192: 0.83 / 2.23 (the build grows with G^2)
+    // Finer cells = fewer candidates per ray, but the build grows with G^2 and is paid per frame.  Measured on B200, render +
+    // rebuild, C2 / C5(8 lights) at 4K: G = 48: 0.946 / -, 64: 0.928 / 2.62 ms, 96: 0.914 / 2.53, 128: 0.914 / 2.53; one eighth
+    // of the rows (one rank of eight): 48: 0.183 / -, 64: 0.190 / 0.458, 96: 0.194 / 0.476, 128: 0.200 / 0.518.
+    const size_t px = ctx->grid_call_px;
+    int G = px >= (4u << 20) ? 128 : px >= (2u << 20) ? 96 : px >= (768u << 10) ? 64 : 48;
     if (const char* e = std::getenv("RTE_GRID_G")) { const int v = std::atoi(e); if (v >= 4 && v <= 512) G = v; }
     const int n_views = 1 + ctx->sc.nl, cpv = 6 * G * G + 1;
     const size_t n_cells = (size_t)n_views * (size_t)cpv;
     if (ctx->grid_dirty || ctx->grid_bias != bias || ctx->grid_G != G) {
         int rc;
         const size_t aggr_bytes = (size_t)grid_scan_blocks((int)n_cells) * 8;
+        const size_t count_cap_was = ctx->b_grid_count.cap;
         if ((rc = reserve(ctx, ctx->b_grid_count, n_cells * 4)) || (rc = reserve(ctx, ctx->b_grid_start, (n_cells + 1) * 4))) return rc;
+        if (ctx->b_grid_count.cap != count_cap_was) {  // the counters are all zero between builds: the fill pass counts them back down
+            RTE_CUDA(ctx, cudaMemsetAsync(ctx->b_grid_count.p, 0, ctx->b_grid_count.cap, ctx->stream));
+        }
         if (ctx->b_grid_aggr.cap < aggr_bytes) {
             if ((rc = reserve(ctx, ctx->b_grid_aggr, aggr_bytes))) return rc;
             RTE_CUDA(ctx, cudaMemsetAsync(ctx->b_grid_aggr.p, 0, ctx->b_grid_aggr.cap, ctx->stream));  // (epoch 0 is never used)
         }
         ctx->grid_epoch = ctx->grid_epoch == 0xFFFFFFFFu ? 1u : ctx->grid_epoch + 1u;
-        RTE_CUDA(ctx, cudaMemsetAsync(ctx->b_grid_count.p, 0, n_cells * 4, ctx->stream));
         RTE_CUDA(ctx, launch_grid_count_scan(ctx->sc, ctx->cam, bias, G, (uint32_t*)ctx->b_grid_count.p, (uint32_t*)ctx->b_grid_start.p,
-                                             (unsigned long long*)ctx->b_grid_aggr.p, ctx->grid_epoch, ctx->stream));
-        RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_grid_total, (uint32_t*)ctx->b_grid_start.p + n_cells, 4, cudaMemcpyDeviceToHost, ctx->stream));
+                                             (unsigned long long*)ctx->b_grid_aggr.p, ctx->grid_epoch, ctx->h_grid_total, ctx->stream));
         const long long shape = ((long long)(ctx->sc.ns + ctx->sc.nt) << 24) ^ ((long long)ctx->sc.nl << 12) ^ (long long)G;
         if (ctx->grid_shape != shape || ctx->b_grid_entries.cap == 0) {
             RTE_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -710,6 +717,7 @@ extern "C" int rte_render(rte_ctx* ctx, const rte_render_opts* opts, const rte_f
     Defaults o;
     int rc = resolve_opts(ctx, opts, o);
     if (rc) return rc;
+    ctx->grid_call_px = (size_t)o.n_rows * (size_t)ctx->cam.width;
     return do_render(ctx, o, frame);
 }
 
@@ -722,6 +730,7 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
     if (rc) return rc;
     const size_t W = (size_t)ctx->cam.width;
     const size_t n = (size_t)o.n_rows * W;
+    ctx->grid_call_px = n;
     rte_frame df{};
     struct Item { void* host; DevBuf* buf; size_t px_bytes; void** dev; };
     Item items[] = {

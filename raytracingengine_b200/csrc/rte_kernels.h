@@ -65,7 +65,7 @@ bool exact_grid_wanted(const RenderParams& p);  // exact path: render_exact_grid
 // (`aggregates`: grid_scan_blocks(n_cells) 64-bit words of scratch; `epoch`: a number that differs from build to build)
 int grid_scan_blocks(int n_cells);
 cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start,
-                                   unsigned long long* aggregates, uint32_t epoch, cudaStream_t stream);
+                                   unsigned long long* aggregates, uint32_t epoch, uint32_t* total_host, cudaStream_t stream);
 cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
                              uint32_t capacity, cudaStream_t stream);
 cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream);

@@ -229,32 +229,73 @@ __device__ __forceinline__ void grid_view_prim(const GridBuildParams& B, int j, 
     // radius (+ bias for a light's grid: the shadow line passes the light within `bias`), + the lateral reach of an FP32 direction
     r = (rad + (j > 0 ? B.bias : 0.0)) * (1.0 + 1e-9) + 4e-6 * F + 1e-12;
 }
-// One WARP per (view, primitive): the lanes walk the cells of the sphere's rectangles together (a sphere close to a light covers
-// hundreds of cells; one thread issuing that many dependent atomics was 0.4 ms of tail).
+// One WARP per (view, primitive).  Lane f < 6 works out face f's rectangle (the FP64 square roots and divisions once per face);
+// the warp walks small rectangles together, rectangles of more than kGridBigRect cells (a sphere close to a light covers
+// thousands) are handed to the whole block, and every thread keeps several atomics in flight: the fill pass waits for each
+// atomic's return value, and one warp walking such a rectangle alone was a 0.4 ms tail on C5.
+constexpr int kGridBuildThreads = 256, kGridBuildWarps = kGridBuildThreads / 32, kGridBigRect = 128;
 template <bool kFill>
-__global__ void __launch_bounds__(256) grid_build_kernel(const GridBuildParams B) {
-    const int n_prims = B.sc.ns + B.sc.nt, total = B.n_views * n_prims, lane = threadIdx.x & 31;
-    const int warps = (gridDim.x * blockDim.x) >> 5;
-    for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < total; t += warps) {
-        const int j = t / n_prims, i = t - j * n_prims;
-        double fx, fy, fz, r;
-        grid_view_prim(B, j, i, fx, fy, fz, r);
-        const uint32_t base = (uint32_t)j * (uint32_t)B.cells_per_view;
-        auto add = [&](uint32_t cell) {
-            if (!kFill) { atomicAdd(B.count + cell, 1u); return; }
-            const uint32_t pos = B.cell_start[cell] + (atomicSub(B.count + cell, 1u) - 1u);
-            if (pos < B.capacity) B.entries[pos] = (uint32_t)i;
-        };
-        if (grid_sphere_is_near(fx, fy, fz, r)) { if (lane == 0) add(base + (uint32_t)(6 * B.G * B.G)); continue; }
-        for (int face = 0; face < 6; ++face) {
-            GridRect rc;
-            if (!grid_rect(B.G, face, fx, fy, fz, r, rc)) continue;  // (warp-uniform: every lane computes the same rectangle)
-            const int w = rc.iu1 - rc.iu0 + 1, n = w * (rc.iv1 - rc.iv0 + 1);
-            for (int c = lane; c < n; c += 32) {
-                const int iv = rc.iv0 + c / w, iu = rc.iu0 + c % w;
-                add(base + (uint32_t)(face * B.G * B.G + iv * B.G + iu));
+__global__ void __launch_bounds__(kGridBuildThreads) grid_build_kernel(const GridBuildParams B) {
+    __shared__ int s_big[kGridBuildWarps * 6][6];  // face base cell, iu0, iv0, width, cells, primitive
+    __shared__ int s_nbig;
+    const int n_prims = B.sc.ns + B.sc.nt, total = B.n_views * n_prims, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int GG = B.G * B.G;
+    // cells [c0, c0 + step * kUnroll) of a rectangle, `step` apart: the atomics are independent, the stores follow
+    auto add_cells = [&](uint32_t face_base, int iu0, int iv0, int w, int n, int prim, int c0, int step) {
+        constexpr int kUnroll = 4;
+        for (int c = c0; c < n; c += step * kUnroll) {
+            uint32_t cell[kUnroll], pos[kUnroll];
+#pragma unroll
+            for (int k = 0; k < kUnroll; ++k) {
+                const int cc = c + k * step;
+                cell[k] = cc < n ? face_base + (uint32_t)((iv0 + cc / w) * B.G + iu0 + cc % w) : 0xFFFFFFFFu;
+            }
+            if (!kFill) {
+#pragma unroll
+                for (int k = 0; k < kUnroll; ++k) if (cell[k] != 0xFFFFFFFFu) atomicAdd(B.count + cell[k], 1u);
+            } else {
+#pragma unroll
+                for (int k = 0; k < kUnroll; ++k) if (cell[k] != 0xFFFFFFFFu) pos[k] = B.cell_start[cell[k]] + (atomicSub(B.count + cell[k], 1u) - 1u);
+#pragma unroll
+                for (int k = 0; k < kUnroll; ++k) if (cell[k] != 0xFFFFFFFFu && pos[k] < B.capacity) B.entries[pos[k]] = (uint32_t)prim;
             }
         }
+    };
+    for (int t0 = blockIdx.x * kGridBuildWarps; t0 < total; t0 += gridDim.x * kGridBuildWarps) {  // (block-uniform)
+        if (threadIdx.x == 0) s_nbig = 0;
+        __syncthreads();
+        const int t = t0 + warp;
+        if (t < total) {
+            const int j = t / n_prims, i = t - j * n_prims;
+            double fx, fy, fz, r;
+            grid_view_prim(B, j, i, fx, fy, fz, r);
+            const uint32_t base = (uint32_t)j * (uint32_t)B.cells_per_view;
+            if (grid_sphere_is_near(fx, fy, fz, r)) {
+                if (lane == 0) add_cells(base + (uint32_t)(6 * GG), 0, 0, 1, 1, i, 0, 1);
+            } else {
+                GridRect mine;
+                mine.iu0 = mine.iu1 = mine.iv0 = mine.iv1 = 0;
+                const bool have = lane < 6 && grid_rect(B.G, lane, fx, fy, fz, r, mine);
+                const unsigned faces = __ballot_sync(0xFFFFFFFFu, have);
+                for (int face = 0; face < 6; ++face) {
+                    if (!(faces >> face & 1u)) continue;
+                    const int iu0 = __shfl_sync(0xFFFFFFFFu, mine.iu0, face), iu1 = __shfl_sync(0xFFFFFFFFu, mine.iu1, face);
+                    const int iv0 = __shfl_sync(0xFFFFFFFFu, mine.iv0, face), iv1 = __shfl_sync(0xFFFFFFFFu, mine.iv1, face);
+                    const int w = iu1 - iu0 + 1, n = w * (iv1 - iv0 + 1);
+                    const uint32_t face_base = base + (uint32_t)(face * GG);
+                    if (n <= kGridBigRect) add_cells(face_base, iu0, iv0, w, n, i, lane, 32);
+                    else if (lane == 0) {
+                        int* e = s_big[atomicAdd(&s_nbig, 1)];
+                        e[0] = (int)face_base; e[1] = iu0; e[2] = iv0; e[3] = w; e[4] = n; e[5] = i;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        const int nbig = s_nbig;
+        for (int k = 0; k < nbig; ++k)
+            add_cells((uint32_t)s_big[k][0], s_big[k][1], s_big[k][2], s_big[k][3], s_big[k][4], s_big[k][5], threadIdx.x, kGridBuildThreads);
+        __syncthreads();  // (s_big / s_nbig are rewritten by the next round)
     }
 }
 
@@ -263,7 +304,7 @@ __global__ void __launch_bounds__(256) grid_build_kernel(const GridBuildParams B
 // (they all run at the same time: the grid is far smaller than one wave) and writes its offsets.
 constexpr int kScanThreads = 256, kScanPer = 16, kScanChunk = kScanThreads * kScanPer;
 __global__ void __launch_bounds__(kScanThreads) grid_scan_kernel(const uint32_t* __restrict__ count, uint32_t* __restrict__ cell_start, int n,
-                                                                 unsigned long long* aggregates, uint32_t epoch) {
+                                                                 unsigned long long* aggregates, uint32_t epoch, uint32_t* total_host) {
     __shared__ uint32_t s_warp[kScanThreads / 32];
     __shared__ uint32_t s_prefix;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -306,7 +347,10 @@ __global__ void __launch_bounds__(kScanThreads) grid_scan_kernel(const uint32_t*
     uint32_t run = s_prefix + woff + inc - sum;
 #pragma unroll
     for (int k = 0; k < kScanPer; ++k) { if (i0 + k < n) cell_start[i0 + k] = run; run += v[k]; }
-    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == kScanThreads - 1) cell_start[n] = s_prefix + btotal;
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == kScanThreads - 1) {
+        cell_start[n] = s_prefix + btotal;
+        if (total_host) *total_host = s_prefix + btotal;  // pinned host word (unified addressing): no copy node on the stream
+    }
 }
 
 static GridBuildParams grid_params(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
@@ -319,12 +363,12 @@ static GridBuildParams grid_params(const DevScene& sc, const DevCamera& cam, dou
 }
 int grid_scan_blocks(int n_cells) { return (n_cells + kScanChunk - 1) / kScanChunk; }
 cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start,
-                                   unsigned long long* aggregates, uint32_t epoch, cudaStream_t stream) {
+                                   unsigned long long* aggregates, uint32_t epoch, uint32_t* total_host, cudaStream_t stream) {
     const GridBuildParams B = grid_params(sc, cam, bias, G, count, cell_start, nullptr, 0);
     const long long total = (long long)B.n_views * (sc.ns + sc.nt);
     const int n_cells = B.n_views * B.cells_per_view;
     if (total > 0) grid_build_kernel<false><<<(unsigned)std::min<long long>((total + 7) / 8, 1 << 20), 256, 0, stream>>>(B);
-    grid_scan_kernel<<<grid_scan_blocks(n_cells), kScanThreads, 0, stream>>>(count, cell_start, n_cells, aggregates, epoch);
+    grid_scan_kernel<<<grid_scan_blocks(n_cells), kScanThreads, 0, stream>>>(count, cell_start, n_cells, aggregates, epoch, total_host);
     return cudaGetLastError();
 }
 cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
@@ -676,12 +720,13 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     const int aa = P.cam.aa;
     const bool words = (W & 3) == 0;  // rows of RGB8 are word aligned: a tile row of 8 pixels is six aligned words
 
-    unsigned int tile = 0;
-    if (lane == 0) tile = atomicAdd(P.tile_counter, 1u);
-    tile = __shfl_sync(kFullMask, tile, 0);
+    // first tile by position, the following ones from the global counter (every warp of the grid fetching its first tile from
+    // one address was ~9 us of serialised atomics in front of the first ray: a quarter of a 1/8-frame band's overhead)
+    const unsigned int n_static = gridDim.x * (kR32Threads / 32);
+    unsigned int tile = blockIdx.x * (kR32Threads / 32) + warp;
     while (tile < n_tiles) {
         unsigned int next = 0;
-        if (lane == 0) next = atomicAdd(P.tile_counter, 1u);  // the next tile id arrives behind the work
+        if (lane == 0) next = n_static + atomicAdd(P.tile_counter, 1u);  // the next tile id arrives behind the work
         int ty = (int)((float)tile * inv_tiles_x);  // tile / tiles_x without the integer-division sequence (tile < 2^24 for every frame <= 16K x 16K)
         if ((unsigned)(ty * tiles_x) > tile) --ty; else if ((unsigned)((ty + 1) * tiles_x) <= tile) ++ty;
         const int tx = (int)tile - ty * tiles_x;
