@@ -454,6 +454,37 @@ def measure(pipe, steps, warmup, flush, stream):
             "wall_ms": wall / steps * 1e3}
 
 
+def breakdown(pipe, m, steps, flush, stream):
+    """N > 1 (peer frames): where a step's time goes.  The same band rendered WITHOUT registered peer frames is the render kernel
+    alone (RGB8 into the local band buffer, no exchange launch, no fence); the rest follows by difference.  Untimed legs."""
+    if pipe.world == 1 or pipe.gather != "peer":
+        return None
+    torch, dist, eng = pipe.torch, pipe.dist, pipe.eng
+    eng.set_rgb8_peers([])
+    if pipe.use_flag_fence:
+        eng.set_fence_peers(pipe.rank, [])
+    ks, ts = [], []
+    for i in range(3 + steps):
+        flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        eng.set_camera(pipe.cam)
+        eng.render_device({"hdr": pipe.hdr.data_ptr(), "rgb8": pipe.rgb_local.data_ptr()}, tonemap_op=pipe.tm_op, **pipe.ropts)
+        b.record(stream)
+        k = eng.stats()["kernel_ms"]
+        if i >= 3:
+            ks.append(k); ts.append(a.elapsed_time(b))
+    t = torch.tensor([sum(ks) / len(ks), sum(ts) / len(ts)], dtype=torch.float64, device=pipe.dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    pipe._reregister()
+    render_ms, local_ms = [float(x) for x in t.tolist()]
+    return {"render_kernel_ms": round(render_ms, 4), "grid_build_ms": round(local_ms - render_ms, 4),
+            "exchange_launch_ms": round(m["kernel_ms_max"] - render_ms, 4),
+            "fence_and_rank_skew_ms": round(m["ms_per_step"] - m["kernel_ms_max"] - (local_ms - render_ms), 4),
+            "note": "max over ranks; render_kernel_ms: the band without peer frames; exchange = (render + exchange launches) - render; "
+                    "fence = step - launches - build (waiting for the slowest rank's flags over NVLink)"}
+
+
 def sharding_text(pipe):
     if pipe.world == 1:
         return "single band"
@@ -501,6 +532,7 @@ def run_gpu(args) -> None:
         pipe.rebuild = False  # the same frame again without rebuilding the grids (reported beside the headline, never as it)
         m_static = measure(pipe, max(3, args.steps // 2), 3, flush, stream)
         pipe.rebuild = True
+        bd = breakdown(pipe, m, max(3, args.steps // 2), flush, stream)
 
     # ---- e2e: C-ABI with HOST buffers — scene description H2D (rte_upload_scene) + render + RGB8 D2H, wall clock
     pin = PinnedBuffer(max(pipe.my_rows, 1) * W * 3)
@@ -554,9 +586,10 @@ def run_gpu(args) -> None:
         p5 = Pipeline(args, "c5", torch, dist, dev, rank, world, local_rank, stream)
         chk5 = p5.frame_check()
         m5 = measure(p5, max(3, args.steps // 4), 3, flush, stream)
+        bd5 = breakdown(p5, m5, 3, flush, stream)
         c5 = {"workload": p5.label, "ms_per_step": round(m5["ms_per_step"], 4), "value": round(m5["value"], 2), "unit": UNIT,
               "rays_per_frame": int(m5["rays"]), "kernel_ms_max": round(m5["kernel_ms_max"], 4), "kernel_ms_min": round(m5["kernel_ms_min"], 4),
-              "steps": max(3, args.steps // 4), "sharding": sharding_text(p5), "fixup_pixels": int(m5["fixup_pixels"]), **chk5}
+              "steps": max(3, args.steps // 4), "sharding": sharding_text(p5), "fixup_pixels": int(m5["fixup_pixels"]), "breakdown": bd5, **chk5}
         p5.close()
 
     if rank != 0:
@@ -585,6 +618,7 @@ def run_gpu(args) -> None:
         "ms_per_frame": round(m["ms_per_step"], 4),
         "static_scene": {"ms_per_step": round(m_static["ms_per_step"], 4), "gpu_launches_per_step": m_static["launches"],
                          "note": "same frame, direction grids of the previous frame reused (scene and camera unchanged): NOT the headline"},
+        "breakdown": bd,
         "grids": "rebuilt inside every timed step (count + scan + fill launches in front of the render kernel)",
         "wall_ms_per_step_incl_flush": round(m["wall_ms"], 3), "clocks": clocks,
         **check,

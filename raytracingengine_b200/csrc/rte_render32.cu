@@ -664,7 +664,11 @@ static __device__ __noinline__ void fix_batch(const RenderParams& P, const uint3
 
 // ------------------------------------------------------------------------------ the kernel
 // Persistent CTAs, one 8 x 4 pixel tile per warp at a time from a global counter (like the exact kernels), one pixel per lane.
-constexpr int kTile32W = 8, kTile32H = 4;
+#ifndef RTE_TW
+#define RTE_TW 8
+#define RTE_TH 4
+#endif
+constexpr int kTile32W = RTE_TW, kTile32H = RTE_TH;
 
 template <bool kAov>
 __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_constant__ RenderParams P) {
@@ -716,7 +720,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     const int tiles_x = (W + kTile32W - 1) / kTile32W, tiles_y = (rows + kTile32H - 1) / kTile32H;
     const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
     const float inv_tiles_x = 1.0f / (float)tiles_x;
-    const int lx = lane & (kTile32W - 1), ly = lane >> 3;
+    const int lx = lane & (kTile32W - 1), ly = lane / kTile32W;
     const int aa = P.cam.aa;
     const bool words = (W & 3) == 0;  // rows of RGB8 are word aligned: a tile row of 8 pixels is six aligned words
 
