@@ -624,10 +624,10 @@ def run_gpu(args) -> None:
         **check,
         "e2e": {"value": round(e2e_value, 2), "unit": UNIT, "ms_per_step": round(e2e_ms, 3), "h2d_bytes_per_step": int(scene_bytes),
                 "d2h_bytes_per_step": int(pipe.my_rows * W * 3), "api": "rte_upload_scene + rte_render_host (pinned host RGB8)"},
-        # per step and rank: the library's launches of one render call (render kernel + fix-up launch; + max luminance + tonemap for the
+        # per step and rank: the library's launches of one render call (grid count / scan / fill + render kernel, + exchange at N > 1; + max luminance + tonemap for the
         # auto-white pipeline); memsets and NCCL are not ours
         "gpu_launches": args.steps * (m["launches"] + (2 if pipe.auto_white else 0)),
-        "roofline": {"bound": "fp32", "kernel": "rte::render32_kernel (+ rte::fixup_kernel, the exact FP64 re-render of the flagged pixels)",
+        "roofline": {"bound": "fp32", "kernel": "rte::render32_kernel (incl. fix_batch, the exact FP64 re-render of the flagged pixels, in the same launch)",
                      "achieved": round(achieved_tf, 3), "peak": round(fp32_peak_tf, 3), "unit": "TFLOP/s", "frac": round(achieved_tf / fp32_peak_tf, 4),
                      "frac_note": "ALGORITHMIC: the reference's 20 flop per ray-sphere test over ALL spheres (SURVEY §8(d)) / time / measured FFMA peak; the "
                                   "direction grids test ~3 of 1024 spheres per ray, so this is a speed-up over brute force, not a hardware utilisation — "

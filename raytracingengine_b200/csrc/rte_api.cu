@@ -111,9 +111,15 @@ int fail(rte_ctx* ctx, int code, const char* fmt, ...) {
     return code;
 }
 
+// Errors that leave the CUDA context healthy (an oversized allocation, a launch configuration the device cannot run, a bad
+// pointer handed to a copy) fail the call only; everything else (launch failures, illegal addresses, ...) poisons the CUDA
+// context for good and makes the ctx sticky: every later call reports it until rte_destroy.
 int cuda_fail(rte_ctx* ctx, cudaError_t e, const char* what) {
-    if (ctx) ctx->sticky = true;
-    return fail(ctx, RTE_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+    const bool limit = e == cudaErrorMemoryAllocation || e == cudaErrorLaunchOutOfResources || e == cudaErrorInvalidConfiguration;
+    const bool recoverable = limit || e == cudaErrorInvalidValue;
+    if (recoverable) (void)cudaGetLastError();  // (clears the per-thread last-error slot)
+    else if (ctx) ctx->sticky = true;
+    return fail(ctx, limit ? RTE_ERR_LIMIT : RTE_ERR_CUDA, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
 }
 
 #define RTE_CUDA(ctx, call)                                       \
@@ -607,7 +613,7 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     p.tile_counter = ctx->d_tile_counter; p.stats = ctx->d_stats;
     if (p.out.rgb8 && p.tonemap_op == RTE_TM_NONE) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 requested but opts.tonemap_op is RTE_TM_NONE");
     // FP32 production path (rte_render32.cu): diffuse sphere / plane scenes with resident views, outputs hdr / rgb8 / prim_id /
-    // light_mask.  The operator runs in the kernel; pixels with an inconclusive FP32 decision go through the exact fix-up launch.
+    // light_mask.  The operator runs in the kernel; pixels with an inconclusive FP32 decision are rendered again, exactly, by fix_batch in the same kernel.
     if (o.n_rows > 0 && fp32_path_eligible(p)) {
         if (p.out.rgb8 && ((uintptr_t)p.out.rgb8 & 3u) != 0 && (ctx->cam.width & 3) == 0) return fail(ctx, RTE_ERR_INVALID, "frame.rgb8 must be 4-byte aligned");
         int rc;
@@ -749,9 +755,18 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
     // launch of the persistent render kernel costs ~0.1 ms (ramp-up plus the tail of ~50 us tiles), the copy 0.48 ms: four
     // equal bands lose more than they hide (3.64 ms against 3.56 ms unsplit), 7/8 + 1/8 hides most of the copy.
     // Bands are whole stripes when the rows are striped; registered peer frames (multi-GPU output exchange) keep one launch.
+    // With a pageable destination cudaMemcpyAsync blocks the host until band 0 has been copied, before band 1 is enqueued:
+    // the split would only add a launch, so it is used for pinned destinations only.
+    bool pinned = true;
+    for (Item& it : items) {
+        if (!it.host) continue;
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, it.host) != cudaSuccess) { (void)cudaGetLastError(); pinned = false; }
+        else if (at.type != cudaMemoryTypeHost) pinned = false;
+    }
     const int unit = o.stripe_rows > 0 ? o.stripe_rows : 4;
     int rows_per = o.n_rows;
-    if (o.n_rows >= kHostBandRows && ctx->n_peers == 0) rows_per = (o.n_rows - o.n_rows / RTE_HOST_TAIL_DIV + unit - 1) / unit * unit;
+    if (o.n_rows >= kHostBandRows && ctx->n_peers == 0 && pinned) rows_per = (o.n_rows - o.n_rows / RTE_HOST_TAIL_DIV + unit - 1) / unit * unit;
     if (rows_per < 1) rows_per = 1;
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_copied, ctx->stream));
     RTE_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_copied, 0));  // the copy stream starts behind earlier work of the context

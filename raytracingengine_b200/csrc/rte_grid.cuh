@@ -14,7 +14,7 @@
 // radius is inflated by `bias` because the true shadow ray starts at P + N*bias (RE/Scene.h:104) and passes the light at a
 // distance of at most `bias`.  Spheres that contain the origin or subtend more than 30 degrees go to a per-origin "near list"
 // that every ray of that origin tests.  A cell may list spheres the ray misses (cost only), never the reverse; the caller
-// still decides every candidate itself (rte_render32.cu: FP32 intervals; rte_render.cu fixup_kernel: the exact FP64 tests).
+// still decides every candidate itself (rte_render32.cu: FP32 intervals; rte_exact_grid.cuh: the exact FP64 tests).
 //
 // Layout (CSR): cells of view j start at j * cells_per_view; cell = face * G*G + iv * G + iu; the view's near list is its
 // last cell (index 6 G*G).  cell_start[c] .. cell_start[c + 1] index `entries` (unordered primitive indices: spheres first,

@@ -1,4 +1,4 @@
-// rte_render.cu — the per-pixel render kernel (sm_100a).
+// rte_render.cu — the EXACT (FP64, bit-identical) per-pixel render kernels (sm_100a); the FP32 production path is rte_render32.cu.
 //
 // Replaces Scene::RenderImage / GeneratePixelAt / TraceRay / directLightning
 // (RE/Scene.h:311-328, 283-304, 131-198, 79-129; "RE/" = /root/reference/RaytracingEngine/).
@@ -9,7 +9,8 @@
 //    bulk copies (cp.async.bulk + mbarrier complete_tx);
 //  * per pixel the ray state is FP64 (bit-identical to the reference's doubles), the O(primitives)
 //    loops are FP32 FMA filters (rte_trace.cuh);
-//  * reflection (material.specular) is an iterative loop; refraction is rejected at upload time.
+//  * reflection / refraction / Fresnel (RE/Scene.h:161-187) run as an explicit per-pixel stack (trace_pixels<K, true>);
+//  * diffuse scenes of any size take render_exact_grid_kernel: the same FP64 tests over the direction grids (rte_exact_grid.cuh).
 #include <vector>
 
 #include "rte_exact_grid.cuh"

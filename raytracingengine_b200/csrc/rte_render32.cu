@@ -1,5 +1,5 @@
-// rte_render32.cu — the FP32 production path of the render call (sm_100a): diffuse sphere / plane scenes whose views are
-// resident in shared memory, outputs HDR float4 / RGB8 (+ the integer AOVs prim_id, light_mask).
+// rte_render32.cu — the FP32 production path of the render call (sm_100a): diffuse sphere / plane scenes over per-origin
+// direction grids (rte_grid.cuh; built here), outputs HDR float4 / RGB8 (+ the integer AOVs prim_id, light_mask).
 //
 // Replaces Scene::RenderImage / TraceRay / directLightning + tonemap()/toColor for those scenes (RE/Scene.h:311-328, 131-198,
 // 79-129; RE/RaytracingEngine.cpp:113-121,165-174; "RE/" = /root/reference/RaytracingEngine/) to the bar BASELINE.json states:
@@ -10,8 +10,8 @@
 //    (hit point, C - origin of a candidate) take a handful of FP64 adds / FMAs — never an FP64 division or square root
 //    (those are ~25 / ~40 SASS instructions each): reciprocal square roots come from MUFU + Newton steps.
 //  * DECISIONS (which primitive is nearest, is a shadow ray cast, is it occluded) are taken from FP32 INTERVALS with explicit
-//    error bounds.  A pixel with any inconclusive decision is rendered again on the spot with the reference's exact FP64
-//    operations (rte_exact_grid.cuh) by the lane that owns it.  So every decision that reaches an output is either certain
+//    error bounds.  A pixel with any inconclusive decision is queued by its warp and rendered again with the reference's
+//    exact FP64 operations (fix_batch, rte_exact_grid.cuh).  So every decision that reaches an output is either certain
 //    or exact, and those pixels (~1e-3 of a frame) are the reference's own bits.
 //  * The operator + toColor run in the kernel (tm32, rte_tonemap.cuh) and a tile row of 8 pixels leaves as six aligned
 //    32-bit words: no FP64 HDR scratch, no second pass.
@@ -25,7 +25,7 @@
 
 namespace rte {
 
-constexpr int kR32Threads = 1024;  // one CTA per SM (the views of C2 are 80 KB)
+constexpr int kR32Threads = 1024;  // one CTA per SM at 64 registers (768 / 512 threads with more registers measured slower)
 constexpr int kR32Planes = 8, kR32Lights = 16;  // scenes with more take the exact path
 
 // ------------------------------------------------------------------------------ cheap FP64 (no DDIV / DSQRT sequences)
@@ -411,7 +411,7 @@ __device__ __forceinline__ uint32_t tonemap_rgb24(int op, float x, float y, floa
 }
 
 // One sample of one pixel per lane, all 32 lanes of the warp in lock step.  Returns false when some decision of the pixel
-// was inconclusive (the pixel then belongs to the fix-up launch and nothing else of the result is meaningful).
+// was inconclusive (the pixel then goes to the warp's exact queue, fix_batch, and nothing else of the result is meaningful).
 struct Px32 {
     float r, g, b;       // linear HDR of the sample
     uint32_t prim, lmask;

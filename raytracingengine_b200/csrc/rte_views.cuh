@@ -487,7 +487,7 @@ __device__ __forceinline__ bool cta_cull_view(const ulonglong2* __restrict__ vie
 // ------------------------------------------------------------------------------ candidate queue
 // With ~2 line candidates per ray and 32 lanes, almost every 32-sphere block has a candidate in SOME lane:
 // resolving candidates where they are found runs the divergent path ~30 times per scan with 1-2 lanes active.
-// Instead every lane appends its candidates, (ray k << 28) | sphere index, to a small private queue during
+// Instead every lane appends its candidates, (ray k << 8) | (sphere index - window start) in 16 bits, to a small private queue during
 // the scan, and the warp resolves the queues lane-parallel in one compact loop per window: trip count =
 // the longest queue in the warp, one copy of the resolution code for all K rays.
 constexpr int kWindow = 256;  // spheres between two resolutions (+ warp vote for any-hit rays): bounds the queue

@@ -1,4 +1,4 @@
-"""GPU parity of the FP32 PRODUCTION path (csrc/rte_render32.cu + the exact fix-up launch): calls that ask for hdr / rgb8 /
+"""GPU parity of the FP32 PRODUCTION path (csrc/rte_render32.cu incl. its exact fix-up batches): calls that ask for hdr / rgb8 /
 prim_id / light_mask only, on diffuse sphere / plane scenes.
 
 Bars (BASELINE.json north_star): nearest-hit (type, index) and shadow visibility bit-exact, RGB8 within +-1 LSB of the
@@ -29,7 +29,7 @@ def check(fast, sf, exact, se, n_px):
     np.testing.assert_allclose(fast["hdr"][:, :3], exact["hdr"][:, :3], rtol=2e-5, atol=1e-5)
     for k in COUNTERS:
         assert sf[k] == se[k], f"counter {k}: fp32 path {sf[k]}, exact path {se[k]}"
-    assert sf["fp64_confirms"] <= 0.02 * n_px, f"{sf['fp64_confirms']} of {n_px} pixels went through the fix-up launch"
+    assert sf["fp64_confirms"] <= 0.02 * n_px, f"{sf['fp64_confirms']} of {n_px} pixels went through the exact fix-up"
 
 
 @pytest.mark.parametrize("cfg", ["c2", "c2_quarter", "c3", "odd", "big_resident", "camera_inside"])

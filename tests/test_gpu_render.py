@@ -239,6 +239,19 @@ def test_errors(engine):
         engine.upload(bad, cam)  # more lights than the documented capacity (4096; light_mask covers the first 16)
     engine.upload(arrays, cam)  # the ctx stays usable after argument errors
     assert engine.render_host(outputs=("prim_id",))["prim_id"].size == cam.width * cam.height
+    # a frame the device cannot hold (2^38 pixels x 16 B of staging): cudaMalloc fails, the call reports RTE_ERR_LIMIT before it
+    # touches the destination, and the ctx is NOT poisoned (recoverable CUDA errors are not sticky)
+    import ctypes as C
+    import dataclasses
+    huge = dataclasses.replace(cam, width=1 << 19, height=1 << 19)
+    engine.set_camera(huge)
+    f = _abi.Frame()
+    dummy = np.zeros(4, np.float32)
+    f.hdr = dummy.ctypes.data
+    rc = engine.lib.rte_render_host(engine.ctx, None, C.byref(f))
+    assert rc == _abi.RTE_ERR_LIMIT, (rc, engine.lib.rte_last_error(engine.ctx))
+    engine.set_camera(cam)
+    assert engine.render_host(outputs=("prim_id",))["prim_id"].size == cam.width * cam.height
 
 
 @pytest.mark.parametrize("cfg", ["c2", "c3", "c2_band", "c2_odd", "c5_streamed", "c5_streamed_band", "big_resident", "c4_blob", "c4_box", "mixed"])
