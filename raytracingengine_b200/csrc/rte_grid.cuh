@@ -53,41 +53,70 @@ __device__ __forceinline__ uint32_t grid_near_cell(const DevGrid& g, int view) {
     return (uint32_t)view * (uint32_t)g.cells_per_view + (uint32_t)(6 * g.G * g.G);
 }
 
+// ------------------------------------------------------------------------------ cheap FP64 (no DDIV / DSQRT sequences)
+// 1/sqrt(x) to ~1e-15 relative for x within FP32's exponent range: MUFU.RSQ seed (1e-7) + two Newton steps in FP64.
+// (Outside that range the result is 0, inf or NaN: callers either cannot get there or treat NaN conservatively.)
+__device__ __forceinline__ double rsqrt64_fast(double x) {
+    double y = (double)rsqrtf((float)x);
+    const double hx = 0.5 * x;
+    y = y * fma(-hx * y, y, 1.5);
+    y = y * fma(-hx * y, y, 1.5);
+    return y;
+}
+// 1/x to ~1e-15 relative: MUFU.RCP seed + two Newton steps.
+__device__ __forceinline__ double rcp64_fast(double x) {
+    double y = (double)__frcp_rn((float)x);
+    y = y * fma(-x, y, 2.0);
+    y = y * fma(-x, y, 2.0);
+    return y;
+}
+__device__ __forceinline__ double sqrt64_fast(double x) { return x > 0.0 ? x * rsqrt64_fast(x) : 0.0; }
+
 // Cells of one face that the sphere {f = C - O (view frame), r} can be seen through: [iu0, iu1] x [iv0, iv1], or false.
-// `near` is set when the sphere belongs to the view's near list instead (then every face returns false).
+// Spheres of the view's near list (grid_sphere_is_near) never get here.  The arithmetic is the cheap FP64 above (a (view,
+// primitive) pair used to cost ~700 warp instructions, most of them IEEE division / square-root sequences): its 1e-15 errors
+// disappear in the margin of 1e-5; anything that comes out as NaN (coordinates beyond FP32's range) takes the whole face.
 struct GridRect { int iu0, iu1, iv0, iv1; };
 __device__ __forceinline__ bool grid_sphere_is_near(double fx, double fy, double fz, double r) {
     return !(fx * fx + fy * fy + fz * fz > 4.0 * r * r);  // origin inside, or the cone's half-angle reaches 30 degrees (also NaN)
 }
+// Straight-line on purpose (selects, no early exits): the six lanes of a warp that work out the six faces of one primitive
+// must not diverge — divergent exits cost the warp one pass per face.
 __device__ __forceinline__ bool grid_rect(int G, int face, double fx, double fy, double fz, double r, GridRect& out) {
     const int axis = face >> 1;
     const double sgn = (face & 1) ? -1.0 : 1.0;
-    double w, x, y;  // depth along the face normal, the two others in cyclic order (same convention as grid_cell)
-    if (axis == 0) { w = sgn * fx; x = fy; y = fz; }
-    else if (axis == 1) { w = sgn * fy; x = fz; y = fx; }
-    else { w = sgn * fz; x = fx; y = fy; }
-    double u0 = -1.0, u1 = 1.0, v0 = -1.0, v1 = 1.0;
-    if (w > r) {  // entirely in front of the plane w = 0: exact bounds of the projected conic
-        const double A = w * w - r * r;
-        const double Du = r * sqrt(fmax(x * x + A, 0.0)), Dv = r * sqrt(fmax(y * y + A, 0.0));
-        u0 = (x * w - Du) / A; u1 = (x * w + Du) / A;
-        v0 = (y * w - Dv) / A; v1 = (y * w + Dv) / A;
-    } else {
-        // straddles w = 0: the cone (half-angle < 30 deg) reaches the face's directions (within 54.74 deg of its normal) only
-        // if angle(axis, normal) - theta < 54.74 deg; then it may touch any cell of the face
-        const double F = sqrt(fx * fx + fy * fy + fz * fz), ca = w / F, st = r / F;
-        const double ct = sqrt(fmax(1.0 - st * st, 0.0)), sa = sqrt(fmax(1.0 - ca * ca, 0.0));
-        if (!(ca * ct + sa * st > 0.5773)) return false;
-    }
+    // depth along the face normal, the two others in cyclic order (same convention as grid_cell)
+    const double w = sgn * (axis == 0 ? fx : axis == 1 ? fy : fz);
+    const double x = axis == 0 ? fy : axis == 1 ? fz : fx, y = axis == 0 ? fz : axis == 1 ? fx : fy;
+    const double A = w * w - r * r;
+    // in front of the plane w = 0 (and not within 1e-6 of touching it: the differences below cancel like w / (w - r), and
+    // 1e-15 * 1e6 stays far below the margin): exact bounds of the projected conic,  u = (x w +- r sqrt(x^2 + A)) / A
+    const bool front = w > r && A > 1e-6 * w * w;
+    const double As = front ? A : 1.0, iA = rcp64_fast(As);
+    const double Du = r * sqrt64_fast(x * x + As), Dv = r * sqrt64_fast(y * y + As);
+    // ... unless it lies outside the face's pyramid |x| <= w, |y| <= w, beyond one of its four planes through the origin
+    // (distance (x - w) / sqrt 2)
+    const double k = r * 1.4142136;
+    const bool outside = x - w > k || -x - w > k || y - w > k || -y - w > k;
+    // behind, straddling or nearly touching w = 0: the cone (half-angle < 30 deg) reaches the face's directions (within 54.74
+    // deg of its normal) only if angle(axis, normal) - theta < 54.74 deg; then it may touch any cell of the face
+    const double iF = rsqrt64_fast(fx * fx + fy * fy + fz * fz), ca = w * iF, st = r * iF;
+    const double ct = sqrt64_fast(1.0 - st * st), sa = sqrt64_fast(1.0 - ca * ca);
+    const bool reach = !(ca * ct + sa * st <= 0.5773);  // (NaN: reaches)
+    const bool any = front ? !outside : (reach && !(w < -r));
+    double u0 = front ? (x * w - Du) * iA : -1.0, u1 = front ? (x * w + Du) * iA : 1.0;
+    double v0 = front ? (y * w - Dv) * iA : -1.0, v1 = front ? (y * w + Dv) * iA : 1.0;
     const double m = 1e-5;  // FP32 direction of the ray + rounding of its cell arithmetic, in units of u
     u0 -= m * (1.0 + fabs(u0)); u1 += m * (1.0 + fabs(u1)); v0 -= m * (1.0 + fabs(v0)); v1 += m * (1.0 + fabs(v1));
-    if (!(u1 >= -1.0 && u0 <= 1.0 && v1 >= -1.0 && v0 <= 1.0)) return false;
+    const bool nan = !(u0 == u0 && u1 == u1 && v0 == v0 && v1 == v1);  // coordinates beyond FP32's range: the whole face
+    u0 = nan ? -1.0 : u0; u1 = nan ? 1.0 : u1; v0 = nan ? -1.0 : v0; v1 = nan ? 1.0 : v1;
+    const bool seen = any && !(u1 < -1.0 || u0 > 1.0 || v1 < -1.0 || v0 > 1.0);
     const double half = 0.5 * (double)G;
     out.iu0 = max(0, min(G - 1, (int)floor((fmax(u0, -1.0) + 1.0) * half - 1e-3)));
     out.iu1 = max(0, min(G - 1, (int)floor((fmin(u1, 1.0) + 1.0) * half + 1e-3)));
     out.iv0 = max(0, min(G - 1, (int)floor((fmax(v0, -1.0) + 1.0) * half - 1e-3)));
     out.iv1 = max(0, min(G - 1, (int)floor((fmin(v1, 1.0) + 1.0) * half + 1e-3)));
-    return true;
+    return seen;
 }
 
 }  // namespace rte

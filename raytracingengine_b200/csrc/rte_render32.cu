@@ -28,22 +28,7 @@ namespace rte {
 constexpr int kR32Threads = 1024;  // one CTA per SM at 64 registers (768 / 512 threads with more registers measured slower)
 constexpr int kR32Planes = 8, kR32Lights = 16;  // scenes with more take the exact path
 
-// ------------------------------------------------------------------------------ cheap FP64 (no DDIV / DSQRT sequences)
-// 1/sqrt(x) to ~1e-16 relative for normal positive x: MUFU.RSQ seed (1e-7) + two Newton steps in FP64.
-__device__ __forceinline__ double rsqrt64_fast(double x) {
-    double y = (double)rsqrtf((float)x);
-    const double hx = 0.5 * x;
-    y = y * fma(-hx * y, y, 1.5);
-    y = y * fma(-hx * y, y, 1.5);
-    return y;
-}
-// 1/x to ~1e-16 relative: MUFU.RCP seed + two Newton steps.
-__device__ __forceinline__ double rcp64_fast(double x) {
-    double y = (double)__frcp_rn((float)x);
-    y = y * fma(-x, y, 2.0);
-    y = y * fma(-x, y, 2.0);
-    return y;
-}
+// (cheap FP64 reciprocals / square roots without DDIV / DSQRT sequences: rsqrt64_fast, rcp64_fast in rte_grid.cuh)
 __device__ __forceinline__ float sqrt_approx(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
 // ------------------------------------------------------------------------------ scene constants in shared memory
@@ -220,12 +205,12 @@ __device__ __forceinline__ void grid_view_prim(const GridBuildParams& B, int j, 
         const double da = (ax - cx) * (ax - cx) + (ay - cy) * (ay - cy) + (az - cz) * (az - cz);
         const double db = (bx - cx) * (bx - cx) + (by - cy) * (by - cy) + (bz - cz) * (bz - cz);
         const double dc = (qx - cx) * (qx - cx) + (qy - cy) * (qy - cy) + (qz - cz) * (qz - cz);
-        rad = sqrt(fmax(da, fmax(db, dc))) * (1.0 + 1e-9) + 1e-300;
+        rad = sqrt64_fast(fmax(da, fmax(db, dc))) * (1.0 + 1e-9) + 1e-300;
     }
     const double ox = j == 0 ? B.cam[0] : B.sc.lights[j - 1].pos[0], oy = j == 0 ? B.cam[1] : B.sc.lights[j - 1].pos[1],
                  oz = j == 0 ? B.cam[2] : B.sc.lights[j - 1].pos[2];
     fx = cx - ox; fy = cy - oy; fz = cz - oz;
-    const double F = sqrt(fx * fx + fy * fy + fz * fz);
+    const double F = sqrt64_fast(fx * fx + fy * fy + fz * fz);  // (only scales the slack below)
     // radius (+ bias for a light's grid: the shadow line passes the light within `bias`), + the lateral reach of an FP32 direction
     r = (rad + (j > 0 ? B.bias : 0.0)) * (1.0 + 1e-9) + 4e-6 * F + 1e-12;
 }
@@ -243,12 +228,15 @@ __global__ void __launch_bounds__(kGridBuildThreads) grid_build_kernel(const Gri
     // cells [c0, c0 + step * kUnroll) of a rectangle, `step` apart: the atomics are independent, the stores follow
     auto add_cells = [&](uint32_t face_base, int iu0, int iv0, int w, int n, int prim, int c0, int step) {
         constexpr int kUnroll = 4;
+        const float inv_w = 1.0f / (float)w;
         for (int c = c0; c < n; c += step * kUnroll) {
             uint32_t cell[kUnroll], pos[kUnroll];
 #pragma unroll
             for (int k = 0; k < kUnroll; ++k) {
                 const int cc = c + k * step;
-                cell[k] = cc < n ? face_base + (uint32_t)((iv0 + cc / w) * B.G + iu0 + cc % w) : 0xFFFFFFFFu;
+                int row = (int)((float)cc * inv_w), col = cc - row * w;  // cc / w without the integer-division sequence (n <= 512^2)
+                if (col < 0) { --row; col += w; } else if (col >= w) { ++row; col -= w; }
+                cell[k] = cc < n ? face_base + (uint32_t)((iv0 + row) * B.G + iu0 + col) : 0xFFFFFFFFu;
             }
             if (!kFill) {
 #pragma unroll
