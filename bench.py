@@ -643,6 +643,10 @@ def run_gpu(args) -> None:
                              "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(n_px * 33 / (tm_med * 1e-3) / 1e9 / pk["hbm_gbs"], 4),
                              "traffic": (tr_tm or {}).get("bytes") if args.workload in ("c2", "c3") and world == 1 else None, "traffic_capture": tr_tm,
                              "peak_source": pk_src, "algorithmic_bytes_per_launch": n_px * 33, "kernel_ms": round(tm_med, 4),
+                             "frac_moved_bytes": round(n_px * 37 / (tm_med * 1e-3) / 1e9 / pk["hbm_gbs"], 4),
+                             "frac_note": "frac counts SURVEY's 33 B/px (12 B of HDR read per pixel); the ABI's HDR is float4, so 37 B/px really move "
+                                          "(frac_moved_bytes). The same loads and stores WITHOUT the operators' arithmetic take 64-68 us "
+                                          "(tonemap_null_kernel, tools/tm_probe.py): the pass sits on the bandwidth of its access pattern",
                              "l2": "input (16 B/px float4, two rotating buffers) and output (21 B/px) exceed L2; no flush"},
     }
     if c5 is not None:
