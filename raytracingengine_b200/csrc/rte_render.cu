@@ -331,9 +331,14 @@ __device__ __forceinline__ void trace_pixels(const RenderParams& P, const DevSce
                 const d3 N = frontFace ? ngeo[k] : -ngeo[k];
                 const double cosTheta = std_max(0.0, dot(N, viewDir[k]));
                 const double etaT = M.refractive_index;
-                const double f0 = pow((etaT - 1.0) / (etaT + 1.0), 2.0);
-                double fresnelAmount = f0 + (1.0 - f0) * pow(1.0 - cosTheta, 5.0);  // Scene::fresnel, RE/Scene.h:26-28
                 const double transparency = std_clamp(M.transparency, 0.0, 1.0);
+                // Scene::fresnel, RE/Scene.h:26-28 — its value only reaches an output through transparent materials (below): opaque
+                // hits skip the two pow() calls (a third of the FP64 instructions of an opaque node)
+                double fresnelAmount = 0.0;
+                if (transparency > 0.0) {
+                    const double f0 = pow((etaT - 1.0) / (etaT + 1.0), 2.0);
+                    fresnelAmount = f0 + (1.0 - f0) * pow(1.0 - cosTheta, 5.0);
+                }
                 d3 fin = mk(0.0, 0.0, 0.0);
                 if (transparency < 1.0) fin = fin + local * (1.0 - transparency);
                 bool has_t = false;
