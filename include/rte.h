@@ -117,7 +117,7 @@ typedef struct rte_camera {
     double position[3];
     double focal;
     uint64_t width, height;
-    double near_plane, far_plane;
+    double near_plane, far_plane;          /* only frame.depth_norm reads them (HitInfo::normalizedDistance) */
     int32_t anti_aliasing; /* Camera::antiAliasingAmount, RE/Math.h:94: samples per pixel, 1..RTE_MAX_AA */
     int32_t jitter_seed;   /* seed of the jitter stream below (upstream seeds from std::random_device, RE/Math.h:109) */
 } rte_camera;
@@ -199,6 +199,9 @@ typedef struct rte_frame {
     float* albedo;       /* float4: HitInfo.material.color, sky colour on miss */
     uint32_t* light_mask;/* bit j: light j contributes at the primary hit (transmittance > bias);
                             bit 16+j: a shadow ray was cast to light j (guards RE/Scene.h:89-101) */
+    float* depth_norm;   /* HitInfo::normalizedDistance(camera), RE/Shape.h:40-42: (distance - near_plane) / (far_plane -
+                            near_plane), evaluated in FP64 like upstream and rounded to FP32; +inf on miss (the depth map
+                            main() used to write, RE/Scene.h:278-281) */
 } rte_frame;
 
 /* Counters accumulated by the render kernels of the last rte_render*() call. */

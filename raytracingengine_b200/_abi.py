@@ -99,7 +99,7 @@ class RenderOpts(C.Structure):
 class Frame(C.Structure):
     _fields_ = [("hdr", C.c_void_p), ("hdr64", C.c_void_p), ("rgb8", C.c_void_p),
                 ("prim_id", C.c_void_p), ("depth", C.c_void_p), ("depth64", C.c_void_p),
-                ("normal", C.c_void_p), ("albedo", C.c_void_p), ("light_mask", C.c_void_p)]
+                ("normal", C.c_void_p), ("albedo", C.c_void_p), ("light_mask", C.c_void_p), ("depth_norm", C.c_void_p)]
 
 
 class Stats(C.Structure):
@@ -114,7 +114,7 @@ class Stats(C.Structure):
 
 
 assert C.sizeof(Camera) == 72 and C.sizeof(SceneDesc) == 128
-assert C.sizeof(RenderOpts) == 56 and C.sizeof(Frame) == 72 and C.sizeof(Stats) == 88
+assert C.sizeof(RenderOpts) == 56 and C.sizeof(Frame) == 80 and C.sizeof(Stats) == 88
 
 # algorithmic flops per ray-primitive test
 FLOP_SPHERE, FLOP_PLANE, FLOP_TRIANGLE = 20, 14, 46

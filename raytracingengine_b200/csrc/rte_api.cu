@@ -94,7 +94,7 @@ struct rte_ctx {
     rte_stats stats{};
 
     // staging for the *_host variants (grow-only)
-    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64, s_hits, s_fix;
+    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64, s_hits, s_fix, s_dnorm, s_dn64;
     DevBuf s_tm_in, s_tm_out[RTE_TM_COUNT], s_q_o, s_q_d, s_q_m, s_q_out;
 };
 
@@ -294,7 +294,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphhl, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
                       &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->b_grid_count, &ctx->b_grid_start, &ctx->b_grid_entries, &ctx->b_grid_aggr, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
-                      &ctx->s_depth64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
+                      &ctx->s_depth64, &ctx->s_dnorm, &ctx->s_dn64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     for (DevBuf& b : ctx->s_tm_out) if (b.p) cudaFree(b.p);
@@ -691,6 +691,11 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     }
     p.out.rgb8 = nullptr;
     p.tonemap_op = RTE_TM_NONE;
+    if (p.out.depth_norm && !p.out.depth64 && o.n_rows > 0) {  // frame.depth_norm is a pass over the FP64 depth
+        int rc = reserve(ctx, ctx->s_dn64, (size_t)o.n_rows * (size_t)ctx->cam.width * 8);
+        if (rc) return rc;
+        p.out.depth64 = (double*)ctx->s_dn64.p;
+    }
     // (d_tile_counter sits right behind d_stats: one memset clears both)
     if (first) {
         RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * (kStatCount + 2), ctx->stream));
@@ -700,6 +705,11 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
     }
     if (o.n_rows > 0) RTE_CUDA(ctx, launch_render(p, ctx->sm_count, ctx->stream));
     if (o.n_rows > 0) ctx->render_launches += (p.hits && two_pass_wanted(p)) ? 2 : 1;
+    if (p.out.depth_norm && o.n_rows > 0) {
+        RTE_CUDA(ctx, launch_depth_norm(p.out.depth64, (int64_t)o.n_rows * ctx->cam.width, ctx->cam_host.near_plane, ctx->cam_host.far_plane, p.out.depth_norm,
+                                        ctx->sm_count, ctx->stream));
+        ctx->render_launches += 1;
+    }
     if (fence) {
         ctx->fence_seq += 1;
         for (int i = 0; i < ctx->n_fence; ++i) tp.fence_flags[i] = ctx->fence_flags[i];
@@ -744,7 +754,7 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
         {hf->rgb8, &ctx->s_rgb8, 3, (void**)&df.rgb8},         {hf->prim_id, &ctx->s_prim, 4, (void**)&df.prim_id},
         {hf->depth, &ctx->s_depth, 4, (void**)&df.depth},      {hf->depth64, &ctx->s_depth64, 8, (void**)&df.depth64},
         {hf->normal, &ctx->s_normal, 16, (void**)&df.normal},  {hf->albedo, &ctx->s_albedo, 16, (void**)&df.albedo},
-        {hf->light_mask, &ctx->s_lmask, 4, (void**)&df.light_mask}};
+        {hf->light_mask, &ctx->s_lmask, 4, (void**)&df.light_mask},  {hf->depth_norm, &ctx->s_dnorm, 4, (void**)&df.depth_norm}};
     for (Item& it : items) {
         if (!it.host) continue;
         if ((rc = reserve(ctx, *it.buf, n * it.px_bytes))) return rc;
@@ -782,7 +792,7 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
         bf.rgb8 = df.rgb8 ? df.rgb8 + off * 3 : nullptr;        bf.prim_id = df.prim_id ? df.prim_id + off : nullptr;
         bf.depth = df.depth ? df.depth + off : nullptr;         bf.depth64 = df.depth64 ? df.depth64 + off : nullptr;
         bf.normal = df.normal ? df.normal + off * 4 : nullptr;  bf.albedo = df.albedo ? df.albedo + off * 4 : nullptr;
-        bf.light_mask = df.light_mask ? df.light_mask + off : nullptr;
+        bf.light_mask = df.light_mask ? df.light_mask + off : nullptr;  bf.depth_norm = df.depth_norm ? df.depth_norm + off : nullptr;
         const bool last = y0 + rows_per >= o.n_rows;
         if ((rc = do_render(ctx, ob, &bf, b == 0, last))) return rc;
         RTE_CUDA(ctx, cudaEventRecord(ctx->ev_band[b], ctx->stream));

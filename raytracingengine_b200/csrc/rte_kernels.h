@@ -114,6 +114,8 @@ struct TonemapParams {
     const float* max_white_dev;  // non-NULL: max_white is read from device memory (auto max-white after the all-reduce)
 };
 cudaError_t launch_tonemap(const TonemapParams& p, int sm_count, cudaStream_t stream);
+// frame.depth_norm: (depth64 - near) / (far - near) per pixel, FP64 like HitInfo::normalizedDistance (RE/Shape.h:40-42), rounded to FP32
+cudaError_t launch_depth_norm(const double* depth64, int64_t n_pixels, double near_plane, double far_plane, float* out, int sm_count, cudaStream_t stream);
 // max luminance (RE/RaytracingEngine.cpp:100-104) into *out (device float, bit pattern max as uint)
 cudaError_t launch_max_luminance(const float4* hdr, int64_t n_pixels, unsigned int* out_bits, int sm_count,
                                  cudaStream_t stream);

@@ -385,8 +385,13 @@ constexpr int kRenderMaxThreads = 512;  // render kernel at 1 CTA/SM (large scen
 constexpr int kTileW = 8, kTileH = 4;   // one warp = K stacked 8x4 pixel groups (coherent primary and shadow rays)
 
 // K = pixels per thread: lane (lx, ly) owns pixels (x0 + lx, y0 + ly + 4k), k < K, of its warp's 8 x 4K tile.
+#ifndef RTE_RK_T
+#define RTE_RK_T 256
+#define RTE_RK_B 2
+#endif
+constexpr int kReflThreads = RTE_RK_T, kReflBlocks = RTE_RK_B;
 template <int K, bool kReflect>
-__global__ void __launch_bounds__(kRenderMaxThreads, 1) render_kernel(const __grid_constant__ RenderParams P) {
+__global__ void __launch_bounds__(kReflect ? kReflThreads : kRenderMaxThreads, kReflect ? kReflBlocks : 1) render_kernel(const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
     __shared__ DevScene s_sc;
     __shared__ __align__(8) uint64_t s_bar;
@@ -1256,7 +1261,11 @@ cudaError_t launch_render(const RenderParams& p0, int sm_count, cudaStream_t str
         return launch_render_fn((const void*)render_fast_kernel<kViewPixels, false, false>, (const void*)render_fast_kernel<kViewPixels, true, false>,
                                 kFastThreads, kFastMinBlocks, kViewPixels, p, sm_count, stream, true, limit, kBigThreads);
     }
-    const void* fn = p.sc.reflective ? (const void*)render_kernel<1, true> : (const void*)render_kernel<1, false>;
+    if (p.sc.reflective) {
+        const void* fr = (const void*)render_kernel<1, true>;
+        return launch_render_fn(fr, fr, kReflThreads, kReflBlocks, 1, p, sm_count, stream, false, 0, kReflThreads);
+    }
+    const void* fn = (const void*)render_kernel<1, false>;
     return launch_render_fn(fn, fn, kRenderThreads, 2, 1, p, sm_count, stream);
 }
 

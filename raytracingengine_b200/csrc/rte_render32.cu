@@ -792,7 +792,7 @@ bool fp32_path_eligible(const RenderParams& p) {
     const rte_frame& f = p.out;
     return !p.sc.reflective && !p.sc.transparent && p.sc.nt == 0 && p.sc.ns > 0 && p.sc.np <= kR32Planes && p.sc.nl <= kR32Lights &&
            !p.exact_shadows && !p.no_filter && !p.force_general && !p.no_cull && p.pass_mode == 0 && !p.exact_fp64 &&
-           !f.hdr64 && !f.depth && !f.depth64 && !f.normal && !f.albedo && p.bias >= 1e-6 && p.bias <= 1e-1;
+           !f.hdr64 && !f.depth && !f.depth64 && !f.depth_norm && !f.normal && !f.albedo && p.bias >= 1e-6 && p.bias <= 1e-1;
 }
 
 cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream) {

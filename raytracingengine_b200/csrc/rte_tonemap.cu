@@ -297,6 +297,19 @@ cudaError_t launch_tonemap64(const Tonemap64Params& p, int sm_count, cudaStream_
     return cudaGetLastError();
 }
 
+// HitInfo::normalizedDistance over the frame's FP64 depth (RE/Shape.h:40-42); a miss (+inf) stays +inf for every finite near < far
+__global__ void __launch_bounds__(kTmThreads) depth_norm_kernel(const double* __restrict__ depth64, int64_t n, double near_plane, double far_plane, float* __restrict__ out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = (float)div64(depth64[i] - near_plane, far_plane - near_plane);
+}
+cudaError_t launch_depth_norm(const double* depth64, int64_t n, double near_plane, double far_plane, float* out, int sm_count, cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    int64_t blocks = (n + kTmThreads - 1) / kTmThreads;
+    if (blocks > (int64_t)sm_count * 8) blocks = (int64_t)sm_count * 8;
+    depth_norm_kernel<<<(unsigned)blocks, kTmThreads, 0, stream>>>(depth64, n, near_plane, far_plane, out);
+    return cudaGetLastError();
+}
+
 // max over pixels of luminance() (RE/RaytracingEngine.cpp:100-104); non-negative floats order like their bits
 __global__ void __launch_bounds__(kTmThreads) max_luminance_kernel(const float4* __restrict__ hdr, int64_t n, unsigned int* out_bits) {
     float m = 0.0f;

@@ -144,7 +144,7 @@ class PinnedBuffer:
 FRAME_FIELDS = {
     "hdr": (np.float32, (4,)), "hdr64": (np.float64, (3,)), "rgb8": (np.uint8, (3,)),
     "prim_id": (np.uint32, ()), "depth": (np.float32, ()), "depth64": (np.float64, ()),
-    "normal": (np.float32, (4,)), "albedo": (np.float32, (4,)), "light_mask": (np.uint32, ()),
+    "normal": (np.float32, (4,)), "albedo": (np.float32, (4,)), "light_mask": (np.uint32, ()), "depth_norm": (np.float32, ()),
 }
 
 

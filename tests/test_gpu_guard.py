@@ -33,11 +33,11 @@ CASES = {
     "fp32_odd": (lambda: scenes.synthetic_room(203, 117, 150.0, 300, 3, 11), ("hdr", "rgb8", "prim_id", "light_mask"), dict(tonemap_op=_abi.TM_ACES)),
     "fp32_band": (lambda: scenes.config2(scale=0.1), ("hdr", "rgb8"), dict(tonemap_op=_abi.TM_REINHARD_JODIE, row0=13, row1=150)),
     "fp32_stripes": (lambda: scenes.config2(scale=0.1), ("rgb8", "prim_id"), dict(tonemap_op=_abi.TM_ACES, row0=8, row1=216, stripe_rows=8, stripe_period=24)),
-    "exact_views": (lambda: scenes.config2(scale=0.1), ("hdr", "hdr64", "rgb8", "prim_id", "depth", "depth64", "normal", "albedo", "light_mask"),
+    "exact_views": (lambda: scenes.config2(scale=0.1), ("hdr", "hdr64", "rgb8", "prim_id", "depth", "depth64", "depth_norm", "normal", "albedo", "light_mask"),
                     dict(tonemap_op=_abi.TM_ACES)),
     "exact_grid": (lambda: scenes.mixed_scene(187, 101, 140.0), ("hdr64", "rgb8", "prim_id", "depth64", "normal", "light_mask"),
                    dict(tonemap_op=_abi.TM_UNCHARTED2, flags=_abi.FLAG_EXACT_GRID)),
-    "reflective": (lambda: scenes.config1(121, 77), ("hdr64", "rgb8", "prim_id"), dict(tonemap_op=_abi.TM_ACES)),
+    "reflective": (lambda: scenes.config1(121, 77), ("hdr64", "rgb8", "prim_id", "depth_norm"), dict(tonemap_op=_abi.TM_ACES)),
 }
 
 
@@ -81,3 +81,27 @@ def test_tonemap_outputs_stay_inside_their_buffers(engine, n):
     engine.max_luminance_device(src.ptr, n, white.ptr)
     engine.synchronize()
     white.check("max luminance")
+
+
+@pytest.mark.parametrize("case", ["c1", "c2", "mixed_grid"])
+def test_depth_norm_is_normalized_distance(engine, case):
+    """frame.depth_norm = HitInfo::normalizedDistance(camera) of the primary hit (RE/Shape.h:40-42), FP64 arithmetic rounded to
+    FP32, +inf on a miss; asking for it alone (no depth64) works too."""
+    flags = 0
+    if case == "c1":
+        arrays, cam = scenes.config1(160, 120)
+    elif case == "c2":
+        arrays, cam = scenes.config2(scale=0.05)
+        cam.nearPlaneDistance, cam.farPlaneDistance = 2.5, 750.0
+    else:
+        arrays, cam = scenes.mixed_scene(150, 90, 120.0)
+        cam.nearPlaneDistance, cam.farPlaneDistance = 1.0, 300.0
+        flags = _abi.FLAG_EXACT_GRID
+    engine.upload(arrays, cam)
+    both = engine.render_host(outputs=("depth64", "depth_norm"), flags=flags)
+    alone = engine.render_host(outputs=("depth_norm",), flags=flags)
+    with np.errstate(invalid="ignore"):
+        want = ((both["depth64"] - cam.nearPlaneDistance) / (cam.farPlaneDistance - cam.nearPlaneDistance)).astype(np.float32)
+    assert np.isfinite(both["depth64"]).any()
+    assert np.array_equal(both["depth_norm"], want) and np.array_equal(alone["depth_norm"], want)
+    assert np.all(np.isinf(want[np.isinf(both["depth64"])]))
