@@ -11,6 +11,9 @@ echo "== pytest -m gpu"; timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | 
 echo "== smoke"; timeout 300 python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -5 | tee $OUT/${TAG}_smoke.txt
 echo "== bench"; timeout 900 python bench.py --steps 20 --warmup 3 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "exit $?"; cut -c1-1500 $OUT/${TAG}_bench.json; tail -5 $OUT/${TAG}_bench.err
 echo "== bench reference"; timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/${TAG}_bench_ref.json 2> $OUT/${TAG}_bench_ref.err; cut -c1-600 $OUT/${TAG}_bench_ref.json; tail -3 $OUT/${TAG}_bench_ref.err
+echo "== C1 (the reference's default workload), both arms, 1 and 32 samples per pixel"; timeout 600 python tools/c1_bench.py > $OUT/${TAG}_c1.json 2> $OUT/${TAG}_c1.err; cut -c1-900 $OUT/${TAG}_c1.json; tail -3 $OUT/${TAG}_c1.err
+echo "== tonemap pass and its memory pattern without arithmetic"; (python tools/tm_probe.py; RTE_TM_NULL=1 python tools/tm_probe.py; RTE_TM_NULL=2 python tools/tm_probe.py) 2>&1 | tee $OUT/${TAG}_tm_probe.txt
+echo "== grid rebuild cost"; (for d in 1 8; do python tools/grid_probe.py c2 $d; python tools/grid_probe.py c5 $d; done) 2>&1 | tee $OUT/${TAG}_grid_probe.txt
 echo "== quick bench all configs"; timeout 600 python tools/quick_bench.py c2 c3 c4 c5 c1 --rgb8 2>&1 | tee $OUT/${TAG}_quick.txt
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-c5"
 echo "== ncu launch list"

@@ -98,10 +98,10 @@ if os.path.exists(ll):
     for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
         lines.append(f"| `{k}` | {n} | {t:.0f} | {100 * t / tot:.1f}% |")
     lines += ["", "(`at::` kernels are torch's L2-flush memsets / clones of the harness, not part of the step; `ffma*_peak_kernel` is the",
-              "FP32-peak micro-benchmark; the step itself is ONE launch, `render32_kernel`; `grid_build_kernel<0|1>` + `grid_scan_kernel` rebuild the direction grids after a scene upload; `render_fast_kernel` / `tonemap64_kernel` are the exact path of the frame check.)", ""]
+              "FP32-peak micro-benchmark; the step itself is `grid_build_kernel<0>` + `grid_scan_kernel` + `grid_build_kernel<1>` (the direction grids, rebuilt every step) + `render32_kernel`; `render_fast_kernel` / `tonemap64_kernel` are the exact path of the frame check.)", ""]
     import shutil
     shutil.copy(ll, f"{P}/{name}_launches.csv")
-for f in ("bench.json", "bench_ref.json", "quick.txt", "gpu.txt", "pytest_gpu.txt", "smoke.txt"):
+for f in ("bench.json", "bench_ref.json", "quick.txt", "gpu.txt", "pytest_gpu.txt", "smoke.txt", "c1.json", "tm_probe.txt", "grid_probe.txt"):
     src = f"{G}/{tag}_{f}"
     if os.path.exists(src):
         import shutil
