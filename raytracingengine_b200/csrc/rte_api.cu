@@ -31,10 +31,7 @@ struct DevBuf {
 
 }  // namespace
 
-#ifndef RTE_HOST_TAIL_DIV
-#define RTE_HOST_TAIL_DIV 8  // the second band = the last 1/8 of the rows (measured on C2 at 4K: 1/4 3.19 ms, 1/6 3.13, 1/8 3.07, 1/12 3.11, 1/16 3.17)
-#endif
-constexpr int kHostBandsMax = 2;    // row bands of one rte_render_host call
+constexpr int kHostBandsMax = 3;    // row bands of one rte_render_host call
 constexpr int kHostBandRows = 1024;  // calls of fewer rows are one band
 
 struct rte_ctx {
@@ -760,11 +757,8 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
         if ((rc = reserve(ctx, *it.buf, n * it.px_bytes))) return rc;
         *it.dev = it.buf->p;
     }
-    // Two row bands: the second (the last eighth of the rows) is rendered and tonemapped on the context's stream while the
-    // outputs of the first travel to the host on the copy stream.  Measured on B200 (C2 at 4K, 24.9 MB of RGB8): every extra
-    // launch of the persistent render kernel costs ~0.1 ms (ramp-up plus the tail of ~50 us tiles), the copy 0.48 ms: four
-    // equal bands lose more than they hide (3.64 ms against 3.56 ms unsplit), 7/8 + 1/8 hides most of the copy.
-    // Bands are whole stripes when the rows are striped; registered peer frames (multi-GPU output exchange) keep one launch.
+    // Row bands: while the outputs of one band travel to the host on the copy stream, the next band is rendered on the context's
+    // stream (schedule below).  Bands are whole stripes when the rows are striped; registered peer frames (multi-GPU output exchange) keep one launch.
     // With a pageable destination cudaMemcpyAsync blocks the host until band 0 has been copied, before band 1 is enqueued:
     // the split would only add a launch, so it is used for pinned destinations only.
     bool pinned = true;
@@ -774,16 +768,40 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
         if (cudaPointerGetAttributes(&at, it.host) != cudaSuccess) { (void)cudaGetLastError(); pinned = false; }
         else if (at.type != cudaMemoryTypeHost) pinned = false;
     }
+    // Band schedule in eighths of the rows.  A band's copy should take about as long as the next band's render, and every launch
+    // of a persistent render kernel costs ~45 us before and after it is full:
+    //   exact kernels (C2 at 4K: 2.8 ms of render against 0.46 ms of copy): 7/8 + 1/8 (measured 1/4 3.19 ms, 1/6 3.13, 1/8 3.07, 1/12 3.11);
+    //   FP32 path (0.86 ms of render against the same copy): 5/8 + 2/8 + 1/8 — the model t_render = 0.86 f + 0.045, t_copy = 0.457 f
+    //   gives 1.25 ms for 7/8 + 1/8, 1.09 for the best two bands and 1.05 for these three; measured 1.33 -> see DESIGN.md §8.
     const int unit = o.stripe_rows > 0 ? o.stripe_rows : 4;
-    int rows_per = o.n_rows;
-    if (o.n_rows >= kHostBandRows && ctx->n_peers == 0 && pinned) rows_per = (o.n_rows - o.n_rows / RTE_HOST_TAIL_DIV + unit - 1) / unit * unit;
-    if (rows_per < 1) rows_per = 1;
+    int band_rows[kHostBandsMax] = {o.n_rows, 0, 0}, n_bands = 1;
+    if (o.n_rows >= kHostBandRows && ctx->n_peers == 0 && pinned) {
+        RenderParams q{};
+        q.sc = ctx->sc; q.cam = ctx->cam; q.out = df; q.bias = o.bias; q.tonemap_op = o.tonemap_op;
+        q.exact_shadows = (o.flags & RTE_FLAG_EXACT_SHADOWS) ? 1 : 0; q.no_filter = (o.flags & RTE_FLAG_NO_FILTER) ? 1 : 0;
+        q.force_general = (o.flags & RTE_FLAG_GENERAL_KERNEL) ? 1 : 0; q.no_cull = (o.flags & RTE_FLAG_NO_CULL) ? 1 : 0;
+        q.pass_mode = (o.flags & RTE_FLAG_SINGLE_PASS) ? 1 : (o.flags & RTE_FLAG_TWO_PASS) ? 2 : 0;
+        q.exact_fp64 = (o.flags & RTE_FLAG_EXACT_FP64) ? 1 : 0;
+        const bool fast = fp32_path_eligible(q);
+        const int eighths[2][kHostBandsMax] = {{7, 1, 0}, {5, 2, 1}};
+        int left = o.n_rows;
+        n_bands = 0;
+        for (int k = 0; k < kHostBandsMax && left > 0; ++k) {
+            const int e = eighths[fast ? 1 : 0][k];
+            if (e == 0) break;
+            const bool final_band = k + 1 == kHostBandsMax || eighths[fast ? 1 : 0][k + 1] == 0;
+            int r = final_band ? left : (int)(((long long)o.n_rows * e / 8 + unit - 1) / unit * unit);
+            if (r > left) r = left;
+            band_rows[n_bands++] = r;
+            left -= r;
+        }
+        if (left > 0) band_rows[n_bands - 1] += left;
+    }
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_copied, ctx->stream));
     RTE_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_copied, 0));  // the copy stream starts behind earlier work of the context
-    int b = 0;
-    for (int y0 = 0; y0 < o.n_rows || b == 0; y0 += rows_per, ++b) {
+    for (int b = 0, y0 = 0; b < n_bands; y0 += band_rows[b], ++b) {
         Defaults ob = o;
-        ob.n_rows = o.n_rows - y0 < rows_per ? o.n_rows - y0 : rows_per;
+        ob.n_rows = band_rows[b];
         if (o.stripe_rows > 0) ob.row0 = o.row0 + (y0 / o.stripe_rows) * o.stripe_period;  // y0 is a multiple of stripe_rows
         else { ob.row0 = o.row0 + y0; ob.row1 = ob.row0 + ob.n_rows; }
         const size_t off = (size_t)y0 * W;
@@ -793,7 +811,7 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
         bf.depth = df.depth ? df.depth + off : nullptr;         bf.depth64 = df.depth64 ? df.depth64 + off : nullptr;
         bf.normal = df.normal ? df.normal + off * 4 : nullptr;  bf.albedo = df.albedo ? df.albedo + off * 4 : nullptr;
         bf.light_mask = df.light_mask ? df.light_mask + off : nullptr;  bf.depth_norm = df.depth_norm ? df.depth_norm + off : nullptr;
-        const bool last = y0 + rows_per >= o.n_rows;
+        const bool last = b + 1 == n_bands;
         if ((rc = do_render(ctx, ob, &bf, b == 0, last))) return rc;
         RTE_CUDA(ctx, cudaEventRecord(ctx->ev_band[b], ctx->stream));
         RTE_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_band[b], 0));
@@ -802,7 +820,6 @@ extern "C" int rte_render_host(rte_ctx* ctx, const rte_render_opts* opts, const 
             if (it.host && bytes)
                 RTE_CUDA(ctx, cudaMemcpyAsync((char*)it.host + off * it.px_bytes, (char*)it.buf->p + off * it.px_bytes, bytes, cudaMemcpyDeviceToHost, ctx->copy_stream));
         }
-        if (last) break;
     }
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_copied, ctx->copy_stream));
     RTE_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copied, 0));  // later work of the context must not overwrite the staging buffers
