@@ -91,7 +91,7 @@ struct rte_ctx {
     rte_stats stats{};
 
     // staging for the *_host variants (grow-only)
-    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64, s_hits, s_fix, s_dnorm, s_dn64;
+    DevBuf s_hdr, s_hdr64, s_rgb8, s_prim, s_depth, s_depth64, s_normal, s_albedo, s_lmask, s_tm64, s_hits, s_fix, s_dnorm, s_dn64, s_tileflags;
     DevBuf s_tm_in, s_tm_out[RTE_TM_COUNT], s_q_o, s_q_d, s_q_m, s_q_out;
 };
 
@@ -291,7 +291,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphhl, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
                       &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->b_grid_count, &ctx->b_grid_start, &ctx->b_grid_entries, &ctx->b_grid_aggr, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
-                      &ctx->s_depth64, &ctx->s_dnorm, &ctx->s_dn64, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
+                      &ctx->s_depth64, &ctx->s_dnorm, &ctx->s_dn64, &ctx->s_tileflags, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
     for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
     for (DevBuf& b : ctx->s_tm_out) if (b.p) cudaFree(b.p);
@@ -643,6 +643,38 @@ static int do_render(rte_ctx* ctx, const Defaults& o, const rte_frame* frame, bo
         RTE_CUDA(ctx, launch_render32(p, ctx->sm_count, ctx->stream));
         ctx->render_launches += 1;
         if (xp.n_peers > 0) { RTE_CUDA(ctx, launch_exchange_rgb8(xp, ctx->sm_count, ctx->stream)); ctx->render_launches += 1; }
+        if (last) {
+            RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
+            RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));
+            ctx->render_timed = true;
+        }
+        return RTE_OK;
+    }
+    // Reflective scenes with few primitives (rte_render32r.cu): FP32 values, interval decisions over all primitives; the tiles it
+    // flags are rendered again by the exact kernel in a second launch (generic filters, no views to build).
+    if (o.n_rows > 0 && fp32r_path_eligible(p)) {
+        const size_t n_tiles = (size_t)((ctx->cam.width + 7) / 8) * (size_t)((o.n_rows + 3) / 4);
+        int rc = reserve(ctx, ctx->s_tileflags, n_tiles);
+        if (rc) return rc;
+        RTE_CUDA(ctx, cudaMemsetAsync(ctx->s_tileflags.p, 0, n_tiles, ctx->stream));
+        if (first) {
+            RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_stats, 0, sizeof(unsigned long long) * (kStatCount + 2), ctx->stream));
+            RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r0, ctx->stream));
+        } else {
+            RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned long long) * 2, ctx->stream));
+        }
+        p.tile_flags = (uint8_t*)ctx->s_tileflags.p;
+        RTE_CUDA(ctx, launch_render32r(p, ctx->sm_count, ctx->stream));
+        RenderParams q = p;
+        q.tile_flags = nullptr; q.tile_mask = (const uint8_t*)ctx->s_tileflags.p;
+        q.plan = SmemPlan{};
+        q.plan.stage_sph = 1; q.plan.stage_tri = 1;
+        q.plan.sph_bytes = (uint32_t)ctx->sc.ns_pad * 16u; q.plan.tri_bytes = (uint32_t)ctx->sc.nt_pad * 48u;
+        q.plan.total = (size_t)q.plan.sph_bytes + q.plan.tri_bytes;
+        q.force_general = 1;
+        RTE_CUDA(ctx, cudaMemsetAsync(ctx->d_tile_counter, 0, sizeof(unsigned int), ctx->stream));
+        RTE_CUDA(ctx, launch_render(q, ctx->sm_count, ctx->stream));
+        ctx->render_launches += 2;
         if (last) {
             RTE_CUDA(ctx, cudaEventRecord(ctx->ev_r1, ctx->stream));
             RTE_CUDA(ctx, cudaMemcpyAsync(ctx->h_stats, ctx->d_stats, sizeof(unsigned long long) * kStatCount, cudaMemcpyDeviceToHost, ctx->stream));

@@ -50,6 +50,8 @@ struct RenderParams {
     int32_t exact_grid;      // RTE_FLAG_EXACT_GRID: the exact path walks the direction grids (render_exact_grid_kernel) even where the views fit
     int32_t exact_fp64;      // RTE_FLAG_EXACT_FP64: never take the FP32 production path (rte_render32.cu)
     DevGrid grid;            // FP32 path: per-origin direction grids (rte_grid.cuh), built per camera / bias
+    uint8_t* tile_flags;               // reflective FP32 path (rte_render32r.cu): one byte per 8 x 4 tile, set when the tile needs the exact kernel
+    const uint8_t* tile_mask;          // exact kernel render_kernel<1, *>: render only the tiles whose byte is set (and write RGB8 itself)
     unsigned int* tile_counter;        // zeroed before launch
     unsigned long long* stats;         // kStatCount counters, zeroed before launch
 };
@@ -69,6 +71,9 @@ cudaError_t launch_grid_count_scan(const DevScene& sc, const DevCamera& cam, dou
 cudaError_t launch_grid_fill(const DevScene& sc, const DevCamera& cam, double bias, int G, uint32_t* count, uint32_t* cell_start, uint32_t* entries,
                              uint32_t capacity, cudaStream_t stream);
 cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream);
+// reflective scenes with few primitives (rte_render32r.cu); tiles it flags are rendered by launch_render with p.tile_mask
+bool fp32r_path_eligible(const RenderParams& p);
+cudaError_t launch_render32r(const RenderParams& p, int sm_count, cudaStream_t stream);
 // would launch_render split this call into a primary-ray launch and a shading launch (it then needs p.hits)?
 bool two_pass_wanted(const RenderParams& p);
 // (re)builds sc.views for this camera / bias (rte_views.cuh); a no-op for scenes without spheres

@@ -420,6 +420,7 @@ __global__ void __launch_bounds__(kReflect ? kReflThreads : kRenderMaxThreads, k
     while (tile < n_tiles) {
         unsigned int next = 0;
         if (lane == 0) next = atomicAdd(P.tile_counter, 1u);  // prefetch the next tile id behind the work
+        if (P.tile_mask && !P.tile_mask[tile]) { tile = __shfl_sync(kFullMask, next, 0); continue; }  // second pass of rte_render32r.cu: flagged tiles only
         const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile % (unsigned)tiles_x);
         int px[K], py[K];
         bool inb[K];
@@ -461,9 +462,15 @@ __global__ void __launch_bounds__(kReflect ? kReflThreads : kRenderMaxThreads, k
             const int64_t oi = out_idx[k];
             if (P.out.hdr) reinterpret_cast<float4*>(P.out.hdr)[oi] = make_float4((float)c[k].x, (float)c[k].y, (float)c[k].z, 0.f);
             if (P.out.hdr64) { P.out.hdr64[3 * oi] = c[k].x; P.out.hdr64[3 * oi + 1] = c[k].y; P.out.hdr64[3 * oi + 2] = c[k].z; }
+            if (P.tile_mask && P.out.rgb8) {  // (the full-frame exact path leaves RGB8 to tonemap64_kernel; a few flagged tiles write their own bytes)
+                const uchar3 u = tm64::to_color(tm64::apply(P.tonemap_op, c[k], P.max_white, P.jodie_a));
+                uint8_t* d = P.out.rgb8 + 3 * oi;
+                d[0] = u.x; d[1] = u.y; d[2] = u.z;
+            }
         }
         // per-warp statistics: one REDUX per counter, lane 0 accumulates in shared memory
-        const uint32_t v[kStatCount] = {n_in, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, cnt.confirms, cnt.sph_exec};
+        // (second pass of rte_render32r.cu: fp64_confirms already holds the pixel samples of the flagged tiles)
+        const uint32_t v[kStatCount] = {n_in, cnt.shadow, cnt.secondary, cnt.sph, cnt.pl, cnt.tri, cnt.marches, P.tile_mask ? 0u : cnt.confirms, cnt.sph_exec};
 #pragma unroll
         for (int k = 0; k < kStatCount; ++k) {
             const uint32_t s = __reduce_add_sync(kFullMask, v[k]);

@@ -1,0 +1,448 @@
+// rte_render32r.cu — the FP32 production path for REFLECTIVE scenes with few primitives (sm_100a): the reference's default
+// scene (main(): five slightly specular planes, a specular box mesh, two lights — config C1) and its relatives.
+//
+// Replaces Scene::TraceRay's recursion with reflection (RE/Scene.h:131-198; no transparent material, so every node has at
+// most one child and the recursion is a chain), directLightning with the Blinn-Phong term (RE/Scene.h:79-129) and
+// tonemap()/toColor for those scenes, to the bar BASELINE.json states: nearest-hit index and shadow visibility of the primary
+// hit bit-exact, RGB8 within +-1 LSB.  ("RE/" = /root/reference/RaytracingEngine/.)
+//
+//  * Values are FP32 (hit points in a handful of cheap FP64 operations), decisions come from FP32 INTERVALS (rte_interval.cuh)
+//    over ALL primitives — a reflected ray has no common origin with its neighbours, so the per-origin direction grids of
+//    rte_render32.cu do not apply; the path takes scenes of at most kRrPrims spheres + triangles, everything in shared memory.
+//  * The CHAIN of rays — origin, direction, hit point, normal, reflected direction — is carried in FP64 with cheap operations
+//    (MUFU seeds + Newton steps instead of DDIV / DSQRT, ~1e-15 relative), ~40 FP64 instructions per bounce: a reflected ray in
+//    FP32 would not be the reference's ray any more (its deviation triples with every bounce, and after two bounces it is of the
+//    order of the shadow bias: measured, every pixel was flagged).  The interval tests see that ray rounded once, like a
+//    primary ray.
+//  * A decision that stays inconclusive flags the pixel — while the path weight (the product of the reflectivenesses so far)
+//    exceeds kRrFreeWeight.  Below it a wrong branch moves the pixel by less than 1e-5 of a radiance difference, far inside
+//    the 1 / 255 of a byte, and the best guess is taken.  A tile with a flagged pixel is rendered again, entirely, by the exact
+//    kernel (rte_render.cu: render_kernel<1, true> over the flagged tiles): those tiles carry the reference's own bits.
+#include <algorithm>
+
+#include "rte_grid.cuh"
+#include "rte_interval.cuh"
+#include "rte_kernels.h"
+#include "rte_tonemap.cuh"
+
+namespace rte {
+
+constexpr int kRrThreads = 256;
+constexpr int kRrPrims = 64, kRrPlanes = 8, kRrLights = 16;
+constexpr float kRrFreeWeight = 1e-5f;
+// A chain ends once its weight falls below this: what the reference still adds below it (down to maxRecursion = 10) is less than
+// 1e-7 of a radiance per node, under the resolution of the FP32 pixel.  (C1: the planes reflect 1 %: four or five nodes instead of
+// ten.)  The ray counters therefore count the rays traced, fewer than the reference's for such scenes.
+constexpr float kRrCutWeight = 1e-7f;
+constexpr unsigned kFullMask = 0xFFFFFFFFu;
+
+struct Sph32r { float hx, hy, hz, r, lx, ly, lz; int mat; };
+struct Light32r { float hi[3], lo[3], E[3]; };
+struct SceneRr {
+    Sph32r sph[kRrPrims];
+    Tri32 tri[kRrPrims];
+    Plane32 pl[kRrPlanes];
+    Light32r li[kRrLights];
+    double cam[3];
+    int ns, nt, np, nl;
+};
+
+#ifdef RTE_RR_DEBUG
+#define RR_WHY(code) do { if (out.why == 0u) out.why = (uint32_t)(code) + 16u * (uint32_t)depth_dbg; } while (0)
+#else
+#define RR_WHY(code) do { } while (0)
+#endif
+struct PxR {
+    uint32_t why;
+    float r, g, b;
+    uint32_t prim, lmask;
+    uint32_t c_shadow, c_secondary, c_sph, c_pl, c_tri;
+};
+
+__device__ __forceinline__ void split64(double v, float& hi, float& lo) { hi = (float)v; lo = (float)(v - (double)hi); }
+
+// One sample of one pixel per lane.  Returns false when a decision that matters was inconclusive (the tile is then rendered
+// again by the exact kernel and nothing of `out` is used).
+__device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S, int px, int py, bool alive, int sample, PxR& out) {
+    const DevScene& sc = P.sc;
+    const int ns = S.ns, nt = S.nt, np = S.np, nl = S.nl;
+    const float bias = (float)P.bias;
+    const int max_depth = P.max_depth;
+    out.r = out.g = out.b = 0.0f; out.why = 0u;
+    int depth_dbg = 0; (void)depth_dbg;
+    out.prim = kMiss; out.lmask = 0u; out.c_shadow = out.c_secondary = out.c_sph = out.c_pl = out.c_tri = 0u;
+    bool ok = true;
+    // ---- Camera::getRay, RE/Math.h:99-121 (the reference's FP64 operations up to the normalisation)
+    double Ox = S.cam[0], Oy = S.cam[1], Oz = S.cam[2];
+    double dx, dy, dz;  // the ray's direction: FP64 like its origin (see the header: the chain of rays is the reference's to ~1e-14)
+    {
+        double sx = (double)px - P.cam.half_w, sy = P.cam.half_h - (double)py;
+        if (sample > 0) {
+            const int64_t pixel = (int64_t)py * P.cam.width + px;
+            sx += jitter01(P.cam.jitter_seed, pixel, sample, 0);
+            sy += jitter01(P.cam.jitter_seed, pixel, sample, 1);
+        }
+        const double vx = sx - Ox, vy = sy - Oy, vz = (Oz + P.cam.focal) - Oz;
+        const double len2 = vx * vx + vy * vy + vz * vz;
+        if (!(len2 > 1e-20) || !(len2 < 1e30)) { RR_WHY(1); ok = false; }
+        const double inv = rsqrt64_fast(len2);
+        dx = vx * inv; dy = vy * inv; dz = vz * inv;
+    }
+    // what the interval tests see of the ray: the FP64 origin as hi + lo floats (exact), the direction rounded to FP32 — the
+    // same deviation (one rounding, part of the built-in margins) at every depth, because the chain itself is carried in FP64
+    const float eo = 0.0f, ed = 4.0f * kEps32;
+    float Dx = (float)dx, Dy = (float)dy, Dz = (float)dz;
+    float w = 1.0f;                       // weight of the node's light in the pixel
+    float ar = 0.0f, ag = 0.0f, ab = 0.0f;
+    bool live = alive && ok;
+    auto sky = [&]() {  // Scene::backgroundColor, RE/Scene.h:30-33
+        const float t = 0.5f * (Dy + 1.0f);
+        ar = __fmaf_rn(w, __fmaf_rn(0.5f, t, 1.0f - t), ar); ag = __fmaf_rn(w, __fmaf_rn(0.7f, t, 1.0f - t), ag); ab = __fmaf_rn(w, 1.0f, ab);
+    };
+#pragma unroll 1
+    for (int depth = 0; __any_sync(kFullMask, live); ++depth) {
+        depth_dbg = depth;
+        if (live && depth >= max_depth) { sky(); live = false; }  // TraceRay(recursionAmount >= maxRecursion), RE/Scene.h:132-134
+        if (!live) continue;
+        const bool free_guess = w <= kRrFreeWeight;  // decisions of this node cannot move a byte: take the best guess
+        float ohx, ohy, ohz, olx, oly, olz;
+        split64(Ox, ohx, olx); split64(Oy, ohy, oly); split64(Oz, ohz, olz);
+        const float o1 = fabsf(ohx) + fabsf(ohy) + fabsf(ohz);
+        // ---- Scene::IntersectClosest, RE/Scene.h:218-257, over every primitive, from intervals
+        Near32 nr;
+        nr.kind = RTE_HIT_NONE; nr.idx = 0; nr.lo = 0.0f; nr.hi = 0.0f; nr.amb_lo = INFINITY;
+#pragma unroll 1
+        for (int i = 0; i < ns; ++i) {
+            const Sph32r& s = S.sph[i];
+            const Cand32 c = classify_sphere(make_float4(s.hx, s.hy, s.hz, s.r), make_float4(s.lx, s.ly, s.lz, 0.0f), ohx, ohy, ohz, olx, oly, olz, Dx, Dy, Dz, eo, ed);
+            float lo, hi;
+            const int cls = reported_t(c, lo, hi);
+            if (cls == kCandHit) near_hit(nr, RTE_HIT_SPHERE, i, lo, hi);
+            else if (cls == kCandUnsure) near_unsure(nr, lo);
+        }
+#pragma unroll 1
+        for (int i = 0; i < np; ++i) {
+            float lo, hi;
+            const int cls = plane_interval(S.pl[i], ohx, ohy, ohz, o1, Dx, Dy, Dz, lo, hi, eo, ed);
+            if (cls == kCandHit) near_hit(nr, RTE_HIT_PLANE, i, lo, hi);
+            else if (cls == kCandUnsure) near_unsure(nr, 0.0f);
+        }
+#pragma unroll 1
+        for (int i = 0; i < nt; ++i) {
+            float lo, hi;
+            const int cls = tri_interval(S.tri[i], ohx, ohy, ohz, olx, oly, olz, Dx, Dy, Dz, eo, ed, lo, hi);
+            if (cls == kCandHit) near_hit(nr, RTE_HIT_TRIANGLE, i, lo, hi);
+            else if (cls == kCandUnsure) near_unsure(nr, lo);
+        }
+        out.c_sph += (uint32_t)ns; out.c_pl += (uint32_t)np; out.c_tri += (uint32_t)nt;
+        if (depth > 0) out.c_secondary += 1u;
+        if (near_ambiguous(nr) && !free_guess) { RR_WHY(2); ok = false; live = false; continue; }
+        if (nr.kind == RTE_HIT_NONE) { sky(); live = false; continue; }
+        // ---- the hit in cheap FP64 (no DDIV / DSQRT: ~1e-15 relative), normal, material
+        double t, nx64, ny64, nz64;
+        float Nx, Ny, Nz;
+        const float eN = 2.0f * kEps32;  // the FP32 copy of the normal
+        int mat, self = -1;
+        uint32_t report;
+        if (nr.kind == RTE_HIT_SPHERE) {
+            const double4 s = sc.sph64[nr.idx];
+            const double ocx = Ox - s.x, ocy = Oy - s.y, ocz = Oz - s.z;
+            const double bq = ocx * dx + ocy * dy + ocz * dz;
+            const double cq = fma(ocx, ocx, fma(ocy, ocy, ocz * ocz)) - s.w * s.w;
+            const double disc = fma(bq, bq, -cq);
+            const double sq = disc > 0.0 ? disc * rsqrt64_fast(disc) : 0.0;
+            const double mid = 0.5 * ((double)nr.lo + (double)nr.hi), t0 = -bq - sq, t1 = -bq + sq;
+            t = fabs(t0 - mid) <= fabs(t1 - mid) ? t0 : t1;  // the root the interval belongs to (near root, or the far one from inside)
+            const double ir = rcp64_fast(fabs(s.w));
+            nx64 = (fma(dx, t, Ox) - s.x) * ir; ny64 = (fma(dy, t, Oy) - s.y) * ir; nz64 = (fma(dz, t, Oz) - s.z) * ir;
+            mat = S.sph[nr.idx].mat; report = (uint32_t)nr.idx;
+        } else if (nr.kind == RTE_HIT_PLANE) {
+            const DevPlane& pl = sc.planes[nr.idx];
+            const double num = (pl.p0[0] - Ox) * pl.n[0] + (pl.p0[1] - Oy) * pl.n[1] + (pl.p0[2] - Oz) * pl.n[2];
+            const double den = pl.n[0] * dx + pl.n[1] * dy + pl.n[2] * dz;
+            t = num * rcp64_fast(den);
+            nx64 = pl.n[0]; ny64 = pl.n[1]; nz64 = pl.n[2];
+            mat = S.pl[nr.idx].mat; report = (uint32_t)nr.idx;
+        } else {
+            const DevTri64& T = sc.tri64[nr.idx];
+            const double hx = dy * T.e2[2] - dz * T.e2[1], hy = dz * T.e2[0] - dx * T.e2[2], hz = dx * T.e2[1] - dy * T.e2[0];
+            const double a = T.e1[0] * hx + T.e1[1] * hy + T.e1[2] * hz;
+            const double sx = Ox - T.a0[0], sy = Oy - T.a0[1], sz = Oz - T.a0[2];
+            const double qx = sy * T.e1[2] - sz * T.e1[1], qy = sz * T.e1[0] - sx * T.e1[2], qz = sx * T.e1[1] - sy * T.e1[0];
+            t = (T.e2[0] * qx + T.e2[1] * qy + T.e2[2] * qz) * rcp64_fast(a);
+            nx64 = T.n[0]; ny64 = T.n[1]; nz64 = T.n[2];
+            mat = S.tri[nr.idx].mat; report = S.tri[nr.idx].report;
+        }
+        const double Px = fma(dx, t, Ox), Py = fma(dy, t, Oy), Pz = fma(dz, t, Oz);
+        float Phx, Phy, Phz, Plx, Ply, Plz;
+        split64(Px, Phx, Plx); split64(Py, Phy, Ply); split64(Pz, Phz, Plz);
+        // the reference's hit point agrees with this one to ~1e-14 of the scene's size (its own FP64 roundings); eP leaves four digits
+        const float eP = 1e-10f * (1.0f + fabsf(Phx) + fabsf(Phy) + fabsf(Phz));
+        // frontFace = normal . incoming < 0, RE/Scene.h:146-148
+        const double nd64 = nx64 * dx + ny64 * dy + nz64 * dz;
+        if (fabs(nd64) <= 1e-11 && !free_guess) { RR_WHY(3); ok = false; live = false; continue; }
+        const bool front = nd64 < 0.0;
+        if (!front) { nx64 = -nx64; ny64 = -ny64; nz64 = -nz64; }
+        Nx = (float)nx64; Ny = (float)ny64; Nz = (float)nz64;
+        if (nr.kind == RTE_HIT_SPHERE && front && bias >= 1e-5f) self = nr.idx;
+        if (depth == 0) out.prim = ((uint32_t)nr.kind << 30) | report;
+        mat = (mat >= 0 && mat < sc.nm) ? mat : sc.nm;
+        const rte_material& M = sc.materials[mat];
+        const float m_spec = (float)M.specular, m_shin = (float)M.shininess;
+        const bool spec_on = M.transparency <= 0.0 && M.specular > 0.0;  // RE/Scene.h:116
+        // ---- Scene::directLightning, RE/Scene.h:79-129; shadow origin so = P + N * bias (RE/Scene.h:104)
+        const double Sx = fma(nx64, P.bias, Px), Sy = fma(ny64, P.bias, Py), Sz = fma(nz64, P.bias, Pz);
+        float shx, shy, shz, slx, sly, slz;
+        split64(Sx, shx, slx); split64(Sy, shy, sly); split64(Sz, shz, slz);
+        const float so1 = fabsf(shx) + fabsf(shy) + fabsf(shz);
+        const float eso = eP;  // (so = P + N * bias with the FP64 normal)
+        float dr = 0.0f, dg = 0.0f, db = 0.0f, sr = 0.0f, sg = 0.0f, sb = 0.0f;
+#pragma unroll 1
+        for (int j = 0; j < nl; ++j) {
+            const Light32r& Lt = S.li[j];
+            const float vx = (Lt.hi[0] - Phx) + (Lt.lo[0] - Plx), vy = (Lt.hi[1] - Phy) + (Lt.lo[1] - Ply), vz = (Lt.hi[2] - Phz) + (Lt.lo[2] - Plz);
+            const float d2 = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, vx * vx));
+            if (!(d2 > 0.0f)) { if (!free_guess && d2 <= eP * eP) { RR_WHY(4); ok = false; } continue; }
+            float inv = rsqrtf(d2);
+            inv = inv * __fmaf_rn(-0.5f * d2 * inv, inv, 1.5f);
+            const float dist = d2 * inv;
+            const float Lx = vx * inv, Ly = vy * inv, Lz = vz * inv;
+            const float eL = 2.0f * eP * inv + 8.0f * kEps32;  // |L - L_ref|
+            const float ndl = __fmaf_rn(Nz, Lz, __fmaf_rn(Ny, Ly, Nx * Lx));
+            // guards of RE/Scene.h:89-101: ndl > 0, dist > bias — certain, or the pixel is flagged
+            bool cast;
+            if (fabsf(ndl) < eN + eL + 32.0f * kEps32 || fabsf(dist - bias) < eP + 1e-5f * bias + 1e-30f) {
+                if (!free_guess) { RR_WHY(5); ok = false; break; }
+                cast = false;
+            } else {
+                cast = ndl > 0.0f && dist > bias;
+            }
+            if (!cast) continue;
+            const float maxDist = dist - bias;
+            const float dt = 24.0f * kEps32 * (dist + so1) + 1e-7f + eP + eso;  // slack of the range ends (maxDist, bias) against the candidate bounds
+            const float tmax_lo = maxDist - dt, tmax_hi = maxDist + dt, bias_hi = bias + dt;
+            // computeTransmittance (RE/Scene.h:35-77) for opaque scenes: some primitive reports t in (bias, maxDist) — unless one
+            // reports t <= bias (the march steps past it): certain occluder, certain miss, or unsure.  Canonical order.
+            bool occl = false, unsure = false;
+            int first_s = ns, first_p = np, first_t = nt;
+#pragma unroll 1
+            for (int i = 0; i < ns && !occl && !unsure; ++i) {
+                if (i == self) continue;  // so lies outside the sphere the point is on, the ray leaves it: both roots < 0
+                const Sph32r& s = S.sph[i];
+                const Cand32 c = classify_sphere(make_float4(s.hx, s.hy, s.hz, s.r), make_float4(s.lx, s.ly, s.lz, 0.0f), shx, shy, shz, slx, sly, slz, Lx, Ly, Lz, eso, eL);
+                float lo, hi;
+                const int cls = reported_t(c, lo, hi);
+                if (cls == kCandMiss || lo > tmax_hi) continue;
+                if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; first_s = i; }
+                else unsure = true;
+            }
+#pragma unroll 1
+            for (int i = 0; i < np && !occl && !unsure; ++i) {
+                float lo, hi;
+                const int cls = plane_interval(S.pl[i], shx, shy, shz, so1, Lx, Ly, Lz, lo, hi, eso, eL);
+                if (cls == kCandMiss) continue;
+                if (cls == kCandHit && lo > tmax_hi) continue;
+                if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; first_p = i; }
+                else unsure = true;
+            }
+#pragma unroll 1
+            for (int i = 0; i < nt && !occl && !unsure; ++i) {
+                float lo, hi;
+                const int cls = tri_interval(S.tri[i], shx, shy, shz, slx, sly, slz, Lx, Ly, Lz, eso, eL, lo, hi);
+                if (cls == kCandMiss || lo > tmax_hi) continue;
+                if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; first_t = i; }
+                else unsure = true;
+            }
+            if (unsure) {
+                if (!free_guess) { RR_WHY(6); ok = false; break; }
+                occl = false;
+            }
+            out.c_shadow += 1u;
+            out.c_sph += first_s < ns ? (uint32_t)first_s + 1u : (uint32_t)ns;
+            if (first_s >= ns) {
+                out.c_pl += first_p < np ? (uint32_t)first_p + 1u : (uint32_t)np;
+                if (first_p >= np) out.c_tri += first_t < nt ? (uint32_t)first_t + 1u : (uint32_t)nt;
+            }
+            if (depth == 0 && j < 16) out.lmask |= 1u << (16 + j);
+            if (occl) continue;
+            if (depth == 0 && j < 16) out.lmask |= 1u << j;
+            const float att = inv * inv;  // 1 / d^2
+            const float wd = att * ndl;
+            dr = __fmaf_rn(Lt.E[0], wd, dr); dg = __fmaf_rn(Lt.E[1], wd, dg); db = __fmaf_rn(Lt.E[2], wd, db);
+            if (spec_on) {  // Blinn-Phong, RE/Scene.h:116-124: halfVector = normalize(lightToHit + viewDir), viewDir = -incoming
+                const float hx = Lx - Dx, hy = Ly - Dy, hz = Lz - Dz;
+                const float h2 = __fmaf_rn(hz, hz, __fmaf_rn(hy, hy, hx * hx));
+                if (h2 > 1e-24f) {  // (normalize() returns 0 below 1e-12: NdotH = 0, no term)
+                    const float ndh = __fmaf_rn(Nz, hz, __fmaf_rn(Ny, hy, Nx * hx)) * rsqrtf(h2);
+                    if (ndh > 0.0f) {
+                        const float sf = tm32::ex2(m_shin * tm32::lg2(fminf(ndh, 1.0f))) * att;
+                        sr = __fmaf_rn(Lt.E[0], sf, sr); sg = __fmaf_rn(Lt.E[1], sf, sg); sb = __fmaf_rn(Lt.E[2], sf, sb);
+                    }
+                }
+            }
+        }
+        if (!ok) { live = false; continue; }
+        // localLight = color * diffuse + specular * material.specular; finalLight += localLight (transparency = 0), RE/Scene.h:126-128,171-173
+        ar = __fmaf_rn(w, __fmaf_rn((float)M.color[0], dr, sr * m_spec), ar);
+        ag = __fmaf_rn(w, __fmaf_rn((float)M.color[1], dg, sg * m_spec), ag);
+        ab = __fmaf_rn(w, __fmaf_rn((float)M.color[2], db, sb * m_spec), ab);
+        // ---- reflection, RE/Scene.h:189-195: reflectiveness = material.specular > bias
+        if (!(M.specular > P.bias)) { live = false; continue; }
+        // reflectDir = incoming.reflect(normal).normalize(); reflectRay = {hitPoint + reflectDir * bias, reflectDir} — in FP64
+        const double k2 = 2.0 * (front ? nd64 : -nd64);  // 2 (d . N) with the flipped normal
+        double rx = fma(-k2, nx64, dx), ry = fma(-k2, ny64, dy), rz = fma(-k2, nz64, dz);
+        const double ri = rsqrt64_fast(rx * rx + ry * ry + rz * rz);
+        rx *= ri; ry *= ri; rz *= ri;
+        Ox = fma(rx, P.bias, Px); Oy = fma(ry, P.bias, Py); Oz = fma(rz, P.bias, Pz);
+        dx = rx; dy = ry; dz = rz;
+        Dx = (float)dx; Dy = (float)dy; Dz = (float)dz;
+        w *= m_spec;
+        if (w < kRrCutWeight) live = false;
+    }
+    out.r = ar; out.g = ag; out.b = ab;
+    return ok || !alive;
+}
+
+// ------------------------------------------------------------------------------ the kernel
+// Persistent CTAs, one 8 x 4 pixel tile per warp at a time (first tile by position, then a global counter), one pixel per lane.
+constexpr int kRrTileW = 8, kRrTileH = 4;
+
+__global__ void __launch_bounds__(kRrThreads, 2) render32r_kernel(const __grid_constant__ RenderParams P) {
+    __shared__ SceneRr S;
+    __shared__ unsigned long long s_stats[kRrThreads / 32][kStatCount];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    {   // scene constants: one thread per primitive / light
+        const DevScene& g = P.sc;
+        const int t = (int)threadIdx.x;
+        if (t == 0) { S.ns = g.ns; S.nt = g.nt; S.np = g.np; S.nl = g.nl; S.cam[0] = P.cam.pos[0]; S.cam[1] = P.cam.pos[1]; S.cam[2] = P.cam.pos[2]; }
+        for (int i = t; i < g.ns; i += kRrThreads) {
+            const double4 s = g.sph64[i];
+            Sph32r& o = S.sph[i];
+            split64(s.x, o.hx, o.lx); split64(s.y, o.hy, o.ly); split64(s.z, o.hz, o.lz);
+            o.r = (float)fabs(s.w); o.mat = g.sph_mat[i];
+        }
+        for (int i = t; i < g.nt; i += kRrThreads) {
+            const DevTri64 T = g.tri64[i];
+            Tri32& o = S.tri[i];
+            for (int c = 0; c < 3; ++c) {
+                split64(T.a0[c], o.ah[c], o.al[c]);
+                o.e1[c] = (float)T.e1[c]; o.e2[c] = (float)T.e2[c]; o.n[c] = (float)T.n[c];
+            }
+            o.E1 = (float)(sqrt64_fast(T.e1[0] * T.e1[0] + T.e1[1] * T.e1[1] + T.e1[2] * T.e1[2]) * 1.000001);
+            o.E2 = (float)(sqrt64_fast(T.e2[0] * T.e2[0] + T.e2[1] * T.e2[1] + T.e2[2] * T.e2[2]) * 1.000001);
+            o.mat = g.tri_info[i].x; o.report = (uint32_t)g.tri_info[i].y;
+        }
+        for (int i = t; i < g.np; i += kRrThreads) {
+            const DevPlane p = g.planes[i];
+            S.pl[i].nx = (float)p.n[0]; S.pl[i].ny = (float)p.n[1]; S.pl[i].nz = (float)p.n[2];
+            S.pl[i].d = (float)(p.n[0] * p.p0[0] + p.n[1] * p.p0[1] + p.n[2] * p.p0[2]);
+            S.pl[i].mat = p.mat;
+        }
+        for (int j = t; j < g.nl; j += kRrThreads) {
+            const DevLight l = g.lights[j];
+            for (int c = 0; c < 3; ++c) { split64(l.pos[c], S.li[j].hi[c], S.li[j].lo[c]); S.li[j].E[c] = (float)l.E[c]; }
+        }
+    }
+    if (lane < kStatCount) s_stats[warp][lane] = 0ull;
+    __syncthreads();
+    tm32::Consts K;
+    {
+        const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f, x = 11.2f;  // 1 / uncharted2_tonemap_partial(11.2)
+        K.white_scale = 1.0f / (((x * (A * x + C * B) + D * E) / (x * (A * x + B) + D * F)) - E / F);
+        K.inv_wsq = (float)(1.0 / (P.max_white * P.max_white));
+        K.jodie_a = (float)P.jodie_a;
+    }
+    const int W = P.cam.width, rows = P.n_rows;
+    const int sr = P.stripe_rows, sp = P.stripe_period;
+    const int tiles_x = (W + kRrTileW - 1) / kRrTileW, tiles_y = (rows + kRrTileH - 1) / kRrTileH;
+    const unsigned int n_tiles = (unsigned int)(tiles_x * tiles_y);
+    const int lx = lane & (kRrTileW - 1), ly = lane / kRrTileW;
+    const int aa = P.cam.aa;
+    const unsigned int n_static = gridDim.x * (kRrThreads / 32);
+    unsigned int tile = blockIdx.x * (kRrThreads / 32) + warp;
+    while (tile < n_tiles) {
+        unsigned int next = 0;
+        if (lane == 0) next = n_static + atomicAdd(P.tile_counter, 1u);
+        const int ty = (int)(tile / (unsigned)tiles_x), tx = (int)(tile - (unsigned)ty * (unsigned)tiles_x);
+        const int band_y = ty * kRrTileH + ly, px = tx * kRrTileW + lx;
+        const int py = P.row0 + (sr > 0 ? (band_y / sr) * sp + band_y % sr : band_y);
+        const bool inb = px < W && band_y < rows;
+        const int64_t pix = (int64_t)band_y * W + px;
+        // GeneratePixelAt, RE/Scene.h:283-304: mean of the samples
+        float cr = 0.0f, cg = 0.0f, cb = 0.0f;
+        uint32_t prim = kMiss, lmask = 0u, n_shadow = 0u, n_sec = 0u, n_sph = 0u, n_pl = 0u, n_tri = 0u;
+        bool ok = true;
+#pragma unroll 1
+        for (int s = 0; s < aa; ++s) {
+            PxR o;
+            ok = trace32r(P, S, px, py, inb && ok, s, o) && ok;
+            cr += o.r; cg += o.g; cb += o.b;
+            n_shadow += o.c_shadow; n_sec += o.c_secondary; n_sph += o.c_sph; n_pl += o.c_pl; n_tri += o.c_tri;
+            if (s == 0) { prim = o.prim; lmask = o.lmask; }
+#ifdef RTE_RR_DEBUG
+            if (s == 0 && !ok) lmask = 0x80000000u | o.why;
+#endif
+        }
+        if (aa > 1) { const float ia = 1.0f / (float)aa; cr *= ia; cg *= ia; cb *= ia; }
+#ifdef RTE_RR_DEBUG
+        ok = true;  // (debug build: no exact pass, light_mask carries the reason code of the first inconclusive decision)
+#endif
+        if (__any_sync(kFullMask, inb && !ok)) {
+            // an inconclusive decision in this tile: the exact kernel renders the whole tile (and counts its rays)
+            const uint32_t n_px = (uint32_t)__popc(__ballot_sync(kFullMask, inb));
+            if (lane == 0) { P.tile_flags[tile] = 1; s_stats[warp][kStatConfirms] += (unsigned long long)n_px * (unsigned)aa; }  // pixel samples left to the exact kernel
+        } else {
+            if (inb) {
+                if (P.out.hdr) __stcs(reinterpret_cast<float4*>(P.out.hdr) + pix, make_float4(cr, cg, cb, 0.f));
+                if (P.out.prim_id) P.out.prim_id[pix] = prim;
+                if (P.out.light_mask) P.out.light_mask[pix] = lmask;
+                if (P.out.rgb8) {
+                    const tm32::Shared sh = tm32::prepare<0u>(tm32::mk3(cr, cg, cb), 1u << P.tonemap_op);
+                    tm32::f3 c;
+                    switch (P.tonemap_op) {
+                        case RTE_TM_SIMPLE: c = tm32::apply_op<RTE_TM_SIMPLE>(sh, K); break;
+                        case RTE_TM_REINHARD_SIMPLE: c = tm32::apply_op<RTE_TM_REINHARD_SIMPLE>(sh, K); break;
+                        case RTE_TM_REINHARD_EXTENDED: c = tm32::apply_op<RTE_TM_REINHARD_EXTENDED>(sh, K); break;
+                        case RTE_TM_REINHARD_EXTENDED_LUMINANCE: c = tm32::apply_op<RTE_TM_REINHARD_EXTENDED_LUMINANCE>(sh, K); break;
+                        case RTE_TM_REINHARD_JODIE: c = tm32::apply_op<RTE_TM_REINHARD_JODIE>(sh, K); break;
+                        case RTE_TM_UNCHARTED2: c = tm32::apply_op<RTE_TM_UNCHARTED2>(sh, K); break;
+                        default: c = tm32::apply_op<RTE_TM_ACES>(sh, K); break;
+                    }
+                    uint8_t* d = P.out.rgb8 + 3 * pix;
+                    d[0] = (uint8_t)(tm32::qbyte(c.x) & 255u); d[1] = (uint8_t)(tm32::qbyte(c.y) & 255u); d[2] = (uint8_t)(tm32::qbyte(c.z) & 255u);
+                }
+            }
+            const uint32_t v[kStatCount] = {inb ? (uint32_t)aa : 0u, n_shadow, n_sec, n_sph, n_pl, n_tri, 0u, 0u, 0u};
+            uint32_t mine = 0;
+#pragma unroll
+            for (int k = 0; k < kStatCount; ++k) {
+                const uint32_t t = __reduce_add_sync(kFullMask, inb ? v[k] : 0u);
+                if (lane == k) mine = t;
+            }
+            if (lane < kStatCount) s_stats[warp][lane] += mine;
+        }
+        tile = __shfl_sync(kFullMask, next, 0);
+    }
+    __syncwarp();
+    if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
+}
+
+// Can this render call take the reflective FP32 path?  Opaque materials only (a transparent one makes TraceRay a tree), few
+// primitives (every ray tests all of them), outputs hdr / rgb8 / prim_id / light_mask, no validation switches.
+bool fp32r_path_eligible(const RenderParams& p) {
+    const rte_frame& f = p.out;
+    return p.sc.reflective && !p.sc.transparent && p.sc.ns <= kRrPrims && p.sc.nt <= kRrPrims && p.sc.ns + p.sc.nt <= kRrPrims && p.sc.ns + p.sc.nt + p.sc.np > 0 &&
+           p.sc.np <= kRrPlanes && p.sc.nl <= kRrLights && !p.exact_shadows && !p.no_filter && !p.force_general && !p.no_cull && p.pass_mode == 0 &&
+           !p.exact_fp64 && !p.exact_grid && !f.hdr64 && !f.depth && !f.depth64 && !f.depth_norm && !f.normal && !f.albedo && p.bias >= 1e-6 && p.bias <= 1e-1;
+}
+
+cudaError_t launch_render32r(const RenderParams& p, int sm_count, cudaStream_t stream) {
+    const long long n_tiles = (long long)((p.cam.width + kRrTileW - 1) / kRrTileW) * ((p.n_rows + kRrTileH - 1) / kRrTileH);
+    long long blocks = (long long)sm_count * 2;
+    const long long needed = (n_tiles + kRrThreads / 32 - 1) / (kRrThreads / 32);
+    if (blocks > needed) blocks = needed > 0 ? needed : 1;
+    render32r_kernel<<<(unsigned)blocks, kRrThreads, 0, stream>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace rte
