@@ -43,6 +43,8 @@ struct SceneRr {
     Tri32 tri[kRrPrims];
     Plane32 pl[kRrPlanes];
     Light32r li[kRrLights];
+    float4 tb[kRrPrims];  // bounding sphere of every triangle {centroid, farthest vertex (inflated)}: far_miss() in front of tri_interval()
+    float4 tb_all;        // ... and of all of them: most rays of a room skip the mesh with one test
     double cam[3];
     int ns, nt, np, nl;
 };
@@ -127,12 +129,15 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
             if (cls == kCandHit) near_hit(nr, RTE_HIT_PLANE, i, lo, hi);
             else if (cls == kCandUnsure) near_unsure(nr, 0.0f);
         }
+        if (nt > 0 && !far_miss(S.tb_all, ohx, ohy, ohz, o1, Dx, Dy, Dz)) {
 #pragma unroll 1
-        for (int i = 0; i < nt; ++i) {
-            float lo, hi;
-            const int cls = tri_interval(S.tri[i], ohx, ohy, ohz, olx, oly, olz, Dx, Dy, Dz, eo, ed, lo, hi);
-            if (cls == kCandHit) near_hit(nr, RTE_HIT_TRIANGLE, i, lo, hi);
-            else if (cls == kCandUnsure) near_unsure(nr, lo);
+            for (int i = 0; i < nt; ++i) {
+                if (far_miss(S.tb[i], ohx, ohy, ohz, o1, Dx, Dy, Dz)) continue;  // the line misses the triangle's bounding sphere
+                float lo, hi;
+                const int cls = tri_interval(S.tri[i], ohx, ohy, ohz, olx, oly, olz, Dx, Dy, Dz, eo, ed, lo, hi);
+                if (cls == kCandHit) near_hit(nr, RTE_HIT_TRIANGLE, i, lo, hi);
+                else if (cls == kCandUnsure) near_unsure(nr, lo);
+            }
         }
         out.c_sph += (uint32_t)ns; out.c_pl += (uint32_t)np; out.c_tri += (uint32_t)nt;
         if (depth > 0) out.c_secondary += 1u;
@@ -245,8 +250,10 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
                 if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; first_p = i; }
                 else unsure = true;
             }
+            const bool mesh = nt > 0 && !far_miss(S.tb_all, shx, shy, shz, so1, Lx, Ly, Lz);
 #pragma unroll 1
-            for (int i = 0; i < nt && !occl && !unsure; ++i) {
+            for (int i = 0; mesh && i < nt && !occl && !unsure; ++i) {
+                if (far_miss(S.tb[i], shx, shy, shz, so1, Lx, Ly, Lz)) continue;
                 float lo, hi;
                 const int cls = tri_interval(S.tri[i], shx, shy, shz, slx, sly, slz, Lx, Ly, Lz, eso, eL, lo, hi);
                 if (cls == kCandMiss || lo > tmax_hi) continue;
@@ -331,6 +338,15 @@ __global__ void __launch_bounds__(kRrThreads, 2) render32r_kernel(const __grid_c
             o.E1 = (float)(sqrt64_fast(T.e1[0] * T.e1[0] + T.e1[1] * T.e1[1] + T.e1[2] * T.e1[2]) * 1.000001);
             o.E2 = (float)(sqrt64_fast(T.e2[0] * T.e2[0] + T.e2[1] * T.e2[1] + T.e2[2] * T.e2[2]) * 1.000001);
             o.mat = g.tri_info[i].x; o.report = (uint32_t)g.tri_info[i].y;
+            const double cx = T.a0[0] + (T.e1[0] + T.e2[0]) * (1.0 / 3.0), cy = T.a0[1] + (T.e1[1] + T.e2[1]) * (1.0 / 3.0), cz = T.a0[2] + (T.e1[2] + T.e2[2]) * (1.0 / 3.0);
+            double r2 = 0.0;
+            for (int v = 0; v < 3; ++v) {
+                const double vx = T.a0[0] + (v == 1 ? T.e1[0] : v == 2 ? T.e2[0] : 0.0) - cx, vy = T.a0[1] + (v == 1 ? T.e1[1] : v == 2 ? T.e2[1] : 0.0) - cy,
+                             vz = T.a0[2] + (v == 1 ? T.e1[2] : v == 2 ? T.e2[2] : 0.0) - cz;
+                r2 = fmax(r2, vx * vx + vy * vy + vz * vz);
+            }
+            // (FP32 centre: its rounding, <= 1e-7 of its size, goes into the radius)
+            S.tb[i] = make_float4((float)cx, (float)cy, (float)cz, (float)(sqrt64_fast(r2) * 1.00001 + 1e-6 * (fabs(cx) + fabs(cy) + fabs(cz)) + 1e-30));
         }
         for (int i = t; i < g.np; i += kRrThreads) {
             const DevPlane p = g.planes[i];
@@ -344,6 +360,18 @@ __global__ void __launch_bounds__(kRrThreads, 2) render32r_kernel(const __grid_c
         }
     }
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;
+    __syncthreads();
+    if (threadIdx.x == 0) {  // one sphere around all the triangles' spheres
+        float cx = 0.f, cy = 0.f, cz = 0.f, r = 0.f;
+        const int nt = P.sc.nt;
+        for (int i = 0; i < nt; ++i) { cx += S.tb[i].x; cy += S.tb[i].y; cz += S.tb[i].z; }
+        if (nt > 0) { const float inv = 1.0f / (float)nt; cx *= inv; cy *= inv; cz *= inv; }
+        for (int i = 0; i < nt; ++i) {
+            const float dx = S.tb[i].x - cx, dy = S.tb[i].y - cy, dz = S.tb[i].z - cz;
+            r = fmaxf(r, sqrtf(dx * dx + dy * dy + dz * dz) * 1.00001f + S.tb[i].w);
+        }
+        S.tb_all = make_float4(cx, cy, cz, r * 1.00001f);
+    }
     __syncthreads();
     tm32::Consts K;
     {
