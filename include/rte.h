@@ -178,8 +178,12 @@ typedef struct rte_render_opts {
  *   EXACT_FP64     never take the FP32 production path.  Without it, a call that asks for hdr / rgb8 / prim_id / light_mask
  *                  only, on a diffuse sphere / plane scene, is shaded in FP32 (hit index and shadow visibility bit-exact — every
  *                  FP32 decision is certain within its error bound or the pixel is re-rendered in FP64 —, HDR to ~1e-6 relative,
- *                  RGB8 within +-1 LSB of the reference: the bars BASELINE.json states).  Every FP64 output (hdr64, depth64), the
- *                  other AOVs and every flag above select the exact FP64 path, whose results are the reference's own bits. */
+ *                  RGB8 within +-1 LSB of the reference: the bars BASELINE.json states).  The same holds for opaque scenes with
+ *                  specular (reflecting) materials and at most 64 spheres + triangles — main()'s scene —: their chains of
+ *                  reflections end once the path weight (the product of the materials' specular factors) is below 1e-7, so
+ *                  rte_stats counts fewer secondary / shadow rays than the reference traces.  Every FP64 output (hdr64,
+ *                  depth64), the other AOVs and every flag above select the exact FP64 path, whose results are the
+ *                  reference's own bits. */
 enum { RTE_FLAG_EXACT_SHADOWS = 1, RTE_FLAG_NO_FILTER = 2, RTE_FLAG_GENERAL_KERNEL = 4, RTE_FLAG_NO_CULL = 8, RTE_FLAG_SINGLE_PASS = 16, RTE_FLAG_TWO_PASS = 32,
        RTE_FLAG_EXACT_FP64 = 64, RTE_FLAG_EXACT_GRID = 128 };
 
