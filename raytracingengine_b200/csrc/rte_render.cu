@@ -397,6 +397,8 @@ __global__ void __launch_bounds__(kReflect ? kReflThreads : kRenderMaxThreads, k
     __shared__ __align__(8) uint64_t s_bar;
     __shared__ unsigned long long s_stats[kRenderMaxThreads / 32][kStatCount];
 
+    // second pass of rte_render32r.cu: that kernel left the number of pixel samples in flagged tiles in the statistics — none: nothing to do
+    if (P.tile_mask && P.stats[kStatConfirms] == 0ull) return;
     if (threadIdx.x == 0) s_sc = P.sc;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (lane < kStatCount) s_stats[warp][lane] = 0ull;

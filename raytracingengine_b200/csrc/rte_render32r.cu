@@ -9,15 +9,17 @@
 //  * Values are FP32 (hit points in a handful of cheap FP64 operations), decisions come from FP32 INTERVALS (rte_interval.cuh)
 //    over ALL primitives — a reflected ray has no common origin with its neighbours, so the per-origin direction grids of
 //    rte_render32.cu do not apply; the path takes scenes of at most kRrPrims spheres + triangles, everything in shared memory.
-//  * The CHAIN of rays — origin, direction, hit point, normal, reflected direction — is carried in FP64 with cheap operations
-//    (MUFU seeds + Newton steps instead of DDIV / DSQRT, ~1e-15 relative), ~40 FP64 instructions per bounce: a reflected ray in
-//    FP32 would not be the reference's ray any more (its deviation triples with every bounce, and after two bounces it is of the
-//    order of the shadow bias: measured, every pixel was flagged).  The interval tests see that ray rounded once, like a
-//    primary ray.
-//  * A decision that stays inconclusive flags the pixel — while the path weight (the product of the reflectivenesses so far)
-//    exceeds kRrFreeWeight.  Below it a wrong branch moves the pixel by less than 1e-5 of a radiance difference, far inside
-//    the 1 / 255 of a byte, and the best guess is taken.  A tile with a flagged pixel is rendered again, entirely, by the exact
-//    kernel (rte_render.cu: render_kernel<1, true> over the flagged tiles): those tiles carry the reference's own bits.
+//  * The CHAIN of rays — origin, direction, hit distance of the chosen primitive, hit point, normal, reflected direction, and
+//    per light the vector, distance and N.L of the shadow-ray guards — is computed with the REFERENCE'S OWN FP64 operations
+//    (rte_device.cuh: the functions of the exact kernels), ~900 instructions per node against ~3500 for the interval tests: the
+//    ray at depth k is the reference's ray bit for bit.  (A reflected ray in FP32 is not the reference's ray any more: its
+//    deviation triples with every bounce and after two bounces it is of the order of the shadow bias — measured, every pixel of
+//    C1 was inconclusive.)  The interval tests see that ray rounded once, like a primary ray.
+//  * Because the chain is the reference's, an inconclusive decision can be settled on the spot by the reference's own test:
+//    overlapping nearest-hit intervals by its IntersectClosest over all primitives (closest_exact_brute), an unsure shadow ray
+//    by its literal transmittance march (march_exact_brute).  C1 needs that on whole pixel rows: its camera sits on the room's
+//    axes and looks exactly along the lines where two planes meet, at every depth.  (The tile-flag mechanism — a tile with an
+//    undecidable pixel is rendered again by the exact kernel, rte_render.cu — remains as the safety net; no scene has used it.)
 #include <algorithm>
 
 #include "rte_grid.cuh"
@@ -29,7 +31,6 @@ namespace rte {
 
 constexpr int kRrThreads = 256;
 constexpr int kRrPrims = 64, kRrPlanes = 8, kRrLights = 16;
-constexpr float kRrFreeWeight = 1e-5f;
 // A chain ends once its weight falls below this: what the reference still adds below it (down to maxRecursion = 10) is less than
 // 1e-7 of a radiance per node, under the resolution of the FP32 pixel.  (C1: the planes reflect 1 %: four or five nodes instead of
 // ten.)  The ray counters therefore count the rays traced, fewer than the reference's for such scenes.
@@ -63,52 +64,78 @@ struct PxR {
 
 __device__ __forceinline__ void split64(double v, float& hi, float& lo) { hi = (float)v; lo = (float)(v - (double)hi); }
 
-// One sample of one pixel per lane.  Returns false when a decision that matters was inconclusive (the tile is then rendered
-// again by the exact kernel and nothing of `out` is used).
+// ------------------------------------------------------------------------------ the reference's own tests, for the rare cases
+// Scene::IntersectClosest, RE/Scene.h:218-257, over every primitive with the exact FP64 tests: canonical order (spheres, planes,
+// triangles — standalone ones, then every model's), strict '<'.  Runs when the FP32 intervals of two candidates overlap (a room
+// corner seen exactly along its edge: C1's camera sits on the room's axes, whole pixel rows look along such lines).
+struct HitX { int kind; int idx; double t; };
+static __device__ __noinline__ HitX closest_exact_brute(const DevScene& sc, d3 o, d3 d) {
+    HitX best;
+    best.kind = RTE_HIT_NONE; best.idx = 0; best.t = 0.0;
+    for (int i = 0; i < sc.ns; ++i) {
+        double t;
+        if (sphere_exact(sc.sph64[i], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t)) { best.kind = RTE_HIT_SPHERE; best.idx = i; best.t = t; }
+    }
+    for (int i = 0; i < sc.np; ++i) {
+        double t;
+        if (plane_exact(sc.planes[i], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t)) { best.kind = RTE_HIT_PLANE; best.idx = i; best.t = t; }
+    }
+    for (int i = 0; i < sc.nt; ++i) {
+        double t;
+        if (tri_exact(sc.tri64[i], o, d, t) && (best.kind == RTE_HIT_NONE || t < best.t)) { best.kind = RTE_HIT_TRIANGLE; best.idx = i; best.t = t; }
+    }
+    return best;
+}
+// Scene::computeTransmittance, RE/Scene.h:35-77, literally.
+static __device__ __noinline__ double march_exact_brute(const DevScene& sc, d3 o, d3 d, double maxDist, double bias) {
+    double T = 1.0, traveled = 0.0;
+    int safety = 64;
+    while (safety-- > 0 && T > 1e-4 && traveled < maxDist) {
+        const HitX h = closest_exact_brute(sc, o, d);
+        if (h.kind == RTE_HIT_NONE) break;
+        const double t = h.t;
+        if (t <= 0.0) { o = o + d * bias; traveled += bias; continue; }
+        if (t <= bias) { o = (o + d * t) + d * bias; traveled += t + bias; continue; }
+        if (traveled + t >= maxDist) break;
+        int m = h.kind == RTE_HIT_SPHERE ? sc.sph_mat[h.idx] : h.kind == RTE_HIT_PLANE ? sc.planes[h.idx].mat : sc.tri_info[h.idx].x;
+        m = (m >= 0 && m < sc.nm) ? m : sc.nm;
+        T *= std_clamp(sc.materials[m].transparency, 0.0, 1.0);
+        o = (o + d * t) + d * bias;
+        traveled += t + bias;
+    }
+    return std_clamp(T, 0.0, 1.0);
+}
+
+// One sample of one pixel per lane.  Returns false when something could not be decided (never seen; the tile would be rendered
+// again by the exact kernel and nothing of `out` used).
 __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S, int px, int py, bool alive, int sample, PxR& out) {
     const DevScene& sc = P.sc;
     const int ns = S.ns, nt = S.nt, np = S.np, nl = S.nl;
+    const double bias64 = P.bias;
     const float bias = (float)P.bias;
     const int max_depth = P.max_depth;
     out.r = out.g = out.b = 0.0f; out.why = 0u;
     int depth_dbg = 0; (void)depth_dbg;
     out.prim = kMiss; out.lmask = 0u; out.c_shadow = out.c_secondary = out.c_sph = out.c_pl = out.c_tri = 0u;
     bool ok = true;
-    // ---- Camera::getRay, RE/Math.h:99-121 (the reference's FP64 operations up to the normalisation)
-    double Ox = S.cam[0], Oy = S.cam[1], Oz = S.cam[2];
-    double dx, dy, dz;  // the ray's direction: FP64 like its origin (see the header: the chain of rays is the reference's to ~1e-14)
-    {
-        double sx = (double)px - P.cam.half_w, sy = P.cam.half_h - (double)py;
-        if (sample > 0) {
-            const int64_t pixel = (int64_t)py * P.cam.width + px;
-            sx += jitter01(P.cam.jitter_seed, pixel, sample, 0);
-            sy += jitter01(P.cam.jitter_seed, pixel, sample, 1);
-        }
-        const double vx = sx - Ox, vy = sy - Oy, vz = (Oz + P.cam.focal) - Oz;
-        const double len2 = vx * vx + vy * vy + vz * vz;
-        if (!(len2 > 1e-20) || !(len2 < 1e30)) { RR_WHY(1); ok = false; }
-        const double inv = rsqrt64_fast(len2);
-        dx = vx * inv; dy = vy * inv; dz = vz * inv;
-    }
-    // what the interval tests see of the ray: the FP64 origin as hi + lo floats (exact), the direction rounded to FP32 — the
-    // same deviation (one rounding, part of the built-in margins) at every depth, because the chain itself is carried in FP64
-    const float eo = 0.0f, ed = 4.0f * kEps32;
-    float Dx = (float)dx, Dy = (float)dy, Dz = (float)dz;
-    float w = 1.0f;                       // weight of the node's light in the pixel
+    // ---- Camera::getRay, RE/Math.h:99-121, with the reference's own operations: the chain of rays below is the reference's, bit for bit
+    d3 o = ld3(P.cam.pos), d = camera_dir(P.cam, px, py, sample);
+    const float eo = 0.0f, ed = 4.0f * kEps32;  // what the interval tests see of a ray: its origin exactly (hi + lo), its direction rounded once
+    float w = 1.0f;                             // weight of the node's light in the pixel
     float ar = 0.0f, ag = 0.0f, ab = 0.0f;
-    bool live = alive && ok;
-    auto sky = [&]() {  // Scene::backgroundColor, RE/Scene.h:30-33
-        const float t = 0.5f * (Dy + 1.0f);
-        ar = __fmaf_rn(w, __fmaf_rn(0.5f, t, 1.0f - t), ar); ag = __fmaf_rn(w, __fmaf_rn(0.7f, t, 1.0f - t), ag); ab = __fmaf_rn(w, 1.0f, ab);
-    };
+    bool live = alive;
 #pragma unroll 1
     for (int depth = 0; __any_sync(kFullMask, live); ++depth) {
         depth_dbg = depth;
+        const float Dx = (float)d.x, Dy = (float)d.y, Dz = (float)d.z;
+        auto sky = [&]() {  // Scene::backgroundColor, RE/Scene.h:30-33
+            const float t = 0.5f * (Dy + 1.0f);
+            ar = __fmaf_rn(w, __fmaf_rn(0.5f, t, 1.0f - t), ar); ag = __fmaf_rn(w, __fmaf_rn(0.7f, t, 1.0f - t), ag); ab = __fmaf_rn(w, 1.0f, ab);
+        };
         if (live && depth >= max_depth) { sky(); live = false; }  // TraceRay(recursionAmount >= maxRecursion), RE/Scene.h:132-134
         if (!live) continue;
-        const bool free_guess = w <= kRrFreeWeight;  // decisions of this node cannot move a byte: take the best guess
         float ohx, ohy, ohz, olx, oly, olz;
-        split64(Ox, ohx, olx); split64(Oy, ohy, oly); split64(Oz, ohz, olz);
+        split64(o.x, ohx, olx); split64(o.y, ohy, oly); split64(o.z, ohz, olz);
         const float o1 = fabsf(ohx) + fabsf(ohy) + fabsf(ohz);
         // ---- Scene::IntersectClosest, RE/Scene.h:218-257, over every primitive, from intervals
         Near32 nr;
@@ -141,90 +168,66 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
         }
         out.c_sph += (uint32_t)ns; out.c_pl += (uint32_t)np; out.c_tri += (uint32_t)nt;
         if (depth > 0) out.c_secondary += 1u;
-        if (near_ambiguous(nr) && !free_guess) { RR_WHY(2); ok = false; live = false; continue; }
-        if (nr.kind == RTE_HIT_NONE) { sky(); live = false; continue; }
-        // ---- the hit in cheap FP64 (no DDIV / DSQRT: ~1e-15 relative), normal, material
-        double t, nx64, ny64, nz64;
-        float Nx, Ny, Nz;
-        const float eN = 2.0f * kEps32;  // the FP32 copy of the normal
+        // ---- the hit: which primitive from the intervals (or, when they overlap, from the reference's own scan), its distance
+        // from the reference's own test of that primitive
+        HitX hx;
+        if (near_ambiguous(nr)) {
+            hx = closest_exact_brute(sc, o, d);
+        } else {
+            hx.kind = nr.kind; hx.idx = nr.idx; hx.t = 0.0;
+            bool hit = true;
+            if (nr.kind == RTE_HIT_SPHERE) hit = sphere_exact(sc.sph64[nr.idx], o, d, hx.t);
+            else if (nr.kind == RTE_HIT_PLANE) hit = plane_exact(sc.planes[nr.idx], o, d, hx.t);
+            else if (nr.kind == RTE_HIT_TRIANGLE) hit = tri_exact(sc.tri64[nr.idx], o, d, hx.t);
+            if (!hit) { RR_WHY(2); ok = false; live = false; continue; }  // (a certain FP32 hit the exact test denies: a bound would be wrong)
+        }
+        if (hx.kind == RTE_HIT_NONE) { sky(); live = false; continue; }
+        // ---- the hit record and TraceRay's frame with the reference's operations (GetHitInfoAt, RE/Shape.h:104-121,165-180,229-243;
+        // RE/Scene.h:144-148), as in trace_pixels (rte_render.cu)
+        const d3 Pn = o + d * hx.t;
+        d3 ngeo;
         int mat, self = -1;
         uint32_t report;
-        if (nr.kind == RTE_HIT_SPHERE) {
-            const double4 s = sc.sph64[nr.idx];
-            const double ocx = Ox - s.x, ocy = Oy - s.y, ocz = Oz - s.z;
-            const double bq = ocx * dx + ocy * dy + ocz * dz;
-            const double cq = fma(ocx, ocx, fma(ocy, ocy, ocz * ocz)) - s.w * s.w;
-            const double disc = fma(bq, bq, -cq);
-            const double sq = disc > 0.0 ? disc * rsqrt64_fast(disc) : 0.0;
-            const double mid = 0.5 * ((double)nr.lo + (double)nr.hi), t0 = -bq - sq, t1 = -bq + sq;
-            t = fabs(t0 - mid) <= fabs(t1 - mid) ? t0 : t1;  // the root the interval belongs to (near root, or the far one from inside)
-            const double ir = rcp64_fast(fabs(s.w));
-            nx64 = (fma(dx, t, Ox) - s.x) * ir; ny64 = (fma(dy, t, Oy) - s.y) * ir; nz64 = (fma(dz, t, Oz) - s.z) * ir;
-            mat = S.sph[nr.idx].mat; report = (uint32_t)nr.idx;
-        } else if (nr.kind == RTE_HIT_PLANE) {
-            const DevPlane& pl = sc.planes[nr.idx];
-            const double num = (pl.p0[0] - Ox) * pl.n[0] + (pl.p0[1] - Oy) * pl.n[1] + (pl.p0[2] - Oz) * pl.n[2];
-            const double den = pl.n[0] * dx + pl.n[1] * dy + pl.n[2] * dz;
-            t = num * rcp64_fast(den);
-            nx64 = pl.n[0]; ny64 = pl.n[1]; nz64 = pl.n[2];
-            mat = S.pl[nr.idx].mat; report = (uint32_t)nr.idx;
+        if (hx.kind == RTE_HIT_SPHERE) {
+            const double4 s = sc.sph64[hx.idx];
+            ngeo = normalize(Pn - mk(s.x, s.y, s.z));
+            mat = S.sph[hx.idx].mat; report = (uint32_t)hx.idx;
+        } else if (hx.kind == RTE_HIT_PLANE) {
+            ngeo = ld3(sc.planes[hx.idx].n);
+            mat = S.pl[hx.idx].mat; report = (uint32_t)hx.idx;
         } else {
-            const DevTri64& T = sc.tri64[nr.idx];
-            const double hx = dy * T.e2[2] - dz * T.e2[1], hy = dz * T.e2[0] - dx * T.e2[2], hz = dx * T.e2[1] - dy * T.e2[0];
-            const double a = T.e1[0] * hx + T.e1[1] * hy + T.e1[2] * hz;
-            const double sx = Ox - T.a0[0], sy = Oy - T.a0[1], sz = Oz - T.a0[2];
-            const double qx = sy * T.e1[2] - sz * T.e1[1], qy = sz * T.e1[0] - sx * T.e1[2], qz = sx * T.e1[1] - sy * T.e1[0];
-            t = (T.e2[0] * qx + T.e2[1] * qy + T.e2[2] * qz) * rcp64_fast(a);
-            nx64 = T.n[0]; ny64 = T.n[1]; nz64 = T.n[2];
-            mat = S.tri[nr.idx].mat; report = S.tri[nr.idx].report;
+            ngeo = ld3(sc.tri64[hx.idx].n);
+            mat = S.tri[hx.idx].mat; report = S.tri[hx.idx].report;
         }
-        const double Px = fma(dx, t, Ox), Py = fma(dy, t, Oy), Pz = fma(dz, t, Oz);
-        float Phx, Phy, Phz, Plx, Ply, Plz;
-        split64(Px, Phx, Plx); split64(Py, Phy, Ply); split64(Pz, Phz, Plz);
-        // the reference's hit point agrees with this one to ~1e-14 of the scene's size (its own FP64 roundings); eP leaves four digits
-        const float eP = 1e-10f * (1.0f + fabsf(Phx) + fabsf(Phy) + fabsf(Phz));
-        // frontFace = normal . incoming < 0, RE/Scene.h:146-148
-        const double nd64 = nx64 * dx + ny64 * dy + nz64 * dz;
-        if (fabs(nd64) <= 1e-11 && !free_guess) { RR_WHY(3); ok = false; live = false; continue; }
-        const bool front = nd64 < 0.0;
-        if (!front) { nx64 = -nx64; ny64 = -ny64; nz64 = -nz64; }
-        Nx = (float)nx64; Ny = (float)ny64; Nz = (float)nz64;
-        if (nr.kind == RTE_HIT_SPHERE && front && bias >= 1e-5f) self = nr.idx;
-        if (depth == 0) out.prim = ((uint32_t)nr.kind << 30) | report;
+        const d3 incoming = normalize(d);
+        const bool front = dot(ngeo, incoming) < 0.0;
+        const d3 N = front ? ngeo : -ngeo;
+        const d3 normal = normalize(N);  // directLightning re-normalises, RE/Scene.h:81
+        const float Nx = (float)normal.x, Ny = (float)normal.y, Nz = (float)normal.z;
+        if (hx.kind == RTE_HIT_SPHERE && front && bias >= 1e-5f) self = hx.idx;
+        if (depth == 0) out.prim = ((uint32_t)hx.kind << 30) | report;
         mat = (mat >= 0 && mat < sc.nm) ? mat : sc.nm;
         const rte_material& M = sc.materials[mat];
         const float m_spec = (float)M.specular, m_shin = (float)M.shininess;
         const bool spec_on = M.transparency <= 0.0 && M.specular > 0.0;  // RE/Scene.h:116
-        // ---- Scene::directLightning, RE/Scene.h:79-129; shadow origin so = P + N * bias (RE/Scene.h:104)
-        const double Sx = fma(nx64, P.bias, Px), Sy = fma(ny64, P.bias, Py), Sz = fma(nz64, P.bias, Pz);
+        // ---- Scene::directLightning, RE/Scene.h:79-129: the guards and the shadow ray in the reference's FP64, the light in FP32
+        const d3 so = Pn + normal * bias64;  // RE/Scene.h:104
         float shx, shy, shz, slx, sly, slz;
-        split64(Sx, shx, slx); split64(Sy, shy, sly); split64(Sz, shz, slz);
+        split64(so.x, shx, slx); split64(so.y, shy, sly); split64(so.z, shz, slz);
         const float so1 = fabsf(shx) + fabsf(shy) + fabsf(shz);
-        const float eso = eP;  // (so = P + N * bias with the FP64 normal)
         float dr = 0.0f, dg = 0.0f, db = 0.0f, sr = 0.0f, sg = 0.0f, sb = 0.0f;
 #pragma unroll 1
         for (int j = 0; j < nl; ++j) {
-            const Light32r& Lt = S.li[j];
-            const float vx = (Lt.hi[0] - Phx) + (Lt.lo[0] - Plx), vy = (Lt.hi[1] - Phy) + (Lt.lo[1] - Ply), vz = (Lt.hi[2] - Phz) + (Lt.lo[2] - Plz);
-            const float d2 = __fmaf_rn(vz, vz, __fmaf_rn(vy, vy, vx * vx));
-            if (!(d2 > 0.0f)) { if (!free_guess && d2 <= eP * eP) { RR_WHY(4); ok = false; } continue; }
-            float inv = rsqrtf(d2);
-            inv = inv * __fmaf_rn(-0.5f * d2 * inv, inv, 1.5f);
-            const float dist = d2 * inv;
-            const float Lx = vx * inv, Ly = vy * inv, Lz = vz * inv;
-            const float eL = 2.0f * eP * inv + 8.0f * kEps32;  // |L - L_ref|
-            const float ndl = __fmaf_rn(Nz, Lz, __fmaf_rn(Ny, Ly, Nx * Lx));
-            // guards of RE/Scene.h:89-101: ndl > 0, dist > bias — certain, or the pixel is flagged
-            bool cast;
-            if (fabsf(ndl) < eN + eL + 32.0f * kEps32 || fabsf(dist - bias) < eP + 1e-5f * bias + 1e-30f) {
-                if (!free_guess) { RR_WHY(5); ok = false; break; }
-                cast = false;
-            } else {
-                cast = ndl > 0.0f && dist > bias;
-            }
-            if (!cast) continue;
-            const float maxDist = dist - bias;
-            const float dt = 24.0f * kEps32 * (dist + so1) + 1e-7f + eP + eso;  // slack of the range ends (maxDist, bias) against the candidate bounds
+            const d3 vecToLight = ld3(sc.lights[j].pos) - Pn;
+            const d4 ul = unit_len(vecToLight);  // {lightToHit, distanceToLight}
+            const double dist64 = ul.w;
+            if (!(dist64 > 0.0)) continue;       // RE/Scene.h:89
+            const d3 L64 = mk(ul.x, ul.y, ul.z);
+            const double ndl64 = std_max(0.0, dot(normal, L64));
+            if (!(ndl64 > 0.0) || !(dist64 > bias64)) continue;  // RE/Scene.h:92-101
+            const float Lx = (float)L64.x, Ly = (float)L64.y, Lz = (float)L64.z, dist = (float)dist64, ndl = (float)ndl64;
+            const float maxDist = (float)(dist64 - bias64);
+            const float dt = 24.0f * kEps32 * (dist + so1) + 1e-7f;  // slack of the range ends (maxDist, bias) against the candidate bounds
             const float tmax_lo = maxDist - dt, tmax_hi = maxDist + dt, bias_hi = bias + dt;
             // computeTransmittance (RE/Scene.h:35-77) for opaque scenes: some primitive reports t in (bias, maxDist) — unless one
             // reports t <= bias (the march steps past it): certain occluder, certain miss, or unsure.  Canonical order.
@@ -234,7 +237,7 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
             for (int i = 0; i < ns && !occl && !unsure; ++i) {
                 if (i == self) continue;  // so lies outside the sphere the point is on, the ray leaves it: both roots < 0
                 const Sph32r& s = S.sph[i];
-                const Cand32 c = classify_sphere(make_float4(s.hx, s.hy, s.hz, s.r), make_float4(s.lx, s.ly, s.lz, 0.0f), shx, shy, shz, slx, sly, slz, Lx, Ly, Lz, eso, eL);
+                const Cand32 c = classify_sphere(make_float4(s.hx, s.hy, s.hz, s.r), make_float4(s.lx, s.ly, s.lz, 0.0f), shx, shy, shz, slx, sly, slz, Lx, Ly, Lz, eo, ed);
                 float lo, hi;
                 const int cls = reported_t(c, lo, hi);
                 if (cls == kCandMiss || lo > tmax_hi) continue;
@@ -244,7 +247,7 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
 #pragma unroll 1
             for (int i = 0; i < np && !occl && !unsure; ++i) {
                 float lo, hi;
-                const int cls = plane_interval(S.pl[i], shx, shy, shz, so1, Lx, Ly, Lz, lo, hi, eso, eL);
+                const int cls = plane_interval(S.pl[i], shx, shy, shz, so1, Lx, Ly, Lz, lo, hi, eo, ed);
                 if (cls == kCandMiss) continue;
                 if (cls == kCandHit && lo > tmax_hi) continue;
                 if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; first_p = i; }
@@ -255,14 +258,15 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
             for (int i = 0; mesh && i < nt && !occl && !unsure; ++i) {
                 if (far_miss(S.tb[i], shx, shy, shz, so1, Lx, Ly, Lz)) continue;
                 float lo, hi;
-                const int cls = tri_interval(S.tri[i], shx, shy, shz, slx, sly, slz, Lx, Ly, Lz, eso, eL, lo, hi);
+                const int cls = tri_interval(S.tri[i], shx, shy, shz, slx, sly, slz, Lx, Ly, Lz, eo, ed, lo, hi);
                 if (cls == kCandMiss || lo > tmax_hi) continue;
                 if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; first_t = i; }
                 else unsure = true;
             }
-            if (unsure) {
-                if (!free_guess) { RR_WHY(6); ok = false; break; }
-                occl = false;
+            if (unsure) {  // the literal march with the reference's tests decides
+                const double T = march_exact_brute(sc, so, L64, dist64 - bias64, bias64);
+                occl = !(T > bias64);
+                first_s = ns; first_p = np; first_t = nt;
             }
             out.c_shadow += 1u;
             out.c_sph += first_s < ns ? (uint32_t)first_s + 1u : (uint32_t)ns;
@@ -273,36 +277,33 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
             if (depth == 0 && j < 16) out.lmask |= 1u << (16 + j);
             if (occl) continue;
             if (depth == 0 && j < 16) out.lmask |= 1u << j;
+            const float inv = __frcp_rn(dist);
             const float att = inv * inv;  // 1 / d^2
             const float wd = att * ndl;
-            dr = __fmaf_rn(Lt.E[0], wd, dr); dg = __fmaf_rn(Lt.E[1], wd, dg); db = __fmaf_rn(Lt.E[2], wd, db);
+            const float Er = (float)sc.lights[j].E[0], Eg = (float)sc.lights[j].E[1], Eb = (float)sc.lights[j].E[2];
+            dr = __fmaf_rn(Er, wd, dr); dg = __fmaf_rn(Eg, wd, dg); db = __fmaf_rn(Eb, wd, db);
             if (spec_on) {  // Blinn-Phong, RE/Scene.h:116-124: halfVector = normalize(lightToHit + viewDir), viewDir = -incoming
-                const float hx = Lx - Dx, hy = Ly - Dy, hz = Lz - Dz;
-                const float h2 = __fmaf_rn(hz, hz, __fmaf_rn(hy, hy, hx * hx));
+                const float hx_ = Lx - Dx, hy_ = Ly - Dy, hz_ = Lz - Dz;
+                const float h2 = __fmaf_rn(hz_, hz_, __fmaf_rn(hy_, hy_, hx_ * hx_));
                 if (h2 > 1e-24f) {  // (normalize() returns 0 below 1e-12: NdotH = 0, no term)
-                    const float ndh = __fmaf_rn(Nz, hz, __fmaf_rn(Ny, hy, Nx * hx)) * rsqrtf(h2);
+                    const float ndh = __fmaf_rn(Nz, hz_, __fmaf_rn(Ny, hy_, Nx * hx_)) * rsqrtf(h2);
                     if (ndh > 0.0f) {
                         const float sf = tm32::ex2(m_shin * tm32::lg2(fminf(ndh, 1.0f))) * att;
-                        sr = __fmaf_rn(Lt.E[0], sf, sr); sg = __fmaf_rn(Lt.E[1], sf, sg); sb = __fmaf_rn(Lt.E[2], sf, sb);
+                        sr = __fmaf_rn(Er, sf, sr); sg = __fmaf_rn(Eg, sf, sg); sb = __fmaf_rn(Eb, sf, sb);
                     }
                 }
             }
         }
-        if (!ok) { live = false; continue; }
         // localLight = color * diffuse + specular * material.specular; finalLight += localLight (transparency = 0), RE/Scene.h:126-128,171-173
         ar = __fmaf_rn(w, __fmaf_rn((float)M.color[0], dr, sr * m_spec), ar);
         ag = __fmaf_rn(w, __fmaf_rn((float)M.color[1], dg, sg * m_spec), ag);
         ab = __fmaf_rn(w, __fmaf_rn((float)M.color[2], db, sb * m_spec), ab);
-        // ---- reflection, RE/Scene.h:189-195: reflectiveness = material.specular > bias
-        if (!(M.specular > P.bias)) { live = false; continue; }
-        // reflectDir = incoming.reflect(normal).normalize(); reflectRay = {hitPoint + reflectDir * bias, reflectDir} — in FP64
-        const double k2 = 2.0 * (front ? nd64 : -nd64);  // 2 (d . N) with the flipped normal
-        double rx = fma(-k2, nx64, dx), ry = fma(-k2, ny64, dy), rz = fma(-k2, nz64, dz);
-        const double ri = rsqrt64_fast(rx * rx + ry * ry + rz * rz);
-        rx *= ri; ry *= ri; rz *= ri;
-        Ox = fma(rx, P.bias, Px); Oy = fma(ry, P.bias, Py); Oz = fma(rz, P.bias, Pz);
-        dx = rx; dy = ry; dz = rz;
-        Dx = (float)dx; Dy = (float)dy; Dz = (float)dz;
+        // ---- reflection, RE/Scene.h:189-195: reflectiveness = material.specular > bias;
+        // reflectDir = incoming.reflect(normal).normalize(); reflectRay = {hitPoint + reflectDir * bias, reflectDir}
+        if (!(M.specular > bias64)) { live = false; continue; }
+        const d3 R = normalize(reflect(incoming, N));
+        o = Pn + R * bias64;
+        d = R;
         w *= m_spec;
         if (w < kRrCutWeight) live = false;
     }

@@ -54,7 +54,7 @@ def test_reflective_fp32_path_against_exact_path(engine, case):
         assert 0 < sf[k] <= se[k], f"counter {k}: fp32 path {sf[k]}, exact path {se[k]}"
     frac = sf["fp64_confirms"] / n_px
     print(f"{case}: {100 * frac:.1f} % of the pixels in flagged tiles; kernel {sf['kernel_ms']:.3f} ms vs exact {se['kernel_ms']:.3f} ms")
-    assert frac < 0.75  # (small frames of symmetric scenes: whole rows of exact ties between two planes, and a tile is 8 x 4 pixels)
+    assert frac == 0.0  # (inconclusive interval decisions are settled in the kernel by the reference's own tests: no tile is left to the exact kernel)
 
 
 def test_reflective_fp32_path_multisample_bands_and_operators(engine):
