@@ -105,9 +105,13 @@ def test_c1_whole_frame(engine, oracle):
     assert np.array_equal(g["depth64"][hit], o["depth"][hit])
     np.testing.assert_allclose(g["hdr64"], o["hdr"], rtol=1e-9, atol=1e-14)
     want = oracle.tonemap_all(o["hdr"])
-    for op in range(_abi.TM_COUNT):
+    for op in range(_abi.TM_COUNT):  # the production path of this scene: the reflective FP32 kernel (rte_render32r.cu)
         p = engine.render_host(outputs=("rgb8",), tonemap_op=op)["rgb8"]
         assert lsb_diff(p, want[op]).max() <= 1, _abi.TM_NAMES[op]
+    p = engine.render_host(outputs=("hdr", "prim_id", "light_mask"))
+    assert engine.last_render_launches() == 2 and engine.stats()["fp64_confirms"] == 0  # that kernel, and no tile left to the exact one
+    assert np.array_equal(p["prim_id"], o["prim_id"]) and np.array_equal(p["light_mask"], o["light_mask"])
+    np.testing.assert_allclose(p["hdr"][:, :3], o["hdr"], rtol=2e-4, atol=2e-4)
 
 
 def test_c5_8k_sampled_rows(engine, oracle):
