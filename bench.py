@@ -485,6 +485,45 @@ def breakdown(pipe, m, steps, flush, stream):
                     "fence = step - launches - build (waiting for the slowest rank's flags over NVLink)"}
 
 
+def c1_leg(torch, stream, flush, local_rank, steps):
+    """C1 = main()'s scene (5 reflective planes, the box mesh, 2 lights, maxRecursion 10) at 1000x1000: device time of rte_render
+    (HDR + RGB8 with ACES) at 1 sample per pixel and at the reference's default 32 (RE/Math.h:94); L2 flushed between frames."""
+    import dataclasses
+    from raytracingengine_b200 import _abi, scenes
+    from raytracingengine_b200.engine import Engine
+    out = {"workload": "C1: main()'s scene at 1000x1000 (5 reflective planes, box mesh, 2 lights, maxRecursion 10), ACES"}
+    for aa in (1, 32):
+        arrays, cam = scenes.config1()
+        cam = dataclasses.replace(cam, antiAliasingAmount=aa, jitterSeed=7)
+        e = Engine(local_rank)
+        e.set_stream(stream.cuda_stream)
+        e.upload(arrays, cam)
+        n = cam.width * cam.height
+        hdr = torch.empty(n * 4, dtype=torch.float32, device="cuda")
+        rgb = torch.empty(n * 3 + 16, dtype=torch.uint8, device="cuda")
+        k = steps if aa == 1 else max(3, steps // 3)
+        ts = []
+        for i in range(3 + k):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            e.set_camera(cam)
+            e.render_device({"hdr": hdr.data_ptr(), "rgb8": rgb.data_ptr()}, tonemap_op=_abi.TM_ACES)
+            b.record(stream)
+            torch.cuda.synchronize()
+            if i >= 3:
+                ts.append(a.elapsed_time(b))
+        s = e.stats()
+        rays = s["primary_rays"] + s["shadow_rays"] + s["secondary_rays"]
+        ms = sum(ts) / len(ts)
+        out[f"spp{aa}"] = {"ms_per_frame": round(ms, 4), "rays_traced": int(rays), "Mrays_per_s": round(rays / ms / 1e3, 1), "steps": k,
+                           "gpu_launches_per_frame": e.last_render_launches(), "pixels_left_to_the_exact_kernel": int(s["fp64_confirms"])}
+        e.close()
+    out["note"] = ("the reflective FP32 kernel ends a chain of reflections below a path weight of 1e-7, so it traces fewer rays than the "
+                   "reference (30.0 M per sample); parity: tests/test_gpu_fullsize.py::test_c1_whole_frame, both arms: tools/c1_bench.py")
+    return out
+
+
 def sharding_text(pipe):
     if pipe.world == 1:
         return "single band"
@@ -592,6 +631,12 @@ def run_gpu(args) -> None:
               "steps": max(3, args.steps // 4), "sharding": sharding_text(p5), "fixup_pixels": int(m5["fixup_pixels"]), "breakdown": bd5, **chk5}
         p5.close()
 
+    # ---- the reference's own default workload in the same run (BASELINE.json configs[0]): main()'s scene at 1000x1000 with 1 and
+    # with the default 32 samples per pixel, one GPU (the frame is 0.7 ms: nothing to shard)
+    c1 = None
+    if world == 1 and not args.no_c5 and args.scale == 1.0:
+        c1 = c1_leg(torch, stream, flush, local_rank, max(3, args.steps // 2))
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -651,6 +696,8 @@ def run_gpu(args) -> None:
     }
     if c5 is not None:
         line["c5_8k"] = c5
+    if c1 is not None:
+        line["c1_default_scene"] = c1
     if not args.no_cpu_baseline and world == 1:
         orc, row_step = cpu_reference_sample(arrays, cam, args.cpu_seconds)
         r = orc.render(arrays, cam, row_step=row_step, threads=host_threads())
