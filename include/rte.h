@@ -176,7 +176,7 @@ typedef struct rte_render_opts {
  *                  staging) even where the view-based kernels apply; it is what scenes too large for those kernels take anyway.
  * And one switch that selects the numerics of the PRODUCTION path:
  *   EXACT_FP64     never take the FP32 production path.  Without it, a call that asks for hdr / rgb8 / prim_id / light_mask
- *                  only, on a diffuse sphere / plane scene, is shaded in FP32 (hit index and shadow visibility bit-exact — every
+ *                  only, on a diffuse scene (spheres, planes, triangles, models), is shaded in FP32 (hit index and shadow visibility bit-exact — every
  *                  FP32 decision is certain within its error bound or the pixel is re-rendered in FP64 —, HDR to ~1e-6 relative,
  *                  RGB8 within +-1 LSB of the reference: the bars BASELINE.json states).  The same holds for opaque scenes with
  *                  specular (reflecting) materials and at most 64 spheres + triangles — main()'s scene —: their chains of

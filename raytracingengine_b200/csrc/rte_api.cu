@@ -48,7 +48,7 @@ struct rte_ctx {
     DevScene sc{};
     DevCamera cam{};
     rte_camera cam_host{};
-    DevBuf b_sph32, b_tri32, b_sph64, b_sphhl, b_sphmat, b_planes, b_tri64, b_triinfo, b_mats, b_lights, b_views, b_tviews, b_views_cold, b_tviews_cold;
+    DevBuf b_sph32, b_tri32, b_sph64, b_sphhl, b_sphmat, b_planes, b_tri64, b_triiv, b_triinfo, b_mats, b_lights, b_views, b_tviews, b_views_cold, b_tviews_cold;
     bool views_dirty = true;
     double views_bias = -1.0;
     // FP32 production path: per-origin direction grids (rte_grid.cuh), rebuilt when the scene, the camera or the bias changes
@@ -289,7 +289,7 @@ extern "C" void rte_destroy(rte_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphhl, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triinfo,
+    DevBuf* bufs[] = {&ctx->b_sph32, &ctx->b_tri32, &ctx->b_sph64, &ctx->b_sphhl, &ctx->b_sphmat, &ctx->b_planes, &ctx->b_tri64, &ctx->b_triiv, &ctx->b_triinfo,
                       &ctx->b_mats, &ctx->b_lights, &ctx->b_views, &ctx->b_tviews, &ctx->b_views_cold, &ctx->b_tviews_cold, &ctx->b_grid_count, &ctx->b_grid_start, &ctx->b_grid_entries, &ctx->b_grid_aggr, &ctx->s_hits, &ctx->s_fix, &ctx->s_hdr, &ctx->s_hdr64, &ctx->s_tm64, &ctx->s_rgb8, &ctx->s_prim, &ctx->s_depth,
                       &ctx->s_depth64, &ctx->s_dnorm, &ctx->s_dn64, &ctx->s_tileflags, &ctx->s_normal, &ctx->s_albedo, &ctx->s_lmask, &ctx->s_tm_in, &ctx->s_q_o, &ctx->s_q_d,
                       &ctx->s_q_m, &ctx->s_q_out};
@@ -415,6 +415,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     std::vector<float4> tri32((size_t)nt_pad * 3);
     std::vector<DevTri64> tri64((size_t)nt_pad);
     std::vector<int2> triinfo((size_t)nt_pad, make_int2(-1, 0));
+    std::vector<Tri32> triiv((size_t)nt_pad);
     double t_ext = 0.0, t_edge = 0.0;
     int k = 0;
     auto add_tri = [&](H3 v0, H3 v1, H3 v2, H3 T, int mat, int report) {
@@ -427,6 +428,16 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
         tri32[3 * (size_t)k + 1] = make_float4((float)e1.x, (float)e1.y, (float)e1.z, 0.f);
         tri32[3 * (size_t)k + 2] = make_float4((float)e2.x, (float)e2.y, (float)e2.z, 0.f);
         triinfo[k] = make_int2(mat, report);
+        {
+            Tri32& q = triiv[k];
+            const double A0[3] = {a0.x, a0.y, a0.z}, E1[3] = {e1.x, e1.y, e1.z}, E2[3] = {e2.x, e2.y, e2.z}, Nn[3] = {n.x, n.y, n.z};
+            for (int c = 0; c < 3; ++c) {
+                q.ah[c] = (float)A0[c]; q.al[c] = (float)(A0[c] - (double)q.ah[c]);
+                q.e1[c] = (float)E1[c]; q.e2[c] = (float)E2[c]; q.n[c] = (float)Nn[c];
+            }
+            q.E1 = (float)(hlen(e1) * 1.000001); q.E2 = (float)(hlen(e2) * 1.000001);
+            q.mat = mat; q.report = (uint32_t)report; q.pad = 0.f;
+        }
         t_ext = std::fmax(t_ext, std::fmax(hlen(a0), std::fmax(hlen(hadd(v1, T)), hlen(hadd(v2, T)))));
         t_edge = std::fmax(t_edge, std::fmax(hlen(e1), hlen(e2)));
         ++k;
@@ -470,11 +481,11 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     if ((rc = reserve(ctx, ctx->b_tviews, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_views_cold, (size_t)(1 + nl) * (size_t)ns_pad * 16))) return rc;
     if ((rc = reserve(ctx, ctx->b_tviews_cold, (size_t)(1 + nl) * (size_t)nt_pad32 * 16))) return rc;
-    if ((rc = stage_begin(ctx, stage_bytes(sph32) + stage_bytes(sph64) + stage_bytes(sphhl) + stage_bytes(sphmat) + stage_bytes(planes) + stage_bytes(tri32) + stage_bytes(tri64) +
+    if ((rc = stage_begin(ctx, stage_bytes(sph32) + stage_bytes(sph64) + stage_bytes(sphhl) + stage_bytes(sphmat) + stage_bytes(planes) + stage_bytes(tri32) + stage_bytes(tri64) + stage_bytes(triiv) +
                                stage_bytes(triinfo) + stage_bytes(mats) + stage_bytes(lights))))
         return rc;
     if ((rc = upload(ctx, ctx->b_sph32, sph32)) || (rc = upload(ctx, ctx->b_sph64, sph64)) || (rc = upload(ctx, ctx->b_sphhl, sphhl)) || (rc = upload(ctx, ctx->b_sphmat, sphmat)) ||
-        (rc = upload(ctx, ctx->b_planes, planes)) || (rc = upload(ctx, ctx->b_tri32, tri32)) || (rc = upload(ctx, ctx->b_tri64, tri64)) ||
+        (rc = upload(ctx, ctx->b_planes, planes)) || (rc = upload(ctx, ctx->b_tri32, tri32)) || (rc = upload(ctx, ctx->b_tri64, tri64)) || (rc = upload(ctx, ctx->b_triiv, triiv)) ||
         (rc = upload(ctx, ctx->b_triinfo, triinfo)) || (rc = upload(ctx, ctx->b_mats, mats)) || (rc = upload(ctx, ctx->b_lights, lights)))
         return rc;
     RTE_CUDA(ctx, cudaEventRecord(ctx->ev_stage, ctx->stream));  // (the copies read the staging buffer, not the host vectors: no sync)
@@ -494,7 +505,7 @@ extern "C" int rte_upload_scene(rte_ctx* ctx, const rte_scene_desc* d) {
     ctx->grid_dirty = true;
     sc.ns = ns; sc.ns_pad = ns_pad; sc.nt = nt; sc.nt_pad = nt_pad;
     sc.sph64 = (const double4*)ctx->b_sph64.p; sc.sph_hl = (const float4*)ctx->b_sphhl.p; sc.sph_mat = (const int32_t*)ctx->b_sphmat.p;
-    sc.planes = (const DevPlane*)ctx->b_planes.p; sc.tri64 = (const DevTri64*)ctx->b_tri64.p;
+    sc.planes = (const DevPlane*)ctx->b_planes.p; sc.tri64 = (const DevTri64*)ctx->b_tri64.p; sc.tri_iv = (const Tri32*)ctx->b_triiv.p;
     sc.tri_info = (const int2*)ctx->b_triinfo.p; sc.materials = (const rte_material*)ctx->b_mats.p;
     sc.lights = (const DevLight*)ctx->b_lights.p;
     sc.np = np; sc.nm = (int)d->n_materials; sc.nl = nl;

@@ -34,6 +34,17 @@ struct DevTri64 {   // Triangle, RE/Shape.h:198-227, evaluated once on the host 
     double n[3];    //   normalize((v1 - v0) x (v2 - v0))  — from the untranslated vertices
 };
 
+// FP32 interval test of a triangle (rte_interval.cuh: tri_interval), built at upload next to DevTri64
+struct __align__(16) Tri32 {
+    float ah[3], al[3];   // a0 = ah + al
+    float e1[3], e2[3];   // edges (FP64 differences, rounded)
+    float n[3];           // unit normal (FP64, rounded): HitInfo.normal
+    float E1, E2;         // upper bounds of |e1|, |e2|
+    int mat;
+    uint32_t report;      // HitInfo.index: the triangle's, or its MODEL's (RE/Shape.h:276)
+    float pad;            // (80 bytes: five 16-byte loads from global memory)
+};
+
 struct DevScene {
     // FP32 filter arrays (sources of the TMA bulk copies into shared memory)
     const float4* sph32;  // {cx, cy, cz, r*r}; padded to a multiple of 32 with never-hit entries
@@ -47,6 +58,7 @@ struct DevScene {
     int32_t ns, ns_pad, nt, nt_pad;
     // FP64 exact arrays
     const double4* sph64; // {cx, cy, cz, r}
+    const Tri32* tri_iv;  // FP32 path: one per (flattened) triangle
     const float4* sph_hl; // FP32 path: two float4 per sphere, {hi(C), |r|} and {lo(C), 0} with C = hi + lo to ~2^-48 (no FP64 -> FP32 conversion per candidate)
     const int32_t* sph_mat;
     const DevPlane* planes;

@@ -158,14 +158,7 @@ __device__ __forceinline__ int plane_shadow(float num, float en, float A, float 
 // Error bounds against the reference's values (edges rounded to FP32: eps |e|; s from hi + lo halves: 2 eps |s| + eo; direction
 // ed; three or four roundings per product), with E1 >= |e1|, E2 >= |e2|, S >= |s|, g = 12 eps:
 //   |da| <= (ed + g) E1 E2,   |dU| <= E2 (eo + S (ed + g)),   |dV| <= E1 (eo + S (ed + g)),   |dT| <= E1 E2 (eo + S g).
-struct Tri32 {
-    float ah[3], al[3];   // a0 = ah + al
-    float e1[3], e2[3];   // edges (FP64 differences, rounded)
-    float n[3];           // unit normal (FP64, rounded): HitInfo.normal
-    float E1, E2;         // upper bounds of |e1|, |e2|
-    int mat;
-    uint32_t report;      // HitInfo.index: the triangle's, or its MODEL's (RE/Shape.h:276)
-};
+// (struct Tri32: rte_device.cuh)
 __device__ __forceinline__ int tri_interval(const Tri32& T, float ohx, float ohy, float ohz, float olx, float oly, float olz, float Dx, float Dy, float Dz,
                                             float eo, float ed, float& lo, float& hi) {
     lo = 0.0f; hi = 0.0f;

@@ -1,4 +1,4 @@
-// rte_render32.cu — the FP32 production path of the render call (sm_100a): diffuse sphere / plane scenes over per-origin
+// rte_render32.cu — the FP32 production path of the render call (sm_100a): diffuse scenes (spheres, planes, triangles, models) over per-origin
 // direction grids (rte_grid.cuh; built here), outputs HDR float4 / RGB8 (+ the integer AOVs prim_id, light_mask).
 //
 // Replaces Scene::RenderImage / TraceRay / directLightning + tonemap()/toColor for those scenes (RE/Scene.h:311-328, 131-198,
@@ -268,17 +268,18 @@ __device__ __forceinline__ uint32_t tonemap_rgb24(int op, float x, float y, floa
 struct Px32 {
     float r, g, b;       // linear HDR of the sample
     uint32_t prim, lmask;
-    uint32_t c_shadow, c_sph, c_pl;  // statistics of this sample (SURVEY §8(d) algorithmic counts)
+    uint32_t c_shadow, c_sph, c_pl, c_tri;  // statistics of this sample (SURVEY §8(d) algorithmic counts)
 };
+template <bool kTris>  // scenes with triangles: a second instance, so that sphere scenes keep their 64 registers without spills (C2 0.85 -> 0.98 ms otherwise)
 __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S, float* __restrict__ pl_num, int px, int py, bool alive, int sample, Px32& out,
                                         uint32_t& executed) {
     const DevScene& sc = P.sc;
     const DevGrid& grid = P.grid;
-    const int ns = sc.ns, np = S.np, nl = S.nl;
+    const int ns = sc.ns, nt = kTris ? sc.nt : 0, np = S.np, nl = S.nl;
     const float bias = (float)P.bias;
     bool ok = true;
     out.r = out.g = out.b = 0.0f;
-    out.prim = kMiss; out.lmask = 0u; out.c_shadow = 0u; out.c_sph = (uint32_t)ns; out.c_pl = (uint32_t)np;
+    out.prim = kMiss; out.lmask = 0u; out.c_shadow = 0u; out.c_sph = (uint32_t)ns; out.c_pl = (uint32_t)np; out.c_tri = (uint32_t)nt;
     // ---- Camera::getRay, RE/Math.h:99-121 (the reference's FP64 operations up to the normalisation)
     double dx, dy, dz;
     {
@@ -303,8 +304,15 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
     const float cam1 = fabsf(cam32x) + fabsf(cam32y) + fabsf(cam32z);
     bool go0 = alive;
     grid_candidates(grid, 0, r.ux, r.uy, r.uz, go0, [&](int idx) {
-        const float4 shi = __ldg(sc.sph_hl + 2 * idx);
         executed += 1u;
+        if (kTris && idx >= ns) {  // a triangle (standalone or a model's): the cell lists hold it through its bounding sphere
+            float lo, hi;
+            const int cls = tri_interval(sc.tri_iv[idx - ns], cam32x, cam32y, cam32z, S.cam_lo[0], S.cam_lo[1], S.cam_lo[2], r.ux, r.uy, r.uz, 0.0f, 4.0f * kEps32, lo, hi);
+            if (cls == kCandHit) near_hit(nr, RTE_HIT_TRIANGLE, idx - ns, lo, hi);
+            else if (cls == kCandUnsure) near_unsure(nr, lo);
+            return;
+        }
+        const float4 shi = __ldg(sc.sph_hl + 2 * idx);
         if (far_miss(shi, cam32x, cam32y, cam32z, cam1, r.ux, r.uy, r.uz)) return;
         const Cand32 c = classify_sphere(shi, __ldg(sc.sph_hl + 2 * idx + 1), cam32x, cam32y, cam32z, S.cam_lo[0], S.cam_lo[1], S.cam_lo[2], r.ux, r.uy, r.uz);
         float lo, hi;
@@ -321,7 +329,7 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
     }
     if (near_ambiguous(nr)) ok = false;
     const bool hitv = alive && ok && nr.kind != RTE_HIT_NONE;
-    if (!alive) { out.c_sph = 0u; out.c_pl = 0u; }
+    if (!alive) { out.c_sph = 0u; out.c_pl = 0u; out.c_tri = 0u; }
     if (alive && nr.kind == RTE_HIT_NONE) {  // Scene::backgroundColor, RE/Scene.h:30-33
         const float t = 0.5f * (r.uy + 1.0f);
         out.r = __fmaf_rn(0.5f, t, 1.0f - t); out.g = __fmaf_rn(0.7f, t, 1.0f - t); out.b = 1.0f;
@@ -346,6 +354,20 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         Nx = nx; Ny = ny; Nz = nz;
         mat = sc.sph_mat[nr.idx];
         out.prim = ((uint32_t)RTE_HIT_SPHERE << 30) | (uint32_t)nr.idx;
+    } else if (kTris && hitv && nr.kind == RTE_HIT_TRIANGLE) {
+        const DevTri64& T = sc.tri64[nr.idx];  // Moeller-Trumbore's t (RE/Shape.h:208-218) in cheap FP64
+        const double hx = dy * T.e2[2] - dz * T.e2[1], hy = dz * T.e2[0] - dx * T.e2[2], hz = dx * T.e2[1] - dy * T.e2[0];
+        const double a = T.e1[0] * hx + T.e1[1] * hy + T.e1[2] * hz;
+        const double sx = S.cam[0] - T.a0[0], sy = S.cam[1] - T.a0[1], sz = S.cam[2] - T.a0[2];
+        const double qx = sy * T.e1[2] - sz * T.e1[1], qy = sz * T.e1[0] - sx * T.e1[2], qz = sx * T.e1[1] - sy * T.e1[0];
+        const double t = (T.e2[0] * qx + T.e2[1] * qy + T.e2[2] * qz) * rcp64_fast(a);
+        Px = fma(dx, t, S.cam[0]); Py = fma(dy, t, S.cam[1]); Pz = fma(dz, t, S.cam[2]);
+        const double nd = T.n[0] * dx + T.n[1] * dy + T.n[2] * dz;
+        if (fabs(nd) < 1e-9) ok = false;            // frontFace = n.d < 0 must be certain
+        const float sg = nd < 0.0 ? 1.0f : -1.0f;
+        Nx = sg * (float)T.n[0]; Ny = sg * (float)T.n[1]; Nz = sg * (float)T.n[2];
+        mat = sc.tri_info[nr.idx].x;
+        out.prim = ((uint32_t)RTE_HIT_TRIANGLE << 30) | (uint32_t)sc.tri_info[nr.idx].y;
     } else if (hitv) {
         const DevPlane& pl = sc.planes[nr.idx];
         const double num = (pl.p0[0] - S.cam[0]) * pl.n[0] + (pl.p0[1] - S.cam[1]) * pl.n[1] + (pl.p0[2] - S.cam[2]) * pl.n[2];
@@ -395,15 +417,23 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
         const float maxDist = dist - bias;
         const float dt = 24.0f * kEps32 * (dist + so1) + 1e-7f;  // slack of the range ends (maxDist, bias) against the candidate bounds
         const float tmax_lo = maxDist - dt, tmax_hi = maxDist + dt, bias_hi = bias + dt;
-        bool occl = false, unsure = false;
-        uint32_t first = (uint32_t)ns;
+        bool occl = false, unsure = false, occl_t = false;
+        uint32_t first = (uint32_t)ns, first_t = (uint32_t)nt;
         bool go = cast;
         // the light's grid is looked up along the reversed ray (from the light towards the shaded point); the candidates
         // are tested against the ray itself: origin so, direction L
         grid_candidates(grid, 1 + j, -Lx, -Ly, -Lz, go, [&](int idx) {
             if (idx == self) return;  // so lies outside the sphere the point is on, the ray leaves it: both roots < 0
-            const float4 hi = __ldg(sc.sph_hl + 2 * idx);
             executed += 1u;
+            if (kTris && idx >= ns) {  // a triangle
+                float lo, hi2;
+                const int cls = tri_interval(sc.tri_iv[idx - ns], so32x, so32y, so32z, solx, soly, solz, Lx, Ly, Lz, 0.0f, 8.0f * kEps32, lo, hi2);
+                if (cls == kCandMiss || lo > tmax_hi) return;
+                if (cls == kCandHit && lo > bias_hi && hi2 < tmax_lo) { first_t = min(first_t, (uint32_t)(idx - ns)); occl_t = true; return; }
+                unsure = true; go = false;
+                return;
+            }
+            const float4 hi = __ldg(sc.sph_hl + 2 * idx);
             if (far_miss(hi, so32x, so32y, so32z, so1, Lx, Ly, Lz)) return;
             const Cand32 c = classify_sphere(hi, __ldg(sc.sph_hl + 2 * idx + 1), so32x, so32y, so32z, solx, soly, solz, Lx, Ly, Lz);
             float lo, hi2;
@@ -430,9 +460,12 @@ __device__ __forceinline__ bool trace32(const RenderParams& P, const Scene32& S,
             }
         }
         if (cast) {
+            // canonical order of the reference's scan: spheres, planes, triangles — tests up to and including the first occluder
             out.c_shadow += 1u;
             out.c_sph += first < (uint32_t)ns ? first + 1u : (uint32_t)ns;
             out.c_pl += first < (uint32_t)ns ? 0u : (firstp < (uint32_t)np ? firstp + 1u : (uint32_t)np);
+            out.c_tri += (first < (uint32_t)ns || firstp < (uint32_t)np) ? 0u : (first_t < (uint32_t)nt ? first_t + 1u : (uint32_t)nt);
+            occl = occl || occl_t;
             if (j < 16) out.lmask |= 1u << (16 + j);
             if (!occl) {
                 if (j < 16) out.lmask |= 1u << j;
@@ -492,8 +525,8 @@ static __device__ __noinline__ void fix_batch(const RenderParams& P, const uint3
             const d3 e = exact_finish(sc, H, diffuse);
             if (aa > 1) v = v + e; else v = e;
             if (s == 0) { prim0 = H.prim; lmask0 = lm; }
-            st[kStatShadow] += c.shadow; st[kStatSphTests] += c.sph; st[kStatPlTests] += c.pl; st[kStatMarches] += c.marches;
-            if (act && j == 0) { st[kStatPrimary] += 1u; st[kStatSphTests] += (uint32_t)sc.ns; st[kStatPlTests] += (uint32_t)sc.np; st[kStatConfirms] += 1u; }
+            st[kStatShadow] += c.shadow; st[kStatSphTests] += c.sph; st[kStatPlTests] += c.pl; st[kStatTriTests] += c.tri; st[kStatMarches] += c.marches;
+            if (act && j == 0) { st[kStatPrimary] += 1u; st[kStatSphTests] += (uint32_t)sc.ns; st[kStatPlTests] += (uint32_t)sc.np; st[kStatTriTests] += (uint32_t)sc.nt; st[kStatConfirms] += 1u; }
         }
         if (aa > 1) v = v / (double)aa;
         if (act && j == 0) {
@@ -523,7 +556,7 @@ static __device__ __noinline__ void fix_batch(const RenderParams& P, const uint3
 #endif
 constexpr int kTile32W = RTE_TW, kTile32H = RTE_TH;
 
-template <bool kAov>
+template <bool kAov, bool kTris>
 __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_constant__ RenderParams P) {
     __shared__ Scene32 s32;
     __shared__ unsigned long long s_stats[kR32Threads / 32][kStatCount];
@@ -593,14 +626,14 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
         const int64_t pix = (int64_t)band_y * W + px;
         // GeneratePixelAt, RE/Scene.h:283-304: mean of the samples
         float cr = 0.0f, cg = 0.0f, cb = 0.0f;
-        uint32_t prim = kMiss, lmask = 0u, n_shadow = 0u, n_sph = 0u, n_pl = 0u, executed = 0u;
+        uint32_t prim = kMiss, lmask = 0u, n_shadow = 0u, n_sph = 0u, n_pl = 0u, n_tri = 0u, executed = 0u;
         bool ok = true;
 #pragma unroll 1
         for (int s = 0; s < aa; ++s) {
             Px32 o;
-            ok = trace32(P, s32, &s_plnum[0][threadIdx.x], px, py, inb, s, o, executed) && ok;
+            ok = trace32<kTris>(P, s32, &s_plnum[0][threadIdx.x], px, py, inb, s, o, executed) && ok;
             cr += o.r; cg += o.g; cb += o.b;
-            n_shadow += o.c_shadow; n_sph += o.c_sph; n_pl += o.c_pl;
+            n_shadow += o.c_shadow; n_sph += o.c_sph; n_pl += o.c_pl; n_tri += o.c_tri;
             if (s == 0) { prim = o.prim; lmask = o.lmask; }
         }
         if (aa > 1) { const float ia = 1.0f / (float)aa; cr *= ia; cg *= ia; cb *= ia; }
@@ -629,7 +662,7 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
             }
         }
         // ---- statistics of the pixels shaded here (fix_batch counts its own; fp64_confirms = pixel samples rendered again in FP64)
-        const uint32_t v[kStatCount] = {mine ? (uint32_t)aa : 0u, mine ? n_shadow : 0u, 0u, mine ? n_sph : 0u, mine ? n_pl : 0u, 0u, 0u, 0u, executed};
+        const uint32_t v[kStatCount] = {mine ? (uint32_t)aa : 0u, mine ? n_shadow : 0u, 0u, mine ? n_sph : 0u, mine ? n_pl : 0u, mine ? n_tri : 0u, 0u, 0u, executed};
         uint32_t sum_mine = 0;
 #pragma unroll
         for (int k = 0; k < kStatCount; ++k) {
@@ -655,14 +688,16 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
 // Can this render call take the FP32 path?  (rte_api.cu decides with it; everything else takes the exact kernels.)
 bool fp32_path_eligible(const RenderParams& p) {
     const rte_frame& f = p.out;
-    return !p.sc.reflective && !p.sc.transparent && p.sc.nt == 0 && p.sc.ns > 0 && p.sc.np <= kR32Planes && p.sc.nl <= kR32Lights &&
+    return !p.sc.reflective && !p.sc.transparent && p.sc.ns + p.sc.nt > 0 && p.sc.np <= kR32Planes && p.sc.nl <= kR32Lights &&
            !p.exact_shadows && !p.no_filter && !p.force_general && !p.no_cull && p.pass_mode == 0 && !p.exact_fp64 &&
            !f.hdr64 && !f.depth && !f.depth64 && !f.depth_norm && !f.normal && !f.albedo && p.bias >= 1e-6 && p.bias <= 1e-1;
 }
 
 cudaError_t launch_render32(const RenderParams& p, int sm_count, cudaStream_t stream) {
     const bool aov = p.out.prim_id || p.out.light_mask;
-    const void* fn = aov ? (const void*)render32_kernel<true> : (const void*)render32_kernel<false>;
+    const bool tris = p.sc.nt > 0;
+    const void* fn = tris ? (aov ? (const void*)render32_kernel<true, true> : (const void*)render32_kernel<false, true>)
+                          : (aov ? (const void*)render32_kernel<true, false> : (const void*)render32_kernel<false, false>);
     const long long n_tiles = (long long)((p.cam.width + kTile32W - 1) / kTile32W) * ((p.n_rows + kTile32H - 1) / kTile32H);
     long long blocks = sm_count;  // persistent: one CTA of 32 warps per SM (64 registers per thread fill the register file)
     const long long needed = (n_tiles + kR32Threads / 32 - 1) / (kR32Threads / 32);

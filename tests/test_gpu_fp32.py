@@ -9,7 +9,7 @@ import pytest
 from raytracingengine_b200 import _abi, scenes
 
 pytestmark = pytest.mark.gpu
-COUNTERS = ("primary_rays", "shadow_rays", "sphere_tests", "plane_tests")
+COUNTERS = ("primary_rays", "shadow_rays", "sphere_tests", "plane_tests", "triangle_tests")
 OUTS = ("hdr", "rgb8", "prim_id", "light_mask")
 
 
@@ -32,7 +32,7 @@ def check(fast, sf, exact, se, n_px):
     assert sf["fp64_confirms"] <= 0.02 * n_px, f"{sf['fp64_confirms']} of {n_px} pixels went through the exact fix-up"
 
 
-@pytest.mark.parametrize("cfg", ["c2", "c2_quarter", "c3", "odd", "big_resident", "camera_inside"])
+@pytest.mark.parametrize("cfg", ["c2", "c2_quarter", "c3", "odd", "big_resident", "camera_inside", "c4_blob", "c4_box", "mixed", "mesh_10k"])
 def test_fp32_path_against_exact_path_and_oracle(engine, oracle, cfg):
     if cfg == "c2":
         arrays, cam = scenes.config2(scale=0.125)
@@ -42,6 +42,14 @@ def test_fp32_path_against_exact_path_and_oracle(engine, oracle, cfg):
         arrays, cam = scenes.config3(scale=0.125)
     elif cfg == "big_resident":  # 2048 spheres x 5 views = 160 KB resident, no room for the cull scratch
         arrays, cam = scenes.synthetic_room(240, 135, 120.0, 2048, 4, 4321)
+    elif cfg == "c4_blob":  # diffuse OBJ-mesh scenes: triangles through the same grids (tri_interval)
+        arrays, cam = scenes.config4("blob", scale=0.25)
+    elif cfg == "c4_box":
+        arrays, cam = scenes.config4("box", scale=0.2)
+    elif cfg == "mixed":  # spheres, planes, free triangles and a model in one scene
+        arrays, cam = scenes.mixed_scene(224, 126, 130.0)
+    elif cfg == "mesh_10k":  # a 5 120-triangle model
+        arrays, cam = scenes.mixed_scene(200, 112, 120.0, n_spheres=40, mesh_level=4)
     elif cfg == "camera_inside":  # the camera sits inside a big sphere: far roots, inward normals
         arrays, cam = scenes.synthetic_room(160, 90, 80.0, 200, 3, 99)
         arrays.spheres[7] = ((0.0, 0.0, -25.0), 60.0, 7, 0)
@@ -57,7 +65,7 @@ def test_fp32_path_against_exact_path_and_oracle(engine, oracle, cfg):
     want = oracle.tonemap_one(_abi.TM_ACES, o["hdr"])
     assert np.abs(fast["rgb8"].astype(np.int16) - want.astype(np.int16)).max() <= 1
     assert sf["primary_rays"] == o["primary_rays"] and sf["shadow_rays"] == o["shadow_rays"]
-    assert sf["sphere_tests"] == o["sphere_tests"] and sf["plane_tests"] == o["plane_tests"]
+    assert sf["sphere_tests"] == o["sphere_tests"] and sf["plane_tests"] == o["plane_tests"] and sf["triangle_tests"] == o["triangle_tests"]
 
 
 def test_fp32_path_all_operators_bands_stripes(engine, oracle):
