@@ -619,6 +619,9 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
     while (tile < n_tiles) {
         unsigned int next = 0;
         if (lane == 0) next = n_static + atomicAdd(P.tile_counter, 1u);  // the next tile id arrives behind the work
+#ifdef RTE_TILE_CLOCK
+        unsigned long long tc0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tc0));
+#endif
         int ty = (int)((float)tile * inv_tiles_x);  // tile / tiles_x without the integer-division sequence (tile < 2^24 for every frame <= 16K x 16K)
         if ((unsigned)(ty * tiles_x) > tile) --ty; else if ((unsigned)((ty + 1) * tiles_x) <= tile) ++ty;
         const int tx = (int)tile - ty * tiles_x;
@@ -680,8 +683,24 @@ __global__ void __launch_bounds__(kR32Threads, 1) render32_kernel(const __grid_c
             __syncwarp();
             // a batch as soon as every lane of it has a (pixel, light) pair: waiting for a fuller queue left up to eight batches
             // (C5: 8 lights, 4 pixels per batch) to the end of the launch, where nothing hides them — ~0.1 ms per launch
-            if (fix_n >= fix_full || fix_n > kFixCap - 32) { fix_batch(P, s_fixq[warp], fix_n, s_stats[warp]); fix_n = 0; }
+            if (fix_n >= fix_full || fix_n > kFixCap - 32) {
+#ifdef RTE_TILE_CLOCK
+                unsigned long long fc0; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(fc0));
+#endif
+                fix_batch(P, s_fixq[warp], fix_n, s_stats[warp]);
+#ifdef RTE_TILE_CLOCK
+                unsigned long long fc1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(fc1));
+                if (lane == 0) atomicMax(&P.stats[kStatTriTests], (fc1 - fc0) * 1000ull + (unsigned long long)fix_n);  // slowest batch: ns * 1000 + pixels
+#endif
+                fix_n = 0;
+            }
         }
+#ifdef RTE_TILE_CLOCK
+        {   // developer probe: slowest tile of the launch in ns (reported as secondary_rays), tiles over 100 us (as exact_marches)
+            unsigned long long tc1; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tc1));
+            if (lane == 0) { atomicMax(&P.stats[kStatSecondary], tc1 - tc0); }
+        }
+#endif
         tile = __shfl_sync(kFullMask, next, 0);
     }
     if (fix_n > 0) fix_batch(P, s_fixq[warp], fix_n, s_stats[warp]);  // what is left of the warp's queue
