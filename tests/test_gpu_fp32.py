@@ -114,3 +114,42 @@ def test_exact_flag_and_fp64_outputs_keep_the_exact_path(engine, oracle):
     a = engine.render_host(outputs=("rgb8",), tonemap_op=_abi.TM_ACES, flags=_abi.FLAG_EXACT_FP64)["rgb8"]
     b = engine.render_host(outputs=("rgb8", "hdr64"), tonemap_op=_abi.TM_ACES)
     assert np.array_equal(a, want) and np.array_equal(b["rgb8"], want) and np.array_equal(b["hdr64"], o["hdr"])
+
+
+def test_fp32_path_on_grid_aligned_edge_cases(engine, oracle):
+    """Rays that pass EXACTLY through triangle vertices and edges, graze spheres tangentially, run parallel to a plane and look
+    along the line where two planes meet (integer scene coordinates against integer pixel offsets: camera at the origin,
+    focal = 64, so the point (x, y, 64) is the centre of pixel (x + W/2, H/2 - y)).  The intervals cannot decide those pixels;
+    the exact batches must, like the reference: hit ids, visibility and bytes against the reference build."""
+    W, H, F = 96, 64, 64.0
+    cam = scenes.Camera((0.0, 0.0, 0.0), F, W, H, 0.0, 200.0)
+    cam.antiAliasingAmount = 1
+    mats = np.array([scenes._material(c) for c in ((1, 1, 1), (1, 0.3, 0.2), (0.2, 0.4, 1), (0.3, 1, 0.3), (1, 1, 0.2))], dtype=_abi.material_dt)
+    planes = np.zeros(3, dtype=_abi.plane_dt)
+    planes[0] = ((0, -20, 0), (0, 1, 0), 0, 0)        # floor: meets the back wall along a pixel row (y / z = -20 / 128 = -10 / 64)
+    planes[1] = ((0, 0, 128), (0, 0, -1), 0, 0)       # back wall
+    planes[2] = ((24, 0, 0), (-1, 0, 0), 3, 0)        # right wall: column x = 24 / 128 * 64 = 12 looks along its edge with the back wall
+    tris = np.zeros(3, dtype=_abi.triangle_dt)
+    tris[0] = ((-16, -8, 64), (0, 8, 64), (-16, 8, 64), (0, 0, 0), 1, 0)    # vertices on pixel centres, one edge along a pixel diagonal
+    tris[1] = ((-16, -8, 64), (0, -8, 64), (0, 8, 64), (0, 0, 0), 2, 0)     # shares that diagonal (the first triangle wins the tie)
+    tris[2] = ((4, -4, 96), (20, -4, 96), (4, 12, 96), (0, 0, 0), 4, 0)     # back-facing from the camera? no: counter-clockwise, seen from behind
+    spheres = np.zeros(2, dtype=_abi.sphere_dt)
+    spheres[0] = ((10.0, -14.0, 70.0), 6.0, 1, 0)     # rests on... above the floor, its shadow falls on the floor
+    spheres[1] = ((-30.0, 10.0, 100.0), 10.0, 2, 0)
+    lights = np.zeros(2, dtype=_abi.light_dt)
+    lights[0] = ((0.0, 40.0, 64.0), (1, 1, 1), 4000.0)
+    lights[1] = ((-16.0, 8.0, 20.0), (1, 0.9, 0.8), 1500.0)   # on the line camera -> vertex (-16, 8, 64): shadow rays along triangle edges
+    arrays = scenes.SceneArrays(materials=mats, spheres=spheres, planes=planes, triangles=tris, lights=lights)
+    engine.upload(arrays, cam)
+    fast, sf, lf, exact, se = both_paths(engine)
+    o = oracle.render(arrays, cam, want_aovs=True)
+    assert np.array_equal(exact["prim_id"], o["prim_id"]) and np.array_equal(exact["light_mask"], o["light_mask"])
+    assert np.array_equal(fast["prim_id"], o["prim_id"]), f"{np.count_nonzero(fast['prim_id'] != o['prim_id'])} nearest-hit mismatches"
+    assert np.array_equal(fast["light_mask"], o["light_mask"]), f"{np.count_nonzero(fast['light_mask'] != o['light_mask'])} visibility mismatches"
+    want = oracle.tonemap_one(_abi.TM_ACES, o["hdr"])
+    assert np.abs(fast["rgb8"].astype(np.int16) - want.astype(np.int16)).max() <= 1
+    for k in COUNTERS:
+        assert sf[k] == se[k], k
+    assert sf["fp64_confirms"] >= W  # at least the row along the floor / wall edge went through the exact batches
+    kinds = set((o["prim_id"][o["prim_id"] != _abi.PRIM_MISS] >> 30).tolist())
+    assert kinds == {_abi.HIT_SPHERE, _abi.HIT_PLANE, _abi.HIT_TRIANGLE}
