@@ -108,6 +108,11 @@ static __device__ __noinline__ double march_exact_brute(const DevScene& sc, d3 o
 
 // One sample of one pixel per lane.  Returns false when something could not be decided (never seen; the tile would be rendered
 // again by the exact kernel and nothing of `out` used).
+// kTree: scenes with transparent materials — TraceRay is a tree (refracted + reflected child, RE/Scene.h:175-195), walked depth
+// first with a small per-pixel stack of pending rays {origin, direction, weight, depth}; without them it is a chain and no stack
+// exists.  pixel = sum over the nodes of  weight * (1 - transparency) * localLight  (+ weight * sky where a branch ends).
+struct NodeR { d3 o, d; float w; int depth; };
+template <bool kTree>
 __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S, int px, int py, bool alive, int sample, PxR& out) {
     const DevScene& sc = P.sc;
     const int ns = S.ns, nt = S.nt, np = S.np, nl = S.nl;
@@ -124,8 +129,13 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
     float w = 1.0f;                             // weight of the node's light in the pixel
     float ar = 0.0f, ag = 0.0f, ab = 0.0f;
     bool live = alive;
+    int depth = 0;
+    NodeR stk[kTree ? RTE_MAX_DEPTH + 2 : 1];
+    int sp = 0;  // pending rays of this pixel
 #pragma unroll 1
-    for (int depth = 0; __any_sync(kFullMask, live); ++depth) {
+    while (true) {
+        if (kTree && !live && sp > 0) { --sp; o = stk[sp].o; d = stk[sp].d; w = stk[sp].w; depth = stk[sp].depth; live = true; }
+        if (!__any_sync(kFullMask, live)) break;
         depth_dbg = depth;
         const float Dx = (float)d.x, Dy = (float)d.y, Dz = (float)d.z;
         auto sky = [&]() {  // Scene::backgroundColor, RE/Scene.h:30-33
@@ -168,6 +178,7 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
         }
         out.c_sph += (uint32_t)ns; out.c_pl += (uint32_t)np; out.c_tri += (uint32_t)nt;
         if (depth > 0) out.c_secondary += 1u;
+        const int node_depth = depth;
         // ---- the hit: which primitive from the intervals (or, when they overlap, from the reference's own scan), its distance
         // from the reference's own test of that primitive
         HitX hx;
@@ -205,7 +216,7 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
         const d3 normal = normalize(N);  // directLightning re-normalises, RE/Scene.h:81
         const float Nx = (float)normal.x, Ny = (float)normal.y, Nz = (float)normal.z;
         if (hx.kind == RTE_HIT_SPHERE && front && bias >= 1e-5f) self = hx.idx;
-        if (depth == 0) out.prim = ((uint32_t)hx.kind << 30) | report;
+        if (node_depth == 0) out.prim = ((uint32_t)hx.kind << 30) | report;
         mat = (mat >= 0 && mat < sc.nm) ? mat : sc.nm;
         const rte_material& M = sc.materials[mat];
         const float m_spec = (float)M.specular, m_shin = (float)M.shininess;
@@ -263,10 +274,14 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
                 if (cls == kCandHit && lo > bias_hi && hi < tmax_lo) { occl = true; first_t = i; }
                 else unsure = true;
             }
-            if (unsure) {  // the literal march with the reference's tests decides
+            float Tf = 1.0f;  // transmittance of an unoccluded ray
+            if (unsure || (kTree && occl)) {
+                // the literal march with the reference's tests decides — and, with transparent materials, every occluded ray takes
+                // it: T is the product of the occluders' transparencies (RE/Scene.h:68-69)
                 const double T = march_exact_brute(sc, so, L64, dist64 - bias64, bias64);
                 occl = !(T > bias64);
-                first_s = ns; first_p = np; first_t = nt;
+                Tf = (float)T;
+                if (unsure) { first_s = ns; first_p = np; first_t = nt; }
             }
             out.c_shadow += 1u;
             out.c_sph += first_s < ns ? (uint32_t)first_s + 1u : (uint32_t)ns;
@@ -274,11 +289,11 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
                 out.c_pl += first_p < np ? (uint32_t)first_p + 1u : (uint32_t)np;
                 if (first_p >= np) out.c_tri += first_t < nt ? (uint32_t)first_t + 1u : (uint32_t)nt;
             }
-            if (depth == 0 && j < 16) out.lmask |= 1u << (16 + j);
+            if (node_depth == 0 && j < 16) out.lmask |= 1u << (16 + j);
             if (occl) continue;
-            if (depth == 0 && j < 16) out.lmask |= 1u << j;
+            if (node_depth == 0 && j < 16) out.lmask |= 1u << j;
             const float inv = __frcp_rn(dist);
-            const float att = inv * inv;  // 1 / d^2
+            const float att = inv * inv * Tf;  // transmittance / d^2
             const float wd = att * ndl;
             const float Er = (float)sc.lights[j].E[0], Eg = (float)sc.lights[j].E[1], Eb = (float)sc.lights[j].E[2];
             dr = __fmaf_rn(Er, wd, dr); dg = __fmaf_rn(Eg, wd, dg); db = __fmaf_rn(Eb, wd, db);
@@ -294,18 +309,54 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
                 }
             }
         }
-        // localLight = color * diffuse + specular * material.specular; finalLight += localLight (transparency = 0), RE/Scene.h:126-128,171-173
-        ar = __fmaf_rn(w, __fmaf_rn((float)M.color[0], dr, sr * m_spec), ar);
-        ag = __fmaf_rn(w, __fmaf_rn((float)M.color[1], dg, sg * m_spec), ag);
-        ab = __fmaf_rn(w, __fmaf_rn((float)M.color[2], db, sb * m_spec), ab);
-        // ---- reflection, RE/Scene.h:189-195: reflectiveness = material.specular > bias;
-        // reflectDir = incoming.reflect(normal).normalize(); reflectRay = {hitPoint + reflectDir * bias, reflectDir}
-        if (!(M.specular > bias64)) { live = false; continue; }
-        const d3 R = normalize(reflect(incoming, N));
-        o = Pn + R * bias64;
-        d = R;
-        w *= m_spec;
-        if (w < kRrCutWeight) live = false;
+        // localLight = color * diffuse + specular * material.specular; finalLight += localLight * (1 - transparency), RE/Scene.h:126-128,171-173
+        const double transparency = kTree ? std_clamp(M.transparency, 0.0, 1.0) : 0.0;
+        const float wl = kTree ? w * (float)(1.0 - transparency) : w;
+        if (!kTree || transparency < 1.0) {
+            ar = __fmaf_rn(wl, __fmaf_rn((float)M.color[0], dr, sr * m_spec), ar);
+            ag = __fmaf_rn(wl, __fmaf_rn((float)M.color[1], dg, sg * m_spec), ag);
+            ab = __fmaf_rn(wl, __fmaf_rn((float)M.color[2], db, sb * m_spec), ab);
+        }
+        // ---- the children, RE/Scene.h:161-195: the refracted ray of a transparent material with weight transparency * (1 - fresnel),
+        // the reflected ray with weight fresnel (transparent) or material.specular, when that exceeds bias — rays and decisions in
+        // the reference's FP64 (Vec3::refract, Scene::fresnel with pow() like the exact kernel)
+        bool has_t = false;
+        d3 to = o, td = d;
+        float wt = 0.0f;
+        double reflectiveness = M.specular;
+        if (kTree && transparency > 0.0) {
+            const double cosTheta = std_max(0.0, dot(N, -incoming));
+            const double etaT = M.refractive_index;
+            const double f0 = pow((etaT - 1.0) / (etaT + 1.0), 2.0);
+            double fresnelAmount = f0 + (1.0 - f0) * pow(1.0 - cosTheta, 5.0);  // Scene::fresnel, RE/Scene.h:26-28
+            const double eta = front ? (1.0 / etaT) : (etaT / 1.0);
+            d3 rd = refract(incoming, N, eta);
+            if (length(rd) > bias64) {
+                rd = normalize(rd);
+                to = Pn + rd * (bias64 * 1e2); td = rd;
+                wt = w * (float)(transparency * (1.0 - fresnelAmount));
+                has_t = wt >= kRrCutWeight;
+            } else {
+                fresnelAmount = 1.0;  // total internal reflection
+            }
+            reflectiveness = fresnelAmount;
+        }
+        bool has_r = reflectiveness > bias64;
+        const float wr = w * (float)reflectiveness;
+        has_r = has_r && wr >= kRrCutWeight;
+        depth = node_depth + 1;
+        if (has_r) {
+            const d3 R = normalize(reflect(incoming, N));  // reflectDir = incoming.reflect(normal).normalize(); origin hitPoint + reflectDir * bias
+            const d3 ro = Pn + R * bias64;
+            if (kTree && has_t) {  // the reflected ray waits on the stack, the refracted one is traced next
+                stk[sp].o = ro; stk[sp].d = R; stk[sp].w = wr; stk[sp].depth = depth; ++sp;
+                o = to; d = td; w = wt;
+            } else { o = ro; d = R; w = wr; }
+        } else if (kTree && has_t) {
+            o = to; d = td; w = wt;
+        } else {
+            live = false;
+        }
     }
     out.r = ar; out.g = ag; out.b = ab;
     return ok || !alive;
@@ -315,6 +366,7 @@ __device__ __forceinline__ bool trace32r(const RenderParams& P, const SceneRr& S
 // Persistent CTAs, one 8 x 4 pixel tile per warp at a time (first tile by position, then a global counter), one pixel per lane.
 constexpr int kRrTileW = 8, kRrTileH = 4;
 
+template <bool kTree>
 __global__ void __launch_bounds__(kRrThreads, 2) render32r_kernel(const __grid_constant__ RenderParams P) {
     __shared__ SceneRr S;
     __shared__ unsigned long long s_stats[kRrThreads / 32][kStatCount];
@@ -404,7 +456,7 @@ __global__ void __launch_bounds__(kRrThreads, 2) render32r_kernel(const __grid_c
 #pragma unroll 1
         for (int s = 0; s < aa; ++s) {
             PxR o;
-            ok = trace32r(P, S, px, py, inb && ok, s, o) && ok;
+            ok = trace32r<kTree>(P, S, px, py, inb && ok, s, o) && ok;
             cr += o.r; cg += o.g; cb += o.b;
             n_shadow += o.c_shadow; n_sec += o.c_secondary; n_sph += o.c_sph; n_pl += o.c_pl; n_tri += o.c_tri;
             if (s == 0) { prim = o.prim; lmask = o.lmask; }
@@ -456,11 +508,11 @@ __global__ void __launch_bounds__(kRrThreads, 2) render32r_kernel(const __grid_c
     if (lane < kStatCount && s_stats[warp][lane]) atomicAdd(&P.stats[lane], s_stats[warp][lane]);
 }
 
-// Can this render call take the reflective FP32 path?  Opaque materials only (a transparent one makes TraceRay a tree), few
+// Can this render call take the reflective FP32 path?  Specular and / or transparent materials, few
 // primitives (every ray tests all of them), outputs hdr / rgb8 / prim_id / light_mask, no validation switches.
 bool fp32r_path_eligible(const RenderParams& p) {
     const rte_frame& f = p.out;
-    return p.sc.reflective && !p.sc.transparent && p.sc.ns <= kRrPrims && p.sc.nt <= kRrPrims && p.sc.ns + p.sc.nt <= kRrPrims && p.sc.ns + p.sc.nt + p.sc.np > 0 &&
+    return p.sc.reflective && p.sc.ns <= kRrPrims && p.sc.nt <= kRrPrims && p.sc.ns + p.sc.nt <= kRrPrims && p.sc.ns + p.sc.nt + p.sc.np > 0 &&
            p.sc.np <= kRrPlanes && p.sc.nl <= kRrLights && !p.exact_shadows && !p.no_filter && !p.force_general && !p.no_cull && p.pass_mode == 0 &&
            !p.exact_fp64 && !p.exact_grid && !f.hdr64 && !f.depth && !f.depth64 && !f.depth_norm && !f.normal && !f.albedo && p.bias >= 1e-6 && p.bias <= 1e-1;
 }
@@ -470,7 +522,8 @@ cudaError_t launch_render32r(const RenderParams& p, int sm_count, cudaStream_t s
     long long blocks = (long long)sm_count * 2;
     const long long needed = (n_tiles + kRrThreads / 32 - 1) / (kRrThreads / 32);
     if (blocks > needed) blocks = needed > 0 ? needed : 1;
-    render32r_kernel<<<(unsigned)blocks, kRrThreads, 0, stream>>>(p);
+    if (p.sc.transparent) render32r_kernel<true><<<(unsigned)blocks, kRrThreads, 0, stream>>>(p);  // refraction: TraceRay is a tree
+    else render32r_kernel<false><<<(unsigned)blocks, kRrThreads, 0, stream>>>(p);
     return cudaGetLastError();
 }
 

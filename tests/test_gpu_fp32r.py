@@ -31,6 +31,8 @@ CASES = {
     "c1_square": lambda: scenes.config1(160, 160),
     "c4_specular": lambda: scenes.config4("box", scale=0.12, specular=True),
     "mirror_room": lambda: mirror_room(200, 120),
+    "glass": lambda: scenes.glass_scene(160, 120),        # refraction, Fresnel, total internal reflection, transparent occluders: TraceRay is a tree
+    "glass_small": lambda: scenes.glass_scene(61, 47),
 }
 
 
@@ -50,7 +52,7 @@ def test_reflective_fp32_path_against_exact_path(engine, case):
     assert d.max() <= 1, f"{np.count_nonzero(d > 1)} bytes differ by more than 1 LSB (max {d.max()})"
     np.testing.assert_allclose(fast["hdr"][:, :3], exact["hdr"][:, :3], rtol=2e-4, atol=2e-4)
     assert sf["primary_rays"] == se["primary_rays"] == n_px
-    for k in ("shadow_rays", "secondary_rays"):  # (chains end below a weight of 1e-7: the production path traces fewer rays than the reference)
+    for k in ("shadow_rays", "secondary_rays"):  # (branches end below a weight of 1e-7: the production path traces fewer rays than the reference)
         assert 0 < sf[k] <= se[k], f"counter {k}: fp32 path {sf[k]}, exact path {se[k]}"
     frac = sf["fp64_confirms"] / n_px
     print(f"{case}: {100 * frac:.1f} % of the pixels in flagged tiles; kernel {sf['kernel_ms']:.3f} ms vs exact {se['kernel_ms']:.3f} ms")

@@ -32,6 +32,11 @@ def random_scene(seed, reflective):
         mats[i] = scenes._material(tuple(rng.uniform(0.1, 1.0, 3)), float(rng.choice([0.5, 8.0, 64.0, 200.0])), spec, 0.0, 1.5)
     if reflective:
         mats[0]["specular"] = 0.5
+        if seed % 3 == 0:  # every third reflective scene has glass: refraction, Fresnel, transparent occluders
+            mats[1]["transparency"] = 0.9
+            mats[1]["refractive_index"] = 1.5
+            mats[2]["transparency"] = float(rng.choice([0.3, 0.6, 1.0]))
+            mats[2]["refractive_index"] = float(rng.choice([1.1, 1.33, 2.0]))
     spheres = np.zeros(ns, dtype=_abi.sphere_dt)
     for i in range(ns):
         r = float(np.float32(rng.choice([0.3, 1.0, 2.5, 6.0, 40.0], p=[0.2, 0.35, 0.3, 0.12, 0.03])))
