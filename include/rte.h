@@ -179,7 +179,7 @@ typedef struct rte_render_opts {
  *                  only, on a diffuse scene (spheres, planes, triangles, models), is shaded in FP32 (hit index and shadow visibility bit-exact — every
  *                  FP32 decision is certain within its error bound or the pixel is re-rendered in FP64 —, HDR to ~1e-6 relative,
  *                  RGB8 within +-1 LSB of the reference: the bars BASELINE.json states).  The same holds for scenes with
- *                  specular (reflecting) or transparent (refracting) materials and at most 64 spheres + triangles — main()'s
+ *                  specular (reflecting) or transparent (refracting) materials and at most 32 spheres + triangles — main()'s
  *                  scene —: their chains / trees of secondary rays end once the path weight is below 1e-7, so
  *                  rte_stats counts fewer secondary / shadow rays than the reference traces.  Every FP64 output (hdr64,
  *                  depth64), the other AOVs and every flag above select the exact FP64 path, whose results are the

@@ -31,6 +31,7 @@ CASES = {
     "c1_square": lambda: scenes.config1(160, 160),
     "c4_specular": lambda: scenes.config4("box", scale=0.12, specular=True),
     "mirror_room": lambda: mirror_room(200, 120),
+    "mirror_room_28": lambda: mirror_room(200, 120, n_spheres=28, seed=5),   # near the limit of 32 primitives
     "glass": lambda: scenes.glass_scene(160, 120),        # refraction, Fresnel, total internal reflection, transparent occluders: TraceRay is a tree
     "glass_small": lambda: scenes.glass_scene(61, 47),
 }

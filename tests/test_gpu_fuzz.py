@@ -19,8 +19,8 @@ def random_scene(seed, reflective):
     W, H = int(rng.integers(40, 120)), int(rng.integers(30, 90))
     cam = scenes.Camera(tuple(rng.uniform(-3, 3, 3) + np.array([0, 0, -30.0])), float(rng.uniform(0.4, 1.2) * W), W, H, 0.0, 300.0)
     cam.antiAliasingAmount = 1
-    ns = int(rng.integers(0, 24 if reflective else 60))
-    nt = int(rng.integers(0, 20 if reflective else 40))
+    ns = int(rng.integers(0, 18 if reflective else 60))
+    nt = int(rng.integers(0, 14 if reflective else 40))
     if ns + nt == 0:
         ns = 3
     n_pl = int(rng.integers(1, 6))
