@@ -679,6 +679,8 @@ def run_gpu(args) -> None:
                                   "the bounded hardware figures are issue_active_pct / pipe_*_pct below (ncu)",
                      "algorithmic_tflops": round(achieved_tf, 3), "algorithmic_flop_per_launch": flops / world,
                      "traffic": r32.get("dram_bytes"), "kernel_ms": round(m["kernel_ms_max"], 4), "kernel_ms_min_rank": round(m["kernel_ms_min"], 4),
+                     "frac_hardware": (round(r32["issue_active_pct"] / 100.0, 4) if r32.get("issue_active_pct") else None),
+                     "frac_hardware_note": "bounded figure: share of the SM's issue slots the kernel used (ncu smsp__issue_active, committed capture) — the kernel is issue-bound, not FMA-bound",
                      "issue_active_pct": r32.get("issue_active_pct"), "pipe_fma_pct": r32.get("pipe_fma_pct"), "pipe_fp64_pct": r32.get("pipe_fp64_pct"),
                      "pipe_alu_pct": r32.get("pipe_alu_pct"), "pipe_xu_pct": r32.get("pipe_xu_pct"), "ncu_kernels": kern, "ncu_source": kern_src,
                      "peak_source": "FFMA micro-benchmark in this process (rte_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
